@@ -1,0 +1,152 @@
+/* linearham_b200 - device C ABI for the phylo-HMM likelihood hot path.
+ *
+ * This is the drop-in boundary. The reference (matsengrp/linearham) has no FFI
+ * for this path: its boundary is the C++ call sequence inside the RunPipeline
+ * loop body,  src/PhyloHMM.cpp:419-430
+ *
+ *     InitializePhyloEmission();          // src/PhyloHMM.cpp:366-383
+ *     lh_loglikelihood_ = LogLikelihood();// src/HMM.cpp:345-354
+ *
+ * executed once per (tree, er, pi, alpha) sample on a fixed clonal family.
+ * The functions below replace that pair for B samples at a time; the host-side
+ * PhyloHMM class of this repo (linearham_b200/csrc/host) calls nothing else.
+ *
+ * Conventions
+ *   - plain C, host pointers unless a name ends in _dev; no torch / Eigen types
+ *   - every call returns 0 on success, non-zero on failure; lh_last_error()
+ *     then returns a thread-local message (the reference throws C++ exceptions
+ *     caught in main(), src/linearham.cpp:447-454)
+ *   - a handle is single-threaded; different handles may be used concurrently
+ *   - there is NO CPU fallback: without a CUDA device lh_family_create fails
+ *   - FP64 end to end; bases are 0..4 = A,C,G,T,N (src/HMM.cpp:50)
+ */
+#ifndef LINEARHAM_B200_H_
+#define LINEARHAM_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LH_MAX_RATES 8
+
+typedef struct lh_family lh_family_t;
+
+/* Per-family constants; replaces what PhyloHMM::InitializeXmsaStructs
+ * (src/PhyloHMM.cpp:45-89), HMM::InitializeStateSpace/InitializeTransition
+ * (src/HMM.cpp:94-246) and pt::pll::Partition::SetTipStates
+ * (lib/libptpll/src/pll_partition.cpp:153-194) leave in host objects.
+ * Matrices are dense column-major exactly as the reference's Eigen::MatrixXd /
+ * MatrixXi members; the library builds its own sparse device forms.           */
+typedef struct lh_family_desc {
+  int32_t n_tips;            /* T = sequences + 1; row 0 is "naive"           */
+  int32_t n_sites;           /* S_x = xMSA columns                            */
+  const uint8_t* tip_codes;  /* [T][S_x] row-major, xmsa_ (PhyloHMM.hpp:27)   */
+
+  int32_t has_d;             /* 1 = igh (7 regions), 0 = igk/igl (5 regions)  */
+  int32_t n_v, n_d, n_j;     /* germline states per region (= genes)          */
+  int32_t vd_sites, vd_states; /* V-D (or V-J) junction: L x S                */
+  int32_t dj_sites, dj_states; /* D-J junction; 0 x 0 when !has_d             */
+
+  /* germline / padding regions: CSR lists of xMSA columns per gene, gene order
+   * = std::map order of *_ggene_ranges_ (src/PhyloHMM.cpp:158-193)           */
+  const int32_t* vpad_off;  const int32_t* vpad_inds;   /* off[n_v+1]         */
+  const int32_t* vgerm_off; const int32_t* vgerm_inds;  /* off[n_v+1]         */
+  const int32_t* dgerm_off; const int32_t* dgerm_inds;  /* off[n_d+1]         */
+  const int32_t* jgerm_off; const int32_t* jgerm_inds;  /* off[n_j+1]         */
+  const int32_t* jpad_off;  const int32_t* jpad_inds;   /* off[n_j+1]         */
+
+  /* junction xMSA index matrices, column-major [sites x states], -1 = no
+   * emission (src/PhyloHMM.cpp:202-215, 489-513)                             */
+  const int32_t* vd_inds;
+  const int32_t* dj_inds;
+
+  /* V-germline start terms (src/HMM.cpp:307-314)                             */
+  const double* v_gene_prob;   /* [n_v] germ_ptr->gene_prob()                 */
+  const double* v_trans_prod;  /* [n_v] prod of in-region germline transitions*/
+  const double* vpad_trans;    /* [n_v] vpadding_transition_                  */
+  const double* jpad_trans;    /* [n_j] jpadding_transition_                  */
+
+  /* transition matrices, column-major (src/HMM.hpp transition members)       */
+  const double* t_v_vd;   /* [n_v x vd_states]       vgerm_vd_junction_       */
+  const double* t_vd;     /* [vd_states x vd_states] vd_junction_             */
+  const double* t_vd_d;   /* [vd_states x n_d] (n_j when !has_d) vd_junction_dgerm_ */
+  const double* t_d_dj;   /* [n_d x dj_states]       dgerm_dj_junction_       */
+  const double* t_dj;     /* [dj_states x dj_states] dj_junction_             */
+  const double* t_dj_j;   /* [dj_states x n_j]       dj_junction_jgerm_       */
+} lh_family_desc_t;
+
+/* B tree samples in structure-of-arrays form; replaces pll_utree_t +
+ * pll_operation_t (libpll pll.h:249-259, 312-334) and pt::pll::Model
+ * (lib/libptpll/src/model.hpp:10-16).
+ * Node ids: tips 0..T-1 are rows of tip_codes; inner node T+i is produced by
+ * operation i. Operations are in any valid post-order (children before
+ * parents); operation T-3 is the virtual root (pll_util.cpp:368-371), whose
+ * remaining neighbour across the evaluated edge is root_child.               */
+typedef struct lh_tree_batch {
+  int32_t n_trees;            /* B                                            */
+  int32_t n_rates;            /* R, 1..LH_MAX_RATES                           */
+  const int32_t* children;    /* [B][T-2][2]                                  */
+  const double*  blen;        /* [B][T-2][2] branch above each child          */
+  const int32_t* root_child;  /* [B]                                          */
+  const double*  root_blen;   /* [B]                                          */
+  const double*  er;          /* [B][6] AC AG AT CG CT GT (models.c:225-237)  */
+  const double*  pi;          /* [B][4] A C G T                               */
+  const double*  rates;       /* [B][R] discrete-Gamma category rates         */
+} lh_tree_batch_t;
+
+/* Optional per-tree read-outs (any pointer may be NULL). What the reference
+ * exposes through accessors after LogLikelihood(): xmsa_emission()
+ * (PhyloHMM.hpp:31), the forward tables and scaler counts (HMM.hpp forward
+ * members) needed by SampleNaiveSequence (src/HMM.cpp:358-431).
+ * Junction tables are column-major [sites x states] per tree.                */
+typedef struct lh_outputs {
+  double*  xmsa_emission;   /* [B][S_x]                                       */
+  double*  vgerm_forward;   /* [B][n_v]                                       */
+  double*  vd_forward;      /* [B][vd_sites*vd_states]                        */
+  double*  dgerm_forward;   /* [B][n_d]                                       */
+  double*  dj_forward;      /* [B][dj_sites*dj_states]                        */
+  double*  jgerm_forward;   /* [B][n_j]                                       */
+  int32_t* germ_scalers;    /* [B][3] vgerm, dgerm, jgerm scaler counts       */
+  int32_t* vd_scalers;      /* [B][vd_sites]                                  */
+  int32_t* dj_scalers;      /* [B][dj_sites]                                  */
+} lh_outputs_t;
+
+typedef struct lh_timings {
+  float ms_h2d, ms_plan, ms_pmatrix, ms_prune, ms_hmm, ms_d2h, ms_total;
+  int32_t n_trees;
+  int32_t kernel_launches;   /* launches of this library's kernels            */
+  int64_t h2d_bytes, d2h_bytes;
+  int32_t prune_slots;       /* CLV stack depth the batch needed              */
+  int32_t prune_tile_sites;  /* xMSA columns per CTA                          */
+} lh_timings_t;
+
+const char* lh_last_error(void);
+const char* lh_version(void);
+int lh_device_count(int* n);
+
+int  lh_family_create(lh_family_t** out, const lh_family_desc_t* desc, int device);
+void lh_family_destroy(lh_family_t* fam);
+
+/* Score B samples: host buffers in, host log-likelihoods out (synchronous).
+ * Includes the host->device and device->host copies.                         */
+int lh_score_batch(lh_family_t* fam, const lh_tree_batch_t* trees,
+                   double* loglik /* [B] */, lh_outputs_t* opt /* or NULL */);
+
+/* Split form for callers that keep a batch resident (bench `value`, pipelining):
+ * upload once, run any number of times, fetch.                               */
+int lh_batch_upload(lh_family_t* fam, const lh_tree_batch_t* trees);
+int lh_batch_run(lh_family_t* fam);                  /* async on the family stream */
+int lh_batch_fetch(lh_family_t* fam, double* loglik, lh_outputs_t* opt); /* syncs */
+int lh_sync(lh_family_t* fam);
+int lh_loglik_dev(lh_family_t* fam, const double** loglik_dev, int32_t* n); /* device ptr of the last run */
+
+int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/score */
+int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
+/* keys: "tile_sites" (0 = auto), "smem_slots" (-1 = auto), "timing" (0/1)    */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LINEARHAM_B200_H_ */

@@ -1,0 +1,173 @@
+"""ctypes mirror of include/linearham_b200.h (the device C ABI).
+
+Only struct layouts, argument marshalling and the library loader live here; no
+arithmetic. The structs are also what the oracle port (oracle/port) consumes in
+the tests, so that the CUDA path and the checker see byte-identical inputs.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblinearham_b200.so")
+
+LH_MAX_RATES = 8
+
+_i32p = C.POINTER(C.c_int32)
+_f64p = C.POINTER(C.c_double)
+_u8p = C.POINTER(C.c_uint8)
+
+
+class FamilyDesc(C.Structure):
+    _fields_ = [
+        ("n_tips", C.c_int32), ("n_sites", C.c_int32), ("tip_codes", _u8p),
+        ("has_d", C.c_int32), ("n_v", C.c_int32), ("n_d", C.c_int32), ("n_j", C.c_int32),
+        ("vd_sites", C.c_int32), ("vd_states", C.c_int32),
+        ("dj_sites", C.c_int32), ("dj_states", C.c_int32),
+        ("vpad_off", _i32p), ("vpad_inds", _i32p),
+        ("vgerm_off", _i32p), ("vgerm_inds", _i32p),
+        ("dgerm_off", _i32p), ("dgerm_inds", _i32p),
+        ("jgerm_off", _i32p), ("jgerm_inds", _i32p),
+        ("jpad_off", _i32p), ("jpad_inds", _i32p),
+        ("vd_inds", _i32p), ("dj_inds", _i32p),
+        ("v_gene_prob", _f64p), ("v_trans_prod", _f64p),
+        ("vpad_trans", _f64p), ("jpad_trans", _f64p),
+        ("t_v_vd", _f64p), ("t_vd", _f64p), ("t_vd_d", _f64p),
+        ("t_d_dj", _f64p), ("t_dj", _f64p), ("t_dj_j", _f64p),
+    ]
+
+
+class TreeBatch(C.Structure):
+    _fields_ = [
+        ("n_trees", C.c_int32), ("n_rates", C.c_int32),
+        ("children", _i32p), ("blen", _f64p),
+        ("root_child", _i32p), ("root_blen", _f64p),
+        ("er", _f64p), ("pi", _f64p), ("rates", _f64p),
+    ]
+
+
+class Outputs(C.Structure):
+    _fields_ = [
+        ("xmsa_emission", _f64p), ("vgerm_forward", _f64p), ("vd_forward", _f64p),
+        ("dgerm_forward", _f64p), ("dj_forward", _f64p), ("jgerm_forward", _f64p),
+        ("germ_scalers", _i32p), ("vd_scalers", _i32p), ("dj_scalers", _i32p),
+    ]
+
+
+class Timings(C.Structure):
+    _fields_ = [
+        ("ms_h2d", C.c_float), ("ms_plan", C.c_float), ("ms_pmatrix", C.c_float),
+        ("ms_prune", C.c_float), ("ms_hmm", C.c_float), ("ms_d2h", C.c_float),
+        ("ms_total", C.c_float), ("n_trees", C.c_int32), ("kernel_launches", C.c_int32),
+        ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
+        ("prune_slots", C.c_int32), ("prune_tile_sites", C.c_int32),
+    ]
+
+
+_FAMILY_ARRAYS = {  # field -> dtype
+    "tip_codes": np.uint8,
+    "vpad_off": np.int32, "vpad_inds": np.int32, "vgerm_off": np.int32, "vgerm_inds": np.int32,
+    "dgerm_off": np.int32, "dgerm_inds": np.int32, "jgerm_off": np.int32, "jgerm_inds": np.int32,
+    "jpad_off": np.int32, "jpad_inds": np.int32, "vd_inds": np.int32, "dj_inds": np.int32,
+    "v_gene_prob": np.float64, "v_trans_prod": np.float64, "vpad_trans": np.float64,
+    "jpad_trans": np.float64, "t_v_vd": np.float64, "t_vd": np.float64, "t_vd_d": np.float64,
+    "t_d_dj": np.float64, "t_dj": np.float64, "t_dj_j": np.float64,
+}
+_FAMILY_SCALARS = ["n_tips", "n_sites", "has_d", "n_v", "n_d", "n_j",
+                   "vd_sites", "vd_states", "dj_sites", "dj_states"]
+_TREE_ARRAYS = {"children": np.int32, "blen": np.float64, "root_child": np.int32,
+                "root_blen": np.float64, "er": np.float64, "pi": np.float64, "rates": np.float64}
+
+
+def _ptr(a, ctype):
+    return a.ctypes.data_as(C.POINTER(ctype))
+
+
+_CT = {np.uint8: C.c_uint8, np.int32: C.c_int32, np.float64: C.c_double}
+
+
+def family_desc(fam):
+    """dict of numpy arrays / ints (see FamilyDesc) -> (FamilyDesc, keepalive list)."""
+    d = FamilyDesc()
+    keep = []
+    for k in _FAMILY_SCALARS:
+        setattr(d, k, int(fam[k]))
+    for k, dt in _FAMILY_ARRAYS.items():
+        a = np.ascontiguousarray(np.asarray(fam[k]).reshape(-1), dtype=dt)
+        if a.size == 0:
+            a = np.zeros(1, dtype=dt)
+        keep.append(a)
+        setattr(d, k, _ptr(a, _CT[dt]))
+    return d, keep
+
+
+def tree_batch(tb):
+    """dict with children[B,T-2,2], blen[B,T-2,2], root_child[B], root_blen[B],
+    er[B,6], pi[B,4], rates[B,R] -> (TreeBatch, keepalive)."""
+    t = TreeBatch()
+    keep = []
+    rates = np.asarray(tb["rates"], dtype=np.float64)
+    t.n_trees = int(np.asarray(tb["root_child"]).shape[0])
+    t.n_rates = int(rates.shape[1])
+    for k, dt in _TREE_ARRAYS.items():
+        a = np.ascontiguousarray(np.asarray(tb[k]).reshape(-1), dtype=dt)
+        keep.append(a)
+        setattr(t, k, _ptr(a, _CT[dt]))
+    return t, keep
+
+
+def alloc_outputs(fam, B, fields=None):
+    """Allocate numpy buffers for lh_outputs_t; returns (Outputs, dict of arrays)."""
+    shapes = {
+        "xmsa_emission": ((B, fam["n_sites"]), np.float64),
+        "vgerm_forward": ((B, fam["n_v"]), np.float64),
+        "vd_forward": ((B, fam["vd_sites"] * fam["vd_states"]), np.float64),
+        "dgerm_forward": ((B, max(fam["n_d"], 1)), np.float64),
+        "dj_forward": ((B, max(fam["dj_sites"] * fam["dj_states"], 1)), np.float64),
+        "jgerm_forward": ((B, fam["n_j"]), np.float64),
+        "germ_scalers": ((B, 3), np.int32),
+        "vd_scalers": ((B, fam["vd_sites"]), np.int32),
+        "dj_scalers": ((B, max(fam["dj_sites"], 1)), np.int32),
+    }
+    o = Outputs()
+    arrs = {}
+    for k, (shape, dt) in shapes.items():
+        if fields is not None and k not in fields:
+            continue
+        a = np.zeros(shape, dtype=dt)
+        arrs[k] = a
+        setattr(o, k, _ptr(a, _CT[dt]))
+    return o, arrs
+
+
+DEVICE_SYMBOLS = [
+    "lh_last_error", "lh_version", "lh_device_count", "lh_family_create", "lh_family_destroy",
+    "lh_score_batch", "lh_batch_upload", "lh_batch_run", "lh_batch_fetch", "lh_sync",
+    "lh_loglik_dev", "lh_get_timings", "lh_set_option",
+]
+
+
+def load_library(path=None):
+    """Load the CUDA library. Fails loudly: there is no fallback implementation."""
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise RuntimeError(
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). linearham_b200 has no CPU fallback.")
+    lib = C.CDLL(path)
+    lib.lh_last_error.restype = C.c_char_p
+    lib.lh_version.restype = C.c_char_p
+    lib.lh_device_count.argtypes = [C.POINTER(C.c_int)]
+    lib.lh_family_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(FamilyDesc), C.c_int]
+    lib.lh_family_destroy.argtypes = [C.c_void_p]
+    lib.lh_family_destroy.restype = None
+    lib.lh_score_batch.argtypes = [C.c_void_p, C.POINTER(TreeBatch), _f64p, C.POINTER(Outputs)]
+    lib.lh_batch_upload.argtypes = [C.c_void_p, C.POINTER(TreeBatch)]
+    lib.lh_batch_run.argtypes = [C.c_void_p]
+    lib.lh_batch_fetch.argtypes = [C.c_void_p, _f64p, C.POINTER(Outputs)]
+    lib.lh_sync.argtypes = [C.c_void_p]
+    lib.lh_loglik_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int32)]
+    lib.lh_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
+    lib.lh_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
+    return lib

@@ -211,9 +211,9 @@ int ref_get_f64(void* h, const char* name, double* out, int* rows, int* cols) {
   if (n == "sr") { vec(p.sr_); return 0; }
   if (n == "er") { vec(p.er_); return 0; }
   if (n == "pi") { vec(p.pi_); return 0; }
-  // per-V-gene prefactor gene_prob * prod(transition segment) used by
-  // ComputeInitialForwardProbabilities (src/HMM.cpp:304-313)
-  if (n == "vgerm_init_prefactor") {
+  // per-V-gene start factors used by ComputeInitialForwardProbabilities
+  // (src/HMM.cpp:304-313): gene_prob and prod(transition segment)
+  if (n == "vgerm_gene_prob" || n == "vgerm_trans_prod") {
     *rows = 1; *cols = (int)p.vgerm_ggene_ranges_.size();
     if (out) {
       int i = 0;
@@ -221,7 +221,8 @@ int ref_get_f64(void* h, const char* name, double* out, int* rows, int* cols) {
         const auto& g = p.ggenes_.at(kv.first);
         int s = p.vgerm_germ_inds_[kv.second.first];
         int len = kv.second.second - kv.second.first - 1;
-        out[i++] = g.germ_ptr->gene_prob() * g.germ_ptr->transition().segment(s, len).prod();
+        out[i++] = (n == "vgerm_gene_prob") ? g.germ_ptr->gene_prob()
+                                            : g.germ_ptr->transition().segment(s, len).prod();
       }
     }
     return 0;
