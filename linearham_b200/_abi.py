@@ -1,8 +1,8 @@
 """ctypes mirror of include/linearham_b200.h (the device C ABI).
 
 Only struct layouts, argument marshalling and the library loader live here; no
-arithmetic. The structs are also what the oracle port (oracle/port) consumes in
-the tests, so that the CUDA path and the checker see byte-identical inputs.
+arithmetic. The tests hand the same structs to their CPU checker, so that the CUDA path and
+the checker see byte-identical inputs.
 """
 import ctypes as C
 import os

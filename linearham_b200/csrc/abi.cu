@@ -1,0 +1,550 @@
+// C ABI of include/linearham_b200.h: device memory management, host-side planning,
+// stream orchestration. No arithmetic of the likelihood path lives here except the two
+// libm constants log(2^256) / log(2^-256) the reference also takes from the host libm.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/linearham_b200.h"
+#include "kernels.hpp"
+#include "plan.hpp"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+
+#define LH_CUDA(expr)                                                                    \
+  do {                                                                                   \
+    cudaError_t e_ = (expr);                                                             \
+    if (e_ != cudaSuccess)                                                               \
+      return fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+// growable device / pinned-host buffers
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 4;
+    LH_CUDA(cudaMalloc(&p, want));
+    cap = want;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 4;
+    LH_CUDA(cudaMallocHost(&p, want));
+    cap = want;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+template <class T>
+int upload(const T* src, size_t n, const T** dst, std::vector<void*>& owned) {
+  void* d = nullptr;
+  size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+  LH_CUDA(cudaMalloc(&d, bytes));
+  owned.push_back(d);
+  if (n) LH_CUDA(cudaMemcpy(d, src, n * sizeof(T), cudaMemcpyHostToDevice));
+  *dst = reinterpret_cast<const T*>(d);
+  return 0;
+}
+
+// dense column-major [rows x cols] -> CSC on the device (rows ascending inside a column,
+// i.e. the order of the reference's dense dot product with the zero terms dropped)
+int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, std::vector<void*>& owned) {
+  std::vector<int32_t> colptr(cols + 1, 0), row;
+  std::vector<double> val;
+  for (int j = 0; j < cols; ++j) {
+    for (int i = 0; i < rows; ++i) {
+      double v = dense[(size_t)j * rows + i];
+      if (v != 0.0) {
+        row.push_back(i);
+        val.push_back(v);
+      }
+    }
+    colptr[j + 1] = (int32_t)row.size();
+  }
+  out->rows = rows;
+  out->cols = cols;
+  if (upload(colptr.data(), colptr.size(), &out->colptr, owned)) return 1;
+  if (upload(row.data(), row.size(), &out->row, owned)) return 1;
+  if (upload(val.data(), val.size(), &out->val, owned)) return 1;
+  return 0;
+}
+
+}  // namespace
+
+struct lh_family {
+  int device = 0;
+  int num_sms = 148;
+  cudaStream_t stream = nullptr;
+  lhb::FamilyDev fd{};
+  std::vector<void*> owned;  // family-constant device allocations
+  // options
+  int opt_tile_sites = 0, opt_smem_slots = -1, opt_timing = 1, opt_threads = 0;
+  size_t opt_chunk_bytes = 48u << 20;
+  // batch state
+  int B = 0, R = 0, slots = 0;
+  DevBuf d_plan, d_pblen, d_er, d_pi, d_rates, d_eig, d_prec, d_xe, d_loglik, d_scratch, d_scratch_cnt;
+  DevBuf d_vgerm, d_vd, d_dgerm, d_dj, d_jgerm, d_gs, d_vds, d_djs;
+  PinBuf h_plan, h_pblen, h_misc, h_out;
+  cudaEvent_t ev[8] = {};
+  lh_timings_t tm{};
+  bool want_tables = false;
+};
+
+extern "C" {
+
+const char* lh_last_error(void) { return g_err.c_str(); }
+const char* lh_version(void) { return "linearham_b200 0.1 (sm_100a)"; }
+
+int lh_device_count(int* n) {
+  *n = 0;
+  LH_CUDA(cudaGetDeviceCount(n));
+  return 0;
+}
+
+void lh_family_destroy(lh_family_t* f) {
+  if (!f) return;
+  cudaSetDevice(f->device);
+  if (f->stream) cudaStreamSynchronize(f->stream);
+  for (void* p : f->owned) cudaFree(p);
+  DevBuf* bufs[] = {&f->d_plan, &f->d_pblen, &f->d_er, &f->d_pi, &f->d_rates, &f->d_eig, &f->d_prec,
+                    &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
+                    &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs};
+  for (DevBuf* b : bufs) b->release();
+  f->h_plan.release();
+  f->h_pblen.release();
+  f->h_misc.release();
+  f->h_out.release();
+  for (auto& e : f->ev)
+    if (e) cudaEventDestroy(e);
+  if (f->stream) cudaStreamDestroy(f->stream);
+  delete f;
+}
+
+int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
+  *out = nullptr;
+  if (!d) return fail("null descriptor");
+  if (d->n_tips < 3) return fail("need at least 3 tips (got %d)", d->n_tips);
+  if (d->n_sites < 1) return fail("empty xMSA");
+  if (d->n_v < 1 || d->n_j < 1 || (d->has_d && d->n_d < 1)) return fail("empty germline region");
+  if (d->vd_sites < 1 || d->vd_states < 1 || (d->has_d && (d->dj_sites < 1 || d->dj_states < 1)))
+    return fail("empty junction region");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail("no CUDA device available (%s); linearham_b200 has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail("device %d out of range (0..%d)", device, ndev - 1);
+  LH_CUDA(cudaSetDevice(device));
+  lh_family* f = new lh_family;
+  f->device = device;
+  cudaDeviceGetAttribute(&f->num_sms, cudaDevAttrMultiProcessorCount, device);
+  auto bail = [&](int) { lh_family_destroy(f); return 1; };
+  if (cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail("cudaStreamCreate failed"));
+  for (auto& ev : f->ev) cudaEventCreate(&ev);
+
+  const int T = d->n_tips, S = d->n_sites;
+  for (size_t i = 0; i < (size_t)T * S; ++i)
+    if (d->tip_codes[i] > 4) return bail(fail("tip_codes[%zu] = %d is not in 0..4", i, d->tip_codes[i]));
+  lhb::FamilyDev& fd = f->fd;
+  fd.T = T;
+  fd.S = S;
+  fd.has_d = d->has_d ? 1 : 0;
+  fd.n_v = d->n_v;
+  fd.n_d = fd.has_d ? d->n_d : 0;
+  fd.n_j = d->n_j;
+  fd.vd_sites = d->vd_sites;
+  fd.vd_states = d->vd_states;
+  fd.dj_sites = fd.has_d ? d->dj_sites : 0;
+  fd.dj_states = fd.has_d ? d->dj_states : 0;
+  fd.g_max = std::max(fd.n_v, std::max(fd.n_d, fd.n_j));
+  fd.s_max = std::max(std::max(fd.vd_states, fd.dj_states), fd.g_max);
+  auto& own = f->owned;
+  int rc = 0;
+  rc |= upload(d->tip_codes, (size_t)T * S, &fd.tip_codes, own);
+  auto region = [&](int n, const int32_t* off, const int32_t* inds, const int32_t** doff,
+                    const int32_t** dinds, const char* name) {
+    if (n == 0) return upload(off, 0, doff, own) | upload(inds, 0, dinds, own);
+    for (int g = 0; g < n; ++g)
+      if (off[g + 1] < off[g]) return fail("%s offsets not monotone", name);
+    for (int j = off[0]; j < off[n]; ++j)
+      if (inds[j] < 0 || inds[j] >= S) return fail("%s xMSA index %d out of range", name, inds[j]);
+    if (off[0] != 0) return fail("%s offsets must start at 0", name);
+    return upload(off, n + 1, doff, own) | upload(inds, off[n], dinds, own);
+  };
+  rc |= region(fd.n_v, d->vpad_off, d->vpad_inds, &fd.vpad_off, &fd.vpad_inds, "vpad");
+  rc |= region(fd.n_v, d->vgerm_off, d->vgerm_inds, &fd.vgerm_off, &fd.vgerm_inds, "vgerm");
+  rc |= region(fd.n_d, d->dgerm_off, d->dgerm_inds, &fd.dgerm_off, &fd.dgerm_inds, "dgerm");
+  rc |= region(fd.n_j, d->jgerm_off, d->jgerm_inds, &fd.jgerm_off, &fd.jgerm_inds, "jgerm");
+  rc |= region(fd.n_j, d->jpad_off, d->jpad_inds, &fd.jpad_off, &fd.jpad_inds, "jpad");
+  if (rc) return bail(1);
+  auto junction = [&](const int32_t* cm, int L, int Sj, const int32_t** dst) {
+    std::vector<int32_t> rm((size_t)L * Sj);
+    for (int i = 0; i < L; ++i)
+      for (int j = 0; j < Sj; ++j) {
+        int32_t v = cm[(size_t)j * L + i];
+        if (v < -1 || v >= S) return fail("junction xMSA index %d out of range", v);
+        rm[(size_t)i * Sj + j] = v;
+      }
+    return upload(rm.data(), rm.size(), dst, own);
+  };
+  rc |= junction(d->vd_inds, fd.vd_sites, fd.vd_states, &fd.vd_inds_rm);
+  rc |= junction(d->dj_inds, fd.dj_sites, fd.dj_states, &fd.dj_inds_rm);
+  rc |= upload(d->v_gene_prob, fd.n_v, &fd.v_gene_prob, own);
+  rc |= upload(d->v_trans_prod, fd.n_v, &fd.v_trans_prod, own);
+  rc |= upload(d->vpad_trans, fd.n_v, &fd.vpad_trans, own);
+  rc |= upload(d->jpad_trans, fd.n_j, &fd.jpad_trans, own);
+  rc |= upload_csc(d->t_v_vd, fd.n_v, fd.vd_states, &fd.t_v_vd, own);
+  rc |= upload_csc(d->t_vd, fd.vd_states, fd.vd_states, &fd.t_vd, own);
+  rc |= upload_csc(d->t_vd_d, fd.vd_states, fd.has_d ? fd.n_d : fd.n_j, &fd.t_vd_d, own);
+  if (fd.has_d) {
+    rc |= upload_csc(d->t_d_dj, fd.n_d, fd.dj_states, &fd.t_d_dj, own);
+    rc |= upload_csc(d->t_dj, fd.dj_states, fd.dj_states, &fd.t_dj, own);
+    rc |= upload_csc(d->t_dj_j, fd.dj_states, fd.n_j, &fd.t_dj_j, own);
+  }
+  if (rc) return bail(1);
+  *out = f;
+  return 0;
+}
+
+int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
+  std::string k(key ? key : "");
+  if (k == "tile_sites") {
+    if (value != 0 && (value < 32 || value > 256 || value % 32)) return fail("tile_sites must be 0 or a multiple of 32 in 32..256");
+    f->opt_tile_sites = (int)value;
+  } else if (k == "smem_slots") {
+    f->opt_smem_slots = (int)value;
+  } else if (k == "timing") {
+    f->opt_timing = value != 0;
+  } else if (k == "host_threads") {
+    f->opt_threads = (int)value;
+  } else if (k == "chunk_bytes") {
+    f->opt_chunk_bytes = (size_t)value;
+  } else {
+    return fail("unknown option '%s'", k.c_str());
+  }
+  return 0;
+}
+
+}  // extern "C"
+
+namespace {
+
+int pick_tile_sites(int S) {
+  static const int cand[] = {128, 160, 192, 224, 256, 96, 64, 32};
+  int best = 128, best_waste = 1 << 30;
+  for (int w : cand) {
+    int waste = ((S + w - 1) / w) * w - S;
+    if (waste < best_waste) {
+      best_waste = waste;
+      best = w;
+    }
+  }
+  return best;
+}
+
+// Plans all trees into the pinned staging buffers (multi-threaded); returns max slots.
+int plan_batch(lh_family* f, const lh_tree_batch_t* tb, lhb::Step* steps, double* pblen, int* max_slots) {
+  const int T = f->fd.T, B = tb->n_trees, n_ops = T - 2, NB = 2 * T - 3;
+  int nthreads = f->opt_threads > 0 ? f->opt_threads : (int)std::thread::hardware_concurrency();
+  nthreads = std::max(1, std::min(nthreads, std::min(32, (B + 255) / 256)));
+  std::atomic<int> bad(-1);
+  std::vector<int> tmax(nthreads, 0);
+  auto work = [&](int tid) {
+    lhb::PlanScratch sc;
+    int mx = 0;
+    for (int t = tid; t < B; t += nthreads) {
+      int s = lhb::plan_tree(T, tb->children + (size_t)t * n_ops * 2, tb->blen + (size_t)t * n_ops * 2,
+                             tb->root_child[t], tb->root_blen[t], steps + (size_t)t * (T - 1),
+                             pblen + (size_t)t * NB, sc);
+      if (s < 0) {
+        bad.store(t);
+        return;
+      }
+      mx = std::max(mx, s);
+    }
+    tmax[tid] = mx;
+  };
+  if (nthreads == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int i = 0; i < nthreads; ++i) th.emplace_back(work, i);
+    for (auto& t : th) t.join();
+  }
+  if (bad.load() >= 0) return fail("tree %d is not a valid post-order operation list", bad.load());
+  *max_slots = *std::max_element(tmax.begin(), tmax.end());
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lh_batch_upload(lh_family_t* f, const lh_tree_batch_t* tb) {
+  if (!f || !tb) return fail("null argument");
+  const int B = tb->n_trees, R = tb->n_rates, T = f->fd.T, S = f->fd.S, NB = 2 * T - 3;
+  if (B < 0) return fail("negative batch size");
+  if (R < 1 || R > LH_MAX_RATES) return fail("n_rates %d outside 1..%d", R, LH_MAX_RATES);
+  LH_CUDA(cudaSetDevice(f->device));
+  f->B = B;
+  f->R = R;
+  f->tm = lh_timings_t{};
+  f->tm.n_trees = B;
+  if (B == 0) return 0;
+  for (int t = 0; t < B; ++t) {
+    for (int i = 0; i < 4; ++i)
+      if (!(tb->pi[4 * t + i] > 0.0)) return fail("tree %d: pi[%d] must be positive", t, i);
+    for (int i = 0; i < NB - 1; ++i)
+      if (!(tb->blen[(size_t)t * (NB - 1) + i] >= 0.0)) return fail("tree %d: negative branch length", t);
+    if (!(tb->root_blen[t] >= 0.0)) return fail("tree %d: negative branch length", t);
+  }
+  const size_t plan_bytes = (size_t)B * (T - 1) * sizeof(lhb::Step);
+  const size_t pblen_bytes = (size_t)B * NB * sizeof(double);
+  const size_t misc_doubles = (size_t)B * (6 + 4 + R);
+  if (f->h_plan.reserve(plan_bytes) || f->h_pblen.reserve(pblen_bytes) ||
+      f->h_misc.reserve(misc_doubles * sizeof(double)))
+    return 1;
+  if (plan_batch(f, tb, f->h_plan.as<lhb::Step>(), f->h_pblen.as<double>(), &f->slots)) return 1;
+  double* misc = f->h_misc.as<double>();
+  std::memcpy(misc, tb->er, sizeof(double) * 6 * B);
+  std::memcpy(misc + (size_t)6 * B, tb->pi, sizeof(double) * 4 * B);
+  std::memcpy(misc + (size_t)10 * B, tb->rates, sizeof(double) * R * B);
+  if (f->d_plan.reserve(plan_bytes) || f->d_pblen.reserve(pblen_bytes) ||
+      f->d_er.reserve(misc_doubles * sizeof(double)) || f->d_eig.reserve((size_t)B * lhb::kEigStride * 8) ||
+      f->d_xe.reserve((size_t)B * S * 8) || f->d_loglik.reserve((size_t)B * 8))
+    return 1;
+  if (f->opt_timing) cudaEventRecord(f->ev[0], f->stream);
+  LH_CUDA(cudaMemcpyAsync(f->d_plan.p, f->h_plan.p, plan_bytes, cudaMemcpyHostToDevice, f->stream));
+  LH_CUDA(cudaMemcpyAsync(f->d_pblen.p, f->h_pblen.p, pblen_bytes, cudaMemcpyHostToDevice, f->stream));
+  LH_CUDA(cudaMemcpyAsync(f->d_er.p, f->h_misc.p, misc_doubles * 8, cudaMemcpyHostToDevice, f->stream));
+  if (f->opt_timing) cudaEventRecord(f->ev[1], f->stream);
+  f->tm.h2d_bytes = (int64_t)(plan_bytes + pblen_bytes + misc_doubles * 8);
+  return 0;
+}
+
+int lh_batch_run(lh_family_t* f) {
+  if (!f) return fail("null family");
+  if (f->B == 0) return 0;
+  LH_CUDA(cudaSetDevice(f->device));
+  const int B = f->B, R = f->R, T = f->fd.T, S = f->fd.S, NB = 2 * T - 3;
+  lhb::BatchDev bd{};
+  bd.B = B;
+  bd.R = R;
+  bd.plan = f->d_plan.as<int4>();
+  bd.pblen = f->d_pblen.as<double>();
+  bd.er = f->d_er.as<double>();
+  bd.pi = bd.er + (size_t)6 * B;
+  bd.rates = bd.er + (size_t)10 * B;
+  bd.eig = f->d_eig.as<double>();
+  bd.xe = f->d_xe.as<double>();
+  bd.loglik = f->d_loglik.as<double>();
+
+  // pruning configuration
+  lhb::PruneCfg pc{};
+  pc.tile_sites = f->opt_tile_sites ? f->opt_tile_sites : pick_tile_sites(S);
+  pc.n_tiles = (S + pc.tile_sites - 1) / pc.tile_sites;
+  pc.total_slots = f->slots;
+  const size_t slot_bytes = (size_t)pc.tile_sites * (4 * R * sizeof(double) + sizeof(int));
+  int occ0 = lhb::prune_max_ctas_per_sm(R, pc.tile_sites, 0);
+  if (occ0 < 1) return fail("pruning kernel cannot be resident (R=%d, tile=%d)", R, pc.tile_sites);
+  int smem_slots = f->opt_smem_slots;
+  if (smem_slots < 0) {
+    size_t per_cta = (size_t)(227 * 1024) / occ0 - 1024;
+    smem_slots = (int)(per_cta / slot_bytes);
+  }
+  smem_slots = std::max(0, std::min(smem_slots, pc.total_slots));
+  while (smem_slots > 0 && lhb::prune_smem_bytes(R, pc.tile_sites, smem_slots) > (size_t)227 * 1024) --smem_slots;
+  pc.smem_slots = smem_slots;
+  int occ = lhb::prune_max_ctas_per_sm(R, pc.tile_sites, pc.smem_slots);
+  if (occ < 1) return fail("pruning kernel cannot be resident with %d shared-memory slots", pc.smem_slots);
+  pc.log_threshold = std::log(1.0 / std::pow(2.0, 256));
+
+  // chunk the batch so one chunk's branch records stay L2-resident
+  const size_t rec_bytes_tree = (size_t)NB * 20 * R * sizeof(double);
+  int chunk = (int)std::max<size_t>(1, f->opt_chunk_bytes / rec_bytes_tree);
+  const int resident = occ * f->num_sms;
+  // keep at least two waves of work items per launch when the batch allows it
+  chunk = std::max(chunk, (2 * resident + pc.n_tiles - 1) / pc.n_tiles);
+  chunk = std::min(chunk, B);
+  if (f->d_prec.reserve((size_t)chunk * rec_bytes_tree)) return 1;
+  bd.prec = f->d_prec.as<double>();
+  pc.grid = std::min(resident, chunk * pc.n_tiles);
+  const int gslots = pc.total_slots - pc.smem_slots;
+  if (gslots > 0) {
+    if (f->d_scratch.reserve((size_t)pc.grid * gslots * 4 * R * pc.tile_sites * sizeof(double)) ||
+        f->d_scratch_cnt.reserve((size_t)pc.grid * gslots * pc.tile_sites * sizeof(int)))
+      return 1;
+  }
+  pc.scratch = f->d_scratch.as<double>();
+  pc.scratch_cnt = f->d_scratch_cnt.as<int32_t>();
+
+  lhb::HmmOut ho{};
+  ho.log_factor = std::log(std::pow(2.0, 256));
+  if (f->want_tables) {
+    const lhb::FamilyDev& fd = f->fd;
+    if (f->d_vgerm.reserve((size_t)B * fd.n_v * 8) || f->d_vd.reserve((size_t)B * fd.vd_sites * fd.vd_states * 8) ||
+        f->d_dgerm.reserve((size_t)B * std::max(fd.n_d, 1) * 8) ||
+        f->d_dj.reserve((size_t)B * std::max(fd.dj_sites * fd.dj_states, 1) * 8) ||
+        f->d_jgerm.reserve((size_t)B * fd.n_j * 8) || f->d_gs.reserve((size_t)B * 3 * 4) ||
+        f->d_vds.reserve((size_t)B * fd.vd_sites * 4) || f->d_djs.reserve((size_t)B * std::max(fd.dj_sites, 1) * 4))
+      return 1;
+    ho.vgerm_forward = f->d_vgerm.as<double>();
+    ho.vd_forward = f->d_vd.as<double>();
+    ho.dgerm_forward = fd.has_d ? f->d_dgerm.as<double>() : nullptr;
+    ho.dj_forward = fd.has_d ? f->d_dj.as<double>() : nullptr;
+    ho.jgerm_forward = f->d_jgerm.as<double>();
+    ho.germ_scalers = f->d_gs.as<int32_t>();
+    ho.vd_scalers = f->d_vds.as<int32_t>();
+    ho.dj_scalers = fd.has_d ? f->d_djs.as<int32_t>() : nullptr;
+  }
+
+  cudaStream_t s = f->stream;
+  int launches = 0;
+  if (f->opt_timing) cudaEventRecord(f->ev[2], s);
+  lhb::launch_eigen(bd, s);
+  ++launches;
+  for (int t0 = 0; t0 < B; t0 += chunk) {
+    const int n = std::min(chunk, B - t0);
+    lhb::launch_pmatrix(f->fd, bd, t0, n, s);
+    lhb::PruneCfg c = pc;
+    c.grid = std::min(pc.grid, n * pc.n_tiles);
+    lhb::launch_prune(f->fd, bd, c, t0, n, s);
+    launches += 2;
+  }
+  if (f->opt_timing) cudaEventRecord(f->ev[3], s);
+  lhb::launch_hmm(f->fd, bd, ho, s);
+  ++launches;
+  if (f->opt_timing) cudaEventRecord(f->ev[4], s);
+  LH_CUDA(cudaGetLastError());
+  f->tm.kernel_launches = launches;
+  f->tm.prune_slots = pc.total_slots;
+  f->tm.prune_tile_sites = pc.tile_sites;
+  return 0;
+}
+
+int lh_sync(lh_family_t* f) {
+  if (!f) return fail("null family");
+  LH_CUDA(cudaSetDevice(f->device));
+  LH_CUDA(cudaStreamSynchronize(f->stream));
+  return 0;
+}
+
+int lh_loglik_dev(lh_family_t* f, const double** p, int32_t* n) {
+  if (!f) return fail("null family");
+  *p = f->d_loglik.as<double>();
+  *n = f->B;
+  return 0;
+}
+
+int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
+  if (!f) return fail("null family");
+  const int B = f->B;
+  if (B == 0) return 0;
+  LH_CUDA(cudaSetDevice(f->device));
+  const lhb::FamilyDev& fd = f->fd;
+  cudaStream_t s = f->stream;
+  if (f->opt_timing) cudaEventRecord(f->ev[5], s);
+  int64_t bytes = 0;
+  auto get = [&](void* dst, const void* src, size_t n) {
+    if (!dst || !n) return 0;
+    bytes += (int64_t)n;
+    LH_CUDA(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, s));
+    return 0;
+  };
+  if (f->h_out.reserve((size_t)B * 8)) return 1;
+  if (get(f->h_out.p, f->d_loglik.p, (size_t)B * 8)) return 1;
+  if (o) {
+    if (get(o->xmsa_emission, f->d_xe.p, (size_t)B * fd.S * 8)) return 1;
+    const bool tables = o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
+                        o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers;
+    if (tables) {
+      if (!f->want_tables) return fail("forward tables were not produced by the last run (internal)");
+      if (get(o->vgerm_forward, f->d_vgerm.p, (size_t)B * fd.n_v * 8) ||
+          get(o->vd_forward, f->d_vd.p, (size_t)B * fd.vd_sites * fd.vd_states * 8) ||
+          get(o->jgerm_forward, f->d_jgerm.p, (size_t)B * fd.n_j * 8) ||
+          get(o->germ_scalers, f->d_gs.p, (size_t)B * 3 * 4) ||
+          get(o->vd_scalers, f->d_vds.p, (size_t)B * fd.vd_sites * 4))
+        return 1;
+      if (fd.has_d && (get(o->dgerm_forward, f->d_dgerm.p, (size_t)B * fd.n_d * 8) ||
+                       get(o->dj_forward, f->d_dj.p, (size_t)B * fd.dj_sites * fd.dj_states * 8) ||
+                       get(o->dj_scalers, f->d_djs.p, (size_t)B * fd.dj_sites * 4)))
+        return 1;
+    }
+  }
+  if (f->opt_timing) cudaEventRecord(f->ev[6], s);
+  LH_CUDA(cudaStreamSynchronize(s));
+  LH_CUDA(cudaGetLastError());
+  std::memcpy(loglik, f->h_out.p, (size_t)B * 8);
+  f->tm.d2h_bytes = bytes;
+  if (f->opt_timing) {
+    cudaEventElapsedTime(&f->tm.ms_h2d, f->ev[0], f->ev[1]);
+    cudaEventElapsedTime(&f->tm.ms_prune, f->ev[2], f->ev[3]);
+    cudaEventElapsedTime(&f->tm.ms_hmm, f->ev[3], f->ev[4]);
+    cudaEventElapsedTime(&f->tm.ms_d2h, f->ev[5], f->ev[6]);
+    cudaEventElapsedTime(&f->tm.ms_total, f->ev[0], f->ev[6]);
+  }
+  return 0;
+}
+
+int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh_outputs_t* o) {
+  if (!f || !tb || !loglik) return fail("null argument");
+  f->want_tables = o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
+                         o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers);
+  if (lh_batch_upload(f, tb)) return 1;
+  if (lh_batch_run(f)) return 1;
+  return lh_batch_fetch(f, loglik, o);
+}
+
+int lh_get_timings(lh_family_t* f, lh_timings_t* out) {
+  if (!f || !out) return fail("null argument");
+  *out = f->tm;
+  return 0;
+}
+
+}  // extern "C"

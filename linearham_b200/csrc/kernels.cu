@@ -1,0 +1,627 @@
+// Hand-written sm_100a kernels for the phylo-HMM likelihood path.
+//
+//   k_eigen    GTR eigen system per tree           (replaces libpll models.c:182-331)
+//   k_pmatrix  per-branch transition records       (replaces core_pmatrix.c:160-237 and the
+//                                                   tip-CLV expansion pll.c:905-964)
+//   k_prune    Felsenstein pruning over the xMSA + edge likelihood + naive correction
+//              (replaces core_partials.c:575-663, core_likelihood_avx.c:1130-1260,
+//               src/PhyloHMM.cpp:228-237)
+//   k_hmm      emission fill + scaled forward pass + log-likelihood
+//              (replaces src/PhyloHMM.cpp:158-215, src/HMM.cpp:254-319,1107-1177,345-354)
+//
+// All arithmetic is FP64 on the CUDA cores: the per-site work is 4x4 matrix-vector
+// products against per-branch matrices (no dense contraction for tcgen05, which has no
+// FP64 kind), and the HMM transition matrices are ~5 % dense.
+#include "kernels.hpp"
+
+#include <cfloat>
+#include <cmath>
+
+namespace lhb {
+
+#define LH_SCALE_FACTOR 1.157920892373162e+77            /* 2^256  (utils.hpp:22, pll.h:89-93) */
+#define LH_SCALE_THRESHOLD 8.636168555094445e-78         /* 2^-256 */
+
+// ------------------------------------------------------------------ k_eigen ---
+
+// Cyclic Jacobi on the symmetrised rate matrix. The reference uses Householder + QL
+// (models.c:24-178); any orthogonal eigensolver gives the same P-matrices to ~1e-16
+// because P = I + sum_m inv[.,m] expm1(..) evecs[m,.] is invariant to the choice of
+// basis inside a degenerate eigenspace.
+__global__ void k_eigen(BatchDev b) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= b.B) return;
+  double r[6], pi[4];
+  for (int i = 0; i < 6; ++i) r[i] = b.er[6 * t + i];
+  for (int i = 0; i < 4; ++i) pi[i] = b.pi[4 * t + i];
+  if (r[5] > 0.0) {  // models.c:198-200
+    double d = r[5];
+    for (int i = 0; i < 6; ++i) r[i] /= d;
+  }
+  double a[4][4], v[4][4];
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) { a[i][j] = 0.0; v[i][j] = (i == j) ? 1.0 : 0.0; }
+  int k = 0;
+  for (int i = 0; i < 4; ++i)
+    for (int j = i + 1; j < 4; ++j) {  // models.c:225-237
+      double f = r[k++];
+      a[i][j] = a[j][i] = f * sqrt(pi[i] * pi[j]);
+      a[i][i] -= f * pi[j];
+      a[j][j] -= f * pi[i];
+    }
+  double mean = 0;
+  for (int i = 0; i < 4; ++i) mean += pi[i] * (-a[i][i]);
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) a[i][j] /= mean;  // models.c:240-244
+
+  for (int sweep = 0; sweep < 64; ++sweep) {
+    double off = 0;
+    for (int p = 0; p < 4; ++p)
+      for (int q = p + 1; q < 4; ++q) off += fabs(a[p][q]);
+    if (off == 0.0) break;
+    for (int p = 0; p < 4; ++p)
+      for (int q = p + 1; q < 4; ++q) {
+        double apq = a[p][q];
+        if (apq == 0.0) continue;
+        double g = 100.0 * fabs(apq);
+        if (sweep > 4 && fabs(a[p][p]) + g == fabs(a[p][p]) && fabs(a[q][q]) + g == fabs(a[q][q])) {
+          a[p][q] = a[q][p] = 0.0;
+          continue;
+        }
+        double h = a[q][q] - a[p][p], tt;
+        if (fabs(h) + g == fabs(h)) {
+          tt = apq / h;
+        } else {
+          double theta = 0.5 * h / apq;
+          tt = 1.0 / (fabs(theta) + sqrt(1.0 + theta * theta));
+          if (theta < 0.0) tt = -tt;
+        }
+        double c = 1.0 / sqrt(1.0 + tt * tt), s = tt * c, tau = s / (1.0 + c);
+        a[p][p] -= tt * apq;
+        a[q][q] += tt * apq;
+        a[p][q] = a[q][p] = 0.0;
+        for (int m = 0; m < 4; ++m) {
+          if (m != p && m != q) {
+            double amp = a[m][p], amq = a[m][q];
+            a[m][p] = a[p][m] = amp - s * (amq + amp * tau);
+            a[m][q] = a[q][m] = amq + s * (amp - amq * tau);
+          }
+          double vmp = v[m][p], vmq = v[m][q];
+          v[m][p] = vmp - s * (vmq + vmp * tau);
+          v[m][q] = vmq + s * (vmp - vmq * tau);
+        }
+      }
+  }
+  double* e = b.eig + (size_t)t * kEigStride;
+  for (int m = 0; m < 4; ++m) e[m] = a[m][m];
+  for (int m = 0; m < 4; ++m)
+    for (int kk = 0; kk < 4; ++kk) {
+      e[4 + m * 4 + kk] = v[kk][m] * sqrt(pi[kk]);   // evecs[m][k]   (models.c:317-320)
+      e[20 + kk * 4 + m] = v[kk][m] / sqrt(pi[kk]);  // inv_evecs[k][m] (models.c:300-315)
+    }
+  for (int i = 0; i < 4; ++i) {
+    e[36 + i] = log(pi[i]);
+    e[40 + i] = pi[i];
+  }
+}
+
+void launch_eigen(const BatchDev& b, cudaStream_t s) {
+  int threads = 128;
+  k_eigen<<<(b.B + threads - 1) / threads, threads, 0, s>>>(b);
+}
+
+// ---------------------------------------------------------------- k_pmatrix ---
+// One thread per (tree, branch, rate category). Branch records are laid out in the
+// order the pruning program consumes them: record 2*step+c for child c of a step, the
+// root edge last; each record is 20*R doubles:
+//   inner child : P[k][i][j] at k*16 + i*4 + j      (row-major as core_pmatrix.c)
+//   tip child   : Q[k][code][i] at k*20 + code*4 + i, code in A,C,G,T,N: the product
+//                 P[k] * tipclv(code) that set_tipclv + the generic kernel would form
+//                 (pll.c:926-930: one-hot for ACGT, all ones for N).
+__global__ void k_pmatrix(FamilyDev f, BatchDev b, int tree0, int ntrees) {
+  const int NB = 2 * f.T - 3, R = b.R;
+  const long long total = (long long)ntrees * NB * R;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(idx % R);
+    const int br = (int)((idx / R) % NB);
+    const int lt = (int)(idx / ((long long)R * NB));
+    const int t = tree0 + lt;
+    const int step = br >> 1;
+    const int4 st = __ldg(b.plan + (size_t)t * (f.T - 1) + step);
+    const int src = (br & 1) ? st.y : st.x;  // for the final step y is the child side
+    const bool tip = (br == NB - 1) ? (st.y >= 0) : (src >= 0);
+    const double* e = b.eig + (size_t)t * kEigStride;
+    const double len = b.pblen[(size_t)t * NB + br];
+    const double rate = b.rates[(size_t)t * R + k];
+    double P[4][4];
+    if (len == 0.0) {  // core_pmatrix.c:174-179
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) P[j][c] = (j == c) ? 1.0 : 0.0;
+    } else {
+      double expd[4];
+#pragma unroll
+      for (int m = 0; m < 4; ++m) expd[m] = expm1(e[m] * rate * len);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        double tmp[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) tmp[m] = e[20 + j * 4 + m] * expd[m];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          double acc = (j == c) ? 1.0 : 0.0;
+#pragma unroll
+          for (int m = 0; m < 4; ++m) acc += tmp[m] * e[4 + m * 4 + c];
+          P[j][c] = acc;
+        }
+      }
+    }
+    double* rec = b.prec + ((size_t)lt * NB + br) * (20 * R);
+    if (!tip) {
+      double2* o = reinterpret_cast<double2*>(rec + k * 16);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        o[2 * j] = make_double2(P[j][0], P[j][1]);
+        o[2 * j + 1] = make_double2(P[j][2], P[j][3]);
+      }
+    } else {
+      double2* o = reinterpret_cast<double2*>(rec + k * 20);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        o[2 * c] = make_double2(P[0][c], P[1][c]);
+        o[2 * c + 1] = make_double2(P[2][c], P[3][c]);
+      }
+      double sN[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) sN[i] = ((P[i][0] + P[i][1]) + P[i][2]) + P[i][3];
+      o[8] = make_double2(sN[0], sN[1]);
+      o[9] = make_double2(sN[2], sN[3]);
+    }
+  }
+}
+
+void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees, cudaStream_t s) {
+  long long total = (long long)ntrees * (2 * f.T - 3) * b.R;
+  int threads = 256;
+  long long blocks = (total + threads - 1) / threads;
+  if (blocks > 148LL * 64) blocks = 148LL * 64;
+  k_pmatrix<<<(unsigned)blocks, threads, 0, s>>>(f, b, tree0, ntrees);
+}
+
+// ------------------------------------------------------------------ k_prune ---
+// Persistent CTAs; a work item is (tree, tile of W xMSA columns); thread = one column.
+// The thread walks the tree's program (plan.hpp). Inner CLVs never exist as arrays in
+// HBM: the running result stays in registers (reg[R][4]), results parked for a later
+// step go to a per-column stack whose first `smem_slots` levels are shared memory
+// ([slot][k*4+j][W], conflict-free because a column is only ever touched by its own
+// thread) and whose deeper levels are an L2-resident scratch ring private to the CTA.
+// No barriers: threads never exchange data.
+
+template <int R>
+struct SlotIO {
+  double* smem_clv;   // [smem_slots][4R][W]
+  int* smem_cnt;      // [smem_slots][W]
+  double* g_clv;      // [gslots][4R][W] (this CTA)
+  int* g_cnt;         // [gslots][W]
+  int smem_slots, W, tid;
+
+  __device__ __forceinline__ void locate(int slot, double*& clv, int*& cnt) const {
+    if (slot < smem_slots) {
+      clv = smem_clv + (size_t)slot * (4 * R) * W + tid;
+      cnt = smem_cnt + slot * W + tid;
+    } else {
+      clv = g_clv + (size_t)(slot - smem_slots) * (4 * R) * W + tid;
+      cnt = g_cnt + (slot - smem_slots) * W + tid;
+    }
+  }
+};
+
+// message of an inner child through its branch: m[i] = sum_j P[k][i][j] * c[j]
+// (core_partials.c:617-624)
+__device__ __forceinline__ void matvec4(const double* __restrict__ Pk, const double c[4], double m[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const double2 p01 = __ldg(reinterpret_cast<const double2*>(Pk + 4 * i));
+    const double2 p23 = __ldg(reinterpret_cast<const double2*>(Pk + 4 * i + 2));
+    double acc = p01.x * c[0];
+    acc += p01.y * c[1];
+    acc += p23.x * c[2];
+    acc += p23.y * c[3];
+    m[i] = acc;
+  }
+}
+
+__device__ __forceinline__ void tipvec4(const double* __restrict__ Qk, int code, double m[4]) {
+  const double2 q01 = __ldg(reinterpret_cast<const double2*>(Qk + 4 * code));
+  const double2 q23 = __ldg(reinterpret_cast<const double2*>(Qk + 4 * code + 2));
+  m[0] = q01.x; m[1] = q01.y; m[2] = q23.x; m[3] = q23.y;
+}
+
+// Computes the per-category messages of one child into m[R][4]; returns its scaler count.
+template <int R>
+__device__ __forceinline__ int child_messages(int src, const double* __restrict__ rec,
+                                              const double (&reg)[R][4], int reg_cnt,
+                                              const SlotIO<R>& io, const uint8_t* __restrict__ codes,
+                                              int S, int site, double (&m)[R][4]) {
+  if (src >= 0) {
+    const int code = __ldg(codes + (size_t)src * S + site);
+#pragma unroll
+    for (int k = 0; k < R; ++k) tipvec4(rec + k * 20, code, m[k]);
+    return 0;
+  }
+  if (src == -1) {
+#pragma unroll
+    for (int k = 0; k < R; ++k) matvec4(rec + k * 16, reg[k], m[k]);
+    return reg_cnt;
+  }
+  double* clv;
+  int* cnt;
+  io.locate(-2 - src, clv, cnt);
+#pragma unroll
+  for (int k = 0; k < R; ++k) {
+    double c[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c[j] = clv[(size_t)(k * 4 + j) * io.W];
+    matvec4(rec + k * 16, c, m[k]);
+  }
+  return *cnt;
+}
+
+template <int R>
+__global__ void __launch_bounds__(256) k_prune(FamilyDev f, BatchDev b, PruneCfg cfg, int tree0, int ntrees) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int W = cfg.tile_sites, tid = threadIdx.x, T = f.T, S = f.S;
+  const int NB = 2 * T - 3, REC = 20 * R, n_steps = T - 2;
+  const int gslots = cfg.total_slots - cfg.smem_slots;
+  SlotIO<R> io;
+  io.smem_clv = reinterpret_cast<double*>(smem_raw);
+  io.smem_cnt = reinterpret_cast<int*>(io.smem_clv + (size_t)cfg.smem_slots * (4 * R) * W);
+  io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * R) * W;
+  io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * W;
+  io.smem_slots = cfg.smem_slots;
+  io.W = W;
+  io.tid = tid;
+
+  const int n_work = ntrees * cfg.n_tiles;
+  for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+    const int lt = w / cfg.n_tiles, tile = w - lt * cfg.n_tiles;
+    const int t = tree0 + lt;
+    const int site = tile * W + tid;
+    if (site >= S) continue;
+    const int4* __restrict__ plan = b.plan + (size_t)t * (T - 1);
+    const double* __restrict__ recs = b.prec + (size_t)lt * NB * REC;
+
+    double reg[R][4];
+    int reg_cnt = 0;
+#pragma unroll
+    for (int k = 0; k < R; ++k)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) reg[k][i] = 0.0;
+
+    for (int s = 0; s < n_steps; ++s) {
+      const int4 st = __ldg(plan + s);
+      const double* recA = recs + (size_t)(2 * s) * REC;
+      double ma[R][4], mb[R][4];
+      const int ca = child_messages<R>(st.x, recA, reg, reg_cnt, io, f.tip_codes, S, site, ma);
+      const int cb = child_messages<R>(st.y, recA + REC, reg, reg_cnt, io, f.tip_codes, S, site, mb);
+      bool all_small = true;
+#pragma unroll
+      for (int k = 0; k < R; ++k)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const double v = ma[k][i] * mb[k][i];  // core_partials.c:626
+          reg[k][i] = v;
+          all_small = all_small && (v < LH_SCALE_THRESHOLD);
+        }
+      reg_cnt = ca + cb;            // fill_parent_scaler, core_partials.c:24-46
+      if (all_small) {              // per-site scaling, core_partials.c:648-659
+#pragma unroll
+        for (int k = 0; k < R; ++k)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) reg[k][i] *= LH_SCALE_FACTOR;
+        reg_cnt += 1;
+      }
+      if (st.z >= 0) {
+        double* clv;
+        int* cnt;
+        io.locate(st.z, clv, cnt);
+#pragma unroll
+        for (int k = 0; k < R; ++k)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) clv[(size_t)(k * 4 + i) * W] = reg[k][i];
+        *cnt = reg_cnt;
+      }
+    }
+
+    // ---- edge likelihood at the virtual root (core_likelihood_avx.c:1130-1260) ----
+    const int4 fin = __ldg(plan + n_steps);
+    const double* recE = recs + (size_t)(NB - 1) * REC;
+    const double* eig = b.eig + (size_t)t * kEigStride;
+    double mc[R][4];
+    const int cc = child_messages<R>(fin.y, recE, reg, reg_cnt, io, f.tip_codes, S, site, mc);
+    int cp = reg_cnt;
+    if (fin.x != -1) {  // the root CLV was parked; fetch it
+      double* clv;
+      int* cnt;
+      io.locate(-2 - fin.x, clv, cnt);
+#pragma unroll
+      for (int k = 0; k < R; ++k)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) reg[k][i] = clv[(size_t)(k * 4 + i) * W];
+      cp = *cnt;
+    }
+    const double pi0 = eig[40], pi1 = eig[41], pi2 = eig[42], pi3 = eig[43];
+    const double weight = 1.0 / R;  // pll.c:746-747
+    double terma = 0.0;
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      const double t0 = (pi0 * mc[k][0]) * reg[k][0];
+      const double t1 = (pi1 * mc[k][1]) * reg[k][1];
+      const double t2 = (pi2 * mc[k][2]) * reg[k][2];
+      const double t3 = (pi3 * mc[k][3]) * reg[k][3];
+      const double terma_r = (t0 + t1) + (t2 + t3);
+      if (terma_r > 0.0) terma += terma_r * weight;   // :1225-1239
+    }
+    double site_lk = log(terma);
+    const int scalings = cp + cc;
+    if (scalings) site_lk += scalings * cfg.log_threshold;   // :1247-1251
+    // naive-sequence correction (src/PhyloHMM.cpp:229-237); xMSA row 0 is the naive
+    const int nb = __ldg(f.tip_codes + site);
+    if (nb != 4) site_lk -= eig[36 + nb];
+    b.xe[(size_t)t * S + site] = exp(site_lk);
+  }
+}
+
+size_t prune_smem_bytes(int R, int tile_sites, int smem_slots) {
+  return (size_t)smem_slots * tile_sites * (4 * R * sizeof(double) + sizeof(int));
+}
+
+template <int R>
+static void launch_prune_r(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0,
+                           int ntrees, cudaStream_t s) {
+  size_t smem = prune_smem_bytes(R, c.tile_sites, c.smem_slots);
+  cudaFuncSetAttribute(k_prune<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_prune<R><<<c.grid, c.tile_sites, smem, s>>>(f, b, c, tree0, ntrees);
+}
+
+template <int R>
+static int prune_occ_r(int tile_sites, size_t smem) {
+  int n = 0;
+  cudaFuncSetAttribute(k_prune<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_prune<R>, tile_sites, smem);
+  return n;
+}
+
+#define LH_DISPATCH_R(R_, CALL)                       \
+  switch (R_) {                                       \
+    case 1: { constexpr int RR = 1; CALL; } break;    \
+    case 2: { constexpr int RR = 2; CALL; } break;    \
+    case 3: { constexpr int RR = 3; CALL; } break;    \
+    case 4: { constexpr int RR = 4; CALL; } break;    \
+    case 5: { constexpr int RR = 5; CALL; } break;    \
+    case 6: { constexpr int RR = 6; CALL; } break;    \
+    case 7: { constexpr int RR = 7; CALL; } break;    \
+    default: { constexpr int RR = 8; CALL; } break;   \
+  }
+
+void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0, int ntrees,
+                  cudaStream_t s) {
+  LH_DISPATCH_R(b.R, launch_prune_r<RR>(f, b, c, tree0, ntrees, s));
+}
+
+int prune_max_ctas_per_sm(int R, int tile_sites, int smem_slots) {
+  size_t smem = prune_smem_bytes(R, tile_sites, smem_slots);
+  int n = 0;
+  LH_DISPATCH_R(R, n = prune_occ_r<RR>(tile_sites, smem));
+  return n;
+}
+
+// -------------------------------------------------------------------- k_hmm ---
+// One warp per tree sample. Per-warp shared memory: two state vectors (ping-pong) and
+// the five germline/padding emission vectors with their scaler counts.
+
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ int warp_max_i(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ScaleMatrix (src/utils.cpp:135-144) on a row of n doubles owned by the warp
+// (entry j belongs to lane j % 32). Multiplying by 2^256 is exact, so the number of
+// rounds the reference's while-loop makes is determined by the smallest positive entry.
+__device__ __forceinline__ int warp_scale_row(double* row, int n, int lane) {
+  double mn = DBL_MAX;
+  for (int j = lane; j < n; j += 32) {
+    const double v = row[j];
+    if (v > 0.0 && v < mn) mn = v;
+  }
+  mn = warp_min(mn);
+  int rounds = 0;
+  while (mn < LH_SCALE_THRESHOLD) {
+    mn *= LH_SCALE_FACTOR;
+    ++rounds;
+  }
+  if (rounds) {
+    for (int j = lane; j < n; j += 32) {
+      double v = row[j];
+      for (int r = 0; r < rounds; ++r) v *= LH_SCALE_FACTOR;
+      row[j] = v;
+    }
+  }
+  __syncwarp();
+  return rounds;
+}
+
+// FillGermlinePaddingEmission (src/PhyloHMM.cpp:158-193) for one region: lane g owns
+// gene g's running product; returns the region's max scaler count.
+__device__ __forceinline__ int fill_region(int n, const int32_t* __restrict__ off,
+                                           const int32_t* __restrict__ inds,
+                                           const double* __restrict__ xe, double* emis, int lane) {
+  int local_max = 0;
+  for (int g = lane; g < n; g += 32) {
+    double x = 1.0;
+    int cnt = 0;
+    const int e = off[g + 1];
+    for (int j = off[g]; j < e; ++j) {
+      x *= xe[inds[j]];
+      while (x > 0.0 && x < LH_SCALE_THRESHOLD) {
+        x *= LH_SCALE_FACTOR;
+        ++cnt;
+      }
+    }
+    emis[g] = x;
+    reinterpret_cast<int*>(emis + n)[g] = cnt;  // counts parked behind the values
+    local_max = max(local_max, cnt);
+  }
+  const int mx = warp_max_i(local_max);
+  __syncwarp();
+  for (int g = lane; g < n; g += 32) {
+    const int d = mx - reinterpret_cast<int*>(emis + n)[g];
+    // std::pow(SCALE_FACTOR, d): 2^(256 d), +inf from d = 4 on (src/PhyloHMM.cpp:191)
+    double pw = 1.0;
+    for (int r = 0; r < d; ++r) pw *= LH_SCALE_FACTOR;
+    emis[g] *= pw;
+  }
+  __syncwarp();
+  return mx;
+}
+
+// row-vector times sparse matrix: out[j] = sum_k prev[k] * M[k][j]
+__device__ __forceinline__ double csc_dot(const CscDev& m, const double* prev, int j) {
+  double acc = 0.0;
+  const int e = m.colptr[j + 1];
+  for (int p = m.colptr[j]; p < e; ++p) acc += prev[m.row[p]] * m.val[p];
+  return acc;
+}
+
+// ComputeJunctionForwardProbabilities (src/HMM.cpp:1107-1139)
+__device__ int junction_forward(const CscDev& t_in, const CscDev& t_jj, const int32_t* __restrict__ inds_rm,
+                                int L, int Sj, const double* __restrict__ xe, double*& prev,
+                                double*& cur, int count, double* fwd_out, int32_t* cnt_out, int lane) {
+  for (int i = 0; i < L; ++i) {
+    const CscDev& m = (i == 0) ? t_in : t_jj;
+    for (int j = lane; j < Sj; j += 32) {
+      double acc = csc_dot(m, prev, j);
+      const int idx = inds_rm[(size_t)i * Sj + j];
+      acc *= (idx < 0) ? 0.0 : xe[idx];   // FillJunctionEmission: 0 where idx == -1
+      cur[j] = acc;
+    }
+    __syncwarp();
+    count += warp_scale_row(cur, Sj, lane);
+    if (fwd_out)
+      for (int j = lane; j < Sj; j += 32) fwd_out[(size_t)j * L + i] = cur[j];
+    if (cnt_out && lane == 0) cnt_out[i] = count;
+    double* tmp = prev; prev = cur; cur = tmp;
+  }
+  return count;
+}
+
+__global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warps = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per_warp = 2 * f.s_max + 5 * (f.g_max + (f.g_max + 1) / 2);
+  double* base = reinterpret_cast<double*>(smem_raw) + (size_t)wid * per_warp;
+  double* bufA = base;
+  double* bufB = base + f.s_max;
+  const int gstride = f.g_max + (f.g_max + 1) / 2;  // values + packed int counts
+  double* e_vpad = base + 2 * f.s_max;
+  double* e_vgerm = e_vpad + gstride;
+  double* e_dgerm = e_vgerm + gstride;
+  double* e_jgerm = e_dgerm + gstride;
+  double* e_jpad = e_jgerm + gstride;
+
+  for (int t = blockIdx.x * warps + wid; t < b.B; t += gridDim.x * warps) {
+    const double* xe = b.xe + (size_t)t * f.S;
+    // emissions (src/PhyloHMM.cpp:94-114); counts reset per tree (:373-375)
+    int c_v = fill_region(f.n_v, f.vpad_off, f.vpad_inds, xe, e_vpad, lane);
+    c_v += fill_region(f.n_v, f.vgerm_off, f.vgerm_inds, xe, e_vgerm, lane);
+    int c_d = 0;
+    if (f.has_d) c_d = fill_region(f.n_d, f.dgerm_off, f.dgerm_inds, xe, e_dgerm, lane);
+    int c_j = fill_region(f.n_j, f.jgerm_off, f.jgerm_inds, xe, e_jgerm, lane);
+    c_j += fill_region(f.n_j, f.jpad_off, f.jpad_inds, xe, e_jpad, lane);
+
+    // ComputeInitialForwardProbabilities (src/HMM.cpp:291-319)
+    double* prev = bufA;
+    double* cur = bufB;
+    for (int g = lane; g < f.n_v; g += 32) {
+      double v = f.v_gene_prob[g];
+      v *= f.vpad_trans[g];
+      v *= e_vpad[g];
+      v *= f.v_trans_prod[g];
+      v *= e_vgerm[g];
+      prev[g] = v;
+    }
+    __syncwarp();
+    c_v += warp_scale_row(prev, f.n_v, lane);
+    if (o.vgerm_forward)
+      for (int g = lane; g < f.n_v; g += 32) o.vgerm_forward[(size_t)t * f.n_v + g] = prev[g];
+
+    // V-D (or V-J) junction
+    int cnt = junction_forward(f.t_v_vd, f.t_vd, f.vd_inds_rm, f.vd_sites, f.vd_states, xe, prev, cur, c_v,
+                               o.vd_forward ? o.vd_forward + (size_t)t * f.vd_sites * f.vd_states : nullptr,
+                               o.vd_scalers ? o.vd_scalers + (size_t)t * f.vd_sites : nullptr, lane);
+    if (f.has_d) {
+      // ComputeGermlineForwardProbabilities for D (src/HMM.cpp:1160-1177; padding terms are ones)
+      for (int g = lane; g < f.n_d; g += 32) {
+        double v = csc_dot(f.t_vd_d, prev, g);
+        v *= e_dgerm[g];
+        cur[g] = v;
+      }
+      __syncwarp();
+      c_d += cnt + warp_scale_row(cur, f.n_d, lane);
+      if (o.dgerm_forward)
+        for (int g = lane; g < f.n_d; g += 32) o.dgerm_forward[(size_t)t * f.n_d + g] = cur[g];
+      { double* tmp = prev; prev = cur; cur = tmp; }
+      cnt = junction_forward(f.t_d_dj, f.t_dj, f.dj_inds_rm, f.dj_sites, f.dj_states, xe, prev, cur, c_d,
+                             o.dj_forward ? o.dj_forward + (size_t)t * f.dj_sites * f.dj_states : nullptr,
+                             o.dj_scalers ? o.dj_scalers + (size_t)t * f.dj_sites : nullptr, lane);
+    }
+    const CscDev& t_out = f.has_d ? f.t_dj_j : f.t_vd_d;
+    for (int g = lane; g < f.n_j; g += 32) {
+      double v = csc_dot(t_out, prev, g);
+      v *= e_jgerm[g];
+      v *= f.jpad_trans[g];
+      v *= e_jpad[g];
+      cur[g] = v;
+    }
+    __syncwarp();
+    c_j += cnt + warp_scale_row(cur, f.n_j, lane);
+    if (o.jgerm_forward)
+      for (int g = lane; g < f.n_j; g += 32) o.jgerm_forward[(size_t)t * f.n_j + g] = cur[g];
+    if (lane == 0) {
+      double sum = 0.0;
+      for (int g = 0; g < f.n_j; ++g) sum += cur[g];
+      // HMM::LogLikelihood (src/HMM.cpp:352-353)
+      b.loglik[t] = log(sum) - c_j * o.log_factor;
+      if (o.germ_scalers) {
+        o.germ_scalers[3 * t] = c_v;
+        o.germ_scalers[3 * t + 1] = c_d;
+        o.germ_scalers[3 * t + 2] = c_j;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+size_t hmm_smem_bytes(const FamilyDev& f, int warps) {
+  size_t per_warp = 2 * (size_t)f.s_max + 5 * ((size_t)f.g_max + (f.g_max + 1) / 2);
+  return per_warp * warps * sizeof(double);
+}
+
+void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, cudaStream_t s) {
+  const int warps = 4;
+  size_t smem = hmm_smem_bytes(f, warps);
+  cudaFuncSetAttribute(k_hmm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int blocks = (b.B + warps - 1) / warps;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  k_hmm<<<blocks, warps * 32, smem, s>>>(f, b, o);
+}
+
+}  // namespace lhb

@@ -1,0 +1,71 @@
+// Device-side data layout and kernel launchers (sm_100a). See DESIGN.md.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace lhb {
+
+constexpr int kEigStride = 44;  // per tree: evals[4] evecs[16] inv_evecs[16] log(pi)[4] pi[4]
+
+// Sparse column form of one HMM transition matrix (family constant).
+struct CscDev {
+  const int32_t* colptr;  // [cols+1]
+  const int32_t* row;     // [nnz]
+  const double* val;      // [nnz]
+  int32_t rows, cols;
+};
+
+struct FamilyDev {
+  int32_t T, S;                 // tips, xMSA columns
+  const uint8_t* tip_codes;     // [T][S]
+  int32_t has_d, n_v, n_d, n_j;
+  int32_t vd_sites, vd_states, dj_sites, dj_states;
+  const int32_t *vpad_off, *vpad_inds, *vgerm_off, *vgerm_inds, *dgerm_off, *dgerm_inds;
+  const int32_t *jgerm_off, *jgerm_inds, *jpad_off, *jpad_inds;
+  const int32_t* vd_inds_rm;    // [vd_sites][vd_states] row-major copy
+  const int32_t* dj_inds_rm;
+  const double *v_gene_prob, *v_trans_prod, *vpad_trans, *jpad_trans;
+  CscDev t_v_vd, t_vd, t_vd_d, t_d_dj, t_dj, t_dj_j;
+  int32_t g_max, s_max;         // max genes per region, max states per region
+};
+
+struct BatchDev {
+  int32_t B, R;
+  const int4* plan;      // [B][T-1]
+  const double* pblen;   // [B][2T-3]
+  const double* er;      // [B][6]
+  const double* pi;      // [B][4]
+  const double* rates;   // [B][R]
+  double* eig;           // [B][kEigStride]
+  double* prec;          // [chunk][2T-3][20R] branch records
+  double* xe;            // [B][S] xmsa_emission
+  double* loglik;        // [B]
+};
+
+struct PruneCfg {
+  int32_t tile_sites;    // W = threads per CTA
+  int32_t n_tiles;
+  int32_t smem_slots;    // stack slots kept in shared memory
+  int32_t total_slots;   // stack slots the batch needs
+  int32_t grid;          // persistent CTAs
+  double* scratch;       // [grid][total_slots-smem_slots][4R][W] doubles
+  int32_t* scratch_cnt;  // [grid][total_slots-smem_slots][W]
+  double log_threshold;  // log(2^-256), host libm (core_likelihood_avx.c:1249)
+};
+
+struct HmmOut {           // optional device buffers (may be null)
+  double *vgerm_forward, *vd_forward, *dgerm_forward, *dj_forward, *jgerm_forward;
+  int32_t *germ_scalers, *vd_scalers, *dj_scalers;
+  double log_factor;      // log(2^256), host libm (src/HMM.cpp:353)
+};
+
+void launch_eigen(const BatchDev& b, cudaStream_t s);
+void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees, cudaStream_t s);
+void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0, int ntrees,
+                  cudaStream_t s);
+void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, cudaStream_t s);
+size_t prune_smem_bytes(int R, int tile_sites, int smem_slots);
+int prune_max_ctas_per_sm(int R, int tile_sites, int smem_slots);
+size_t hmm_smem_bytes(const FamilyDev& f, int warps);
+
+}  // namespace lhb

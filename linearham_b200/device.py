@@ -1,0 +1,93 @@
+"""Thin Python handle over the device C ABI (include/linearham_b200.h) for tests and bench.py.
+No arithmetic here; every number comes out of liblinearham_b200.so (CUDA, sm_100a).
+There is no fallback: if the library or a GPU is missing the calls raise."""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+
+_f64p = C.POINTER(C.c_double)
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = _abi.load_library()
+    return _lib
+
+
+class DeviceError(RuntimeError):
+    pass
+
+
+def device_count():
+    n = C.c_int()
+    if lib().lh_device_count(C.byref(n)):
+        return 0
+    return n.value
+
+
+class Family:
+    """Device-resident clonal family (lh_family_t)."""
+
+    def __init__(self, fam, device=0):
+        self.fam = fam
+        self._h = C.c_void_p()
+        d, keep = _abi.family_desc(fam)
+        if lib().lh_family_create(C.byref(self._h), C.byref(d), int(device)):
+            raise DeviceError(lib().lh_last_error().decode())
+        self._tb_keep = None
+
+    def close(self):
+        if self._h:
+            lib().lh_family_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc:
+            raise DeviceError(lib().lh_last_error().decode())
+
+    def set_option(self, key, value):
+        self._ck(lib().lh_set_option(self._h, key.encode(), int(value)))
+
+    def score(self, tb, outputs=False):
+        """Host buffers in, host results out (lh_score_batch). -> loglik[B] (, dict of read-outs)."""
+        t, keep = _abi.tree_batch(tb)
+        ll = np.zeros(t.n_trees)
+        if outputs:
+            o, arrs = _abi.alloc_outputs(self.fam, t.n_trees, None if outputs is True else outputs)
+            self._ck(lib().lh_score_batch(self._h, C.byref(t), ll.ctypes.data_as(_f64p), C.byref(o)))
+            return ll, arrs
+        self._ck(lib().lh_score_batch(self._h, C.byref(t), ll.ctypes.data_as(_f64p), None))
+        return ll
+
+    # split form --------------------------------------------------------------
+    def upload(self, tb):
+        t, keep = _abi.tree_batch(tb)
+        self._tb_keep = (t, keep)
+        self._ck(lib().lh_batch_upload(self._h, C.byref(t)))
+        self._n = t.n_trees
+
+    def run(self):
+        self._ck(lib().lh_batch_run(self._h))
+
+    def sync(self):
+        self._ck(lib().lh_sync(self._h))
+
+    def fetch(self):
+        ll = np.zeros(self._n)
+        self._ck(lib().lh_batch_fetch(self._h, ll.ctypes.data_as(_f64p), None))
+        return ll
+
+    def timings(self):
+        t = _abi.Timings()
+        self._ck(lib().lh_get_timings(self._h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in _abi.Timings._fields_}

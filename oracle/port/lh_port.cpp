@@ -46,7 +46,8 @@ double incomplete_gamma(double x, double alpha, double ln_gamma_alpha) {
       term *= x / rn;
       gin += term;
     } while (term > accurate);
-    return gin * factor / p;
+    gin *= factor / p;  // note: gin * (factor / p), as gamma.c:61
+    return gin;
   }
   // continued fraction
   double pn[6];

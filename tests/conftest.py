@@ -1,0 +1,38 @@
+import glob
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+GOLDEN_NAMES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def load_golden(name):
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"), allow_pickle=False)
+    fam = {k[4:]: (int(z[k]) if z[k].ndim == 0 else z[k]) for k in z.files if k.startswith("fam_")}
+    tb = {k[3:]: z[k] for k in z.files if k.startswith("tb_")}
+    exp = {k[4:]: z[k] for k in z.files if k.startswith("exp_")}
+    meta = {k: z[k] for k in ("alpha", "newicks", "labels", "xmsa_seqs")}
+    return fam, tb, exp, meta
+
+
+@pytest.fixture(params=GOLDEN_NAMES)
+def golden(request):
+    return (request.param,) + load_golden(request.param)
+
+
+def rel_err(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    denom = np.maximum(np.abs(b), 1e-300)
+    return float(np.max(np.abs(a - b) / denom)) if a.size else 0.0
