@@ -114,12 +114,21 @@ typedef struct lh_outputs {
 } lh_outputs_t;
 
 typedef struct lh_timings {
-  float ms_h2d, ms_plan, ms_pmatrix, ms_prune, ms_hmm, ms_d2h, ms_total;
+  float ms_h2d;              /* host->device copies of the batch (CUDA events)           */
+  float ms_plan;             /* host traversal planning (wall clock)                     */
+  float ms_pmatrix;          /* sum over k_pmatrix launches                              */
+  float ms_prune;            /* sum over k_prune launches                                */
+  float ms_hmm;              /* k_hmm                                                    */
+  float ms_d2h, ms_total;    /* device->host; first H2D event to last D2H event          */
+  float ms_kernels;          /* k_eigen start to k_hmm end                               */
   int32_t n_trees;
-  int32_t kernel_launches;   /* launches of this library's kernels            */
+  int32_t kernel_launches;   /* launches of this library's kernels                       */
+  int32_t prune_launches;    /* of which k_prune                                         */
   int64_t h2d_bytes, d2h_bytes;
-  int32_t prune_slots;       /* CLV stack depth the batch needed              */
-  int32_t prune_tile_sites;  /* xMSA columns per CTA                          */
+  int32_t prune_slots;       /* CLV stack depth the batch needed                         */
+  int32_t prune_smem_slots;  /* of which held in shared memory                           */
+  int32_t prune_tile_sites;  /* xMSA columns per CTA                                     */
+  int32_t prune_grid, prune_ctas_per_sm;
 } lh_timings_t;
 
 const char* lh_last_error(void);
@@ -143,8 +152,18 @@ int lh_sync(lh_family_t* fam);
 int lh_loglik_dev(lh_family_t* fam, const double** loglik_dev, int32_t* n); /* device ptr of the last run */
 
 int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/score */
+/* Diagnostic: sustained FP64 FMA rate of a register-resident DFMA loop (TFLOP/s); the
+ * denominator for the FP64-pipe view of the pruning kernel (no reference counterpart). */
+int lh_measure_fp64_peak(int device, double* tflops);
 int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
-/* keys: "tile_sites" (0 = auto), "smem_slots" (-1 = auto), "timing" (0/1)    */
+/* keys: "tile_sites" (0 = auto), "smem_slots" (-1 = auto), "timing" (0/1), "host_threads",
+ * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair), "stream" (a
+ * caller-owned cudaStream_t cast to int64; 0 = private stream)                          */
+
+/* CUDA-event stopwatch on the family's stream (8 slots), so callers can time a region of
+ * lh_batch_run calls on the stream the kernels are launched on.                          */
+int lh_timer_mark(lh_family_t* fam, int32_t slot);
+int lh_timer_elapsed_ms(lh_family_t* fam, int32_t from_slot, int32_t to_slot, float* ms);
 
 #ifdef __cplusplus
 }

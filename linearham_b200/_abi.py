@@ -59,9 +59,11 @@ class Timings(C.Structure):
     _fields_ = [
         ("ms_h2d", C.c_float), ("ms_plan", C.c_float), ("ms_pmatrix", C.c_float),
         ("ms_prune", C.c_float), ("ms_hmm", C.c_float), ("ms_d2h", C.c_float),
-        ("ms_total", C.c_float), ("n_trees", C.c_int32), ("kernel_launches", C.c_int32),
+        ("ms_total", C.c_float), ("ms_kernels", C.c_float),
+        ("n_trees", C.c_int32), ("kernel_launches", C.c_int32), ("prune_launches", C.c_int32),
         ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
-        ("prune_slots", C.c_int32), ("prune_tile_sites", C.c_int32),
+        ("prune_slots", C.c_int32), ("prune_smem_slots", C.c_int32), ("prune_tile_sites", C.c_int32),
+        ("prune_grid", C.c_int32), ("prune_ctas_per_sm", C.c_int32),
     ]
 
 
@@ -144,7 +146,8 @@ def alloc_outputs(fam, B, fields=None):
 DEVICE_SYMBOLS = [
     "lh_last_error", "lh_version", "lh_device_count", "lh_family_create", "lh_family_destroy",
     "lh_score_batch", "lh_batch_upload", "lh_batch_run", "lh_batch_fetch", "lh_sync",
-    "lh_loglik_dev", "lh_get_timings", "lh_set_option",
+    "lh_loglik_dev", "lh_get_timings", "lh_set_option", "lh_measure_fp64_peak",
+    "lh_timer_mark", "lh_timer_elapsed_ms",
 ]
 
 
@@ -170,4 +173,23 @@ def load_library(path=None):
     lib.lh_loglik_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int32)]
     lib.lh_get_timings.argtypes = [C.c_void_p, C.POINTER(Timings)]
     lib.lh_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
+    lib.lh_measure_fp64_peak.argtypes = [C.c_int, _f64p]
+    lib.lh_timer_mark.argtypes = [C.c_void_p, C.c_int32]
+    lib.lh_timer_elapsed_ms.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_float)]
+    return lib
+
+
+# ---- host-side C ABI (include/linearham_b200_host.h) ------------------------------------
+
+HOST_SYMBOLS = ["lhh_last_error", "lhh_plan_trees", "lhh_gamma_cats", "lhh_gamma_cats_batch",
+                "lhh_newick_to_ops"]
+
+
+def bind_host(lib):
+    lib.lhh_last_error.restype = C.c_char_p
+    lib.lhh_gamma_cats.argtypes = [C.c_double, C.c_int32, _f64p]
+    lib.lhh_gamma_cats_batch.argtypes = [C.c_int32, _f64p, C.c_int32, _f64p]
+    lib.lhh_newick_to_ops.argtypes = [C.c_int32, C.POINTER(C.c_char_p), C.c_int32, C.POINTER(C.c_char_p),
+                                      C.c_int32, _i32p, _f64p, _i32p, _f64p]
+    lib.lhh_plan_trees.argtypes = [C.c_int32, C.c_int32, _i32p, _f64p, _i32p, _f64p, _i32p, _f64p, _i32p]
     return lib

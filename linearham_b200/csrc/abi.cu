@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -131,6 +132,10 @@ struct lh_family {
   DevBuf d_vgerm, d_vd, d_dgerm, d_dj, d_jgerm, d_gs, d_vds, d_djs;
   PinBuf h_plan, h_pblen, h_misc, h_out;
   cudaEvent_t ev[8] = {};
+  cudaEvent_t user_ev[8] = {};
+  std::vector<cudaEvent_t> chunk_ev;  // 3 per chunk: pmatrix start, prune start, prune end
+  int n_chunks = 0;
+  bool own_stream = true;
   lh_timings_t tm{};
   bool want_tables = false;
 };
@@ -161,7 +166,10 @@ void lh_family_destroy(lh_family_t* f) {
   f->h_out.release();
   for (auto& e : f->ev)
     if (e) cudaEventDestroy(e);
-  if (f->stream) cudaStreamDestroy(f->stream);
+  for (auto& e : f->user_ev)
+    if (e) cudaEventDestroy(e);
+  for (auto& e : f->chunk_ev) cudaEventDestroy(e);
+  if (f->stream && f->own_stream) cudaStreamDestroy(f->stream);
   delete f;
 }
 
@@ -187,6 +195,7 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
   if (cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking) != cudaSuccess)
     return bail(fail("cudaStreamCreate failed"));
   for (auto& ev : f->ev) cudaEventCreate(&ev);
+  for (auto& ev : f->user_ev) cudaEventCreate(&ev);
 
   const int T = d->n_tips, S = d->n_sites;
   for (size_t i = 0; i < (size_t)T * S; ++i)
@@ -265,6 +274,19 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_threads = (int)value;
   } else if (k == "chunk_bytes") {
     f->opt_chunk_bytes = (size_t)value;
+  } else if (k == "stream") {
+    // run on a caller-owned CUDA stream (e.g. torch.cuda.current_stream().cuda_stream); 0 restores
+    // a private stream
+    cudaSetDevice(f->device);
+    if (f->stream) cudaStreamSynchronize(f->stream);
+    if (f->stream && f->own_stream) cudaStreamDestroy(f->stream);
+    if (value == 0) {
+      f->own_stream = true;
+      if (cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking) != cudaSuccess) return fail("cudaStreamCreate failed");
+    } else {
+      f->own_stream = false;
+      f->stream = reinterpret_cast<cudaStream_t>(static_cast<intptr_t>(value));
+    }
   } else {
     return fail("unknown option '%s'", k.c_str());
   }
@@ -350,7 +372,9 @@ int lh_batch_upload(lh_family_t* f, const lh_tree_batch_t* tb) {
   if (f->h_plan.reserve(plan_bytes) || f->h_pblen.reserve(pblen_bytes) ||
       f->h_misc.reserve(misc_doubles * sizeof(double)))
     return 1;
+  const auto plan_t0 = std::chrono::steady_clock::now();
   if (plan_batch(f, tb, f->h_plan.as<lhb::Step>(), f->h_pblen.as<double>(), &f->slots)) return 1;
+  f->tm.ms_plan = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - plan_t0).count();
   double* misc = f->h_misc.as<double>();
   std::memcpy(misc, tb->er, sizeof(double) * 6 * B);
   std::memcpy(misc + (size_t)6 * B, tb->pi, sizeof(double) * 4 * B);
@@ -409,8 +433,11 @@ int lh_batch_run(lh_family_t* f) {
   const size_t rec_bytes_tree = (size_t)NB * 20 * R * sizeof(double);
   int chunk = (int)std::max<size_t>(1, f->opt_chunk_bytes / rec_bytes_tree);
   const int resident = occ * f->num_sms;
-  // keep at least two waves of work items per launch when the batch allows it
-  chunk = std::max(chunk, (2 * resident + pc.n_tiles - 1) / pc.n_tiles);
+  // at least 16 waves of work items per launch when the batch allows it, so the partial last
+  // wave costs a few percent. The records then exceed L2 for large trees, which is harmless: they
+  // are written once and read once per site tile by CTAs that run at the same time (the tiles
+  // of a tree are adjacent work items), ~2.6 MB of DRAM traffic per 1001-tip tree.
+  chunk = std::max(chunk, (16 * resident + pc.n_tiles - 1) / pc.n_tiles);
   chunk = std::min(chunk, B);
   if (f->d_prec.reserve((size_t)chunk * rec_bytes_tree)) return 1;
   bd.prec = f->d_prec.as<double>();
@@ -446,15 +473,26 @@ int lh_batch_run(lh_family_t* f) {
 
   cudaStream_t s = f->stream;
   int launches = 0;
+  const int n_chunks = (B + chunk - 1) / chunk;
+  f->n_chunks = n_chunks;
+  if (f->opt_timing)
+    while ((int)f->chunk_ev.size() < 3 * n_chunks) {
+      cudaEvent_t e;
+      LH_CUDA(cudaEventCreate(&e));
+      f->chunk_ev.push_back(e);
+    }
   if (f->opt_timing) cudaEventRecord(f->ev[2], s);
   lhb::launch_eigen(bd, s);
   ++launches;
-  for (int t0 = 0; t0 < B; t0 += chunk) {
+  for (int t0 = 0, ci = 0; t0 < B; t0 += chunk, ++ci) {
     const int n = std::min(chunk, B - t0);
+    if (f->opt_timing) cudaEventRecord(f->chunk_ev[3 * ci], s);
     lhb::launch_pmatrix(f->fd, bd, t0, n, s);
+    if (f->opt_timing) cudaEventRecord(f->chunk_ev[3 * ci + 1], s);
     lhb::PruneCfg c = pc;
     c.grid = std::min(pc.grid, n * pc.n_tiles);
     lhb::launch_prune(f->fd, bd, c, t0, n, s);
+    if (f->opt_timing) cudaEventRecord(f->chunk_ev[3 * ci + 2], s);
     launches += 2;
   }
   if (f->opt_timing) cudaEventRecord(f->ev[3], s);
@@ -463,8 +501,30 @@ int lh_batch_run(lh_family_t* f) {
   if (f->opt_timing) cudaEventRecord(f->ev[4], s);
   LH_CUDA(cudaGetLastError());
   f->tm.kernel_launches = launches;
+  f->tm.prune_launches = n_chunks;
   f->tm.prune_slots = pc.total_slots;
   f->tm.prune_tile_sites = pc.tile_sites;
+  f->tm.prune_smem_slots = pc.smem_slots;
+  f->tm.prune_grid = pc.grid;
+  f->tm.prune_ctas_per_sm = occ;
+  return 0;
+}
+
+// Per-kernel device times of the last lh_batch_run (syncs the stream).
+static int collect_run_timings(lh_family* f) {
+  if (!f->opt_timing || f->B == 0) return 0;
+  LH_CUDA(cudaEventSynchronize(f->ev[4]));
+  float pm = 0, pr = 0, x = 0;
+  for (int ci = 0; ci < f->n_chunks; ++ci) {
+    cudaEventElapsedTime(&x, f->chunk_ev[3 * ci], f->chunk_ev[3 * ci + 1]);
+    pm += x;
+    cudaEventElapsedTime(&x, f->chunk_ev[3 * ci + 1], f->chunk_ev[3 * ci + 2]);
+    pr += x;
+  }
+  f->tm.ms_pmatrix = pm;
+  f->tm.ms_prune = pr;
+  cudaEventElapsedTime(&f->tm.ms_hmm, f->ev[3], f->ev[4]);
+  cudaEventElapsedTime(&f->tm.ms_kernels, f->ev[2], f->ev[4]);
   return 0;
 }
 
@@ -523,9 +583,8 @@ int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
   std::memcpy(loglik, f->h_out.p, (size_t)B * 8);
   f->tm.d2h_bytes = bytes;
   if (f->opt_timing) {
+    collect_run_timings(f);
     cudaEventElapsedTime(&f->tm.ms_h2d, f->ev[0], f->ev[1]);
-    cudaEventElapsedTime(&f->tm.ms_prune, f->ev[2], f->ev[3]);
-    cudaEventElapsedTime(&f->tm.ms_hmm, f->ev[3], f->ev[4]);
     cudaEventElapsedTime(&f->tm.ms_d2h, f->ev[5], f->ev[6]);
     cudaEventElapsedTime(&f->tm.ms_total, f->ev[0], f->ev[6]);
   }
@@ -541,9 +600,57 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   return lh_batch_fetch(f, loglik, o);
 }
 
+int lh_measure_fp64_peak(int device, double* tflops) {
+  if (!tflops) return fail("null argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return fail("no such CUDA device %d", device);
+  LH_CUDA(cudaSetDevice(device));
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const int blocks = sms * 8;
+  double* scratch = nullptr;
+  LH_CUDA(cudaMalloc(&scratch, (size_t)blocks * 256 * sizeof(double)));
+  cudaEvent_t a, b;
+  cudaEventCreate(&a);
+  cudaEventCreate(&b);
+  double best = 0.0;
+  for (int rep = 0; rep < 4; ++rep) {
+    cudaEventRecord(a, 0);
+    const double flops = lhb::fp64_peak_flops_per_launch(scratch, blocks, 4096, 0);
+    cudaEventRecord(b, 0);
+    cudaEventSynchronize(b);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    if (rep && ms > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  cudaFree(scratch);
+  LH_CUDA(cudaGetLastError());
+  *tflops = best;
+  return 0;
+}
+
 int lh_get_timings(lh_family_t* f, lh_timings_t* out) {
   if (!f || !out) return fail("null argument");
+  LH_CUDA(cudaSetDevice(f->device));
+  if (collect_run_timings(f)) return 1;
   *out = f->tm;
+  return 0;
+}
+
+int lh_timer_mark(lh_family_t* f, int32_t slot) {
+  if (!f || slot < 0 || slot >= 8) return fail("timer slot out of range");
+  LH_CUDA(cudaSetDevice(f->device));
+  LH_CUDA(cudaEventRecord(f->user_ev[slot], f->stream));
+  return 0;
+}
+
+int lh_timer_elapsed_ms(lh_family_t* f, int32_t a, int32_t b, float* ms) {
+  if (!f || !ms || a < 0 || a >= 8 || b < 0 || b >= 8) return fail("timer slot out of range");
+  LH_CUDA(cudaSetDevice(f->device));
+  LH_CUDA(cudaEventSynchronize(f->user_ev[b]));
+  LH_CUDA(cudaEventElapsedTime(ms, f->user_ev[a], f->user_ev[b]));
   return 0;
 }
 

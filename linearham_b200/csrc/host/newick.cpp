@@ -1,0 +1,211 @@
+// Host tree ingest: Newick strings -> the flat operation arrays of lh_tree_batch_t.
+//
+// Replaces, per tree sample, the reference's
+//   std::regex_replace("[&index=N]") + pll_utree_parse_newick_string   src/PhyloHMM.cpp:419-421
+//   set_missing_branch_length(tree, EPS)                               pll_util.cpp:46-62
+//   pll_utree_traverse(POSTORDER) + pll_utree_create_operations         utree.c:284-329, 379-442
+// without building a node graph: one pass over the characters, an explicit stack of open
+// parentheses, no allocation per node. Conventions kept from the reference:
+//   * grammar (parse_utree.y:179-246): top level "(a,b,c)" trifurcation, every other inner node
+//     binary, optional inner labels (ignored), optional ":length" (atof; missing -> 0)
+//   * the virtual root is the trifurcation; the likelihood is evaluated on the edge to its FIRST
+//     listed subtree (pll_util.cpp:368-371, pll_partition.cpp:309-315) -> root_child / root_blen
+//   * operations in post-order: subtrees in listed order, the trifurcation last with the second
+//     and third subtree as its children
+//   * a zero or missing branch length becomes EPS = 1e-6 (src/utils.hpp:20)
+// Tip labels are mapped to xMSA rows through the label list of the family (xmsa_labels_,
+// src/PhyloHMM.cpp:48-53; Partition::SetTipStates matches by label, pll_partition.cpp:153-194).
+#include <atomic>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../../../include/linearham_b200_host.h"
+#include "host_error.hpp"
+
+namespace lhb {
+namespace {
+
+constexpr double kEps = 1e-6;  // src/utils.hpp:20
+
+struct Open {        // one unclosed '('
+  int32_t n;         // children seen so far
+  int32_t id[3];
+  double len[3];
+};
+
+struct LabelMap {
+  std::unordered_map<std::string, int32_t> rows;
+};
+
+inline bool is_delim(char c) {
+  return c == '(' || c == ')' || c == ',' || c == ':' || c == ';' || c == '[' || c == ' ' || c == '\t' ||
+         c == '\n' || c == '\r' || c == '\0';
+}
+
+// skips blanks and [...] comments (the reference strips "[&index=N]" with a regex)
+inline const char* skip(const char* p) {
+  for (;;) {
+    while (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r') ++p;
+    if (*p != '[') return p;
+    while (*p && *p != ']') ++p;
+    if (*p == ']') ++p;
+  }
+}
+
+inline const char* branch_length(const char* p, double* len) {
+  p = skip(p);
+  double v = 0.0;
+  if (*p == ':') {
+    p = skip(p + 1);
+    char* end = nullptr;
+    v = std::strtod(p, &end);
+    if (end == p) return nullptr;
+    p = end;
+  }
+  *len = v ? v : kEps;
+  return p;
+}
+
+// Returns nullptr on success, else a static message.
+const char* flatten_one(const char* s, const LabelMap& labels, int T, std::vector<Open>& stack,
+                        std::vector<uint8_t>& seen, int32_t* children, double* blen, int32_t* root_child,
+                        double* root_blen, std::string& detail) {
+  const int n_ops = T - 2;
+  stack.clear();
+  seen.assign(T, 0);
+  int emitted = 0;
+  bool done = false;
+  const char* p = skip(s);
+  if (*p != '(') return "tree does not start with '('";
+  while (!done) {
+    p = skip(p);
+    const char c = *p;
+    if (c == '(') {
+      stack.push_back(Open{0, {0, 0, 0}, {0, 0, 0}});
+      ++p;
+    } else if (c == ',') {
+      ++p;
+    } else if (c == ')') {
+      ++p;
+      if (stack.empty()) return "unbalanced ')'";
+      const Open o = stack.back();
+      stack.pop_back();
+      p = skip(p);
+      while (!is_delim(*p)) ++p;  // inner label, ignored
+      if (stack.empty()) {
+        // the trifurcation (a trailing ":len" on it is accepted and ignored)
+        double ignored;
+        const char* q = branch_length(p, &ignored);
+        if (!q) return "malformed branch length";
+        p = skip(q);
+        if (*p != ';') return "expected ';' after the top-level node";
+        if (o.n != 3) return "top level must have exactly three subtrees";
+        if (emitted != n_ops - 1) return "wrong number of tips for this family";
+        children[2 * emitted] = o.id[1];
+        children[2 * emitted + 1] = o.id[2];
+        blen[2 * emitted] = o.len[1];
+        blen[2 * emitted + 1] = o.len[2];
+        ++emitted;
+        *root_child = o.id[0];
+        *root_blen = o.len[0];
+        done = true;
+      } else {
+        if (o.n != 2) return "inner nodes must be binary";
+        if (emitted >= n_ops - 1) return "wrong number of tips for this family";
+        double len;
+        p = branch_length(p, &len);
+        if (!p) return "malformed branch length";
+        children[2 * emitted] = o.id[0];
+        children[2 * emitted + 1] = o.id[1];
+        blen[2 * emitted] = o.len[0];
+        blen[2 * emitted + 1] = o.len[1];
+        Open& up = stack.back();
+        if (up.n >= 3) return "node with more than three children";
+        up.id[up.n] = T + emitted;
+        up.len[up.n] = len;
+        ++up.n;
+        ++emitted;
+      }
+    } else if (c == '\0' || c == ';' || c == ':') {
+      return "unexpected end of tree";
+    } else {
+      const char* b = p;
+      while (!is_delim(*p)) ++p;
+      if (stack.empty()) return "tip outside parentheses";
+      std::string name(b, p - b);
+      auto it = labels.rows.find(name);
+      if (it == labels.rows.end()) {
+        detail = name;
+        return "tip label is not a sequence of this family";
+      }
+      if (seen[it->second]) {
+        detail = name;
+        return "tip label appears twice";
+      }
+      seen[it->second] = 1;
+      double len;
+      p = branch_length(p, &len);
+      if (!p) return "malformed branch length";
+      Open& up = stack.back();
+      if (up.n >= 3) return "node with more than three children";
+      up.id[up.n] = it->second;
+      up.len[up.n] = len;
+      ++up.n;
+    }
+  }
+  for (int i = 0; i < T; ++i)
+    if (!seen[i]) return "tree is missing a sequence of this family";
+  return nullptr;
+}
+
+}  // namespace
+}  // namespace lhb
+
+extern "C" int lhh_newick_to_ops(int32_t n_tips, const char* const* labels, int32_t n_trees,
+                                 const char* const* newicks, int32_t n_threads, int32_t* children,
+                                 double* blen, int32_t* root_child, double* root_blen) {
+  using namespace lhb;
+  if (n_tips < 3) return host_fail("need at least 3 tips (got %d)", n_tips);
+  LabelMap map;
+  for (int i = 0; i < n_tips; ++i)
+    if (!map.rows.emplace(labels[i], i).second) return host_fail("duplicate label '%s'", labels[i]);
+  const size_t per = (size_t)(n_tips - 2) * 2;
+  int nt = n_threads > 0 ? n_threads : (int)std::thread::hardware_concurrency();
+  nt = std::max(1, std::min(nt, std::min(64, (n_trees + 63) / 64)));
+  std::atomic<int> bad(-1);
+  std::vector<std::string> msg(nt);
+  auto work = [&](int tid) {
+    std::vector<Open> stack;
+    std::vector<uint8_t> seen;
+    stack.reserve(256);
+    for (int t = tid; t < n_trees; t += nt) {
+      std::string detail;
+      const char* err = flatten_one(newicks[t], map, n_tips, stack, seen, children + t * per, blen + t * per,
+                                    root_child + t, root_blen + t, detail);
+      if (err) {
+        int expect = -1;
+        if (bad.compare_exchange_strong(expect, t))
+          msg[tid] = std::string(err) + (detail.empty() ? "" : " ('" + detail + "')");
+        return;
+      }
+    }
+  };
+  if (nt == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int i = 0; i < nt; ++i) th.emplace_back(work, i);
+    for (auto& t : th) t.join();
+  }
+  if (bad.load() >= 0) {
+    std::string m;
+    for (auto& s : msg)
+      if (!s.empty()) m = s;
+    return host_fail("tree %d: %s", bad.load(), m.c_str());
+  }
+  return 0;
+}

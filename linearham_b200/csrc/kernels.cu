@@ -624,4 +624,24 @@ void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, cudaStre
   k_hmm<<<blocks, warps * 32, smem, s>>>(f, b, o);
 }
 
+// ------------------------------------------------------------- diagnostics ---
+// Register-resident DFMA loop: the FP64 denominator for the on-chip pruning regime
+// (MEASURED_PEAKS.json has no FP64 entry). 8 independent chains per thread.
+__global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters, double a, double b) {
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+      x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+    }
+  }
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+
+double fp64_peak_flops_per_launch(double* scratch, int blocks, int iters, cudaStream_t s) {
+  k_fp64_peak<<<blocks, 256, 0, s>>>(scratch, iters, 0.999999, 1e-9);
+  return 2.0 * 64.0 * iters * 256.0 * blocks;
+}
+
 }  // namespace lhb

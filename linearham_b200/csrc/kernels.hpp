@@ -67,5 +67,7 @@ void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, cudaStre
 size_t prune_smem_bytes(int R, int tile_sites, int smem_slots);
 int prune_max_ctas_per_sm(int R, int tile_sites, int smem_slots);
 size_t hmm_smem_bytes(const FamilyDev& f, int warps);
+// launches the DFMA diagnostic kernel; returns the flop count of the launch
+double fp64_peak_flops_per_launch(double* scratch, int blocks, int iters, cudaStream_t s);
 
 }  // namespace lhb

@@ -29,6 +29,14 @@ def device_count():
     return n.value
 
 
+def fp64_peak_tflops(device=0):
+    """Measured DFMA rate of this GPU (diagnostic kernel in the library)."""
+    v = C.c_double()
+    if lib().lh_measure_fp64_peak(int(device), C.byref(v)):
+        raise DeviceError(lib().lh_last_error().decode())
+    return v.value
+
+
 class Family:
     """Device-resident clonal family (lh_family_t)."""
 
@@ -86,6 +94,20 @@ class Family:
         ll = np.zeros(self._n)
         self._ck(lib().lh_batch_fetch(self._h, ll.ctypes.data_as(_f64p), None))
         return ll
+
+    def mark(self, slot):
+        self._ck(lib().lh_timer_mark(self._h, int(slot)))
+
+    def elapsed_ms(self, a, b):
+        ms = C.c_float()
+        self._ck(lib().lh_timer_elapsed_ms(self._h, int(a), int(b), C.byref(ms)))
+        return ms.value
+
+    def loglik_dev(self):
+        """(device pointer, n) of the log-likelihoods of the last run."""
+        p, n = C.c_void_p(), C.c_int32()
+        self._ck(lib().lh_loglik_dev(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
 
     def timings(self):
         t = _abi.Timings()

@@ -251,9 +251,16 @@ def evolve(rng, tree, naive_seq):
     return seqs
 
 
-def tree_samples(rng, tree, B):
-    """Sample 0 = `tree`; sample i = sample i-1 after Poisson(3) NNIs and LogNormal(0,0.3) branch noise."""
+def tree_samples(rng, tree, B, walk="anchored"):
+    """Sample 0 = `tree`; sample i = sample i-1 after Poisson(3) NNIs, with LogNormal(0,0.3) branch noise.
+
+    walk="anchored" (default): the noise multiplies the branch lengths of `tree` (node ids are stable
+    under NNI), so lengths stay on the scale of the family however long the chain is.
+    walk="cumulative": the noise compounds from sample to sample (SURVEY.md 8(d) as written). Over
+    thousands of samples the lengths random-walk over many orders of magnitude and the reference
+    itself returns inf/NaN; the committed golden bundles (<= 6 samples) were made this way."""
     cur = tree.copy()
+    base = list(tree.blen)
     out = []
     for i in range(B):
         if i:
@@ -261,7 +268,8 @@ def tree_samples(rng, tree, B):
             for _ in range(int(rng.poisson(3))):
                 cur.nni(rng)
             for j in range(1, len(cur.blen)):
-                cur.blen[j] *= float(rng.lognormal(0.0, 0.3))
+                noise = float(rng.lognormal(0.0, 0.3))
+                cur.blen[j] = (cur.blen[j] if walk == "cumulative" else base[j]) * noise
         er = rng.dirichlet(np.ones(6))
         pi = np.maximum(rng.dirichlet(np.ones(4)), 0.01)
         pi /= pi.sum()

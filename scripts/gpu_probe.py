@@ -34,7 +34,7 @@ def probe(name, opts_list, n_port=2, reps=3):
             tm = f.timings()
             if best is None or tm["ms_prune"] < best["ms_prune"]:
                 best = dict(tm); best["wall_e2e_s"] = t
-        assert np.array_equal(ll, ll2)
+        assert np.array_equal(ll, ll2, equal_nan=True)
         tps = B / (best["ms_prune"] + best["ms_hmm"]) * 1e3
         print(json.dumps({"bundle": name, "opts": opts, "B": B, "T": T, "S": S, "err_vs_ref": float(err_ref),
                           "err_vs_port": float(err_port), "ms_prune_stage": best["ms_prune"], "ms_hmm": best["ms_hmm"],
@@ -45,5 +45,6 @@ def probe(name, opts_list, n_port=2, reps=3):
         f.close()
 
 if __name__ == "__main__":
+    print(json.dumps({"fp64_peak_tflops": device.fp64_peak_tflops(0)}), flush=True)
     probe("probe_c3", [{}, {"smem_slots": 0}, {"tile_sites": 64}, {"tile_sites": 256}, {"chunk_bytes": 1 << 30}])
     probe("probe_c4", [{}, {"smem_slots": 0}], n_port=1)

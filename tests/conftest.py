@@ -10,7 +10,10 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
-GOLDEN_NAMES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+# sample bundles (family + tree batch + reference outputs); family_*.npz hold a family description only
+GOLDEN_NAMES = sorted(n for n in (os.path.splitext(os.path.basename(p))[0]
+                                  for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+                      if not n.startswith("family_"))
 
 
 def pytest_configure(config):
@@ -24,6 +27,13 @@ def load_golden(name):
     exp = {k[4:]: z[k] for k in z.files if k.startswith("exp_")}
     meta = {k: z[k] for k in ("alpha", "newicks", "labels", "xmsa_seqs")}
     return fam, tb, exp, meta
+
+
+def load_family_bundle(name):
+    """tests/golden/family_<name>.npz -> (family dict, labels, sha of the generating files)."""
+    z = np.load(os.path.join(GOLDEN_DIR, f"family_{name}.npz"), allow_pickle=False)
+    fam = {k[4:]: (int(z[k]) if z[k].ndim == 0 else z[k]) for k in z.files if k.startswith("fam_")}
+    return fam, [str(s) for s in z["labels"]], str(z["sha"])
 
 
 @pytest.fixture(params=GOLDEN_NAMES)

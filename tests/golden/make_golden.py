@@ -93,7 +93,7 @@ def main():
         for name, n, B, R, seed in [("synth_n12", 12, 6, 4, 1301), ("synth_n40", 40, 4, 4, 1302),
                                     ("synth_n24_r1", 24, 3, 1, 1303), ("synth_n200", 200, 2, 4, 1304)]:
             fam = synth.make_family(d, genes, n, seed=seed, name=name)
-            samples = synth.tree_samples(np.random.default_rng(seed + 1000), fam["tree"], B)
+            samples = synth.tree_samples(np.random.default_rng(seed + 1000), fam["tree"], B, walk="cumulative")
             bundle(name, fam["yaml_path"], os.path.join(d, "hmm"), samples, R)
 
 
