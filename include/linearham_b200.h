@@ -128,6 +128,7 @@ typedef struct lh_timings {
   int32_t prune_slots;       /* CLV stack depth the batch needed                         */
   int32_t prune_smem_slots;  /* of which held in shared memory                           */
   int32_t prune_tile_sites;  /* xMSA columns per CTA                                     */
+  int32_t prune_sites_per_thread;
   int32_t prune_grid, prune_ctas_per_sm;
 } lh_timings_t;
 
@@ -156,7 +157,8 @@ int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/scor
  * denominator for the FP64-pipe view of the pruning kernel (no reference counterpart). */
 int lh_measure_fp64_peak(int device, double* tflops);
 int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
-/* keys: "tile_sites" (0 = auto), "smem_slots" (-1 = auto), "timing" (0/1), "host_threads",
+/* keys: "cta_threads" (0 = auto; 32..128), "sites_per_thread" (0 = auto; xMSA columns per
+ * thread), "smem_slots" (-1 = auto), "timing" (0/1), "host_threads",
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair), "stream" (a
  * caller-owned cudaStream_t cast to int64; 0 = private stream)                          */
 

@@ -124,7 +124,7 @@ struct lh_family {
   lhb::FamilyDev fd{};
   std::vector<void*> owned;  // family-constant device allocations
   // options
-  int opt_tile_sites = 0, opt_smem_slots = -1, opt_timing = 1, opt_threads = 0;
+  int opt_cta_threads = 0, opt_sites_per_thread = 0, opt_smem_slots = -1, opt_timing = 1, opt_threads = 0;
   size_t opt_chunk_bytes = 48u << 20;
   // batch state
   int B = 0, R = 0, slots = 0;
@@ -263,9 +263,12 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
 
 int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
   std::string k(key ? key : "");
-  if (k == "tile_sites") {
-    if (value != 0 && (value < 32 || value > 256 || value % 32)) return fail("tile_sites must be 0 or a multiple of 32 in 32..256");
-    f->opt_tile_sites = (int)value;
+  if (k == "cta_threads") {
+    if (value != 0 && (value < 32 || value > 128 || value % 32)) return fail("cta_threads must be 0 or a multiple of 32 in 32..128");
+    f->opt_cta_threads = (int)value;
+  } else if (k == "sites_per_thread") {
+    if (value < 0 || value > 8 || value == 7) return fail("sites_per_thread must be 0 (auto), 1..6 or 8");
+    f->opt_sites_per_thread = (int)value;
   } else if (k == "smem_slots") {
     f->opt_smem_slots = (int)value;
   } else if (k == "timing") {
@@ -297,14 +300,17 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
 
 namespace {
 
-int pick_tile_sites(int S) {
-  static const int cand[] = {128, 160, 192, 224, 256, 96, 64, 32};
-  int best = 128, best_waste = 1 << 30;
-  for (int w : cand) {
-    int waste = ((S + w - 1) / w) * w - S;
-    if (waste < best_waste) {
-      best_waste = waste;
-      best = w;
+// xMSA columns per thread: fewest padded columns over the whole xMSA; ties go to the smaller
+// register footprint.
+int pick_sites_per_thread(int S, int threads) {
+  if (S <= 4 * threads) return std::max(1, (S + threads - 1) / threads);
+  int best = 4, best_pad = 1 << 30;
+  for (int ns : {4, 5, 6}) {
+    const int tile = ns * threads;
+    const int pad = ((S + tile - 1) / tile) * tile - S;
+    if (pad < best_pad) {
+      best_pad = pad;
+      best = ns;
     }
   }
   return best;
@@ -411,21 +417,23 @@ int lh_batch_run(lh_family_t* f) {
 
   // pruning configuration
   lhb::PruneCfg pc{};
-  pc.tile_sites = f->opt_tile_sites ? f->opt_tile_sites : pick_tile_sites(S);
-  pc.n_tiles = (S + pc.tile_sites - 1) / pc.tile_sites;
+  pc.threads = f->opt_cta_threads ? f->opt_cta_threads : 32;
+  pc.sites_per_thread = f->opt_sites_per_thread ? f->opt_sites_per_thread : pick_sites_per_thread(S, pc.threads);
+  const int tile_sites = pc.threads * pc.sites_per_thread;
+  pc.n_tiles = (S + tile_sites - 1) / tile_sites;
   pc.total_slots = f->slots;
-  const size_t slot_bytes = (size_t)pc.tile_sites * (4 * R * sizeof(double) + sizeof(int));
-  int occ0 = lhb::prune_max_ctas_per_sm(R, pc.tile_sites, 0);
-  if (occ0 < 1) return fail("pruning kernel cannot be resident (R=%d, tile=%d)", R, pc.tile_sites);
+  const size_t slot_bytes = (size_t)tile_sites * (4 * sizeof(double) + sizeof(int));
+  int occ0 = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.threads, 0);
+  if (occ0 < 1) return fail("pruning kernel cannot be resident (sites/thread=%d, threads=%d)", pc.sites_per_thread, pc.threads);
   int smem_slots = f->opt_smem_slots;
   if (smem_slots < 0) {
     size_t per_cta = (size_t)(227 * 1024) / occ0 - 1024;
     smem_slots = (int)(per_cta / slot_bytes);
   }
   smem_slots = std::max(0, std::min(smem_slots, pc.total_slots));
-  while (smem_slots > 0 && lhb::prune_smem_bytes(R, pc.tile_sites, smem_slots) > (size_t)227 * 1024) --smem_slots;
+  while (smem_slots > 0 && lhb::prune_smem_bytes(pc.sites_per_thread, pc.threads, smem_slots) > (size_t)227 * 1024) --smem_slots;
   pc.smem_slots = smem_slots;
-  int occ = lhb::prune_max_ctas_per_sm(R, pc.tile_sites, pc.smem_slots);
+  int occ = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.threads, pc.smem_slots);
   if (occ < 1) return fail("pruning kernel cannot be resident with %d shared-memory slots", pc.smem_slots);
   pc.log_threshold = std::log(1.0 / std::pow(2.0, 256));
 
@@ -444,8 +452,8 @@ int lh_batch_run(lh_family_t* f) {
   pc.grid = std::min(resident, chunk * pc.n_tiles);
   const int gslots = pc.total_slots - pc.smem_slots;
   if (gslots > 0) {
-    if (f->d_scratch.reserve((size_t)pc.grid * gslots * 4 * R * pc.tile_sites * sizeof(double)) ||
-        f->d_scratch_cnt.reserve((size_t)pc.grid * gslots * pc.tile_sites * sizeof(int)))
+    if (f->d_scratch.reserve((size_t)pc.grid * gslots * 4 * tile_sites * sizeof(double)) ||
+        f->d_scratch_cnt.reserve((size_t)pc.grid * gslots * tile_sites * sizeof(int)))
       return 1;
   }
   pc.scratch = f->d_scratch.as<double>();
@@ -503,7 +511,8 @@ int lh_batch_run(lh_family_t* f) {
   f->tm.kernel_launches = launches;
   f->tm.prune_launches = n_chunks;
   f->tm.prune_slots = pc.total_slots;
-  f->tm.prune_tile_sites = pc.tile_sites;
+  f->tm.prune_tile_sites = tile_sites;
+  f->tm.prune_sites_per_thread = pc.sites_per_thread;
   f->tm.prune_smem_slots = pc.smem_slots;
   f->tm.prune_grid = pc.grid;
   f->tm.prune_ctas_per_sm = occ;

@@ -19,8 +19,8 @@
 
 namespace lhb {
 
-#define LH_SCALE_FACTOR 1.157920892373162e+77            /* 2^256  (utils.hpp:22, pll.h:89-93) */
-#define LH_SCALE_THRESHOLD 8.636168555094445e-78         /* 2^-256 */
+#define LH_SCALE_FACTOR 0x1p+256             /* 2^256  (utils.hpp:22, pll.h:89-93) */
+#define LH_SCALE_THRESHOLD 0x1p-256         /* 2^-256 */
 
 // ------------------------------------------------------------------ k_eigen ---
 
@@ -191,230 +191,293 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 }
 
 // ------------------------------------------------------------------ k_prune ---
-// Persistent CTAs; a work item is (tree, tile of W xMSA columns); thread = one column.
-// The thread walks the tree's program (plan.hpp). Inner CLVs never exist as arrays in
-// HBM: the running result stays in registers (reg[R][4]), results parked for a later
-// step go to a per-column stack whose first `smem_slots` levels are shared memory
-// ([slot][k*4+j][W], conflict-free because a column is only ever touched by its own
+// Persistent CTAs; a work item is (tree, tile of W*NS xMSA columns); a thread owns NS columns
+// (column tile_base + u*W + tid, u < NS) and walks the tree's program (plan.hpp) once per rate
+// category ("category-outer"): the categories of a site never mix before the edge likelihood,
+// so a pass needs only 4 doubles of state per column. That lets one thread carry NS columns in
+// registers, and the 4x4 transition matrix of a branch, loaded once into registers, is used for
+// NS columns. The matrix loads are warp-uniform but still cost 512 B of L1 data-pipe per warp per
+// LDG.128; with one column per thread that pipe, not the FP64 pipe, bounded the kernel (ncu,
+// profiles/r1a: lsu wavefronts 57 %, fp64 14 %).
+//
+// Inner CLVs never exist as arrays in HBM: the running result stays in registers, results
+// parked for a later step go to a per-column stack whose first `smem_slots` levels are shared
+// memory ([slot][u][state][W], conflict-free because a column is only ever touched by its own
 // thread) and whose deeper levels are an L2-resident scratch ring private to the CTA.
 // No barriers: threads never exchange data.
+//
+// Scaling. libpll rescales a site by 2^256 when ALL 4R entries of a node are below 2^-256
+// (core_partials.c:648-659). Here each category keeps its own count and rescales when its own 4
+// entries are below the threshold; the counts are reconciled exactly (powers of two) when the
+// categories are summed at the root edge. The two schemes give the same doubles whenever the
+// reference's unscaled categories stay normal numbers; where they would go subnormal in the
+// reference, this kernel keeps their full precision (a relative contribution < 2^-256).
 
-template <int R>
+template <int NS>
 struct SlotIO {
-  double* smem_clv;   // [smem_slots][4R][W]
-  int* smem_cnt;      // [smem_slots][W]
-  double* g_clv;      // [gslots][4R][W] (this CTA)
-  int* g_cnt;         // [gslots][W]
+  double* smem_clv;   // [smem_slots][NS*4][W]
+  int* smem_cnt;      // [smem_slots][NS][W]
+  double* g_clv;      // [gslots][NS*4][W] (this CTA)
+  int* g_cnt;         // [gslots][NS][W]
   int smem_slots, W, tid;
 
   __device__ __forceinline__ void locate(int slot, double*& clv, int*& cnt) const {
     if (slot < smem_slots) {
-      clv = smem_clv + (size_t)slot * (4 * R) * W + tid;
-      cnt = smem_cnt + slot * W + tid;
+      clv = smem_clv + (size_t)slot * (4 * NS) * W + tid;
+      cnt = smem_cnt + slot * NS * W + tid;
     } else {
-      clv = g_clv + (size_t)(slot - smem_slots) * (4 * R) * W + tid;
-      cnt = g_cnt + (slot - smem_slots) * W + tid;
+      clv = g_clv + (size_t)(slot - smem_slots) * (4 * NS) * W + tid;
+      cnt = g_cnt + (slot - smem_slots) * NS * W + tid;
     }
   }
 };
 
-// message of an inner child through its branch: m[i] = sum_j P[k][i][j] * c[j]
-// (core_partials.c:617-624)
-__device__ __forceinline__ void matvec4(const double* __restrict__ Pk, const double c[4], double m[4]) {
+// v < 2^-256 on the high word: 2^-256 = 0x2FF0000000000000, so for v >= +0 the comparison of the
+// bit patterns reduces to the high words, and every negative v (sign bit set) is below the
+// threshold as a signed integer too. Keeps the test off the FP64 pipe.
+__device__ __forceinline__ bool below_threshold(double v) { return __double2hiint(v) < 0x2FF00000; }
+
+// Per-category messages of one child for the NS columns of this thread, m[u][i] =
+// sum_j P[k][i][j] * c[u][j] (core_partials.c:617-624); returns the child's scaler counts.
+template <int NS>
+__device__ __forceinline__ void child_messages(int src, const double* __restrict__ rec, int k,
+                                               const double (&reg)[NS][4], const int (&reg_cnt)[NS],
+                                               const SlotIO<NS>& io, const uint8_t* __restrict__ codes,
+                                               int S, const int (&site)[NS], double (&m)[NS][4],
+                                               int (&cnt)[NS]) {
+  if (src >= 0) {  // tip: column `code` of Q (k_pmatrix), one 32-byte lookup per site
+    const uint8_t* __restrict__ row = codes + (size_t)src * S;
+    const double* __restrict__ Qk = rec + k * 20;
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+      const int code = __ldg(row + site[u]);
+      const double2 q01 = __ldg(reinterpret_cast<const double2*>(Qk + 4 * code));
+      const double2 q23 = __ldg(reinterpret_cast<const double2*>(Qk + 4 * code + 2));
+      m[u][0] = q01.x; m[u][1] = q01.y; m[u][2] = q23.x; m[u][3] = q23.y;
+      cnt[u] = 0;
+    }
+    return;
+  }
+  double P[4][4];
+  const double* __restrict__ Pk = rec + k * 16;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const double2 p01 = __ldg(reinterpret_cast<const double2*>(Pk + 4 * i));
     const double2 p23 = __ldg(reinterpret_cast<const double2*>(Pk + 4 * i + 2));
-    double acc = p01.x * c[0];
-    acc += p01.y * c[1];
-    acc += p23.x * c[2];
-    acc += p23.y * c[3];
-    m[i] = acc;
-  }
-}
-
-__device__ __forceinline__ void tipvec4(const double* __restrict__ Qk, int code, double m[4]) {
-  const double2 q01 = __ldg(reinterpret_cast<const double2*>(Qk + 4 * code));
-  const double2 q23 = __ldg(reinterpret_cast<const double2*>(Qk + 4 * code + 2));
-  m[0] = q01.x; m[1] = q01.y; m[2] = q23.x; m[3] = q23.y;
-}
-
-// Computes the per-category messages of one child into m[R][4]; returns its scaler count.
-template <int R>
-__device__ __forceinline__ int child_messages(int src, const double* __restrict__ rec,
-                                              const double (&reg)[R][4], int reg_cnt,
-                                              const SlotIO<R>& io, const uint8_t* __restrict__ codes,
-                                              int S, int site, double (&m)[R][4]) {
-  if (src >= 0) {
-    const int code = __ldg(codes + (size_t)src * S + site);
-#pragma unroll
-    for (int k = 0; k < R; ++k) tipvec4(rec + k * 20, code, m[k]);
-    return 0;
+    P[i][0] = p01.x; P[i][1] = p01.y; P[i][2] = p23.x; P[i][3] = p23.y;
   }
   if (src == -1) {
 #pragma unroll
-    for (int k = 0; k < R; ++k) matvec4(rec + k * 16, reg[k], m[k]);
-    return reg_cnt;
+    for (int u = 0; u < NS; ++u) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        double acc = P[i][0] * reg[u][0];
+        acc += P[i][1] * reg[u][1];
+        acc += P[i][2] * reg[u][2];
+        acc += P[i][3] * reg[u][3];
+        m[u][i] = acc;
+      }
+      cnt[u] = reg_cnt[u];
+    }
+    return;
   }
   double* clv;
-  int* cnt;
-  io.locate(-2 - src, clv, cnt);
+  int* pc;
+  io.locate(-2 - src, clv, pc);
 #pragma unroll
-  for (int k = 0; k < R; ++k) {
+  for (int u = 0; u < NS; ++u) {
     double c[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) c[j] = clv[(size_t)(k * 4 + j) * io.W];
-    matvec4(rec + k * 16, c, m[k]);
+    for (int j = 0; j < 4; ++j) c[j] = clv[(size_t)(u * 4 + j) * io.W];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      double acc = P[i][0] * c[0];
+      acc += P[i][1] * c[1];
+      acc += P[i][2] * c[2];
+      acc += P[i][3] * c[3];
+      m[u][i] = acc;
+    }
+    cnt[u] = pc[u * io.W];
   }
-  return *cnt;
 }
 
-template <int R>
-__global__ void __launch_bounds__(256) k_prune(FamilyDev f, BatchDev b, PruneCfg cfg, int tree0, int ntrees) {
+template <int NS>
+__global__ void __launch_bounds__(128) k_prune(FamilyDev f, BatchDev b, PruneCfg cfg, int tree0, int ntrees) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int W = cfg.tile_sites, tid = threadIdx.x, T = f.T, S = f.S;
+  const int W = blockDim.x, tid = threadIdx.x, T = f.T, S = f.S, R = b.R;
   const int NB = 2 * T - 3, REC = 20 * R, n_steps = T - 2;
   const int gslots = cfg.total_slots - cfg.smem_slots;
-  SlotIO<R> io;
+  SlotIO<NS> io;
   io.smem_clv = reinterpret_cast<double*>(smem_raw);
-  io.smem_cnt = reinterpret_cast<int*>(io.smem_clv + (size_t)cfg.smem_slots * (4 * R) * W);
-  io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * R) * W;
-  io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * W;
+  io.smem_cnt = reinterpret_cast<int*>(io.smem_clv + (size_t)cfg.smem_slots * (4 * NS) * W);
+  io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * NS) * W;
+  io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * W;
   io.smem_slots = cfg.smem_slots;
   io.W = W;
   io.tid = tid;
+  const double weight = 1.0 / R;  // pll.c:746-747
+  constexpr double kDown = LH_SCALE_THRESHOLD;
 
   const int n_work = ntrees * cfg.n_tiles;
   for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
     const int lt = w / cfg.n_tiles, tile = w - lt * cfg.n_tiles;
     const int t = tree0 + lt;
-    const int site = tile * W + tid;
-    if (site >= S) continue;
+    int site[NS];
+    bool live[NS];
+    bool any_live = false;
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+      const int s = tile * (W * NS) + u * W + tid;
+      live[u] = s < S;
+      any_live = any_live || live[u];
+      site[u] = live[u] ? s : S - 1;  // padding columns recompute the last column, never stored
+    }
+    if (!any_live) continue;
     const int4* __restrict__ plan = b.plan + (size_t)t * (T - 1);
     const double* __restrict__ recs = b.prec + (size_t)lt * NB * REC;
-
-    double reg[R][4];
-    int reg_cnt = 0;
-#pragma unroll
-    for (int k = 0; k < R; ++k)
-#pragma unroll
-      for (int i = 0; i < 4; ++i) reg[k][i] = 0.0;
-
-    for (int s = 0; s < n_steps; ++s) {
-      const int4 st = __ldg(plan + s);
-      const double* recA = recs + (size_t)(2 * s) * REC;
-      double ma[R][4], mb[R][4];
-      const int ca = child_messages<R>(st.x, recA, reg, reg_cnt, io, f.tip_codes, S, site, ma);
-      const int cb = child_messages<R>(st.y, recA + REC, reg, reg_cnt, io, f.tip_codes, S, site, mb);
-      bool all_small = true;
-#pragma unroll
-      for (int k = 0; k < R; ++k)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const double v = ma[k][i] * mb[k][i];  // core_partials.c:626
-          reg[k][i] = v;
-          all_small = all_small && (v < LH_SCALE_THRESHOLD);
-        }
-      reg_cnt = ca + cb;            // fill_parent_scaler, core_partials.c:24-46
-      if (all_small) {              // per-site scaling, core_partials.c:648-659
-#pragma unroll
-        for (int k = 0; k < R; ++k)
-#pragma unroll
-          for (int i = 0; i < 4; ++i) reg[k][i] *= LH_SCALE_FACTOR;
-        reg_cnt += 1;
-      }
-      if (st.z >= 0) {
-        double* clv;
-        int* cnt;
-        io.locate(st.z, clv, cnt);
-#pragma unroll
-        for (int k = 0; k < R; ++k)
-#pragma unroll
-          for (int i = 0; i < 4; ++i) clv[(size_t)(k * 4 + i) * W] = reg[k][i];
-        *cnt = reg_cnt;
-      }
-    }
-
-    // ---- edge likelihood at the virtual root (core_likelihood_avx.c:1130-1260) ----
-    const int4 fin = __ldg(plan + n_steps);
-    const double* recE = recs + (size_t)(NB - 1) * REC;
-    const double* eig = b.eig + (size_t)t * kEigStride;
-    double mc[R][4];
-    const int cc = child_messages<R>(fin.y, recE, reg, reg_cnt, io, f.tip_codes, S, site, mc);
-    int cp = reg_cnt;
-    if (fin.x != -1) {  // the root CLV was parked; fetch it
-      double* clv;
-      int* cnt;
-      io.locate(-2 - fin.x, clv, cnt);
-#pragma unroll
-      for (int k = 0; k < R; ++k)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) reg[k][i] = clv[(size_t)(k * 4 + i) * W];
-      cp = *cnt;
-    }
+    const double* __restrict__ eig = b.eig + (size_t)t * kEigStride;
     const double pi0 = eig[40], pi1 = eig[41], pi2 = eig[42], pi3 = eig[43];
-    const double weight = 1.0 / R;  // pll.c:746-747
-    double terma = 0.0;
+
+    // sum over categories of the edge terms, kept as acc * 2^(-256 * acc_cnt)
+    double acc[NS];
+    int acc_cnt[NS];
 #pragma unroll
+    for (int u = 0; u < NS; ++u) { acc[u] = 0.0; acc_cnt[u] = 0; }
+
     for (int k = 0; k < R; ++k) {
-      const double t0 = (pi0 * mc[k][0]) * reg[k][0];
-      const double t1 = (pi1 * mc[k][1]) * reg[k][1];
-      const double t2 = (pi2 * mc[k][2]) * reg[k][2];
-      const double t3 = (pi3 * mc[k][3]) * reg[k][3];
-      const double terma_r = (t0 + t1) + (t2 + t3);
-      if (terma_r > 0.0) terma += terma_r * weight;   // :1225-1239
+      double reg[NS][4];
+      int reg_cnt[NS];
+#pragma unroll
+      for (int u = 0; u < NS; ++u) {
+        reg_cnt[u] = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) reg[u][i] = 0.0;
+      }
+      for (int s = 0; s < n_steps; ++s) {
+        const int4 st = __ldg(plan + s);
+        const double* recA = recs + (size_t)(2 * s) * REC;
+        double ma[NS][4], mb[NS][4];
+        int ca[NS], cb[NS];
+        child_messages<NS>(st.x, recA, k, reg, reg_cnt, io, f.tip_codes, S, site, ma, ca);
+        child_messages<NS>(st.y, recA + REC, k, reg, reg_cnt, io, f.tip_codes, S, site, mb, cb);
+#pragma unroll
+        for (int u = 0; u < NS; ++u) {
+          bool all_small = true;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const double v = ma[u][i] * mb[u][i];  // core_partials.c:626
+            reg[u][i] = v;
+            all_small = all_small && below_threshold(v);
+          }
+          reg_cnt[u] = ca[u] + cb[u];  // fill_parent_scaler, core_partials.c:24-46
+          if (all_small) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) reg[u][i] *= LH_SCALE_FACTOR;
+            reg_cnt[u] += 1;
+          }
+        }
+        if (st.z >= 0) {
+          double* clv;
+          int* pc;
+          io.locate(st.z, clv, pc);
+#pragma unroll
+          for (int u = 0; u < NS; ++u) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) clv[(size_t)(u * 4 + i) * W] = reg[u][i];
+            pc[u * W] = reg_cnt[u];
+          }
+        }
+      }
+
+      // ---- edge term of this category (core_likelihood_avx.c:1130-1239) ----
+      const int4 fin = __ldg(plan + n_steps);
+      const double* recE = recs + (size_t)(NB - 1) * REC;
+      double mc[NS][4];
+      int cc[NS];
+      child_messages<NS>(fin.y, recE, k, reg, reg_cnt, io, f.tip_codes, S, site, mc, cc);
+      if (fin.x != -1) {  // the root CLV was parked; fetch it
+        double* clv;
+        int* pc;
+        io.locate(-2 - fin.x, clv, pc);
+#pragma unroll
+        for (int u = 0; u < NS; ++u) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) reg[u][i] = clv[(size_t)(u * 4 + i) * W];
+          reg_cnt[u] = pc[u * W];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < NS; ++u) {
+        const double t0 = (pi0 * mc[u][0]) * reg[u][0];
+        const double t1 = (pi1 * mc[u][1]) * reg[u][1];
+        const double t2 = (pi2 * mc[u][2]) * reg[u][2];
+        const double t3 = (pi3 * mc[u][3]) * reg[u][3];
+        double term = (t0 + t1) + (t2 + t3);
+        if (term > 0.0) {  // :1225
+          term *= weight;
+          int c = reg_cnt[u] + cc[u];
+          // bring acc and term to the smaller count (exact: powers of two)
+          if (acc[u] == 0.0) acc_cnt[u] = c;
+          while (c > acc_cnt[u]) { term *= kDown; --c; if (term == 0.0) c = acc_cnt[u]; }
+          while (acc_cnt[u] > c) { acc[u] *= kDown; --acc_cnt[u]; if (acc[u] == 0.0) acc_cnt[u] = c; }
+          acc[u] += term;
+        }
+      }
     }
-    double site_lk = log(terma);
-    const int scalings = cp + cc;
-    if (scalings) site_lk += scalings * cfg.log_threshold;   // :1247-1251
-    // naive-sequence correction (src/PhyloHMM.cpp:229-237); xMSA row 0 is the naive
-    const int nb = __ldg(f.tip_codes + site);
-    if (nb != 4) site_lk -= eig[36 + nb];
-    b.xe[(size_t)t * S + site] = exp(site_lk);
+
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+      if (!live[u]) continue;
+      double site_lk = log(acc[u]);
+      if (acc_cnt[u]) site_lk += acc_cnt[u] * cfg.log_threshold;   // :1247-1251
+      // naive-sequence correction (src/PhyloHMM.cpp:229-237); xMSA row 0 is the naive
+      const int nb = __ldg(f.tip_codes + site[u]);
+      if (nb != 4) site_lk -= eig[36 + nb];
+      b.xe[(size_t)t * S + site[u]] = exp(site_lk);
+    }
   }
 }
 
-size_t prune_smem_bytes(int R, int tile_sites, int smem_slots) {
-  return (size_t)smem_slots * tile_sites * (4 * R * sizeof(double) + sizeof(int));
+size_t prune_smem_bytes(int ns, int threads, int smem_slots) {
+  return (size_t)smem_slots * threads * ns * (4 * sizeof(double) + sizeof(int));
 }
 
-template <int R>
-static void launch_prune_r(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0,
+#define LH_DISPATCH_NS(NS_, CALL)                     \
+  switch (NS_) {                                      \
+    case 1: { constexpr int NN = 1; CALL; } break;    \
+    case 2: { constexpr int NN = 2; CALL; } break;    \
+    case 3: { constexpr int NN = 3; CALL; } break;    \
+    case 4: { constexpr int NN = 4; CALL; } break;    \
+    case 5: { constexpr int NN = 5; CALL; } break;    \
+    case 6: { constexpr int NN = 6; CALL; } break;    \
+    default: { constexpr int NN = 8; CALL; } break;   \
+  }
+
+template <int NS>
+static void launch_prune_n(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0,
                            int ntrees, cudaStream_t s) {
-  size_t smem = prune_smem_bytes(R, c.tile_sites, c.smem_slots);
-  cudaFuncSetAttribute(k_prune<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_prune<R><<<c.grid, c.tile_sites, smem, s>>>(f, b, c, tree0, ntrees);
+  size_t smem = prune_smem_bytes(NS, c.threads, c.smem_slots);
+  cudaFuncSetAttribute(k_prune<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_prune<NS><<<c.grid, c.threads, smem, s>>>(f, b, c, tree0, ntrees);
 }
 
-template <int R>
-static int prune_occ_r(int tile_sites, size_t smem) {
+template <int NS>
+static int prune_occ_n(int threads, size_t smem) {
   int n = 0;
-  cudaFuncSetAttribute(k_prune<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_prune<R>, tile_sites, smem);
+  cudaFuncSetAttribute(k_prune<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_prune<NS>, threads, smem);
   return n;
 }
 
-#define LH_DISPATCH_R(R_, CALL)                       \
-  switch (R_) {                                       \
-    case 1: { constexpr int RR = 1; CALL; } break;    \
-    case 2: { constexpr int RR = 2; CALL; } break;    \
-    case 3: { constexpr int RR = 3; CALL; } break;    \
-    case 4: { constexpr int RR = 4; CALL; } break;    \
-    case 5: { constexpr int RR = 5; CALL; } break;    \
-    case 6: { constexpr int RR = 6; CALL; } break;    \
-    case 7: { constexpr int RR = 7; CALL; } break;    \
-    default: { constexpr int RR = 8; CALL; } break;   \
-  }
-
 void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0, int ntrees,
                   cudaStream_t s) {
-  LH_DISPATCH_R(b.R, launch_prune_r<RR>(f, b, c, tree0, ntrees, s));
+  LH_DISPATCH_NS(c.sites_per_thread, launch_prune_n<NN>(f, b, c, tree0, ntrees, s));
 }
 
-int prune_max_ctas_per_sm(int R, int tile_sites, int smem_slots) {
-  size_t smem = prune_smem_bytes(R, tile_sites, smem_slots);
+int prune_max_ctas_per_sm(int ns, int threads, int smem_slots) {
+  size_t smem = prune_smem_bytes(ns, threads, smem_slots);
   int n = 0;
-  LH_DISPATCH_R(R, n = prune_occ_r<RR>(tile_sites, smem));
+  LH_DISPATCH_NS(ns, n = prune_occ_n<NN>(threads, smem));
   return n;
 }
 

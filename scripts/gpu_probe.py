@@ -40,11 +40,11 @@ def probe(name, opts_list, n_port=2, reps=3):
                           "err_vs_port": float(err_port), "ms_prune_stage": best["ms_prune"], "ms_hmm": best["ms_hmm"],
                           "ms_h2d": best["ms_h2d"], "ms_d2h": best["ms_d2h"], "wall_e2e_s": best["wall_e2e_s"],
                           "trees_per_s_kernels": tps, "algo_GBps": tps * bytes_tree(T, S) / 1e9,
-                          "slots": best["prune_slots"], "tile": best["prune_tile_sites"],
+                          "slots": best["prune_slots"], "smem_slots": best["prune_smem_slots"], "tile": best["prune_tile_sites"], "ns": best["prune_sites_per_thread"], "occ": best["prune_ctas_per_sm"], "grid": best["prune_grid"],
                           "launches": best["kernel_launches"], "finite": bool(np.all(np.isfinite(ll)))}), flush=True)
         f.close()
 
 if __name__ == "__main__":
     print(json.dumps({"fp64_peak_tflops": device.fp64_peak_tflops(0)}), flush=True)
-    probe("probe_c3", [{}, {"smem_slots": 0}, {"tile_sites": 64}, {"tile_sites": 256}, {"chunk_bytes": 1 << 30}])
-    probe("probe_c4", [{}, {"smem_slots": 0}], n_port=1)
+    probe("probe_c3", [{}, {"sites_per_thread": 5}, {"sites_per_thread": 3}, {"sites_per_thread": 2}, {"sites_per_thread": 6}, {"smem_slots": 0}, {"cta_threads": 64}])
+    probe("probe_c4", [{}, {"sites_per_thread": 5}, {"smem_slots": 0}], n_port=1)
