@@ -124,7 +124,7 @@ struct lh_family {
   lhb::FamilyDev fd{};
   std::vector<void*> owned;  // family-constant device allocations
   // options
-  int opt_cta_threads = 0, opt_sites_per_thread = 0, opt_smem_slots = -1, opt_timing = 1, opt_threads = 0;
+  int opt_sites_per_thread = 0, opt_smem_slots = -1, opt_timing = 1, opt_threads = 0;
   size_t opt_chunk_bytes = 48u << 20;
   // batch state
   int B = 0, R = 0, slots = 0;
@@ -215,7 +215,14 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
   fd.s_max = std::max(std::max(fd.vd_states, fd.dj_states), fd.g_max);
   auto& own = f->owned;
   int rc = 0;
-  rc |= upload(d->tip_codes, (size_t)T * S, &fd.tip_codes, own);
+  {
+    // rows padded to a 16-byte pitch (cp.async staging), 512 zero bytes behind the last row so a
+    // partial last tile may read past column S
+    fd.tip_pitch = (S + 15) / 16 * 16;
+    std::vector<uint8_t> padded((size_t)T * fd.tip_pitch + 512, 0);
+    for (int r = 0; r < T; ++r) std::memcpy(padded.data() + (size_t)r * fd.tip_pitch, d->tip_codes + (size_t)r * S, S);
+    rc |= upload(padded.data(), padded.size(), &fd.tip_codes, own);
+  }
   auto region = [&](int n, const int32_t* off, const int32_t* inds, const int32_t** doff,
                     const int32_t** dinds, const char* name) {
     if (n == 0) return upload(off, 0, doff, own) | upload(inds, 0, dinds, own);
@@ -263,11 +270,8 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
 
 int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
   std::string k(key ? key : "");
-  if (k == "cta_threads") {
-    if (value != 0 && (value < 32 || value > 128 || value % 32)) return fail("cta_threads must be 0 or a multiple of 32 in 32..128");
-    f->opt_cta_threads = (int)value;
-  } else if (k == "sites_per_thread") {
-    if (value < 0 || value > 8 || value == 7) return fail("sites_per_thread must be 0 (auto), 1..6 or 8");
+  if (k == "sites_per_thread") {
+    if (value < 0 || value > 6) return fail("sites_per_thread must be 0 (auto) or 1..6");
     f->opt_sites_per_thread = (int)value;
   } else if (k == "smem_slots") {
     f->opt_smem_slots = (int)value;
@@ -417,23 +421,22 @@ int lh_batch_run(lh_family_t* f) {
 
   // pruning configuration
   lhb::PruneCfg pc{};
-  pc.threads = f->opt_cta_threads ? f->opt_cta_threads : 32;
-  pc.sites_per_thread = f->opt_sites_per_thread ? f->opt_sites_per_thread : pick_sites_per_thread(S, pc.threads);
-  const int tile_sites = pc.threads * pc.sites_per_thread;
+  pc.sites_per_thread = f->opt_sites_per_thread ? f->opt_sites_per_thread : pick_sites_per_thread(S, 32);
+  const int tile_sites = 32 * pc.sites_per_thread;
   pc.n_tiles = (S + tile_sites - 1) / tile_sites;
   pc.total_slots = f->slots;
   const size_t slot_bytes = (size_t)tile_sites * (4 * sizeof(double) + sizeof(int));
-  int occ0 = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.threads, 0);
-  if (occ0 < 1) return fail("pruning kernel cannot be resident (sites/thread=%d, threads=%d)", pc.sites_per_thread, pc.threads);
+  int occ0 = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, 0);
+  if (occ0 < 1) return fail("pruning kernel cannot be resident (sites/thread=%d)", pc.sites_per_thread);
   int smem_slots = f->opt_smem_slots;
   if (smem_slots < 0) {
-    size_t per_cta = (size_t)(227 * 1024) / occ0 - 1024;
+    size_t per_cta = (size_t)(227 * 1024) / occ0 - 1024 - lhb::prune_smem_bytes(pc.sites_per_thread, 0);
     smem_slots = (int)(per_cta / slot_bytes);
   }
   smem_slots = std::max(0, std::min(smem_slots, pc.total_slots));
-  while (smem_slots > 0 && lhb::prune_smem_bytes(pc.sites_per_thread, pc.threads, smem_slots) > (size_t)227 * 1024) --smem_slots;
+  while (smem_slots > 0 && lhb::prune_smem_bytes(pc.sites_per_thread, smem_slots) > (size_t)227 * 1024) --smem_slots;
   pc.smem_slots = smem_slots;
-  int occ = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.threads, pc.smem_slots);
+  int occ = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.smem_slots);
   if (occ < 1) return fail("pruning kernel cannot be resident with %d shared-memory slots", pc.smem_slots);
   pc.log_threshold = std::log(1.0 / std::pow(2.0, 256));
 

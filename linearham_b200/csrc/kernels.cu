@@ -113,8 +113,8 @@ void launch_eigen(const BatchDev& b, cudaStream_t s) {
 // ---------------------------------------------------------------- k_pmatrix ---
 // One thread per (tree, branch, rate category). Branch records are laid out in the
 // order the pruning program consumes them: record 2*step+c for child c of a step, the
-// root edge last; each record is 20*R doubles:
-//   inner child : P[k][i][j] at k*16 + i*4 + j      (row-major as core_pmatrix.c)
+// root edge last; each record is R blocks of 20 doubles (one per category):
+//   inner child : P[k][i][j] at k*20 + i*4 + j      (row-major as core_pmatrix.c; 4 pad)
 //   tip child   : Q[k][code][i] at k*20 + code*4 + i, code in A,C,G,T,N: the product
 //                 P[k] * tipclv(code) that set_tipclv + the generic kernel would form
 //                 (pll.c:926-930: one-hot for ACGT, all ones for N).
@@ -160,7 +160,7 @@ __global__ void k_pmatrix(FamilyDev f, BatchDev b, int tree0, int ntrees) {
     }
     double* rec = b.prec + ((size_t)lt * NB + br) * (20 * R);
     if (!tip) {
-      double2* o = reinterpret_cast<double2*>(rec + k * 16);
+      double2* o = reinterpret_cast<double2*>(rec + k * 20);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         o[2 * j] = make_double2(P[j][0], P[j][1]);
@@ -191,20 +191,25 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 }
 
 // ------------------------------------------------------------------ k_prune ---
-// Persistent CTAs; a work item is (tree, tile of W*NS xMSA columns); a thread owns NS columns
-// (column tile_base + u*W + tid, u < NS) and walks the tree's program (plan.hpp) once per rate
+// One warp per CTA, persistent; a work item is (tree, tile of 32*NS xMSA columns); lane l owns
+// columns tile_base + u*32 + l (u < NS) and walks the tree's program (plan.hpp) once per rate
 // category ("category-outer"): the categories of a site never mix before the edge likelihood,
 // so a pass needs only 4 doubles of state per column. That lets one thread carry NS columns in
-// registers, and the 4x4 transition matrix of a branch, loaded once into registers, is used for
-// NS columns. The matrix loads are warp-uniform but still cost 512 B of L1 data-pipe per warp per
-// LDG.128; with one column per thread that pipe, not the FP64 pipe, bounded the kernel (ncu,
-// profiles/r1a: lsu wavefronts 57 %, fp64 14 %).
+// registers, and the 4x4 transition matrix of a branch, read once into registers, serves NS
+// columns. (With one column per thread the warp-uniform matrix loads saturated the L1 data pipe,
+// not the FP64 pipe: ncu r1a, lsu wavefronts 57 %, fp64 14 %.)
+//
+// Everything a step reads from global memory is staged into shared memory two steps ahead with
+// cp.async, so the dependent chain plan -> branch record -> tip code -> Q column never waits on
+// L2 (ncu r1a: 13.9 warps stalled on long scoreboard per issue):
+//   plan ring   64 steps, refilled 32 at a time
+//   record ring 4 steps x 2 children x 20 doubles (the category's P or Q block)
+//   code ring   4 steps x 2 children x 32*NS tip codes of this tile
 //
 // Inner CLVs never exist as arrays in HBM: the running result stays in registers, results
 // parked for a later step go to a per-column stack whose first `smem_slots` levels are shared
-// memory ([slot][u][state][W], conflict-free because a column is only ever touched by its own
+// memory ([slot][u][state][lane], conflict-free because a column is only ever touched by its own
 // thread) and whose deeper levels are an L2-resident scratch ring private to the CTA.
-// No barriers: threads never exchange data.
 //
 // Scaling. libpll rescales a site by 2^256 when ALL 4R entries of a node are below 2^-256
 // (core_partials.c:648-659). Here each category keeps its own count and rescales when its own 4
@@ -213,21 +218,37 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 // reference's unscaled categories stay normal numbers; where they would go subnormal in the
 // reference, this kernel keeps their full precision (a relative contribution < 2^-256).
 
+#ifndef LH_PRUNE_MIN_CTAS
+#define LH_PRUNE_MIN_CTAS 10
+#endif
+
+constexpr int kRecRing = 4;    // steps of branch records / tip codes in flight
+constexpr int kPlanRing = 64;  // plan entries resident
+constexpr int kRecDoubles = 20;
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
 template <int NS>
 struct SlotIO {
-  double* smem_clv;   // [smem_slots][NS*4][W]
-  int* smem_cnt;      // [smem_slots][NS][W]
-  double* g_clv;      // [gslots][NS*4][W] (this CTA)
-  int* g_cnt;         // [gslots][NS][W]
-  int smem_slots, W, tid;
+  double* smem_clv;   // [smem_slots][NS*4][32]
+  int* smem_cnt;      // [smem_slots][NS][32]
+  double* g_clv;      // [gslots][NS*4][32] (this CTA)
+  int* g_cnt;         // [gslots][NS][32]
+  int smem_slots, lane;
 
   __device__ __forceinline__ void locate(int slot, double*& clv, int*& cnt) const {
     if (slot < smem_slots) {
-      clv = smem_clv + (size_t)slot * (4 * NS) * W + tid;
-      cnt = smem_cnt + slot * NS * W + tid;
+      clv = smem_clv + (size_t)slot * (4 * NS) * 32 + lane;
+      cnt = smem_cnt + slot * NS * 32 + lane;
     } else {
-      clv = g_clv + (size_t)(slot - smem_slots) * (4 * NS) * W + tid;
-      cnt = g_cnt + (slot - smem_slots) * NS * W + tid;
+      clv = g_clv + (size_t)(slot - smem_slots) * (4 * NS) * 32 + lane;
+      cnt = g_cnt + (slot - smem_slots) * NS * 32 + lane;
     }
   }
 };
@@ -237,33 +258,29 @@ struct SlotIO {
 // threshold as a signed integer too. Keeps the test off the FP64 pipe.
 __device__ __forceinline__ bool below_threshold(double v) { return __double2hiint(v) < 0x2FF00000; }
 
-// Per-category messages of one child for the NS columns of this thread, m[u][i] =
-// sum_j P[k][i][j] * c[u][j] (core_partials.c:617-624); returns the child's scaler counts.
+// Messages of one child for the NS columns of this thread, m[u][i] = sum_j P[i][j] * c[u][j]
+// (core_partials.c:617-624), from the staged record `rec` (P row-major, or the 5 Q columns for
+// a tip) and the staged tip codes; also returns the child's scaler counts.
 template <int NS>
-__device__ __forceinline__ void child_messages(int src, const double* __restrict__ rec, int k,
+__device__ __forceinline__ void child_messages(int src, const double* rec, const uint8_t* codes,
                                                const double (&reg)[NS][4], const int (&reg_cnt)[NS],
-                                               const SlotIO<NS>& io, const uint8_t* __restrict__ codes,
-                                               int S, const int (&site)[NS], double (&m)[NS][4],
-                                               int (&cnt)[NS]) {
+                                               const SlotIO<NS>& io, double (&m)[NS][4], int (&cnt)[NS]) {
   if (src >= 0) {  // tip: column `code` of Q (k_pmatrix), one 32-byte lookup per site
-    const uint8_t* __restrict__ row = codes + (size_t)src * S;
-    const double* __restrict__ Qk = rec + k * 20;
 #pragma unroll
     for (int u = 0; u < NS; ++u) {
-      const int code = __ldg(row + site[u]);
-      const double2 q01 = __ldg(reinterpret_cast<const double2*>(Qk + 4 * code));
-      const double2 q23 = __ldg(reinterpret_cast<const double2*>(Qk + 4 * code + 2));
+      const int code = codes[u * 32 + io.lane];
+      const double2 q01 = *reinterpret_cast<const double2*>(rec + 4 * code);
+      const double2 q23 = *reinterpret_cast<const double2*>(rec + 4 * code + 2);
       m[u][0] = q01.x; m[u][1] = q01.y; m[u][2] = q23.x; m[u][3] = q23.y;
       cnt[u] = 0;
     }
     return;
   }
   double P[4][4];
-  const double* __restrict__ Pk = rec + k * 16;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const double2 p01 = __ldg(reinterpret_cast<const double2*>(Pk + 4 * i));
-    const double2 p23 = __ldg(reinterpret_cast<const double2*>(Pk + 4 * i + 2));
+    const double2 p01 = *reinterpret_cast<const double2*>(rec + 4 * i);
+    const double2 p23 = *reinterpret_cast<const double2*>(rec + 4 * i + 2);
     P[i][0] = p01.x; P[i][1] = p01.y; P[i][2] = p23.x; P[i][3] = p23.y;
   }
   if (src == -1) {
@@ -288,7 +305,7 @@ __device__ __forceinline__ void child_messages(int src, const double* __restrict
   for (int u = 0; u < NS; ++u) {
     double c[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) c[j] = clv[(size_t)(u * 4 + j) * io.W];
+    for (int j = 0; j < 4; ++j) c[j] = clv[(u * 4 + j) * 32];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       double acc = P[i][0] * c[0];
@@ -297,45 +314,48 @@ __device__ __forceinline__ void child_messages(int src, const double* __restrict
       acc += P[i][3] * c[3];
       m[u][i] = acc;
     }
-    cnt[u] = pc[u * io.W];
+    cnt[u] = pc[u * 32];
   }
 }
 
+size_t prune_smem_bytes(int ns, int smem_slots) {
+  return (size_t)kRecRing * 2 * kRecDoubles * sizeof(double) + kPlanRing * sizeof(int4) +
+         (size_t)kRecRing * 2 * ns * 32 + (size_t)smem_slots * 32 * ns * (4 * sizeof(double) + sizeof(int));
+}
+
 template <int NS>
-__global__ void __launch_bounds__(128) k_prune(FamilyDev f, BatchDev b, PruneCfg cfg, int tree0, int ntrees) {
+__global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
+    k_prune(FamilyDev f, BatchDev b, PruneCfg cfg, int tree0, int ntrees) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int W = blockDim.x, tid = threadIdx.x, T = f.T, S = f.S, R = b.R;
-  const int NB = 2 * T - 3, REC = 20 * R, n_steps = T - 2;
+  const int lane = threadIdx.x, T = f.T, S = f.S, R = b.R;
+  const int NB = 2 * T - 3, n_steps = T - 2, n_iter = T - 1;  // node updates + the edge evaluation
   const int gslots = cfg.total_slots - cfg.smem_slots;
+  double* ring_rec = reinterpret_cast<double*>(smem_raw);                       // [kRecRing][2][20]
+  int4* ring_plan = reinterpret_cast<int4*>(ring_rec + kRecRing * 2 * kRecDoubles);  // [kPlanRing]
+  uint8_t* ring_code = reinterpret_cast<uint8_t*>(ring_plan + kPlanRing);       // [kRecRing][2][NS*32]
   SlotIO<NS> io;
-  io.smem_clv = reinterpret_cast<double*>(smem_raw);
-  io.smem_cnt = reinterpret_cast<int*>(io.smem_clv + (size_t)cfg.smem_slots * (4 * NS) * W);
-  io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * NS) * W;
-  io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * W;
+  io.smem_clv = reinterpret_cast<double*>(ring_code + kRecRing * 2 * NS * 32);
+  io.smem_cnt = reinterpret_cast<int*>(io.smem_clv + (size_t)cfg.smem_slots * (4 * NS) * 32);
+  io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * NS) * 32;
+  io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * 32;
   io.smem_slots = cfg.smem_slots;
-  io.W = W;
-  io.tid = tid;
+  io.lane = lane;
   const double weight = 1.0 / R;  // pll.c:746-747
   constexpr double kDown = LH_SCALE_THRESHOLD;
+  // lane roles in the staging copies (16 bytes per lane)
+  const int rec_child = lane / 10, rec_part = lane % 10;  // lanes 0..19: 2 children x 160 bytes
+  const bool rec_lane = lane < 20;
+  const bool code_lane = lane < 2 * NS;                   // 32*NS code bytes per tip child
 
   const int n_work = ntrees * cfg.n_tiles;
   for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
     const int lt = w / cfg.n_tiles, tile = w - lt * cfg.n_tiles;
     const int t = tree0 + lt;
-    int site[NS];
-    bool live[NS];
-    bool any_live = false;
-#pragma unroll
-    for (int u = 0; u < NS; ++u) {
-      const int s = tile * (W * NS) + u * W + tid;
-      live[u] = s < S;
-      any_live = any_live || live[u];
-      site[u] = live[u] ? s : S - 1;  // padding columns recompute the last column, never stored
-    }
-    if (!any_live) continue;
+    const int tile_base = tile * (32 * NS);
     const int4* __restrict__ plan = b.plan + (size_t)t * (T - 1);
-    const double* __restrict__ recs = b.prec + (size_t)lt * NB * REC;
+    const double* __restrict__ recs = b.prec + (size_t)lt * NB * (kRecDoubles * R);
     const double* __restrict__ eig = b.eig + (size_t)t * kEigStride;
+    const uint8_t* __restrict__ code_base = f.tip_codes + tile_base + lane * 16;
     const double pi0 = eig[40], pi1 = eig[41], pi2 = eig[42], pi3 = eig[43];
 
     // sum over categories of the edge terms, kept as acc * 2^(-256 * acc_cnt)
@@ -345,6 +365,38 @@ __global__ void __launch_bounds__(128) k_prune(FamilyDev f, BatchDev b, PruneCfg
     for (int u = 0; u < NS; ++u) { acc[u] = 0.0; acc_cnt[u] = 0; }
 
     for (int k = 0; k < R; ++k) {
+      // stage the plan entries [q0, q0+32) into their half of the plan ring
+      auto stage_plan = [&](int q0) {
+        const int q = q0 + lane;
+        if (q < n_iter) cp_async16(ring_plan + (q & (kPlanRing - 1)), plan + q);
+      };
+      // stage what step q reads: the category's record of both branches and the codes of tip children
+      auto stage_step = [&](int q) {
+        if (q >= n_iter) return;
+        const int slot = q & (kRecRing - 1);
+        if (rec_lane) {
+          const int ri = 2 * q + rec_child;
+          if (ri < NB)
+            cp_async16(ring_rec + (slot * 2 + rec_child) * kRecDoubles + rec_part * 2,
+                       recs + ((size_t)ri * R + k) * kRecDoubles + rec_part * 2);
+        }
+        const int4 sq = ring_plan[q & (kPlanRing - 1)];
+        if (code_lane) {
+          if (sq.x >= 0) cp_async16(ring_code + (slot * 2 + 0) * (NS * 32) + lane * 16, code_base + (size_t)sq.x * f.tip_pitch);
+          if (sq.y >= 0) cp_async16(ring_code + (slot * 2 + 1) * (NS * 32) + lane * 16, code_base + (size_t)sq.y * f.tip_pitch);
+        }
+      };
+      __syncwarp();  // the previous pass / work item is done with the rings
+      stage_plan(0);
+      stage_plan(32);
+      cp_async_commit();
+      cp_async_wait<0>();
+      __syncwarp();
+      stage_step(0);
+      cp_async_commit();
+      stage_step(1);
+      cp_async_commit();
+
       double reg[NS][4];
       int reg_cnt[NS];
 #pragma unroll
@@ -353,93 +405,102 @@ __global__ void __launch_bounds__(128) k_prune(FamilyDev f, BatchDev b, PruneCfg
 #pragma unroll
         for (int i = 0; i < 4; ++i) reg[u][i] = 0.0;
       }
-      for (int s = 0; s < n_steps; ++s) {
-        const int4 st = __ldg(plan + s);
-        const double* recA = recs + (size_t)(2 * s) * REC;
-        double ma[NS][4], mb[NS][4];
-        int ca[NS], cb[NS];
-        child_messages<NS>(st.x, recA, k, reg, reg_cnt, io, f.tip_codes, S, site, ma, ca);
-        child_messages<NS>(st.y, recA + REC, k, reg, reg_cnt, io, f.tip_codes, S, site, mb, cb);
-#pragma unroll
-        for (int u = 0; u < NS; ++u) {
-          bool all_small = true;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const double v = ma[u][i] * mb[u][i];  // core_partials.c:626
-            reg[u][i] = v;
-            all_small = all_small && below_threshold(v);
-          }
-          reg_cnt[u] = ca[u] + cb[u];  // fill_parent_scaler, core_partials.c:24-46
-          if (all_small) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) reg[u][i] *= LH_SCALE_FACTOR;
-            reg_cnt[u] += 1;
-          }
+      for (int s = 0; s < n_iter; ++s) {
+        if ((s & 31) == 0 && s > 0) {
+          __syncwarp();           // every lane has read the plan entries of the half being replaced
+          stage_plan(s + 32);
         }
-        if (st.z >= 0) {
-          double* clv;
-          int* pc;
-          io.locate(st.z, clv, pc);
+        stage_step(s + 2);
+        cp_async_commit();
+        cp_async_wait<2>();       // everything staged for step s (two commits ago) has landed
+        __syncwarp();
+        const int slot = s & (kRecRing - 1);
+        const int4 st = ring_plan[s & (kPlanRing - 1)];
+        const double* recA = ring_rec + (slot * 2) * kRecDoubles;
+        const uint8_t* codeA = ring_code + (slot * 2) * (NS * 32);
+        if (s < n_steps) {
+          double ma[NS][4], mb[NS][4];
+          int ca[NS], cb[NS];
+          child_messages<NS>(st.x, recA, codeA, reg, reg_cnt, io, ma, ca);
+          child_messages<NS>(st.y, recA + kRecDoubles, codeA + NS * 32, reg, reg_cnt, io, mb, cb);
 #pragma unroll
           for (int u = 0; u < NS; ++u) {
+            bool all_small = true;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) clv[(size_t)(u * 4 + i) * W] = reg[u][i];
-            pc[u * W] = reg_cnt[u];
+            for (int i = 0; i < 4; ++i) {
+              const double v = ma[u][i] * mb[u][i];  // core_partials.c:626
+              reg[u][i] = v;
+              all_small = all_small && below_threshold(v);
+            }
+            reg_cnt[u] = ca[u] + cb[u];  // fill_parent_scaler, core_partials.c:24-46
+            if (all_small) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) reg[u][i] *= LH_SCALE_FACTOR;
+              reg_cnt[u] += 1;
+            }
+          }
+          if (st.z >= 0) {
+            double* clv;
+            int* pc;
+            io.locate(st.z, clv, pc);
+#pragma unroll
+            for (int u = 0; u < NS; ++u) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) clv[(u * 4 + i) * 32] = reg[u][i];
+              pc[u * 32] = reg_cnt[u];
+            }
+          }
+        } else {
+          // ---- edge term of this category (core_likelihood_avx.c:1130-1239); the edge's record
+          // sits in the first child position of the last step, st.y is the child across it ----
+          double mc[NS][4];
+          int cc[NS];
+          child_messages<NS>(st.y, recA, codeA + NS * 32, reg, reg_cnt, io, mc, cc);
+          if (st.x != -1) {  // the root CLV was parked; fetch it
+            double* clv;
+            int* pc;
+            io.locate(-2 - st.x, clv, pc);
+#pragma unroll
+            for (int u = 0; u < NS; ++u) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) reg[u][i] = clv[(u * 4 + i) * 32];
+              reg_cnt[u] = pc[u * 32];
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < NS; ++u) {
+            const double t0 = (pi0 * mc[u][0]) * reg[u][0];
+            const double t1 = (pi1 * mc[u][1]) * reg[u][1];
+            const double t2 = (pi2 * mc[u][2]) * reg[u][2];
+            const double t3 = (pi3 * mc[u][3]) * reg[u][3];
+            double term = (t0 + t1) + (t2 + t3);
+            if (term > 0.0) {  // :1225
+              term *= weight;
+              int c = reg_cnt[u] + cc[u];
+              // bring acc and term to the smaller count (exact: powers of two)
+              if (acc[u] == 0.0) acc_cnt[u] = c;
+              while (c > acc_cnt[u]) { term *= kDown; --c; if (term == 0.0) c = acc_cnt[u]; }
+              while (acc_cnt[u] > c) { acc[u] *= kDown; --acc_cnt[u]; if (acc[u] == 0.0) acc_cnt[u] = c; }
+              acc[u] += term;
+            }
           }
         }
       }
-
-      // ---- edge term of this category (core_likelihood_avx.c:1130-1239) ----
-      const int4 fin = __ldg(plan + n_steps);
-      const double* recE = recs + (size_t)(NB - 1) * REC;
-      double mc[NS][4];
-      int cc[NS];
-      child_messages<NS>(fin.y, recE, k, reg, reg_cnt, io, f.tip_codes, S, site, mc, cc);
-      if (fin.x != -1) {  // the root CLV was parked; fetch it
-        double* clv;
-        int* pc;
-        io.locate(-2 - fin.x, clv, pc);
-#pragma unroll
-        for (int u = 0; u < NS; ++u) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) reg[u][i] = clv[(size_t)(u * 4 + i) * W];
-          reg_cnt[u] = pc[u * W];
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < NS; ++u) {
-        const double t0 = (pi0 * mc[u][0]) * reg[u][0];
-        const double t1 = (pi1 * mc[u][1]) * reg[u][1];
-        const double t2 = (pi2 * mc[u][2]) * reg[u][2];
-        const double t3 = (pi3 * mc[u][3]) * reg[u][3];
-        double term = (t0 + t1) + (t2 + t3);
-        if (term > 0.0) {  // :1225
-          term *= weight;
-          int c = reg_cnt[u] + cc[u];
-          // bring acc and term to the smaller count (exact: powers of two)
-          if (acc[u] == 0.0) acc_cnt[u] = c;
-          while (c > acc_cnt[u]) { term *= kDown; --c; if (term == 0.0) c = acc_cnt[u]; }
-          while (acc_cnt[u] > c) { acc[u] *= kDown; --acc_cnt[u]; if (acc[u] == 0.0) acc_cnt[u] = c; }
-          acc[u] += term;
-        }
-      }
+      cp_async_wait<0>();
     }
 
 #pragma unroll
     for (int u = 0; u < NS; ++u) {
-      if (!live[u]) continue;
+      const int site = tile_base + u * 32 + lane;
+      if (site >= S) continue;
       double site_lk = log(acc[u]);
       if (acc_cnt[u]) site_lk += acc_cnt[u] * cfg.log_threshold;   // :1247-1251
       // naive-sequence correction (src/PhyloHMM.cpp:229-237); xMSA row 0 is the naive
-      const int nb = __ldg(f.tip_codes + site[u]);
+      const int nb = __ldg(f.tip_codes + site);
       if (nb != 4) site_lk -= eig[36 + nb];
-      b.xe[(size_t)t * S + site[u]] = exp(site_lk);
+      b.xe[(size_t)t * S + site] = exp(site_lk);
     }
   }
-}
-
-size_t prune_smem_bytes(int ns, int threads, int smem_slots) {
-  return (size_t)smem_slots * threads * ns * (4 * sizeof(double) + sizeof(int));
 }
 
 #define LH_DISPATCH_NS(NS_, CALL)                     \
@@ -449,23 +510,22 @@ size_t prune_smem_bytes(int ns, int threads, int smem_slots) {
     case 3: { constexpr int NN = 3; CALL; } break;    \
     case 4: { constexpr int NN = 4; CALL; } break;    \
     case 5: { constexpr int NN = 5; CALL; } break;    \
-    case 6: { constexpr int NN = 6; CALL; } break;    \
-    default: { constexpr int NN = 8; CALL; } break;   \
+    default: { constexpr int NN = 6; CALL; } break;   \
   }
 
 template <int NS>
 static void launch_prune_n(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0,
                            int ntrees, cudaStream_t s) {
-  size_t smem = prune_smem_bytes(NS, c.threads, c.smem_slots);
+  size_t smem = prune_smem_bytes(NS, c.smem_slots);
   cudaFuncSetAttribute(k_prune<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k_prune<NS><<<c.grid, c.threads, smem, s>>>(f, b, c, tree0, ntrees);
+  k_prune<NS><<<c.grid, 32, smem, s>>>(f, b, c, tree0, ntrees);
 }
 
 template <int NS>
-static int prune_occ_n(int threads, size_t smem) {
+static int prune_occ_n(size_t smem) {
   int n = 0;
   cudaFuncSetAttribute(k_prune<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_prune<NS>, threads, smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_prune<NS>, 32, smem);
   return n;
 }
 
@@ -474,10 +534,10 @@ void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int 
   LH_DISPATCH_NS(c.sites_per_thread, launch_prune_n<NN>(f, b, c, tree0, ntrees, s));
 }
 
-int prune_max_ctas_per_sm(int ns, int threads, int smem_slots) {
-  size_t smem = prune_smem_bytes(ns, threads, smem_slots);
+int prune_max_ctas_per_sm(int ns, int smem_slots) {
+  size_t smem = prune_smem_bytes(ns, smem_slots);
   int n = 0;
-  LH_DISPATCH_NS(ns, n = prune_occ_n<NN>(threads, smem));
+  LH_DISPATCH_NS(ns, n = prune_occ_n<NN>(smem));
   return n;
 }
 

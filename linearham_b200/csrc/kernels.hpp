@@ -17,7 +17,8 @@ struct CscDev {
 
 struct FamilyDev {
   int32_t T, S;                 // tips, xMSA columns
-  const uint8_t* tip_codes;     // [T][S]
+  const uint8_t* tip_codes;     // [T][tip_pitch], zero-padded tail
+  int32_t tip_pitch;            // row pitch in bytes, a multiple of 16
   int32_t has_d, n_v, n_d, n_j;
   int32_t vd_sites, vd_states, dj_sites, dj_states;
   const int32_t *vpad_off, *vpad_inds, *vgerm_off, *vgerm_inds, *dgerm_off, *dgerm_inds;
@@ -43,14 +44,13 @@ struct BatchDev {
 };
 
 struct PruneCfg {
-  int32_t threads;           // W = threads per CTA
-  int32_t sites_per_thread;  // NS; a CTA covers W*NS xMSA columns
+  int32_t sites_per_thread;  // NS; a CTA (one warp) covers 32*NS xMSA columns
   int32_t n_tiles;
   int32_t smem_slots;    // stack slots kept in shared memory
   int32_t total_slots;   // stack slots the batch needs
   int32_t grid;          // persistent CTAs
-  double* scratch;       // [grid][total_slots-smem_slots][4 NS][W] doubles
-  int32_t* scratch_cnt;  // [grid][total_slots-smem_slots][NS][W]
+  double* scratch;       // [grid][total_slots-smem_slots][4 NS][32] doubles
+  int32_t* scratch_cnt;  // [grid][total_slots-smem_slots][NS][32]
   double log_threshold;  // log(2^-256), host libm (core_likelihood_avx.c:1249)
 };
 
@@ -65,8 +65,8 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0, int ntrees,
                   cudaStream_t s);
 void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, cudaStream_t s);
-size_t prune_smem_bytes(int sites_per_thread, int threads, int smem_slots);
-int prune_max_ctas_per_sm(int sites_per_thread, int threads, int smem_slots);
+size_t prune_smem_bytes(int sites_per_thread, int smem_slots);
+int prune_max_ctas_per_sm(int sites_per_thread, int smem_slots);
 size_t hmm_smem_bytes(const FamilyDev& f, int warps);
 // launches the DFMA diagnostic kernel; returns the flop count of the launch
 double fp64_peak_flops_per_launch(double* scratch, int blocks, int iters, cudaStream_t s);

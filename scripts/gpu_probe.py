@@ -15,8 +15,10 @@ def load(name):
 def bytes_tree(T, S, R=4):
     return (T - 2) * S * (2 * 32 * R + 8) + T * S + 2 * (2 * T - 3) * R * 128 + S * 8
 
-def probe(name, opts_list, n_port=2, reps=3):
+def probe(name, opts_list, n_port=2, reps=3, rep=1):
     fam, tb, ref_ll = load(name)
+    if rep > 1:
+        tb = {k: np.concatenate([v] * rep) for k, v in tb.items()}
     B = tb["root_child"].shape[0]
     T, S = fam["n_tips"], fam["n_sites"]
     sub = {k: v[:n_port] for k, v in tb.items()}
@@ -46,5 +48,5 @@ def probe(name, opts_list, n_port=2, reps=3):
 
 if __name__ == "__main__":
     print(json.dumps({"fp64_peak_tflops": device.fp64_peak_tflops(0)}), flush=True)
-    probe("probe_c3", [{}, {"sites_per_thread": 5}, {"sites_per_thread": 3}, {"sites_per_thread": 2}, {"sites_per_thread": 6}, {"smem_slots": 0}, {"cta_threads": 64}])
-    probe("probe_c4", [{}, {"sites_per_thread": 5}, {"smem_slots": 0}], n_port=1)
+    probe("probe_c3", [{}, {"sites_per_thread": 5}, {"sites_per_thread": 3}, {"sites_per_thread": 2}, {"sites_per_thread": 6}, {"smem_slots": 0}, {"smem_slots": 2}])
+    probe("probe_c4", [{}, {"sites_per_thread": 5}, {"smem_slots": 0}, {"smem_slots": 3}], n_port=1, rep=8)
