@@ -157,7 +157,7 @@ int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/scor
  * denominator for the FP64-pipe view of the pruning kernel (no reference counterpart). */
 int lh_measure_fp64_peak(int device, double* tflops);
 int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
-/* keys: "sites_per_thread" (0 = auto, 1..6: xMSA columns per thread; a CTA is one warp and
+/* keys: "sites_per_thread" (0 = auto, 1..4: xMSA columns per thread; a CTA is one warp and
  * covers 32x that many columns), "smem_slots" (-1 = auto), "timing" (0/1), "host_threads",
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair), "stream" (a
  * caller-owned cudaStream_t cast to int64; 0 = private stream)                          */

@@ -136,6 +136,9 @@ struct lh_family {
   std::vector<cudaEvent_t> chunk_ev;  // 3 per chunk: pmatrix start, prune start, prune end
   int n_chunks = 0;
   bool own_stream = true;
+  std::vector<uint8_t> h_tip_codes;  // host copy, re-tiled per sites_per_thread
+  DevBuf d_codes_t;
+  int codes_ns = 0;
   lh_timings_t tm{};
   bool want_tables = false;
 };
@@ -158,7 +161,7 @@ void lh_family_destroy(lh_family_t* f) {
   for (void* p : f->owned) cudaFree(p);
   DevBuf* bufs[] = {&f->d_plan, &f->d_pblen, &f->d_er, &f->d_pi, &f->d_rates, &f->d_eig, &f->d_prec,
                     &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
-                    &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs};
+                    &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->d_codes_t};
   for (DevBuf* b : bufs) b->release();
   f->h_plan.release();
   f->h_pblen.release();
@@ -215,14 +218,8 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
   fd.s_max = std::max(std::max(fd.vd_states, fd.dj_states), fd.g_max);
   auto& own = f->owned;
   int rc = 0;
-  {
-    // rows padded to a 16-byte pitch (cp.async staging), 512 zero bytes behind the last row so a
-    // partial last tile may read past column S
-    fd.tip_pitch = (S + 15) / 16 * 16;
-    std::vector<uint8_t> padded((size_t)T * fd.tip_pitch + 512, 0);
-    for (int r = 0; r < T; ++r) std::memcpy(padded.data() + (size_t)r * fd.tip_pitch, d->tip_codes + (size_t)r * S, S);
-    rc |= upload(padded.data(), padded.size(), &fd.tip_codes, own);
-  }
+  rc |= upload(d->tip_codes, (size_t)T * S, &fd.tip_codes, own);
+  f->h_tip_codes.assign(d->tip_codes, d->tip_codes + (size_t)T * S);
   auto region = [&](int n, const int32_t* off, const int32_t* inds, const int32_t** doff,
                     const int32_t** dinds, const char* name) {
     if (n == 0) return upload(off, 0, doff, own) | upload(inds, 0, dinds, own);
@@ -271,7 +268,7 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
 int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
   std::string k(key ? key : "");
   if (k == "sites_per_thread") {
-    if (value < 0 || value > 6) return fail("sites_per_thread must be 0 (auto) or 1..6");
+    if (value < 0 || value > 4) return fail("sites_per_thread must be 0 (auto) or 1..4");
     f->opt_sites_per_thread = (int)value;
   } else if (k == "smem_slots") {
     f->opt_smem_slots = (int)value;
@@ -308,16 +305,11 @@ namespace {
 // register footprint.
 int pick_sites_per_thread(int S, int threads) {
   if (S <= 4 * threads) return std::max(1, (S + threads - 1) / threads);
-  int best = 4, best_pad = 1 << 30;
-  for (int ns : {4, 5, 6}) {
-    const int tile = ns * threads;
-    const int pad = ((S + tile - 1) / tile) * tile - S;
-    if (pad < best_pad) {
-      best_pad = pad;
-      best = ns;
-    }
-  }
-  return best;
+  // 4 columns per thread amortise the per-step work best; fall back to 3 only when that pads
+  // the xMSA by a quarter less
+  const int pad4 = ((S + 4 * threads - 1) / (4 * threads)) * 4 * threads;
+  const int pad3 = ((S + 3 * threads - 1) / (3 * threads)) * 3 * threads;
+  return (pad3 * 4 < pad4 * 3) ? 3 : 4;
 }
 
 // Plans all trees into the pinned staging buffers (multi-threaded); returns max slots.
@@ -439,6 +431,26 @@ int lh_batch_run(lh_family_t* f) {
   int occ = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.smem_slots);
   if (occ < 1) return fail("pruning kernel cannot be resident with %d shared-memory slots", pc.smem_slots);
   pc.log_threshold = std::log(1.0 / std::pow(2.0, 256));
+  if (f->codes_ns != pc.sites_per_thread) {
+    // re-tile the tip codes for this NS (once per family and NS)
+    const int NS = pc.sites_per_thread;
+    std::vector<uint32_t> ct((size_t)T * pc.n_tiles * 32, 0u);
+    for (int r = 0; r < T; ++r)
+      for (int tile = 0; tile < pc.n_tiles; ++tile)
+        for (int lane = 0; lane < 32; ++lane) {
+          uint32_t word = 0;
+          for (int u = 0; u < NS; ++u) {
+            const int site = tile * 32 * NS + u * 32 + lane;
+            if (site < S) word |= (uint32_t)(f->h_tip_codes[(size_t)r * S + site] * 32u) << (8 * u);
+          }
+          ct[((size_t)r * pc.n_tiles + tile) * 32 + lane] = word;
+        }
+    if (f->d_codes_t.reserve(ct.size() * 4)) return 1;
+    LH_CUDA(cudaMemcpyAsync(f->d_codes_t.p, ct.data(), ct.size() * 4, cudaMemcpyHostToDevice, f->stream));
+    LH_CUDA(cudaStreamSynchronize(f->stream));
+    f->codes_ns = NS;
+  }
+  pc.codes_t = f->d_codes_t.as<uint32_t>();
 
   // chunk the batch so one chunk's branch records stay L2-resident
   const size_t rec_bytes_tree = (size_t)NB * 20 * R * sizeof(double);

@@ -111,11 +111,11 @@ void launch_eigen(const BatchDev& b, cudaStream_t s) {
 }
 
 // ---------------------------------------------------------------- k_pmatrix ---
-// One thread per (tree, branch, rate category). Branch records are laid out in the
-// order the pruning program consumes them: record 2*step+c for child c of a step, the
-// root edge last; each record is R blocks of 20 doubles (one per category):
-//   inner child : P[k][i][j] at k*20 + i*4 + j      (row-major as core_pmatrix.c; 4 pad)
-//   tip child   : Q[k][code][i] at k*20 + code*4 + i, code in A,C,G,T,N: the product
+// One thread per (tree, branch, rate category). Branch records are laid out in the order
+// the pruning program consumes them, one contiguous stream per (tree, category): record
+// 2*step+c for child c of a step, the root edge last; a record is 20 doubles:
+//   inner child : P[i][j] at i*4 + j                (row-major as core_pmatrix.c; 4 pad)
+//   tip child   : Q[code][i] at code*4 + i, code in A,C,G,T,N: the product
 //                 P[k] * tipclv(code) that set_tipclv + the generic kernel would form
 //                 (pll.c:926-930: one-hot for ACGT, all ones for N).
 __global__ void k_pmatrix(FamilyDev f, BatchDev b, int tree0, int ntrees) {
@@ -158,16 +158,16 @@ __global__ void k_pmatrix(FamilyDev f, BatchDev b, int tree0, int ntrees) {
         }
       }
     }
-    double* rec = b.prec + ((size_t)lt * NB + br) * (20 * R);
+    double* rec = b.prec + (((size_t)lt * R + k) * NB + br) * 20;
     if (!tip) {
-      double2* o = reinterpret_cast<double2*>(rec + k * 20);
+      double2* o = reinterpret_cast<double2*>(rec);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         o[2 * j] = make_double2(P[j][0], P[j][1]);
         o[2 * j + 1] = make_double2(P[j][2], P[j][3]);
       }
     } else {
-      double2* o = reinterpret_cast<double2*>(rec + k * 20);
+      double2* o = reinterpret_cast<double2*>(rec);
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         o[2 * c] = make_double2(P[0][c], P[1][c]);
@@ -199,12 +199,12 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 // columns. (With one column per thread the warp-uniform matrix loads saturated the L1 data pipe,
 // not the FP64 pipe: ncu r1a, lsu wavefronts 57 %, fp64 14 %.)
 //
-// Everything a step reads from global memory is staged into shared memory two steps ahead with
-// cp.async, so the dependent chain plan -> branch record -> tip code -> Q column never waits on
-// L2 (ncu r1a: 13.9 warps stalled on long scoreboard per issue):
-//   plan ring   64 steps, refilled 32 at a time
-//   record ring 4 steps x 2 children x 20 doubles (the category's P or Q block)
-//   code ring   4 steps x 2 children x 32*NS tip codes of this tile
+// Nothing in a step waits on L2 (ncu r1a: 13.9 warps stalled on long scoreboard per issue):
+//   plan ring   64 steps in shared memory, refilled 32 at a time with cp.async
+//   record ring 4 steps x 2 branches x 20 doubles (the category's P or Q blocks; the records of a
+//               pass are one contiguous stream, 320 bytes per step), cp.async two steps ahead
+//   tip codes   one 32-bit load per tip child (the NS codes of the lane, pre-multiplied by 32 =
+//               byte offset of the Q column), issued one step ahead into registers
 //
 // Inner CLVs never exist as arrays in HBM: the running result stays in registers, results
 // parked for a later step go to a per-column stack whose first `smem_slots` levels are shared
@@ -219,20 +219,32 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 // reference, this kernel keeps their full precision (a relative contribution < 2^-256).
 
 #ifndef LH_PRUNE_MIN_CTAS
-#define LH_PRUNE_MIN_CTAS 10
+#define LH_PRUNE_MIN_CTAS 12
 #endif
 
-constexpr int kRecRing = 4;    // steps of branch records / tip codes in flight
+constexpr int kRecRing = 4;    // steps of branch records in flight
 constexpr int kPlanRing = 64;  // plan entries resident
 constexpr int kRecDoubles = 20;
+constexpr int kStepBytes = 2 * kRecDoubles * 8;  // both branches of a step, one category
 
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
+__device__ __forceinline__ void cp_async16(unsigned smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_dst), "l"(gmem_src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// v < 2^-256 on the high word: 2^-256 = 0x2FF0000000000000, so for v >= +0 the comparison of the
+// bit patterns reduces to the high words, and every negative v (sign bit set) is below the
+// threshold as a signed integer too. Keeps the test off the FP64 pipe.
+constexpr int kThresholdHi = 0x2FF00000;
+
+// One parked CLV level of this lane: [u][state] doubles at stride 32 and [u] counts at stride 32.
+template <int NS>
+struct Slot {
+  double* clv;
+  int* cnt;
+};
 
 template <int NS>
 struct SlotIO {
@@ -242,85 +254,112 @@ struct SlotIO {
   int* g_cnt;         // [gslots][NS][32]
   int smem_slots, lane;
 
-  __device__ __forceinline__ void locate(int slot, double*& clv, int*& cnt) const {
-    if (slot < smem_slots) {
-      clv = smem_clv + (size_t)slot * (4 * NS) * 32 + lane;
-      cnt = smem_cnt + slot * NS * 32 + lane;
-    } else {
-      clv = g_clv + (size_t)(slot - smem_slots) * (4 * NS) * 32 + lane;
-      cnt = g_cnt + (slot - smem_slots) * NS * 32 + lane;
-    }
+  __device__ __forceinline__ bool in_smem(int slot) const { return slot < smem_slots; }
+  __device__ __forceinline__ Slot<NS> shared(int slot) const {
+    return {smem_clv + slot * (4 * NS) * 32 + lane, smem_cnt + slot * NS * 32 + lane};
+  }
+  __device__ __forceinline__ Slot<NS> global(int slot) const {
+    return {g_clv + (size_t)(slot - smem_slots) * (4 * NS) * 32 + lane, g_cnt + (slot - smem_slots) * NS * 32 + lane};
   }
 };
 
-// v < 2^-256 on the high word: 2^-256 = 0x2FF0000000000000, so for v >= +0 the comparison of the
-// bit patterns reduces to the high words, and every negative v (sign bit set) is below the
-// threshold as a signed integer too. Keeps the test off the FP64 pipe.
-__device__ __forceinline__ bool below_threshold(double v) { return __double2hiint(v) < 0x2FF00000; }
-
-// Messages of one child for the NS columns of this thread, m[u][i] = sum_j P[i][j] * c[u][j]
-// (core_partials.c:617-624), from the staged record `rec` (P row-major, or the 5 Q columns for
-// a tip) and the staged tip codes; also returns the child's scaler counts.
+// m[u][i] = sum_j P[i][j] * c[u][j]   (core_partials.c:617-624), P row-major in shared memory
 template <int NS>
-__device__ __forceinline__ void child_messages(int src, const double* rec, const uint8_t* codes,
-                                               const double (&reg)[NS][4], const int (&reg_cnt)[NS],
-                                               const SlotIO<NS>& io, double (&m)[NS][4], int (&cnt)[NS]) {
-  if (src >= 0) {  // tip: column `code` of Q (k_pmatrix), one 32-byte lookup per site
-#pragma unroll
-    for (int u = 0; u < NS; ++u) {
-      const int code = codes[u * 32 + io.lane];
-      const double2 q01 = *reinterpret_cast<const double2*>(rec + 4 * code);
-      const double2 q23 = *reinterpret_cast<const double2*>(rec + 4 * code + 2);
-      m[u][0] = q01.x; m[u][1] = q01.y; m[u][2] = q23.x; m[u][3] = q23.y;
-      cnt[u] = 0;
-    }
-    return;
-  }
-  double P[4][4];
+__device__ __forceinline__ void load_p(const double* rec, double (&P)[4][4]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const double2 p01 = *reinterpret_cast<const double2*>(rec + 4 * i);
     const double2 p23 = *reinterpret_cast<const double2*>(rec + 4 * i + 2);
     P[i][0] = p01.x; P[i][1] = p01.y; P[i][2] = p23.x; P[i][3] = p23.y;
   }
+}
+__device__ __forceinline__ void matvec(const double (&P)[4][4], const double (&c)[4], double (&m)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    double acc = P[i][0] * c[0];
+    acc += P[i][1] * c[1];
+    acc += P[i][2] * c[2];
+    acc += P[i][3] * c[3];
+    m[i] = acc;
+  }
+}
+
+// Messages of one child for the NS columns of this thread and the child's scaler counts.
+//   src >= 0  tip: column `code` of the staged Q block; `codes` holds the lane's NS byte offsets
+//   src == -1 the running result in registers
+//   else      a parked CLV
+template <int NS>
+__device__ __forceinline__ void child_messages(int src, const double* rec, unsigned codes,
+                                               const double (&reg)[NS][4], const int (&reg_cnt)[NS],
+                                               const SlotIO<NS>& io, double (&m)[NS][4], int (&cnt)[NS]) {
+  if (src >= 0) {
+    const char* q = reinterpret_cast<const char*>(rec);
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+      const unsigned off = (codes >> (8 * u)) & 0xffu;
+      const double2 q01 = *reinterpret_cast<const double2*>(q + off);
+      const double2 q23 = *reinterpret_cast<const double2*>(q + off + 16);
+      m[u][0] = q01.x; m[u][1] = q01.y; m[u][2] = q23.x; m[u][3] = q23.y;
+      cnt[u] = 0;
+    }
+    return;
+  }
+  double P[4][4];
+  load_p<NS>(rec, P);
   if (src == -1) {
 #pragma unroll
     for (int u = 0; u < NS; ++u) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        double acc = P[i][0] * reg[u][0];
-        acc += P[i][1] * reg[u][1];
-        acc += P[i][2] * reg[u][2];
-        acc += P[i][3] * reg[u][3];
-        m[u][i] = acc;
-      }
+      matvec(P, reg[u], m[u]);
       cnt[u] = reg_cnt[u];
     }
     return;
   }
-  double* clv;
-  int* pc;
-  io.locate(-2 - src, clv, pc);
+  const int slot = -2 - src;
+  if (io.in_smem(slot)) {
+    const Slot<NS> sl = io.shared(slot);
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+      double c[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) c[j] = sl.clv[(u * 4 + j) * 32];
+      matvec(P, c, m[u]);
+      cnt[u] = sl.cnt[u * 32];
+    }
+  } else {
+    const Slot<NS> sl = io.global(slot);
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+      double c[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) c[j] = sl.clv[(u * 4 + j) * 32];
+      matvec(P, c, m[u]);
+      cnt[u] = sl.cnt[u * 32];
+    }
+  }
+}
+
+template <int NS>
+__device__ __forceinline__ void park(const Slot<NS>& sl, const double (&reg)[NS][4], const int (&reg_cnt)[NS]) {
 #pragma unroll
   for (int u = 0; u < NS; ++u) {
-    double c[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) c[j] = clv[(u * 4 + j) * 32];
+    for (int i = 0; i < 4; ++i) sl.clv[(u * 4 + i) * 32] = reg[u][i];
+    sl.cnt[u * 32] = reg_cnt[u];
+  }
+}
+template <int NS>
+__device__ __forceinline__ void unpark(const Slot<NS>& sl, double (&reg)[NS][4], int (&reg_cnt)[NS]) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      double acc = P[i][0] * c[0];
-      acc += P[i][1] * c[1];
-      acc += P[i][2] * c[2];
-      acc += P[i][3] * c[3];
-      m[u][i] = acc;
-    }
-    cnt[u] = pc[u * 32];
+  for (int u = 0; u < NS; ++u) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) reg[u][i] = sl.clv[(u * 4 + i) * 32];
+    reg_cnt[u] = sl.cnt[u * 32];
   }
 }
 
 size_t prune_smem_bytes(int ns, int smem_slots) {
-  return (size_t)kRecRing * 2 * kRecDoubles * sizeof(double) + kPlanRing * sizeof(int4) +
-         (size_t)kRecRing * 2 * ns * 32 + (size_t)smem_slots * 32 * ns * (4 * sizeof(double) + sizeof(int));
+  return (size_t)kRecRing * kStepBytes + kPlanRing * sizeof(int4) +
+         (size_t)smem_slots * 32 * ns * (4 * sizeof(double) + sizeof(int));
 }
 
 template <int NS>
@@ -330,11 +369,10 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
   const int lane = threadIdx.x, T = f.T, S = f.S, R = b.R;
   const int NB = 2 * T - 3, n_steps = T - 2, n_iter = T - 1;  // node updates + the edge evaluation
   const int gslots = cfg.total_slots - cfg.smem_slots;
-  double* ring_rec = reinterpret_cast<double*>(smem_raw);                       // [kRecRing][2][20]
-  int4* ring_plan = reinterpret_cast<int4*>(ring_rec + kRecRing * 2 * kRecDoubles);  // [kPlanRing]
-  uint8_t* ring_code = reinterpret_cast<uint8_t*>(ring_plan + kPlanRing);       // [kRecRing][2][NS*32]
+  double* ring_rec = reinterpret_cast<double*>(smem_raw);                            // [kRecRing][2][20]
+  int4* ring_plan = reinterpret_cast<int4*>(smem_raw + kRecRing * kStepBytes);       // [kPlanRing]
   SlotIO<NS> io;
-  io.smem_clv = reinterpret_cast<double*>(ring_code + kRecRing * 2 * NS * 32);
+  io.smem_clv = reinterpret_cast<double*>(ring_plan + kPlanRing);
   io.smem_cnt = reinterpret_cast<int*>(io.smem_clv + (size_t)cfg.smem_slots * (4 * NS) * 32);
   io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * NS) * 32;
   io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * 32;
@@ -342,20 +380,20 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
   io.lane = lane;
   const double weight = 1.0 / R;  // pll.c:746-747
   constexpr double kDown = LH_SCALE_THRESHOLD;
-  // lane roles in the staging copies (16 bytes per lane)
-  const int rec_child = lane / 10, rec_part = lane % 10;  // lanes 0..19: 2 children x 160 bytes
-  const bool rec_lane = lane < 20;
-  const bool code_lane = lane < 2 * NS;                   // 32*NS code bytes per tip child
+  // staging roles: lanes 0..19 each copy 16 of the 320 record bytes of a step
+  const bool rec_lane = lane < kStepBytes / 16;
+  const unsigned ring_rec_s = (unsigned)__cvta_generic_to_shared(ring_rec) + lane * 16;
+  const unsigned ring_plan_s = (unsigned)__cvta_generic_to_shared(ring_plan);
+  const size_t pass_bytes = (size_t)NB * kRecDoubles * 8;  // records of one (tree, category)
+  const size_t code_pitch = (size_t)cfg.n_tiles * 32;      // words per tip row
 
   const int n_work = ntrees * cfg.n_tiles;
   for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
     const int lt = w / cfg.n_tiles, tile = w - lt * cfg.n_tiles;
     const int t = tree0 + lt;
-    const int tile_base = tile * (32 * NS);
     const int4* __restrict__ plan = b.plan + (size_t)t * (T - 1);
-    const double* __restrict__ recs = b.prec + (size_t)lt * NB * (kRecDoubles * R);
     const double* __restrict__ eig = b.eig + (size_t)t * kEigStride;
-    const uint8_t* __restrict__ code_base = f.tip_codes + tile_base + lane * 16;
+    const unsigned* __restrict__ my_codes = cfg.codes_t + (size_t)tile * 32 + lane;
     const double pi0 = eig[40], pi1 = eig[41], pi2 = eig[42], pi3 = eig[43];
 
     // sum over categories of the edge terms, kept as acc * 2^(-256 * acc_cnt)
@@ -365,37 +403,26 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
     for (int u = 0; u < NS; ++u) { acc[u] = 0.0; acc_cnt[u] = 0; }
 
     for (int k = 0; k < R; ++k) {
-      // stage the plan entries [q0, q0+32) into their half of the plan ring
+      // the record stream of this (tree, category): step q at rec_src + q * 320 bytes
+      const char* rec_src = reinterpret_cast<const char*>(b.prec) + ((size_t)lt * R + k) * pass_bytes + lane * 16;
+      const size_t rec_end = pass_bytes;  // bytes valid in the stream
       auto stage_plan = [&](int q0) {
         const int q = q0 + lane;
-        if (q < n_iter) cp_async16(ring_plan + (q & (kPlanRing - 1)), plan + q);
+        if (q < n_iter) cp_async16(ring_plan_s + (q & (kPlanRing - 1)) * 16, plan + q);
       };
-      // stage what step q reads: the category's record of both branches and the codes of tip children
-      auto stage_step = [&](int q) {
-        if (q >= n_iter) return;
-        const int slot = q & (kRecRing - 1);
-        if (rec_lane) {
-          const int ri = 2 * q + rec_child;
-          if (ri < NB)
-            cp_async16(ring_rec + (slot * 2 + rec_child) * kRecDoubles + rec_part * 2,
-                       recs + ((size_t)ri * R + k) * kRecDoubles + rec_part * 2);
-        }
-        const int4 sq = ring_plan[q & (kPlanRing - 1)];
-        if (code_lane) {
-          if (sq.x >= 0) cp_async16(ring_code + (slot * 2 + 0) * (NS * 32) + lane * 16, code_base + (size_t)sq.x * f.tip_pitch);
-          if (sq.y >= 0) cp_async16(ring_code + (slot * 2 + 1) * (NS * 32) + lane * 16, code_base + (size_t)sq.y * f.tip_pitch);
-        }
+      auto stage_records = [&](int q) {  // the last step has a single record (the root edge)
+        if (rec_lane && (size_t)q * kStepBytes + lane * 16 < rec_end)
+          cp_async16(ring_rec_s + (q & (kRecRing - 1)) * kStepBytes, rec_src + (size_t)q * kStepBytes);
       };
       __syncwarp();  // the previous pass / work item is done with the rings
       stage_plan(0);
       stage_plan(32);
+      stage_records(0);
       cp_async_commit();
-      cp_async_wait<0>();
+      stage_records(1);
+      cp_async_commit();
+      cp_async_wait<1>();
       __syncwarp();
-      stage_step(0);
-      cp_async_commit();
-      stage_step(1);
-      cp_async_commit();
 
       double reg[NS][4];
       int reg_cnt[NS];
@@ -405,67 +432,70 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
 #pragma unroll
         for (int i = 0; i < 4; ++i) reg[u][i] = 0.0;
       }
+      // software pipeline registers: the step being executed and the next one
+      int4 st_next = ring_plan[0];
+      unsigned cA_next = 0, cB_next = 0;
+      if (st_next.x >= 0) cA_next = __ldg(my_codes + (size_t)st_next.x * code_pitch);
+      if (st_next.y >= 0) cB_next = __ldg(my_codes + (size_t)st_next.y * code_pitch);
+
       for (int s = 0; s < n_iter; ++s) {
         if ((s & 31) == 0 && s > 0) {
           __syncwarp();           // every lane has read the plan entries of the half being replaced
           stage_plan(s + 32);
         }
-        stage_step(s + 2);
+        stage_records(s + 2);
         cp_async_commit();
-        cp_async_wait<2>();       // everything staged for step s (two commits ago) has landed
+        cp_async_wait<2>();       // the records of step s (two commits ago) have landed
         __syncwarp();
-        const int slot = s & (kRecRing - 1);
-        const int4 st = ring_plan[s & (kPlanRing - 1)];
-        const double* recA = ring_rec + (slot * 2) * kRecDoubles;
-        const uint8_t* codeA = ring_code + (slot * 2) * (NS * 32);
+        const int4 st = st_next;
+        const unsigned cA = cA_next, cB = cB_next;
+        if (s + 1 < n_iter) {     // plan and tip codes of the next step
+          st_next = ring_plan[(s + 1) & (kPlanRing - 1)];
+          if (st_next.x >= 0) cA_next = __ldg(my_codes + (size_t)st_next.x * code_pitch);
+          if (st_next.y >= 0) cB_next = __ldg(my_codes + (size_t)st_next.y * code_pitch);
+        }
+        const double* recA = ring_rec + (s & (kRecRing - 1)) * (2 * kRecDoubles);
         if (s < n_steps) {
           double ma[NS][4], mb[NS][4];
           int ca[NS], cb[NS];
-          child_messages<NS>(st.x, recA, codeA, reg, reg_cnt, io, ma, ca);
-          child_messages<NS>(st.y, recA + kRecDoubles, codeA + NS * 32, reg, reg_cnt, io, mb, cb);
+          child_messages<NS>(st.x, recA, cA, reg, reg_cnt, io, ma, ca);
+          child_messages<NS>(st.y, recA + kRecDoubles, cB, reg, reg_cnt, io, mb, cb);
+          int lowest = 0x7fffffff;  // min over columns of the largest high word
 #pragma unroll
           for (int u = 0; u < NS; ++u) {
-            bool all_small = true;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const double v = ma[u][i] * mb[u][i];  // core_partials.c:626
-              reg[u][i] = v;
-              all_small = all_small && below_threshold(v);
-            }
+            for (int i = 0; i < 4; ++i) reg[u][i] = ma[u][i] * mb[u][i];  // core_partials.c:626
             reg_cnt[u] = ca[u] + cb[u];  // fill_parent_scaler, core_partials.c:24-46
-            if (all_small) {
+            const int hi = max(max(__double2hiint(reg[u][0]), __double2hiint(reg[u][1])),
+                               max(__double2hiint(reg[u][2]), __double2hiint(reg[u][3])));
+            lowest = min(lowest, hi);
+          }
+          if (lowest < kThresholdHi) {  // some column has all four entries below 2^-256
 #pragma unroll
-              for (int i = 0; i < 4; ++i) reg[u][i] *= LH_SCALE_FACTOR;
-              reg_cnt[u] += 1;
+            for (int u = 0; u < NS; ++u) {
+              const int hi = max(max(__double2hiint(reg[u][0]), __double2hiint(reg[u][1])),
+                                 max(__double2hiint(reg[u][2]), __double2hiint(reg[u][3])));
+              if (hi < kThresholdHi) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) reg[u][i] *= LH_SCALE_FACTOR;
+                reg_cnt[u] += 1;
+              }
             }
           }
           if (st.z >= 0) {
-            double* clv;
-            int* pc;
-            io.locate(st.z, clv, pc);
-#pragma unroll
-            for (int u = 0; u < NS; ++u) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) clv[(u * 4 + i) * 32] = reg[u][i];
-              pc[u * 32] = reg_cnt[u];
-            }
+            if (io.in_smem(st.z)) park<NS>(io.shared(st.z), reg, reg_cnt);
+            else park<NS>(io.global(st.z), reg, reg_cnt);
           }
         } else {
           // ---- edge term of this category (core_likelihood_avx.c:1130-1239); the edge's record
-          // sits in the first child position of the last step, st.y is the child across it ----
+          // sits in the first branch position of the last step, st.y is the child across it ----
           double mc[NS][4];
           int cc[NS];
-          child_messages<NS>(st.y, recA, codeA + NS * 32, reg, reg_cnt, io, mc, cc);
+          child_messages<NS>(st.y, recA, cB, reg, reg_cnt, io, mc, cc);
           if (st.x != -1) {  // the root CLV was parked; fetch it
-            double* clv;
-            int* pc;
-            io.locate(-2 - st.x, clv, pc);
-#pragma unroll
-            for (int u = 0; u < NS; ++u) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) reg[u][i] = clv[(u * 4 + i) * 32];
-              reg_cnt[u] = pc[u * 32];
-            }
+            const int slot = -2 - st.x;
+            if (io.in_smem(slot)) unpark<NS>(io.shared(slot), reg, reg_cnt);
+            else unpark<NS>(io.global(slot), reg, reg_cnt);
           }
 #pragma unroll
           for (int u = 0; u < NS; ++u) {
@@ -489,14 +519,15 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
       cp_async_wait<0>();
     }
 
+    const unsigned naive = __ldg(my_codes);  // xMSA row 0 is the naive sequence
 #pragma unroll
     for (int u = 0; u < NS; ++u) {
-      const int site = tile_base + u * 32 + lane;
+      const int site = tile * (32 * NS) + u * 32 + lane;
       if (site >= S) continue;
       double site_lk = log(acc[u]);
       if (acc_cnt[u]) site_lk += acc_cnt[u] * cfg.log_threshold;   // :1247-1251
-      // naive-sequence correction (src/PhyloHMM.cpp:229-237); xMSA row 0 is the naive
-      const int nb = __ldg(f.tip_codes + site);
+      // naive-sequence correction (src/PhyloHMM.cpp:229-237)
+      const int nb = ((naive >> (8 * u)) & 0xffu) >> 5;
       if (nb != 4) site_lk -= eig[36 + nb];
       b.xe[(size_t)t * S + site] = exp(site_lk);
     }
@@ -508,9 +539,7 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
     case 1: { constexpr int NN = 1; CALL; } break;    \
     case 2: { constexpr int NN = 2; CALL; } break;    \
     case 3: { constexpr int NN = 3; CALL; } break;    \
-    case 4: { constexpr int NN = 4; CALL; } break;    \
-    case 5: { constexpr int NN = 5; CALL; } break;    \
-    default: { constexpr int NN = 6; CALL; } break;   \
+    default: { constexpr int NN = 4; CALL; } break;   \
   }
 
 template <int NS>

@@ -17,8 +17,7 @@ struct CscDev {
 
 struct FamilyDev {
   int32_t T, S;                 // tips, xMSA columns
-  const uint8_t* tip_codes;     // [T][tip_pitch], zero-padded tail
-  int32_t tip_pitch;            // row pitch in bytes, a multiple of 16
+  const uint8_t* tip_codes;     // [T][S]
   int32_t has_d, n_v, n_d, n_j;
   int32_t vd_sites, vd_states, dj_sites, dj_states;
   const int32_t *vpad_off, *vpad_inds, *vgerm_off, *vgerm_inds, *dgerm_off, *dgerm_inds;
@@ -38,7 +37,7 @@ struct BatchDev {
   const double* pi;      // [B][4]
   const double* rates;   // [B][R]
   double* eig;           // [B][kEigStride]
-  double* prec;          // [chunk][2T-3][20R] branch records
+  double* prec;          // [chunk][R][2T-3][20] branch records
   double* xe;            // [B][S] xmsa_emission
   double* loglik;        // [B]
 };
@@ -52,6 +51,9 @@ struct PruneCfg {
   double* scratch;       // [grid][total_slots-smem_slots][4 NS][32] doubles
   int32_t* scratch_cnt;  // [grid][total_slots-smem_slots][NS][32]
   double log_threshold;  // log(2^-256), host libm (core_likelihood_avx.c:1249)
+  // tip codes re-tiled for this NS: word [tip][tile][lane], byte u = 32 * code of column
+  // tile*32*NS + u*32 + lane (0 beyond S); 32*code is the byte offset of the Q column
+  const uint32_t* codes_t;
 };
 
 struct HmmOut {           // optional device buffers (may be null)

@@ -48,5 +48,5 @@ def probe(name, opts_list, n_port=2, reps=3, rep=1):
 
 if __name__ == "__main__":
     print(json.dumps({"fp64_peak_tflops": device.fp64_peak_tflops(0)}), flush=True)
-    probe("probe_c3", [{}, {"sites_per_thread": 5}, {"sites_per_thread": 3}, {"sites_per_thread": 2}, {"sites_per_thread": 6}, {"smem_slots": 0}, {"smem_slots": 2}])
-    probe("probe_c4", [{}, {"sites_per_thread": 5}, {"smem_slots": 0}, {"smem_slots": 3}], n_port=1, rep=8)
+    probe("probe_c3", [{}, {"sites_per_thread": 3}, {"sites_per_thread": 2}, {"smem_slots": 0}, {"smem_slots": 2}])
+    probe("probe_c4", [{}, {"sites_per_thread": 3}, {"smem_slots": 0}, {"smem_slots": 2}, {"smem_slots": 4}], n_port=1, rep=8)

@@ -48,7 +48,7 @@ def test_matches_oracle_port(name):
     _check(fam, tb, pll, pout, name)
 
 
-@pytest.mark.parametrize("ns,slots", [(1, 0), (2, 1), (3, -1), (5, 0), (4, 2), (6, -1)])
+@pytest.mark.parametrize("ns,slots", [(1, 0), (2, 1), (3, -1), (4, 0), (4, 2), (3, 1)])
 def test_tiling_and_stack_placement_do_not_change_results(ns, slots):
     """Results are independent of the site tiling (xMSA columns per thread) and of where the CLV
     stack lives (shared memory / L2 scratch)."""
