@@ -39,6 +39,41 @@ int lhh_newick_to_ops(int32_t n_tips, const char* const* labels, int32_t n_trees
                       const char* const* newicks, int32_t n_threads, int32_t* children,
                       double* blen, int32_t* root_child, double* root_blen);
 
+/* ---- linearham::PhyloHMM (linearham_b200/csrc/host/phylo_hmm.hpp), the host-side mirror of the
+ * reference class (src/PhyloHMM.hpp:24-127, src/HMM.hpp:31-413), behind a C handle so that
+ * non-C++ callers (the ctypes tests, bench.py) can drive it. Construction is pure host work
+ * (YAML -> state space -> transitions -> xMSA) and needs no GPU; the scoring calls go through the
+ * device ABI and fail without one.                                                            */
+struct lh_family_desc;
+typedef struct lhh_phylohmm lhh_phylohmm_t;
+
+/* PhyloHMM(yaml_path, cluster_ind, hmm_param_dir, seed) - src/PhyloHMM.cpp:29-34. NULL on failure. */
+lhh_phylohmm_t* lhh_phylohmm_new(const char* yaml_path, int32_t cluster_ind, const char* hmm_param_dir, int32_t seed);
+void lhh_phylohmm_free(lhh_phylohmm_t* h);
+int lhh_phylohmm_set_device(lhh_phylohmm_t* h, int32_t device);
+/* The flat family description for lh_family_create; pointers live as long as the handle. */
+int lhh_phylohmm_family_desc(lhh_phylohmm_t* h, struct lh_family_desc* out);
+/* InitializePhyloParameters(newick_path, er, pi, alpha, num_rates) - src/PhyloHMM.cpp:350-361 */
+int lhh_phylohmm_init_params(lhh_phylohmm_t* h, const char* newick_path, const double* er /*[6]*/,
+                             const double* pi /*[4]*/, double alpha, int32_t num_rates);
+int lhh_phylohmm_init_emission(lhh_phylohmm_t* h);             /* InitializePhyloEmission(), :366-383 */
+int lhh_phylohmm_loglikelihood(lhh_phylohmm_t* h, double* out); /* LogLikelihood(), src/HMM.cpp:345-354 */
+int lhh_phylohmm_sample_naive(lhh_phylohmm_t* h, char* out, int32_t cap); /* SampleNaiveSequence(), :358-431 */
+/* RunPipeline(input_path, output_path, num_rates) - src/PhyloHMM.cpp:393-446 - scoring batch_size
+ * RevBayes samples per device call.                                                            */
+int lhh_phylohmm_run_pipeline(lhh_phylohmm_t* h, const char* input_path, const char* output_path,
+                              int32_t num_rates, int32_t batch_size);
+/* The loop body :419-430 for n samples at once: log-likelihoods only.                           */
+int lhh_phylohmm_score_samples(lhh_phylohmm_t* h, int32_t n, const char* const* newicks, const double* er,
+                               const double* pi, const double* alpha, int32_t num_rates, double* loglik);
+/* pll_utree_export_newick of a Newick string (libpll utree.c:148-270), as written to the output TSV. */
+int lhh_export_newick(const char* newick, char* out, int32_t cap);
+/* Named read-outs of the object's members (accessor names of src/HMM.hpp / src/PhyloHMM.hpp
+ * without the trailing underscore), column-major; out = NULL queries the shape.                 */
+int lhh_phylohmm_get_f64(lhh_phylohmm_t* h, const char* name, double* out, int32_t* rows, int32_t* cols);
+int lhh_phylohmm_get_i32(lhh_phylohmm_t* h, const char* name, int32_t* out, int32_t* rows, int32_t* cols);
+int lhh_phylohmm_get_str(lhh_phylohmm_t* h, const char* name, char* out, int32_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,526 @@
+// linearham::PhyloHMM - xMSA construction (bit-exact restatement of src/PhyloHMM.cpp:45-89,
+// 123-144, 461-536), the per-sample entry points of the reference API routed to the CUDA library,
+// and the batched RunPipeline (src/PhyloHMM.cpp:393-446 with B rows per device call).
+#include "phylo_hmm.hpp"
+
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <stdexcept>
+
+#include "../../../include/linearham_b200.h"
+#include "../../../include/linearham_b200_host.h"
+
+namespace lhb {
+int gamma_mean_rates(double alpha, int n, double* out);  // gamma.cpp
+}
+
+namespace linearham {
+
+namespace {
+
+const double kEps = 1e-6;  // src/utils.hpp:20
+
+// ({naive base, MSA site} -> xMSA column), columns numbered in first-insertion order
+typedef std::map<std::pair<int, int>, int> XmsaIds;
+
+int StoreXmsaIndex(std::pair<int, int> id, XmsaIds& ids) {
+  auto ins = ids.emplace(id, (int)ids.size());
+  return ins.first->second;
+}
+
+void StoreGermlinePaddingXmsaIndices(GermlineRegion& R, XmsaIds& ids) {
+  R.xmsa_inds.assign(R.naive_bases.size(), -1);
+  for (std::size_t i = 0; i < R.naive_bases.size(); ++i) R.xmsa_inds[i] = StoreXmsaIndex({R.naive_bases[i], R.site_inds[i]}, ids);
+}
+
+void StoreJunctionXmsaIndices(JunctionRegion& R, std::pair<int, int> lfb, std::pair<int, int> rfb, XmsaIds& ids) {
+  const int site_start = lfb.first, site_end = rfb.second;
+  R.xmsa_inds.assign(site_end - site_start, (int)R.naive_bases.size(), -1);
+  for (std::size_t i = 0; i < R.naive_bases.size(); ++i) {
+    if (R.site_inds[i] == -1) {  // an NTI state may sit at every junction site
+      for (int s = site_start; s < site_end; ++s) R.xmsa_inds(s - site_start, (int)i) = StoreXmsaIndex({R.naive_bases[i], s}, ids);
+    } else {
+      R.xmsa_inds(R.site_inds[i] - site_start, (int)i) = StoreXmsaIndex({R.naive_bases[i], R.site_inds[i]}, ids);
+    }
+  }
+}
+
+std::string read_file(const std::string& path) {
+  std::ifstream in(path);
+  if (!in) throw std::runtime_error("cannot open " + path);
+  std::stringstream ss;
+  ss << in.rdbuf();
+  return ss.str();
+}
+
+// one line of a tab-separated file with "" quoting (fast-cpp-csv-parser double_quote_escape<'\t','"'>)
+std::vector<std::string> split_tsv(const std::string& line) {
+  std::vector<std::string> out;
+  std::string cur;
+  bool quoted = false;
+  for (std::size_t i = 0; i < line.size(); ++i) {
+    const char c = line[i];
+    if (quoted) {
+      if (c == '"') {
+        if (i + 1 < line.size() && line[i + 1] == '"') { cur.push_back('"'); ++i; }
+        else quoted = false;
+      } else {
+        cur.push_back(c);
+      }
+    } else if (c == '"') {
+      quoted = true;
+    } else if (c == '\t') {
+      out.push_back(cur);
+      cur.clear();
+    } else if (c != '\r') {
+      cur.push_back(c);
+    }
+  }
+  out.push_back(cur);
+  return out;
+}
+
+double to_double(const std::string& s, const std::string& what) {
+  char* end = nullptr;
+  const double v = std::strtod(s.c_str(), &end);
+  if (end == s.c_str()) throw std::runtime_error("cannot parse " + what + " \"" + s + "\"");
+  return v;
+}
+
+// ---- Newick re-export (pll_utree_export_newick, utree.c:148-270) ----------------------------
+struct NwParser {
+  const std::string& s;
+  std::size_t p = 0;
+  explicit NwParser(const std::string& str) : s(str) {}
+  void skip() {
+    for (;;) {
+      while (p < s.size() && (s[p] == ' ' || s[p] == '\t' || s[p] == '\n' || s[p] == '\r')) ++p;
+      if (p < s.size() && s[p] == '[') {
+        while (p < s.size() && s[p] != ']') ++p;
+        if (p < s.size()) ++p;
+      } else {
+        return;
+      }
+    }
+  }
+  std::string label() {
+    skip();
+    const std::size_t b = p;
+    while (p < s.size() && std::strchr("(),:;[ \t\n\r", s[p]) == nullptr) ++p;
+    return s.substr(b, p - b);
+  }
+  double length() {
+    skip();
+    double v = 0.0;
+    if (p < s.size() && s[p] == ':') {
+      ++p;
+      skip();
+      char* end = nullptr;
+      v = std::strtod(s.c_str() + p, &end);
+      if (end == s.c_str() + p) throw std::invalid_argument("malformed branch length in Newick string");
+      p = end - s.c_str();
+    }
+    return v ? v : kEps;
+  }
+  std::string subtree(bool top) {
+    skip();
+    char buf[64];
+    if (p < s.size() && s[p] == '(') {
+      ++p;
+      std::vector<std::string> kids;
+      kids.push_back(subtree(false));
+      skip();
+      while (p < s.size() && s[p] == ',') {
+        ++p;
+        kids.push_back(subtree(false));
+        skip();
+      }
+      if (p >= s.size() || s[p] != ')') throw std::invalid_argument("unbalanced Newick string");
+      ++p;
+      const std::string lab = label();
+      const double len = length();
+      if (kids.size() != (top ? 3u : 2u)) throw std::invalid_argument("Newick tree is not an unrooted binary tree");
+      std::string out = "(" + kids[0];
+      for (std::size_t i = 1; i < kids.size(); ++i) out += "," + kids[i];
+      if (top) return out + ")" + lab + ":0.0;";
+      std::snprintf(buf, sizeof(buf), ":%f", len);
+      return out + ")" + lab + buf;
+    }
+    const std::string lab = label();
+    if (lab.empty()) throw std::invalid_argument("empty tip label in Newick string");
+    std::snprintf(buf, sizeof(buf), ":%f", length());
+    return lab + buf;
+  }
+};
+
+}  // namespace
+
+std::string ExportNewick(const std::string& newick) {
+  NwParser ps(newick);
+  return ps.subtree(true);
+}
+
+// flat arrays behind lh_family_desc_t
+struct PhyloHMM::FlatFamily {
+  std::vector<uint8_t> tip_codes;
+  std::vector<int32_t> off[5], inds[5];
+  std::vector<int32_t> vd_inds, dj_inds;
+  std::vector<double> v_gene_prob, v_trans_prod;
+  std::vector<const char*> label_ptrs;
+  lh_family_desc_t desc;
+};
+
+PhyloHMM::PhyloHMM(const std::string& yaml_path, int cluster_ind, const std::string& hmm_param_dir, int seed)
+    : HMM(yaml_path, cluster_ind, hmm_param_dir, seed) {
+  InitializeXmsaStructs();
+  BuildFlatFamily();
+}
+
+PhyloHMM::~PhyloHMM() {
+  if (dev_family_) lh_family_destroy(dev_family_);
+}
+
+// src/PhyloHMM.cpp:45-89, 123-144
+void PhyloHMM::InitializeXmsaStructs() {
+  xmsa_labels_.clear();
+  xmsa_labels_.push_back("naive");
+  for (const auto& id : cluster_data_.at("unique_ids").seq) xmsa_labels_.push_back(id.as_string());
+  xmsa_naive_ind_ = 0;
+
+  XmsaIds ids;
+  StoreGermlinePaddingXmsaIndices(vpadding_, ids);
+  StoreGermlinePaddingXmsaIndices(vgerm_, ids);
+  if (locus_ == "igh") {
+    StoreJunctionXmsaIndices(vd_junction_, flexbounds_.at("v_r"), flexbounds_.at("d_l"), ids);
+    StoreGermlinePaddingXmsaIndices(dgerm_, ids);
+    StoreJunctionXmsaIndices(dj_junction_, flexbounds_.at("d_r"), flexbounds_.at("j_l"), ids);
+  } else {
+    StoreJunctionXmsaIndices(vd_junction_, flexbounds_.at("v_r"), flexbounds_.at("j_l"), ids);
+  }
+  StoreGermlinePaddingXmsaIndices(jgerm_, ids);
+  StoreGermlinePaddingXmsaIndices(jpadding_, ids);
+
+  // BuildXmsa: column = [naive base ; the MSA column of the site]
+  const int n = msa_.rows();
+  xmsa_.assign(n + 1, (int)ids.size(), -1);
+  for (const auto& kv : ids) {
+    const int naive_base = kv.first.first, site = kv.first.second, col = kv.second;
+    if (site < 0 || site >= msa_.cols()) throw std::runtime_error("flexbounds / relpos reach outside the alignment");
+    xmsa_(0, col) = naive_base;
+    for (int i = 0; i < n; ++i) xmsa_(i + 1, col) = msa_(i, site);
+  }
+  xmsa_seqs_.assign(n + 1, std::string(xmsa_.cols(), ' '));
+  for (int i = 0; i <= n; ++i)
+    for (int j = 0; j < xmsa_.cols(); ++j) xmsa_seqs_[i][j] = alphabet_.at(xmsa_(i, j));
+}
+
+void PhyloHMM::BuildFlatFamily() {
+  flat_.reset(new FlatFamily);
+  FlatFamily& F = *flat_;
+  const int T = xmsa_.rows(), S = xmsa_.cols();
+  F.tip_codes.resize((std::size_t)T * S);
+  for (int i = 0; i < T; ++i)
+    for (int j = 0; j < S; ++j) F.tip_codes[(std::size_t)i * S + j] = (uint8_t)xmsa_(i, j);
+  const GermlineRegion* regions[5] = {&vpadding_, &vgerm_, &dgerm_, &jgerm_, &jpadding_};
+  for (int r = 0; r < 5; ++r) {
+    const GermlineRegion& R = *regions[r];
+    F.off[r].assign(1, 0);
+    for (const auto& kv : R.ggene_ranges) {  // ranges are contiguous in map order
+      for (int i = kv.second.first; i < kv.second.second; ++i) F.inds[r].push_back(R.xmsa_inds[i]);
+      F.off[r].push_back((int32_t)F.inds[r].size());
+    }
+    if (F.inds[r].empty()) F.inds[r].push_back(0);
+  }
+  F.vd_inds.assign(vd_junction_.xmsa_inds.v.begin(), vd_junction_.xmsa_inds.v.end());
+  F.dj_inds.assign(dj_junction_.xmsa_inds.v.begin(), dj_junction_.xmsa_inds.v.end());
+  if (F.dj_inds.empty()) F.dj_inds.push_back(-1);
+  for (const auto& kv : vgerm_.ggene_ranges) {  // src/HMM.cpp:296-314
+    const lhb::GermlineGene& g = ggenes_.at(kv.first);
+    F.v_gene_prob.push_back(g.gene_prob);
+    // product of the in-region germline transitions in Eigen's reduction order (see hmm_model.cpp)
+    const int s = vgerm_.germ_inds.at(kv.second.first), len = kv.second.second - kv.second.first - 1;
+    const double prod = EigenOrderProduct(g.transition.data() + s, len, s);
+    F.v_trans_prod.push_back(prod);
+  }
+  for (const std::string& l : xmsa_labels_) F.label_ptrs.push_back(l.c_str());
+
+  lh_family_desc_t& d = F.desc;
+  std::memset(&d, 0, sizeof(d));
+  d.n_tips = T;
+  d.n_sites = S;
+  d.tip_codes = F.tip_codes.data();
+  d.has_d = locus_ == "igh";
+  d.n_v = (int)vgerm_.state_strs.size();
+  d.n_d = (int)dgerm_.state_strs.size();
+  d.n_j = (int)jgerm_.state_strs.size();
+  d.vd_sites = vd_junction_.xmsa_inds.rows();
+  d.vd_states = vd_junction_.xmsa_inds.cols();
+  d.dj_sites = dj_junction_.xmsa_inds.rows();
+  d.dj_states = dj_junction_.xmsa_inds.cols();
+  d.vpad_off = F.off[0].data();  d.vpad_inds = F.inds[0].data();
+  d.vgerm_off = F.off[1].data(); d.vgerm_inds = F.inds[1].data();
+  d.dgerm_off = F.off[2].data(); d.dgerm_inds = F.inds[2].data();
+  d.jgerm_off = F.off[3].data(); d.jgerm_inds = F.inds[3].data();
+  d.jpad_off = F.off[4].data();  d.jpad_inds = F.inds[4].data();
+  d.vd_inds = F.vd_inds.data();
+  d.dj_inds = F.dj_inds.data();
+  d.v_gene_prob = F.v_gene_prob.data();
+  d.v_trans_prod = F.v_trans_prod.data();
+  d.vpad_trans = vpadding_transition_.data();
+  d.jpad_trans = jpadding_transition_.data();
+  d.t_v_vd = vgerm_vd_junction_transition_.data();
+  d.t_vd = vd_junction_transition_.data();
+  d.t_vd_d = vd_junction_dgerm_transition_.data();
+  d.t_d_dj = dgerm_dj_junction_transition_.data();
+  d.t_dj = dj_junction_transition_.data();
+  d.t_dj_j = dj_junction_jgerm_transition_.data();
+}
+
+const lh_family_desc& PhyloHMM::family_desc() const { return flat_->desc; }
+
+void PhyloHMM::EnsureDeviceFamily() {
+  if (dev_family_) return;
+  if (lh_family_create(&dev_family_, &flat_->desc, device_)) throw std::runtime_error(lh_last_error());
+}
+
+// src/PhyloHMM.cpp:350-361
+void PhyloHMM::InitializePhyloParameters(const std::string& newick_path, const std::vector<double>& er,
+                                         const std::vector<double>& pi, double alpha, int num_rates) {
+  if (er.size() != 6 || pi.size() != 4) throw std::invalid_argument("er must have 6 and pi 4 entries");
+  tree_ = read_file(newick_path);
+  er_ = er;
+  pi_ = pi;
+  alpha_ = alpha;
+  sr_.assign(num_rates, 0.0);
+  if (lhb::gamma_mean_rates(alpha_, num_rates, sr_.data())) throw std::invalid_argument(lhh_last_error());
+}
+
+// One device call = Partition construction + pruning + emission fill (InitializePhyloEmission,
+// src/PhyloHMM.cpp:366-383) + the forward pass (RunForwardAlgorithm, src/HMM.cpp:254-287).
+void PhyloHMM::ScoreCurrentSample() {
+  EnsureDeviceFamily();
+  const int T = xmsa_.rows(), R = (int)sr_.size();
+  std::vector<int32_t> children((std::size_t)2 * (T - 2)), root_child(1);
+  std::vector<double> blen((std::size_t)2 * (T - 2)), root_blen(1);
+  const char* nw = tree_.c_str();
+  if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), 1, &nw, 1, children.data(), blen.data(), root_child.data(), root_blen.data()))
+    throw std::invalid_argument(lhh_last_error());
+  lh_tree_batch_t tb{1, R, children.data(), blen.data(), root_child.data(), root_blen.data(), er_.data(), pi_.data(), sr_.data()};
+  const lh_family_desc_t& d = flat_->desc;
+  xmsa_emission_.assign(d.n_sites, 0.0);
+  vgerm_.forward.assign(d.n_v, 0.0);
+  dgerm_.forward.assign(d.n_d, 0.0);
+  jgerm_.forward.assign(d.n_j, 0.0);
+  vd_junction_.forward.assign(d.vd_sites, d.vd_states, 0.0);
+  dj_junction_.forward.assign(d.dj_sites, d.dj_states, 0.0);
+  vd_junction_.scaler_counts.assign(d.vd_sites, 0);
+  dj_junction_.scaler_counts.assign(d.dj_sites, 0);
+  int32_t gs[3] = {0, 0, 0};
+  std::vector<double> dgerm_dummy(1), dj_dummy(1);
+  std::vector<int32_t> djs_dummy(1);
+  lh_outputs_t o;
+  std::memset(&o, 0, sizeof(o));
+  o.xmsa_emission = xmsa_emission_.data();
+  o.vgerm_forward = vgerm_.forward.data();
+  o.vd_forward = vd_junction_.forward.data();
+  o.dgerm_forward = d.has_d ? dgerm_.forward.data() : dgerm_dummy.data();
+  o.dj_forward = d.has_d ? dj_junction_.forward.data() : dj_dummy.data();
+  o.jgerm_forward = jgerm_.forward.data();
+  o.germ_scalers = gs;
+  o.vd_scalers = vd_junction_.scaler_counts.data();
+  o.dj_scalers = d.has_d ? dj_junction_.scaler_counts.data() : djs_dummy.data();
+  double ll = 0.0;
+  if (lh_score_batch(dev_family_, &tb, &ll, &o)) throw std::runtime_error(lh_last_error());
+  vgerm_.scaler_count = gs[0];
+  dgerm_.scaler_count = gs[1];
+  jgerm_.scaler_count = gs[2];
+  loglik_cached_ = ll;
+  cache_forward_ = false;
+}
+
+void PhyloHMM::InitializePhyloEmission() {
+  if (tree_.empty()) throw std::runtime_error("InitializePhyloEmission() called before a tree was set");
+  ScoreCurrentSample();
+}
+
+void PhyloHMM::RunForwardAlgorithm() { ScoreCurrentSample(); }
+
+// src/HMM.cpp:345-354
+double PhyloHMM::LogLikelihood() {
+  if (cache_forward_) {
+    RunForwardAlgorithm();
+    cache_forward_ = false;
+  }
+  return loglik_cached_;
+}
+
+std::vector<double> PhyloHMM::ScoreSamples(const std::vector<std::string>& newicks, const std::vector<double>& er,
+                                           const std::vector<double>& pi, const std::vector<double>& alpha, int num_rates) {
+  EnsureDeviceFamily();
+  const int B = (int)newicks.size(), T = xmsa_.rows();
+  if ((int)er.size() != 6 * B || (int)pi.size() != 4 * B || (int)alpha.size() != B)
+    throw std::invalid_argument("ScoreSamples: er / pi / alpha do not match the number of trees");
+  std::vector<const char*> nw(B);
+  for (int b = 0; b < B; ++b) nw[b] = newicks[b].c_str();
+  std::vector<int32_t> children((std::size_t)B * 2 * (T - 2)), root_child(B);
+  std::vector<double> blen((std::size_t)B * 2 * (T - 2)), root_blen(B), rates((std::size_t)B * num_rates), ll(B);
+  if (B == 0) return ll;
+  if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), B, nw.data(), 0, children.data(), blen.data(), root_child.data(), root_blen.data()))
+    throw std::invalid_argument(lhh_last_error());
+  if (lhh_gamma_cats_batch(B, alpha.data(), num_rates, rates.data())) throw std::invalid_argument(lhh_last_error());
+  lh_tree_batch_t tb{B, num_rates, children.data(), blen.data(), root_child.data(), root_blen.data(), er.data(), pi.data(), rates.data()};
+  if (lh_score_batch(dev_family_, &tb, ll.data(), nullptr)) throw std::runtime_error(lh_last_error());
+  return ll;
+}
+
+// src/PhyloHMM.cpp:244-282
+void PhyloHMM::WriteOutputHeaders(std::ostream& out) const {
+  out << "Iteration\tRBLogLikelihood\tPrior\talpha\t";
+  for (std::size_t i = 1; i <= er_.size(); ++i) out << "er[" << i << "]\t";
+  for (std::size_t i = 1; i <= pi_.size(); ++i) out << "pi[" << i << "]\t";
+  out << "tree\t";
+  for (std::size_t i = 1; i <= sr_.size(); ++i) out << "sr[" << i << "]\t";
+  out << "LHLogLikelihood\tLogWeight\tNaiveSequence\tVGene\tV5pDel\tV3pDel\tVFwkInsertion\t";
+  if (locus_ == "igh") out << "VDInsertion\tDGene\tD5pDel\tD3pDel\tDJInsertion\t";
+  else out << "VJInsertion\t";
+  out << "JGene\tJ5pDel\tJ3pDel\tJFwkInsertion\n";
+}
+
+// src/PhyloHMM.cpp:288-327
+void PhyloHMM::WriteOutputLine(std::ostream& out) const {
+  out << iteration_ << "\t" << rb_loglikelihood_ << "\t" << prior_ << "\t" << alpha_ << "\t";
+  for (double v : er_) out << v << "\t";
+  for (double v : pi_) out << v << "\t";
+  out << ExportNewick(tree_) << "\t";
+  for (double v : sr_) out << v << "\t";
+  out << lh_loglikelihood_ << "\t" << logweight_ << "\t" << naive_sequence_ << "\t";
+  out << vgerm_state_str_samp_ << "\t" << vgerm_left_del_samp_ << "\t" << vgerm_right_del_samp_ << "\t"
+      << vgerm_left_insertion_samp_ << "\t";
+  if (locus_ == "igh") {
+    out << vd_junction_insertion_samp_ << "\t" << dgerm_state_str_samp_ << "\t" << dgerm_left_del_samp_ << "\t"
+        << dgerm_right_del_samp_ << "\t" << dj_junction_insertion_samp_ << "\t";
+  } else {
+    out << vd_junction_insertion_samp_ << "\t";
+  }
+  out << jgerm_state_str_samp_ << "\t" << jgerm_left_del_samp_ << "\t" << jgerm_right_del_samp_ << "\t"
+      << jgerm_right_insertion_samp_ << "\n";
+}
+
+// src/PhyloHMM.cpp:393-446, batched: read up to batch_size rows, score them in one device call with
+// the forward tables returned, then finish every row on the host in file order (the RNG advances
+// exactly as in the reference: one SampleNaiveSequence per row).
+void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& output_path, int num_rates, int batch_size) {
+  if (batch_size < 1) throw std::invalid_argument("batch_size must be positive");
+  std::ifstream in(input_path);
+  if (!in) throw std::runtime_error("cannot open " + input_path);
+  std::string line;
+  if (!std::getline(in, line)) throw std::runtime_error(input_path + " is empty");
+  const std::vector<std::string> header = split_tsv(line);
+  static const char* kCols[15] = {"Iteration", "Likelihood", "Prior", "alpha", "er[1]", "er[2]", "er[3]", "er[4]",
+                                  "er[5]", "er[6]", "pi[1]", "pi[2]", "pi[3]", "pi[4]", "tree"};
+  int col[15];
+  for (int k = 0; k < 15; ++k) {
+    col[k] = -1;
+    for (std::size_t j = 0; j < header.size(); ++j)
+      if (header[j] == kCols[k]) col[k] = (int)j;
+    if (col[k] < 0) throw std::runtime_error(std::string("missing column \"") + kCols[k] + "\" in " + input_path);
+  }
+  std::ofstream outfile(output_path);
+  if (!outfile) throw std::runtime_error("cannot open " + output_path);
+  EnsureDeviceFamily();
+  const lh_family_desc_t& d = flat_->desc;
+  const int T = xmsa_.rows();
+  const std::size_t vd_n = (std::size_t)d.vd_sites * d.vd_states, dj_n = (std::size_t)d.dj_sites * d.dj_states;
+  sr_.assign(num_rates, 0.0);
+  bool first = true;
+
+  struct Row {
+    int iteration;
+    double rb, prior, alpha, er[6], pi[4];
+    std::string tree;
+  };
+  std::vector<Row> rows;
+  bool eof = false;
+  while (!eof) {
+    rows.clear();
+    while ((int)rows.size() < batch_size) {
+      if (!std::getline(in, line)) { eof = true; break; }
+      if (line.empty()) continue;
+      const std::vector<std::string> f = split_tsv(line);
+      if ((int)f.size() < (int)header.size()) throw std::runtime_error("too few columns in a row of " + input_path);
+      Row r;
+      r.iteration = (int)to_double(f[col[0]], "Iteration");
+      r.rb = to_double(f[col[1]], "Likelihood");
+      r.prior = to_double(f[col[2]], "Prior");
+      r.alpha = to_double(f[col[3]], "alpha");
+      for (int k = 0; k < 6; ++k) r.er[k] = to_double(f[col[4 + k]], "er");
+      for (int k = 0; k < 4; ++k) r.pi[k] = to_double(f[col[10 + k]], "pi");
+      r.tree = f[col[14]];
+      rows.push_back(r);
+    }
+    const int B = (int)rows.size();
+    if (B == 0) break;
+    std::vector<const char*> nw(B);
+    std::vector<double> er(6 * (std::size_t)B), pi(4 * (std::size_t)B), alpha(B), rates((std::size_t)B * num_rates), ll(B);
+    for (int b = 0; b < B; ++b) {
+      nw[b] = rows[b].tree.c_str();
+      std::memcpy(&er[6 * b], rows[b].er, sizeof(double) * 6);
+      std::memcpy(&pi[4 * b], rows[b].pi, sizeof(double) * 4);
+      alpha[b] = rows[b].alpha;
+    }
+    std::vector<int32_t> children((std::size_t)B * 2 * (T - 2)), root_child(B);
+    std::vector<double> blen((std::size_t)B * 2 * (T - 2)), root_blen(B);
+    if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), B, nw.data(), 0, children.data(), blen.data(), root_child.data(), root_blen.data()))
+      throw std::invalid_argument(lhh_last_error());
+    if (lhh_gamma_cats_batch(B, alpha.data(), num_rates, rates.data())) throw std::invalid_argument(lhh_last_error());
+    lh_tree_batch_t tb{B, num_rates, children.data(), blen.data(), root_child.data(), root_blen.data(), er.data(), pi.data(), rates.data()};
+    std::vector<double> xe((std::size_t)B * d.n_sites), fv((std::size_t)B * d.n_v), fvd(B * vd_n), fd((std::size_t)B * std::max(d.n_d, 1)),
+        fdj(B * std::max<std::size_t>(dj_n, 1)), fj((std::size_t)B * d.n_j);
+    std::vector<int32_t> gs((std::size_t)B * 3), vds((std::size_t)B * d.vd_sites), djs((std::size_t)B * std::max(d.dj_sites, 1));
+    lh_outputs_t o{xe.data(), fv.data(), fvd.data(), fd.data(), fdj.data(), fj.data(), gs.data(), vds.data(), djs.data()};
+    if (lh_score_batch(dev_family_, &tb, ll.data(), &o)) throw std::runtime_error(lh_last_error());
+
+    for (int b = 0; b < B; ++b) {
+      const Row& r = rows[b];
+      iteration_ = r.iteration;
+      rb_loglikelihood_ = r.rb;
+      prior_ = r.prior;
+      alpha_ = r.alpha;
+      er_.assign(r.er, r.er + 6);
+      pi_.assign(r.pi, r.pi + 4);
+      tree_ = r.tree;
+      sr_.assign(rates.begin() + (std::size_t)b * num_rates, rates.begin() + (std::size_t)(b + 1) * num_rates);
+      xmsa_emission_.assign(xe.begin() + (std::size_t)b * d.n_sites, xe.begin() + (std::size_t)(b + 1) * d.n_sites);
+      vgerm_.forward.assign(fv.begin() + (std::size_t)b * d.n_v, fv.begin() + (std::size_t)(b + 1) * d.n_v);
+      jgerm_.forward.assign(fj.begin() + (std::size_t)b * d.n_j, fj.begin() + (std::size_t)(b + 1) * d.n_j);
+      vd_junction_.forward.assign(d.vd_sites, d.vd_states, 0.0);
+      std::memcpy(vd_junction_.forward.data(), &fvd[b * vd_n], vd_n * sizeof(double));
+      vd_junction_.scaler_counts.assign(vds.begin() + (std::size_t)b * d.vd_sites, vds.begin() + (std::size_t)(b + 1) * d.vd_sites);
+      if (d.has_d) {
+        dgerm_.forward.assign(fd.begin() + (std::size_t)b * d.n_d, fd.begin() + (std::size_t)(b + 1) * d.n_d);
+        dj_junction_.forward.assign(d.dj_sites, d.dj_states, 0.0);
+        std::memcpy(dj_junction_.forward.data(), &fdj[b * dj_n], dj_n * sizeof(double));
+        dj_junction_.scaler_counts.assign(djs.begin() + (std::size_t)b * d.dj_sites, djs.begin() + (std::size_t)(b + 1) * d.dj_sites);
+      }
+      vgerm_.scaler_count = gs[3 * b];
+      dgerm_.scaler_count = gs[3 * b + 1];
+      jgerm_.scaler_count = gs[3 * b + 2];
+      loglik_cached_ = ll[b];
+      cache_forward_ = false;
+      lh_loglikelihood_ = ll[b];
+      logweight_ = lh_loglikelihood_ - rb_loglikelihood_;
+      naive_sequence_ = SampleNaiveSequence();
+      if (first) {
+        WriteOutputHeaders(outfile);
+        first = false;
+      }
+      WriteOutputLine(outfile);
+    }
+  }
+  tree_.clear();
+  outfile.close();
+}
+
+}  // namespace linearham

@@ -58,3 +58,123 @@ def tree_batch(newicks, labels, er, pi, alpha, n_rates, n_threads=0):
     tb["pi"] = np.ascontiguousarray(pi, dtype=np.float64).reshape(B, 4)
     tb["rates"] = gamma_cats(np.asarray(alpha, dtype=np.float64).reshape(B), n_rates)
     return tb
+
+
+def export_newick(newick):
+    """pll_utree_export_newick of a Newick string (the `tree` column of the output TSV)."""
+    _abi.bind_phylohmm(lib())
+    buf = C.create_string_buffer(len(newick) * 3 + 64)
+    _ck(lib().lhh_export_newick(newick.encode(), buf, len(buf)))
+    return buf.value.decode()
+
+
+class PhyloHMM:
+    """Handle over the C++ linearham::PhyloHMM of this repo (csrc/host/phylo_hmm.hpp), which mirrors the
+    reference class (src/PhyloHMM.hpp:24-127). Construction is host-only; scoring needs the GPU."""
+
+    def __init__(self, yaml_path, cluster_ind, hmm_param_dir, seed=0, device=0):
+        self._lib = _abi.bind_phylohmm(lib())
+        self._h = self._lib.lhh_phylohmm_new(str(yaml_path).encode(), int(cluster_ind), str(hmm_param_dir).encode(), int(seed))
+        if not self._h:
+            raise HostError(self._lib.lhh_last_error().decode())
+        _ck(self._lib.lhh_phylohmm_set_device(self._h, int(device)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.lhh_phylohmm_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- read-outs ---------------------------------------------------------------------------
+    def f64(self, name):
+        r, c = C.c_int32(), C.c_int32()
+        _ck(self._lib.lhh_phylohmm_get_f64(self._h, name.encode(), None, C.byref(r), C.byref(c)))
+        out = np.zeros((c.value, r.value))
+        _ck(self._lib.lhh_phylohmm_get_f64(self._h, name.encode(), out.ctypes.data_as(_abi._f64p), C.byref(r), C.byref(c)))
+        return out.T.copy()
+
+    def i32(self, name):
+        r, c = C.c_int32(), C.c_int32()
+        _ck(self._lib.lhh_phylohmm_get_i32(self._h, name.encode(), None, C.byref(r), C.byref(c)))
+        out = np.zeros((c.value, r.value), dtype=np.int32)
+        _ck(self._lib.lhh_phylohmm_get_i32(self._h, name.encode(), out.ctypes.data_as(_abi._i32p), C.byref(r), C.byref(c)))
+        return out.T.copy()
+
+    def strs(self, name):
+        n = self._lib.lhh_phylohmm_get_str(self._h, name.encode(), None, 0)
+        if n < 0:
+            raise KeyError(name)
+        buf = C.create_string_buffer(n)
+        self._lib.lhh_phylohmm_get_str(self._h, name.encode(), buf, n)
+        s = buf.value.decode()
+        return s.split("\n") if s else []
+
+    def family(self):
+        """The flat family description as a dict of numpy arrays (what lh_family_create takes)."""
+        d = _abi.FamilyDesc()
+        _ck(self._lib.lhh_phylohmm_family_desc(self._h, C.byref(d)))
+        T, S = d.n_tips, d.n_sites
+        fam = {k: int(getattr(d, k)) for k in _abi._FAMILY_SCALARS}
+
+        def arr(ptr, n, dt):
+            return np.ctypeslib.as_array(ptr, shape=(max(n, 1),))[:n].astype(dt, copy=True)
+
+        fam["tip_codes"] = arr(d.tip_codes, T * S, np.uint8).reshape(T, S)
+        for reg, n in (("vpad", d.n_v), ("vgerm", d.n_v), ("dgerm", d.n_d), ("jgerm", d.n_j), ("jpad", d.n_j)):
+            off = arr(getattr(d, reg + "_off"), n + 1, np.int32)
+            fam[reg + "_off"] = off
+            fam[reg + "_inds"] = arr(getattr(d, reg + "_inds"), int(off[-1]), np.int32)
+        fam["vd_inds"] = arr(d.vd_inds, d.vd_sites * d.vd_states, np.int32)
+        fam["dj_inds"] = arr(d.dj_inds, d.dj_sites * d.dj_states, np.int32)
+        fam["v_gene_prob"] = arr(d.v_gene_prob, d.n_v, np.float64)
+        fam["v_trans_prod"] = arr(d.v_trans_prod, d.n_v, np.float64)
+        fam["vpad_trans"] = arr(d.vpad_trans, d.n_v, np.float64)
+        fam["jpad_trans"] = arr(d.jpad_trans, d.n_j, np.float64)
+        n_mid = d.n_d if d.has_d else d.n_j
+        fam["t_v_vd"] = arr(d.t_v_vd, d.n_v * d.vd_states, np.float64)
+        fam["t_vd"] = arr(d.t_vd, d.vd_states * d.vd_states, np.float64)
+        fam["t_vd_d"] = arr(d.t_vd_d, d.vd_states * n_mid, np.float64)
+        fam["t_d_dj"] = arr(d.t_d_dj, d.n_d * d.dj_states, np.float64) if d.has_d else np.zeros(0)
+        fam["t_dj"] = arr(d.t_dj, d.dj_states * d.dj_states, np.float64) if d.has_d else np.zeros(0)
+        fam["t_dj_j"] = arr(d.t_dj_j, d.dj_states * d.n_j, np.float64) if d.has_d else np.zeros(0)
+        return fam
+
+    # ---- the reference API -------------------------------------------------------------------
+    def InitializePhyloParameters(self, newick_path, er, pi, alpha, num_rates):
+        er = np.ascontiguousarray(er, dtype=np.float64)
+        pi = np.ascontiguousarray(pi, dtype=np.float64)
+        _ck(self._lib.lhh_phylohmm_init_params(self._h, str(newick_path).encode(), er.ctypes.data_as(_abi._f64p),
+                                               pi.ctypes.data_as(_abi._f64p), float(alpha), int(num_rates)))
+
+    def InitializePhyloEmission(self):
+        _ck(self._lib.lhh_phylohmm_init_emission(self._h))
+
+    def LogLikelihood(self):
+        v = C.c_double()
+        _ck(self._lib.lhh_phylohmm_loglikelihood(self._h, C.byref(v)))
+        return v.value
+
+    def SampleNaiveSequence(self):
+        buf = C.create_string_buffer(1 << 16)
+        _ck(self._lib.lhh_phylohmm_sample_naive(self._h, buf, len(buf)))
+        return buf.value.decode()
+
+    def RunPipeline(self, input_path, output_path, num_rates, batch_size=1024):
+        _ck(self._lib.lhh_phylohmm_run_pipeline(self._h, str(input_path).encode(), str(output_path).encode(),
+                                                int(num_rates), int(batch_size)))
+
+    def ScoreSamples(self, newicks, er, pi, alpha, num_rates):
+        n = len(newicks)
+        arr = (C.c_char_p * n)(*[s.encode() for s in newicks])
+        er = np.ascontiguousarray(er, dtype=np.float64).reshape(n, 6)
+        pi = np.ascontiguousarray(pi, dtype=np.float64).reshape(n, 4)
+        alpha = np.ascontiguousarray(alpha, dtype=np.float64).reshape(n)
+        ll = np.zeros(n)
+        _ck(self._lib.lhh_phylohmm_score_samples(self._h, n, arr, er.ctypes.data_as(_abi._f64p), pi.ctypes.data_as(_abi._f64p),
+                                                 alpha.ctypes.data_as(_abi._f64p), int(num_rates), ll.ctypes.data_as(_abi._f64p)))
+        return ll

@@ -13,7 +13,7 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 # sample bundles (family + tree batch + reference outputs); family_*.npz hold a family description only
 GOLDEN_NAMES = sorted(n for n in (os.path.splitext(os.path.basename(p))[0]
                                   for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-                      if not n.startswith("family_"))
+                      if not n.startswith(("family_", "pipeline_")))
 
 
 def pytest_configure(config):

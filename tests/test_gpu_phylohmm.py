@@ -1,0 +1,98 @@
+"""The product's PhyloHMM class (C++, reference API) on the GPU against outputs of the reference's own
+C++ stored in tests/golden/pipeline_tiny.npz (made by tests/golden/make_pipeline_golden.py):
+the --compute-logl / --sample call sequence and the batched RunPipeline.
+Tolerances: log-likelihood 1e-9 relative; printed TSV numbers 2e-6 relative (6 significant digits
+are printed); every sampled string (naive sequence, genes, insertions, deletions) identical."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_DIR
+from linearham_b200 import host, workload
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def tiny():
+    z = np.load(os.path.join(GOLDEN_DIR, "pipeline_tiny.npz"), allow_pickle=False)
+    d = tempfile.mkdtemp(prefix="lh_tiny_")
+    ff = workload.write_family_files(workload.CONFIGS["tiny"], d)
+    assert ff["sha"] == str(z["sha"])
+    return z, ff, d
+
+
+def test_compute_logl_and_sample_like_the_reference_cli(tiny):
+    """src/linearham.cpp:322-389: ctor, InitializePhyloParameters, InitializePhyloEmission, LogLikelihood,
+    N x SampleNaiveSequence; as the reference's Catch test does on its fixture (test/test.cpp:755-758, 968-974)."""
+    z, ff, d = tiny
+    path = os.path.join(d, "first.tree")
+    open(path, "w").write(str(z["first_newick"]))
+    h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+    h.InitializePhyloParameters(path, z["first_er"], z["first_pi"], float(z["first_alpha"]), int(z["num_rates"]))
+    h.InitializePhyloEmission()
+    ll = h.LogLikelihood()
+    assert abs(ll - float(z["first_loglik"])) <= 1e-9 * abs(float(z["first_loglik"]))
+    draws = [h.SampleNaiveSequence() for _ in range(5)]
+    assert draws == [str(s) for s in z["first_draws"]]
+    assert h.LogLikelihood() == ll   # cached; sampling does not disturb it
+    h.close()
+
+
+@pytest.mark.parametrize("batch_size", [1, 5, 1024])
+def test_run_pipeline_matches_reference_output(tiny, batch_size):
+    z, ff, d = tiny
+    tin, tout = os.path.join(d, "in.trees"), os.path.join(d, f"out_{batch_size}.trees")
+    open(tin, "w").write(str(z["tsv_in"]))
+    h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+    h.RunPipeline(tin, tout, int(z["num_rates"]), batch_size=batch_size)
+    h.close()
+    got = [l.split("\t") for l in open(tout).read().splitlines()]
+    exp = [l.split("\t") for l in str(z["tsv_out"]).splitlines()]
+    assert got[0] == exp[0]                      # header
+    assert len(got) == len(exp) == 13
+    for g, e in zip(got[1:], exp[1:]):
+        assert len(g) == len(e)
+        for name, a, b in zip(exp[0], g, e):
+            try:
+                fb = float(b)
+            except ValueError:
+                assert a == b, name              # tree, naive sequence, genes, insertions
+                continue
+            assert abs(float(a) - fb) <= 2e-6 * max(1.0, abs(fb)), (name, a, b)
+
+
+def test_score_samples_equals_pipeline_loglik(tiny):
+    z, ff, d = tiny
+    rows = [l.split("\t") for l in str(z["tsv_in"]).splitlines()]
+    hdr, rows = rows[0], rows[1:]
+    c = {n: i for i, n in enumerate(hdr)}
+    newicks = [r[c["tree"]] for r in rows]
+    er = np.array([[float(r[c[f"er[{i}]"]]) for i in range(1, 7)] for r in rows])
+    pi = np.array([[float(r[c[f"pi[{i}]"]]) for i in range(1, 5)] for r in rows])
+    alpha = np.array([float(r[c["alpha"]]) for r in rows])
+    h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+    ll = h.ScoreSamples(newicks, er, pi, alpha, int(z["num_rates"]))
+    h.close()
+    out = [l.split("\t") for l in str(z["tsv_out"]).splitlines()]
+    k = out[0].index("LHLogLikelihood")
+    exp = np.array([float(r[k]) for r in out[1:]])
+    assert np.allclose(ll, exp, rtol=6e-6, atol=0)   # 6 significant digits are printed
+    assert abs(ll[0] - float(z["first_loglik"])) <= 1e-9 * abs(float(z["first_loglik"]))
+
+
+def test_errors_surface_as_exceptions(tiny):
+    z, ff, d = tiny
+    h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+    with pytest.raises(host.HostError):
+        h.InitializePhyloEmission()                           # no tree yet
+    bad = os.path.join(d, "bad.tree")
+    open(bad, "w").write("((0:0.1,1:0.1):0.1,naive:0.1,nosuchtip:0.1);")
+    h.InitializePhyloParameters(bad, [1] * 6, [0.25] * 4, 1.0, 4)
+    with pytest.raises(host.HostError):                       # label mismatch (pll_partition.cpp:157-189)
+        h.InitializePhyloEmission()
+    with pytest.raises(host.HostError):                       # gamma.c:238
+        h.InitializePhyloParameters(bad, [1] * 6, [0.25] * 4, 0.001, 4)
+    h.close()
