@@ -35,12 +35,6 @@ METRIC = "PhyloHMM tree-likelihood evals/sec"
 UNIT = "trees/s"
 
 
-def load_family_bundle(name):
-    z = np.load(os.path.join(ROOT, "tests", "golden", f"family_{name}.npz"), allow_pickle=False)
-    fam = {k[4:]: (int(z[k]) if z[k].ndim == 0 else z[k]) for k in z.files if k.startswith("fam_")}
-    return fam, [str(s) for s in z["labels"]], str(z["sha"])
-
-
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -187,15 +181,18 @@ def main():
     if args.impl == "reference" and rank != 0:
         return 0
 
-    from linearham_b200 import workload
+    from linearham_b200 import host, sharding, workload
     cfg = dict(workload.CONFIGS[args.config])
     B_total = args.batch or cfg["B"]
-    fam, labels, sha = load_family_bundle(args.config)
-    T, S, R = fam["n_tips"], fam["n_sites"], cfg["R"]
     workdir = tempfile.mkdtemp(prefix="lhbench_")
     ff = workload.write_family_files(cfg, workdir)
-    if ff["sha"] != sha or labels != ff["labels"]:
-        raise RuntimeError("tests/golden/family_%s.npz does not belong to the generated family files" % args.config)
+    # per-family host work of the product: partis YAML + HMM parameter dir -> state space, transition
+    # matrices, xMSA (C++ linearham::PhyloHMM of this repo; bit-exact vs the reference, tests/test_host_model.py)
+    phmm = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+    fam, labels = phmm.family(), phmm.strs("xmsa_labels")
+    if labels != ff["labels"]:
+        raise RuntimeError("xMSA labels do not match the generated family")
+    T, S, R = fam["n_tips"], fam["n_sites"], cfg["R"]
     tb, newicks, alpha = workload.tree_batch(cfg, ff, B_total, n_topo=args.topologies)
     cores = os.cpu_count() or 1
     config = {"workload": f"{args.config}: {cfg['desc']}", "n_tips": T, "xmsa_columns": S, "gamma_categories": R,
@@ -257,9 +254,8 @@ def main():
                         "stage_core_seconds": stages}
 
     # shard the batch: contiguous, equal chunks (trees of one family cost the same)
-    per = (B_total + world - 1) // world
-    lo, hi = rank * per, min(B_total, (rank + 1) * per)
-    shard = {k: np.ascontiguousarray(v[lo:hi]) for k, v in tb.items()}
+    per = sharding.per_rank(B_total, world)
+    shard, lo, hi = sharding.shard_batch(tb, rank, world)
     Bs = hi - lo
 
     f = device.Family(fam, device=dev)
@@ -286,11 +282,7 @@ def main():
         local = torch.as_tensor(_DevArr(ptr, n), device=f"cuda:{dev}")
         if gathered is None:
             gathered = torch.empty(world * per, dtype=torch.float64, device=f"cuda:{dev}")
-        if n < per:
-            pad = torch.zeros(per, dtype=torch.float64, device=f"cuda:{dev}")
-            pad[:n] = local
-            local = pad
-        dist.all_gather_into_tensor(gathered, local)
+        sharding.gather_loglik(dist, local, B_total, out=gathered)
 
     sampler = ClockSampler(dev)
     # -------- value: batch resident in HBM -------------------------------------
