@@ -118,7 +118,8 @@ typedef struct lh_timings {
   float ms_plan;             /* host traversal planning (wall clock)                     */
   float ms_pmatrix;          /* sum over k_pmatrix launches                              */
   float ms_prune;            /* sum over k_prune launches                                */
-  float ms_hmm;              /* k_hmm                                                    */
+  float ms_edge;             /* sum over k_edge launches                                 */
+  float ms_hmm;              /* sum over k_hmm launches                                  */
   float ms_d2h, ms_total;    /* device->host; first H2D event to last D2H event          */
   float ms_kernels;          /* k_eigen start to k_hmm end                               */
   int32_t n_trees;
@@ -130,6 +131,8 @@ typedef struct lh_timings {
   int32_t prune_tile_sites;  /* xMSA columns per CTA                                     */
   int32_t prune_sites_per_thread;
   int32_t prune_grid, prune_ctas_per_sm;
+  int32_t prune_columns;     /* columns k_prune walked: S_x, or the distinct site patterns */
+  int32_t pattern_trees;     /* trees of the batch pruned on site patterns               */
 } lh_timings_t;
 
 const char* lh_last_error(void);
@@ -159,8 +162,13 @@ int lh_measure_fp64_peak(int device, double* tflops);
 int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
 /* keys: "sites_per_thread" (0 = auto, 1..4: xMSA columns per thread; a CTA is one warp and
  * covers 32x that many columns), "smem_slots" (-1 = auto), "timing" (0/1), "host_threads",
- * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair), "stream" (a
- * caller-owned cudaStream_t cast to int64; 0 = private stream)                          */
+ * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never
+ * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "stream" (a
+ * caller-owned cudaStream_t cast to int64; 0 = private stream), "site_patterns" (1 =
+ * default: trees that have the naive tip on the root edge or under the virtual root are
+ * pruned on the distinct site patterns of xMSA rows 1.., and k_edge applies the naive row's
+ * factor per xMSA column; other trees, and every tree when 0, are pruned on all S_x
+ * columns. The results are the same doubles either way)                                */
 
 /* CUDA-event stopwatch on the family's stream (8 slots), so callers can time a region of
  * lh_batch_run calls on the stream the kernels are launched on.                          */

@@ -58,12 +58,13 @@ class Outputs(C.Structure):
 class Timings(C.Structure):
     _fields_ = [
         ("ms_h2d", C.c_float), ("ms_plan", C.c_float), ("ms_pmatrix", C.c_float),
-        ("ms_prune", C.c_float), ("ms_hmm", C.c_float), ("ms_d2h", C.c_float),
+        ("ms_prune", C.c_float), ("ms_edge", C.c_float), ("ms_hmm", C.c_float), ("ms_d2h", C.c_float),
         ("ms_total", C.c_float), ("ms_kernels", C.c_float),
         ("n_trees", C.c_int32), ("kernel_launches", C.c_int32), ("prune_launches", C.c_int32),
         ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
         ("prune_slots", C.c_int32), ("prune_smem_slots", C.c_int32), ("prune_tile_sites", C.c_int32),
         ("prune_sites_per_thread", C.c_int32), ("prune_grid", C.c_int32), ("prune_ctas_per_sm", C.c_int32),
+        ("prune_columns", C.c_int32), ("pattern_trees", C.c_int32),
     ]
 
 

@@ -12,6 +12,7 @@
 #include <cstring>
 #include <string>
 #include <thread>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/linearham_b200.h"
@@ -126,19 +127,50 @@ struct lh_family {
   // options
   int opt_sites_per_thread = 0, opt_smem_slots = -1, opt_timing = 1, opt_threads = 0;
   size_t opt_chunk_bytes = 48u << 20;
+  int opt_chunk_trees = 0;
   // batch state
   int B = 0, R = 0, slots = 0;
   DevBuf d_plan, d_pblen, d_er, d_pi, d_rates, d_eig, d_prec, d_xe, d_loglik, d_scratch, d_scratch_cnt;
   DevBuf d_vgerm, d_vd, d_dgerm, d_dj, d_jgerm, d_gs, d_vds, d_djs;
-  PinBuf h_plan, h_pblen, h_misc, h_out;
+  PinBuf h_misc, h_out;
+  // staging ring: planned steps + branch lengths of one segment of trees per slot; the copy
+  // stream drains a slot while the host plans into the next one
+  static constexpr int kRing = 3;
+  PinBuf h_ring[kRing];
+  cudaEvent_t ring_ev[kRing] = {};
+  bool ring_busy[kRing] = {};
+  cudaEvent_t misc_ev = nullptr, list_ev = nullptr;  // h_misc / h_list have been copied
+  bool misc_busy = false, list_busy = false;
+  cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev[8] = {};
   cudaEvent_t user_ev[8] = {};
-  std::vector<cudaEvent_t> chunk_ev;  // 3 per chunk: pmatrix start, prune start, prune end
+  std::vector<cudaEvent_t> chunk_ev;  // 5 per chunk: pmatrix, prune, edge, hmm start; hmm end
+  std::vector<cudaEvent_t> staged_ev;  // per chunk: its last segment has landed in HBM
   int n_chunks = 0;
   bool own_stream = true;
-  std::vector<uint8_t> h_tip_codes;  // host copy, re-tiled per sites_per_thread
-  DevBuf d_codes_t;
-  int codes_ns = 0;
+  // pruning column sets: [0] all S xMSA columns, [1] the distinct patterns of rows 1..T-1
+  struct ColumnSet {
+    int n_cols = 0;
+    std::vector<uint8_t> codes;  // [T][n_cols] host copy, re-tiled per sites_per_thread
+    DevBuf d_codes_t;
+    int codes_ns = 0;
+  } cols[2];
+  const int32_t* d_col_of_site = nullptr;  // [S] pattern index of each xMSA column
+  DevBuf d_ebuf, d_ecnt, d_enaive;
+  int opt_site_patterns = 1;
+  // launch configuration of the current batch (configure_batch)
+  lhb::BatchDev bd{};
+  lhb::PruneCfg pc[2] = {};  // per column set
+  lhb::EdgeCfg ec{};
+  lhb::HmmOut ho{};
+  int chunk = 0, seg = 0, occ[2] = {0, 0};
+  // trees that can run on site patterns (naive tip on the root edge or under the virtual root)
+  std::vector<uint8_t> on_patterns;
+  int n_pattern_trees = 0;
+  std::vector<int> starts;         // chunk boundaries of the current batch
+  std::vector<int> chunk_n_pat;    // per chunk: trees on patterns (listed first in d_list)
+  DevBuf d_list;                   // [B] tree indices, per chunk: pattern trees, then the others
+  PinBuf h_list;
   lh_timings_t tm{};
   bool want_tables = false;
 };
@@ -158,20 +190,28 @@ void lh_family_destroy(lh_family_t* f) {
   if (!f) return;
   cudaSetDevice(f->device);
   if (f->stream) cudaStreamSynchronize(f->stream);
+  if (f->copy_stream) cudaStreamSynchronize(f->copy_stream);
   for (void* p : f->owned) cudaFree(p);
   DevBuf* bufs[] = {&f->d_plan, &f->d_pblen, &f->d_er, &f->d_pi, &f->d_rates, &f->d_eig, &f->d_prec,
                     &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
-                    &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->d_codes_t};
+                    &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
+                    &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list};
   for (DevBuf* b : bufs) b->release();
-  f->h_plan.release();
-  f->h_pblen.release();
+  for (auto& r : f->h_ring) r.release();
   f->h_misc.release();
+  f->h_list.release();
   f->h_out.release();
   for (auto& e : f->ev)
     if (e) cudaEventDestroy(e);
   for (auto& e : f->user_ev)
     if (e) cudaEventDestroy(e);
+  for (auto& e : f->ring_ev)
+    if (e) cudaEventDestroy(e);
+  if (f->misc_ev) cudaEventDestroy(f->misc_ev);
+  if (f->list_ev) cudaEventDestroy(f->list_ev);
   for (auto& e : f->chunk_ev) cudaEventDestroy(e);
+  for (auto& e : f->staged_ev) cudaEventDestroy(e);
+  if (f->copy_stream) cudaStreamDestroy(f->copy_stream);
   if (f->stream && f->own_stream) cudaStreamDestroy(f->stream);
   delete f;
 }
@@ -197,6 +237,11 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
   auto bail = [&](int) { lh_family_destroy(f); return 1; };
   if (cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking) != cudaSuccess)
     return bail(fail("cudaStreamCreate failed"));
+  if (cudaStreamCreateWithFlags(&f->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail("cudaStreamCreate failed"));
+  for (auto& ev : f->ring_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&f->misc_ev, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&f->list_ev, cudaEventDisableTiming);
   for (auto& ev : f->ev) cudaEventCreate(&ev);
   for (auto& ev : f->user_ev) cudaEventCreate(&ev);
 
@@ -219,7 +264,30 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
   auto& own = f->owned;
   int rc = 0;
   rc |= upload(d->tip_codes, (size_t)T * S, &fd.tip_codes, own);
-  f->h_tip_codes.assign(d->tip_codes, d->tip_codes + (size_t)T * S);
+  {
+    // site patterns: xMSA columns that agree on every row but the naive row (row 0) share all
+    // CLVs away from the naive tip, so pruning visits each pattern once (first occurrence order)
+    f->cols[0].n_cols = S;
+    f->cols[0].codes.assign(d->tip_codes, d->tip_codes + (size_t)T * S);
+    std::vector<int32_t> col_of_site(S), rep;
+    std::unordered_map<std::string, int32_t> seen;
+    std::string key((size_t)T - 1, '\0');
+    for (int c = 0; c < S; ++c) {
+      for (int r = 1; r < T; ++r) key[r - 1] = (char)d->tip_codes[(size_t)r * S + c];
+      auto it = seen.find(key);
+      if (it == seen.end()) {
+        it = seen.emplace(key, (int32_t)rep.size()).first;
+        rep.push_back(c);
+      }
+      col_of_site[c] = it->second;
+    }
+    const int U = (int)rep.size();
+    f->cols[1].n_cols = U;
+    f->cols[1].codes.assign((size_t)T * U, 4);  // row 0 (the deferred naive tip) reads as N
+    for (int r = 1; r < T; ++r)
+      for (int u = 0; u < U; ++u) f->cols[1].codes[(size_t)r * U + u] = d->tip_codes[(size_t)r * S + rep[u]];
+    rc |= upload(col_of_site.data(), (size_t)S, &f->d_col_of_site, own);
+  }
   auto region = [&](int n, const int32_t* off, const int32_t* inds, const int32_t** doff,
                     const int32_t** dinds, const char* name) {
     if (n == 0) return upload(off, 0, doff, own) | upload(inds, 0, dinds, own);
@@ -272,10 +340,15 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_sites_per_thread = (int)value;
   } else if (k == "smem_slots") {
     f->opt_smem_slots = (int)value;
+  } else if (k == "site_patterns") {
+    f->opt_site_patterns = value != 0;
   } else if (k == "timing") {
     f->opt_timing = value != 0;
   } else if (k == "host_threads") {
     f->opt_threads = (int)value;
+  } else if (k == "chunk_trees") {
+    if (value < 0) return fail("chunk_trees must be >= 0 (0 = auto)");
+    f->opt_chunk_trees = (int)value;
   } else if (k == "chunk_bytes") {
     f->opt_chunk_bytes = (size_t)value;
   } else if (k == "stream") {
@@ -312,20 +385,25 @@ int pick_sites_per_thread(int S, int threads) {
   return (pad3 * 4 < pad4 * 3) ? 3 : 4;
 }
 
-// Plans all trees into the pinned staging buffers (multi-threaded); returns max slots.
-int plan_batch(lh_family* f, const lh_tree_batch_t* tb, lhb::Step* steps, double* pblen, int* max_slots) {
-  const int T = f->fd.T, B = tb->n_trees, n_ops = T - 2, NB = 2 * T - 3;
+// Plans trees [t0, t0+n) into `steps` / `pblen` (segment-local, multi-threaded); raises
+// *max_slots to the deepest register stack met.
+int plan_range(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, lhb::Step* steps, double* pblen,
+               int* max_slots) {
+  const int T = f->fd.T, n_ops = T - 2, NB = 2 * T - 3;
   int nthreads = f->opt_threads > 0 ? f->opt_threads : (int)std::thread::hardware_concurrency();
-  nthreads = std::max(1, std::min(nthreads, std::min(32, (B + 255) / 256)));
+  nthreads = std::max(1, std::min(nthreads, std::min(32, (n + 15) / 16)));
   std::atomic<int> bad(-1);
   std::vector<int> tmax(nthreads, 0);
   auto work = [&](int tid) {
     lhb::PlanScratch sc;
     int mx = 0;
-    for (int t = tid; t < B; t += nthreads) {
+    // contiguous blocks per thread: each thread streams its own part of the pinned slot
+    const int lo = (int)((int64_t)n * tid / nthreads), hi = (int)((int64_t)n * (tid + 1) / nthreads);
+    for (int i = lo; i < hi; ++i) {
+      const int t = t0 + i;
       int s = lhb::plan_tree(T, tb->children + (size_t)t * n_ops * 2, tb->blen + (size_t)t * n_ops * 2,
-                             tb->root_child[t], tb->root_blen[t], steps + (size_t)t * (T - 1),
-                             pblen + (size_t)t * NB, sc);
+                             tb->root_child[t], tb->root_blen[t], steps + (size_t)i * (T - 1),
+                             pblen + (size_t)i * NB, sc);
       if (s < 0) {
         bad.store(t);
         return;
@@ -342,25 +420,14 @@ int plan_batch(lh_family* f, const lh_tree_batch_t* tb, lhb::Step* steps, double
     for (auto& t : th) t.join();
   }
   if (bad.load() >= 0) return fail("tree %d is not a valid post-order operation list", bad.load());
-  *max_slots = *std::max_element(tmax.begin(), tmax.end());
+  *max_slots = std::max(*max_slots, *std::max_element(tmax.begin(), tmax.end()));
   return 0;
 }
 
-}  // namespace
-
-extern "C" {
-
-int lh_batch_upload(lh_family_t* f, const lh_tree_batch_t* tb) {
-  if (!f || !tb) return fail("null argument");
-  const int B = tb->n_trees, R = tb->n_rates, T = f->fd.T, S = f->fd.S, NB = 2 * T - 3;
+int check_batch(lh_family* f, const lh_tree_batch_t* tb) {
+  const int B = tb->n_trees, R = tb->n_rates, NB = 2 * f->fd.T - 3;
   if (B < 0) return fail("negative batch size");
   if (R < 1 || R > LH_MAX_RATES) return fail("n_rates %d outside 1..%d", R, LH_MAX_RATES);
-  LH_CUDA(cudaSetDevice(f->device));
-  f->B = B;
-  f->R = R;
-  f->tm = lh_timings_t{};
-  f->tm.n_trees = B;
-  if (B == 0) return 0;
   for (int t = 0; t < B; ++t) {
     for (int i = 0; i < 4; ++i)
       if (!(tb->pi[4 * t + i] > 0.0)) return fail("tree %d: pi[%d] must be positive", t, i);
@@ -368,38 +435,43 @@ int lh_batch_upload(lh_family_t* f, const lh_tree_batch_t* tb) {
       if (!(tb->blen[(size_t)t * (NB - 1) + i] >= 0.0)) return fail("tree %d: negative branch length", t);
     if (!(tb->root_blen[t] >= 0.0)) return fail("tree %d: negative branch length", t);
   }
-  const size_t plan_bytes = (size_t)B * (T - 1) * sizeof(lhb::Step);
-  const size_t pblen_bytes = (size_t)B * NB * sizeof(double);
-  const size_t misc_doubles = (size_t)B * (6 + 4 + R);
-  if (f->h_plan.reserve(plan_bytes) || f->h_pblen.reserve(pblen_bytes) ||
-      f->h_misc.reserve(misc_doubles * sizeof(double)))
-    return 1;
-  const auto plan_t0 = std::chrono::steady_clock::now();
-  if (plan_batch(f, tb, f->h_plan.as<lhb::Step>(), f->h_pblen.as<double>(), &f->slots)) return 1;
-  f->tm.ms_plan = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - plan_t0).count();
-  double* misc = f->h_misc.as<double>();
-  std::memcpy(misc, tb->er, sizeof(double) * 6 * B);
-  std::memcpy(misc + (size_t)6 * B, tb->pi, sizeof(double) * 4 * B);
-  std::memcpy(misc + (size_t)10 * B, tb->rates, sizeof(double) * R * B);
-  if (f->d_plan.reserve(plan_bytes) || f->d_pblen.reserve(pblen_bytes) ||
-      f->d_er.reserve(misc_doubles * sizeof(double)) || f->d_eig.reserve((size_t)B * lhb::kEigStride * 8) ||
-      f->d_xe.reserve((size_t)B * S * 8) || f->d_loglik.reserve((size_t)B * 8))
-    return 1;
-  if (f->opt_timing) cudaEventRecord(f->ev[0], f->stream);
-  LH_CUDA(cudaMemcpyAsync(f->d_plan.p, f->h_plan.p, plan_bytes, cudaMemcpyHostToDevice, f->stream));
-  LH_CUDA(cudaMemcpyAsync(f->d_pblen.p, f->h_pblen.p, pblen_bytes, cudaMemcpyHostToDevice, f->stream));
-  LH_CUDA(cudaMemcpyAsync(f->d_er.p, f->h_misc.p, misc_doubles * 8, cudaMemcpyHostToDevice, f->stream));
-  if (f->opt_timing) cudaEventRecord(f->ev[1], f->stream);
-  f->tm.h2d_bytes = (int64_t)(plan_bytes + pblen_bytes + misc_doubles * 8);
+  // A tree can run on site patterns when the naive tip (xMSA row 0) is on the root edge or under
+  // the virtual root (the last operation): then no other node's CLV depends on the naive row.
+  const int n_ops = f->fd.T - 2;
+  f->on_patterns.assign((size_t)B, 0);
+  f->n_pattern_trees = 0;
+  if (f->opt_site_patterns && f->cols[1].n_cols < f->cols[0].n_cols)
+    for (int t = 0; t < B; ++t) {
+      const int32_t* last = tb->children + ((size_t)t * n_ops + (n_ops - 1)) * 2;
+      const bool ok = tb->root_child[t] == 0 || last[0] == 0 || last[1] == 0;
+      f->on_patterns[t] = ok;
+      f->n_pattern_trees += ok;
+    }
   return 0;
 }
 
-int lh_batch_run(lh_family_t* f) {
-  if (!f) return fail("null family");
-  if (f->B == 0) return 0;
-  LH_CUDA(cudaSetDevice(f->device));
-  const int B = f->B, R = f->R, T = f->fd.T, S = f->fd.S, NB = 2 * T - 3;
-  lhb::BatchDev bd{};
+// Device buffers and launch configuration for a batch of B trees with R rate categories.
+// Everything here depends on (family, B, R) only, so it can run before any tree is planned: the
+// number of CLV slots is bounded by the Strahler bound floor(log2 T) + 1 of a T-tip tree rather
+// than by the planned maximum.
+int configure_batch(lh_family* f, int B, int R) {
+  const int T = f->fd.T, S = f->fd.S, NB = 2 * T - 3;
+  f->B = B;
+  f->R = R;
+  f->slots = 0;
+  f->tm = lh_timings_t{};
+  f->tm.n_trees = B;
+  if (B == 0) return 0;
+  const size_t plan_bytes = (size_t)B * (T - 1) * sizeof(lhb::Step);
+  const size_t pblen_bytes = (size_t)B * NB * sizeof(double);
+  const size_t misc_doubles = (size_t)B * (6 + 4 + R);
+  if (f->d_plan.reserve(plan_bytes) || f->d_pblen.reserve(pblen_bytes) ||
+      f->d_er.reserve(misc_doubles * sizeof(double)) || f->d_eig.reserve((size_t)B * lhb::kEigStride * 8) ||
+      f->d_xe.reserve((size_t)B * S * 8) || f->d_loglik.reserve((size_t)B * 8) ||
+      f->h_misc.reserve(misc_doubles * sizeof(double)))
+    return 1;
+  lhb::BatchDev& bd = f->bd;
+  bd = lhb::BatchDev{};
   bd.B = B;
   bd.R = R;
   bd.plan = f->d_plan.as<int4>();
@@ -411,70 +483,123 @@ int lh_batch_run(lh_family_t* f) {
   bd.xe = f->d_xe.as<double>();
   bd.loglik = f->d_loglik.as<double>();
 
-  // pruning configuration
-  lhb::PruneCfg pc{};
-  pc.sites_per_thread = f->opt_sites_per_thread ? f->opt_sites_per_thread : pick_sites_per_thread(S, 32);
-  const int tile_sites = 32 * pc.sites_per_thread;
-  pc.n_tiles = (S + tile_sites - 1) / tile_sites;
-  pc.total_slots = f->slots;
-  const size_t slot_bytes = (size_t)tile_sites * (4 * sizeof(double) + sizeof(int));
-  int occ0 = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, 0);
-  if (occ0 < 1) return fail("pruning kernel cannot be resident (sites/thread=%d)", pc.sites_per_thread);
-  int smem_slots = f->opt_smem_slots;
-  if (smem_slots < 0) {
-    size_t per_cta = (size_t)(227 * 1024) / occ0 - 1024 - lhb::prune_smem_bytes(pc.sites_per_thread, 0);
-    smem_slots = (int)(per_cta / slot_bytes);
-  }
-  smem_slots = std::max(0, std::min(smem_slots, pc.total_slots));
-  while (smem_slots > 0 && lhb::prune_smem_bytes(pc.sites_per_thread, smem_slots) > (size_t)227 * 1024) --smem_slots;
-  pc.smem_slots = smem_slots;
-  int occ = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.smem_slots);
-  if (occ < 1) return fail("pruning kernel cannot be resident with %d shared-memory slots", pc.smem_slots);
-  pc.log_threshold = std::log(1.0 / std::pow(2.0, 256));
-  if (f->codes_ns != pc.sites_per_thread) {
-    // re-tile the tip codes for this NS (once per family and NS)
-    const int NS = pc.sites_per_thread;
-    std::vector<uint32_t> ct((size_t)T * pc.n_tiles * 32, 0u);
-    for (int r = 0; r < T; ++r)
-      for (int tile = 0; tile < pc.n_tiles; ++tile)
-        for (int lane = 0; lane < 32; ++lane) {
-          uint32_t word = 0;
-          for (int u = 0; u < NS; ++u) {
-            const int site = tile * 32 * NS + u * 32 + lane;
-            if (site < S) word |= (uint32_t)(f->h_tip_codes[(size_t)r * S + site] * 32u) << (8 * u);
-          }
-          ct[((size_t)r * pc.n_tiles + tile) * 32 + lane] = word;
-        }
-    if (f->d_codes_t.reserve(ct.size() * 4)) return 1;
-    LH_CUDA(cudaMemcpyAsync(f->d_codes_t.p, ct.data(), ct.size() * 4, cudaMemcpyHostToDevice, f->stream));
-    LH_CUDA(cudaStreamSynchronize(f->stream));
-    f->codes_ns = NS;
-  }
-  pc.codes_t = f->d_codes_t.as<uint32_t>();
-
-  // chunk the batch so one chunk's branch records stay L2-resident
+  // pruning launch configuration per column set in use: [0] all columns, [1] site patterns
   const size_t rec_bytes_tree = (size_t)NB * 20 * R * sizeof(double);
+  int strahler = 1;
+  while ((2 << (strahler - 1)) <= T) ++strahler;  // floor(log2 T) + 1
+  const bool use[2] = {f->n_pattern_trees < B, f->n_pattern_trees > 0};
+  size_t scratch_bytes = 0, scratch_cnt_bytes = 0;
+  for (int g = 0; g < 2; ++g) {
+    lhb::PruneCfg& pc = f->pc[g];
+    pc = lhb::PruneCfg{};
+    if (!use[g]) continue;
+    lh_family::ColumnSet& cset = f->cols[g];
+    const int NC = cset.n_cols;
+    pc.n_cols = NC;
+    pc.defer_naive = g;
+    pc.sites_per_thread = f->opt_sites_per_thread ? f->opt_sites_per_thread : pick_sites_per_thread(NC, 32);
+    const int tile_sites = 32 * pc.sites_per_thread;
+    pc.n_tiles = (NC + tile_sites - 1) / tile_sites;
+    pc.cols_pad = pc.n_tiles * tile_sites;
+    pc.total_slots = strahler + 1;  // + the virtual-root edge
+    const size_t slot_bytes = (size_t)tile_sites * (4 * sizeof(double) + sizeof(int));
+    int occ0 = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, 0);
+    if (occ0 < 1) return fail("pruning kernel cannot be resident (sites/thread=%d)", pc.sites_per_thread);
+    int smem_slots = f->opt_smem_slots;
+    if (smem_slots < 0) {
+      size_t per_cta = (size_t)(227 * 1024) / occ0 - 1024 - lhb::prune_smem_bytes(pc.sites_per_thread, 0);
+      smem_slots = (int)(per_cta / slot_bytes);
+    }
+    smem_slots = std::max(0, std::min(smem_slots, pc.total_slots));
+    while (smem_slots > 0 && lhb::prune_smem_bytes(pc.sites_per_thread, smem_slots) > (size_t)227 * 1024) --smem_slots;
+    pc.smem_slots = smem_slots;
+    f->occ[g] = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.smem_slots);
+    if (f->occ[g] < 1) return fail("pruning kernel cannot be resident with %d shared-memory slots", pc.smem_slots);
+    pc.log_threshold = std::log(1.0 / std::pow(2.0, 256));
+    if (cset.codes_ns != pc.sites_per_thread) {
+      // re-tile the tip codes for this NS (once per family, column set and NS)
+      const int NS = pc.sites_per_thread;
+      std::vector<uint32_t> ct((size_t)T * pc.n_tiles * 32, 0u);
+      for (int r = 0; r < T; ++r)
+        for (int tile = 0; tile < pc.n_tiles; ++tile)
+          for (int lane = 0; lane < 32; ++lane) {
+            uint32_t word = 0;
+            for (int u = 0; u < NS; ++u) {
+              const int site = tile * 32 * NS + u * 32 + lane;
+              if (site < NC) word |= (uint32_t)(cset.codes[(size_t)r * NC + site] * 32u) << (8 * u);
+            }
+            ct[((size_t)r * pc.n_tiles + tile) * 32 + lane] = word;
+          }
+      LH_CUDA(cudaStreamSynchronize(f->stream));
+      if (cset.d_codes_t.reserve(ct.size() * 4)) return 1;
+      LH_CUDA(cudaMemcpy(cset.d_codes_t.p, ct.data(), ct.size() * 4, cudaMemcpyHostToDevice));
+      cset.codes_ns = NS;
+    }
+    pc.codes_t = cset.d_codes_t.as<uint32_t>();
+  }
+
+  // chunk the batch: one launch of each kernel per chunk (k_prune: one per column set in use).
+  // The chunk is sized on the column set most trees use.
+  const int gmain = f->n_pattern_trees * 2 >= B ? 1 : 0;
   int chunk = (int)std::max<size_t>(1, f->opt_chunk_bytes / rec_bytes_tree);
-  const int resident = occ * f->num_sms;
   // at least 16 waves of work items per launch when the batch allows it, so the partial last
   // wave costs a few percent. The records then exceed L2 for large trees, which is harmless: they
   // are written once and read once per site tile by CTAs that run at the same time (the tiles
   // of a tree are adjacent work items), ~2.6 MB of DRAM traffic per 1001-tip tree.
-  chunk = std::max(chunk, (16 * resident + pc.n_tiles - 1) / pc.n_tiles);
+  chunk = std::max(chunk, (16 * f->occ[gmain] * f->num_sms + f->pc[gmain].n_tiles - 1) / f->pc[gmain].n_tiles);
+  if (f->opt_chunk_trees > 0) chunk = f->opt_chunk_trees;
   chunk = std::min(chunk, B);
+  f->chunk = chunk;
   if (f->d_prec.reserve((size_t)chunk * rec_bytes_tree)) return 1;
   bd.prec = f->d_prec.as<double>();
-  pc.grid = std::min(resident, chunk * pc.n_tiles);
-  const int gslots = pc.total_slots - pc.smem_slots;
-  if (gslots > 0) {
-    if (f->d_scratch.reserve((size_t)pc.grid * gslots * 4 * tile_sites * sizeof(double)) ||
-        f->d_scratch_cnt.reserve((size_t)pc.grid * gslots * tile_sites * sizeof(int)))
-      return 1;
+  const int pad_max = std::max(f->pc[0].cols_pad, f->pc[1].cols_pad);
+  const int64_t e_stride = (int64_t)R * 8 * pad_max, c_stride = (int64_t)R * pad_max;
+  if (f->d_ebuf.reserve((size_t)chunk * e_stride * sizeof(double)) ||
+      f->d_ecnt.reserve((size_t)chunk * c_stride * sizeof(int32_t)) ||
+      f->d_enaive.reserve((size_t)chunk * sizeof(int32_t)) || f->d_list.reserve((size_t)B * sizeof(int32_t)))
+    return 1;
+  for (int g = 0; g < 2; ++g) {
+    lhb::PruneCfg& pc = f->pc[g];
+    if (!use[g]) continue;
+    const int tile_sites = 32 * pc.sites_per_thread;
+    pc.grid = std::min(f->occ[g] * f->num_sms, chunk * pc.n_tiles);
+    const int gslots = pc.total_slots - pc.smem_slots;
+    if (gslots > 0) {
+      scratch_bytes = std::max(scratch_bytes, (size_t)pc.grid * gslots * 4 * tile_sites * sizeof(double));
+      scratch_cnt_bytes = std::max(scratch_cnt_bytes, (size_t)pc.grid * gslots * tile_sites * sizeof(int));
+    }
+    pc.ebuf = f->d_ebuf.as<double>();
+    pc.ecnt = f->d_ecnt.as<int32_t>();
+    pc.enaive = f->d_enaive.as<int32_t>();
+    pc.e_stride = e_stride;
+    pc.c_stride = c_stride;
   }
-  pc.scratch = f->d_scratch.as<double>();
-  pc.scratch_cnt = f->d_scratch_cnt.as<int32_t>();
+  if (f->d_scratch.reserve(scratch_bytes) || f->d_scratch_cnt.reserve(scratch_cnt_bytes)) return 1;
+  for (auto& pc : f->pc) {
+    pc.scratch = f->d_scratch.as<double>();
+    pc.scratch_cnt = f->d_scratch_cnt.as<int32_t>();
+  }
+  lhb::EdgeCfg& ec = f->ec;
+  ec = lhb::EdgeCfg{};
+  ec.ebuf = f->d_ebuf.as<double>();
+  ec.ecnt = f->d_ecnt.as<int32_t>();
+  ec.enaive = f->d_enaive.as<int32_t>();
+  ec.e_stride = e_stride;
+  ec.c_stride = c_stride;
+  ec.cols_pad_all = f->pc[0].cols_pad;
+  ec.cols_pad_pat = f->pc[1].cols_pad;
+  ec.col_of_site = f->d_col_of_site;
+  ec.log_threshold = std::log(1.0 / std::pow(2.0, 256));
 
-  lhb::HmmOut ho{};
+  // staging segments: ~32 MB of plan + branch lengths per ring slot, never more than a chunk
+  const size_t stage_bytes_tree = (size_t)(T - 1) * sizeof(lhb::Step) + (size_t)NB * sizeof(double);
+  int seg = (int)std::max<size_t>(64, ((size_t)32 << 20) / stage_bytes_tree);
+  f->seg = std::min(seg, chunk);
+  for (auto& r : f->h_ring)
+    if (r.reserve((size_t)f->seg * stage_bytes_tree)) return 1;
+
+  lhb::HmmOut& ho = f->ho;
+  ho = lhb::HmmOut{};
   ho.log_factor = std::log(std::pow(2.0, 256));
   if (f->want_tables) {
     const lhb::FamilyDev& fd = f->fd;
@@ -493,61 +618,193 @@ int lh_batch_run(lh_family_t* f) {
     ho.vd_scalers = f->d_vds.as<int32_t>();
     ho.dj_scalers = fd.has_d ? f->d_djs.as<int32_t>() : nullptr;
   }
-
-  cudaStream_t s = f->stream;
-  int launches = 0;
-  const int n_chunks = (B + chunk - 1) / chunk;
-  f->n_chunks = n_chunks;
-  if (f->opt_timing)
-    while ((int)f->chunk_ev.size() < 3 * n_chunks) {
-      cudaEvent_t e;
-      LH_CUDA(cudaEventCreate(&e));
-      f->chunk_ev.push_back(e);
-    }
-  if (f->opt_timing) cudaEventRecord(f->ev[2], s);
-  lhb::launch_eigen(bd, s);
-  ++launches;
-  for (int t0 = 0, ci = 0; t0 < B; t0 += chunk, ++ci) {
-    const int n = std::min(chunk, B - t0);
-    if (f->opt_timing) cudaEventRecord(f->chunk_ev[3 * ci], s);
-    lhb::launch_pmatrix(f->fd, bd, t0, n, s);
-    if (f->opt_timing) cudaEventRecord(f->chunk_ev[3 * ci + 1], s);
-    lhb::PruneCfg c = pc;
-    c.grid = std::min(pc.grid, n * pc.n_tiles);
-    lhb::launch_prune(f->fd, bd, c, t0, n, s);
-    if (f->opt_timing) cudaEventRecord(f->chunk_ev[3 * ci + 2], s);
-    launches += 2;
-  }
-  if (f->opt_timing) cudaEventRecord(f->ev[3], s);
-  lhb::launch_hmm(f->fd, bd, ho, s);
-  ++launches;
-  if (f->opt_timing) cudaEventRecord(f->ev[4], s);
-  LH_CUDA(cudaGetLastError());
-  f->tm.kernel_launches = launches;
-  f->tm.prune_launches = n_chunks;
-  f->tm.prune_slots = pc.total_slots;
-  f->tm.prune_tile_sites = tile_sites;
-  f->tm.prune_sites_per_thread = pc.sites_per_thread;
-  f->tm.prune_smem_slots = pc.smem_slots;
-  f->tm.prune_grid = pc.grid;
-  f->tm.prune_ctas_per_sm = occ;
+  const lhb::PruneCfg& pm = f->pc[gmain];
+  f->tm.prune_slots = pm.total_slots;
+  f->tm.prune_tile_sites = 32 * pm.sites_per_thread;
+  f->tm.prune_sites_per_thread = pm.sites_per_thread;
+  f->tm.prune_smem_slots = pm.smem_slots;
+  f->tm.prune_grid = pm.grid;
+  f->tm.prune_ctas_per_sm = f->occ[gmain];
+  f->tm.prune_columns = pm.n_cols;
+  f->tm.pattern_trees = f->n_pattern_trees;
   return 0;
 }
 
-// Per-kernel device times of the last lh_batch_run (syncs the stream).
-static int collect_run_timings(lh_family* f) {
-  if (!f->opt_timing || f->B == 0) return 0;
-  LH_CUDA(cudaEventSynchronize(f->ev[4]));
-  float pm = 0, pr = 0, x = 0;
+// Plans trees [t0, t0+n) into ring slot `slot` and queues their copy to HBM on `s`.
+int stage_segment(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, int slot, cudaStream_t s) {
+  const int T = f->fd.T, NB = 2 * T - 3;
+  if (f->ring_busy[slot]) {
+    LH_CUDA(cudaEventSynchronize(f->ring_ev[slot]));
+    f->ring_busy[slot] = false;
+  }
+  lhb::Step* steps = f->h_ring[slot].as<lhb::Step>();
+  double* pblen = reinterpret_cast<double*>(steps + (size_t)n * (T - 1));
+  const auto t_a = std::chrono::steady_clock::now();
+  if (plan_range(f, tb, t0, n, steps, pblen, &f->slots)) return 1;
+  f->tm.ms_plan += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_a).count();
+  const int slot_bound = std::max(f->pc[0].total_slots, f->pc[1].total_slots);
+  if (f->slots > slot_bound) return fail("internal: tree needs %d CLV slots, bound is %d", f->slots, slot_bound);
+  const size_t plan_bytes = (size_t)n * (T - 1) * sizeof(lhb::Step), pblen_bytes = (size_t)n * NB * sizeof(double);
+  LH_CUDA(cudaMemcpyAsync(f->d_plan.as<lhb::Step>() + (size_t)t0 * (T - 1), steps, plan_bytes,
+                          cudaMemcpyHostToDevice, s));
+  LH_CUDA(cudaMemcpyAsync(f->d_pblen.as<double>() + (size_t)t0 * NB, pblen, pblen_bytes, cudaMemcpyHostToDevice, s));
+  LH_CUDA(cudaEventRecord(f->ring_ev[slot], s));
+  f->ring_busy[slot] = true;
+  f->tm.h2d_bytes += (int64_t)(plan_bytes + pblen_bytes);
+  return 0;
+}
+
+// Substitution parameters of the whole batch (10 + R doubles per tree) -> HBM on `s`.
+int stage_params(lh_family* f, const lh_tree_batch_t* tb, cudaStream_t s) {
+  const size_t B = (size_t)f->B, R = (size_t)f->R;
+  if (f->misc_busy) LH_CUDA(cudaEventSynchronize(f->misc_ev));
+  double* misc = f->h_misc.as<double>();
+  std::memcpy(misc, tb->er, sizeof(double) * 6 * B);
+  std::memcpy(misc + 6 * B, tb->pi, sizeof(double) * 4 * B);
+  std::memcpy(misc + 10 * B, tb->rates, sizeof(double) * R * B);
+  LH_CUDA(cudaMemcpyAsync(f->d_er.p, misc, B * (10 + R) * 8, cudaMemcpyHostToDevice, s));
+  LH_CUDA(cudaEventRecord(f->misc_ev, s));
+  f->misc_busy = true;
+  f->tm.h2d_bytes += (int64_t)(B * (10 + R) * 8);
+  return 0;
+}
+
+int ensure_chunk_events(lh_family* f, int n_chunks) {
+  while ((int)f->chunk_ev.size() < 5 * n_chunks) {
+    cudaEvent_t e;
+    LH_CUDA(cudaEventCreate(&e));
+    f->chunk_ev.push_back(e);
+  }
+  while ((int)f->staged_ev.size() < n_chunks) {
+    cudaEvent_t e;
+    LH_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    f->staged_ev.push_back(e);
+  }
+  return 0;
+}
+
+// The four kernels of one chunk of trees, in stream order: eigen systems, branch records,
+// pruning (xMSA emission), HMM forward pass.
+void launch_chunk(lh_family* f, int ci, int t0, int n) {
+  cudaStream_t s = f->stream;
+  const bool tm = f->opt_timing;
+  if (tm) cudaEventRecord(f->chunk_ev[5 * ci], s);
+  lhb::launch_eigen(f->bd, t0, n, s);
+  lhb::launch_pmatrix(f->fd, f->bd, t0, n, s);
+  if (tm) cudaEventRecord(f->chunk_ev[5 * ci + 1], s);
+  // trees on site patterns are listed first in the chunk's part of d_list, the others after
+  const int n_pat = f->chunk_n_pat[ci];
+  const int count[2] = {n - n_pat, n_pat};
+  const int32_t* list[2] = {f->d_list.as<int32_t>() + t0 + n_pat, f->d_list.as<int32_t>() + t0};
+  for (int g = 1; g >= 0; --g) {
+    if (!count[g]) continue;
+    lhb::PruneCfg c = f->pc[g];
+    c.tree_list = list[g];
+    c.grid = std::min(c.grid, count[g] * c.n_tiles);
+    lhb::launch_prune(f->fd, f->bd, c, t0, count[g], s);
+    f->tm.kernel_launches += 1;
+    f->tm.prune_launches += 1;
+  }
+  if (tm) cudaEventRecord(f->chunk_ev[5 * ci + 2], s);
+  lhb::launch_edge(f->fd, f->bd, f->ec, t0, n, s);
+  if (tm) cudaEventRecord(f->chunk_ev[5 * ci + 3], s);
+  lhb::launch_hmm(f->fd, f->bd, f->ho, t0, n, s);
+  if (tm) cudaEventRecord(f->chunk_ev[5 * ci + 4], s);
+  f->tm.kernel_launches += 4;
+}
+
+// Fixes the chunk boundaries of the batch and queues the per-chunk tree lists on `s`.
+int stage_lists(lh_family* f, std::vector<int> starts, cudaStream_t s) {
+  f->starts = std::move(starts);
+  f->n_chunks = (int)f->starts.size() - 1;
+  f->chunk_n_pat.assign(f->n_chunks, 0);
+  if (f->list_busy) LH_CUDA(cudaEventSynchronize(f->list_ev));
+  if (f->h_list.reserve((size_t)f->B * sizeof(int32_t))) return 1;
+  int32_t* l = f->h_list.as<int32_t>();
   for (int ci = 0; ci < f->n_chunks; ++ci) {
-    cudaEventElapsedTime(&x, f->chunk_ev[3 * ci], f->chunk_ev[3 * ci + 1]);
+    int w = f->starts[ci];
+    for (int t = f->starts[ci]; t < f->starts[ci + 1]; ++t)
+      if (f->on_patterns[t]) l[w++] = t;
+    f->chunk_n_pat[ci] = w - f->starts[ci];
+    for (int t = f->starts[ci]; t < f->starts[ci + 1]; ++t)
+      if (!f->on_patterns[t]) l[w++] = t;
+  }
+  LH_CUDA(cudaMemcpyAsync(f->d_list.p, l, (size_t)f->B * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+  LH_CUDA(cudaEventRecord(f->list_ev, s));
+  f->list_busy = true;
+  f->tm.h2d_bytes += (int64_t)f->B * 4;
+  return ensure_chunk_events(f, f->n_chunks);
+}
+
+// Chunk boundaries. A resident batch runs in equal chunks; the pipelined path opens with two
+// short chunks so the first kernels start after a fraction of the host planning.
+std::vector<int> chunk_starts(const lh_family* f, bool ramp) {
+  std::vector<int> st;
+  int t0 = 0;
+  if (ramp && f->B > 2 * f->chunk) {
+    const int q = std::max(1, f->chunk / 4);  // opening chunks of chunk/4 and chunk/2 trees
+    st.push_back(0);
+    st.push_back(q);
+    t0 = std::min(f->B, 3 * q);
+  }
+  for (; t0 < f->B; t0 += f->chunk) st.push_back(t0);
+  st.push_back(f->B);
+  return st;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lh_batch_upload(lh_family_t* f, const lh_tree_batch_t* tb) {
+  if (!f || !tb) return fail("null argument");
+  LH_CUDA(cudaSetDevice(f->device));
+  if (check_batch(f, tb)) return 1;
+  if (configure_batch(f, tb->n_trees, tb->n_rates)) return 1;
+  if (f->B == 0) return 0;
+  cudaStream_t s = f->stream;
+  if (f->opt_timing) cudaEventRecord(f->ev[0], s);
+  if (stage_params(f, tb, s)) return 1;
+  if (stage_lists(f, chunk_starts(f, false), s)) return 1;
+  for (int t0 = 0, k = 0; t0 < f->B; t0 += f->seg, ++k)
+    if (stage_segment(f, tb, t0, std::min(f->seg, f->B - t0), k % lh_family::kRing, s)) return 1;
+  if (f->opt_timing) cudaEventRecord(f->ev[1], s);
+  return 0;
+}
+
+int lh_batch_run(lh_family_t* f) {
+  if (!f) return fail("null family");
+  if (f->B == 0) return 0;
+  LH_CUDA(cudaSetDevice(f->device));
+  const std::vector<int>& st = f->starts;
+  f->tm.kernel_launches = 0;
+  f->tm.prune_launches = 0;
+  if (f->opt_timing) cudaEventRecord(f->ev[2], f->stream);
+  for (int ci = 0; ci < f->n_chunks; ++ci) launch_chunk(f, ci, st[ci], st[ci + 1] - st[ci]);
+  if (f->opt_timing) cudaEventRecord(f->ev[4], f->stream);
+  LH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Per-kernel device times of the last run (syncs the stream).
+static int collect_run_timings(lh_family* f) {
+  if (!f->opt_timing || f->B == 0 || f->n_chunks == 0) return 0;
+  LH_CUDA(cudaEventSynchronize(f->ev[4]));
+  float pm = 0, pr = 0, ed = 0, hm = 0, x = 0;
+  for (int ci = 0; ci < f->n_chunks; ++ci) {
+    cudaEventElapsedTime(&x, f->chunk_ev[5 * ci], f->chunk_ev[5 * ci + 1]);
     pm += x;
-    cudaEventElapsedTime(&x, f->chunk_ev[3 * ci + 1], f->chunk_ev[3 * ci + 2]);
+    cudaEventElapsedTime(&x, f->chunk_ev[5 * ci + 1], f->chunk_ev[5 * ci + 2]);
     pr += x;
+    cudaEventElapsedTime(&x, f->chunk_ev[5 * ci + 2], f->chunk_ev[5 * ci + 3]);
+    ed += x;
+    cudaEventElapsedTime(&x, f->chunk_ev[5 * ci + 3], f->chunk_ev[5 * ci + 4]);
+    hm += x;
   }
   f->tm.ms_pmatrix = pm;
   f->tm.ms_prune = pr;
-  cudaEventElapsedTime(&f->tm.ms_hmm, f->ev[3], f->ev[4]);
+  f->tm.ms_edge = ed;
+  f->tm.ms_hmm = hm;
   cudaEventElapsedTime(&f->tm.ms_kernels, f->ev[2], f->ev[4]);
   return 0;
 }
@@ -619,8 +876,34 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   if (!f || !tb || !loglik) return fail("null argument");
   f->want_tables = o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
                          o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers);
-  if (lh_batch_upload(f, tb)) return 1;
-  if (lh_batch_run(f)) return 1;
+  LH_CUDA(cudaSetDevice(f->device));
+  if (check_batch(f, tb)) return 1;
+  if (configure_batch(f, tb->n_trees, tb->n_rates)) return 1;
+  if (f->B == 0) return 0;
+  // Pipeline: the host plans one segment of trees at a time into the pinned ring, the copy
+  // stream moves it to HBM, and the compute stream starts a chunk's kernels as soon as the
+  // chunk's last segment has landed - planning and H2D of chunk c+1 overlap the kernels of c.
+  cudaStream_t cs = f->copy_stream;
+  // the copy stream must not overwrite buffers an earlier run on the compute stream still reads
+  LH_CUDA(cudaEventRecord(f->ev[7], f->stream));
+  LH_CUDA(cudaStreamWaitEvent(cs, f->ev[7], 0));
+  if (f->opt_timing) cudaEventRecord(f->ev[0], cs);
+  if (stage_params(f, tb, cs)) return 1;
+  if (stage_lists(f, chunk_starts(f, true), cs)) return 1;
+  const std::vector<int>& st = f->starts;
+  for (int ci = 0, k = 0; ci < f->n_chunks; ++ci) {
+    for (int t0 = st[ci]; t0 < st[ci + 1]; t0 += f->seg, ++k)
+      if (stage_segment(f, tb, t0, std::min(f->seg, st[ci + 1] - t0), k % lh_family::kRing, cs)) return 1;
+    LH_CUDA(cudaEventRecord(f->staged_ev[ci], cs));
+    LH_CUDA(cudaStreamWaitEvent(f->stream, f->staged_ev[ci], 0));
+    if (ci == 0 && f->opt_timing) cudaEventRecord(f->ev[2], f->stream);
+    launch_chunk(f, ci, st[ci], st[ci + 1] - st[ci]);
+  }
+  if (f->opt_timing) {
+    cudaEventRecord(f->ev[1], cs);
+    cudaEventRecord(f->ev[4], f->stream);
+  }
+  LH_CUDA(cudaGetLastError());
   return lh_batch_fetch(f, loglik, o);
 }
 

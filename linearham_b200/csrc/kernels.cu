@@ -28,9 +28,10 @@ namespace lhb {
 // (models.c:24-178); any orthogonal eigensolver gives the same P-matrices to ~1e-16
 // because P = I + sum_m inv[.,m] expm1(..) evecs[m,.] is invariant to the choice of
 // basis inside a degenerate eigenspace.
-__global__ void k_eigen(BatchDev b) {
+__global__ void k_eigen(BatchDev b, int tree0, int ntrees) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= b.B) return;
+  if (t >= ntrees) return;
+  t += tree0;
   double r[6], pi[4];
   for (int i = 0; i < 6; ++i) r[i] = b.er[6 * t + i];
   for (int i = 0; i < 4; ++i) pi[i] = b.pi[4 * t + i];
@@ -105,9 +106,9 @@ __global__ void k_eigen(BatchDev b) {
   }
 }
 
-void launch_eigen(const BatchDev& b, cudaStream_t s) {
+void launch_eigen(const BatchDev& b, int tree0, int ntrees, cudaStream_t s) {
   int threads = 128;
-  k_eigen<<<(b.B + threads - 1) / threads, threads, 0, s>>>(b);
+  k_eigen<<<(ntrees + threads - 1) / threads, threads, 0, s>>>(b, tree0, ntrees);
 }
 
 // ---------------------------------------------------------------- k_pmatrix ---
@@ -366,7 +367,7 @@ template <int NS>
 __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
     k_prune(FamilyDev f, BatchDev b, PruneCfg cfg, int tree0, int ntrees) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int lane = threadIdx.x, T = f.T, S = f.S, R = b.R;
+  const int lane = threadIdx.x, T = f.T, R = b.R;
   const int NB = 2 * T - 3, n_steps = T - 2, n_iter = T - 1;  // node updates + the edge evaluation
   const int gslots = cfg.total_slots - cfg.smem_slots;
   double* ring_rec = reinterpret_cast<double*>(smem_raw);                            // [kRecRing][2][20]
@@ -378,8 +379,6 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
   io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * 32;
   io.smem_slots = cfg.smem_slots;
   io.lane = lane;
-  const double weight = 1.0 / R;  // pll.c:746-747
-  constexpr double kDown = LH_SCALE_THRESHOLD;
   // staging roles: lanes 0..19 each copy 16 of the 320 record bytes of a step
   const bool rec_lane = lane < kStepBytes / 16;
   const unsigned ring_rec_s = (unsigned)__cvta_generic_to_shared(ring_rec) + lane * 16;
@@ -389,18 +388,12 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
 
   const int n_work = ntrees * cfg.n_tiles;
   for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
-    const int lt = w / cfg.n_tiles, tile = w - lt * cfg.n_tiles;
-    const int t = tree0 + lt;
+    const int li = w / cfg.n_tiles, tile = w - li * cfg.n_tiles;
+    const int t = __ldg(cfg.tree_list + li);
+    const int lt = t - tree0;
     const int4* __restrict__ plan = b.plan + (size_t)t * (T - 1);
-    const double* __restrict__ eig = b.eig + (size_t)t * kEigStride;
     const unsigned* __restrict__ my_codes = cfg.codes_t + (size_t)tile * 32 + lane;
-    const double pi0 = eig[40], pi1 = eig[41], pi2 = eig[42], pi3 = eig[43];
-
-    // sum over categories of the edge terms, kept as acc * 2^(-256 * acc_cnt)
-    double acc[NS];
-    int acc_cnt[NS];
-#pragma unroll
-    for (int u = 0; u < NS; ++u) { acc[u] = 0.0; acc_cnt[u] = 0; }
+    int naive_br = -1;  // record index of the naive tip's branch when its factor is deferred
 
     for (int k = 0; k < R; ++k) {
       // the record stream of this (tree, category): step q at rec_src + q * 320 bytes
@@ -460,6 +453,22 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
           int ca[NS], cb[NS];
           child_messages<NS>(st.x, recA, cA, reg, reg_cnt, io, ma, ca);
           child_messages<NS>(st.y, recA + kRecDoubles, cB, reg, reg_cnt, io, mb, cb);
+          // Pattern columns: the node under which the naive tip hangs keeps the other child's
+          // message only; k_edge multiplies the naive tip's Q column in, per xMSA column.
+          const bool defer_a = cfg.defer_naive && st.x == 0, defer_b = cfg.defer_naive && st.y == 0;
+          if (defer_a | defer_b) {
+            naive_br = 2 * s + (defer_a ? 0 : 1);
+#pragma unroll
+            for (int u = 0; u < NS; ++u) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                ma[u][i] = defer_a ? mb[u][i] : ma[u][i];
+                mb[u][i] = 1.0;
+              }
+              if (defer_a) ca[u] = cb[u];
+              cb[u] = 0;
+            }
+          }
           int lowest = 0x7fffffff;  // min over columns of the largest high word
 #pragma unroll
           for (int u = 0; u < NS; ++u) {
@@ -470,7 +479,8 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
                                max(__double2hiint(reg[u][2]), __double2hiint(reg[u][3])));
             lowest = min(lowest, hi);
           }
-          if (lowest < kThresholdHi) {  // some column has all four entries below 2^-256
+          // (a deferred node is rescaled by k_edge, once the naive factor is in)
+          if (lowest < kThresholdHi && !(defer_a | defer_b)) {  // some column has all four entries below 2^-256
 #pragma unroll
             for (int u = 0; u < NS; ++u) {
               const int hi = max(max(__double2hiint(reg[u][0]), __double2hiint(reg[u][1])),
@@ -497,40 +507,25 @@ __global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
             if (io.in_smem(slot)) unpark<NS>(io.shared(slot), reg, reg_cnt);
             else unpark<NS>(io.global(slot), reg, reg_cnt);
           }
+          // hand the edge term's inputs to k_edge
+          double* eo = cfg.ebuf + (size_t)lt * cfg.e_stride + (size_t)k * 8 * cfg.cols_pad + tile * (32 * NS) + lane;
+          int* co = cfg.ecnt + (size_t)lt * cfg.c_stride + (size_t)k * cfg.cols_pad + tile * (32 * NS) + lane;
 #pragma unroll
           for (int u = 0; u < NS; ++u) {
-            const double t0 = (pi0 * mc[u][0]) * reg[u][0];
-            const double t1 = (pi1 * mc[u][1]) * reg[u][1];
-            const double t2 = (pi2 * mc[u][2]) * reg[u][2];
-            const double t3 = (pi3 * mc[u][3]) * reg[u][3];
-            double term = (t0 + t1) + (t2 + t3);
-            if (term > 0.0) {  // :1225
-              term *= weight;
-              int c = reg_cnt[u] + cc[u];
-              // bring acc and term to the smaller count (exact: powers of two)
-              if (acc[u] == 0.0) acc_cnt[u] = c;
-              while (c > acc_cnt[u]) { term *= kDown; --c; if (term == 0.0) c = acc_cnt[u]; }
-              while (acc_cnt[u] > c) { acc[u] *= kDown; --acc_cnt[u]; if (acc[u] == 0.0) acc_cnt[u] = c; }
-              acc[u] += term;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              eo[(size_t)i * cfg.cols_pad + u * 32] = mc[u][i];
+              eo[(size_t)(4 + i) * cfg.cols_pad + u * 32] = reg[u][i];
             }
+            co[u * 32] = reg_cnt[u] + cc[u];
           }
+          if (cfg.defer_naive && st.y == 0) naive_br = 2 * n_steps;
         }
       }
       cp_async_wait<0>();
     }
 
-    const unsigned naive = __ldg(my_codes);  // xMSA row 0 is the naive sequence
-#pragma unroll
-    for (int u = 0; u < NS; ++u) {
-      const int site = tile * (32 * NS) + u * 32 + lane;
-      if (site >= S) continue;
-      double site_lk = log(acc[u]);
-      if (acc_cnt[u]) site_lk += acc_cnt[u] * cfg.log_threshold;   // :1247-1251
-      // naive-sequence correction (src/PhyloHMM.cpp:229-237)
-      const int nb = ((naive >> (8 * u)) & 0xffu) >> 5;
-      if (nb != 4) site_lk -= eig[36 + nb];
-      b.xe[(size_t)t * S + site] = exp(site_lk);
-    }
+    if (tile == 0 && lane == 0) cfg.enaive[lt] = naive_br;
   }
 }
 
@@ -568,6 +563,88 @@ int prune_max_ctas_per_sm(int ns, int smem_slots) {
   int n = 0;
   LH_DISPATCH_NS(ns, n = prune_occ_n<NN>(smem));
   return n;
+}
+
+// ------------------------------------------------------------------- k_edge ---
+// One thread per (tree, xMSA column): the edge log-likelihood of the column from the two CLV
+// messages k_prune left per category (core_likelihood_avx.c:1130-1251), the naive-sequence
+// correction and the exponential (src/PhyloHMM.cpp:219-240). When the pruning ran on site
+// patterns, the naive tip's factor - column `code` of its branch's Q block - is multiplied in
+// here, with the node's rescaling test (core_partials.c:648-659) applied to the product as the
+// reference applies it.
+__global__ void __launch_bounds__(128) k_edge(FamilyDev f, BatchDev b, EdgeCfg cfg, int tree0, int ntrees) {
+  const int S = f.S, R = b.R, NB = 2 * f.T - 3, edge_br = NB - 1;
+  const double weight = 1.0 / R;  // pll.c:746-747
+  constexpr double kDown = LH_SCALE_THRESHOLD;
+  const long long total = (long long)ntrees * S;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int lt = (int)(idx / S), site = (int)(idx - (long long)lt * S);
+    const int t = tree0 + lt;
+    const int code = __ldg(f.tip_codes + site);  // xMSA row 0 is the naive sequence
+    const int nbr = __ldg(cfg.enaive + lt);
+    const int col = nbr >= 0 ? __ldg(cfg.col_of_site + site) : site;
+    const size_t pitch = nbr >= 0 ? cfg.cols_pad_pat : cfg.cols_pad_all;
+    const double* eig = b.eig + (size_t)t * kEigStride;
+    const double pi0 = eig[40], pi1 = eig[41], pi2 = eig[42], pi3 = eig[43];
+    // sum over categories of the edge terms, kept as acc * 2^(-256 * acc_cnt)
+    double acc = 0.0;
+    int acc_cnt = 0;
+    for (int k = 0; k < R; ++k) {
+      const double* e = cfg.ebuf + (size_t)lt * cfg.e_stride + (size_t)k * 8 * pitch + col;
+      double mc[4], rg[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        mc[i] = e[(size_t)i * pitch];
+        rg[i] = e[(size_t)(4 + i) * pitch];
+      }
+      int c = cfg.ecnt[(size_t)lt * cfg.c_stride + (size_t)k * pitch + col];
+      if (nbr >= 0) {
+        const double* q = b.prec + (((size_t)lt * R + k) * NB + nbr) * kRecDoubles + code * 4;
+        if (nbr == edge_br) {  // the naive tip is the node across the root edge
+#pragma unroll
+          for (int i = 0; i < 4; ++i) mc[i] = q[i];
+        } else {               // the naive tip hangs under the virtual root
+#pragma unroll
+          for (int i = 0; i < 4; ++i) rg[i] *= q[i];  // core_partials.c:626
+          const int hi = max(max(__double2hiint(rg[0]), __double2hiint(rg[1])),
+                             max(__double2hiint(rg[2]), __double2hiint(rg[3])));
+          if (hi < kThresholdHi) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) rg[i] *= LH_SCALE_FACTOR;
+            c += 1;
+          }
+        }
+      }
+      const double t0 = (pi0 * mc[0]) * rg[0];
+      const double t1 = (pi1 * mc[1]) * rg[1];
+      const double t2 = (pi2 * mc[2]) * rg[2];
+      const double t3 = (pi3 * mc[3]) * rg[3];
+      double term = (t0 + t1) + (t2 + t3);
+      if (term > 0.0) {  // :1225
+        term *= weight;
+        // bring acc and term to the smaller count (exact: powers of two)
+        if (acc == 0.0) acc_cnt = c;
+        while (c > acc_cnt) { term *= kDown; --c; if (term == 0.0) c = acc_cnt; }
+        while (acc_cnt > c) { acc *= kDown; --acc_cnt; if (acc == 0.0) acc_cnt = c; }
+        acc += term;
+      }
+    }
+    double site_lk = log(acc);
+    if (acc_cnt) site_lk += acc_cnt * cfg.log_threshold;   // :1247-1251
+    // naive-sequence correction (src/PhyloHMM.cpp:229-237)
+    if (code != 4) site_lk -= eig[36 + code];
+    b.xe[(size_t)t * S + site] = exp(site_lk);
+  }
+}
+
+void launch_edge(const FamilyDev& f, const BatchDev& b, const EdgeCfg& c, int tree0, int ntrees,
+                 cudaStream_t s) {
+  const long long total = (long long)ntrees * f.S;
+  const int threads = 128;
+  long long blocks = (total + threads - 1) / threads;
+  if (blocks > 148LL * 64) blocks = 148LL * 64;
+  k_edge<<<(unsigned)blocks, threads, 0, s>>>(f, b, c, tree0, ntrees);
 }
 
 // -------------------------------------------------------------------- k_hmm ---
@@ -675,7 +752,7 @@ __device__ int junction_forward(const CscDev& t_in, const CscDev& t_jj, const in
   return count;
 }
 
-__global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o) {
+__global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o, int tree0, int ntrees) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warps = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int per_warp = 2 * f.s_max + 5 * (f.g_max + (f.g_max + 1) / 2);
@@ -689,7 +766,7 @@ __global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o) 
   double* e_jgerm = e_dgerm + gstride;
   double* e_jpad = e_jgerm + gstride;
 
-  for (int t = blockIdx.x * warps + wid; t < b.B; t += gridDim.x * warps) {
+  for (int t = tree0 + blockIdx.x * warps + wid; t < tree0 + ntrees; t += gridDim.x * warps) {
     const double* xe = b.xe + (size_t)t * f.S;
     // emissions (src/PhyloHMM.cpp:94-114); counts reset per tree (:373-375)
     int c_v = fill_region(f.n_v, f.vpad_off, f.vpad_inds, xe, e_vpad, lane);
@@ -767,13 +844,13 @@ size_t hmm_smem_bytes(const FamilyDev& f, int warps) {
   return per_warp * warps * sizeof(double);
 }
 
-void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, cudaStream_t s) {
+void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, int tree0, int ntrees, cudaStream_t s) {
   const int warps = 4;
   size_t smem = hmm_smem_bytes(f, warps);
   cudaFuncSetAttribute(k_hmm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  int blocks = (b.B + warps - 1) / warps;
+  int blocks = (ntrees + warps - 1) / warps;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  k_hmm<<<blocks, warps * 32, smem, s>>>(f, b, o);
+  k_hmm<<<blocks, warps * 32, smem, s>>>(f, b, o, tree0, ntrees);
 }
 
 // ------------------------------------------------------------- diagnostics ---

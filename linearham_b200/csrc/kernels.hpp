@@ -54,6 +54,29 @@ struct PruneCfg {
   // tip codes re-tiled for this NS: word [tip][tile][lane], byte u = 32 * code of column
   // tile*32*NS + u*32 + lane (0 beyond S); 32*code is the byte offset of the Q column
   const uint32_t* codes_t;
+  // pruning columns. k_prune walks `n_cols` columns: either all S xMSA columns, or - for trees
+  // that have the naive tip (xMSA row 0) on the root edge or under the virtual root - the U
+  // distinct site patterns of rows 1..T-1, with the naive tip's factor deferred to k_edge.
+  int32_t n_cols;        // S or U
+  int32_t cols_pad;      // n_tiles * 32 * NS
+  int32_t defer_naive;   // 1: pattern columns, naive factor applied by k_edge
+  const int32_t* tree_list;  // trees of this launch (batch indices inside the chunk)
+  // per (chunk tree, category, column) inputs of the edge term, written by k_prune:
+  double* ebuf;          // tree at e_stride doubles: [R][8][cols_pad] message across the root edge [4], root CLV [4]
+  int32_t* ecnt;         // tree at c_stride ints:    [R][cols_pad] scaler count of the two
+  int32_t* enaive;       // [chunk] record index of the naive tip's branch, -1 when not deferred
+  int64_t e_stride, c_stride;
+};
+
+// k_edge reads what the (up to two) k_prune launches of a chunk left behind
+struct EdgeCfg {
+  const double* ebuf;
+  const int32_t* ecnt;
+  const int32_t* enaive;
+  int64_t e_stride, c_stride;
+  int32_t cols_pad_all, cols_pad_pat;  // column pitch of trees pruned on all columns / on patterns
+  const int32_t* col_of_site;          // [S] pattern index of each xMSA column
+  double log_threshold;
 };
 
 struct HmmOut {           // optional device buffers (may be null)
@@ -62,11 +85,16 @@ struct HmmOut {           // optional device buffers (may be null)
   double log_factor;      // log(2^256), host libm (src/HMM.cpp:353)
 };
 
-void launch_eigen(const BatchDev& b, cudaStream_t s);
+void launch_eigen(const BatchDev& b, int tree0, int ntrees, cudaStream_t s);
 void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees, cudaStream_t s);
-void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0, int ntrees,
+// prunes the `nlist` trees c.tree_list names; tree0 is the first tree of the chunk (its branch
+// records and edge buffers are chunk-relative)
+void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0, int nlist,
                   cudaStream_t s);
-void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, cudaStream_t s);
+void launch_edge(const FamilyDev& f, const BatchDev& b, const EdgeCfg& c, int tree0, int ntrees,
+                 cudaStream_t s);
+void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, int tree0, int ntrees,
+                cudaStream_t s);
 size_t prune_smem_bytes(int sites_per_thread, int smem_slots);
 int prune_max_ctas_per_sm(int sites_per_thread, int smem_slots);
 size_t hmm_smem_bytes(const FamilyDev& f, int warps);

@@ -187,13 +187,15 @@ class Tree:
     def inner_nonroot(self):
         return [i for i in range(1, len(self.parent)) if self.children[i]]
 
-    def nni(self, rng):
+    def nni(self, rng, fixed=None):
+        """One nearest-neighbour interchange across a random inner edge. `fixed`: a node that never
+        moves (the outgroup tip under the root)."""
         cand = self.inner_nonroot()
         if not cand:
             return
         v = cand[int(rng.integers(len(cand)))]
         p = self.parent[v]
-        sibs = [c for c in self.children[p] if c != v]
+        sibs = [c for c in self.children[p] if c != v and c != fixed]
         s = sibs[int(rng.integers(len(sibs)))]
         c = self.children[v][int(rng.integers(2))]
         # swap subtree c (child of v) with subtree s (sibling of v)
@@ -251,22 +253,27 @@ def evolve(rng, tree, naive_seq):
     return seqs
 
 
-def tree_samples(rng, tree, B, walk="anchored"):
+def tree_samples(rng, tree, B, walk="anchored", outgroup=None):
     """Sample 0 = `tree`; sample i = sample i-1 after Poisson(3) NNIs, with LogNormal(0,0.3) branch noise.
 
     walk="anchored" (default): the noise multiplies the branch lengths of `tree` (node ids are stable
     under NNI), so lengths stay on the scale of the family however long the chain is.
     walk="cumulative": the noise compounds from sample to sample (SURVEY.md 8(d) as written). Over
     thousands of samples the lengths random-walk over many orders of magnitude and the reference
-    itself returns inf/NaN; the committed golden bundles (<= 6 samples) were made this way."""
+    itself returns inf/NaN; the committed golden bundles (<= 6 samples) were made this way.
+    outgroup: label of a tip that stays under the trifurcation, as the naive sequence does in the
+    trees linearham scores (templates/revbayes_template.rev:55, dnUniformTopology(outgroup=...))."""
     cur = tree.copy()
+    fixed = None
+    if outgroup is not None:
+        fixed = next(i for i, lab in enumerate(tree.label) if lab == outgroup)
     base = list(tree.blen)
     out = []
     for i in range(B):
         if i:
             cur = cur.copy()
             for _ in range(int(rng.poisson(3))):
-                cur.nni(rng)
+                cur.nni(rng, fixed)
             for j in range(1, len(cur.blen)):
                 noise = float(rng.lognormal(0.0, 0.3))
                 cur.blen[j] = (cur.blen[j] if walk == "cumulative" else base[j]) * noise

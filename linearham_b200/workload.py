@@ -11,9 +11,9 @@ from . import host, synth
 
 # name -> leaves, trees per batch (whole job), Gamma categories, family seed, tree seed
 CONFIGS = {
-    "c3": dict(n_leaves=128, B=4096, R=4, fam_seed=1300, tree_seed=2003,
+    "c3": dict(n_leaves=128, B=4096, R=4, fam_seed=1300, tree_seed=2003, outgroup="naive",
                desc="synthetic 128-leaf IGH family, 400 nt naive, Gamma-4 GTR, batch 4096 trees"),
-    "c4": dict(n_leaves=1000, B=16384, R=4, fam_seed=1400, tree_seed=2004,
+    "c4": dict(n_leaves=1000, B=16384, R=4, fam_seed=1400, tree_seed=2004, outgroup="naive",
                desc="synthetic 1000-leaf IGH family, 400 nt, Gamma-4, batch 16384 trees"),
     "tiny": dict(n_leaves=24, B=256, R=4, fam_seed=1500, tree_seed=2005,
                  desc="synthetic 24-leaf IGH family (tests)"),
@@ -37,14 +37,15 @@ def write_family_files(cfg, outdir):
 
 def tree_batch(cfg, fam_files, B, n_topo=None, n_threads=0):
     """B tree samples for the family. The first n_topo samples are a Markov chain of topologies
-    (Poisson(3) NNIs per step, LogNormal(0,0.3) branch noise anchored on the true tree) written
+    (Poisson(3) NNIs per step - with cfg["outgroup"] the naive tip stays under the trifurcation, as
+    RevBayes' outgroup constraint keeps it - LogNormal(0,0.3) branch noise anchored on the true tree) written
     as RevBayes-style Newick strings; sample b >= n_topo reuses topology b % n_topo with fresh
     LogNormal(0,0.1) noise on every branch. er ~ Dirichlet(1), pi ~ Dirichlet(1) floored at
     0.01, alpha = max(0.05, Exp(1)) are fresh for every sample.
     -> (tb dict for the C ABI, newicks[n_topo], alpha[B])"""
     rng = np.random.default_rng(cfg["tree_seed"])
     n_topo = min(B, n_topo or B)
-    samples = synth.tree_samples(rng, fam_files["tree"], n_topo)
+    samples = synth.tree_samples(rng, fam_files["tree"], n_topo, outgroup=cfg.get("outgroup"))
     newicks = [s["newick"] for s in samples]
     base = host.newick_to_ops(newicks, fam_files["labels"], n_threads)
     reps = (B + n_topo - 1) // n_topo

@@ -64,7 +64,7 @@ def test_batch_replication_and_chunking_are_bit_identical():
     rep = 50
     big = {k: np.concatenate([v] * rep) for k, v in tb.items()}
     f = device.Family(fam)
-    f.set_option("chunk_bytes", 1 << 16)  # force many chunks
+    f.set_option("chunk_trees", 37)  # force many chunks
     ll = f.score(big)
     ll1 = f.score(tb)
     assert np.array_equal(ll, np.tile(ll1, rep))
@@ -90,3 +90,96 @@ def test_empty_batch_and_errors():
     badfam["tip_codes"][0, 0] = 9
     with pytest.raises(device.DeviceError):
         device.Family(badfam)
+
+
+def _score_with(fam, tb, **opts):
+    f = device.Family(fam)
+    for k, v in opts.items():
+        f.set_option(k, v)
+    ll, out = f.score(tb, outputs=True)
+    tm = f.timings()
+    f.close()
+    return ll, out, tm
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_site_patterns_are_bit_identical_to_all_columns(name):
+    """Pruning the distinct site patterns of rows 1.. and applying the naive row in k_edge gives
+    the same doubles as pruning every xMSA column."""
+    fam, tb, _, _ = load_golden(name)
+    a, oa, ta = _score_with(fam, tb, site_patterns=1)
+    b, ob, tb_ = _score_with(fam, tb, site_patterns=0)
+    assert tb_["pattern_trees"] == 0 and tb_["prune_columns"] == fam["n_sites"]
+    if name.startswith("synth"):
+        assert ta["pattern_trees"] > 0 and ta["prune_columns"] < fam["n_sites"]
+    assert np.array_equal(a, b)
+    assert np.array_equal(oa["xmsa_emission"], ob["xmsa_emission"])
+
+
+def _rotate_root_to_naive(tb):
+    """Moves the evaluation edge onto the naive tip's branch (same unrooted tree): the naive tip,
+    a child of the last operation, becomes root_child."""
+    out = {k: v.copy() for k, v in tb.items()}
+    for t in range(len(out["root_child"])):
+        last, lb = out["children"][t, -1], out["blen"][t, -1]
+        j = int(np.flatnonzero(last == 0)[0])
+        x, lx, ln = last[1 - j], lb[1 - j], lb[j]
+        c, lc = out["root_child"][t], out["root_blen"][t]
+        out["children"][t, -1] = (c, x)
+        out["blen"][t, -1] = (lc, lx)
+        out["root_child"][t], out["root_blen"][t] = 0, ln
+    return out
+
+
+@pytest.mark.parametrize("name", ["synth_n12", "synth_n40"])
+def test_naive_tip_across_the_root_edge(name):
+    fam, tb, _, _ = load_golden(name)
+    keep = [t for t in range(len(tb["root_child"])) if 0 in tb["children"][t, -1]]
+    tb = {k: v[keep] for k, v in tb.items()}
+    rot = _rotate_root_to_naive(tb)
+    pll, pout = po.port_score_batch(fam, rot)
+    a, oa, ta = _score_with(fam, rot, site_patterns=1)
+    b, ob, _ = _score_with(fam, rot, site_patterns=0)
+    assert ta["pattern_trees"] == len(keep)
+    assert np.array_equal(a, b) and np.array_equal(oa["xmsa_emission"], ob["xmsa_emission"])
+    assert rel_err(a, pll) <= TOL and rel_err(oa["xmsa_emission"], pout["xmsa_emission"]) <= TOL
+
+
+def test_naive_tip_deep_in_the_tree_falls_back_to_all_columns():
+    """With the naive row swapped onto a tip that is not next to the virtual root, no column can be
+    shared: the batch runs on all xMSA columns and still matches the oracle."""
+    fam, tb, _, _ = load_golden("synth_n40")
+    near_root = set(tb["children"][:, -1].ravel()) | set(tb["root_child"])
+    r = next(i for i in range(1, fam["n_tips"]) if i not in near_root)
+    fam2 = dict(fam)
+    codes = fam["tip_codes"].copy()
+    codes[[0, r]] = codes[[r, 0]]
+    fam2["tip_codes"] = codes
+    relabel = {k: v.copy() for k, v in tb.items()}
+    for key in ("children", "root_child"):
+        a = relabel[key]
+        is0, isr = a == 0, a == r
+        a[is0], a[isr] = r, 0
+    pll, pout = po.port_score_batch(fam2, relabel)
+    ll, out, tm = _score_with(fam2, relabel)
+    assert tm["pattern_trees"] == 0 and tm["prune_columns"] == fam["n_sites"]
+    assert rel_err(ll, pll) <= TOL and rel_err(out["xmsa_emission"], pout["xmsa_emission"]) <= TOL
+
+
+def test_pipelined_call_matches_resident_batch():
+    """lh_score_batch (segments planned and copied while earlier chunks run) and the split
+    upload / run / fetch form give the same doubles, across short opening chunks and a ragged tail."""
+    fam, tb, _, _ = load_golden("synth_n12")
+    rep = 397
+    big = {k: np.concatenate([v] * rep) for k, v in tb.items()}
+    f = device.Family(fam)
+    f.set_option("chunk_trees", 100)
+    a = f.score(big)
+    n_launch = f.timings()["prune_launches"]
+    f.upload(big)
+    f.run()
+    b = f.fetch()
+    f.close()
+    assert n_launch >= 3
+    assert np.array_equal(a, b)
+    assert np.array_equal(a, np.tile(a[:len(tb["root_child"])], rep))
