@@ -170,6 +170,8 @@ def main():
     ap.add_argument("--topologies", type=int, default=256, help="distinct tree topologies in the batch")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE",
+                    help="lh_set_option on the family (e.g. pipe_waves=4); recorded in config")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -259,6 +261,11 @@ def main():
     Bs = hi - lo
 
     f = device.Family(fam, device=dev)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        f.set_option(k, int(v))
+    if args.opt:
+        config["options"] = list(args.opt)
     gathered = None
     if world > 1:
         f.set_option("stream", torch.cuda.current_stream().cuda_stream)
@@ -293,7 +300,7 @@ def main():
     sync_all()
     sampler.start()
     f.mark(0)
-    acc = {"ms_prune": 0.0, "ms_pmatrix": 0.0, "ms_edge": 0.0, "ms_hmm": 0.0, "prune_launches": 0, "kernel_launches": 0}
+    acc = {"ms_prune": 0.0, "ms_pmatrix": 0.0, "ms_repeats": 0.0, "ms_edge": 0.0, "ms_hmm": 0.0, "prune_launches": 0, "kernel_launches": 0}
     for _ in range(args.steps):
         f.run()
         gather_step()
@@ -306,7 +313,7 @@ def main():
     ll_dev = f.fetch()
 
     # -------- e2e: host buffers in, host log-likelihoods out --------------------
-    e2e_s, h2d, d2h, ms_plan = None, 0, 0, 0.0
+    e2e_s, h2d, d2h, ms_plan, e2e_detail = None, 0, 0, 0.0, None
     if not args.no_e2e:
         for _ in range(max(1, min(args.warmup, 2))):
             f.score(shard)
@@ -316,6 +323,7 @@ def main():
             ll_e2e = f.score(shard)
             t2 = f.timings()
             h2d, d2h, ms_plan = t2["h2d_bytes"], t2["d2h_bytes"], t2["ms_plan"]
+            e2e_detail = {k: t2[k] for k in ("ms_call", "ms_setup", "ms_plan", "ms_h2d", "ms_kernels", "ms_d2h")}
         sync_all()
         e2e_s = time.perf_counter() - t0
         assert np.array_equal(ll_e2e, ll_dev, equal_nan=True)
@@ -344,6 +352,7 @@ def main():
         flops_tree = workload.flops_per_tree(T, cols, R)
         config["prune_columns"] = cols
         config["pattern_trees_rank0"] = int(tm["pattern_trees"])
+        config["site_repeats"] = bool(tm["site_repeats"])
         prune_s = acc["ms_prune"] * 1e-3
         achieved = bytes_tree * Bs * args.steps / prune_s / 1e9
         fp64_peak = device.fp64_peak_tflops(dev)
@@ -375,12 +384,12 @@ def main():
                          "fp64": {"achieved_tflops": flops_tree * Bs * args.steps / prune_s / 1e12, "peak_tflops": fp64_peak,
                                   "frac": flops_tree * Bs * args.steps / prune_s / 1e12 / fp64_peak,
                                   "peak_source": "lh_measure_fp64_peak (DFMA loop, this run)"}},
-            "stage_ms_per_step": {"k_pmatrix": acc["ms_pmatrix"] / args.steps, "k_prune": acc["ms_prune"] / args.steps,
+            "stage_ms_per_step": {"k_pmatrix": acc["ms_pmatrix"] / args.steps, "k_repeats": acc["ms_repeats"] / args.steps, "k_prune": acc["ms_prune"] / args.steps,
                                   "k_edge": acc["ms_edge"] / args.steps, "k_hmm": acc["ms_hmm"] / args.steps, "rank": 0},
             "cpu_baseline": cpu_baseline,
             "e2e": None if e2e_s is None else {"value": B_total * args.steps / e2e_s, "unit": UNIT,
                                                "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
-                                               "host_plan_ms_per_step_rank0": ms_plan,
+                                               "host_plan_ms_per_step_rank0": ms_plan, "last_call_ms_rank0": e2e_detail,
                                                "api": "lh_score_batch (host arrays in, host log-likelihoods out)"},
             "gpu_launches": launches_total, "clocks": clocks, "parity": parity,
             "finite_fraction": float(np.mean(np.isfinite(full))),

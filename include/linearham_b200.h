@@ -133,6 +133,12 @@ typedef struct lh_timings {
   int32_t prune_grid, prune_ctas_per_sm;
   int32_t prune_columns;     /* columns k_prune walked: S_x, or the distinct site patterns */
   int32_t pattern_trees;     /* trees of the batch pruned on site patterns               */
+  float ms_call;             /* wall clock of the last lh_score_batch call               */
+  float ms_setup;            /* of which validation + buffer set-up before the pipeline  */
+  float ms_repeats;          /* sum over k_repeats launches                              */
+  int32_t site_repeats;      /* 1 when the pattern trees ran on site-repeat classes      */
+  int32_t sr_arena;          /* shared-memory CLV arena entries per warp (k_prune_sr)    */
+  int32_t sr_ctas_per_sm;
 } lh_timings_t;
 
 const char* lh_last_error(void);
@@ -163,8 +169,11 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
 /* keys: "sites_per_thread" (0 = auto, 1..4: xMSA columns per thread; a CTA is one warp and
  * covers 32x that many columns), "smem_slots" (-1 = auto), "timing" (0/1), "host_threads",
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never
- * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "stream" (a
- * caller-owned cudaStream_t cast to int64; 0 = private stream), "site_patterns" (1 =
+ * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "pipe_waves" (default 4:
+ * lh_score_batch launches a chunk's kernels every that many waves of CTAs), "stream" (a
+ * caller-owned cudaStream_t cast to int64; 0 = private stream), "site_repeats" (0/1: prune the
+ * pattern trees on per-node site-repeat classes, k_repeats + k_prune_sr), "sr_arena" (0 = auto:
+ * shared-memory CLV entries per warp of k_prune_sr), "site_patterns" (1 =
  * default: trees that have the naive tip on the root edge or under the virtual root are
  * pruned on the distinct site patterns of xMSA rows 1.., and k_edge applies the naive row's
  * factor per xMSA column; other trees, and every tree when 0, are pruned on all S_x

@@ -10,6 +10,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <thread>
 #include <unordered_map>
@@ -18,6 +19,7 @@
 #include "../../include/linearham_b200.h"
 #include "kernels.hpp"
 #include "plan.hpp"
+#include "pool.hpp"
 
 namespace {
 
@@ -118,6 +120,8 @@ int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, std::v
 
 }  // namespace
 
+constexpr int kChunkEvents = 6;
+
 struct lh_family {
   int device = 0;
   int num_sms = 148;
@@ -127,7 +131,7 @@ struct lh_family {
   // options
   int opt_sites_per_thread = 0, opt_smem_slots = -1, opt_timing = 1, opt_threads = 0;
   size_t opt_chunk_bytes = 48u << 20;
-  int opt_chunk_trees = 0;
+  int opt_chunk_trees = 0, opt_pipe_waves = 4;
   // batch state
   int B = 0, R = 0, slots = 0;
   DevBuf d_plan, d_pblen, d_er, d_pi, d_rates, d_eig, d_prec, d_xe, d_loglik, d_scratch, d_scratch_cnt;
@@ -144,7 +148,7 @@ struct lh_family {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev[8] = {};
   cudaEvent_t user_ev[8] = {};
-  std::vector<cudaEvent_t> chunk_ev;  // 5 per chunk: pmatrix, prune, edge, hmm start; hmm end
+  std::vector<cudaEvent_t> chunk_ev;  // kChunkEvents per chunk: pmatrix, repeats, prune, edge, hmm start; hmm end
   std::vector<cudaEvent_t> staged_ev;  // per chunk: its last segment has landed in HBM
   int n_chunks = 0;
   bool own_stream = true;
@@ -158,12 +162,19 @@ struct lh_family {
   const int32_t* d_col_of_site = nullptr;  // [S] pattern index of each xMSA column
   DevBuf d_ebuf, d_ecnt, d_enaive;
   int opt_site_patterns = 1;
+  // site repeats (k_repeats + k_prune_sr) for the trees that run on site patterns
+  int opt_site_repeats = 0, opt_sr_arena = 0;
+  bool use_sr = false;
+  const uint8_t* d_pat_codes = nullptr;  // [T][U rounded up to 32] pattern codes, row-major
+  DevBuf d_rs_steps, d_rs_idx, d_rs_ecls, d_rs_peak, d_rs_gclv, d_rs_gcnt;
+  lhb::RepeatCfg rc{};
+  int sr_occ = 0;
   // launch configuration of the current batch (configure_batch)
   lhb::BatchDev bd{};
   lhb::PruneCfg pc[2] = {};  // per column set
   lhb::EdgeCfg ec{};
   lhb::HmmOut ho{};
-  int chunk = 0, seg = 0, occ[2] = {0, 0};
+  int chunk = 0, chunk_pipe = 0, wave_pipe = 0, seg = 0, occ[2] = {0, 0};
   // trees that can run on site patterns (naive tip on the root edge or under the virtual root)
   std::vector<uint8_t> on_patterns;
   int n_pattern_trees = 0;
@@ -173,6 +184,8 @@ struct lh_family {
   PinBuf h_list;
   lh_timings_t tm{};
   bool want_tables = false;
+  std::unique_ptr<lhb::WorkerPool> pool;  // planner threads, started on first use
+  std::vector<lhb::PlanScratch> plan_scratch;
 };
 
 extern "C" {
@@ -195,7 +208,8 @@ void lh_family_destroy(lh_family_t* f) {
   DevBuf* bufs[] = {&f->d_plan, &f->d_pblen, &f->d_er, &f->d_pi, &f->d_rates, &f->d_eig, &f->d_prec,
                     &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
                     &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
-                    &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list};
+                    &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_rs_steps,
+                    &f->d_rs_idx, &f->d_rs_ecls, &f->d_rs_peak, &f->d_rs_gclv, &f->d_rs_gcnt};
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
   f->h_misc.release();
@@ -287,6 +301,13 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
     for (int r = 1; r < T; ++r)
       for (int u = 0; u < U; ++u) f->cols[1].codes[(size_t)r * U + u] = d->tip_codes[(size_t)r * S + rep[u]];
     rc |= upload(col_of_site.data(), (size_t)S, &f->d_col_of_site, own);
+    {
+      // row-major copy for k_repeats, rows padded to a multiple of 32 bytes (cp.async chunks)
+      const int up = (U + 31) / 32 * 32;
+      std::vector<uint8_t> padded((size_t)T * up, 4);
+      for (int r = 0; r < T; ++r) std::memcpy(&padded[(size_t)r * up], &f->cols[1].codes[(size_t)r * U], (size_t)U);
+      rc |= upload(padded.data(), padded.size(), &f->d_pat_codes, own);
+    }
   }
   auto region = [&](int n, const int32_t* off, const int32_t* inds, const int32_t** doff,
                     const int32_t** dinds, const char* name) {
@@ -340,15 +361,24 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_sites_per_thread = (int)value;
   } else if (k == "smem_slots") {
     f->opt_smem_slots = (int)value;
+  } else if (k == "site_repeats") {
+    f->opt_site_repeats = value != 0;
+  } else if (k == "sr_arena") {
+    if (value < 0 || value > 4096) return fail("sr_arena must be 0 (auto) or a shared-memory entry count up to 4096");
+    f->opt_sr_arena = (int)value;
   } else if (k == "site_patterns") {
     f->opt_site_patterns = value != 0;
   } else if (k == "timing") {
     f->opt_timing = value != 0;
   } else if (k == "host_threads") {
     f->opt_threads = (int)value;
+    f->pool.reset();
   } else if (k == "chunk_trees") {
     if (value < 0) return fail("chunk_trees must be >= 0 (0 = auto)");
     f->opt_chunk_trees = (int)value;
+  } else if (k == "pipe_waves") {
+    if (value < 1) return fail("pipe_waves must be >= 1");
+    f->opt_pipe_waves = (int)value;
   } else if (k == "chunk_bytes") {
     f->opt_chunk_bytes = (size_t)value;
   } else if (k == "stream") {
@@ -390,37 +420,42 @@ int pick_sites_per_thread(int S, int threads) {
 int plan_range(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, lhb::Step* steps, double* pblen,
                int* max_slots) {
   const int T = f->fd.T, n_ops = T - 2, NB = 2 * T - 3;
-  int nthreads = f->opt_threads > 0 ? f->opt_threads : (int)std::thread::hardware_concurrency();
-  nthreads = std::max(1, std::min(nthreads, std::min(32, (n + 15) / 16)));
-  std::atomic<int> bad(-1);
-  std::vector<int> tmax(nthreads, 0);
-  auto work = [&](int tid) {
-    lhb::PlanScratch sc;
+  if (!f->pool) {
+    int nthreads = f->opt_threads > 0 ? f->opt_threads : (int)std::thread::hardware_concurrency();
+    nthreads = std::max(1, std::min(nthreads, 32));
+    f->pool.reset(new lhb::WorkerPool(nthreads - 1));  // the calling thread works too
+    f->plan_scratch.resize(nthreads);
+  }
+  std::atomic<int> bad(-1), bad_len(-1), deepest(0);
+  constexpr int kBlock = 16;  // trees per task
+  const int n_tasks = (n + kBlock - 1) / kBlock;
+  f->pool->run(n_tasks, [&](int task, int worker) {
+    lhb::PlanScratch& sc = f->plan_scratch[worker];
     int mx = 0;
-    // contiguous blocks per thread: each thread streams its own part of the pinned slot
-    const int lo = (int)((int64_t)n * tid / nthreads), hi = (int)((int64_t)n * (tid + 1) / nthreads);
+    const int lo = task * kBlock, hi = std::min(n, lo + kBlock);
     for (int i = lo; i < hi; ++i) {
       const int t = t0 + i;
-      int s = lhb::plan_tree(T, tb->children + (size_t)t * n_ops * 2, tb->blen + (size_t)t * n_ops * 2,
-                             tb->root_child[t], tb->root_blen[t], steps + (size_t)i * (T - 1),
-                             pblen + (size_t)i * NB, sc);
+      const double* bl = tb->blen + (size_t)t * n_ops * 2;
+      bool neg = !(tb->root_blen[t] >= 0.0);
+      for (int j = 0; j < 2 * n_ops; ++j) neg |= !(bl[j] >= 0.0);
+      if (neg) {
+        bad_len.store(t);
+        return;
+      }
+      int s = lhb::plan_tree(T, tb->children + (size_t)t * n_ops * 2, bl, tb->root_child[t], tb->root_blen[t],
+                             steps + (size_t)i * (T - 1), pblen + (size_t)i * NB, sc);
       if (s < 0) {
         bad.store(t);
         return;
       }
       mx = std::max(mx, s);
     }
-    tmax[tid] = mx;
-  };
-  if (nthreads == 1) {
-    work(0);
-  } else {
-    std::vector<std::thread> th;
-    for (int i = 0; i < nthreads; ++i) th.emplace_back(work, i);
-    for (auto& t : th) t.join();
-  }
+    int cur = deepest.load();
+    while (mx > cur && !deepest.compare_exchange_weak(cur, mx)) {}
+  });
+  if (bad_len.load() >= 0) return fail("tree %d: negative branch length", bad_len.load());
   if (bad.load() >= 0) return fail("tree %d is not a valid post-order operation list", bad.load());
-  *max_slots = std::max(*max_slots, *std::max_element(tmax.begin(), tmax.end()));
+  *max_slots = std::max(*max_slots, deepest.load());
   return 0;
 }
 
@@ -428,13 +463,10 @@ int check_batch(lh_family* f, const lh_tree_batch_t* tb) {
   const int B = tb->n_trees, R = tb->n_rates, NB = 2 * f->fd.T - 3;
   if (B < 0) return fail("negative batch size");
   if (R < 1 || R > LH_MAX_RATES) return fail("n_rates %d outside 1..%d", R, LH_MAX_RATES);
-  for (int t = 0; t < B; ++t) {
+  for (int t = 0; t < B; ++t)
     for (int i = 0; i < 4; ++i)
       if (!(tb->pi[4 * t + i] > 0.0)) return fail("tree %d: pi[%d] must be positive", t, i);
-    for (int i = 0; i < NB - 1; ++i)
-      if (!(tb->blen[(size_t)t * (NB - 1) + i] >= 0.0)) return fail("tree %d: negative branch length", t);
-    if (!(tb->root_blen[t] >= 0.0)) return fail("tree %d: negative branch length", t);
-  }
+  // (branch lengths are checked by the planner threads, tree by tree, as they stream them)
   // A tree can run on site patterns when the naive tip (xMSA row 0) is on the root edge or under
   // the virtual root (the last operation): then no other node's CLV depends on the naive row.
   const int n_ops = f->fd.T - 2;
@@ -541,15 +573,30 @@ int configure_batch(lh_family* f, int B, int R) {
   // chunk the batch: one launch of each kernel per chunk (k_prune: one per column set in use).
   // The chunk is sized on the column set most trees use.
   const int gmain = f->n_pattern_trees * 2 >= B ? 1 : 0;
+  // A wave = the trees whose work items fill the resident CTAs exactly once. CTAs stride over the
+  // items of a launch and items of one family cost the same, so a chunk of whole waves leaves no
+  // partial last wave.
+  auto gcd = [](int a, int b) { while (b) { int r = a % b; a = b; b = r; } return a; };
+  const int resident = f->occ[gmain] * f->num_sms, tiles = f->pc[gmain].n_tiles;
+  const int wave = resident / gcd(resident, tiles);  // smallest tree count with trees*tiles % resident == 0
   int chunk = (int)std::max<size_t>(1, f->opt_chunk_bytes / rec_bytes_tree);
-  // at least 16 waves of work items per launch when the batch allows it, so the partial last
-  // wave costs a few percent. The records then exceed L2 for large trees, which is harmless: they
-  // are written once and read once per site tile by CTAs that run at the same time (the tiles
-  // of a tree are adjacent work items), ~2.6 MB of DRAM traffic per 1001-tip tree.
-  chunk = std::max(chunk, (16 * f->occ[gmain] * f->num_sms + f->pc[gmain].n_tiles - 1) / f->pc[gmain].n_tiles);
-  if (f->opt_chunk_trees > 0) chunk = f->opt_chunk_trees;
+  // A resident batch runs 16 waves per launch (the records then exceed L2 for large trees, which is
+  // harmless: they are written once and read once per site tile by CTAs that run at the same time,
+  // ~2.6 MB of DRAM traffic per 1001-tip tree).
+  const int waves16 = (16 * resident + tiles - 1) / tiles;
+  chunk = std::max(chunk, waves16);
+  if (chunk > wave) chunk -= chunk % wave;
+  // The pipelined call launches every `pipe_waves` waves, so its first kernels start after a
+  // small part of the host planning and the copy of one chunk hides behind the kernels of another.
+  f->wave_pipe = std::max(wave, (resident + tiles - 1) / tiles);
+  int chunk_pipe = std::max(1, f->opt_pipe_waves) * f->wave_pipe;
+  if (f->opt_chunk_trees > 0) {
+    chunk = chunk_pipe = f->opt_chunk_trees;
+    f->wave_pipe = 0;
+  }
   chunk = std::min(chunk, B);
   f->chunk = chunk;
+  f->chunk_pipe = std::min(chunk_pipe, chunk);
   if (f->d_prec.reserve((size_t)chunk * rec_bytes_tree)) return 1;
   bd.prec = f->d_prec.as<double>();
   const int pad_max = std::max(f->pc[0].cols_pad, f->pc[1].cols_pad);
@@ -591,10 +638,62 @@ int configure_batch(lh_family* f, int B, int R) {
   ec.col_of_site = f->d_col_of_site;
   ec.log_threshold = std::log(1.0 / std::pow(2.0, 256));
 
-  // staging segments: ~32 MB of plan + branch lengths per ring slot, never more than a chunk
+  // site repeats for the trees on patterns
+  f->use_sr = false;
+  if (f->opt_site_repeats && use[1]) {
+    const int U = f->cols[1].n_cols, up = (U + 31) / 32 * 32, n_bufs = f->pc[1].total_slots + 1;
+    if (U <= lhb::kRepeatMaxCols && (size_t)n_bufs * up <= 16384 && T - 1 < 65536) {
+      lhb::RepeatCfg& r = f->rc;
+      r = lhb::RepeatCfg{};
+      r.n_cols = U;
+      r.cols_pad = f->pc[1].cols_pad;
+      r.codes = f->d_pat_codes;
+      r.idx_cap = ((int64_t)(T - 1) * U + 127) / 128 * 128;
+      r.idx_ring = lhb::prune_sr_idx_ring(U);
+      r.n_bufs = n_bufs;
+      r.defer_naive = 1;
+      // shared-memory arena: as many entries as leave 4 CTAs per SM, never more than a tree can use
+      int cap = f->opt_sr_arena;
+      if (cap <= 0) cap = (int)(((size_t)227 * 1024 / 4 - 1024 - lhb::prune_sr_smem_bytes(0, r.idx_ring)) / 36);
+      cap = std::min(cap, n_bufs * up);
+      cap -= cap % 32;
+      r.arena_smem = std::max(cap, 64);
+      const int g_half = n_bufs * up;
+      r.arena_total = r.arena_smem + 2 * g_half;
+      f->sr_occ = lhb::prune_sr_max_ctas_per_sm(r.arena_smem, r.idx_ring);
+      if (f->sr_occ < 1) return fail("site-repeat kernel cannot be resident with %d arena entries", r.arena_smem);
+      r.grid = f->sr_occ * f->num_sms;
+      // the class lists are sized for the worst case (every pattern its own class at every node)
+      const size_t idx_bytes_tree = (size_t)r.idx_cap * sizeof(ushort2);
+      const int sr_chunk_max = (int)std::max<size_t>(1, ((size_t)8 << 30) / idx_bytes_tree);
+      if (f->chunk > sr_chunk_max) {
+        f->chunk = sr_chunk_max;
+        f->chunk_pipe = std::min(f->chunk_pipe, f->chunk);
+      }
+      if (f->d_rs_steps.reserve((size_t)f->chunk * (T - 1) * sizeof(int4)) ||
+          f->d_rs_idx.reserve((size_t)f->chunk * idx_bytes_tree + (size_t)r.idx_ring * sizeof(ushort2)) ||  // ring read-ahead
+          
+          f->d_rs_ecls.reserve((size_t)f->chunk * r.cols_pad * sizeof(uint16_t)) ||
+          f->d_rs_peak.reserve((size_t)f->chunk * sizeof(int32_t)) ||
+          f->d_rs_gclv.reserve((size_t)r.grid * 4 * 2 * g_half * sizeof(double)) ||
+          f->d_rs_gcnt.reserve((size_t)r.grid * 2 * g_half * sizeof(int32_t)))
+        return 1;
+      r.steps = f->d_rs_steps.as<int4>();
+      r.idx = f->d_rs_idx.as<ushort2>();
+      r.ecls = f->d_rs_ecls.as<uint16_t>();
+      r.peak = f->d_rs_peak.as<int32_t>();
+      r.g_clv = f->d_rs_gclv.as<double>();
+      r.g_cnt = f->d_rs_gcnt.as<int32_t>();
+      ec.ecls = r.ecls;
+      f->use_sr = true;
+    }
+  }
+
+  // staging segments: up to ~48 MB of plan + branch lengths per ring slot, never more than a
+  // pipelined chunk
   const size_t stage_bytes_tree = (size_t)(T - 1) * sizeof(lhb::Step) + (size_t)NB * sizeof(double);
-  int seg = (int)std::max<size_t>(64, ((size_t)32 << 20) / stage_bytes_tree);
-  f->seg = std::min(seg, chunk);
+  int seg = (int)std::max<size_t>(64, ((size_t)48 << 20) / stage_bytes_tree);
+  f->seg = std::min(seg, f->chunk_pipe);
   for (auto& r : f->h_ring)
     if (r.reserve((size_t)f->seg * stage_bytes_tree)) return 1;
 
@@ -627,6 +726,9 @@ int configure_batch(lh_family* f, int B, int R) {
   f->tm.prune_ctas_per_sm = f->occ[gmain];
   f->tm.prune_columns = pm.n_cols;
   f->tm.pattern_trees = f->n_pattern_trees;
+  f->tm.site_repeats = f->use_sr ? 1 : 0;
+  f->tm.sr_arena = f->use_sr ? f->rc.arena_smem : 0;
+  f->tm.sr_ctas_per_sm = f->use_sr ? f->sr_occ : 0;
   return 0;
 }
 
@@ -670,7 +772,7 @@ int stage_params(lh_family* f, const lh_tree_batch_t* tb, cudaStream_t s) {
 }
 
 int ensure_chunk_events(lh_family* f, int n_chunks) {
-  while ((int)f->chunk_ev.size() < 5 * n_chunks) {
+  while ((int)f->chunk_ev.size() < kChunkEvents * n_chunks) {
     cudaEvent_t e;
     LH_CUDA(cudaEventCreate(&e));
     f->chunk_ev.push_back(e);
@@ -688,28 +790,43 @@ int ensure_chunk_events(lh_family* f, int n_chunks) {
 void launch_chunk(lh_family* f, int ci, int t0, int n) {
   cudaStream_t s = f->stream;
   const bool tm = f->opt_timing;
-  if (tm) cudaEventRecord(f->chunk_ev[5 * ci], s);
+  cudaEvent_t* ev = f->chunk_ev.data() + (size_t)kChunkEvents * ci;
+  if (tm) cudaEventRecord(ev[0], s);
   lhb::launch_eigen(f->bd, t0, n, s);
   lhb::launch_pmatrix(f->fd, f->bd, t0, n, s);
-  if (tm) cudaEventRecord(f->chunk_ev[5 * ci + 1], s);
+  if (tm) cudaEventRecord(ev[1], s);
   // trees on site patterns are listed first in the chunk's part of d_list, the others after
   const int n_pat = f->chunk_n_pat[ci];
   const int count[2] = {n - n_pat, n_pat};
   const int32_t* list[2] = {f->d_list.as<int32_t>() + t0 + n_pat, f->d_list.as<int32_t>() + t0};
+  const bool sr = f->use_sr && count[1] > 0;
+  if (sr) {
+    lhb::RepeatCfg r = f->rc;
+    r.tree_list = list[1];
+    lhb::launch_repeats(f->fd, f->bd, r, t0, count[1], s);
+    f->tm.kernel_launches += 1;
+  }
+  if (tm) cudaEventRecord(ev[2], s);
   for (int g = 1; g >= 0; --g) {
     if (!count[g]) continue;
     lhb::PruneCfg c = f->pc[g];
     c.tree_list = list[g];
-    c.grid = std::min(c.grid, count[g] * c.n_tiles);
-    lhb::launch_prune(f->fd, f->bd, c, t0, count[g], s);
+    if (g == 1 && sr) {
+      lhb::RepeatCfg r = f->rc;
+      r.tree_list = list[1];
+      lhb::launch_prune_sr(f->fd, f->bd, c, r, t0, count[1], s);
+    } else {
+      c.grid = std::min(c.grid, count[g] * c.n_tiles);
+      lhb::launch_prune(f->fd, f->bd, c, t0, count[g], s);
+    }
     f->tm.kernel_launches += 1;
     f->tm.prune_launches += 1;
   }
-  if (tm) cudaEventRecord(f->chunk_ev[5 * ci + 2], s);
+  if (tm) cudaEventRecord(ev[3], s);
   lhb::launch_edge(f->fd, f->bd, f->ec, t0, n, s);
-  if (tm) cudaEventRecord(f->chunk_ev[5 * ci + 3], s);
+  if (tm) cudaEventRecord(ev[4], s);
   lhb::launch_hmm(f->fd, f->bd, f->ho, t0, n, s);
-  if (tm) cudaEventRecord(f->chunk_ev[5 * ci + 4], s);
+  if (tm) cudaEventRecord(ev[5], s);
   f->tm.kernel_launches += 4;
 }
 
@@ -736,18 +853,19 @@ int stage_lists(lh_family* f, std::vector<int> starts, cudaStream_t s) {
   return ensure_chunk_events(f, f->n_chunks);
 }
 
-// Chunk boundaries. A resident batch runs in equal chunks; the pipelined path opens with two
-// short chunks so the first kernels start after a fraction of the host planning.
-std::vector<int> chunk_starts(const lh_family* f, bool ramp) {
+// Chunk boundaries: 16-wave chunks for a resident batch; the pipelined call opens with chunks of
+// one and two waves (the first kernels start after a sliver of the host planning) and goes on in
+// chunks of `pipe_waves` waves.
+std::vector<int> chunk_starts(const lh_family* f, bool pipelined) {
   std::vector<int> st;
   int t0 = 0;
-  if (ramp && f->B > 2 * f->chunk) {
-    const int q = std::max(1, f->chunk / 4);  // opening chunks of chunk/4 and chunk/2 trees
+  if (pipelined && f->wave_pipe > 0 && f->chunk_pipe >= 4 * f->wave_pipe && f->B >= 2 * f->chunk_pipe) {
     st.push_back(0);
-    st.push_back(q);
-    t0 = std::min(f->B, 3 * q);
+    st.push_back(f->wave_pipe);
+    t0 = 3 * f->wave_pipe;
   }
-  for (; t0 < f->B; t0 += f->chunk) st.push_back(t0);
+  const int step = pipelined ? f->chunk_pipe : f->chunk;
+  for (; t0 < f->B; t0 += step) st.push_back(t0);
   st.push_back(f->B);
   return st;
 }
@@ -790,21 +908,17 @@ int lh_batch_run(lh_family_t* f) {
 static int collect_run_timings(lh_family* f) {
   if (!f->opt_timing || f->B == 0 || f->n_chunks == 0) return 0;
   LH_CUDA(cudaEventSynchronize(f->ev[4]));
-  float pm = 0, pr = 0, ed = 0, hm = 0, x = 0;
-  for (int ci = 0; ci < f->n_chunks; ++ci) {
-    cudaEventElapsedTime(&x, f->chunk_ev[5 * ci], f->chunk_ev[5 * ci + 1]);
-    pm += x;
-    cudaEventElapsedTime(&x, f->chunk_ev[5 * ci + 1], f->chunk_ev[5 * ci + 2]);
-    pr += x;
-    cudaEventElapsedTime(&x, f->chunk_ev[5 * ci + 2], f->chunk_ev[5 * ci + 3]);
-    ed += x;
-    cudaEventElapsedTime(&x, f->chunk_ev[5 * ci + 3], f->chunk_ev[5 * ci + 4]);
-    hm += x;
-  }
-  f->tm.ms_pmatrix = pm;
-  f->tm.ms_prune = pr;
-  f->tm.ms_edge = ed;
-  f->tm.ms_hmm = hm;
+  float sum[kChunkEvents - 1] = {}, x = 0;
+  for (int ci = 0; ci < f->n_chunks; ++ci)
+    for (int k = 0; k + 1 < kChunkEvents; ++k) {
+      cudaEventElapsedTime(&x, f->chunk_ev[kChunkEvents * ci + k], f->chunk_ev[kChunkEvents * ci + k + 1]);
+      sum[k] += x;
+    }
+  f->tm.ms_pmatrix = sum[0];
+  f->tm.ms_repeats = sum[1];
+  f->tm.ms_prune = sum[2];
+  f->tm.ms_edge = sum[3];
+  f->tm.ms_hmm = sum[4];
   cudaEventElapsedTime(&f->tm.ms_kernels, f->ev[2], f->ev[4]);
   return 0;
 }
@@ -877,9 +991,12 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   f->want_tables = o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
                          o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers);
   LH_CUDA(cudaSetDevice(f->device));
+  const auto call_t0 = std::chrono::steady_clock::now();
+  auto since = [&]() { return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - call_t0).count(); };
   if (check_batch(f, tb)) return 1;
   if (configure_batch(f, tb->n_trees, tb->n_rates)) return 1;
   if (f->B == 0) return 0;
+  f->tm.ms_setup = since();
   // Pipeline: the host plans one segment of trees at a time into the pinned ring, the copy
   // stream moves it to HBM, and the compute stream starts a chunk's kernels as soon as the
   // chunk's last segment has landed - planning and H2D of chunk c+1 overlap the kernels of c.
@@ -904,7 +1021,9 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
     cudaEventRecord(f->ev[4], f->stream);
   }
   LH_CUDA(cudaGetLastError());
-  return lh_batch_fetch(f, loglik, o);
+  const int rc = lh_batch_fetch(f, loglik, o);
+  f->tm.ms_call = since();
+  return rc;
 }
 
 int lh_measure_fp64_peak(int device, double* tflops) {

@@ -11,6 +11,7 @@ struct Frame {
   int32_t held_slot;  // slot holding the first-evaluated child (phase 1), or -1
   int32_t held_is_a;  // 1 if the held child is child a
   int32_t phase;      // 0 = expand, 1 = emit the node's own step, 2 = occupy one slot
+  int32_t depth;      // edges between the node and the root edge
 };
 }  // namespace
 
@@ -56,23 +57,23 @@ int plan_tree(int T, const int32_t* children, const double* blen, int32_t root_c
   // A parked result occupies its slot only from the moment it is produced: the slot index
   // is the stack depth when the producing subtree starts (its evaluation returns the depth
   // to that level), and the depth is bumped by a marker frame once the subtree is done.
-  const Frame occupy{0, 0, 0, 0, 2};
+  const Frame occupy{0, 0, 0, 0, 2, 0};
 
   const int32_t root_node = T + n_ops - 1;
   Step final_step{kSrcReg, root_child, -1, 0};
   // Frames are pushed in reverse order of execution.
   if (!is_inner(root_child)) {
-    fr.push_back({root_node, -1, -1, 0, 0});
+    fr.push_back({root_node, -1, -1, 0, 0, 0});
   } else if (need[root_child - T] >= need[n_ops - 1]) {
     final_step = {kSrcReg, src_slot(0), -1, 0};
-    fr.push_back({root_node, -1, -1, 0, 0});
+    fr.push_back({root_node, -1, -1, 0, 0, 0});
     fr.push_back(occupy);
-    fr.push_back({root_child, 0, -1, 0, 0});
+    fr.push_back({root_child, 0, -1, 0, 0, 0});
   } else {
     final_step = {src_slot(0), kSrcReg, -1, 0};
-    fr.push_back({root_child, -1, -1, 0, 0});
+    fr.push_back({root_child, -1, -1, 0, 0, 0});
     fr.push_back(occupy);
-    fr.push_back({root_node, 0, -1, 0, 0});
+    fr.push_back({root_node, 0, -1, 0, 0, 0});
   }
 
   while (!fr.empty()) {
@@ -90,19 +91,19 @@ int plan_tree(int T, const int32_t* children, const double* blen, int32_t root_c
       if (ia && ib) {
         const bool a_first = need[a - T] >= need[b - T];
         const int s = depth;
-        fr.push_back({f.node, f.want_slot, s, a_first ? 1 : 0, 1});
-        fr.push_back({a_first ? b : a, -1, -1, 0, 0});  // second: ends in REG
+        fr.push_back({f.node, f.want_slot, s, a_first ? 1 : 0, 1, f.depth});
+        fr.push_back({a_first ? b : a, -1, -1, 0, 0, f.depth + 1});  // second: ends in REG
         fr.push_back(occupy);
-        fr.push_back({a_first ? a : b, s, -1, 0, 0});   // first: parked in slot s
+        fr.push_back({a_first ? a : b, s, -1, 0, 0, f.depth + 1});   // first: parked in slot s
       } else {
-        fr.push_back({f.node, f.want_slot, -1, 0, 1});
-        if (ia) fr.push_back({a, -1, -1, 0, 0});
-        if (ib) fr.push_back({b, -1, -1, 0, 0});
+        fr.push_back({f.node, f.want_slot, -1, 0, 1, f.depth});
+        if (ia) fr.push_back({a, -1, -1, 0, 0, f.depth + 1});
+        if (ib) fr.push_back({b, -1, -1, 0, 0, f.depth + 1});
       }
       continue;
     }
     Step st;
-    st.pad = 0;
+    st.pad = f.depth & 1;  // parity of the node's depth: picks the CLV arena end (k_repeats)
     st.dst = f.want_slot;
     if (ia && ib) {
       st.a = f.held_is_a ? src_slot(f.held_slot) : kSrcReg;

@@ -27,7 +27,7 @@ inline int32_t src_slot(int slot) { return -2 - slot; }
 struct Step {          // 16 bytes, loaded as one int4 by the kernel
   int32_t a, b;        // sources of the two children (for the final step: parent, child)
   int32_t dst;         // slot to copy the result into, or -1
-  int32_t pad;
+  int32_t pad;         // node steps: parity of the node's depth below the root edge
 };
 
 // Plans one tree.
