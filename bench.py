@@ -353,6 +353,8 @@ def main():
         config["prune_columns"] = cols
         config["pattern_trees_rank0"] = int(tm["pattern_trees"])
         config["site_repeats"] = bool(tm["site_repeats"])
+        if tm["site_repeats"]:
+            config["sr_arena_entries"], config["sr_ctas_per_sm"] = int(tm["sr_arena"]), int(tm["sr_ctas_per_sm"])
         prune_s = acc["ms_prune"] * 1e-3
         achieved = bytes_tree * Bs * args.steps / prune_s / 1e9
         fp64_peak = device.fp64_peak_tflops(dev)

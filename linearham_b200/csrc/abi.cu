@@ -652,9 +652,11 @@ int configure_batch(lh_family* f, int B, int R) {
       r.idx_ring = lhb::prune_sr_idx_ring(U);
       r.n_bufs = n_bufs;
       r.defer_naive = 1;
-      // shared-memory arena: as many entries as leave 4 CTAs per SM, never more than a tree can use
+      // shared-memory arena: small by default. Measured on B200 (C4): the kernel is bound by the
+      // latency of its dependent steps, so CTAs per SM matter more than keeping CLV entries out of
+      // L2 (64 entries, 16 CTAs/SM: 49 ms; 512 entries, 7 CTAs/SM: 72 ms; 1280 entries, 4: 99 ms)
       int cap = f->opt_sr_arena;
-      if (cap <= 0) cap = (int)(((size_t)227 * 1024 / 4 - 1024 - lhb::prune_sr_smem_bytes(0, r.idx_ring)) / 36);
+      if (cap <= 0) cap = 64;
       cap = std::min(cap, n_bufs * up);
       cap -= cap % 32;
       r.arena_smem = std::max(cap, 64);

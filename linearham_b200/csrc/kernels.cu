@@ -221,6 +221,9 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 
 #ifndef LH_PRUNE_MIN_CTAS
 #define LH_PRUNE_MIN_CTAS 12
+#define LH_PRUNE_MIN_CTAS3 12
+#define LH_PRUNE_MIN_CTAS2 16
+#define LH_PRUNE_MIN_CTAS1 24
 #endif
 
 constexpr int kRecRing = 4;    // steps of branch records in flight
@@ -364,7 +367,7 @@ size_t prune_smem_bytes(int ns, int smem_slots) {
 }
 
 template <int NS>
-__global__ void __launch_bounds__(32, LH_PRUNE_MIN_CTAS)
+__global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? LH_PRUNE_MIN_CTAS3 : NS == 2 ? LH_PRUNE_MIN_CTAS2 : LH_PRUNE_MIN_CTAS1))
     k_prune(FamilyDev f, BatchDev b, PruneCfg cfg, int tree0, int ntrees) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x, T = f.T, R = b.R;
@@ -793,8 +796,10 @@ size_t prune_sr_smem_bytes(int arena_smem, int idx_ring) {
 }
 
 // message of one child for one class: tip -> column `ci` of the staged Q block; inner -> P * entry
-__device__ __forceinline__ void sr_message(bool tip, const double* rec, const double (&P)[4][4], const Arena& ar,
-                                           int off, unsigned ci, double (&m)[4], int& cnt) {
+// (P is read from the staged record here, per class group, rather than held across the groups of a
+// step: two resident matrices cost 64 registers and four CTAs per SM)
+__device__ __forceinline__ void sr_message(bool tip, const double* rec, const Arena& ar, int off, unsigned ci,
+                                           double (&m)[4], int& cnt) {
   if (tip) {
     const double2 q01 = *reinterpret_cast<const double2*>(rec + ci * 4);
     const double2 q23 = *reinterpret_cast<const double2*>(rec + ci * 4 + 2);
@@ -803,11 +808,23 @@ __device__ __forceinline__ void sr_message(bool tip, const double* rec, const do
   } else {
     double c[4];
     ar.load(off + (int)ci, c, cnt);
-    matvec(P, c, m);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const double2 p01 = *reinterpret_cast<const double2*>(rec + 4 * i);
+      const double2 p23 = *reinterpret_cast<const double2*>(rec + 4 * i + 2);
+      double acc = p01.x * c[0];
+      acc += p01.y * c[1];
+      acc += p23.x * c[2];
+      acc += p23.y * c[3];
+      m[i] = acc;
+    }
   }
 }
 
-__global__ void __launch_bounds__(32) k_prune_sr(FamilyDev f, BatchDev b, PruneCfg cfg, RepeatCfg rc, int tree0, int nlist) {
+#ifndef LH_SR_MIN_CTAS
+#define LH_SR_MIN_CTAS 16
+#endif
+__global__ void __launch_bounds__(32, LH_SR_MIN_CTAS) k_prune_sr(FamilyDev f, BatchDev b, PruneCfg cfg, RepeatCfg rc, int tree0, int nlist) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x, T = f.T, R = b.R;
   const int NB = 2 * T - 3, n_steps = T - 2, n_iter = T - 1;
@@ -886,9 +903,6 @@ __global__ void __launch_bounds__(32) k_prune_sr(FamilyDev f, BatchDev b, PruneC
       const double* recA = ring_rec + (s & (kRecRing - 1)) * (2 * kRecDoubles);
       const double* recB = recA + kRecDoubles;
       if (s < n_steps) {
-        double Pa[4][4], Pb[4][4];
-        if (!a_tip) load_p<1>(recA, Pa);
-        if (!b_tip) load_p<1>(recB, Pb);
         if (a_def | b_def) naive_br = 2 * s + (a_def ? 0 : 1);
         for (int j0 = 0; j0 < n; j0 += 32) {
           const int j = j0 + lane;
@@ -896,8 +910,8 @@ __global__ void __launch_bounds__(32) k_prune_sr(FamilyDev f, BatchDev b, PruneC
             const ushort2 ix = ring_idx[(rs.x + j) & ring_mask];
             double ma[4], mb[4], r[4];
             int ca, cb, cnt;
-            sr_message(a_tip, recA, Pa, ar, a_off, ix.x, ma, ca);
-            sr_message(b_tip, recB, Pb, ar, b_off, ix.y, mb, cb);
+            sr_message(a_tip, recA, ar, a_off, ix.x, ma, ca);
+            sr_message(b_tip, recB, ar, b_off, ix.y, mb, cb);
             if (a_def) {         // the naive tip's factor is applied by k_edge
 #pragma unroll
               for (int i = 0; i < 4; ++i) r[i] = mb[i];
@@ -923,8 +937,6 @@ __global__ void __launch_bounds__(32) k_prune_sr(FamilyDev f, BatchDev b, PruneC
         }
       } else {
         // ---- edge step: a = the root CLV, b = the node across the edge (record in position A) ----
-        double Pb[4][4];
-        if (!b_tip) load_p<1>(recA, Pb);
         if (b_def) naive_br = 2 * n_steps;
         double* eo = cfg.ebuf + (size_t)lt * cfg.e_stride + (size_t)k * 8 * cfg.cols_pad;
         int* co = cfg.ecnt + (size_t)lt * cfg.c_stride + (size_t)k * cfg.cols_pad;
@@ -935,7 +947,7 @@ __global__ void __launch_bounds__(32) k_prune_sr(FamilyDev f, BatchDev b, PruneC
             double rg[4], mc[4];
             int ca, cb;
             ar.load(a_off + ix.x, rg, ca);
-            sr_message(b_tip, recA, Pb, ar, b_off, ix.y, mc, cb);
+            sr_message(b_tip, recA, ar, b_off, ix.y, mc, cb);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               eo[(size_t)i * cfg.cols_pad + j] = mc[i];

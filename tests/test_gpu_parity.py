@@ -186,10 +186,10 @@ def test_pipelined_call_matches_resident_batch():
 
 
 @pytest.mark.parametrize("name", GOLDEN_NAMES)
-@pytest.mark.parametrize("arena", [0, 64])
+@pytest.mark.parametrize("arena", [0, 1024])
 def test_site_repeats_are_bit_identical(name, arena):
     """k_repeats + k_prune_sr (one CLV entry per class of patterns that agree below a node) give the
-    same doubles as pruning every column; arena=64 pushes most CLV entries to the global part."""
+    same doubles as pruning every column; the default arena (64 entries) keeps most CLV entries in the global part, 1024 keeps them in shared memory."""
     fam, tb, exp, _ = load_golden(name)
     a, oa, ta = _score_with(fam, tb, site_repeats=1, sr_arena=arena)
     b, ob, _ = _score_with(fam, tb, site_patterns=0)
