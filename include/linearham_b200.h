@@ -128,6 +128,7 @@ typedef struct lh_timings {
   int64_t h2d_bytes, d2h_bytes;
   int32_t prune_slots;       /* CLV stack depth the batch needed                         */
   int32_t prune_smem_slots;  /* of which held in shared memory                           */
+  int32_t prune_smem_lo;     /* first stack level of the shared-memory window            */
   int32_t prune_tile_sites;  /* xMSA columns per CTA                                     */
   int32_t prune_sites_per_thread;
   int32_t prune_grid, prune_ctas_per_sm;
@@ -167,7 +168,8 @@ int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/scor
 int lh_measure_fp64_peak(int device, double* tflops);
 int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
 /* keys: "sites_per_thread" (0 = auto, 1..4: xMSA columns per thread; a CTA is one warp and
- * covers 32x that many columns), "smem_slots" (-1 = auto), "timing" (0/1), "host_threads",
+ * covers 32x that many columns), "smem_slots" (-1 = auto), "smem_lo" (-1 = auto: first CLV stack level
+ * of the shared-memory window), "timing" (0/1), "host_threads",
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never
  * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "pipe_waves" (default 4:
  * lh_score_batch launches a chunk's kernels every that many waves of CTAs), "stream" (a

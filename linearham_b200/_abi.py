@@ -62,7 +62,7 @@ class Timings(C.Structure):
         ("ms_total", C.c_float), ("ms_kernels", C.c_float),
         ("n_trees", C.c_int32), ("kernel_launches", C.c_int32), ("prune_launches", C.c_int32),
         ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
-        ("prune_slots", C.c_int32), ("prune_smem_slots", C.c_int32), ("prune_tile_sites", C.c_int32),
+        ("prune_slots", C.c_int32), ("prune_smem_slots", C.c_int32), ("prune_smem_lo", C.c_int32), ("prune_tile_sites", C.c_int32),
         ("prune_sites_per_thread", C.c_int32), ("prune_grid", C.c_int32), ("prune_ctas_per_sm", C.c_int32),
         ("prune_columns", C.c_int32), ("pattern_trees", C.c_int32),
         ("ms_call", C.c_float), ("ms_setup", C.c_float), ("ms_repeats", C.c_float),

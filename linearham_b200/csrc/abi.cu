@@ -129,7 +129,8 @@ struct lh_family {
   lhb::FamilyDev fd{};
   std::vector<void*> owned;  // family-constant device allocations
   // options
-  int opt_sites_per_thread = 0, opt_smem_slots = -1, opt_timing = 1, opt_threads = 0;
+  int opt_sites_per_thread = 0, opt_smem_slots = -1, opt_smem_lo = -1, opt_timing = 1, opt_threads = 0;
+  bool window_set = false;  // smem_lo of the batch has been chosen
   size_t opt_chunk_bytes = 48u << 20;
   int opt_chunk_trees = 0, opt_pipe_waves = 4;
   // batch state
@@ -361,6 +362,8 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_sites_per_thread = (int)value;
   } else if (k == "smem_slots") {
     f->opt_smem_slots = (int)value;
+  } else if (k == "smem_lo") {
+    f->opt_smem_lo = (int)value;
   } else if (k == "site_repeats") {
     f->opt_site_repeats = value != 0;
   } else if (k == "sr_arena") {
@@ -491,6 +494,7 @@ int configure_batch(lh_family* f, int B, int R) {
   f->B = B;
   f->R = R;
   f->slots = 0;
+  f->window_set = false;
   f->tm = lh_timings_t{};
   f->tm.n_trees = B;
   if (B == 0) return 0;
@@ -745,6 +749,29 @@ int stage_segment(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, int sl
   double* pblen = reinterpret_cast<double*>(steps + (size_t)n * (T - 1));
   const auto t_a = std::chrono::steady_clock::now();
   if (plan_range(f, tb, t0, n, steps, pblen, &f->slots)) return 1;
+  if (!f->window_set) {
+    // which CLV stack levels live in shared memory: the window of smem_slots consecutive levels
+    // that the first trees of the batch park results in most often
+    int64_t hist[32] = {};
+    const int sample = std::min(n, 64);
+    for (int i = 0; i < sample; ++i)
+      for (int q = 0; q < T - 2; ++q) {
+        const int dst = steps[(size_t)i * (T - 1) + q].dst;
+        if (dst >= 0 && dst < 32) ++hist[dst];
+      }
+    for (auto& pc : f->pc) {
+      int best = 0;
+      int64_t best_sum = -1;
+      for (int lo = 0; lo + pc.smem_slots <= std::max(pc.total_slots, pc.smem_slots); ++lo) {
+        int64_t sum = 0;
+        for (int k = lo; k < lo + pc.smem_slots && k < 32; ++k) sum += hist[k];
+        if (sum > best_sum) { best_sum = sum; best = lo; }
+      }
+      pc.smem_lo = f->opt_smem_lo >= 0 ? std::min(f->opt_smem_lo, std::max(0, pc.total_slots - pc.smem_slots)) : best;
+    }
+    f->tm.prune_smem_lo = f->pc[f->n_pattern_trees * 2 >= f->B ? 1 : 0].smem_lo;
+    f->window_set = true;
+  }
   f->tm.ms_plan += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_a).count();
   const int slot_bound = std::max(f->pc[0].total_slots, f->pc[1].total_slots);
   if (f->slots > slot_bound) return fail("internal: tree needs %d CLV slots, bound is %d", f->slots, slot_bound);

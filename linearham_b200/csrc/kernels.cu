@@ -208,7 +208,7 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 //               byte offset of the Q column), issued one step ahead into registers
 //
 // Inner CLVs never exist as arrays in HBM: the running result stays in registers, results
-// parked for a later step go to a per-column stack whose first `smem_slots` levels are shared
+// parked for a later step go to a per-column stack of which `smem_slots` levels (the busiest) are shared
 // memory ([slot][u][state][lane], conflict-free because a column is only ever touched by its own
 // thread) and whose deeper levels are an L2-resident scratch ring private to the CTA.
 //
@@ -256,14 +256,15 @@ struct SlotIO {
   int* smem_cnt;      // [smem_slots][NS][32]
   double* g_clv;      // [gslots][NS*4][32] (this CTA)
   int* g_cnt;         // [gslots][NS][32]
-  int smem_slots, lane;
+  int smem_slots, smem_lo, lane;  // slots smem_lo .. smem_lo + smem_slots - 1 live in shared memory
 
-  __device__ __forceinline__ bool in_smem(int slot) const { return slot < smem_slots; }
+  __device__ __forceinline__ bool in_smem(int slot) const { return (unsigned)(slot - smem_lo) < (unsigned)smem_slots; }
   __device__ __forceinline__ Slot<NS> shared(int slot) const {
-    return {smem_clv + slot * (4 * NS) * 32 + lane, smem_cnt + slot * NS * 32 + lane};
+    return {smem_clv + (slot - smem_lo) * (4 * NS) * 32 + lane, smem_cnt + (slot - smem_lo) * NS * 32 + lane};
   }
   __device__ __forceinline__ Slot<NS> global(int slot) const {
-    return {g_clv + (size_t)(slot - smem_slots) * (4 * NS) * 32 + lane, g_cnt + (slot - smem_slots) * NS * 32 + lane};
+    const int g = slot < smem_lo ? slot : slot - smem_slots;
+    return {g_clv + (size_t)g * (4 * NS) * 32 + lane, g_cnt + g * NS * 32 + lane};
   }
 };
 
@@ -381,6 +382,7 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * NS) * 32;
   io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * 32;
   io.smem_slots = cfg.smem_slots;
+  io.smem_lo = cfg.smem_lo;
   io.lane = lane;
   // staging roles: lanes 0..19 each copy 16 of the 320 record bytes of a step
   const bool rec_lane = lane < kStepBytes / 16;

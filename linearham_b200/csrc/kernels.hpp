@@ -45,7 +45,8 @@ struct BatchDev {
 struct PruneCfg {
   int32_t sites_per_thread;  // NS; a CTA (one warp) covers 32*NS xMSA columns
   int32_t n_tiles;
-  int32_t smem_slots;    // stack slots kept in shared memory
+  int32_t smem_slots;    // stack slots kept in shared memory ...
+  int32_t smem_lo;       // ... starting with this one (the host picks the busiest window)
   int32_t total_slots;   // stack slots the batch needs
   int32_t grid;          // persistent CTAs
   double* scratch;       // [grid][total_slots-smem_slots][4 NS][32] doubles

@@ -230,3 +230,13 @@ def test_site_repeats_mixed_batch_and_chunks():
     f.close()
     assert 0 < tm["pattern_trees"] < len(a) and tm["site_repeats"] == 1
     assert np.array_equal(a, b) and np.array_equal(a, c)
+
+
+@pytest.mark.parametrize("slots,lo", [(1, 0), (1, 1), (1, 2), (2, 1), (2, 3)])
+def test_shared_memory_slot_window_does_not_change_results(slots, lo):
+    """Which CLV stack levels sit in shared memory (the rest in the L2 scratch) is a placement choice."""
+    fam, tb, exp, _ = load_golden("synth_n40")
+    a, oa, ta = _score_with(fam, tb, smem_slots=slots, smem_lo=lo, site_patterns=0)
+    b, ob, _ = _score_with(fam, tb, site_patterns=0)
+    assert np.array_equal(a, b) and np.array_equal(oa["xmsa_emission"], ob["xmsa_emission"])
+    assert rel_err(a, exp["loglik"]) <= TOL
