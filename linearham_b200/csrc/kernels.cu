@@ -119,76 +119,88 @@ void launch_eigen(const BatchDev& b, int tree0, int ntrees, cudaStream_t s) {
 //   tip child   : Q[code][i] at code*4 + i, code in A,C,G,T,N: the product
 //                 P[k] * tipclv(code) that set_tipclv + the generic kernel would form
 //                 (pll.c:926-930: one-hot for ACGT, all ones for N).
-__global__ void k_pmatrix(FamilyDev f, BatchDev b, int tree0, int ntrees) {
+constexpr int kRecDoublesPm = 20;  // doubles per branch record (kRecDoubles)
+
+__global__ void __launch_bounds__(128) k_pmatrix(FamilyDev f, BatchDev b, int tree0, int ntrees) {
+  // A warp takes 32 consecutive branches of one (tree, category) pass: their records are 5120
+  // contiguous bytes of the stream, written with full 512-byte warp stores after a transpose
+  // through shared memory (a thread storing its own 160-byte record would touch ten half-used sectors).
+  __shared__ double tile[4][32 * 21];  // per warp: 32 records x 20 doubles, pitch 21 (conflict-free)
   const int NB = 2 * f.T - 3, R = b.R;
-  const long long total = (long long)ntrees * NB * R;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int k = (int)(idx % R);
-    const int br = (int)((idx / R) % NB);
-    const int lt = (int)(idx / ((long long)R * NB));
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int groups = (NB + 31) / 32;  // branch groups per pass
+  const long long total = (long long)ntrees * R * groups;
+  double* my = tile[wid];
+  for (long long g = (long long)blockIdx.x * 4 + wid; g < total; g += (long long)gridDim.x * 4) {
+    const int bg = (int)(g % groups);
+    const int k = (int)((g / groups) % R);
+    const int lt = (int)(g / ((long long)groups * R));
     const int t = tree0 + lt;
-    const int step = br >> 1;
-    const int4 st = __ldg(b.plan + (size_t)t * (f.T - 1) + step);
-    const int src = (br & 1) ? st.y : st.x;  // for the final step y is the child side
-    const bool tip = (br == NB - 1) ? (st.y >= 0) : (src >= 0);
-    const double* e = b.eig + (size_t)t * kEigStride;
-    const double len = b.pblen[(size_t)t * NB + br];
-    const double rate = b.rates[(size_t)t * R + k];
-    double P[4][4];
-    if (len == 0.0) {  // core_pmatrix.c:174-179
+    const int br = bg * 32 + lane;
+    __syncwarp();
+    if (br < NB) {
+      const int step = br >> 1;
+      const int4 st = __ldg(b.plan + (size_t)t * (f.T - 1) + step);
+      const int src = (br & 1) ? st.y : st.x;  // for the final step y is the child side
+      const bool tip = (br == NB - 1) ? (st.y >= 0) : (src >= 0);
+      const double* e = b.eig + (size_t)t * kEigStride;
+      const double len = b.pblen[(size_t)t * NB + br];
+      const double rate = b.rates[(size_t)t * R + k];
+      double P[4][4];
+      if (len == 0.0) {  // core_pmatrix.c:174-179
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
+        for (int j = 0; j < 4; ++j)
 #pragma unroll
-        for (int c = 0; c < 4; ++c) P[j][c] = (j == c) ? 1.0 : 0.0;
-    } else {
-      double expd[4];
+          for (int c = 0; c < 4; ++c) P[j][c] = (j == c) ? 1.0 : 0.0;
+      } else {
+        double expd[4];
 #pragma unroll
-      for (int m = 0; m < 4; ++m) expd[m] = expm1(e[m] * rate * len);
+        for (int m = 0; m < 4; ++m) expd[m] = expm1(e[m] * rate * len);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        double tmp[4];
+        for (int j = 0; j < 4; ++j) {
+          double tmp[4];
 #pragma unroll
-        for (int m = 0; m < 4; ++m) tmp[m] = e[20 + j * 4 + m] * expd[m];
+          for (int m = 0; m < 4; ++m) tmp[m] = e[20 + j * 4 + m] * expd[m];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          double acc = (j == c) ? 1.0 : 0.0;
+          for (int c = 0; c < 4; ++c) {
+            double acc = (j == c) ? 1.0 : 0.0;
 #pragma unroll
-          for (int m = 0; m < 4; ++m) acc += tmp[m] * e[4 + m * 4 + c];
-          P[j][c] = acc;
+            for (int m = 0; m < 4; ++m) acc += tmp[m] * e[4 + m * 4 + c];
+            P[j][c] = acc;
+          }
         }
       }
-    }
-    double* rec = b.prec + (((size_t)lt * R + k) * NB + br) * 20;
-    if (!tip) {
-      double2* o = reinterpret_cast<double2*>(rec);
+      double* o = my + lane * 21;
+      if (!tip) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        o[2 * j] = make_double2(P[j][0], P[j][1]);
-        o[2 * j + 1] = make_double2(P[j][2], P[j][3]);
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) o[j * 4 + c] = P[j][c];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) o[16 + c] = 0.0;
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) o[c * 4 + j] = P[j][c];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o[16 + i] = ((P[i][0] + P[i][1]) + P[i][2]) + P[i][3];
       }
-    } else {
-      double2* o = reinterpret_cast<double2*>(rec);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        o[2 * c] = make_double2(P[0][c], P[1][c]);
-        o[2 * c + 1] = make_double2(P[2][c], P[3][c]);
-      }
-      double sN[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) sN[i] = ((P[i][0] + P[i][1]) + P[i][2]) + P[i][3];
-      o[8] = make_double2(sN[0], sN[1]);
-      o[9] = make_double2(sN[2], sN[3]);
     }
+    __syncwarp();
+    // the group's records are contiguous: doubles [first, first + n*20) of the pass stream
+    const int n_rec = min(32, NB - bg * 32);
+    double* dst = b.prec + (((size_t)lt * R + k) * NB + (size_t)bg * 32) * kRecDoublesPm;
+    for (int i = lane; i < n_rec * kRecDoublesPm; i += 32) dst[i] = my[(i / kRecDoublesPm) * 21 + (i % kRecDoublesPm)];
   }
 }
 
 void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees, cudaStream_t s) {
-  long long total = (long long)ntrees * (2 * f.T - 3) * b.R;
-  int threads = 256;
-  long long blocks = (total + threads - 1) / threads;
+  const int groups = (2 * f.T - 3 + 31) / 32;
+  long long total = (long long)ntrees * b.R * groups;  // warps of work
+  long long blocks = (total + 3) / 4;
   if (blocks > 148LL * 64) blocks = 148LL * 64;
-  k_pmatrix<<<(unsigned)blocks, threads, 0, s>>>(f, b, tree0, ntrees);
+  k_pmatrix<<<(unsigned)blocks, 128, 0, s>>>(f, b, tree0, ntrees);
 }
 
 // ------------------------------------------------------------------ k_prune ---
