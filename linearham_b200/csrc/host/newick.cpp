@@ -16,11 +16,11 @@
 // Tip labels are mapped to xMSA rows through the label list of the family (xmsa_labels_,
 // src/PhyloHMM.cpp:48-53; Partition::SetTipStates matches by label, pll_partition.cpp:153-194).
 #include <atomic>
+#include <charconv>
 #include <cstdlib>
 #include <cstring>
 #include <string>
 #include <thread>
-#include <unordered_map>
 #include <vector>
 
 #include "../../../include/linearham_b200_host.h"
@@ -37,34 +37,89 @@ struct Open {        // one unclosed '('
   double len[3];
 };
 
+// Tip label -> xMSA row: open addressing on the FNV-1a hash the scanner computes while it walks
+// the label, so a lookup builds no std::string.
 struct LabelMap {
-  std::unordered_map<std::string, int32_t> rows;
+  struct Slot {
+    const char* s = nullptr;
+    uint32_t len = 0, hash = 0;
+    int32_t row = -1;
+  };
+  std::vector<Slot> slots;
+  uint32_t mask = 0;
+  static uint32_t hash_of(const char* s, size_t n) {
+    uint32_t h = 2166136261u;
+    for (size_t i = 0; i < n; ++i) h = (h ^ (unsigned char)s[i]) * 16777619u;
+    return h;
+  }
+  void init(int n) {
+    size_t cap = 8;
+    while (cap < (size_t)n * 2) cap <<= 1;
+    slots.assign(cap, Slot{});
+    mask = (uint32_t)cap - 1;
+  }
+  bool insert(const char* s, int32_t row) {  // false: duplicate
+    const uint32_t len = (uint32_t)std::strlen(s), h = hash_of(s, len);
+    for (uint32_t i = h & mask;; i = (i + 1) & mask) {
+      Slot& e = slots[i];
+      if (e.row < 0) {
+        e = Slot{s, len, h, row};
+        return true;
+      }
+      if (e.hash == h && e.len == len && std::memcmp(e.s, s, len) == 0) return false;
+    }
+  }
+  int32_t find(const char* s, uint32_t len, uint32_t h) const {
+    for (uint32_t i = h & mask;; i = (i + 1) & mask) {
+      const Slot& e = slots[i];
+      if (e.row < 0) return -1;
+      if (e.hash == h && e.len == len && std::memcmp(e.s, s, len) == 0) return e.row;
+    }
+  }
 };
 
-inline bool is_delim(char c) {
-  return c == '(' || c == ')' || c == ',' || c == ':' || c == ';' || c == '[' || c == ' ' || c == '\t' ||
-         c == '\n' || c == '\r' || c == '\0';
-}
+// delimiter table: ( ) , : ; [ blank tab newline cr nul
+struct DelimTable {
+  bool t[256] = {};
+  constexpr DelimTable() {
+    for (unsigned char c : {'(', ')', ',', ':', ';', '[', ' ', '\t', '\n', '\r', '\0'}) t[c] = true;
+  }
+};
+constexpr DelimTable kDelim{};
+inline bool is_delim(char c) { return kDelim.t[(unsigned char)c]; }
 
 // skips blanks and [...] comments (the reference strips "[&index=N]" with a regex)
 inline const char* skip(const char* p) {
   for (;;) {
     while (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r') ++p;
     if (*p != '[') return p;
-    while (*p && *p != ']') ++p;
-    if (*p == ']') ++p;
+    const char* e = std::strchr(p, ']');
+    if (!e) return p + std::strlen(p);
+    p = e + 1;
   }
+}
+
+// Decimal -> double. std::from_chars (libstdc++: Eisel-Lemire with an exact fallback) returns the
+// correctly rounded double, as strtod / atof (the reference's lexer path, parse_utree.y) does, at a
+// fraction of the cost; forms it does not take (leading '+', hex, locale) go to strtod.
+inline const char* parse_double(const char* p, double* out) {
+  if ((*p >= '0' && *p <= '9') || *p == '-' || *p == '.') {
+    const char* e = p;
+    while (!is_delim(*e)) ++e;
+    const auto r = std::from_chars(p, e, *out);
+    if (r.ec == std::errc() && r.ptr == e) return e;
+  }
+  char* end = nullptr;
+  *out = std::strtod(p, &end);
+  return end == p ? nullptr : end;
 }
 
 inline const char* branch_length(const char* p, double* len) {
   p = skip(p);
   double v = 0.0;
   if (*p == ':') {
-    p = skip(p + 1);
-    char* end = nullptr;
-    v = std::strtod(p, &end);
-    if (end == p) return nullptr;
-    p = end;
+    p = parse_double(skip(p + 1), &v);
+    if (!p) return nullptr;
   }
   *len = v ? v : kEps;
   return p;
@@ -134,25 +189,25 @@ const char* flatten_one(const char* s, const LabelMap& labels, int T, std::vecto
       return "unexpected end of tree";
     } else {
       const char* b = p;
-      while (!is_delim(*p)) ++p;
+      uint32_t h = 2166136261u;
+      for (; !is_delim(*p); ++p) h = (h ^ (unsigned char)*p) * 16777619u;
       if (stack.empty()) return "tip outside parentheses";
-      std::string name(b, p - b);
-      auto it = labels.rows.find(name);
-      if (it == labels.rows.end()) {
-        detail = name;
+      const int32_t row = labels.find(b, (uint32_t)(p - b), h);
+      if (row < 0) {
+        detail.assign(b, p - b);
         return "tip label is not a sequence of this family";
       }
-      if (seen[it->second]) {
-        detail = name;
+      if (seen[row]) {
+        detail.assign(b, p - b);
         return "tip label appears twice";
       }
-      seen[it->second] = 1;
+      seen[row] = 1;
       double len;
       p = branch_length(p, &len);
       if (!p) return "malformed branch length";
       Open& up = stack.back();
       if (up.n >= 3) return "node with more than three children";
-      up.id[up.n] = it->second;
+      up.id[up.n] = row;
       up.len[up.n] = len;
       ++up.n;
     }
@@ -171,8 +226,9 @@ extern "C" int lhh_newick_to_ops(int32_t n_tips, const char* const* labels, int3
   using namespace lhb;
   if (n_tips < 3) return host_fail("need at least 3 tips (got %d)", n_tips);
   LabelMap map;
+  map.init(n_tips);
   for (int i = 0; i < n_tips; ++i)
-    if (!map.rows.emplace(labels[i], i).second) return host_fail("duplicate label '%s'", labels[i]);
+    if (!map.insert(labels[i], i)) return host_fail("duplicate label '%s'", labels[i]);
   const size_t per = (size_t)(n_tips - 2) * 2;
   int nt = n_threads > 0 ? n_threads : (int)std::thread::hardware_concurrency();
   nt = std::max(1, std::min(nt, std::min(64, (n_trees + 63) / 64)));

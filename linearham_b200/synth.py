@@ -108,23 +108,27 @@ def write_gene_yaml(path, gname, seq, gtype, gene_prob, rng):
         f.write("\n".join(lines))
 
 
-def make_germline_set(outdir, seed=7, n_v=3, n_d=5, n_j=2, v_len=296, j_len=63):
-    """Writes the parameter dir; returns {display name: (type, sequence)} with '*' names."""
+def make_germline_set(outdir, seed=7, n_v=3, n_d=5, n_j=2, v_len=296, j_len=63, locus="igh"):
+    """Writes the parameter dir; returns {display name: (type, sequence)} with '*' names.
+    locus "igk" / "igl": light chain, no D genes (src/HMM.cpp:125-170)."""
+    pre = {"igh": "IGH", "igk": "IGK", "igl": "IGL"}[locus]
+    if locus != "igh":
+        n_d = 0
     rng = np.random.default_rng(seed)
     os.makedirs(outdir, exist_ok=True)
     genes = {}
     v0 = _rand_seq(rng, v_len)
     j0 = _rand_seq(rng, j_len)
-    gp = {"V": rng.dirichlet(np.ones(n_v) * 5), "D": rng.dirichlet(np.ones(n_d) * 5),
+    gp = {"V": rng.dirichlet(np.ones(n_v) * 5), "D": rng.dirichlet(np.ones(max(n_d, 1)) * 5),
           "J": rng.dirichlet(np.ones(n_j) * 5)}
     for i in range(n_v):
         seq = v0 if i == 0 else _mutate_seq(rng, v0, 6)[int(rng.integers(0, 4)):]
-        genes[f"IGHV{i + 1}-1*01"] = ("V", seq, gp["V"][i])
+        genes[f"{pre}V{i + 1}-1*01"] = ("V", seq, gp["V"][i])
     for i in range(n_d):
-        genes[f"IGHD{i + 1}-1*01"] = ("D", _rand_seq(rng, int(rng.integers(17, 32))), gp["D"][i])
+        genes[f"{pre}D{i + 1}-1*01"] = ("D", _rand_seq(rng, int(rng.integers(17, 32))), gp["D"][i])
     for i in range(n_j):
         seq = j0 if i == 0 else _mutate_seq(rng, j0, 4)[int(rng.integers(0, 6)):]
-        genes[f"IGHJ{i + 1}*01"] = ("J", seq, gp["J"][i])
+        genes[f"{pre}J{i + 1}*01"] = ("J", seq, gp["J"][i])
     for name, (t, seq, p) in genes.items():
         fname = name.replace("*", "_star_").replace("/", "_slash_")
         write_gene_yaml(os.path.join(outdir, fname + ".yaml"), fname, seq, t, p, rng)
@@ -298,6 +302,43 @@ def write_tsv(path, samples):
 
 
 # ------------------------------------------------------------------------------ families ---
+
+def make_light_family(outdir, genes, n_leaves, seed, L=400, name="family", locus="igk"):
+    """Light-chain family (V-J, one junction): naive = lead Ns + V + 8 inserted bases + J + Ns."""
+    rng = np.random.default_rng(seed)
+    vs = [g for g, (t, _) in genes.items() if t == "V"]
+    js = [g for g, (t, _) in genes.items() if t == "J"]
+    V0, J0 = genes[vs[0]][1], genes[js[0]][1]
+    lead = 15
+    naive = "N" * lead + V0[:len(V0) - 6]
+    vend = len(naive)
+    naive += _rand_seq(rng, 8)
+    jstart = len(naive)
+    naive += J0[4:]
+    jend = len(naive)
+    assert jend <= L, (jend, L)
+    naive += "N" * (L - jend)
+    flex = {"v_l": [0, lead], "v_r": [vend - 20, vend - 10], "j_l": [jstart + 4, jstart + 14], "j_r": [jend, L]}
+    relpos = {vs[0]: lead, js[0]: jstart - 4}
+    for v in vs[1:]:
+        relpos[v] = lead + len(V0) - len(genes[v][1])
+    for j in js[1:]:
+        relpos[j] = (jstart - 4) + len(J0) - len(genes[j][1])
+    tree = random_tree(rng, n_leaves)
+    seqs = evolve(rng, tree, naive)
+    ids = [str(i) for i in range(n_leaves)]
+    import json
+    doc = {"germline-info": {"locus": locus},
+           "events": [{"unique_ids": ids, "naive_seq": naive, "input_seqs": [seqs[i] for i in ids],
+                       "has_shm_indels": [False] * n_leaves,
+                       "linearham-info": {"flexbounds": flex, "relpos": relpos}}]}
+    os.makedirs(outdir, exist_ok=True)
+    path = os.path.join(outdir, name + ".yaml")
+    with open(path, "w") as f:
+        json.dump(doc, f)
+    return {"yaml_path": path, "tree": tree, "labels": ["naive"] + ids, "naive": naive,
+            "flexbounds": flex, "relpos": relpos}
+
 
 def make_family(outdir, genes, n_leaves, seed, L=400, name="family"):
     """Writes <outdir>/<name>.yaml; returns dict(yaml_path, tree, labels, naive)."""

@@ -95,6 +95,17 @@ def main():
             fam = synth.make_family(d, genes, n, seed=seed, name=name)
             samples = synth.tree_samples(np.random.default_rng(seed + 1000), fam["tree"], B, walk="cumulative")
             bundle(name, fam["yaml_path"], os.path.join(d, "hmm"), samples, R)
+    make_light()
+
+
+def make_light():
+    """Light-chain family (igk: V-J, no D region; src/HMM.cpp:125-170, src/PhyloHMM.cpp:76,106) -
+    the reference's own tests hold no light-chain fixture."""
+    with tempfile.TemporaryDirectory() as d:
+        genes = synth.make_germline_set(os.path.join(d, "hmmk"), seed=9, locus="igk")
+        fam = synth.make_light_family(d, genes, 30, seed=1305, name="synth_igk_n30")
+        samples = synth.tree_samples(np.random.default_rng(2305), fam["tree"], 4, outgroup="naive")
+        bundle("synth_igk_n30", fam["yaml_path"], os.path.join(d, "hmmk"), samples, 4)
 
 
 if __name__ == "__main__":

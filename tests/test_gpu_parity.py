@@ -240,3 +240,20 @@ def test_shared_memory_slot_window_does_not_change_results(slots, lo):
     b, ob, _ = _score_with(fam, tb, site_patterns=0)
     assert np.array_equal(a, b) and np.array_equal(oa["xmsa_emission"], ob["xmsa_emission"])
     assert rel_err(a, exp["loglik"]) <= TOL
+
+
+@pytest.mark.parametrize("n_rates", [1, 2, 3, 8])
+def test_rate_category_counts_match_the_port(n_rates):
+    """1..LH_MAX_RATES discrete-Gamma categories (the goldens hold R = 1 and 4)."""
+    from linearham_b200 import host
+    fam, tb, _, meta = load_golden("synth_n40")
+    tb = dict(tb)
+    tb["rates"] = host.gamma_cats(meta["alpha"], n_rates)
+    pll, pout = po.port_score_batch(fam, tb)
+    for sp in (1, 0):
+        ll, out, _ = _score_with(fam, tb, site_patterns=sp)
+        assert rel_err(ll, pll) <= TOL and rel_err(out["xmsa_emission"], pout["xmsa_emission"]) <= TOL
+    with pytest.raises(device.DeviceError):
+        bad = dict(tb)
+        bad["rates"] = np.ones((len(tb["root_child"]), 9))
+        device.Family(fam).score(bad)

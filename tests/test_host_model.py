@@ -118,3 +118,32 @@ def test_export_newick_format():
     # pll_utree_export_newick: %f lengths, EPS for missing/zero, ":0.0;" at the root (utree.c:148-270)
     assert host.export_newick("((0:0.03,1)x[&index=5]:0.0,naive:0.3,2[&index=1]);") == \
         "((0:0.030000,1:0.000001)x:0.000001,naive:0.300000,2:0.000001):0.0;"
+
+
+@pytest.mark.skipif(not have_ref_data, reason="needs /root/reference and oracle/_ref")
+@pytest.mark.parametrize("locus,n_leaves,seed", [("igk", 9, 41), ("igl", 30, 42)])
+def test_light_chain_families_member_by_member(locus, n_leaves, seed):
+    """V-J loci have one junction and no D region (src/HMM.cpp:125-170, src/PhyloHMM.cpp:76,106); the
+    reference's own tests hold no light-chain fixture, so the compiled reference is the oracle here."""
+    from linearham_b200 import synth
+    with tempfile.TemporaryDirectory() as d:
+        genes = synth.make_germline_set(os.path.join(d, "hmm"), seed=9, locus=locus)
+        ff = synth.make_light_family(d, genes, n_leaves, seed=seed, locus=locus)
+        ref = po.RefPhyloHMM(ff["yaml_path"], 0, os.path.join(d, "hmm"), 0)
+        h = host.PhyloHMM(ff["yaml_path"], 0, os.path.join(d, "hmm"), 0)
+        assert h.strs("locus") == [locus]
+        skip = ("dgerm", "dj_junction")
+        for f in I32_FIELDS:
+            if not f.startswith(skip):
+                assert same(h.i32(f), ref.i32(f)), f
+        for f in F64_FIELDS:
+            if not f.startswith(skip) and "dgerm" not in f:
+                assert same(h.f64(f), ref.f64(f)), f
+        for f in STR_FIELDS:
+            if not f.startswith(skip):
+                assert h.strs(f) == ref.strs(f), f
+        fam, rfam = h.family(), ref.family()
+        assert fam["has_d"] == 0 and rfam["has_d"] == 0
+        for k in ("tip_codes", "vpad_inds", "vgerm_inds", "jgerm_inds", "jpad_inds", "vd_inds", "v_gene_prob", "v_trans_prod",
+                  "vpad_trans", "jpad_trans", "t_v_vd", "t_vd", "t_vd_d"):
+            assert np.array_equal(np.asarray(fam[k]).reshape(-1), np.asarray(rfam[k]).reshape(-1)), k
