@@ -170,6 +170,8 @@ def main():
     ap.add_argument("--topologies", type=int, default=256, help="distinct tree topologies in the batch")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-newick", action="store_true", help="skip the Newick-string class-API measurement")
+    ap.add_argument("--newick-trees", type=int, default=4096, help="tree samples per step of e2e_newick")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE",
                     help="lh_set_option on the family (e.g. pipe_waves=4); recorded in config")
     args = ap.parse_args()
@@ -190,7 +192,7 @@ def main():
     ff = workload.write_family_files(cfg, workdir)
     # per-family host work of the product: partis YAML + HMM parameter dir -> state space, transition
     # matrices, xMSA (C++ linearham::PhyloHMM of this repo; bit-exact vs the reference, tests/test_host_model.py)
-    phmm = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+    phmm = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0, device=local_rank if world > 1 else 0)
     fam, labels = phmm.family(), phmm.strs("xmsa_labels")
     if labels != ff["labels"]:
         raise RuntimeError("xMSA labels do not match the generated family")
@@ -327,14 +329,34 @@ def main():
         sync_all()
         e2e_s = time.perf_counter() - t0
         assert np.array_equal(ll_e2e, ll_dev, equal_nan=True)
+    # -------- e2e from Newick strings: the class API a linearham user calls -------------
+    # PhyloHMM::ScoreSamples(newick strings, er, pi, alpha) -> log-likelihoods: Newick ingest on the host
+    # threads overlapped with lh_score_batch of the previous chunk. The strings are marshalled to a C array
+    # once, outside the timed region (a C++ caller holds them as char* already).
+    nw_s, nw_n = None, 0
+    if not args.no_e2e and not args.no_newick:
+        nw_n = min(Bs, args.newick_trees)
+        nt = len(newicks)
+        arr = host.encode_newicks([newicks[(lo + i) % nt] for i in range(nw_n)])
+        er_n, pi_n, al_n = shard["er"][:nw_n], shard["pi"][:nw_n], alpha[lo:lo + nw_n]
+        ll_nw = phmm.ScoreSamples(arr, er_n, pi_n, al_n, R)
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            ll_nw = phmm.ScoreSamples(arr, er_n, pi_n, al_n, R)
+        sync_all()
+        nw_s = time.perf_counter() - t0
+        k = max(0, min(nw_n, nt - lo))  # samples whose branch lengths are the strings' own
+        assert np.array_equal(ll_nw[:k], ll_dev[:k], equal_nan=True)
     clocks = sampler.stop()
 
     # -------- max over ranks ------------------------------------------------------
     if dist is not None:
-        t = torch.tensor([ms_kernels, e2e_s or 0.0, acc["ms_prune"]], dtype=torch.float64, device=f"cuda:{dev}")
+        t = torch.tensor([ms_kernels, e2e_s or 0.0, acc["ms_prune"], nw_s or 0.0], dtype=torch.float64, device=f"cuda:{dev}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_kernels, e2e_max, _ = t.tolist()
+        ms_kernels, e2e_max, _, nw_max = t.tolist()
         e2e_s = e2e_max if e2e_s is not None else None
+        nw_s = nw_max if nw_s is not None else None
         full = gathered[:B_total].cpu().numpy() if gathered is not None else ll_dev
         lt = torch.tensor([acc["kernel_launches"]], dtype=torch.float64, device=f"cuda:{dev}")
         dist.all_reduce(lt, op=dist.ReduceOp.SUM)
@@ -393,6 +415,11 @@ def main():
                                                "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
                                                "host_plan_ms_per_step_rank0": ms_plan, "last_call_ms_rank0": e2e_detail,
                                                "api": "lh_score_batch (host arrays in, host log-likelihoods out)"},
+            "e2e_newick": None if nw_s is None else {
+                "value": nw_n * world * args.steps / nw_s, "unit": UNIT, "trees_per_step": nw_n * world,
+                "host_threads": cores,
+                "api": "PhyloHMM::ScoreSamples (Newick strings + er/pi/alpha in, log-likelihoods out; "
+                       "Newick ingest on host threads overlapped with lh_score_batch)"},
             "gpu_launches": launches_total, "clocks": clocks, "parity": parity,
             "finite_fraction": float(np.mean(np.isfinite(full))),
         }

@@ -127,10 +127,7 @@ int lhh_phylohmm_run_pipeline(lhh_phylohmm_t* h, const char* input_path, const c
 int lhh_phylohmm_score_samples(lhh_phylohmm_t* h, int32_t n, const char* const* newicks, const double* er, const double* pi,
                                const double* alpha, int32_t num_rates, double* loglik) {
   return guarded([&] {
-    std::vector<std::string> nw(newicks, newicks + n);
-    std::vector<double> ll = H(h).ScoreSamples(nw, std::vector<double>(er, er + 6 * (size_t)n), std::vector<double>(pi, pi + 4 * (size_t)n),
-                                               std::vector<double>(alpha, alpha + n), num_rates);
-    std::copy(ll.begin(), ll.end(), loglik);
+    H(h).ScoreSamples(n, newicks, er, pi, alpha, num_rates, loglik);
   });
 }
 

@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <future>
 #include <sstream>
 #include <stdexcept>
 
@@ -358,21 +359,55 @@ double PhyloHMM::LogLikelihood() {
 
 std::vector<double> PhyloHMM::ScoreSamples(const std::vector<std::string>& newicks, const std::vector<double>& er,
                                            const std::vector<double>& pi, const std::vector<double>& alpha, int num_rates) {
-  EnsureDeviceFamily();
-  const int B = (int)newicks.size(), T = xmsa_.rows();
+  const int B = (int)newicks.size();
   if ((int)er.size() != 6 * B || (int)pi.size() != 4 * B || (int)alpha.size() != B)
     throw std::invalid_argument("ScoreSamples: er / pi / alpha do not match the number of trees");
   std::vector<const char*> nw(B);
   for (int b = 0; b < B; ++b) nw[b] = newicks[b].c_str();
-  std::vector<int32_t> children((std::size_t)B * 2 * (T - 2)), root_child(B);
-  std::vector<double> blen((std::size_t)B * 2 * (T - 2)), root_blen(B), rates((std::size_t)B * num_rates), ll(B);
-  if (B == 0) return ll;
-  if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), B, nw.data(), 0, children.data(), blen.data(), root_child.data(), root_blen.data()))
-    throw std::invalid_argument(lhh_last_error());
-  if (lhh_gamma_cats_batch(B, alpha.data(), num_rates, rates.data())) throw std::invalid_argument(lhh_last_error());
-  lh_tree_batch_t tb{B, num_rates, children.data(), blen.data(), root_child.data(), root_blen.data(), er.data(), pi.data(), rates.data()};
-  if (lh_score_batch(dev_family_, &tb, ll.data(), nullptr)) throw std::runtime_error(lh_last_error());
+  std::vector<double> ll(B);
+  ScoreSamples(B, nw.data(), er.data(), pi.data(), alpha.data(), num_rates, ll.data());
   return ll;
+}
+
+// Newick ingest (host threads) of one chunk of samples overlaps the scoring of the previous chunk
+// (lh_score_batch: planner threads, copies, kernels).
+void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er, const double* pi, const double* alpha,
+                            int num_rates, double* loglik) {
+  EnsureDeviceFamily();
+  if (B <= 0) return;
+  const int T = xmsa_.rows();
+  const std::size_t per = (std::size_t)2 * (T - 2);
+  constexpr int kChunk = 2048;
+  struct Flat {
+    std::vector<int32_t> children, root_child;
+    std::vector<double> blen, root_blen, rates;
+  } flat[2];
+  auto ingest = [&](int b0, int n, Flat& f) -> std::string {
+    f.children.resize(n * per);
+    f.blen.resize(n * per);
+    f.root_child.resize(n);
+    f.root_blen.resize(n);
+    f.rates.resize((std::size_t)n * num_rates);
+    if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), n, newicks + b0, 0, f.children.data(), f.blen.data(),
+                          f.root_child.data(), f.root_blen.data()))
+      return lhh_last_error();
+    if (lhh_gamma_cats_batch(n, alpha + b0, num_rates, f.rates.data())) return lhh_last_error();
+    return std::string();
+  };
+  std::string err = ingest(0, std::min(kChunk, B), flat[0]);
+  if (!err.empty()) throw std::invalid_argument(err);
+  for (int b0 = 0, c = 0; b0 < B; b0 += kChunk, ++c) {
+    const int n = std::min(kChunk, B - b0), b1 = b0 + kChunk;
+    std::future<std::string> next;
+    if (b1 < B) next = std::async(std::launch::async, ingest, b1, std::min(kChunk, B - b1), std::ref(flat[(c + 1) & 1]));
+    Flat& f = flat[c & 1];
+    lh_tree_batch_t tb{n, num_rates, f.children.data(), f.blen.data(), f.root_child.data(), f.root_blen.data(),
+                       er + (std::size_t)6 * b0, pi + (std::size_t)4 * b0, f.rates.data()};
+    const int rc = lh_score_batch(dev_family_, &tb, loglik + b0, nullptr);
+    if (next.valid()) err = next.get();
+    if (rc) throw std::runtime_error(lh_last_error());
+    if (!err.empty()) throw std::invalid_argument(err);
+  }
 }
 
 // src/PhyloHMM.cpp:244-282

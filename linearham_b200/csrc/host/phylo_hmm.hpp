@@ -173,6 +173,9 @@ class PhyloHMM : public HMM {
   // current-sample state: log-likelihood of every (newick, er, pi, alpha) sample.
   std::vector<double> ScoreSamples(const std::vector<std::string>& newicks, const std::vector<double>& er,
                                    const std::vector<double>& pi, const std::vector<double>& alpha, int num_rates);
+  // pointer form: nothing is copied; Newick ingest of one chunk overlaps the scoring of the previous one
+  void ScoreSamples(int n, const char* const* newicks, const double* er, const double* pi, const double* alpha,
+                    int num_rates, double* loglik);
 
   void set_device(int device) { device_ = device; }
 

@@ -34,6 +34,11 @@ def gamma_cats(alpha, n_rates):
     return out[0] if np.ndim(alpha) == 0 else out
 
 
+def encode_newicks(newicks):
+    """list of str -> (c_char_p * n) array for the C ABI (keeps the encoded bytes alive)"""
+    return (C.c_char_p * len(newicks))(*[s if isinstance(s, bytes) else str(s).encode() for s in newicks])
+
+
 def newick_to_ops(newicks, labels, n_threads=0):
     """Newick strings + xMSA row labels -> dict(children[B,T-2,2], blen[B,T-2,2], root_child[B], root_blen[B])."""
     T, B = len(labels), len(newicks)
@@ -169,8 +174,9 @@ class PhyloHMM:
                                                 int(num_rates), int(batch_size)))
 
     def ScoreSamples(self, newicks, er, pi, alpha, num_rates):
+        """newicks: list of str, or a ctypes array made by encode_newicks (marshalled once, reused)."""
         n = len(newicks)
-        arr = (C.c_char_p * n)(*[s.encode() for s in newicks])
+        arr = newicks if isinstance(newicks, C.Array) else encode_newicks(newicks)
         er = np.ascontiguousarray(er, dtype=np.float64).reshape(n, 6)
         pi = np.ascontiguousarray(pi, dtype=np.float64).reshape(n, 4)
         alpha = np.ascontiguousarray(alpha, dtype=np.float64).reshape(n)

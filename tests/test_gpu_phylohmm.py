@@ -83,6 +83,36 @@ def test_score_samples_equals_pipeline_loglik(tiny):
     assert abs(ll[0] - float(z["first_loglik"])) <= 1e-9 * abs(float(z["first_loglik"]))
 
 
+def test_score_samples_chunks_overlap_ingest_and_match_one_by_one(tiny):
+    """More samples than one ingest chunk (2048): chunk c+1 is parsed while chunk c is scored; the result
+    is the per-sample result, and a malformed string in a LATER chunk still raises."""
+    z, ff, d = tiny
+    rows = [l.split("\t") for l in str(z["tsv_in"]).splitlines()]
+    hdr, rows = rows[0], rows[1:]
+    c = {n: i for i, n in enumerate(hdr)}
+    base = [r[c["tree"]] for r in rows]
+    n = 5000
+    rng = np.random.default_rng(3)
+    newicks = [base[i % len(base)] for i in range(n)]
+    er = rng.dirichlet(np.ones(6), n)
+    pi = np.maximum(rng.dirichlet(np.ones(4), n), 0.05)
+    pi /= pi.sum(axis=1, keepdims=True)
+    alpha = np.maximum(0.1, rng.exponential(1.0, n))
+    R = int(z["num_rates"])
+    h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+    ll = h.ScoreSamples(host.encode_newicks(newicks), er, pi, alpha, R)
+    for lo, hi in ((0, 7), (2040, 2060), (4990, 5000)):
+        part = h.ScoreSamples(newicks[lo:hi], er[lo:hi], pi[lo:hi], alpha[lo:hi], R)
+        assert np.array_equal(part, ll[lo:hi])
+    bad = list(newicks)
+    bad[4500] = "((0:0.1,1:0.1):0.1,naive:0.1,nosuchtip:0.1);"
+    with pytest.raises(host.HostError):
+        h.ScoreSamples(bad, er, pi, alpha, R)
+    again = h.ScoreSamples(newicks[:9], er[:9], pi[:9], alpha[:9], R)   # the handle stays usable
+    assert np.array_equal(again, ll[:9])
+    h.close()
+
+
 def test_errors_surface_as_exceptions(tiny):
     z, ff, d = tiny
     h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
