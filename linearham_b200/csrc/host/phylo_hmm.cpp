@@ -377,7 +377,7 @@ void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er,
   if (B <= 0) return;
   const int T = xmsa_.rows();
   const std::size_t per = (std::size_t)2 * (T - 2);
-  constexpr int kChunk = 2048;
+  constexpr int kChunk = 1024;
   struct Flat {
     std::vector<int32_t> children, root_child;
     std::vector<double> blen, root_blen, rates;
@@ -394,12 +394,14 @@ void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er,
     if (lhh_gamma_cats_batch(n, alpha + b0, num_rates, f.rates.data())) return lhh_last_error();
     return std::string();
   };
-  std::string err = ingest(0, std::min(kChunk, B), flat[0]);
+  // a short opening chunk (nothing overlaps its ingest), then kChunk samples at a time
+  auto chunk_end = [&](int b0) { return std::min(B, b0 == 0 ? kChunk / 4 : b0 + kChunk); };
+  std::string err = ingest(0, chunk_end(0), flat[0]);
   if (!err.empty()) throw std::invalid_argument(err);
-  for (int b0 = 0, c = 0; b0 < B; b0 += kChunk, ++c) {
-    const int n = std::min(kChunk, B - b0), b1 = b0 + kChunk;
+  for (int b0 = 0, c = 0; b0 < B; ++c) {
+    const int b1 = chunk_end(b0), n = b1 - b0;
     std::future<std::string> next;
-    if (b1 < B) next = std::async(std::launch::async, ingest, b1, std::min(kChunk, B - b1), std::ref(flat[(c + 1) & 1]));
+    if (b1 < B) next = std::async(std::launch::async, ingest, b1, chunk_end(b1) - b1, std::ref(flat[(c + 1) & 1]));
     Flat& f = flat[c & 1];
     lh_tree_batch_t tb{n, num_rates, f.children.data(), f.blen.data(), f.root_child.data(), f.root_blen.data(),
                        er + (std::size_t)6 * b0, pi + (std::size_t)4 * b0, f.rates.data()};
@@ -407,6 +409,7 @@ void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er,
     if (next.valid()) err = next.get();
     if (rc) throw std::runtime_error(lh_last_error());
     if (!err.empty()) throw std::invalid_argument(err);
+    b0 = b1;
   }
 }
 

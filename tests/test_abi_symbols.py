@@ -54,3 +54,25 @@ def test_product_does_not_reference_oracle():
                 text = open(os.path.join(dirpath, fn), errors="ignore").read()
                 for pat in (r"(from|import)\s+oracle", r"oracle/", r"pyoracle", r"libport", r"libref_linearham"):
                     assert not re.search(pat, text), (pat, os.path.join(dirpath, fn))
+
+
+def test_command_line_is_built_and_rejects_bad_usage():
+    """linearham_b200/linearham: the reference's subcommands and flag names (src/linearham.cpp:268-455)."""
+    import subprocess
+    from linearham_b200 import host
+    cli = os.path.join(os.path.dirname(os.path.abspath(host.__file__)), "linearham")
+    assert os.access(cli, os.X_OK), "run __graft_entry__.build()"
+    r = subprocess.run([cli, "--help"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0
+    for sub in ("--compute-logl", "--sample", "--pipeline"):
+        assert sub in r.stdout
+        h = subprocess.run([cli, sub, "--help"], capture_output=True, text=True, timeout=60)
+        assert h.returncode == 0 and "--yaml-path" in h.stdout and "--hmm-param-dir" in h.stdout
+    r = subprocess.run([cli, "--frobnicate"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "ERROR: '--frobnicate' is not a valid subcommand." in r.stderr
+    r = subprocess.run([cli, "--pipeline", "--yaml-path", "x"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and r.stderr.startswith("ERROR: ")
+    # a missing input file is the constructor's error, not a crash
+    r = subprocess.run([cli, "--pipeline", "--yaml-path", "/nonexistent.yaml", "--cluster-ind", "0", "--hmm-param-dir", "/nonexistent",
+                        "--input-path", "a", "--output-path", "b"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and r.stderr.startswith("ERROR: ")

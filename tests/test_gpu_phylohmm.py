@@ -84,7 +84,7 @@ def test_score_samples_equals_pipeline_loglik(tiny):
 
 
 def test_score_samples_chunks_overlap_ingest_and_match_one_by_one(tiny):
-    """More samples than one ingest chunk (2048): chunk c+1 is parsed while chunk c is scored; the result
+    """More samples than one ingest chunk (256 first, then 1024): chunk c+1 is parsed while chunk c is scored; the result
     is the per-sample result, and a malformed string in a LATER chunk still raises."""
     z, ff, d = tiny
     rows = [l.split("\t") for l in str(z["tsv_in"]).splitlines()]
@@ -101,7 +101,7 @@ def test_score_samples_chunks_overlap_ingest_and_match_one_by_one(tiny):
     R = int(z["num_rates"])
     h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
     ll = h.ScoreSamples(host.encode_newicks(newicks), er, pi, alpha, R)
-    for lo, hi in ((0, 7), (2040, 2060), (4990, 5000)):
+    for lo, hi in ((0, 7), (250, 260), (1270, 1290), (4990, 5000)):
         part = h.ScoreSamples(newicks[lo:hi], er[lo:hi], pi[lo:hi], alpha[lo:hi], R)
         assert np.array_equal(part, ll[lo:hi])
     bad = list(newicks)
@@ -126,3 +126,61 @@ def test_errors_surface_as_exceptions(tiny):
     with pytest.raises(host.HostError):                       # gamma.c:238
         h.InitializePhyloParameters(bad, [1] * 6, [0.25] * 4, 0.001, 4)
     h.close()
+
+
+# ---- the command line (linearham_b200/linearham; flags of src/linearham.cpp:268-455) ------------------
+CLI = os.path.join(os.path.dirname(os.path.abspath(host.__file__)), "linearham")
+
+
+def _cli(*args):
+    import subprocess
+    return subprocess.run([CLI, *[str(a) for a in args]], capture_output=True, text=True, timeout=300)
+
+
+def _tree_flags(z, path):
+    flags = ["--newick-path", path, "--alpha", repr(float(z["first_alpha"])), "--num-rates", int(z["num_rates"])]
+    for x in z["first_er"]:
+        flags += ["--er", repr(float(x))]
+    for x in z["first_pi"]:
+        flags += ["--pi", repr(float(x))]
+    return flags
+
+
+def test_cli_compute_logl_sample_and_pipeline(tiny):
+    z, ff, d = tiny
+    path = os.path.join(d, "cli_first.tree")
+    open(path, "w").write(str(z["first_newick"]))
+    common = ["--yaml-path", ff["yaml_path"], "--cluster-ind", 0, "--hmm-param-dir", ff["hmm_dir"], "--seed", 0]
+    r = _cli("--compute-logl", *common, *_tree_flags(z, path))
+    assert r.returncode == 0, r.stderr
+    # std::cout << double prints 6 significant digits (src/linearham.cpp:344)
+    assert r.stdout.strip() == "%g" % float(z["first_loglik"])
+    r = _cli("--sample", *common, *_tree_flags(z, path), "--N", 5)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout.split() == [str(s) for s in z["first_draws"]]
+    tin, tout = os.path.join(d, "cli_in.trees"), os.path.join(d, "cli_out.trees")
+    open(tin, "w").write(str(z["tsv_in"]))
+    r = _cli("--pipeline", *common, "--num-rates", int(z["num_rates"]), "--input-path", tin, "--output-path", tout,
+             "--batch-size", 7)
+    assert r.returncode == 0, r.stderr
+    got = [l.split("\t") for l in open(tout).read().splitlines()]
+    exp = [l.split("\t") for l in str(z["tsv_out"]).splitlines()]
+    assert got[0] == exp[0] and len(got) == len(exp)
+    for g, e in zip(got[1:], exp[1:]):
+        for name, a, b in zip(exp[0], g, e):
+            try:
+                fb = float(b)
+            except ValueError:
+                assert a == b, name
+                continue
+            assert abs(float(a) - fb) <= 2e-6 * max(1.0, abs(fb)), (name, a, b)
+
+
+def test_cli_reports_errors_like_the_reference(tiny):
+    z, ff, d = tiny
+    common = ["--yaml-path", ff["yaml_path"], "--cluster-ind", 0, "--hmm-param-dir", ff["hmm_dir"]]
+    bad = os.path.join(d, "cli_bad.tree")
+    open(bad, "w").write("((0:0.1,1:0.1):0.1,naive:0.1,nosuchtip:0.1);")
+    r = _cli("--compute-logl", *common, "--newick-path", bad, *sum((["--er", 1] for _ in range(6)), []),
+             *sum((["--pi", 0.25] for _ in range(4)), []))
+    assert r.returncode == 1 and r.stderr.startswith("ERROR: ") and r.stdout == ""
