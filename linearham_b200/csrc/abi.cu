@@ -581,8 +581,9 @@ int configure_batch(lh_family* f, int B, int R) {
   // items of a launch and items of one family cost the same, so a chunk of whole waves leaves no
   // partial last wave.
   auto gcd = [](int a, int b) { while (b) { int r = a % b; a = b; b = r; } return a; };
-  const int resident = f->occ[gmain] * f->num_sms, tiles = f->pc[gmain].n_tiles;
-  const int wave = resident / gcd(resident, tiles);  // smallest tree count with trees*tiles % resident == 0
+  // (a work item of k_prune is one (tree, tile, category))
+  const int resident = f->occ[gmain] * f->num_sms, tiles = f->pc[gmain].n_tiles, items = tiles * R;
+  const int wave = resident / gcd(resident, items);  // smallest tree count with trees*items % resident == 0
   int chunk = (int)std::max<size_t>(1, f->opt_chunk_bytes / rec_bytes_tree);
   // A resident batch runs 16 waves per launch (the records then exceed L2 for large trees, which is
   // harmless: they are written once and read once per site tile by CTAs that run at the same time,
@@ -592,7 +593,7 @@ int configure_batch(lh_family* f, int B, int R) {
   if (chunk > wave) chunk -= chunk % wave;
   // The pipelined call launches every `pipe_waves` waves, so its first kernels start after a
   // small part of the host planning and the copy of one chunk hides behind the kernels of another.
-  f->wave_pipe = std::max(wave, (resident + tiles - 1) / tiles);
+  f->wave_pipe = (std::max(wave, (resident + tiles - 1) / tiles) + wave - 1) / wave * wave;
   int chunk_pipe = std::max(1, f->opt_pipe_waves) * f->wave_pipe;
   if (f->opt_chunk_trees > 0) {
     chunk = chunk_pipe = f->opt_chunk_trees;
@@ -613,7 +614,7 @@ int configure_batch(lh_family* f, int B, int R) {
     lhb::PruneCfg& pc = f->pc[g];
     if (!use[g]) continue;
     const int tile_sites = 32 * pc.sites_per_thread;
-    pc.grid = std::min(f->occ[g] * f->num_sms, chunk * pc.n_tiles);
+    pc.grid = (int)std::min<int64_t>((int64_t)f->occ[g] * f->num_sms, (int64_t)chunk * pc.n_tiles * R);
     const int gslots = pc.total_slots - pc.smem_slots;
     if (gslots > 0) {
       scratch_bytes = std::max(scratch_bytes, (size_t)pc.grid * gslots * 4 * tile_sites * sizeof(double));
@@ -845,7 +846,7 @@ void launch_chunk(lh_family* f, int ci, int t0, int n) {
       r.tree_list = list[1];
       lhb::launch_prune_sr(f->fd, f->bd, c, r, t0, count[1], s);
     } else {
-      c.grid = std::min(c.grid, count[g] * c.n_tiles);
+      c.grid = (int)std::min<int64_t>(c.grid, (int64_t)count[g] * c.n_tiles * f->R);
       lhb::launch_prune(f->fd, f->bd, c, t0, count[g], s);
     }
     f->tm.kernel_launches += 1;

@@ -93,32 +93,29 @@ inline const char* skip(const char* p) {
   for (;;) {
     while (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r') ++p;
     if (*p != '[') return p;
-    const char* e = std::strchr(p, ']');
-    if (!e) return p + std::strlen(p);
-    p = e + 1;
+    while (*p != ']' && *p) ++p;  // comments are a dozen characters: a call to strchr costs more
+    if (*p) ++p;
   }
 }
 
 // Decimal -> double. std::from_chars (libstdc++: Eisel-Lemire with an exact fallback) returns the
 // correctly rounded double, as strtod / atof (the reference's lexer path, parse_utree.y) does, at a
 // fraction of the cost; forms it does not take (leading '+', hex, locale) go to strtod.
-inline const char* parse_double(const char* p, double* out) {
+inline const char* parse_double(const char* p, const char* end, double* out) {
   if ((*p >= '0' && *p <= '9') || *p == '-' || *p == '.') {
-    const char* e = p;
-    while (!is_delim(*e)) ++e;
-    const auto r = std::from_chars(p, e, *out);
-    if (r.ec == std::errc() && r.ptr == e) return e;
+    const auto r = std::from_chars(p, end, *out);  // stops at the first character that is not part of the number
+    if (r.ec == std::errc() && is_delim(*r.ptr)) return r.ptr;
   }
-  char* end = nullptr;
-  *out = std::strtod(p, &end);
-  return end == p ? nullptr : end;
+  char* stop = nullptr;
+  *out = std::strtod(p, &stop);
+  return stop == p ? nullptr : stop;
 }
 
-inline const char* branch_length(const char* p, double* len) {
+inline const char* branch_length(const char* p, const char* end, double* len) {
   p = skip(p);
   double v = 0.0;
   if (*p == ':') {
-    p = parse_double(skip(p + 1), &v);
+    p = parse_double(skip(p + 1), end, &v);
     if (!p) return nullptr;
   }
   *len = v ? v : kEps;
@@ -134,6 +131,7 @@ const char* flatten_one(const char* s, const LabelMap& labels, int T, std::vecto
   seen.assign(T, 0);
   int emitted = 0;
   bool done = false;
+  const char* const end = s + std::strlen(s);
   const char* p = skip(s);
   if (*p != '(') return "tree does not start with '('";
   while (!done) {
@@ -154,7 +152,7 @@ const char* flatten_one(const char* s, const LabelMap& labels, int T, std::vecto
       if (stack.empty()) {
         // the trifurcation (a trailing ":len" on it is accepted and ignored)
         double ignored;
-        const char* q = branch_length(p, &ignored);
+        const char* q = branch_length(p, end, &ignored);
         if (!q) return "malformed branch length";
         p = skip(q);
         if (*p != ';') return "expected ';' after the top-level node";
@@ -172,7 +170,7 @@ const char* flatten_one(const char* s, const LabelMap& labels, int T, std::vecto
         if (o.n != 2) return "inner nodes must be binary";
         if (emitted >= n_ops - 1) return "wrong number of tips for this family";
         double len;
-        p = branch_length(p, &len);
+        p = branch_length(p, end, &len);
         if (!p) return "malformed branch length";
         children[2 * emitted] = o.id[0];
         children[2 * emitted + 1] = o.id[1];
@@ -203,7 +201,7 @@ const char* flatten_one(const char* s, const LabelMap& labels, int T, std::vecto
       }
       seen[row] = 1;
       double len;
-      p = branch_length(p, &len);
+      p = branch_length(p, end, &len);
       if (!p) return "malformed branch length";
       Open& up = stack.back();
       if (up.n >= 3) return "node with more than three children";

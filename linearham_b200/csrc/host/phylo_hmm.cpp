@@ -6,6 +6,9 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
 #include <future>
 #include <sstream>
 #include <stdexcept>
@@ -377,40 +380,86 @@ void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er,
   if (B <= 0) return;
   const int T = xmsa_.rows();
   const std::size_t per = (std::size_t)2 * (T - 2);
-  constexpr int kChunk = 1024;
+  constexpr int kChunk = 1024, kBuffers = 3;
   struct Flat {
     std::vector<int32_t> children, root_child;
     std::vector<double> blen, root_blen, rates;
-  } flat[2];
-  auto ingest = [&](int b0, int n, Flat& f) -> std::string {
+    int b0 = 0, n = 0;
+    std::string err;
+  } flat[kBuffers];
+  auto ingest = [&](Flat& f) {
+    const int n = f.n;
     f.children.resize(n * per);
     f.blen.resize(n * per);
     f.root_child.resize(n);
     f.root_blen.resize(n);
     f.rates.resize((std::size_t)n * num_rates);
-    if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), n, newicks + b0, 0, f.children.data(), f.blen.data(),
-                          f.root_child.data(), f.root_blen.data()))
-      return lhh_last_error();
-    if (lhh_gamma_cats_batch(n, alpha + b0, num_rates, f.rates.data())) return lhh_last_error();
-    return std::string();
+    f.err.clear();
+    if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), n, newicks + f.b0, 0, f.children.data(), f.blen.data(),
+                          f.root_child.data(), f.root_blen.data()) ||
+        lhh_gamma_cats_batch(n, alpha + f.b0, num_rates, f.rates.data()))
+      f.err = lhh_last_error();
   };
-  // a short opening chunk (nothing overlaps its ingest), then kChunk samples at a time
-  auto chunk_end = [&](int b0) { return std::min(B, b0 == 0 ? kChunk / 4 : b0 + kChunk); };
-  std::string err = ingest(0, chunk_end(0), flat[0]);
-  if (!err.empty()) throw std::invalid_argument(err);
-  for (int b0 = 0, c = 0; b0 < B; ++c) {
-    const int b1 = chunk_end(b0), n = b1 - b0;
-    std::future<std::string> next;
-    if (b1 < B) next = std::async(std::launch::async, ingest, b1, chunk_end(b1) - b1, std::ref(flat[(c + 1) & 1]));
-    Flat& f = flat[c & 1];
-    lh_tree_batch_t tb{n, num_rates, f.children.data(), f.blen.data(), f.root_child.data(), f.root_blen.data(),
-                       er + (std::size_t)6 * b0, pi + (std::size_t)4 * b0, f.rates.data()};
-    const int rc = lh_score_batch(dev_family_, &tb, loglik + b0, nullptr);
-    if (next.valid()) err = next.get();
-    if (rc) throw std::runtime_error(lh_last_error());
-    if (!err.empty()) throw std::invalid_argument(err);
-    b0 = b1;
+  // The ingest thread runs ahead of the device by up to kBuffers - 1 chunks; a short opening chunk gets the
+  // device started early.
+  std::mutex m;
+  std::condition_variable cv;
+  int produced = 0, consumed = 0;
+  bool stop = false;
+  std::thread producer([&] {
+    for (int b0 = 0, c = 0; b0 < B; ++c) {
+      {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return stop || c - consumed < kBuffers; });
+        if (stop) return;
+      }
+      Flat& f = flat[c % kBuffers];
+      f.b0 = b0;
+      f.n = std::min(B - b0, c == 0 ? kChunk / 4 : kChunk);
+      ingest(f);
+      b0 += f.n;
+      const bool failed = !f.err.empty();
+      {
+        std::lock_guard<std::mutex> lk(m);
+        ++produced;
+      }
+      cv.notify_all();
+      if (failed) return;
+    }
+  });
+  std::string err;
+  bool device_failed = false;
+  for (int done = 0, c = 0; done < B; ++c) {
+    {
+      std::unique_lock<std::mutex> lk(m);
+      cv.wait(lk, [&] { return produced > c; });
+    }
+    Flat& f = flat[c % kBuffers];
+    if (!f.err.empty()) {
+      err = f.err;
+      break;
+    }
+    lh_tree_batch_t tb{f.n, num_rates, f.children.data(), f.blen.data(), f.root_child.data(), f.root_blen.data(),
+                       er + (std::size_t)6 * f.b0, pi + (std::size_t)4 * f.b0, f.rates.data()};
+    if (lh_score_batch(dev_family_, &tb, loglik + f.b0, nullptr)) {
+      device_failed = true;
+      break;
+    }
+    done += f.n;
+    {
+      std::lock_guard<std::mutex> lk(m);
+      ++consumed;
+    }
+    cv.notify_all();
   }
+  {
+    std::lock_guard<std::mutex> lk(m);
+    stop = true;
+  }
+  cv.notify_all();
+  producer.join();
+  if (device_failed) throw std::runtime_error(lh_last_error());
+  if (!err.empty()) throw std::invalid_argument(err);
 }
 
 // src/PhyloHMM.cpp:244-282

@@ -403,16 +403,20 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   const size_t pass_bytes = (size_t)NB * kRecDoubles * 8;  // records of one (tree, category)
   const size_t code_pitch = (size_t)cfg.n_tiles * 32;      // words per tip row
 
-  const int n_work = ntrees * cfg.n_tiles;
+  // work item = (tree, tile, category): the categories of a tile are independent until k_edge sums
+  // them, and items this fine keep the last wave of a small batch full
+  const int per_tree = cfg.n_tiles * R;
+  const int n_work = ntrees * per_tree;
   for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
-    const int li = w / cfg.n_tiles, tile = w - li * cfg.n_tiles;
+    const int li = w / per_tree, rem = w - li * per_tree;
+    const int tile = rem / R, k = rem - tile * R;
     const int t = __ldg(cfg.tree_list + li);
     const int lt = t - tree0;
     const int4* __restrict__ plan = b.plan + (size_t)t * (T - 1);
     const unsigned* __restrict__ my_codes = cfg.codes_t + (size_t)tile * 32 + lane;
     int naive_br = -1;  // record index of the naive tip's branch when its factor is deferred
 
-    for (int k = 0; k < R; ++k) {
+    {
       // the record stream of this (tree, category): step q at rec_src + q * 320 bytes
       const char* rec_src = reinterpret_cast<const char*>(b.prec) + ((size_t)lt * R + k) * pass_bytes + lane * 16;
       const size_t rec_end = pass_bytes;  // bytes valid in the stream
@@ -542,7 +546,7 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
       cp_async_wait<0>();
     }
 
-    if (tile == 0 && lane == 0) cfg.enaive[lt] = naive_br;
+    if (tile == 0 && k == 0 && lane == 0) cfg.enaive[lt] = naive_br;
   }
 }
 

@@ -37,8 +37,13 @@ struct Step {          // 16 bytes, loaded as one int4 by the kernel
 //   pblen         : [2(T-2)+1] out; branch length of step s child c at 2s+c, root edge last
 //   scratch       : reusable work buffer
 // Returns the number of stack slots the program needs, or -1 for a malformed tree.
+struct Step;
 struct PlanScratch {
-  std::vector<int32_t> need, stack;
+  std::vector<uint32_t> up;
+  std::vector<int32_t> order;
+  std::vector<Step> by_op;
+  std::vector<uint64_t> down;
+  std::vector<uint8_t> uses;
 };
 int plan_tree(int n_tips, const int32_t* children, const double* blen, int32_t root_child,
               double root_blen, Step* steps, double* pblen, PlanScratch& scratch);
