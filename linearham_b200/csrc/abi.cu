@@ -555,6 +555,7 @@ int configure_batch(lh_family* f, int B, int R) {
     if (cset.codes_ns != pc.sites_per_thread) {
       // re-tile the tip codes for this NS (once per family, column set and NS)
       const int NS = pc.sites_per_thread;
+      if ((uint64_t)T * pc.n_tiles * 32 >= (1ull << 32)) return fail("tip-code table too large");  // the kernel indexes it with 32 bits
       std::vector<uint32_t> ct((size_t)T * pc.n_tiles * 32, 0u);
       for (int r = 0; r < T; ++r)
         for (int tile = 0; tile < pc.n_tiles; ++tile)

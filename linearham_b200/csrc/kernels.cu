@@ -250,43 +250,63 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
+// Shared-memory accesses by 32-bit shared-space address: through generic pointers every access
+// site first rebuilds the CTA's shared window base (S2UR SR_CgaCtaId, UMOV, ULEA).
+__device__ __forceinline__ double2 lds_f64x2(unsigned a) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ double lds_f64(unsigned a) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ int lds_s32(unsigned a) {
+  int v;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ int4 lds_s32x4(unsigned a) {
+  int4 v;
+  asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_f64(unsigned a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v)); }
+__device__ __forceinline__ void sts_s32(unsigned a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v)); }
+
 // v < 2^-256 on the high word: 2^-256 = 0x2FF0000000000000, so for v >= +0 the comparison of the
 // bit patterns reduces to the high words, and every negative v (sign bit set) is below the
 // threshold as a signed integer too. Keeps the test off the FP64 pipe.
 constexpr int kThresholdHi = 0x2FF00000;
 
-// One parked CLV level of this lane: [u][state] doubles at stride 32 and [u] counts at stride 32.
-template <int NS>
-struct Slot {
-  double* clv;
-  int* cnt;
-};
-
+// Parked CLV levels of this lane: [slot][u][state] doubles at stride 32 and [slot][u] counts at
+// stride 32; the levels smem_lo .. smem_lo + smem_slots - 1 live in shared memory (addressed by
+// 32-bit shared-space address), the others in the CTA's global scratch.
 template <int NS>
 struct SlotIO {
-  double* smem_clv;   // [smem_slots][NS*4][32]
-  int* smem_cnt;      // [smem_slots][NS][32]
-  double* g_clv;      // [gslots][NS*4][32] (this CTA)
-  int* g_cnt;         // [gslots][NS][32]
-  int smem_slots, smem_lo, lane;  // slots smem_lo .. smem_lo + smem_slots - 1 live in shared memory
+  unsigned s_clv, s_cnt;  // shared-space byte addresses of this lane's element of level smem_lo
+  double* g_clv;          // [gslots][NS*4][32] (this CTA), already offset by the lane
+  int* g_cnt;             // [gslots][NS][32]
+  int smem_slots, smem_lo;
 
   __device__ __forceinline__ bool in_smem(int slot) const { return (unsigned)(slot - smem_lo) < (unsigned)smem_slots; }
-  __device__ __forceinline__ Slot<NS> shared(int slot) const {
-    return {smem_clv + (slot - smem_lo) * (4 * NS) * 32 + lane, smem_cnt + (slot - smem_lo) * NS * 32 + lane};
+  __device__ __forceinline__ unsigned shared_clv(int slot) const { return s_clv + (unsigned)(slot - smem_lo) * (4 * NS * 32 * 8); }
+  __device__ __forceinline__ unsigned shared_cnt(int slot) const { return s_cnt + (unsigned)(slot - smem_lo) * (NS * 32 * 4); }
+  __device__ __forceinline__ double* global_clv(int slot) const {
+    return g_clv + (size_t)(slot < smem_lo ? slot : slot - smem_slots) * (4 * NS) * 32;
   }
-  __device__ __forceinline__ Slot<NS> global(int slot) const {
-    const int g = slot < smem_lo ? slot : slot - smem_slots;
-    return {g_clv + (size_t)g * (4 * NS) * 32 + lane, g_cnt + g * NS * 32 + lane};
+  __device__ __forceinline__ int* global_cnt(int slot) const {
+    return g_cnt + (slot < smem_lo ? slot : slot - smem_slots) * NS * 32;
   }
 };
 
 // m[u][i] = sum_j P[i][j] * c[u][j]   (core_partials.c:617-624), P row-major in shared memory
-template <int NS>
-__device__ __forceinline__ void load_p(const double* rec, double (&P)[4][4]) {
+__device__ __forceinline__ void load_p(unsigned rec, double (&P)[4][4]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const double2 p01 = *reinterpret_cast<const double2*>(rec + 4 * i);
-    const double2 p23 = *reinterpret_cast<const double2*>(rec + 4 * i + 2);
+    const double2 p01 = lds_f64x2(rec + 32 * i);
+    const double2 p23 = lds_f64x2(rec + 32 * i + 16);
     P[i][0] = p01.x; P[i][1] = p01.y; P[i][2] = p23.x; P[i][3] = p23.y;
   }
 }
@@ -305,24 +325,24 @@ __device__ __forceinline__ void matvec(const double (&P)[4][4], const double (&c
 //   src >= 0  tip: column `code` of the staged Q block; `codes` holds the lane's NS byte offsets
 //   src == -1 the running result in registers
 //   else      a parked CLV
+// `rec` is the shared-space address of the child's staged record.
 template <int NS>
-__device__ __forceinline__ void child_messages(int src, const double* rec, unsigned codes,
+__device__ __forceinline__ void child_messages(int src, unsigned rec, unsigned codes,
                                                const double (&reg)[NS][4], const int (&reg_cnt)[NS],
                                                const SlotIO<NS>& io, double (&m)[NS][4], int (&cnt)[NS]) {
   if (src >= 0) {
-    const char* q = reinterpret_cast<const char*>(rec);
 #pragma unroll
     for (int u = 0; u < NS; ++u) {
       const unsigned off = (codes >> (8 * u)) & 0xffu;
-      const double2 q01 = *reinterpret_cast<const double2*>(q + off);
-      const double2 q23 = *reinterpret_cast<const double2*>(q + off + 16);
+      const double2 q01 = lds_f64x2(rec + off);
+      const double2 q23 = lds_f64x2(rec + off + 16);
       m[u][0] = q01.x; m[u][1] = q01.y; m[u][2] = q23.x; m[u][3] = q23.y;
       cnt[u] = 0;
     }
     return;
   }
   double P[4][4];
-  load_p<NS>(rec, P);
+  load_p(rec, P);
   if (src == -1) {
 #pragma unroll
     for (int u = 0; u < NS; ++u) {
@@ -333,50 +353,79 @@ __device__ __forceinline__ void child_messages(int src, const double* rec, unsig
   }
   const int slot = -2 - src;
   if (io.in_smem(slot)) {
-    const Slot<NS> sl = io.shared(slot);
+    const unsigned clv = io.shared_clv(slot), sc = io.shared_cnt(slot);
 #pragma unroll
     for (int u = 0; u < NS; ++u) {
       double c[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) c[j] = sl.clv[(u * 4 + j) * 32];
+      for (int j = 0; j < 4; ++j) c[j] = lds_f64(clv + (u * 4 + j) * 32 * 8);
       matvec(P, c, m[u]);
-      cnt[u] = sl.cnt[u * 32];
+      cnt[u] = lds_s32(sc + u * 32 * 4);
     }
   } else {
-    const Slot<NS> sl = io.global(slot);
+    const double* clv = io.global_clv(slot);
+    const int* sc = io.global_cnt(slot);
 #pragma unroll
     for (int u = 0; u < NS; ++u) {
       double c[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) c[j] = sl.clv[(u * 4 + j) * 32];
+      for (int j = 0; j < 4; ++j) c[j] = clv[(u * 4 + j) * 32];
       matvec(P, c, m[u]);
-      cnt[u] = sl.cnt[u * 32];
+      cnt[u] = sc[u * 32];
     }
   }
 }
 
 template <int NS>
-__device__ __forceinline__ void park(const Slot<NS>& sl, const double (&reg)[NS][4], const int (&reg_cnt)[NS]) {
+__device__ __forceinline__ void park(const SlotIO<NS>& io, int slot, const double (&reg)[NS][4], const int (&reg_cnt)[NS]) {
+  if (io.in_smem(slot)) {
+    const unsigned clv = io.shared_clv(slot), sc = io.shared_cnt(slot);
 #pragma unroll
-  for (int u = 0; u < NS; ++u) {
+    for (int u = 0; u < NS; ++u) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) sl.clv[(u * 4 + i) * 32] = reg[u][i];
-    sl.cnt[u * 32] = reg_cnt[u];
+      for (int i = 0; i < 4; ++i) sts_f64(clv + (u * 4 + i) * 32 * 8, reg[u][i]);
+      sts_s32(sc + u * 32 * 4, reg_cnt[u]);
+    }
+  } else {
+    double* clv = io.global_clv(slot);
+    int* sc = io.global_cnt(slot);
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) clv[(u * 4 + i) * 32] = reg[u][i];
+      sc[u * 32] = reg_cnt[u];
+    }
   }
 }
 template <int NS>
-__device__ __forceinline__ void unpark(const Slot<NS>& sl, double (&reg)[NS][4], int (&reg_cnt)[NS]) {
+__device__ __forceinline__ void unpark(const SlotIO<NS>& io, int slot, double (&reg)[NS][4], int (&reg_cnt)[NS]) {
+  if (io.in_smem(slot)) {
+    const unsigned clv = io.shared_clv(slot), sc = io.shared_cnt(slot);
 #pragma unroll
-  for (int u = 0; u < NS; ++u) {
+    for (int u = 0; u < NS; ++u) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) reg[u][i] = sl.clv[(u * 4 + i) * 32];
-    reg_cnt[u] = sl.cnt[u * 32];
+      for (int i = 0; i < 4; ++i) reg[u][i] = lds_f64(clv + (u * 4 + i) * 32 * 8);
+      reg_cnt[u] = lds_s32(sc + u * 32 * 4);
+    }
+  } else {
+    const double* clv = io.global_clv(slot);
+    const int* sc = io.global_cnt(slot);
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) reg[u][i] = clv[(u * 4 + i) * 32];
+      reg_cnt[u] = sc[u * 32];
+    }
   }
 }
 
+// dynamic part: the parked CLV levels; static part: the two rings (compile-time addresses, so the
+// ring reads need no base register)
+static size_t prune_dynamic_smem_bytes(int ns, int smem_slots) {
+  return (size_t)smem_slots * 32 * ns * (4 * sizeof(double) + sizeof(int));
+}
 size_t prune_smem_bytes(int ns, int smem_slots) {
-  return (size_t)kRecRing * kStepBytes + kPlanRing * sizeof(int4) +
-         (size_t)smem_slots * 32 * ns * (4 * sizeof(double) + sizeof(int));
+  return (size_t)kRecRing * kStepBytes + kPlanRing * sizeof(int4) + prune_dynamic_smem_bytes(ns, smem_slots);
 }
 
 template <int NS>
@@ -386,22 +435,23 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   const int lane = threadIdx.x, T = f.T, R = b.R;
   const int NB = 2 * T - 3, n_steps = T - 2, n_iter = T - 1;  // node updates + the edge evaluation
   const int gslots = cfg.total_slots - cfg.smem_slots;
-  double* ring_rec = reinterpret_cast<double*>(smem_raw);                            // [kRecRing][2][20]
-  int4* ring_plan = reinterpret_cast<int4*>(smem_raw + kRecRing * kStepBytes);       // [kPlanRing]
+  __shared__ __align__(16) double ring_rec[kRecRing * 2 * kRecDoubles];
+  __shared__ int4 ring_plan[kPlanRing];
   SlotIO<NS> io;
-  io.smem_clv = reinterpret_cast<double*>(ring_plan + kPlanRing);
-  io.smem_cnt = reinterpret_cast<int*>(io.smem_clv + (size_t)cfg.smem_slots * (4 * NS) * 32);
-  io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * NS) * 32;
-  io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * 32;
+  io.s_clv = (unsigned)__cvta_generic_to_shared(smem_raw) + lane * 8;
+  io.s_cnt = (unsigned)__cvta_generic_to_shared(smem_raw) + (unsigned)cfg.smem_slots * (4 * NS * 32 * 8) + lane * 4;
+  io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * NS) * 32 + lane;
+  io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * 32 + lane;
   io.smem_slots = cfg.smem_slots;
   io.smem_lo = cfg.smem_lo;
-  io.lane = lane;
-  // staging roles: lanes 0..19 each copy 16 of the 320 record bytes of a step
-  const bool rec_lane = lane < kStepBytes / 16;
-  const unsigned ring_rec_s = (unsigned)__cvta_generic_to_shared(ring_rec) + lane * 16;
+  const unsigned ring_rec_0 = (unsigned)__cvta_generic_to_shared(ring_rec);
+  const unsigned ring_rec_s = ring_rec_0 + lane * 16;
   const unsigned ring_plan_s = (unsigned)__cvta_generic_to_shared(ring_plan);
+  // the last step this lane stages records for: lanes 0..19 copy 16 bytes each of a step's two
+  // records; the last step has a single record (the root edge), lanes 0..9
+  const int my_last_rec = lane < kRecDoubles * 8 / 16 ? n_steps : (lane < kStepBytes / 16 ? n_steps - 1 : -1);
   const size_t pass_bytes = (size_t)NB * kRecDoubles * 8;  // records of one (tree, category)
-  const size_t code_pitch = (size_t)cfg.n_tiles * 32;      // words per tip row
+  const unsigned code_pitch = (unsigned)cfg.n_tiles * 32u;  // words per tip row (the table is far below 2^32 words)
 
   // work item = (tree, tile, category): the categories of a tile are independent until k_edge sums
   // them, and items this fine keep the last wave of a small batch full
@@ -419,14 +469,15 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
     {
       // the record stream of this (tree, category): step q at rec_src + q * 320 bytes
       const char* rec_src = reinterpret_cast<const char*>(b.prec) + ((size_t)lt * R + k) * pass_bytes + lane * 16;
-      const size_t rec_end = pass_bytes;  // bytes valid in the stream
       auto stage_plan = [&](int q0) {
         const int q = q0 + lane;
         if (q < n_iter) cp_async16(ring_plan_s + (q & (kPlanRing - 1)) * 16, plan + q);
       };
-      auto stage_records = [&](int q) {  // the last step has a single record (the root edge)
-        if (rec_lane && (size_t)q * kStepBytes + lane * 16 < rec_end)
-          cp_async16(ring_rec_s + (q & (kRecRing - 1)) * kStepBytes, rec_src + (size_t)q * kStepBytes);
+      // records of step q; `rec_next` walks the stream, one step per call
+      const char* rec_next = rec_src;
+      auto stage_records = [&](int q) {
+        if (q <= my_last_rec) cp_async16(ring_rec_s + (q & (kRecRing - 1)) * kStepBytes, rec_next);
+        rec_next += kStepBytes;
       };
       __syncwarp();  // the previous pass / work item is done with the rings
       stage_plan(0);
@@ -447,10 +498,10 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
         for (int i = 0; i < 4; ++i) reg[u][i] = 0.0;
       }
       // software pipeline registers: the step being executed and the next one
-      int4 st_next = ring_plan[0];
+      int4 st_next = lds_s32x4(ring_plan_s);
       unsigned cA_next = 0, cB_next = 0;
-      if (st_next.x >= 0) cA_next = __ldg(my_codes + (size_t)st_next.x * code_pitch);
-      if (st_next.y >= 0) cB_next = __ldg(my_codes + (size_t)st_next.y * code_pitch);
+      if (st_next.x >= 0) cA_next = __ldg(my_codes + (unsigned)st_next.x * code_pitch);
+      if (st_next.y >= 0) cB_next = __ldg(my_codes + (unsigned)st_next.y * code_pitch);
 
       for (int s = 0; s < n_iter; ++s) {
         if ((s & 31) == 0 && s > 0) {
@@ -464,16 +515,16 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
         const int4 st = st_next;
         const unsigned cA = cA_next, cB = cB_next;
         if (s + 1 < n_iter) {     // plan and tip codes of the next step
-          st_next = ring_plan[(s + 1) & (kPlanRing - 1)];
-          if (st_next.x >= 0) cA_next = __ldg(my_codes + (size_t)st_next.x * code_pitch);
-          if (st_next.y >= 0) cB_next = __ldg(my_codes + (size_t)st_next.y * code_pitch);
+          st_next = lds_s32x4(ring_plan_s + ((s + 1) & (kPlanRing - 1)) * 16);
+          if (st_next.x >= 0) cA_next = __ldg(my_codes + (unsigned)st_next.x * code_pitch);
+          if (st_next.y >= 0) cB_next = __ldg(my_codes + (unsigned)st_next.y * code_pitch);
         }
-        const double* recA = ring_rec + (s & (kRecRing - 1)) * (2 * kRecDoubles);
+        const unsigned recA = ring_rec_0 + (s & (kRecRing - 1)) * kStepBytes;
         if (s < n_steps) {
           double ma[NS][4], mb[NS][4];
           int ca[NS], cb[NS];
           child_messages<NS>(st.x, recA, cA, reg, reg_cnt, io, ma, ca);
-          child_messages<NS>(st.y, recA + kRecDoubles, cB, reg, reg_cnt, io, mb, cb);
+          child_messages<NS>(st.y, recA + kRecDoubles * 8, cB, reg, reg_cnt, io, mb, cb);
           // Pattern columns: the node under which the naive tip hangs keeps the other child's
           // message only; k_edge multiplies the naive tip's Q column in, per xMSA column.
           const bool defer_a = cfg.defer_naive && st.x == 0, defer_b = cfg.defer_naive && st.y == 0;
@@ -513,21 +564,14 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
               }
             }
           }
-          if (st.z >= 0) {
-            if (io.in_smem(st.z)) park<NS>(io.shared(st.z), reg, reg_cnt);
-            else park<NS>(io.global(st.z), reg, reg_cnt);
-          }
+          if (st.z >= 0) park<NS>(io, st.z, reg, reg_cnt);
         } else {
           // ---- edge term of this category (core_likelihood_avx.c:1130-1239); the edge's record
           // sits in the first branch position of the last step, st.y is the child across it ----
           double mc[NS][4];
           int cc[NS];
           child_messages<NS>(st.y, recA, cB, reg, reg_cnt, io, mc, cc);
-          if (st.x != -1) {  // the root CLV was parked; fetch it
-            const int slot = -2 - st.x;
-            if (io.in_smem(slot)) unpark<NS>(io.shared(slot), reg, reg_cnt);
-            else unpark<NS>(io.global(slot), reg, reg_cnt);
-          }
+          if (st.x != -1) unpark<NS>(io, -2 - st.x, reg, reg_cnt);  // the root CLV was parked; fetch it
           // hand the edge term's inputs to k_edge
           double* eo = cfg.ebuf + (size_t)lt * cfg.e_stride + (size_t)k * 8 * cfg.cols_pad + tile * (32 * NS) + lane;
           int* co = cfg.ecnt + (size_t)lt * cfg.c_stride + (size_t)k * cfg.cols_pad + tile * (32 * NS) + lane;
@@ -561,7 +605,7 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
 template <int NS>
 static void launch_prune_n(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0,
                            int ntrees, cudaStream_t s) {
-  size_t smem = prune_smem_bytes(NS, c.smem_slots);
+  size_t smem = prune_dynamic_smem_bytes(NS, c.smem_slots);
   cudaFuncSetAttribute(k_prune<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   k_prune<NS><<<c.grid, 32, smem, s>>>(f, b, c, tree0, ntrees);
 }
@@ -580,7 +624,7 @@ void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int 
 }
 
 int prune_max_ctas_per_sm(int ns, int smem_slots) {
-  size_t smem = prune_smem_bytes(ns, smem_slots);
+  size_t smem = prune_dynamic_smem_bytes(ns, smem_slots);  // (the occupancy query adds the static part)
   int n = 0;
   LH_DISPATCH_NS(ns, n = prune_occ_n<NN>(smem));
   return n;
