@@ -238,7 +238,8 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 #define LH_PRUNE_MIN_CTAS1 24
 #endif
 
-constexpr int kRecRing = 4;    // steps of branch records in flight
+constexpr int kRecRing = 4;    // k_prune_sr: steps of branch records in flight
+constexpr int kBlk = 4;        // k_prune: steps per staged block of branch records (two blocks resident)
 constexpr int kPlanRing = 64;  // plan entries resident
 constexpr int kRecDoubles = 20;
 constexpr int kStepBytes = 2 * kRecDoubles * 8;  // both branches of a step, one category
@@ -249,6 +250,33 @@ __device__ __forceinline__ void cp_async16(unsigned smem_dst, const void* gmem_s
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// Bulk asynchronous copies (one instruction moves a whole staged block; completion is counted in
+// bytes on an mbarrier that every lane then waits on).
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "LH_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra LH_DONE;\n"
+      "bra LH_WAIT;\n"
+      "LH_DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
 
 // Shared-memory accesses by 32-bit shared-space address: through generic pointers every access
 // site first rebuilds the CTA's shared window base (S2UR SR_CgaCtaId, UMOV, ULEA).
@@ -425,7 +453,8 @@ static size_t prune_dynamic_smem_bytes(int ns, int smem_slots) {
   return (size_t)smem_slots * 32 * ns * (4 * sizeof(double) + sizeof(int));
 }
 size_t prune_smem_bytes(int ns, int smem_slots) {
-  return (size_t)kRecRing * kStepBytes + kPlanRing * sizeof(int4) + prune_dynamic_smem_bytes(ns, smem_slots);
+  return (size_t)2 * kBlk * kStepBytes + kPlanRing * sizeof(int4) + 4 * sizeof(unsigned long long) +
+         prune_dynamic_smem_bytes(ns, smem_slots);
 }
 
 template <int NS>
@@ -435,8 +464,9 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   const int lane = threadIdx.x, T = f.T, R = b.R;
   const int NB = 2 * T - 3, n_steps = T - 2, n_iter = T - 1;  // node updates + the edge evaluation
   const int gslots = cfg.total_slots - cfg.smem_slots;
-  __shared__ __align__(16) double ring_rec[kRecRing * 2 * kRecDoubles];
-  __shared__ int4 ring_plan[kPlanRing];
+  __shared__ __align__(16) double ring_rec[2 * kBlk * 2 * kRecDoubles];  // two blocks of kBlk steps
+  __shared__ int4 ring_plan[kPlanRing];                                  // two halves of 32 steps
+  __shared__ __align__(8) unsigned long long bars[4];                    // records 0/1, plan 0/1
   SlotIO<NS> io;
   io.s_clv = (unsigned)__cvta_generic_to_shared(smem_raw) + lane * 8;
   io.s_cnt = (unsigned)__cvta_generic_to_shared(smem_raw) + (unsigned)cfg.smem_slots * (4 * NS * 32 * 8) + lane * 4;
@@ -445,11 +475,17 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   io.smem_slots = cfg.smem_slots;
   io.smem_lo = cfg.smem_lo;
   const unsigned ring_rec_0 = (unsigned)__cvta_generic_to_shared(ring_rec);
-  const unsigned ring_rec_s = ring_rec_0 + lane * 16;
   const unsigned ring_plan_s = (unsigned)__cvta_generic_to_shared(ring_plan);
-  // the last step this lane stages records for: lanes 0..19 copy 16 bytes each of a step's two
-  // records; the last step has a single record (the root edge), lanes 0..9
-  const int my_last_rec = lane < kRecDoubles * 8 / 16 ? n_steps : (lane < kStepBytes / 16 ? n_steps - 1 : -1);
+  const unsigned bars_s = (unsigned)__cvta_generic_to_shared(bars);
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) mbar_init(bars_s + 8 * i, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  unsigned phase = 0;  // bit i: the parity the next wait on bars[i] looks for
+  constexpr unsigned kBlkBytes = kBlk * kStepBytes, kHalfBytes = 32 * sizeof(int4);
+  const int n_blocks = (n_iter + kBlk - 1) / kBlk, n_halves = (n_iter + 31) / 32;
   const size_t pass_bytes = (size_t)NB * kRecDoubles * 8;  // records of one (tree, category)
   const unsigned code_pitch = (unsigned)cfg.n_tiles * 32u;  // words per tip row (the table is far below 2^32 words)
 
@@ -467,27 +503,35 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
     int naive_br = -1;  // record index of the naive tip's branch when its factor is deferred
 
     {
-      // the record stream of this (tree, category): step q at rec_src + q * 320 bytes
-      const char* rec_src = reinterpret_cast<const char*>(b.prec) + ((size_t)lt * R + k) * pass_bytes + lane * 16;
-      auto stage_plan = [&](int q0) {
-        const int q = q0 + lane;
-        if (q < n_iter) cp_async16(ring_plan_s + (q & (kPlanRing - 1)) * 16, plan + q);
+      // The record stream of this (tree, category) - step q at rec_src + q * 320 bytes, the last
+      // step a single record - is staged kBlk steps per bulk copy, two blocks resident; the plan
+      // 32 steps per copy, two halves resident. Lane 0 issues, every lane waits.
+      const char* rec_src = reinterpret_cast<const char*>(b.prec) + ((size_t)lt * R + k) * pass_bytes;
+      auto issue_records = [&](int jb) {
+        const unsigned off = (unsigned)jb * kBlkBytes;
+        const unsigned bytes = min(kBlkBytes, (unsigned)pass_bytes - off);
+        const unsigned bar = bars_s + 8 * (jb & 1);
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(ring_rec_0 + (jb & 1) * kBlkBytes, rec_src + off, bytes, bar);
       };
-      // records of step q; `rec_next` walks the stream, one step per call
-      const char* rec_next = rec_src;
-      auto stage_records = [&](int q) {
-        if (q <= my_last_rec) cp_async16(ring_rec_s + (q & (kRecRing - 1)) * kStepBytes, rec_next);
-        rec_next += kStepBytes;
+      auto issue_plan = [&](int h) {
+        const unsigned bytes = (unsigned)min(32, n_iter - 32 * h) * (unsigned)sizeof(int4);
+        const unsigned bar = bars_s + 16 + 8 * (h & 1);
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(ring_plan_s + (h & 1) * kHalfBytes, plan + 32 * h, bytes, bar);
       };
-      __syncwarp();  // the previous pass / work item is done with the rings
-      stage_plan(0);
-      stage_plan(32);
-      stage_records(0);
-      cp_async_commit();
-      stage_records(1);
-      cp_async_commit();
-      cp_async_wait<1>();
-      __syncwarp();
+      auto wait_on = [&](int i) {
+        mbar_wait(bars_s + 8 * i, (phase >> i) & 1u);
+        phase ^= 1u << i;
+      };
+      __syncwarp();  // the previous work item is done with the rings
+      if (lane == 0) {
+        issue_plan(0);
+        if (n_halves > 1) issue_plan(1);
+        issue_records(0);
+        if (n_blocks > 1) issue_records(1);
+      }
+      wait_on(2);
 
       double reg[NS][4];
       int reg_cnt[NS];
@@ -503,15 +547,14 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
       if (st_next.x >= 0) cA_next = __ldg(my_codes + (unsigned)st_next.x * code_pitch);
       if (st_next.y >= 0) cB_next = __ldg(my_codes + (unsigned)st_next.y * code_pitch);
 
-      for (int s = 0; s < n_iter; ++s) {
-        if ((s & 31) == 0 && s > 0) {
-          __syncwarp();           // every lane has read the plan entries of the half being replaced
-          stage_plan(s + 32);
-        }
-        stage_records(s + 2);
-        cp_async_commit();
-        cp_async_wait<2>();       // the records of step s (two commits ago) have landed
-        __syncwarp();
+      for (int jb = 0; jb < n_blocks; ++jb) {
+        wait_on(jb & 1);  // the records of this block
+        // the step before a new plan half reads that half's first entry
+        if ((jb & 7) == 7 && (jb >> 3) + 1 < n_halves) wait_on(2 + (((jb >> 3) + 1) & 1));
+        const int s_end = min(n_iter, (jb + 1) * kBlk);
+        unsigned recA = ring_rec_0 + (jb & 1) * kBlkBytes;
+#pragma unroll 1
+        for (int s = jb * kBlk; s < s_end; ++s, recA += kStepBytes) {
         const int4 st = st_next;
         const unsigned cA = cA_next, cB = cB_next;
         if (s + 1 < n_iter) {     // plan and tip codes of the next step
@@ -519,7 +562,6 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
           if (st_next.x >= 0) cA_next = __ldg(my_codes + (unsigned)st_next.x * code_pitch);
           if (st_next.y >= 0) cB_next = __ldg(my_codes + (unsigned)st_next.y * code_pitch);
         }
-        const unsigned recA = ring_rec_0 + (s & (kRecRing - 1)) * kStepBytes;
         if (s < n_steps) {
           double ma[NS][4], mb[NS][4];
           int ca[NS], cb[NS];
@@ -586,8 +628,13 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
           }
           if (cfg.defer_naive && st.y == 0) naive_br = 2 * n_steps;
         }
+        }
+        __syncwarp();  // every lane is done with this block's records (and, at a half's end, its plan entries)
+        if (lane == 0) {
+          if (jb + 2 < n_blocks) issue_records(jb + 2);
+          if ((jb & 7) == 7 && (jb >> 3) + 2 < n_halves) issue_plan((jb >> 3) + 2);
+        }
       }
-      cp_async_wait<0>();
     }
 
     if (tile == 0 && k == 0 && lane == 0) cfg.enaive[lt] = naive_br;
