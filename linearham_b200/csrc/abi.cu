@@ -520,7 +520,7 @@ int configure_batch(lh_family* f, int B, int R) {
   bd.loglik = f->d_loglik.as<double>();
 
   // pruning launch configuration per column set in use: [0] all columns, [1] site patterns
-  const size_t rec_bytes_tree = (size_t)NB * 20 * R * sizeof(double);
+  const size_t rec_bytes_tree = (size_t)lhb::records_per_pass(T) * 20 * R * sizeof(double);
   int strahler = 1;
   while ((2 << (strahler - 1)) <= T) ++strahler;  // floor(log2 T) + 1
   const bool use[2] = {f->n_pattern_trees < B, f->n_pattern_trees > 0};

@@ -114,7 +114,8 @@ void launch_eigen(const BatchDev& b, int tree0, int ntrees, cudaStream_t s) {
 // ---------------------------------------------------------------- k_pmatrix ---
 // One thread per (tree, branch, rate category). Branch records are laid out in the order
 // the pruning program consumes them, one contiguous stream per (tree, category): record
-// 2*step+c for child c of a step, the root edge last; a record is 20 doubles:
+// 2*step+c for child c of a step, then the root edge, then an identity matrix (the edge
+// evaluation runs as one more step: the root CLV "crosses" the identity); a record is 20 doubles:
 //   inner child : P[i][j] at i*4 + j                (row-major as core_pmatrix.c; 4 pad)
 //   tip child   : Q[code][i] at code*4 + i, code in A,C,G,T,N: the product
 //                 P[k] * tipclv(code) that set_tipclv + the generic kernel would form
@@ -126,9 +127,9 @@ __global__ void __launch_bounds__(128) k_pmatrix(FamilyDev f, BatchDev b, int tr
   // contiguous bytes of the stream, written with full 512-byte warp stores after a transpose
   // through shared memory (a thread storing its own 160-byte record would touch ten half-used sectors).
   __shared__ double tile[4][32 * 21];  // per warp: 32 records x 20 doubles, pitch 21 (conflict-free)
-  const int NB = 2 * f.T - 3, R = b.R;
+  const int NB = 2 * f.T - 3, NR = records_per_pass(f.T), R = b.R;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int groups = (NB + 31) / 32;  // branch groups per pass
+  const int groups = (NR + 31) / 32;  // record groups per pass
   const long long total = (long long)ntrees * R * groups;
   double* my = tile[wid];
   for (long long g = (long long)blockIdx.x * 4 + wid; g < total; g += (long long)gridDim.x * 4) {
@@ -138,16 +139,16 @@ __global__ void __launch_bounds__(128) k_pmatrix(FamilyDev f, BatchDev b, int tr
     const int t = tree0 + lt;
     const int br = bg * 32 + lane;
     __syncwarp();
-    if (br < NB) {
-      const int step = br >> 1;
+    if (br < NR) {
+      const int step = min(br, NB - 1) >> 1;
       const int4 st = __ldg(b.plan + (size_t)t * (f.T - 1) + step);
       const int src = (br & 1) ? st.y : st.x;  // for the final step y is the child side
-      const bool tip = (br == NB - 1) ? (st.y >= 0) : (src >= 0);
+      const bool tip = br < NB && ((br == NB - 1) ? (st.y >= 0) : (src >= 0));
       const double* e = b.eig + (size_t)t * kEigStride;
-      const double len = b.pblen[(size_t)t * NB + br];
+      const double len = br < NB ? b.pblen[(size_t)t * NB + br] : 0.0;
       const double rate = b.rates[(size_t)t * R + k];
       double P[4][4];
-      if (len == 0.0) {  // core_pmatrix.c:174-179
+      if (len == 0.0) {  // core_pmatrix.c:174-179 (and the closing identity record)
 #pragma unroll
         for (int j = 0; j < 4; ++j)
 #pragma unroll
@@ -189,14 +190,14 @@ __global__ void __launch_bounds__(128) k_pmatrix(FamilyDev f, BatchDev b, int tr
     }
     __syncwarp();
     // the group's records are contiguous: doubles [first, first + n*20) of the pass stream
-    const int n_rec = min(32, NB - bg * 32);
-    double* dst = b.prec + (((size_t)lt * R + k) * NB + (size_t)bg * 32) * kRecDoublesPm;
+    const int n_rec = min(32, NR - bg * 32);
+    double* dst = b.prec + (((size_t)lt * R + k) * NR + (size_t)bg * 32) * kRecDoublesPm;
     for (int i = lane; i < n_rec * kRecDoublesPm; i += 32) dst[i] = my[(i / kRecDoublesPm) * 21 + (i % kRecDoublesPm)];
   }
 }
 
 void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees, cudaStream_t s) {
-  const int groups = (2 * f.T - 3 + 31) / 32;
+  const int groups = (records_per_pass(f.T) + 31) / 32;
   long long total = (long long)ntrees * b.R * groups;  // warps of work
   long long blocks = (total + 3) / 4;
   if (blocks > 148LL * 64) blocks = 148LL * 64;
@@ -349,58 +350,16 @@ __device__ __forceinline__ void matvec(const double (&P)[4][4], const double (&c
   }
 }
 
-// Messages of one child for the NS columns of this thread and the child's scaler counts.
-//   src >= 0  tip: column `code` of the staged Q block; `codes` holds the lane's NS byte offsets
-//   src == -1 the running result in registers
-//   else      a parked CLV
-// `rec` is the shared-space address of the child's staged record.
+// Messages of a tip child for the NS columns of this thread: column `code` of the staged Q block
+// (`codes` holds the lane's NS byte offsets into it; `rec` is the block's shared-space address).
 template <int NS>
-__device__ __forceinline__ void child_messages(int src, unsigned rec, unsigned codes,
-                                               const double (&reg)[NS][4], const int (&reg_cnt)[NS],
-                                               const SlotIO<NS>& io, double (&m)[NS][4], int (&cnt)[NS]) {
-  if (src >= 0) {
+__device__ __forceinline__ void tip_messages(unsigned rec, unsigned codes, double (&m)[NS][4]) {
 #pragma unroll
-    for (int u = 0; u < NS; ++u) {
-      const unsigned off = (codes >> (8 * u)) & 0xffu;
-      const double2 q01 = lds_f64x2(rec + off);
-      const double2 q23 = lds_f64x2(rec + off + 16);
-      m[u][0] = q01.x; m[u][1] = q01.y; m[u][2] = q23.x; m[u][3] = q23.y;
-      cnt[u] = 0;
-    }
-    return;
-  }
-  double P[4][4];
-  load_p(rec, P);
-  if (src == -1) {
-#pragma unroll
-    for (int u = 0; u < NS; ++u) {
-      matvec(P, reg[u], m[u]);
-      cnt[u] = reg_cnt[u];
-    }
-    return;
-  }
-  const int slot = -2 - src;
-  if (io.in_smem(slot)) {
-    const unsigned clv = io.shared_clv(slot), sc = io.shared_cnt(slot);
-#pragma unroll
-    for (int u = 0; u < NS; ++u) {
-      double c[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) c[j] = lds_f64(clv + (u * 4 + j) * 32 * 8);
-      matvec(P, c, m[u]);
-      cnt[u] = lds_s32(sc + u * 32 * 4);
-    }
-  } else {
-    const double* clv = io.global_clv(slot);
-    const int* sc = io.global_cnt(slot);
-#pragma unroll
-    for (int u = 0; u < NS; ++u) {
-      double c[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) c[j] = clv[(u * 4 + j) * 32];
-      matvec(P, c, m[u]);
-      cnt[u] = sc[u * 32];
-    }
+  for (int u = 0; u < NS; ++u) {
+    const unsigned off = (codes >> (8 * u)) & 0xffu;
+    const double2 q01 = lds_f64x2(rec + off);
+    const double2 q23 = lds_f64x2(rec + off + 16);
+    m[u][0] = q01.x; m[u][1] = q01.y; m[u][2] = q23.x; m[u][3] = q23.y;
   }
 }
 
@@ -425,28 +384,6 @@ __device__ __forceinline__ void park(const SlotIO<NS>& io, int slot, const doubl
     }
   }
 }
-template <int NS>
-__device__ __forceinline__ void unpark(const SlotIO<NS>& io, int slot, double (&reg)[NS][4], int (&reg_cnt)[NS]) {
-  if (io.in_smem(slot)) {
-    const unsigned clv = io.shared_clv(slot), sc = io.shared_cnt(slot);
-#pragma unroll
-    for (int u = 0; u < NS; ++u) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) reg[u][i] = lds_f64(clv + (u * 4 + i) * 32 * 8);
-      reg_cnt[u] = lds_s32(sc + u * 32 * 4);
-    }
-  } else {
-    const double* clv = io.global_clv(slot);
-    const int* sc = io.global_cnt(slot);
-#pragma unroll
-    for (int u = 0; u < NS; ++u) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) reg[u][i] = clv[(u * 4 + i) * 32];
-      reg_cnt[u] = sc[u * 32];
-    }
-  }
-}
-
 // dynamic part: the parked CLV levels; static part: the two rings (compile-time addresses, so the
 // ring reads need no base register)
 static size_t prune_dynamic_smem_bytes(int ns, int smem_slots) {
@@ -486,7 +423,7 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   unsigned phase = 0;  // bit i: the parity the next wait on bars[i] looks for
   constexpr unsigned kBlkBytes = kBlk * kStepBytes, kHalfBytes = 32 * sizeof(int4);
   const int n_blocks = (n_iter + kBlk - 1) / kBlk, n_halves = (n_iter + 31) / 32;
-  const size_t pass_bytes = (size_t)NB * kRecDoubles * 8;  // records of one (tree, category)
+  const size_t pass_bytes = (size_t)records_per_pass(T) * kRecDoubles * 8;  // records of one (tree, category)
   const unsigned code_pitch = (unsigned)cfg.n_tiles * 32u;  // words per tip row (the table is far below 2^32 words)
 
   // work item = (tree, tile, category): the categories of a tile are independent until k_edge sums
@@ -562,39 +499,125 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
           if (st_next.x >= 0) cA_next = __ldg(my_codes + (unsigned)st_next.x * code_pitch);
           if (st_next.y >= 0) cB_next = __ldg(my_codes + (unsigned)st_next.y * code_pitch);
         }
-        if (s < n_steps) {
-          double ma[NS][4], mb[NS][4];
-          int ca[NS], cb[NS];
-          child_messages<NS>(st.x, recA, cA, reg, reg_cnt, io, ma, ca);
-          child_messages<NS>(st.y, recA + kRecDoubles * 8, cB, reg, reg_cnt, io, mb, cb);
-          // Pattern columns: the node under which the naive tip hangs keeps the other child's
-          // message only; k_edge multiplies the naive tip's Q column in, per xMSA column.
-          const bool defer_a = cfg.defer_naive && st.x == 0, defer_b = cfg.defer_naive && st.y == 0;
-          if (defer_a | defer_b) {
-            naive_br = 2 * s + (defer_a ? 0 : 1);
+        // A step combines two messages (core_partials.c:617-628). At most one child is the running
+        // result (REG) and a parked child only ever meets REG, so a step is: the message of the
+        // "other" child (a tip's column lookup, or a parked CLV through its matrix), times REG through
+        // its matrix - or a second lookup for a cherry. The edge evaluation is one more step of the
+        // same shape: its records are the root edge (child side, st.y) and an identity (root side,
+        // st.x), and the two messages go to k_edge instead of being multiplied.
+        const bool last = s == n_steps;
+        const unsigned recX = last ? recA + kRecDoubles * 8 : recA;  // record of child st.x
+        const unsigned recY = last ? recA : recA + kRecDoubles * 8;  // record of child st.y
+        const bool a_reg = st.x == -1, any_reg = a_reg | (st.y == -1);
+        const int o_src = a_reg ? st.y : st.x;
+        const unsigned o_rec = a_reg ? recY : recX, o_codes = a_reg ? cB : cA;
+        double m[NS][4];
+        int mc[NS];
+        // Pattern columns: the node under which the naive tip (row 0) hangs keeps the other child's
+        // message only; k_edge multiplies the naive tip's Q column in, per xMSA column, and applies
+        // the node's rescaling test then.
+        bool deferred = false;
+        if (o_src >= 0) {
+#pragma unroll
+          for (int u = 0; u < NS; ++u) mc[u] = 0;
+          if (cfg.defer_naive && o_src == 0) {
+            deferred = true;
+            naive_br = 2 * s + (o_rec != recA ? 1 : 0);
+#pragma unroll
+            for (int u = 0; u < NS; ++u)
+#pragma unroll
+              for (int i = 0; i < 4; ++i) m[u][i] = 1.0;
+          } else {
+            tip_messages<NS>(o_rec, o_codes, m);
+          }
+        } else {
+          double P[4][4];
+          load_p(o_rec, P);
+          const int slot = -2 - o_src;
+          if (io.in_smem(slot)) {
+            const unsigned clv = io.shared_clv(slot), sc = io.shared_cnt(slot);
+#pragma unroll
+            for (int u = 0; u < NS; ++u) {
+              double c[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) c[j] = lds_f64(clv + (u * 4 + j) * 32 * 8);
+              matvec(P, c, m[u]);
+              mc[u] = lds_s32(sc + u * 32 * 4);
+            }
+          } else {
+            const double* clv = io.global_clv(slot);
+            const int* sc = io.global_cnt(slot);
+#pragma unroll
+            for (int u = 0; u < NS; ++u) {
+              double c[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) c[j] = clv[(u * 4 + j) * 32];
+              matvec(P, c, m[u]);
+              mc[u] = sc[u * 32];
+            }
+          }
+        }
+        if (any_reg) {
+          double P[4][4];
+          load_p(a_reg ? recX : recY, P);
+          if (!last) {
+#pragma unroll
+            for (int u = 0; u < NS; ++u) {
+              double mr[4];
+              matvec(P, reg[u], mr);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) reg[u][i] = m[u][i] * mr[i];  // core_partials.c:626
+              reg_cnt[u] += mc[u];  // fill_parent_scaler, core_partials.c:24-46
+            }
+          } else {
+            // ---- edge term of this category (core_likelihood_avx.c:1130-1239): hand its inputs to
+            // k_edge, rows 0..3 the message of the node across the edge, rows 4..7 the root CLV ----
+            double* eo = cfg.ebuf + (size_t)lt * cfg.e_stride + (size_t)k * 8 * cfg.cols_pad + tile * (32 * NS) + lane;
+            int* co = cfg.ecnt + (size_t)lt * cfg.c_stride + (size_t)k * cfg.cols_pad + tile * (32 * NS) + lane;
+            double* e_other = eo + (a_reg ? (size_t)0 : (size_t)4 * cfg.cols_pad);  // st.x is the root side
+            double* e_reg = eo + (a_reg ? (size_t)4 * cfg.cols_pad : (size_t)0);
+#pragma unroll
+            for (int u = 0; u < NS; ++u) {
+              double mr[4];
+              matvec(P, reg[u], mr);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                e_other[(size_t)i * cfg.cols_pad + u * 32] = m[u][i];
+                e_reg[(size_t)i * cfg.cols_pad + u * 32] = mr[i];
+              }
+              co[u * 32] = reg_cnt[u] + mc[u];
+            }
+          }
+        } else {  // a cherry: two tips
+          if (cfg.defer_naive && st.y == 0) {
+            deferred = true;
+            naive_br = 2 * s + 1;
 #pragma unroll
             for (int u = 0; u < NS; ++u) {
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                ma[u][i] = defer_a ? mb[u][i] : ma[u][i];
-                mb[u][i] = 1.0;
-              }
-              if (defer_a) ca[u] = cb[u];
-              cb[u] = 0;
+              for (int i = 0; i < 4; ++i) reg[u][i] = m[u][i];
+              reg_cnt[u] = 0;
+            }
+          } else {
+            double m2[NS][4];
+            tip_messages<NS>(recY, cB, m2);
+#pragma unroll
+            for (int u = 0; u < NS; ++u) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) reg[u][i] = m[u][i] * m2[u][i];
+              reg_cnt[u] = 0;
             }
           }
+        }
+        if (!last) {
           int lowest = 0x7fffffff;  // min over columns of the largest high word
 #pragma unroll
           for (int u = 0; u < NS; ++u) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) reg[u][i] = ma[u][i] * mb[u][i];  // core_partials.c:626
-            reg_cnt[u] = ca[u] + cb[u];  // fill_parent_scaler, core_partials.c:24-46
             const int hi = max(max(__double2hiint(reg[u][0]), __double2hiint(reg[u][1])),
                                max(__double2hiint(reg[u][2]), __double2hiint(reg[u][3])));
             lowest = min(lowest, hi);
           }
-          // (a deferred node is rescaled by k_edge, once the naive factor is in)
-          if (lowest < kThresholdHi && !(defer_a | defer_b)) {  // some column has all four entries below 2^-256
+          if (lowest < kThresholdHi && !deferred) {  // some column has all four entries below 2^-256
 #pragma unroll
             for (int u = 0; u < NS; ++u) {
               const int hi = max(max(__double2hiint(reg[u][0]), __double2hiint(reg[u][1])),
@@ -607,26 +630,6 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
             }
           }
           if (st.z >= 0) park<NS>(io, st.z, reg, reg_cnt);
-        } else {
-          // ---- edge term of this category (core_likelihood_avx.c:1130-1239); the edge's record
-          // sits in the first branch position of the last step, st.y is the child across it ----
-          double mc[NS][4];
-          int cc[NS];
-          child_messages<NS>(st.y, recA, cB, reg, reg_cnt, io, mc, cc);
-          if (st.x != -1) unpark<NS>(io, -2 - st.x, reg, reg_cnt);  // the root CLV was parked; fetch it
-          // hand the edge term's inputs to k_edge
-          double* eo = cfg.ebuf + (size_t)lt * cfg.e_stride + (size_t)k * 8 * cfg.cols_pad + tile * (32 * NS) + lane;
-          int* co = cfg.ecnt + (size_t)lt * cfg.c_stride + (size_t)k * cfg.cols_pad + tile * (32 * NS) + lane;
-#pragma unroll
-          for (int u = 0; u < NS; ++u) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              eo[(size_t)i * cfg.cols_pad + u * 32] = mc[u][i];
-              eo[(size_t)(4 + i) * cfg.cols_pad + u * 32] = reg[u][i];
-            }
-            co[u * 32] = reg_cnt[u] + cc[u];
-          }
-          if (cfg.defer_naive && st.y == 0) naive_br = 2 * n_steps;
         }
         }
         __syncwarp();  // every lane is done with this block's records (and, at a half's end, its plan entries)
@@ -952,7 +955,7 @@ __global__ void __launch_bounds__(32, LH_SR_MIN_CTAS) k_prune_sr(FamilyDev f, Ba
   const unsigned ring_rec_s = (unsigned)__cvta_generic_to_shared(ring_rec) + lane * 16;
   const unsigned ring_step_s = (unsigned)__cvta_generic_to_shared(ring_step);
   const unsigned ring_idx_s = (unsigned)__cvta_generic_to_shared(ring_idx);
-  const size_t pass_bytes = (size_t)NB * kRecDoubles * 8;
+  const size_t pass_bytes = (size_t)records_per_pass(T) * kRecDoubles * 8;  // (the closing identity record is staged, never read)
 
   const int n_work = nlist * R;
   for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
@@ -1124,7 +1127,7 @@ __global__ void __launch_bounds__(128) k_edge(FamilyDev f, BatchDev b, EdgeCfg c
       }
       int c = cfg.ecnt[(size_t)lt * cfg.c_stride + (size_t)k * pitch + col];
       if (nbr >= 0) {
-        const double* q = b.prec + (((size_t)lt * R + k) * NB + nbr) * kRecDoubles + code * 4;
+        const double* q = b.prec + (((size_t)lt * R + k) * records_per_pass(f.T) + nbr) * kRecDoubles + code * 4;
         if (nbr == edge_br) {  // the naive tip is the node across the root edge
 #pragma unroll
           for (int i = 0; i < 4; ++i) mc[i] = q[i];

@@ -29,6 +29,13 @@ struct FamilyDev {
   int32_t g_max, s_max;         // max genes per region, max states per region
 };
 
+// Branch records of one (tree, category) pass: the 2T-3 branches in the order the program consumes
+// them, then one identity record (the root CLV's side of the edge evaluation).
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+inline int records_per_pass(int n_tips) { return 2 * n_tips - 2; }
+
 struct BatchDev {
   int32_t B, R;
   const int4* plan;      // [B][T-1]
@@ -37,7 +44,7 @@ struct BatchDev {
   const double* pi;      // [B][4]
   const double* rates;   // [B][R]
   double* eig;           // [B][kEigStride]
-  double* prec;          // [chunk][R][2T-3][20] branch records
+  double* prec;          // [chunk][R][records_per_pass(T)][20] branch records
   double* xe;            // [B][S] xmsa_emission
   double* loglik;        // [B]
 };
