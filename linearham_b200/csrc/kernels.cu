@@ -512,14 +512,11 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
         const int o_src = a_reg ? st.y : st.x;
         const unsigned o_rec = a_reg ? recY : recX, o_codes = a_reg ? cB : cA;
         double m[NS][4];
-        int mc[NS];
         // Pattern columns: the node under which the naive tip (row 0) hangs keeps the other child's
-        // message only; k_edge multiplies the naive tip's Q column in, per xMSA column, and applies
-        // the node's rescaling test then.
+        // message only (a factor of exactly 1 stands in for the tip's); k_edge multiplies the naive
+        // tip's Q column in, per xMSA column, and applies the node's rescaling test then.
         bool deferred = false;
         if (o_src >= 0) {
-#pragma unroll
-          for (int u = 0; u < NS; ++u) mc[u] = 0;
           if (cfg.defer_naive && o_src == 0) {
             deferred = true;
             naive_br = 2 * s + (o_rec != recA ? 1 : 0);
@@ -531,6 +528,8 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
             tip_messages<NS>(o_rec, o_codes, m);
           }
         } else {
+          // a parked CLV through its matrix; its scaler counts join REG's right away (a parked child
+          // only ever meets REG; fill_parent_scaler, core_partials.c:24-46)
           double P[4][4];
           load_p(o_rec, P);
           const int slot = -2 - o_src;
@@ -542,7 +541,7 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
 #pragma unroll
               for (int j = 0; j < 4; ++j) c[j] = lds_f64(clv + (u * 4 + j) * 32 * 8);
               matvec(P, c, m[u]);
-              mc[u] = lds_s32(sc + u * 32 * 4);
+              reg_cnt[u] += lds_s32(sc + u * 32 * 4);
             }
           } else {
             const double* clv = io.global_clv(slot);
@@ -553,7 +552,7 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
 #pragma unroll
               for (int j = 0; j < 4; ++j) c[j] = clv[(u * 4 + j) * 32];
               matvec(P, c, m[u]);
-              mc[u] = sc[u * 32];
+              reg_cnt[u] += sc[u * 32];
             }
           }
         }
@@ -567,7 +566,6 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
               matvec(P, reg[u], mr);
 #pragma unroll
               for (int i = 0; i < 4; ++i) reg[u][i] = m[u][i] * mr[i];  // core_partials.c:626
-              reg_cnt[u] += mc[u];  // fill_parent_scaler, core_partials.c:24-46
             }
           } else {
             // ---- edge term of this category (core_likelihood_avx.c:1130-1239): hand its inputs to
@@ -585,28 +583,26 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
                 e_other[(size_t)i * cfg.cols_pad + u * 32] = m[u][i];
                 e_reg[(size_t)i * cfg.cols_pad + u * 32] = mr[i];
               }
-              co[u * 32] = reg_cnt[u] + mc[u];
+              co[u * 32] = reg_cnt[u];
             }
           }
         } else {  // a cherry: two tips
+          double m2[NS][4];
           if (cfg.defer_naive && st.y == 0) {
             deferred = true;
             naive_br = 2 * s + 1;
 #pragma unroll
-            for (int u = 0; u < NS; ++u) {
+            for (int u = 0; u < NS; ++u)
 #pragma unroll
-              for (int i = 0; i < 4; ++i) reg[u][i] = m[u][i];
-              reg_cnt[u] = 0;
-            }
+              for (int i = 0; i < 4; ++i) m2[u][i] = 1.0;
           } else {
-            double m2[NS][4];
             tip_messages<NS>(recY, cB, m2);
+          }
 #pragma unroll
-            for (int u = 0; u < NS; ++u) {
+          for (int u = 0; u < NS; ++u) {
 #pragma unroll
-              for (int i = 0; i < 4; ++i) reg[u][i] = m[u][i] * m2[u][i];
-              reg_cnt[u] = 0;
-            }
+            for (int i = 0; i < 4; ++i) reg[u][i] = m[u][i] * m2[u][i];
+            reg_cnt[u] = 0;
           }
         }
         if (!last) {
