@@ -14,6 +14,8 @@
 // FP64 kind), and the HMM transition matrices are ~5 % dense.
 #include "kernels.hpp"
 
+#include <cstddef>
+
 #include <cfloat>
 #include <cmath>
 
@@ -279,6 +281,12 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
       : "memory");
 }
 
+__device__ __forceinline__ unsigned shared_address_opaque(const void* p) {
+  unsigned a;
+  asm volatile("{\n.reg .u64 t;\ncvta.to.shared.u64 t, %1;\ncvt.u32.u64 %0, t;\n}\n" : "=r"(a) : "l"(p));
+  return a;
+}
+
 // Shared-memory accesses by 32-bit shared-space address: through generic pointers every access
 // site first rebuilds the CTA's shared window base (S2UR SR_CgaCtaId, UMOV, ULEA).
 __device__ __forceinline__ double2 lds_f64x2(unsigned a) {
@@ -401,19 +409,25 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   const int lane = threadIdx.x, T = f.T, R = b.R;
   const int NB = 2 * T - 3, n_steps = T - 2, n_iter = T - 1;  // node updates + the edge evaluation
   const int gslots = cfg.total_slots - cfg.smem_slots;
-  __shared__ __align__(16) double ring_rec[2 * kBlk * 2 * kRecDoubles];  // two blocks of kBlk steps
-  __shared__ int4 ring_plan[kPlanRing];                                  // two halves of 32 steps
-  __shared__ __align__(8) unsigned long long bars[4];                    // records 0/1, plan 0/1
+  struct __align__(16) Rings {
+    double rec[2 * kBlk * 2 * kRecDoubles];  // two blocks of kBlk steps of branch records
+    int4 plan[kPlanRing];                    // two halves of 32 steps
+    unsigned long long bars[4];              // mbarriers: records 0/1, plan 0/1
+  };
+  __shared__ Rings rings;
+  // One register holds the shared-space address everything static hangs off, one the dynamic part's.
+  // (Opaque to the compiler on purpose: it would otherwise rebuild the window base at every use.)
+  const unsigned rings_s = shared_address_opaque(&rings);
+  const unsigned ring_rec_0 = rings_s + (unsigned)offsetof(Rings, rec);
+  const unsigned ring_plan_s = rings_s + (unsigned)offsetof(Rings, plan);
+  const unsigned bars_s = rings_s + (unsigned)offsetof(Rings, bars);
   SlotIO<NS> io;
-  io.s_clv = (unsigned)__cvta_generic_to_shared(smem_raw) + lane * 8;
-  io.s_cnt = (unsigned)__cvta_generic_to_shared(smem_raw) + (unsigned)cfg.smem_slots * (4 * NS * 32 * 8) + lane * 4;
+  io.s_clv = shared_address_opaque(smem_raw) + lane * 8;
+  io.s_cnt = io.s_clv + (unsigned)cfg.smem_slots * (4 * NS * 32 * 8) - lane * 4;
   io.g_clv = cfg.scratch + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * (4 * NS) * 32 + lane;
   io.g_cnt = cfg.scratch_cnt + (size_t)blockIdx.x * (gslots > 0 ? gslots : 0) * NS * 32 + lane;
   io.smem_slots = cfg.smem_slots;
   io.smem_lo = cfg.smem_lo;
-  const unsigned ring_rec_0 = (unsigned)__cvta_generic_to_shared(ring_rec);
-  const unsigned ring_plan_s = (unsigned)__cvta_generic_to_shared(ring_plan);
-  const unsigned bars_s = (unsigned)__cvta_generic_to_shared(bars);
   if (lane == 0) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) mbar_init(bars_s + 8 * i, 1);
