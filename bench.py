@@ -269,8 +269,12 @@ def main():
     if args.opt:
         config["options"] = list(args.opt)
     gathered = None
+    # ranks of one node share its host cores: each takes its share for traversal planning and Newick ingest
+    host_threads = max(2, cores // int(os.environ.get("LOCAL_WORLD_SIZE", world))) if world > 1 else cores
     if world > 1:
         f.set_option("stream", torch.cuda.current_stream().cuda_stream)
+        f.set_option("host_threads", host_threads)
+        phmm.set_host_threads(host_threads)
 
     class _DevArr:
         def __init__(self, ptr, n):
@@ -413,11 +417,11 @@ def main():
             "cpu_baseline": cpu_baseline,
             "e2e": None if e2e_s is None else {"value": B_total * args.steps / e2e_s, "unit": UNIT,
                                                "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
-                                               "host_plan_ms_per_step_rank0": ms_plan, "last_call_ms_rank0": e2e_detail,
+                                               "host_plan_ms_per_step_rank0": ms_plan, "host_threads_per_rank": host_threads, "last_call_ms_rank0": e2e_detail,
                                                "api": "lh_score_batch (host arrays in, host log-likelihoods out)"},
             "e2e_newick": None if nw_s is None else {
                 "value": nw_n * world * args.steps / nw_s, "unit": UNIT, "trees_per_step": nw_n * world,
-                "host_threads": cores,
+                "host_threads": host_threads,
                 "api": "PhyloHMM::ScoreSamples (Newick strings + er/pi/alpha in, log-likelihoods out; "
                        "Newick ingest on host threads overlapped with lh_score_batch)"},
             "gpu_launches": launches_total, "clocks": clocks, "parity": parity,

@@ -51,6 +51,9 @@ typedef struct lhh_phylohmm lhh_phylohmm_t;
 lhh_phylohmm_t* lhh_phylohmm_new(const char* yaml_path, int32_t cluster_ind, const char* hmm_param_dir, int32_t seed);
 void lhh_phylohmm_free(lhh_phylohmm_t* h);
 int lhh_phylohmm_set_device(lhh_phylohmm_t* h, int32_t device);
+/* Host threads this object may use (Newick ingest and traversal planning); 0 = all hardware threads.
+ * A job with several ranks per node gives each rank its share. */
+int lhh_phylohmm_set_host_threads(lhh_phylohmm_t* h, int32_t n_threads);
 /* The flat family description for lh_family_create; pointers live as long as the handle. */
 int lhh_phylohmm_family_desc(lhh_phylohmm_t* h, struct lh_family_desc* out);
 /* InitializePhyloParameters(newick_path, er, pi, alpha, num_rates) - src/PhyloHMM.cpp:350-361 */

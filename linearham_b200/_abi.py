@@ -198,7 +198,7 @@ def bind_host(lib):
     return lib
 
 
-HOST_SYMBOLS += ["lhh_phylohmm_new", "lhh_phylohmm_free", "lhh_phylohmm_set_device", "lhh_phylohmm_family_desc",
+HOST_SYMBOLS += ["lhh_phylohmm_new", "lhh_phylohmm_free", "lhh_phylohmm_set_device", "lhh_phylohmm_set_host_threads", "lhh_phylohmm_family_desc",
                  "lhh_phylohmm_init_params", "lhh_phylohmm_init_emission", "lhh_phylohmm_loglikelihood",
                  "lhh_phylohmm_sample_naive", "lhh_phylohmm_run_pipeline", "lhh_phylohmm_score_samples",
                  "lhh_export_newick", "lhh_phylohmm_get_f64", "lhh_phylohmm_get_i32", "lhh_phylohmm_get_str"]
@@ -210,6 +210,7 @@ def bind_phylohmm(lib):
     lib.lhh_phylohmm_free.argtypes = [C.c_void_p]
     lib.lhh_phylohmm_free.restype = None
     lib.lhh_phylohmm_set_device.argtypes = [C.c_void_p, C.c_int32]
+    lib.lhh_phylohmm_set_host_threads.argtypes = [C.c_void_p, C.c_int32]
     lib.lhh_phylohmm_family_desc.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
     lib.lhh_phylohmm_init_params.argtypes = [C.c_void_p, C.c_char_p, _f64p, _f64p, C.c_double, C.c_int32]
     lib.lhh_phylohmm_init_emission.argtypes = [C.c_void_p]

@@ -91,6 +91,9 @@ void lhh_phylohmm_free(lhh_phylohmm_t* h) { delete reinterpret_cast<Handle*>(h);
 int lhh_phylohmm_set_device(lhh_phylohmm_t* h, int32_t device) {
   return guarded([&] { H(h).set_device(device); });
 }
+int lhh_phylohmm_set_host_threads(lhh_phylohmm_t* h, int32_t n_threads) {
+  return guarded([&] { H(h).set_host_threads(n_threads); });
+}
 
 int lhh_phylohmm_family_desc(lhh_phylohmm_t* h, lh_family_desc_t* out) {
   return guarded([&] { *out = H(h).family_desc(); });

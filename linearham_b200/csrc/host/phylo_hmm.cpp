@@ -287,6 +287,13 @@ const lh_family_desc& PhyloHMM::family_desc() const { return flat_->desc; }
 void PhyloHMM::EnsureDeviceFamily() {
   if (dev_family_) return;
   if (lh_family_create(&dev_family_, &flat_->desc, device_)) throw std::runtime_error(lh_last_error());
+  if (host_threads_ > 0 && lh_set_option(dev_family_, "host_threads", host_threads_)) throw std::runtime_error(lh_last_error());
+}
+
+void PhyloHMM::set_host_threads(int n) {
+  if (n < 0) throw std::invalid_argument("host thread count must not be negative");
+  host_threads_ = n;
+  if (dev_family_ && n > 0 && lh_set_option(dev_family_, "host_threads", n)) throw std::runtime_error(lh_last_error());
 }
 
 // src/PhyloHMM.cpp:350-361
@@ -395,7 +402,7 @@ void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er,
     f.root_blen.resize(n);
     f.rates.resize((std::size_t)n * num_rates);
     f.err.clear();
-    if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), n, newicks + f.b0, 0, f.children.data(), f.blen.data(),
+    if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), n, newicks + f.b0, host_threads_, f.children.data(), f.blen.data(),
                           f.root_child.data(), f.root_blen.data()) ||
         lhh_gamma_cats_batch(n, alpha + f.b0, num_rates, f.rates.data()))
       f.err = lhh_last_error();

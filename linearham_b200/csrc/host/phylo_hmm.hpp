@@ -178,6 +178,8 @@ class PhyloHMM : public HMM {
                     int num_rates, double* loglik);
 
   void set_device(int device) { device_ = device; }
+  // host threads for Newick ingest and traversal planning (0 = all hardware threads)
+  void set_host_threads(int n);
 
   const MatrixXi& xmsa() const { return xmsa_; }
   const std::vector<std::string>& xmsa_labels() const { return xmsa_labels_; }
@@ -231,7 +233,7 @@ class PhyloHMM : public HMM {
 
   std::unique_ptr<FlatFamily> flat_;
   lh_family* dev_family_ = nullptr;
-  int device_ = 0;
+  int device_ = 0, host_threads_ = 0;
 };
 
 typedef std::shared_ptr<PhyloHMM> PhyloHMMPtr;

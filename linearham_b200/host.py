@@ -84,6 +84,10 @@ class PhyloHMM:
             raise HostError(self._lib.lhh_last_error().decode())
         _ck(self._lib.lhh_phylohmm_set_device(self._h, int(device)))
 
+    def set_host_threads(self, n):
+        """host threads for Newick ingest and traversal planning (0 = all hardware threads)"""
+        _ck(self._lib.lhh_phylohmm_set_host_threads(self._h, int(n)))
+
     def close(self):
         if getattr(self, "_h", None):
             self._lib.lhh_phylohmm_free(self._h)
