@@ -886,16 +886,21 @@ int stage_lists(lh_family* f, std::vector<int> starts, cudaStream_t s) {
 
 // Chunk boundaries: 16-wave chunks for a resident batch; the pipelined call opens with chunks of
 // one and two waves (the first kernels start after a sliver of the host planning) and goes on in
-// chunks of `pipe_waves` waves.
+// chunks of `pipe_waves` waves. A batch too small for that (a shard of a multi-GPU job) is cut
+// into about four chunks of whole waves, so that planning and kernels still overlap.
 std::vector<int> chunk_starts(const lh_family* f, bool pipelined) {
   std::vector<int> st;
   int t0 = 0;
-  if (pipelined && f->wave_pipe > 0 && f->chunk_pipe >= 4 * f->wave_pipe && f->B >= 2 * f->chunk_pipe) {
-    st.push_back(0);
-    st.push_back(f->wave_pipe);
-    t0 = 3 * f->wave_pipe;
+  int step = pipelined ? f->chunk_pipe : f->chunk;
+  if (pipelined && f->wave_pipe > 0) {
+    if (f->chunk_pipe >= 4 * f->wave_pipe && f->B >= 2 * f->chunk_pipe) {
+      st.push_back(0);
+      st.push_back(f->wave_pipe);
+      t0 = 3 * f->wave_pipe;
+    } else {
+      step = std::min(step, std::max(f->wave_pipe, f->B / 4 / f->wave_pipe * f->wave_pipe));
+    }
   }
-  const int step = pipelined ? f->chunk_pipe : f->chunk;
   for (; t0 < f->B; t0 += step) st.push_back(t0);
   st.push_back(f->B);
   return st;
