@@ -176,6 +176,7 @@ struct lh_family {
   lhb::EdgeCfg ec{};
   lhb::HmmOut ho{};
   int chunk = 0, chunk_pipe = 0, wave_pipe = 0, seg = 0, occ[2] = {0, 0};
+  size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
   // trees that can run on site patterns (naive tip on the root edge or under the virtual root)
   std::vector<uint8_t> on_patterns;
   int n_pattern_trees = 0;
@@ -521,6 +522,7 @@ int configure_batch(lh_family* f, int B, int R) {
 
   // pruning launch configuration per column set in use: [0] all columns, [1] site patterns
   const size_t rec_bytes_tree = (size_t)lhb::records_per_pass(T) * 20 * R * sizeof(double);
+  f->rec_bytes_tree = rec_bytes_tree;
   int strahler = 1;
   while ((2 << (strahler - 1)) <= T) ++strahler;  // floor(log2 T) + 1
   const bool use[2] = {f->n_pattern_trees < B, f->n_pattern_trees > 0};
@@ -898,7 +900,10 @@ std::vector<int> chunk_starts(const lh_family* f, bool pipelined) {
       st.push_back(f->wave_pipe);
       t0 = 3 * f->wave_pipe;
     } else {
-      step = std::min(step, std::max(f->wave_pipe, f->B / 4 / f->wave_pipe * f->wave_pipe));
+      // (but no chunk so short - under ~2 ms of kernels, gauged by its bytes of branch records -
+      // that the per-chunk launches and stream hand-offs show)
+      const int floor_trees = (int)(((size_t)400 << 20) / f->rec_bytes_tree) / f->wave_pipe * f->wave_pipe;
+      step = std::min(step, std::max({f->wave_pipe, f->B / 4 / f->wave_pipe * f->wave_pipe, floor_trees}));
     }
   }
   for (; t0 < f->B; t0 += step) st.push_back(t0);
