@@ -169,7 +169,8 @@ int lh_measure_fp64_peak(int device, double* tflops);
 int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
 /* keys: "sites_per_thread" (0 = auto, 1..4: xMSA columns per thread; a CTA is one warp and
  * covers 32x that many columns), "smem_slots" (-1 = auto), "smem_lo" (-1 = auto: first CLV stack level
- * of the shared-memory window), "timing" (0/1), "host_threads",
+ * of the shared-memory window), "timing" (0/1), "host_threads", "hmm_overlap" (1 = default: the forward
+ * pass of a chunk runs on its own stream beside the next chunk's pruning),
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never
  * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "pipe_waves" (default 4:
  * lh_score_batch launches a chunk's kernels every that many waves of CTAs), "stream" (a

@@ -120,7 +120,7 @@ int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, std::v
 
 }  // namespace
 
-constexpr int kChunkEvents = 6;
+constexpr int kChunkEvents = 7;
 
 struct lh_family {
   int device = 0;
@@ -147,9 +147,16 @@ struct lh_family {
   cudaEvent_t misc_ev = nullptr, list_ev = nullptr;  // h_misc / h_list have been copied
   bool misc_busy = false, list_busy = false;
   cudaStream_t copy_stream = nullptr;
+  // The forward pass of a chunk runs here, beside the pruning of the next chunk (it is latency-bound:
+  // a chunk's worth of trees leaves most of every SM idle).
+  cudaStream_t hmm_stream = nullptr;
+  cudaEvent_t hmm_done = nullptr;
+  std::vector<cudaEvent_t> edge_ev;  // per chunk: k_edge finished
+  int opt_hmm_overlap = 1;
+  DevBuf d_counters;
   cudaEvent_t ev[8] = {};
   cudaEvent_t user_ev[8] = {};
-  std::vector<cudaEvent_t> chunk_ev;  // kChunkEvents per chunk: pmatrix, repeats, prune, edge, hmm start; hmm end
+  std::vector<cudaEvent_t> chunk_ev;  // kChunkEvents per chunk: start, pmatrix | repeats | prune | edge ends (compute stream); hmm start, hmm end (its stream)
   std::vector<cudaEvent_t> staged_ev;  // per chunk: its last segment has landed in HBM
   int n_chunks = 0;
   bool own_stream = true;
@@ -206,12 +213,13 @@ void lh_family_destroy(lh_family_t* f) {
   cudaSetDevice(f->device);
   if (f->stream) cudaStreamSynchronize(f->stream);
   if (f->copy_stream) cudaStreamSynchronize(f->copy_stream);
+  if (f->hmm_stream) cudaStreamSynchronize(f->hmm_stream);
   for (void* p : f->owned) cudaFree(p);
   DevBuf* bufs[] = {&f->d_plan, &f->d_pblen, &f->d_er, &f->d_pi, &f->d_rates, &f->d_eig, &f->d_prec,
                     &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
                     &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
                     &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_rs_steps,
-                    &f->d_rs_idx, &f->d_rs_ecls, &f->d_rs_peak, &f->d_rs_gclv, &f->d_rs_gcnt};
+                    &f->d_rs_idx, &f->d_rs_ecls, &f->d_rs_peak, &f->d_rs_gclv, &f->d_rs_gcnt, &f->d_counters};
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
   f->h_misc.release();
@@ -227,6 +235,9 @@ void lh_family_destroy(lh_family_t* f) {
   if (f->list_ev) cudaEventDestroy(f->list_ev);
   for (auto& e : f->chunk_ev) cudaEventDestroy(e);
   for (auto& e : f->staged_ev) cudaEventDestroy(e);
+  for (auto& e : f->edge_ev) cudaEventDestroy(e);
+  if (f->hmm_done) cudaEventDestroy(f->hmm_done);
+  if (f->hmm_stream) cudaStreamDestroy(f->hmm_stream);
   if (f->copy_stream) cudaStreamDestroy(f->copy_stream);
   if (f->stream && f->own_stream) cudaStreamDestroy(f->stream);
   delete f;
@@ -255,6 +266,10 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
     return bail(fail("cudaStreamCreate failed"));
   if (cudaStreamCreateWithFlags(&f->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
     return bail(fail("cudaStreamCreate failed"));
+  if (cudaStreamCreateWithFlags(&f->hmm_stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail("cudaStreamCreate failed"));
+  cudaEventCreateWithFlags(&f->hmm_done, cudaEventDisableTiming);
+  if (f->d_counters.reserve(64)) return bail(1);
   for (auto& ev : f->ring_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&f->misc_ev, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&f->list_ev, cudaEventDisableTiming);
@@ -372,6 +387,8 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_sr_arena = (int)value;
   } else if (k == "site_patterns") {
     f->opt_site_patterns = value != 0;
+  } else if (k == "hmm_overlap") {
+    f->opt_hmm_overlap = value != 0;
   } else if (k == "timing") {
     f->opt_timing = value != 0;
   } else if (k == "host_threads") {
@@ -815,6 +832,11 @@ int ensure_chunk_events(lh_family* f, int n_chunks) {
     LH_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     f->staged_ev.push_back(e);
   }
+  while ((int)f->edge_ev.size() < n_chunks) {
+    cudaEvent_t e;
+    LH_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    f->edge_ev.push_back(e);
+  }
   return 0;
 }
 
@@ -844,6 +866,7 @@ void launch_chunk(lh_family* f, int ci, int t0, int n) {
     if (!count[g]) continue;
     lhb::PruneCfg c = f->pc[g];
     c.tree_list = list[g];
+    c.work_counter = f->d_counters.as<int32_t>() + g;
     if (g == 1 && sr) {
       lhb::RepeatCfg r = f->rc;
       r.tree_list = list[1];
@@ -858,9 +881,23 @@ void launch_chunk(lh_family* f, int ci, int t0, int n) {
   if (tm) cudaEventRecord(ev[3], s);
   lhb::launch_edge(f->fd, f->bd, f->ec, t0, n, s);
   if (tm) cudaEventRecord(ev[4], s);
-  lhb::launch_hmm(f->fd, f->bd, f->ho, t0, n, s);
-  if (tm) cudaEventRecord(ev[5], s);
+  // the forward pass goes to its own stream: the next chunk's kernels do not wait for it
+  cudaStream_t hs = f->opt_hmm_overlap ? f->hmm_stream : s;
+  if (hs != s) {
+    cudaEventRecord(f->edge_ev[ci], s);
+    cudaStreamWaitEvent(hs, f->edge_ev[ci], 0);
+  }
+  if (tm) cudaEventRecord(ev[5], hs);
+  lhb::launch_hmm(f->fd, f->bd, f->ho, t0, n, hs);
+  if (tm) cudaEventRecord(ev[6], hs);
   f->tm.kernel_launches += 4;
+}
+
+// Makes the compute stream wait for the forward passes queued on the HMM stream.
+void join_hmm_stream(lh_family* f) {
+  if (!f->opt_hmm_overlap) return;
+  cudaEventRecord(f->hmm_done, f->hmm_stream);
+  cudaStreamWaitEvent(f->stream, f->hmm_done, 0);
 }
 
 // Fixes the chunk boundaries of the batch and queues the per-chunk tree lists on `s`.
@@ -940,6 +977,7 @@ int lh_batch_run(lh_family_t* f) {
   f->tm.prune_launches = 0;
   if (f->opt_timing) cudaEventRecord(f->ev[2], f->stream);
   for (int ci = 0; ci < f->n_chunks; ++ci) launch_chunk(f, ci, st[ci], st[ci + 1] - st[ci]);
+  join_hmm_stream(f);
   if (f->opt_timing) cudaEventRecord(f->ev[4], f->stream);
   LH_CUDA(cudaGetLastError());
   return 0;
@@ -949,10 +987,12 @@ int lh_batch_run(lh_family_t* f) {
 static int collect_run_timings(lh_family* f) {
   if (!f->opt_timing || f->B == 0 || f->n_chunks == 0) return 0;
   LH_CUDA(cudaEventSynchronize(f->ev[4]));
-  float sum[kChunkEvents - 1] = {}, x = 0;
+  // (k_hmm of a chunk overlaps the next chunk's kernels, so the stage times can add up to more than ms_kernels)
+  float sum[5] = {}, x = 0;
+  static const int from[5] = {0, 1, 2, 3, 5};
   for (int ci = 0; ci < f->n_chunks; ++ci)
-    for (int k = 0; k + 1 < kChunkEvents; ++k) {
-      cudaEventElapsedTime(&x, f->chunk_ev[kChunkEvents * ci + k], f->chunk_ev[kChunkEvents * ci + k + 1]);
+    for (int k = 0; k < 5; ++k) {
+      cudaEventElapsedTime(&x, f->chunk_ev[kChunkEvents * ci + from[k]], f->chunk_ev[kChunkEvents * ci + from[k] + 1]);
       sum[k] += x;
     }
   f->tm.ms_pmatrix = sum[0];
@@ -1057,6 +1097,7 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
     if (ci == 0 && f->opt_timing) cudaEventRecord(f->ev[2], f->stream);
     launch_chunk(f, ci, st[ci], st[ci + 1] - st[ci]);
   }
+  join_hmm_stream(f);
   if (f->opt_timing) {
     cudaEventRecord(f->ev[1], cs);
     cudaEventRecord(f->ev[4], f->stream);

@@ -444,7 +444,10 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   // them, and items this fine keep the last wave of a small batch full
   const int per_tree = cfg.n_tiles * R;
   const int n_work = ntrees * per_tree;
-  for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+  for (int w = blockIdx.x; w < n_work;) {
+    // claim the next item now; the answer is needed when this one is done
+    int w_next = 0;
+    if (lane == 0) w_next = (int)gridDim.x + atomicAdd(cfg.work_counter, 1);
     const int li = w / per_tree, rem = w - li * per_tree;
     const int tile = rem / R, k = rem - tile * R;
     const int t = __ldg(cfg.tree_list + li);
@@ -651,6 +654,7 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
     }
 
     if (tile == 0 && k == 0 && lane == 0) cfg.enaive[lt] = naive_br;
+    w = __shfl_sync(0xffffffffu, w_next, 0);
   }
 }
 
@@ -667,6 +671,7 @@ static void launch_prune_n(const FamilyDev& f, const BatchDev& b, const PruneCfg
                            int ntrees, cudaStream_t s) {
   size_t smem = prune_dynamic_smem_bytes(NS, c.smem_slots);
   cudaFuncSetAttribute(k_prune<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaMemsetAsync(c.work_counter, 0, sizeof(int32_t), s);
   k_prune<NS><<<c.grid, 32, smem, s>>>(f, b, c, tree0, ntrees);
 }
 

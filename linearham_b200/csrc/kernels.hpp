@@ -69,6 +69,10 @@ struct PruneCfg {
   int32_t cols_pad;      // n_tiles * 32 * NS
   int32_t defer_naive;   // 1: pattern columns, naive factor applied by k_edge
   const int32_t* tree_list;  // trees of this launch (batch indices inside the chunk)
+  // Work items beyond a CTA's first are handed out through this counter (zeroed before the launch):
+  // a CTA that starts late - the forward pass of the previous chunk may still hold part of an SM -
+  // simply takes fewer items.
+  int32_t* work_counter;
   // per (chunk tree, category, column) inputs of the edge term, written by k_prune:
   double* ebuf;          // tree at e_stride doubles: [R][8][cols_pad] message across the root edge [4], root CLV [4]
   int32_t* ecnt;         // tree at c_stride ints:    [R][cols_pad] scaler count of the two
