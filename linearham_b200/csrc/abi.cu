@@ -354,6 +354,40 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
   };
   rc |= junction(d->vd_inds, fd.vd_sites, fd.vd_states, &fd.vd_inds_rm);
   rc |= junction(d->dj_inds, fd.dj_sites, fd.dj_states, &fd.dj_inds_rm);
+  // per junction site, the states that can emit there (k_hmm skips the dot products of the others)
+  auto emitting = [&](const int32_t* cm, int L, int Sj, const int32_t** doff, const int2** dpairs) {
+    std::vector<int32_t> off(L + 1, 0), pairs;
+    for (int i = 0; i < L; ++i) {
+      for (int j = 0; j < Sj; ++j)
+        if (cm[(size_t)j * L + i] >= 0) {
+          pairs.push_back(j);
+          pairs.push_back(cm[(size_t)j * L + i]);
+        }
+      off[i + 1] = (int32_t)(pairs.size() / 2);
+    }
+    if (pairs.empty()) pairs.assign(2, 0);
+    const int32_t* flat = nullptr;
+    if (upload(off.data(), off.size(), doff, own) || upload(pairs.data(), pairs.size(), &flat, own)) return 1;
+    *dpairs = reinterpret_cast<const int2*>(flat);
+    return 0;
+  };
+  rc |= emitting(d->vd_inds, fd.vd_sites, fd.vd_states, &fd.vd_valid_off, &fd.vd_valid);
+  if (d->has_d) rc |= emitting(d->dj_inds, fd.dj_sites, fd.dj_states, &fd.dj_valid_off, &fd.dj_valid);
+  {
+    // a silent state's value is (finite dot product) * 0 = 0 as long as the dot product cannot overflow:
+    // rows are checked on the device (entries <= 1e150), the matrices here (entries <= 1e100)
+    bool small = true;
+    auto scan = [&](const double* m, size_t n) {
+      for (size_t i = 0; i < n; ++i) small &= (std::fabs(m[i]) <= 1e100);
+    };
+    scan(d->t_v_vd, (size_t)fd.n_v * fd.vd_states);
+    scan(d->t_vd, (size_t)fd.vd_states * fd.vd_states);
+    if (d->has_d) {
+      scan(d->t_d_dj, (size_t)fd.n_d * fd.dj_states);
+      scan(d->t_dj, (size_t)fd.dj_states * fd.dj_states);
+    }
+    fd.skip_silent = small ? 1 : 0;
+  }
   rc |= upload(d->v_gene_prob, fd.n_v, &fd.v_gene_prob, own);
   rc |= upload(d->v_trans_prod, fd.n_v, &fd.v_trans_prod, own);
   rc |= upload(d->vpad_trans, fd.n_v, &fd.vpad_trans, own);

@@ -1207,16 +1207,22 @@ __device__ __forceinline__ int warp_max_i(int v) {
 // ScaleMatrix (src/utils.cpp:135-144) on a row of n doubles owned by the warp
 // (entry j belongs to lane j % 32). Multiplying by 2^256 is exact, so the number of
 // rounds the reference's while-loop makes is determined by the smallest positive entry.
-__device__ __forceinline__ int warp_scale_row(double* row, int n, int lane) {
-  double mn = DBL_MAX;
+// `tame` comes back true when every entry of the scaled row is a number no larger than 1e150.
+__device__ __forceinline__ int warp_scale_row(double* row, int n, int lane, bool& tame) {
+  double mn = DBL_MAX, mx = 0.0;
+  bool odd = false;  // NaN, infinity or a negative entry
   for (int j = lane; j < n; j += 32) {
     const double v = row[j];
     if (v > 0.0 && v < mn) mn = v;
+    mx = fmax(mx, v);
+    odd |= !(v >= 0.0 && v <= DBL_MAX);
   }
   mn = warp_min(mn);
+  mx = -warp_min(-mx);
   int rounds = 0;
   while (mn < LH_SCALE_THRESHOLD) {
     mn *= LH_SCALE_FACTOR;
+    mx *= LH_SCALE_FACTOR;
     ++rounds;
   }
   if (rounds) {
@@ -1226,8 +1232,13 @@ __device__ __forceinline__ int warp_scale_row(double* row, int n, int lane) {
       row[j] = v;
     }
   }
+  tame = !__any_sync(0xffffffffu, odd) && mx <= 1e150;
   __syncwarp();
   return rounds;
+}
+__device__ __forceinline__ int warp_scale_row(double* row, int n, int lane) {
+  bool tame;
+  return warp_scale_row(row, n, lane, tame);
 }
 
 // FillGermlinePaddingEmission (src/PhyloHMM.cpp:158-193) for one region: lane g owns
@@ -1272,20 +1283,36 @@ __device__ __forceinline__ double csc_dot(const CscDev& m, const double* prev, i
   return acc;
 }
 
-// ComputeJunctionForwardProbabilities (src/HMM.cpp:1107-1139)
-__device__ int junction_forward(const CscDev& t_in, const CscDev& t_jj, const int32_t* __restrict__ inds_rm,
-                                int L, int Sj, const double* __restrict__ xe, double*& prev,
-                                double*& cur, int count, double* fwd_out, int32_t* cnt_out, int lane) {
+// ComputeJunctionForwardProbabilities (src/HMM.cpp:1107-1139). Most (state, site) pairs of a junction
+// are silent - the state cannot emit at the site, its emission is 0 (FillJunctionEmission) - and their
+// value is (dot product) * 0. While the previous row is tame (finite, <= 1e150; the matrices are checked
+// on the host) that is exactly 0, so only the emitting states of a site get a dot product: 14 % of
+// them at the benchmark shapes. A row that is not tame takes the full path.
+__device__ int junction_forward(const FamilyDev& f, const CscDev& t_in, const CscDev& t_jj,
+                                const int32_t* __restrict__ inds_rm, const int32_t* __restrict__ valid_off,
+                                const int2* __restrict__ valid, int L, int Sj, const double* __restrict__ xe,
+                                double*& prev, double*& cur, int count, bool tame, double* fwd_out,
+                                int32_t* cnt_out, int lane) {
   for (int i = 0; i < L; ++i) {
     const CscDev& m = (i == 0) ? t_in : t_jj;
-    for (int j = lane; j < Sj; j += 32) {
-      double acc = csc_dot(m, prev, j);
-      const int idx = inds_rm[(size_t)i * Sj + j];
-      acc *= (idx < 0) ? 0.0 : xe[idx];   // FillJunctionEmission: 0 where idx == -1
-      cur[j] = acc;
+    if (tame && f.skip_silent) {
+      for (int j = lane; j < Sj; j += 32) cur[j] = 0.0;
+      __syncwarp();
+      const int e = valid_off[i + 1];
+      for (int q = valid_off[i] + lane; q < e; q += 32) {
+        const int2 sv = valid[q];
+        cur[sv.x] = csc_dot(m, prev, sv.x) * xe[sv.y];
+      }
+    } else {
+      for (int j = lane; j < Sj; j += 32) {
+        double acc = csc_dot(m, prev, j);
+        const int idx = inds_rm[(size_t)i * Sj + j];
+        acc *= (idx < 0) ? 0.0 : xe[idx];   // FillJunctionEmission: 0 where idx == -1
+        cur[j] = acc;
+      }
     }
     __syncwarp();
-    count += warp_scale_row(cur, Sj, lane);
+    count += warp_scale_row(cur, Sj, lane, tame);
     if (fwd_out)
       for (int j = lane; j < Sj; j += 32) fwd_out[(size_t)j * L + i] = cur[j];
     if (cnt_out && lane == 0) cnt_out[i] = count;
@@ -1330,12 +1357,14 @@ __global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o, 
       prev[g] = v;
     }
     __syncwarp();
-    c_v += warp_scale_row(prev, f.n_v, lane);
+    bool tame;
+    c_v += warp_scale_row(prev, f.n_v, lane, tame);
     if (o.vgerm_forward)
       for (int g = lane; g < f.n_v; g += 32) o.vgerm_forward[(size_t)t * f.n_v + g] = prev[g];
 
     // V-D (or V-J) junction
-    int cnt = junction_forward(f.t_v_vd, f.t_vd, f.vd_inds_rm, f.vd_sites, f.vd_states, xe, prev, cur, c_v,
+    int cnt = junction_forward(f, f.t_v_vd, f.t_vd, f.vd_inds_rm, f.vd_valid_off, f.vd_valid, f.vd_sites,
+                               f.vd_states, xe, prev, cur, c_v, tame,
                                o.vd_forward ? o.vd_forward + (size_t)t * f.vd_sites * f.vd_states : nullptr,
                                o.vd_scalers ? o.vd_scalers + (size_t)t * f.vd_sites : nullptr, lane);
     if (f.has_d) {
@@ -1346,11 +1375,12 @@ __global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o, 
         cur[g] = v;
       }
       __syncwarp();
-      c_d += cnt + warp_scale_row(cur, f.n_d, lane);
+      c_d += cnt + warp_scale_row(cur, f.n_d, lane, tame);
       if (o.dgerm_forward)
         for (int g = lane; g < f.n_d; g += 32) o.dgerm_forward[(size_t)t * f.n_d + g] = cur[g];
       { double* tmp = prev; prev = cur; cur = tmp; }
-      cnt = junction_forward(f.t_d_dj, f.t_dj, f.dj_inds_rm, f.dj_sites, f.dj_states, xe, prev, cur, c_d,
+      cnt = junction_forward(f, f.t_d_dj, f.t_dj, f.dj_inds_rm, f.dj_valid_off, f.dj_valid, f.dj_sites,
+                             f.dj_states, xe, prev, cur, c_d, tame,
                              o.dj_forward ? o.dj_forward + (size_t)t * f.dj_sites * f.dj_states : nullptr,
                              o.dj_scalers ? o.dj_scalers + (size_t)t * f.dj_sites : nullptr, lane);
     }

@@ -24,6 +24,11 @@ struct FamilyDev {
   const int32_t *jgerm_off, *jgerm_inds, *jpad_off, *jpad_inds;
   const int32_t* vd_inds_rm;    // [vd_sites][vd_states] row-major copy
   const int32_t* dj_inds_rm;
+  // the states that can emit at a junction site (xMSA index >= 0), site by site:
+  // pairs (state, xMSA index) [valid_off[i], valid_off[i+1]) for site i
+  const int32_t *vd_valid_off, *dj_valid_off;
+  const int2 *vd_valid, *dj_valid;
+  int32_t skip_silent;          // 1: every transition entry is small enough for the skip below to be exact
   const double *v_gene_prob, *v_trans_prod, *vpad_trans, *jpad_trans;
   CscDev t_v_vd, t_vd, t_vd_d, t_d_dj, t_dj, t_dj_j;
   int32_t g_max, s_max;         // max genes per region, max states per region
