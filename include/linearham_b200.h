@@ -148,6 +148,11 @@ int lh_device_count(int* n);
 
 int  lh_family_create(lh_family_t** out, const lh_family_desc_t* desc, int device);
 void lh_family_destroy(lh_family_t* fam);
+/* Bind another clonal family to an existing handle (what constructing the next PhyloHMM object,
+ * src/PhyloHMM.cpp:17-40, is to the reference): the family constants go to the handle's device
+ * arena in one copy; streams, planner threads, pinned staging and batch buffers are reused.
+ * After a failed rebind the handle holds no family until a rebind succeeds.                     */
+int  lh_family_rebind(lh_family_t* fam, const lh_family_desc_t* desc);
 
 /* Score B samples: host buffers in, host log-likelihoods out (synchronous).
  * Includes the host->device and device->host copies.                         */
@@ -186,6 +191,32 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
  * lh_batch_run calls on the stream the kernels are launched on.                          */
 int lh_timer_mark(lh_family_t* fam, int32_t slot);
 int lh_timer_elapsed_ms(lh_family_t* fam, int32_t from_slot, int32_t to_slot, float* ms);
+
+/* ---- repertoire: many independent clonal families on one device (BASELINE config 5) --------
+ * The reference runs one linearham process per cluster (SConstruct:344-352, 428-447;
+ * src/linearham.cpp:377-386). A repertoire keeps n_slots device handles; one host thread per slot
+ * pulls families off a queue (largest first), rebinds its handle and calls lh_score_batch, so the
+ * host planning / copies of one family overlap the kernels of another. Results do not depend on
+ * the slot, the order or n_slots.                                                             */
+typedef struct lh_repertoire lh_repertoire_t;
+typedef struct lh_repertoire_item {
+  const lh_family_desc_t* desc;   /* the family                                          */
+  const lh_tree_batch_t*  trees;  /* its tree samples                                    */
+  double*  loglik;                /* out [trees->n_trees]                                */
+  int32_t  status;                /* out: 0 scored, 1 failed, -1 not reached             */
+} lh_repertoire_item_t;
+typedef struct lh_repertoire_stats {
+  float   ms_wall;                /* wall clock of the call                              */
+  float   ms_bind, ms_score;      /* summed over slots: create/rebind, lh_score_batch    */
+  int32_t n_families, n_failed, n_slots, host_threads_per_slot;
+  int64_t n_trees;                /* scored                                              */
+  int64_t kernel_launches, h2d_bytes, d2h_bytes;
+} lh_repertoire_stats_t;
+int  lh_repertoire_create(lh_repertoire_t** out, int device, int n_slots, int host_threads /*0 = cores / n_slots*/);
+int  lh_repertoire_score(lh_repertoire_t* rep, lh_repertoire_item_t* items, int32_t n_items,
+                         lh_repertoire_stats_t* stats /* or NULL */);
+void lh_repertoire_destroy(lh_repertoire_t* rep);
+const char* lh_repertoire_last_error(void);
 
 #ifdef __cplusplus
 }

@@ -150,8 +150,21 @@ DEVICE_SYMBOLS = [
     "lh_last_error", "lh_version", "lh_device_count", "lh_family_create", "lh_family_destroy",
     "lh_score_batch", "lh_batch_upload", "lh_batch_run", "lh_batch_fetch", "lh_sync",
     "lh_loglik_dev", "lh_get_timings", "lh_set_option", "lh_measure_fp64_peak",
-    "lh_timer_mark", "lh_timer_elapsed_ms",
+    "lh_timer_mark", "lh_timer_elapsed_ms", "lh_family_rebind",
+    "lh_repertoire_create", "lh_repertoire_score", "lh_repertoire_destroy", "lh_repertoire_last_error",
 ]
+
+
+class RepertoireItem(C.Structure):
+    _fields_ = [("desc", C.POINTER(FamilyDesc)), ("trees", C.POINTER(TreeBatch)), ("loglik", _f64p),
+                ("status", C.c_int32)]
+
+
+class RepertoireStats(C.Structure):
+    _fields_ = [("ms_wall", C.c_float), ("ms_bind", C.c_float), ("ms_score", C.c_float),
+                ("n_families", C.c_int32), ("n_failed", C.c_int32), ("n_slots", C.c_int32),
+                ("host_threads_per_slot", C.c_int32), ("n_trees", C.c_int64),
+                ("kernel_launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64)]
 
 
 def load_library(path=None):
@@ -179,6 +192,13 @@ def load_library(path=None):
     lib.lh_measure_fp64_peak.argtypes = [C.c_int, _f64p]
     lib.lh_timer_mark.argtypes = [C.c_void_p, C.c_int32]
     lib.lh_timer_elapsed_ms.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_float)]
+    lib.lh_family_rebind.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
+    lib.lh_repertoire_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int]
+    lib.lh_repertoire_score.argtypes = [C.c_void_p, C.POINTER(RepertoireItem), C.c_int32,
+                                        C.POINTER(RepertoireStats)]
+    lib.lh_repertoire_destroy.argtypes = [C.c_void_p]
+    lib.lh_repertoire_destroy.restype = None
+    lib.lh_repertoire_last_error.restype = C.c_char_p
     return lib
 
 

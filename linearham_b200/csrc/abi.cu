@@ -84,20 +84,32 @@ struct PinBuf {
   template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// Family constants are laid out in ONE host blob and go to HBM in one copy into one device arena
+// (the handle keeps both, so binding another family to the handle allocates nothing once the arena
+// has grown to the largest family seen). add() records where the device address of each array goes.
+struct ConstArena {
+  std::vector<uint8_t> host;
+  struct Fix { const void** where; size_t off; };
+  std::vector<Fix> fixes;
+  void clear() { host.clear(); fixes.clear(); }
+  template <class T>
+  int add(const T* src, size_t n, const T** dst) {
+    const size_t off = (host.size() + 255) / 256 * 256;
+    host.resize(off + std::max<size_t>(n, 1) * sizeof(T), 0);
+    if (n) std::memcpy(host.data() + off, src, n * sizeof(T));
+    fixes.push_back({reinterpret_cast<const void**>(dst), off});
+    return 0;
+  }
+};
+
 template <class T>
-int upload(const T* src, size_t n, const T** dst, std::vector<void*>& owned) {
-  void* d = nullptr;
-  size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
-  LH_CUDA(cudaMalloc(&d, bytes));
-  owned.push_back(d);
-  if (n) LH_CUDA(cudaMemcpy(d, src, n * sizeof(T), cudaMemcpyHostToDevice));
-  *dst = reinterpret_cast<const T*>(d);
-  return 0;
+int upload(const T* src, size_t n, const T** dst, ConstArena& arena) {
+  return arena.add(src, n, dst);
 }
 
 // dense column-major [rows x cols] -> CSC on the device (rows ascending inside a column,
 // i.e. the order of the reference's dense dot product with the zero terms dropped)
-int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, std::vector<void*>& owned) {
+int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, ConstArena& owned) {
   std::vector<int32_t> colptr(cols + 1, 0), row;
   std::vector<double> val;
   for (int j = 0; j < cols; ++j) {
@@ -127,7 +139,9 @@ struct lh_family {
   int num_sms = 148;
   cudaStream_t stream = nullptr;
   lhb::FamilyDev fd{};
-  std::vector<void*> owned;  // family-constant device allocations
+  ConstArena owned;   // family constants: host blob + address fix-ups
+  DevBuf d_const;     // ... and their device arena
+  PinBuf h_const;
   // options
   int opt_sites_per_thread = 0, opt_smem_slots = -1, opt_smem_lo = -1, opt_timing = 1, opt_threads = 0;
   bool window_set = false;  // smem_lo of the batch has been chosen
@@ -160,6 +174,7 @@ struct lh_family {
   std::vector<cudaEvent_t> staged_ev;  // per chunk: its last segment has landed in HBM
   int n_chunks = 0;
   bool own_stream = true;
+  bool bound = false;  // a family is bound (false after a failed rebind)
   // pruning column sets: [0] all S xMSA columns, [1] the distinct patterns of rows 1..T-1
   struct ColumnSet {
     int n_cols = 0;
@@ -214,8 +229,7 @@ void lh_family_destroy(lh_family_t* f) {
   if (f->stream) cudaStreamSynchronize(f->stream);
   if (f->copy_stream) cudaStreamSynchronize(f->copy_stream);
   if (f->hmm_stream) cudaStreamSynchronize(f->hmm_stream);
-  for (void* p : f->owned) cudaFree(p);
-  DevBuf* bufs[] = {&f->d_plan, &f->d_pblen, &f->d_er, &f->d_pi, &f->d_rates, &f->d_eig, &f->d_prec,
+  DevBuf* bufs[] = {&f->d_const, &f->d_plan, &f->d_pblen, &f->d_er, &f->d_pi, &f->d_rates, &f->d_eig, &f->d_prec,
                     &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
                     &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
                     &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_rs_steps,
@@ -223,6 +237,7 @@ void lh_family_destroy(lh_family_t* f) {
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
   f->h_misc.release();
+  f->h_const.release();
   f->h_list.release();
   f->h_out.release();
   for (auto& e : f->ev)
@@ -243,39 +258,32 @@ void lh_family_destroy(lh_family_t* f) {
   delete f;
 }
 
-int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
-  *out = nullptr;
+static int check_desc(const lh_family_desc_t* d) {
   if (!d) return fail("null descriptor");
   if (d->n_tips < 3) return fail("need at least 3 tips (got %d)", d->n_tips);
   if (d->n_sites < 1) return fail("empty xMSA");
   if (d->n_v < 1 || d->n_j < 1 || (d->has_d && d->n_d < 1)) return fail("empty germline region");
   if (d->vd_sites < 1 || d->vd_states < 1 || (d->has_d && (d->dj_sites < 1 || d->dj_states < 1)))
     return fail("empty junction region");
-  int ndev = 0;
-  cudaError_t e = cudaGetDeviceCount(&ndev);
-  if (e != cudaSuccess || ndev == 0)
-    return fail("no CUDA device available (%s); linearham_b200 has no CPU fallback",
-                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
-  if (device < 0 || device >= ndev) return fail("device %d out of range (0..%d)", device, ndev - 1);
-  LH_CUDA(cudaSetDevice(device));
-  lh_family* f = new lh_family;
-  f->device = device;
-  cudaDeviceGetAttribute(&f->num_sms, cudaDevAttrMultiProcessorCount, device);
-  auto bail = [&](int) { lh_family_destroy(f); return 1; };
-  if (cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking) != cudaSuccess)
-    return bail(fail("cudaStreamCreate failed"));
-  if (cudaStreamCreateWithFlags(&f->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
-    return bail(fail("cudaStreamCreate failed"));
-  if (cudaStreamCreateWithFlags(&f->hmm_stream, cudaStreamNonBlocking) != cudaSuccess)
-    return bail(fail("cudaStreamCreate failed"));
-  cudaEventCreateWithFlags(&f->hmm_done, cudaEventDisableTiming);
-  if (f->d_counters.reserve(64)) return bail(1);
-  for (auto& ev : f->ring_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
-  cudaEventCreateWithFlags(&f->misc_ev, cudaEventDisableTiming);
-  cudaEventCreateWithFlags(&f->list_ev, cudaEventDisableTiming);
-  for (auto& ev : f->ev) cudaEventCreate(&ev);
-  for (auto& ev : f->user_ev) cudaEventCreate(&ev);
+  return 0;
+}
 
+// Binds the family described by `d` to the handle: builds every family constant into the handle's
+// host blob and moves it to the handle's device arena in one copy. Batch buffers are kept.
+static int bind_family(lh_family* f, const lh_family_desc_t* d) {
+  LH_CUDA(cudaSetDevice(f->device));
+  // nothing of an earlier family may still be running on the arena
+  LH_CUDA(cudaStreamSynchronize(f->stream));
+  LH_CUDA(cudaStreamSynchronize(f->copy_stream));
+  LH_CUDA(cudaStreamSynchronize(f->hmm_stream));
+  f->owned.clear();
+  f->fd = lhb::FamilyDev{};
+  f->B = 0;
+  f->n_chunks = 0;
+  f->window_set = false;
+  f->use_sr = false;
+  for (auto& c : f->cols) c.codes_ns = 0;
+  auto bail = [&](int) { return 1; };
   const int T = d->n_tips, S = d->n_sites;
   for (size_t i = 0; i < (size_t)T * S; ++i)
     if (d->tip_codes[i] > 4) return bail(fail("tip_codes[%zu] = %d is not in 0..4", i, d->tip_codes[i]));
@@ -366,10 +374,8 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
       off[i + 1] = (int32_t)(pairs.size() / 2);
     }
     if (pairs.empty()) pairs.assign(2, 0);
-    const int32_t* flat = nullptr;
-    if (upload(off.data(), off.size(), doff, own) || upload(pairs.data(), pairs.size(), &flat, own)) return 1;
-    *dpairs = reinterpret_cast<const int2*>(flat);
-    return 0;
+    return upload(off.data(), off.size(), doff, own) |
+           upload(pairs.data(), pairs.size(), reinterpret_cast<const int32_t**>(dpairs), own);
   };
   rc |= emitting(d->vd_inds, fd.vd_sites, fd.vd_states, &fd.vd_valid_off, &fd.vd_valid);
   if (d->has_d) rc |= emitting(d->dj_inds, fd.dj_sites, fd.dj_states, &fd.dj_valid_off, &fd.dj_valid);
@@ -401,8 +407,57 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
     rc |= upload_csc(d->t_dj_j, fd.dj_states, fd.n_j, &fd.t_dj_j, own);
   }
   if (rc) return bail(1);
+  // one copy of the blob; the recorded fields then get their device addresses
+  const size_t bytes = own.host.size();
+  if (f->d_const.reserve(bytes) || f->h_const.reserve(bytes)) return 1;
+  std::memcpy(f->h_const.p, own.host.data(), bytes);
+  LH_CUDA(cudaMemcpyAsync(f->d_const.p, f->h_const.p, bytes, cudaMemcpyHostToDevice, f->stream));
+  LH_CUDA(cudaStreamSynchronize(f->stream));
+  for (const auto& fx : own.fixes) *fx.where = f->d_const.as<uint8_t>() + fx.off;
+  f->bound = true;
+  return 0;
+}
+
+
+int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
+  *out = nullptr;
+  if (check_desc(d)) return 1;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail("no CUDA device available (%s); linearham_b200 has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail("device %d out of range (0..%d)", device, ndev - 1);
+  LH_CUDA(cudaSetDevice(device));
+  lh_family* f = new lh_family;
+  f->device = device;
+  cudaDeviceGetAttribute(&f->num_sms, cudaDevAttrMultiProcessorCount, device);
+  auto bail = [&](int) { lh_family_destroy(f); return 1; };
+  if (cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail("cudaStreamCreate failed"));
+  if (cudaStreamCreateWithFlags(&f->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail("cudaStreamCreate failed"));
+  if (cudaStreamCreateWithFlags(&f->hmm_stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail("cudaStreamCreate failed"));
+  cudaEventCreateWithFlags(&f->hmm_done, cudaEventDisableTiming);
+  if (f->d_counters.reserve(64)) return bail(1);
+  for (auto& ev : f->ring_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&f->misc_ev, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&f->list_ev, cudaEventDisableTiming);
+  for (auto& ev : f->ev) cudaEventCreate(&ev);
+  for (auto& ev : f->user_ev) cudaEventCreate(&ev);
+  if (bind_family(f, d)) return bail(1);
   *out = f;
   return 0;
+}
+
+// The handle takes on another family (same device); its streams, events, planner threads, pinned
+// staging and device buffers are reused, so scoring many small families pays no allocation per family.
+int lh_family_rebind(lh_family_t* f, const lh_family_desc_t* d) {
+  if (!f) return fail("null family");
+  if (check_desc(d)) return 1;
+  f->bound = false;
+  return bind_family(f, d);
 }
 
 int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
@@ -988,6 +1043,7 @@ extern "C" {
 
 int lh_batch_upload(lh_family_t* f, const lh_tree_batch_t* tb) {
   if (!f || !tb) return fail("null argument");
+  if (!f->bound) return fail("no family bound to the handle (the last lh_family_rebind failed)");
   LH_CUDA(cudaSetDevice(f->device));
   if (check_batch(f, tb)) return 1;
   if (configure_batch(f, tb->n_trees, tb->n_rates)) return 1;
@@ -1103,6 +1159,7 @@ int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
 
 int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh_outputs_t* o) {
   if (!f || !tb || !loglik) return fail("null argument");
+  if (!f->bound) return fail("no family bound to the handle (the last lh_family_rebind failed)");
   f->want_tables = o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
                          o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers);
   LH_CUDA(cudaSetDevice(f->device));

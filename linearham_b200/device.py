@@ -48,6 +48,13 @@ class Family:
             raise DeviceError(lib().lh_last_error().decode())
         self._tb_keep = None
 
+    def rebind(self, fam):
+        """The handle takes on another family (lh_family_rebind); buffers, streams and threads stay."""
+        d, keep = _abi.family_desc(fam)
+        self._ck(lib().lh_family_rebind(self._h, C.byref(d)))
+        self.fam = fam
+        self._tb_keep = None
+
     def close(self):
         if self._h:
             lib().lh_family_destroy(self._h)
@@ -113,3 +120,57 @@ class Family:
         t = _abi.Timings()
         self._ck(lib().lh_get_timings(self._h, C.byref(t)))
         return {k: getattr(t, k) for k, _ in _abi.Timings._fields_}
+
+
+class Repertoire:
+    """Many independent clonal families on one device (lh_repertoire_t): n_slots device handles, one
+    host thread per slot."""
+
+    def __init__(self, device=0, n_slots=3, host_threads=0):
+        self._h = C.c_void_p()
+        if lib().lh_repertoire_create(C.byref(self._h), int(device), int(n_slots), int(host_threads)):
+            raise DeviceError(lib().lh_repertoire_last_error().decode())
+
+    def close(self):
+        if self._h:
+            lib().lh_repertoire_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def prepare(families):
+        """[(family dict, tree-batch dict), ...] -> marshalled items (reusable across score calls)."""
+        n = len(families)
+        items = (_abi.RepertoireItem * max(n, 1))()
+        keep, outs = [], []
+        for i, (fam, tb) in enumerate(families):
+            d, kd = _abi.family_desc(fam)
+            t, kt = _abi.tree_batch(tb)
+            ll = np.full(t.n_trees, np.nan)
+            items[i].desc = C.pointer(d)
+            items[i].trees = C.pointer(t)
+            items[i].loglik = ll.ctypes.data_as(_f64p)
+            keep.append((d, kd, t, kt))
+            outs.append(ll)
+        return dict(items=items, n=n, keep=keep, loglik=outs)
+
+    def score_prepared(self, prep):
+        """-> (list of loglik arrays (views, overwritten by the next call), stats dict)."""
+        st = _abi.RepertoireStats()
+        rc = lib().lh_repertoire_score(self._h, prep["items"], prep["n"], C.byref(st))
+        stats = {k: getattr(st, k) for k, _ in _abi.RepertoireStats._fields_}
+        stats["status"] = [prep["items"][i].status for i in range(prep["n"])]
+        if rc:
+            err = DeviceError(lib().lh_repertoire_last_error().decode())
+            err.stats = stats
+            raise err
+        return prep["loglik"], stats
+
+    def score(self, families):
+        ll, stats = self.score_prepared(self.prepare(families))
+        return [a.copy() for a in ll], stats

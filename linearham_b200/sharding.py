@@ -48,3 +48,34 @@ def assign_families(costs, world):
         out[r].append(f)
         load[r] += costs[f]
     return out
+
+
+def family_cost(n_tips, n_sites, n_trees, n_rates=4):
+    """Pruning cost model of one family: trees x inner nodes x xMSA columns x categories."""
+    return float(n_trees) * max(1, n_tips - 2) * n_sites * n_rates
+
+
+def gather_family_loglik(dist, local, assignment, n_trees, device=None):
+    """Repertoire gather: every rank scored the families assignment[rank] (lists of family ids, the same
+    on every rank - assign_families is deterministic); local = {family id: 1-D float64 torch tensor}.
+    One all-gather of the ranks' concatenated log-likelihoods, padded to the longest rank.
+    -> list over all families of 1-D tensors, on every rank."""
+    import torch
+    world, rank = dist.get_world_size(), dist.get_rank()
+    per = max(1, max(sum(n_trees[f] for f in fams) for fams in assignment))
+    mine = [local[f] for f in assignment[rank]]
+    if device is None:
+        device = mine[0].device if mine else "cpu"
+    buf = torch.zeros(per, dtype=torch.float64, device=device)
+    if mine:
+        cat = torch.cat(mine)
+        buf[:cat.numel()] = cat
+    out = torch.empty(world * per, dtype=torch.float64, device=buf.device)
+    dist.all_gather_into_tensor(out, buf)
+    res = [None] * len(n_trees)
+    for r, fams in enumerate(assignment):
+        o = r * per
+        for f in fams:
+            res[f] = out[o:o + n_trees[f]]
+            o += n_trees[f]
+    return res

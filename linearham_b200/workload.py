@@ -15,6 +15,10 @@ CONFIGS = {
                desc="synthetic 128-leaf IGH family, 400 nt naive, Gamma-4 GTR, batch 4096 trees"),
     "c4": dict(n_leaves=1000, B=16384, R=4, fam_seed=1400, tree_seed=2004, outgroup="naive",
                desc="synthetic 1000-leaf IGH family, 400 nt, Gamma-4, batch 16384 trees"),
+    # repertoire sweep: independent families, leaves log-uniform in [20, 500] (SURVEY.md 8(d) "C5");
+    # BASELINE names 10 000 families x 1000 samples - bench and tests state the subset they run
+    "c5": dict(n_families=10000, leaves=(20, 500), B=1000, R=4, fam_seed=1500000, tree_seed=2500000, outgroup="naive",
+               desc="repertoire sweep: synthetic clonal families of 20-500 leaves scored independently"),
     "tiny": dict(n_leaves=24, B=256, R=4, fam_seed=1500, tree_seed=2005,
                  desc="synthetic 24-leaf IGH family (tests)"),
 }
@@ -65,6 +69,35 @@ def tree_batch(cfg, fam_files, B, n_topo=None, n_threads=0):
     tb["er"], tb["pi"] = np.ascontiguousarray(er), np.ascontiguousarray(pi)
     tb["rates"] = host.gamma_cats(alpha, cfg["R"])
     return tb, newicks, alpha
+
+
+def repertoire_sizes(cfg, n_families):
+    """Leaf counts of the first n_families families of a repertoire config: round(exp(U(log lo, log hi)))."""
+    lo, hi = cfg["leaves"]
+    rng = np.random.default_rng(cfg["fam_seed"])
+    return np.rint(np.exp(rng.uniform(np.log(lo), np.log(hi), n_families))).astype(int)
+
+
+def repertoire(cfg, outdir, n_families, B=None, n_topo=16, device=0, n_threads=0):
+    """The first n_families families of a repertoire config, each with B tree samples:
+    -> list of dict(fam=family description built by the product's C++ PhyloHMM host class, tb, newicks,
+    alpha, files, n_leaves). The HMM parameter directory is shared (one germline set per repertoire)."""
+    B = B or cfg["B"]
+    hmm_dir = os.path.join(outdir, "hmm")
+    genes = synth.make_germline_set(hmm_dir, seed=GERMLINE_SEED)
+    out = []
+    for i, n_leaves in enumerate(repertoire_sizes(cfg, n_families)):
+        ff = synth.make_family(outdir, genes, int(n_leaves), seed=cfg["fam_seed"] + 1 + i, name=f"family_{i}")
+        ff["hmm_dir"] = hmm_dir
+        ph = host.PhyloHMM(ff["yaml_path"], 0, hmm_dir, 0, device=device)
+        fam, labels = ph.family(), ph.strs("xmsa_labels")
+        ph.close()
+        if labels != ff["labels"]:
+            raise RuntimeError("xMSA labels do not match the generated family")
+        sub = dict(cfg, tree_seed=cfg["tree_seed"] + i)
+        tb, newicks, alpha = tree_batch(sub, ff, B, n_topo=n_topo, n_threads=n_threads)
+        out.append(dict(fam=fam, tb=tb, newicks=newicks, alpha=alpha, files=ff, n_leaves=int(n_leaves)))
+    return out
 
 
 def bytes_per_tree(T, S, R=4):

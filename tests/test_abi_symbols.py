@@ -76,3 +76,15 @@ def test_command_line_is_built_and_rejects_bad_usage():
     r = subprocess.run([cli, "--pipeline", "--yaml-path", "/nonexistent.yaml", "--cluster-ind", "0", "--hmm-param-dir", "/nonexistent",
                         "--input-path", "a", "--output-path", "b"], capture_output=True, text=True, timeout=60)
     assert r.returncode == 1 and r.stderr.startswith("ERROR: ")
+
+
+def test_repertoire_fails_loudly_without_device():
+    from linearham_b200 import device
+    if device.device_count() > 0:
+        return
+    try:
+        device.Repertoire(n_slots=2)
+    except device.DeviceError as e:
+        assert "CUDA" in str(e)
+    else:
+        raise AssertionError("Repertoire() succeeded without a GPU")
