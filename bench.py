@@ -175,7 +175,7 @@ def main():
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE",
                     help="lh_set_option on the family (e.g. pipe_waves=4); recorded in config")
     ap.add_argument("--families", type=int, default=256, help="config c5: families scored per pass (whole job)")
-    ap.add_argument("--slots", type=int, default=4, help="config c5: device handles per GPU")
+    ap.add_argument("--slots", type=int, default=6, help="config c5: device handles per GPU")
     ap.add_argument("--topologies-c5", dest="topologies_c5", type=int, default=16,
                     help="config c5: distinct topologies per family")
     args = ap.parse_args()
@@ -189,12 +189,13 @@ def main():
     if args.impl == "reference" and rank != 0:
         return 0
 
-    if args.config == "c5":
+    if args.config in ("c5", "c2"):
         if args.impl == "reference":
             print(json.dumps({"impl": "reference", "unavailable": "the reference arm is timed on config c4 (bench.py default)"}))
             return 0
+        import bench_c2
         import bench_c5
-        return bench_c5.run(args, rank, world, local_rank)
+        return (bench_c5 if args.config == "c5" else bench_c2).run(args, rank, world, local_rank)
 
     from linearham_b200 import host, sharding, workload
     cfg = dict(workload.CONFIGS[args.config])

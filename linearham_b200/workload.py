@@ -100,6 +100,20 @@ def repertoire(cfg, outdir, n_families, B=None, n_topo=16, device=0, n_threads=0
     return out
 
 
+def liao_batch(z):
+    """BASELINE config 2: rebuilds the 1024-sample tree batch (device-ABI layout) of tests/golden/liao_b1024.npz
+    from its arrays - 32 topologies x 128 noise vectors (int8 indices into a stored table of doubles), exact
+    IEEE products, so every machine gets the doubles the reference scored (scripts/make_liao_bundle.py)."""
+    topo, noise, table = z["topo_of"], z["noise_of"], z["noise_table"]
+    return {"children": np.ascontiguousarray(z["base_children"][topo]),
+            "blen": np.ascontiguousarray(z["base_blen"][topo] * table[z["noise_k"][noise].astype(np.int64) + 128]),
+            "root_child": np.ascontiguousarray(z["base_root_child"][topo]),
+            "root_blen": np.ascontiguousarray(z["base_root_blen"][topo]
+                                              * table[z["noise_root_k"][noise].astype(np.int64) + 128]),
+            "er": np.ascontiguousarray(z["er"]), "pi": np.ascontiguousarray(z["pi"]),
+            "rates": np.ascontiguousarray(z["rates"])}
+
+
 def bytes_per_tree(T, S, R=4):
     """ALGORITHMIC bytes of one tree evaluation under the streaming model:
     every inner CLV written once and read once with its per-site uint32 scaler, tip codes read once,

@@ -13,7 +13,7 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 # sample bundles (family + tree batch + reference outputs); family_*.npz hold a family description only
 GOLDEN_NAMES = sorted(n for n in (os.path.splitext(os.path.basename(p))[0]
                                   for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-                      if not n.startswith(("family_", "pipeline_")))
+                      if not n.startswith(("family_", "pipeline_", "liao_")))
 
 
 def pytest_configure(config):
@@ -34,6 +34,15 @@ def load_family_bundle(name):
     z = np.load(os.path.join(GOLDEN_DIR, f"family_{name}.npz"), allow_pickle=False)
     fam = {k[4:]: (int(z[k]) if z[k].ndim == 0 else z[k]) for k in z.files if k.startswith("fam_")}
     return fam, [str(s) for s in z["labels"]], str(z["sha"])
+
+
+def load_liao():
+    """BASELINE config 2 bundle -> (family, tree batch of 1024 samples, reference outputs, bundle)."""
+    from linearham_b200 import workload
+    z = np.load(os.path.join(GOLDEN_DIR, "liao_b1024.npz"), allow_pickle=False)
+    fam = {k[4:]: (int(z[k]) if z[k].ndim == 0 else z[k]) for k in z.files if k.startswith("fam_")}
+    exp = {k[4:]: z[k] for k in z.files if k.startswith("exp_")}
+    return fam, workload.liao_batch(z), exp, z
 
 
 @pytest.fixture(params=GOLDEN_NAMES)
