@@ -341,7 +341,8 @@ def main():
             ll_e2e = f.score(shard)
             t2 = f.timings()
             h2d, d2h, ms_plan = t2["h2d_bytes"], t2["d2h_bytes"], t2["ms_plan"]
-            e2e_detail = {k: t2[k] for k in ("ms_call", "ms_setup", "ms_plan", "ms_h2d", "ms_kernels", "ms_d2h")}
+            e2e_detail = {k: t2[k] for k in ("ms_call", "ms_setup", "ms_plan", "ms_h2d", "ms_kernels", "ms_d2h",
+                                             "ms_plan_dev", "device_plan")}
         sync_all()
         e2e_s = time.perf_counter() - t0
         assert np.array_equal(ll_e2e, ll_dev, equal_nan=True)

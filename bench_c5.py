@@ -45,6 +45,9 @@ def run(args, rank, world, local_rank):
     slots = args.slots
     host_threads = max(1, cores // local_world // slots)
     rep = device.Repertoire(device=dev, n_slots=slots, host_threads=host_threads)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        rep.set_option(k, int(v))
     prep = rep.prepare([(fams[i]["fam"], fams[i]["tb"]) for i in mine])
 
     def sync_all():
@@ -124,7 +127,7 @@ def run(args, rank, world, local_rank):
                        "families": n_fam, "trees_per_family": n_trees_f, "leaves_min_median_max":
                            [int(min(leaves)), int(np.median(leaves)), int(max(leaves))],
                        "gamma_categories": cfg["R"], "distinct_topologies_per_family": args.topologies_c5,
-                       "slots_per_gpu": slots, "host_threads_per_slot": host_threads,
+                       "slots_per_gpu": slots, "options": list(args.opt), "host_threads_per_slot": host_threads,
                        "parallelism": f"whole families assigned to {world} GPU(s) longest-first; no data-path "
                                       "collective; one all-gather of the per-tree log-likelihoods per pass",
                        "l2": "every family is new to the device each pass (bind + H2D inside the timed region)"},

@@ -140,6 +140,8 @@ typedef struct lh_timings {
   int32_t site_repeats;      /* 1 when the pattern trees ran on site-repeat classes      */
   int32_t sr_arena;          /* shared-memory CLV arena entries per warp (k_prune_sr)    */
   int32_t sr_ctas_per_sm;
+  float ms_plan_dev;         // sum over k_plan launches (device traversal planning)             
+  int32_t device_plan;       // 1 when the batch was planned by k_plan                           
 } lh_timings_t;
 
 const char* lh_last_error(void);
@@ -168,6 +170,9 @@ int lh_sync(lh_family_t* fam);
 int lh_loglik_dev(lh_family_t* fam, const double** loglik_dev, int32_t* n); /* device ptr of the last run */
 
 int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/score */
+/* Test hook: the traversal programs of the current batch as the device holds them
+ * (steps [B][T-1][4] int32, pblen [B][2T-3]); compared with the host planner in the tests. */
+int lh_debug_fetch_plan(lh_family_t* fam, int32_t* steps, double* pblen);
 /* Diagnostic: sustained FP64 FMA rate of a register-resident DFMA loop (TFLOP/s); the
  * denominator for the FP64-pipe view of the pruning kernel (no reference counterpart). */
 int lh_measure_fp64_peak(int device, double* tflops);
@@ -176,6 +181,9 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
  * covers 32x that many columns), "smem_slots" (-1 = auto), "smem_lo" (-1 = auto: first CLV stack level
  * of the shared-memory window), "timing" (0/1), "host_threads", "hmm_overlap" (1 = default: the forward
  * pass of a chunk runs on its own stream beside the next chunk's pruning),
+ * "device_plan" (1: the traversal programs are built on the device by k_plan from the operation
+ * lists as the caller holds them; 0: by the host planner threads; -1 = default: by the device when
+ * the handle's host threads would not keep ahead of the kernels - the programs are the same),
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never
  * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "pipe_waves" (default 4:
  * lh_score_batch launches a chunk's kernels every that many waves of CTAs), "stream" (a
@@ -215,6 +223,7 @@ typedef struct lh_repertoire_stats {
 int  lh_repertoire_create(lh_repertoire_t** out, int device, int n_slots, int host_threads /*0 = cores / n_slots*/);
 int  lh_repertoire_score(lh_repertoire_t* rep, lh_repertoire_item_t* items, int32_t n_items,
                          lh_repertoire_stats_t* stats /* or NULL */);
+int  lh_repertoire_set_option(lh_repertoire_t* rep, const char* key, int64_t value); /* lh_set_option on every slot */
 void lh_repertoire_destroy(lh_repertoire_t* rep);
 const char* lh_repertoire_last_error(void);
 

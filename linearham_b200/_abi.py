@@ -67,6 +67,7 @@ class Timings(C.Structure):
         ("prune_columns", C.c_int32), ("pattern_trees", C.c_int32),
         ("ms_call", C.c_float), ("ms_setup", C.c_float), ("ms_repeats", C.c_float),
         ("site_repeats", C.c_int32), ("sr_arena", C.c_int32), ("sr_ctas_per_sm", C.c_int32),
+        ("ms_plan_dev", C.c_float), ("device_plan", C.c_int32),
     ]
 
 
@@ -150,8 +151,8 @@ DEVICE_SYMBOLS = [
     "lh_last_error", "lh_version", "lh_device_count", "lh_family_create", "lh_family_destroy",
     "lh_score_batch", "lh_batch_upload", "lh_batch_run", "lh_batch_fetch", "lh_sync",
     "lh_loglik_dev", "lh_get_timings", "lh_set_option", "lh_measure_fp64_peak",
-    "lh_timer_mark", "lh_timer_elapsed_ms", "lh_family_rebind",
-    "lh_repertoire_create", "lh_repertoire_score", "lh_repertoire_destroy", "lh_repertoire_last_error",
+    "lh_timer_mark", "lh_timer_elapsed_ms", "lh_family_rebind", "lh_debug_fetch_plan",
+    "lh_repertoire_create", "lh_repertoire_score", "lh_repertoire_destroy", "lh_repertoire_set_option", "lh_repertoire_last_error",
 ]
 
 
@@ -192,10 +193,12 @@ def load_library(path=None):
     lib.lh_measure_fp64_peak.argtypes = [C.c_int, _f64p]
     lib.lh_timer_mark.argtypes = [C.c_void_p, C.c_int32]
     lib.lh_timer_elapsed_ms.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_float)]
+    lib.lh_debug_fetch_plan.argtypes = [C.c_void_p, _i32p, _f64p]
     lib.lh_family_rebind.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
     lib.lh_repertoire_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int]
     lib.lh_repertoire_score.argtypes = [C.c_void_p, C.POINTER(RepertoireItem), C.c_int32,
                                         C.POINTER(RepertoireStats)]
+    lib.lh_repertoire_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     lib.lh_repertoire_destroy.argtypes = [C.c_void_p]
     lib.lh_repertoire_destroy.restype = None
     lib.lh_repertoire_last_error.restype = C.c_char_p

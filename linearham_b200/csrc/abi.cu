@@ -132,7 +132,7 @@ int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, ConstA
 
 }  // namespace
 
-constexpr int kChunkEvents = 7;
+constexpr int kChunkEvents = 9;  // [7], [8]: k_plan of the chunk started / finished (plan stream)
 
 struct lh_family {
   int device = 0;
@@ -168,6 +168,15 @@ struct lh_family {
   std::vector<cudaEvent_t> edge_ev;  // per chunk: k_edge finished
   int opt_hmm_overlap = 1;
   DevBuf d_counters;
+  // device planning (k_plan): the caller's operation lists go to HBM as they are
+  int opt_device_plan = -1;    // -1 auto, 0 host planner threads, 1 k_plan
+  bool dev_plan = false;       // the current batch is planned on the device
+  DevBuf d_rchildren, d_rblen, d_rroot_child, d_rroot_blen, d_flags;
+  PinBuf h_flags;              // [0..3] init values, [4..7] read-back
+  cudaStream_t plan_stream = nullptr;  // k_plan of a chunk runs here, beside the kernels of the chunk before
+  bool plan_in_call = false;           // the chunk events [7], [8] of the current batch bracket k_plan launches
+  bool flags_pending = false;  // k_plan ran for the batch and its flags have not been checked yet
+  bool run_recorded = false;   // the kernels of the current batch have been queued (their chunk events exist)
   cudaEvent_t ev[8] = {};
   cudaEvent_t user_ev[8] = {};
   std::vector<cudaEvent_t> chunk_ev;  // kChunkEvents per chunk: start, pmatrix | repeats | prune | edge ends (compute stream); hmm start, hmm end (its stream)
@@ -233,11 +242,13 @@ void lh_family_destroy(lh_family_t* f) {
                     &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
                     &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
                     &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_rs_steps,
-                    &f->d_rs_idx, &f->d_rs_ecls, &f->d_rs_peak, &f->d_rs_gclv, &f->d_rs_gcnt, &f->d_counters};
+                    &f->d_rs_idx, &f->d_rs_ecls, &f->d_rs_peak, &f->d_rs_gclv, &f->d_rs_gcnt, &f->d_counters,
+                    &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags};
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
   f->h_misc.release();
   f->h_const.release();
+  f->h_flags.release();
   f->h_list.release();
   f->h_out.release();
   for (auto& e : f->ev)
@@ -253,6 +264,7 @@ void lh_family_destroy(lh_family_t* f) {
   for (auto& e : f->edge_ev) cudaEventDestroy(e);
   if (f->hmm_done) cudaEventDestroy(f->hmm_done);
   if (f->hmm_stream) cudaStreamDestroy(f->hmm_stream);
+  if (f->plan_stream) cudaStreamDestroy(f->plan_stream);
   if (f->copy_stream) cudaStreamDestroy(f->copy_stream);
   if (f->stream && f->own_stream) cudaStreamDestroy(f->stream);
   delete f;
@@ -276,6 +288,7 @@ static int bind_family(lh_family* f, const lh_family_desc_t* d) {
   LH_CUDA(cudaStreamSynchronize(f->stream));
   LH_CUDA(cudaStreamSynchronize(f->copy_stream));
   LH_CUDA(cudaStreamSynchronize(f->hmm_stream));
+  LH_CUDA(cudaStreamSynchronize(f->plan_stream));
   f->owned.clear();
   f->fd = lhb::FamilyDev{};
   f->B = 0;
@@ -439,6 +452,8 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
     return bail(fail("cudaStreamCreate failed"));
   if (cudaStreamCreateWithFlags(&f->hmm_stream, cudaStreamNonBlocking) != cudaSuccess)
     return bail(fail("cudaStreamCreate failed"));
+  if (cudaStreamCreateWithFlags(&f->plan_stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail("cudaStreamCreate failed"));
   cudaEventCreateWithFlags(&f->hmm_done, cudaEventDisableTiming);
   if (f->d_counters.reserve(64)) return bail(1);
   for (auto& ev : f->ring_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
@@ -476,6 +491,9 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_sr_arena = (int)value;
   } else if (k == "site_patterns") {
     f->opt_site_patterns = value != 0;
+  } else if (k == "device_plan") {
+    if (value < -1 || value > 1) return fail("device_plan must be -1 (auto), 0 or 1");
+    f->opt_device_plan = (int)value;
   } else if (k == "hmm_overlap") {
     f->opt_hmm_overlap = value != 0;
   } else if (k == "timing") {
@@ -613,6 +631,28 @@ int configure_batch(lh_family* f, int B, int R) {
       f->d_xe.reserve((size_t)B * S * 8) || f->d_loglik.reserve((size_t)B * 8) ||
       f->h_misc.reserve(misc_doubles * sizeof(double)))
     return 1;
+  {
+    // Who plans the traversals. The host planner threads cost the GPU nothing as long as they stay
+    // ahead of the kernels (about 20 ns per operation and thread against 2.7 ps per operation, column
+    // and category of k_prune, both measured on C4); k_plan costs about 2 % of a step but no host time.
+    // Auto: the device plans when the host threads this handle has would need more than half the
+    // kernel time (few threads per GPU: 8 ranks on one host, repertoire slots).
+    int threads = f->opt_threads > 0 ? f->opt_threads : (int)std::thread::hardware_concurrency();
+    threads = std::max(1, std::min(threads, 32));
+    const int cols = (f->opt_site_patterns && f->n_pattern_trees * 2 >= B) ? f->cols[1].n_cols : f->cols[0].n_cols;
+    const double host_ns = 20.0 / threads, kernel_ns = 2.7e-3 * cols * R;
+    const bool want = f->opt_device_plan < 0 ? host_ns > 0.5 * kernel_ns : f->opt_device_plan != 0;
+    f->dev_plan = want && lhb::plan_on_device_ok(T);
+  }
+  f->flags_pending = false;
+  f->run_recorded = false;
+  if (f->dev_plan) {
+    const size_t n2 = (size_t)B * (T - 2) * 2;
+    if (f->d_rchildren.reserve(n2 * sizeof(int32_t)) || f->d_rblen.reserve(n2 * sizeof(double)) ||
+        f->d_rroot_child.reserve((size_t)B * sizeof(int32_t)) || f->d_rroot_blen.reserve((size_t)B * sizeof(double)) ||
+        f->d_flags.reserve(4 * sizeof(int32_t)) || f->h_flags.reserve(8 * sizeof(int32_t)))
+      return 1;
+  }
   lhb::BatchDev& bd = f->bd;
   bd = lhb::BatchDev{};
   bd.B = B;
@@ -842,11 +882,14 @@ int configure_batch(lh_family* f, int B, int R) {
   f->tm.prune_ctas_per_sm = f->occ[gmain];
   f->tm.prune_columns = pm.n_cols;
   f->tm.pattern_trees = f->n_pattern_trees;
+  f->tm.device_plan = f->dev_plan ? 1 : 0;
   f->tm.site_repeats = f->use_sr ? 1 : 0;
   f->tm.sr_arena = f->use_sr ? f->rc.arena_smem : 0;
   f->tm.sr_ctas_per_sm = f->use_sr ? f->sr_occ : 0;
   return 0;
 }
+
+void launch_plan_trees(lh_family* f, int t0, int n, cudaStream_t s);
 
 // Plans trees [t0, t0+n) into ring slot `slot` and queues their copy to HBM on `s`.
 int stage_segment(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, int slot, cudaStream_t s) {
@@ -858,7 +901,19 @@ int stage_segment(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, int sl
   lhb::Step* steps = f->h_ring[slot].as<lhb::Step>();
   double* pblen = reinterpret_cast<double*>(steps + (size_t)n * (T - 1));
   const auto t_a = std::chrono::steady_clock::now();
-  if (plan_range(f, tb, t0, n, steps, pblen, &f->slots)) return 1;
+  // Device planning: the segment's operation lists are only copied into the pinned slot (the host
+  // threads share the memcpy); the first trees of a batch are still planned here, into a scratch,
+  // because their steps choose the shared-memory window of the CLV stack.
+  std::vector<lhb::Step> probe_steps;
+  std::vector<double> probe_pblen;
+  const int n_planned = f->dev_plan ? (f->window_set ? 0 : std::min(n, 64)) : n;
+  if (f->dev_plan && n_planned) {
+    probe_steps.resize((size_t)n_planned * (T - 1));
+    probe_pblen.resize((size_t)n_planned * NB);
+    steps = probe_steps.data();
+    pblen = probe_pblen.data();
+  }
+  if (n_planned && plan_range(f, tb, t0, n_planned, steps, pblen, &f->slots)) return 1;
   if (!f->window_set) {
     // which CLV stack levels live in shared memory: the window of smem_slots consecutive levels
     // that the first trees of the batch park results in most often
@@ -885,6 +940,41 @@ int stage_segment(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, int sl
   f->tm.ms_plan += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_a).count();
   const int slot_bound = std::max(f->pc[0].total_slots, f->pc[1].total_slots);
   if (f->slots > slot_bound) return fail("internal: tree needs %d CLV slots, bound is %d", f->slots, slot_bound);
+  if (f->dev_plan) {
+    // raw layout of a slot: children [n][T-2][2] | blen [n][T-2][2] | root_blen [n] | root_child [n]
+    const auto t_b = std::chrono::steady_clock::now();
+    const size_t per = (size_t)(T - 2) * 2;
+    uint8_t* base = f->h_ring[slot].as<uint8_t>();
+    int32_t* r_ch = reinterpret_cast<int32_t*>(base);
+    double* r_bl = reinterpret_cast<double*>(base + ((size_t)n * per * sizeof(int32_t) + 15) / 16 * 16);
+    double* r_rb = r_bl + (size_t)n * per;
+    int32_t* r_rc = reinterpret_cast<int32_t*>(r_rb + n);
+    if (!f->pool) {
+      int nthreads = f->opt_threads > 0 ? f->opt_threads : (int)std::thread::hardware_concurrency();
+      nthreads = std::max(1, std::min(nthreads, 32));
+      f->pool.reset(new lhb::WorkerPool(nthreads - 1));
+      f->plan_scratch.resize(nthreads);
+    }
+    constexpr int kBlock = 32;  // trees per task
+    f->pool->run((n + kBlock - 1) / kBlock, [&](int task, int) {
+      const int lo = task * kBlock, cnt = std::min(n, lo + kBlock) - lo;
+      std::memcpy(r_ch + (size_t)lo * per, tb->children + ((size_t)t0 + lo) * per, (size_t)cnt * per * sizeof(int32_t));
+      std::memcpy(r_bl + (size_t)lo * per, tb->blen + ((size_t)t0 + lo) * per, (size_t)cnt * per * sizeof(double));
+    });
+    std::memcpy(r_rb, tb->root_blen + t0, (size_t)n * sizeof(double));
+    std::memcpy(r_rc, tb->root_child + t0, (size_t)n * sizeof(int32_t));
+    f->tm.ms_plan += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_b).count();
+    LH_CUDA(cudaMemcpyAsync(f->d_rchildren.as<int32_t>() + (size_t)t0 * per, r_ch, (size_t)n * per * sizeof(int32_t),
+                            cudaMemcpyHostToDevice, s));
+    LH_CUDA(cudaMemcpyAsync(f->d_rblen.as<double>() + (size_t)t0 * per, r_bl, (size_t)n * per * sizeof(double),
+                            cudaMemcpyHostToDevice, s));
+    LH_CUDA(cudaMemcpyAsync(f->d_rroot_blen.as<double>() + t0, r_rb, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+    LH_CUDA(cudaMemcpyAsync(f->d_rroot_child.as<int32_t>() + t0, r_rc, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    LH_CUDA(cudaEventRecord(f->ring_ev[slot], s));
+    f->ring_busy[slot] = true;
+    f->tm.h2d_bytes += (int64_t)((size_t)n * per * 12 + (size_t)n * 12);
+    return 0;
+  }
   const size_t plan_bytes = (size_t)n * (T - 1) * sizeof(lhb::Step), pblen_bytes = (size_t)n * NB * sizeof(double);
   LH_CUDA(cudaMemcpyAsync(f->d_plan.as<lhb::Step>() + (size_t)t0 * (T - 1), steps, plan_bytes,
                           cudaMemcpyHostToDevice, s));
@@ -931,6 +1021,31 @@ int ensure_chunk_events(lh_family* f, int n_chunks) {
 
 // The four kernels of one chunk of trees, in stream order: eigen systems, branch records,
 // pruning (xMSA emission), HMM forward pass.
+void launch_plan_trees(lh_family* f, int t0, int n, cudaStream_t s) {
+  lhb::PlanDev p{};
+  p.T = f->fd.T;
+  p.tree0 = t0;
+  p.children = f->d_rchildren.as<int32_t>();
+  p.blen = f->d_rblen.as<double>();
+  p.root_child = f->d_rroot_child.as<int32_t>();
+  p.root_blen = f->d_rroot_blen.as<double>();
+  p.plan = f->d_plan.as<int4>();
+  p.pblen = f->d_pblen.as<double>();
+  p.flags = f->d_flags.as<int32_t>();
+  lhb::launch_plan(p, n, s);
+  f->flags_pending = true;
+}
+
+// Start values of the k_plan flags -> HBM on `s` (before any k_plan of the batch).
+int stage_flags(lh_family* f, cudaStream_t s) {
+  if (!f->dev_plan) return 0;
+  int32_t* h = f->h_flags.as<int32_t>();
+  h[0] = h[1] = INT32_MAX;
+  h[2] = h[3] = 0;
+  LH_CUDA(cudaMemcpyAsync(f->d_flags.p, h, 4 * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+  return 0;
+}
+
 void launch_chunk(lh_family* f, int ci, int t0, int n) {
   cudaStream_t s = f->stream;
   const bool tm = f->opt_timing;
@@ -1050,10 +1165,13 @@ int lh_batch_upload(lh_family_t* f, const lh_tree_batch_t* tb) {
   if (f->B == 0) return 0;
   cudaStream_t s = f->stream;
   if (f->opt_timing) cudaEventRecord(f->ev[0], s);
-  if (stage_params(f, tb, s)) return 1;
+  if (stage_params(f, tb, s) || stage_flags(f, s)) return 1;
   if (stage_lists(f, chunk_starts(f, false), s)) return 1;
   for (int t0 = 0, k = 0; t0 < f->B; t0 += f->seg, ++k)
     if (stage_segment(f, tb, t0, std::min(f->seg, f->B - t0), k % lh_family::kRing, s)) return 1;
+  // a resident batch is planned once, here; lh_batch_run re-runs the likelihood kernels only
+  f->plan_in_call = false;
+  if (f->dev_plan) launch_plan_trees(f, 0, f->B, s);
   if (f->opt_timing) cudaEventRecord(f->ev[1], s);
   return 0;
 }
@@ -1069,22 +1187,26 @@ int lh_batch_run(lh_family_t* f) {
   for (int ci = 0; ci < f->n_chunks; ++ci) launch_chunk(f, ci, st[ci], st[ci + 1] - st[ci]);
   join_hmm_stream(f);
   if (f->opt_timing) cudaEventRecord(f->ev[4], f->stream);
+  f->run_recorded = true;
   LH_CUDA(cudaGetLastError());
   return 0;
 }
 
 // Per-kernel device times of the last run (syncs the stream).
 static int collect_run_timings(lh_family* f) {
-  if (!f->opt_timing || f->B == 0 || f->n_chunks == 0) return 0;
+  if (!f->opt_timing || f->B == 0 || f->n_chunks == 0 || !f->run_recorded) return 0;
   LH_CUDA(cudaEventSynchronize(f->ev[4]));
   // (k_hmm of a chunk overlaps the next chunk's kernels, so the stage times can add up to more than ms_kernels)
-  float sum[5] = {}, x = 0;
-  static const int from[5] = {0, 1, 2, 3, 5};
+  float sum[6] = {}, x = 0;
+  static const int from[6] = {0, 1, 2, 3, 5, 7}, to[6] = {1, 2, 3, 4, 6, 8};
+  const int n_spans = f->plan_in_call ? 6 : 5;
+  f->tm.ms_plan_dev = 0.f;
   for (int ci = 0; ci < f->n_chunks; ++ci)
-    for (int k = 0; k < 5; ++k) {
-      cudaEventElapsedTime(&x, f->chunk_ev[kChunkEvents * ci + from[k]], f->chunk_ev[kChunkEvents * ci + from[k] + 1]);
+    for (int k = 0; k < n_spans; ++k) {
+      cudaEventElapsedTime(&x, f->chunk_ev[kChunkEvents * ci + from[k]], f->chunk_ev[kChunkEvents * ci + to[k]]);
       sum[k] += x;
     }
+  f->tm.ms_plan_dev = sum[5];
   f->tm.ms_pmatrix = sum[0];
   f->tm.ms_repeats = sum[1];
   f->tm.ms_prune = sum[2];
@@ -1125,6 +1247,8 @@ int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
   };
   if (f->h_out.reserve((size_t)B * 8)) return 1;
   if (get(f->h_out.p, f->d_loglik.p, (size_t)B * 8)) return 1;
+  const bool check_flags = f->dev_plan && f->flags_pending;
+  if (check_flags && get(f->h_flags.as<int32_t>() + 4, f->d_flags.p, 4 * sizeof(int32_t))) return 1;
   if (o) {
     if (get(o->xmsa_emission, f->d_xe.p, (size_t)B * fd.S * 8)) return 1;
     const bool tables = o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
@@ -1146,6 +1270,16 @@ int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
   if (f->opt_timing) cudaEventRecord(f->ev[6], s);
   LH_CUDA(cudaStreamSynchronize(s));
   LH_CUDA(cudaGetLastError());
+  if (check_flags) {
+    // what the host planner reports while planning, k_plan reports here
+    const int32_t* fl = f->h_flags.as<int32_t>() + 4;
+    f->flags_pending = false;
+    if (fl[0] != INT32_MAX) return fail("tree %d: negative branch length", fl[0]);
+    if (fl[1] != INT32_MAX) return fail("tree %d is not a valid post-order operation list", fl[1]);
+    f->slots = std::max(f->slots, (int)fl[2]);
+    const int slot_bound = std::max(f->pc[0].total_slots, f->pc[1].total_slots);
+    if (f->slots > slot_bound) return fail("internal: tree needs %d CLV slots, bound is %d", f->slots, slot_bound);
+  }
   std::memcpy(loglik, f->h_out.p, (size_t)B * 8);
   f->tm.d2h_bytes = bytes;
   if (f->opt_timing) {
@@ -1177,14 +1311,29 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   LH_CUDA(cudaEventRecord(f->ev[7], f->stream));
   LH_CUDA(cudaStreamWaitEvent(cs, f->ev[7], 0));
   if (f->opt_timing) cudaEventRecord(f->ev[0], cs);
-  if (stage_params(f, tb, cs)) return 1;
+  if (stage_params(f, tb, cs) || stage_flags(f, cs)) return 1;
   if (stage_lists(f, chunk_starts(f, true), cs)) return 1;
+  f->plan_in_call = f->dev_plan;
+  // (the plan stream must not overwrite programs an earlier run on the compute stream still reads)
+  if (f->dev_plan) LH_CUDA(cudaStreamWaitEvent(f->plan_stream, f->ev[7], 0));
   const std::vector<int>& st = f->starts;
   for (int ci = 0, k = 0; ci < f->n_chunks; ++ci) {
     for (int t0 = st[ci]; t0 < st[ci + 1]; t0 += f->seg, ++k)
       if (stage_segment(f, tb, t0, std::min(f->seg, st[ci + 1] - t0), k % lh_family::kRing, cs)) return 1;
     LH_CUDA(cudaEventRecord(f->staged_ev[ci], cs));
-    LH_CUDA(cudaStreamWaitEvent(f->stream, f->staged_ev[ci], 0));
+    if (f->dev_plan) {
+      // k_plan of the chunk on its own stream: it runs as soon as the chunk has landed, which is while
+      // the chunk before is still in its kernels (in the space k_prune's last CTAs, k_edge and k_hmm leave)
+      cudaEvent_t* pev = f->chunk_ev.data() + (size_t)kChunkEvents * ci + 7;
+      LH_CUDA(cudaStreamWaitEvent(f->plan_stream, f->staged_ev[ci], 0));
+      LH_CUDA(cudaEventRecord(pev[0], f->plan_stream));
+      launch_plan_trees(f, st[ci], st[ci + 1] - st[ci], f->plan_stream);
+      f->tm.kernel_launches += 1;
+      LH_CUDA(cudaEventRecord(pev[1], f->plan_stream));
+      LH_CUDA(cudaStreamWaitEvent(f->stream, pev[1], 0));
+    } else {
+      LH_CUDA(cudaStreamWaitEvent(f->stream, f->staged_ev[ci], 0));
+    }
     if (ci == 0 && f->opt_timing) cudaEventRecord(f->ev[2], f->stream);
     launch_chunk(f, ci, st[ci], st[ci + 1] - st[ci]);
   }
@@ -1193,6 +1342,7 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
     cudaEventRecord(f->ev[1], cs);
     cudaEventRecord(f->ev[4], f->stream);
   }
+  f->run_recorded = true;
   LH_CUDA(cudaGetLastError());
   const int rc = lh_batch_fetch(f, loglik, o);
   f->tm.ms_call = since();
@@ -1227,6 +1377,18 @@ int lh_measure_fp64_peak(int device, double* tflops) {
   cudaFree(scratch);
   LH_CUDA(cudaGetLastError());
   *tflops = best;
+  return 0;
+}
+
+// Test hook: the traversal programs of the current batch as the device holds them.
+int lh_debug_fetch_plan(lh_family_t* f, int32_t* steps, double* pblen) {
+  if (!f || !steps || !pblen) return fail("null argument");
+  if (f->B == 0) return 0;
+  LH_CUDA(cudaSetDevice(f->device));
+  LH_CUDA(cudaStreamSynchronize(f->stream));
+  const size_t T = f->fd.T;
+  LH_CUDA(cudaMemcpy(steps, f->d_plan.p, (size_t)f->B * (T - 1) * sizeof(lhb::Step), cudaMemcpyDeviceToHost));
+  LH_CUDA(cudaMemcpy(pblen, f->d_pblen.p, (size_t)f->B * (2 * T - 3) * sizeof(double), cudaMemcpyDeviceToHost));
   return 0;
 }
 

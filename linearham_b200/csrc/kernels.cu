@@ -670,7 +670,7 @@ template <int NS>
 static void launch_prune_n(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0,
                            int ntrees, cudaStream_t s) {
   size_t smem = prune_dynamic_smem_bytes(NS, c.smem_slots);
-  cudaFuncSetAttribute(k_prune<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_prune<NS>), smem);
   cudaMemsetAsync(c.work_counter, 0, sizeof(int32_t), s);
   k_prune<NS><<<c.grid, 32, smem, s>>>(f, b, c, tree0, ntrees);
 }
@@ -678,7 +678,7 @@ static void launch_prune_n(const FamilyDev& f, const BatchDev& b, const PruneCfg
 template <int NS>
 static int prune_occ_n(size_t smem) {
   int n = 0;
-  cudaFuncSetAttribute(k_prune<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_prune<NS>), smem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_prune<NS>, 32, smem);
   return n;
 }
@@ -865,7 +865,7 @@ __global__ void __launch_bounds__(32) k_repeats(FamilyDev f, BatchDev b, RepeatC
 void launch_repeats(const FamilyDev& f, const BatchDev& b, const RepeatCfg& r, int tree0, int nlist,
                     cudaStream_t s) {
   const size_t smem = repeats_smem_bytes(r.n_cols, r.n_bufs);
-  cudaFuncSetAttribute(k_repeats, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_repeats), smem);
   int occ = 0;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_repeats, 32, smem);
   int grid = std::max(1, occ) * 148;
@@ -1093,7 +1093,7 @@ __global__ void __launch_bounds__(32, LH_SR_MIN_CTAS) k_prune_sr(FamilyDev f, Ba
 void launch_prune_sr(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, const RepeatCfg& r, int tree0,
                      int nlist, cudaStream_t s) {
   const size_t smem = prune_sr_smem_bytes(r.arena_smem, r.idx_ring);
-  cudaFuncSetAttribute(k_prune_sr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_prune_sr), smem);
   int grid = std::min(r.grid, nlist * b.R);
   k_prune_sr<<<grid, 32, smem, s>>>(f, b, c, r, tree0, nlist);
 }
@@ -1101,7 +1101,7 @@ void launch_prune_sr(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, c
 int prune_sr_max_ctas_per_sm(int arena_smem, int idx_ring) {
   const size_t smem = prune_sr_smem_bytes(arena_smem, idx_ring);
   int n = 0;
-  cudaFuncSetAttribute(k_prune_sr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_prune_sr), smem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_prune_sr, 32, smem);
   return n;
 }
@@ -1419,7 +1419,7 @@ size_t hmm_smem_bytes(const FamilyDev& f, int warps) {
 void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, int tree0, int ntrees, cudaStream_t s) {
   const int warps = 4;
   size_t smem = hmm_smem_bytes(f, warps);
-  cudaFuncSetAttribute(k_hmm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_hmm), smem);
   int blocks = (ntrees + warps - 1) / warps;
   if (blocks > 148 * 16) blocks = 148 * 16;
   k_hmm<<<blocks, warps * 32, smem, s>>>(f, b, o, tree0, ntrees);

@@ -137,6 +137,26 @@ struct HmmOut {           // optional device buffers (may be null)
   double log_factor;      // log(2^256), host libm (src/HMM.cpp:353)
 };
 
+// k_plan (plan_dev.cu): the traversal planner on the device; arrays are indexed by batch tree
+struct PlanDev {
+  int32_t T;
+  int32_t tree0;               // first tree of the launch
+  const int32_t* children;     // [B][T-2][2] as in lh_tree_batch_t
+  const double* blen;          // [B][T-2][2]
+  const int32_t* root_child;   // [B]
+  const double* root_blen;     // [B]
+  int4* plan;                  // [B][T-1] out
+  double* pblen;               // [B][2T-3] out
+  int32_t* flags;              // [0] min tree with a negative branch length, [1] min malformed tree
+                               // (both INT_MAX when none), [2] deepest CLV stack met
+};
+// Raises a kernel's dynamic shared-memory limit to at least `bytes`; the limit only ever grows, so
+// handles that launch the same kernel with different sizes from different host threads do not race.
+void ensure_dynamic_smem(const void* kernel, size_t bytes);
+size_t plan_smem_bytes(int n_tips);
+bool plan_on_device_ok(int n_tips);
+void launch_plan(const PlanDev& p, int ntrees, cudaStream_t s);
+
 void launch_eigen(const BatchDev& b, int tree0, int ntrees, cudaStream_t s);
 void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees, cudaStream_t s);
 // prunes the `nlist` trees c.tree_list names; tree0 is the first tree of the chunk (its branch

@@ -116,6 +116,15 @@ class Family:
         self._ck(lib().lh_loglik_dev(self._h, C.byref(p), C.byref(n)))
         return p.value, n.value
 
+    def fetch_plan(self):
+        """(steps [B][T-1][4] int32, pblen [B][2T-3]) of the current batch as the device holds them."""
+        T = int(self.fam["n_tips"])
+        steps = np.zeros((self._n, T - 1, 4), dtype=np.int32)
+        pblen = np.zeros((self._n, 2 * T - 3))
+        self._ck(lib().lh_debug_fetch_plan(self._h, steps.ctypes.data_as(C.POINTER(C.c_int32)),
+                                           pblen.ctypes.data_as(_f64p)))
+        return steps, pblen
+
     def timings(self):
         t = _abi.Timings()
         self._ck(lib().lh_get_timings(self._h, C.byref(t)))
@@ -141,6 +150,10 @@ class Repertoire:
             self.close()
         except Exception:
             pass
+
+    def set_option(self, key, value):
+        if lib().lh_repertoire_set_option(self._h, key.encode(), int(value)):
+            raise DeviceError(lib().lh_repertoire_last_error().decode())
 
     @staticmethod
     def prepare(families):
