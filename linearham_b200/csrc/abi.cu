@@ -16,6 +16,8 @@
 #include <unordered_map>
 #include <vector>
 
+#include <emmintrin.h>
+
 #include "../../include/linearham_b200.h"
 #include "kernels.hpp"
 #include "plan.hpp"
@@ -41,6 +43,31 @@ int fail(const char* fmt, ...) {
     if (e_ != cudaSuccess)                                                               \
       return fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
   } while (0)
+
+// memcpy into a pinned staging buffer with non-temporal stores. Lines written with ordinary stores sit
+// dirty in the caches of the host cores that wrote them, and the GPU's DMA read then runs at ~8 GB/s
+// (measured: 6.7 MB in 0.8 ms); streamed lines go to memory and are read at the link rate.
+inline void stream_copy(void* dst, const void* src, size_t bytes) {
+  uint8_t* d = static_cast<uint8_t*>(dst);
+  const uint8_t* s = static_cast<const uint8_t*>(src);
+  if ((reinterpret_cast<uintptr_t>(d) & 15) != 0 || bytes < 64) {
+    std::memcpy(d, s, bytes);
+    return;
+  }
+  size_t i = 0;
+  for (; i + 64 <= bytes; i += 64) {
+    const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(s + i));
+    const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(s + i + 16));
+    const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(s + i + 32));
+    const __m128i e = _mm_loadu_si128(reinterpret_cast<const __m128i*>(s + i + 48));
+    _mm_stream_si128(reinterpret_cast<__m128i*>(d + i), a);
+    _mm_stream_si128(reinterpret_cast<__m128i*>(d + i + 16), b);
+    _mm_stream_si128(reinterpret_cast<__m128i*>(d + i + 32), c);
+    _mm_stream_si128(reinterpret_cast<__m128i*>(d + i + 48), e);
+  }
+  if (i < bytes) std::memcpy(d + i, s + i, bytes - i);
+  _mm_sfence();
+}
 
 // growable device / pinned-host buffers
 struct DevBuf {
@@ -423,7 +450,7 @@ static int bind_family(lh_family* f, const lh_family_desc_t* d) {
   // one copy of the blob; the recorded fields then get their device addresses
   const size_t bytes = own.host.size();
   if (f->d_const.reserve(bytes) || f->h_const.reserve(bytes)) return 1;
-  std::memcpy(f->h_const.p, own.host.data(), bytes);
+  stream_copy(f->h_const.p, own.host.data(), bytes);
   LH_CUDA(cudaMemcpyAsync(f->d_const.p, f->h_const.p, bytes, cudaMemcpyHostToDevice, f->stream));
   LH_CUDA(cudaStreamSynchronize(f->stream));
   for (const auto& fx : own.fixes) *fx.where = f->d_const.as<uint8_t>() + fx.off;
@@ -641,7 +668,11 @@ int configure_batch(lh_family* f, int B, int R) {
     threads = std::max(1, std::min(threads, 32));
     const int cols = (f->opt_site_patterns && f->n_pattern_trees * 2 >= B) ? f->cols[1].n_cols : f->cols[0].n_cols;
     const double host_ns = 20.0 / threads, kernel_ns = 2.7e-3 * cols * R;
-    const bool want = f->opt_device_plan < 0 ? host_ns > 0.5 * kernel_ns : f->opt_device_plan != 0;
+    // A batch of one or two chunks has nothing to hide its first chunk's planning behind: there the
+    // device planner's shorter lead-in wins whatever the thread count (Liao, 1024 samples, 16 threads:
+    // 3.48 ms per call with the host planner, 2.45 ms with k_plan).
+    const bool small = (size_t)B * lhb::records_per_pass(T) * 20 * R * sizeof(double) <= ((size_t)1 << 30);
+    const bool want = f->opt_device_plan < 0 ? (small || host_ns > 0.5 * kernel_ns) : f->opt_device_plan != 0;
     f->dev_plan = want && lhb::plan_on_device_ok(T);
   }
   f->flags_pending = false;
@@ -946,7 +977,7 @@ int stage_segment(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, int sl
     const size_t per = (size_t)(T - 2) * 2;
     uint8_t* base = f->h_ring[slot].as<uint8_t>();
     int32_t* r_ch = reinterpret_cast<int32_t*>(base);
-    double* r_bl = reinterpret_cast<double*>(base + ((size_t)n * per * sizeof(int32_t) + 15) / 16 * 16);
+    double* r_bl = reinterpret_cast<double*>(base + ((size_t)n * per * sizeof(int32_t) + 63) / 64 * 64);
     double* r_rb = r_bl + (size_t)n * per;
     int32_t* r_rc = reinterpret_cast<int32_t*>(r_rb + n);
     if (!f->pool) {
@@ -958,8 +989,8 @@ int stage_segment(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, int sl
     constexpr int kBlock = 32;  // trees per task
     f->pool->run((n + kBlock - 1) / kBlock, [&](int task, int) {
       const int lo = task * kBlock, cnt = std::min(n, lo + kBlock) - lo;
-      std::memcpy(r_ch + (size_t)lo * per, tb->children + ((size_t)t0 + lo) * per, (size_t)cnt * per * sizeof(int32_t));
-      std::memcpy(r_bl + (size_t)lo * per, tb->blen + ((size_t)t0 + lo) * per, (size_t)cnt * per * sizeof(double));
+      stream_copy(r_ch + (size_t)lo * per, tb->children + ((size_t)t0 + lo) * per, (size_t)cnt * per * sizeof(int32_t));
+      stream_copy(r_bl + (size_t)lo * per, tb->blen + ((size_t)t0 + lo) * per, (size_t)cnt * per * sizeof(double));
     });
     std::memcpy(r_rb, tb->root_blen + t0, (size_t)n * sizeof(double));
     std::memcpy(r_rc, tb->root_child + t0, (size_t)n * sizeof(int32_t));
@@ -990,9 +1021,9 @@ int stage_params(lh_family* f, const lh_tree_batch_t* tb, cudaStream_t s) {
   const size_t B = (size_t)f->B, R = (size_t)f->R;
   if (f->misc_busy) LH_CUDA(cudaEventSynchronize(f->misc_ev));
   double* misc = f->h_misc.as<double>();
-  std::memcpy(misc, tb->er, sizeof(double) * 6 * B);
-  std::memcpy(misc + 6 * B, tb->pi, sizeof(double) * 4 * B);
-  std::memcpy(misc + 10 * B, tb->rates, sizeof(double) * R * B);
+  stream_copy(misc, tb->er, sizeof(double) * 6 * B);
+  stream_copy(misc + 6 * B, tb->pi, sizeof(double) * 4 * B);
+  stream_copy(misc + 10 * B, tb->rates, sizeof(double) * R * B);
   LH_CUDA(cudaMemcpyAsync(f->d_er.p, misc, B * (10 + R) * 8, cudaMemcpyHostToDevice, s));
   LH_CUDA(cudaEventRecord(f->misc_ev, s));
   f->misc_busy = true;
@@ -1299,10 +1330,22 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   LH_CUDA(cudaSetDevice(f->device));
   const auto call_t0 = std::chrono::steady_clock::now();
   auto since = [&]() { return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - call_t0).count(); };
+  static const bool trace = getenv("LH_TRACE") != nullptr;
+  std::vector<std::pair<const char*, cudaEvent_t>> dev_marks;
+  auto mark = [&](const char* what) { if (trace) fprintf(stderr, "LHTRACE %-14s %.3f ms\n", what, since()); };
+  auto dmark = [&](const char* what, cudaStream_t st_) {
+    if (!trace) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st_);
+    dev_marks.emplace_back(what, e);
+  };
   if (check_batch(f, tb)) return 1;
+  mark("check");
   if (configure_batch(f, tb->n_trees, tb->n_rates)) return 1;
   if (f->B == 0) return 0;
   f->tm.ms_setup = since();
+  mark("configure");
   // Pipeline: the host plans one segment of trees at a time into the pinned ring, the copy
   // stream moves it to HBM, and the compute stream starts a chunk's kernels as soon as the
   // chunk's last segment has landed - planning and H2D of chunk c+1 overlap the kernels of c.
@@ -1312,7 +1355,10 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   LH_CUDA(cudaStreamWaitEvent(cs, f->ev[7], 0));
   if (f->opt_timing) cudaEventRecord(f->ev[0], cs);
   if (stage_params(f, tb, cs) || stage_flags(f, cs)) return 1;
+  dmark("cs start", cs);
   if (stage_lists(f, chunk_starts(f, true), cs)) return 1;
+  mark("params+lists");
+  dmark("cs params+lists", cs);
   f->plan_in_call = f->dev_plan;
   // (the plan stream must not overwrite programs an earlier run on the compute stream still reads)
   if (f->dev_plan) LH_CUDA(cudaStreamWaitEvent(f->plan_stream, f->ev[7], 0));
@@ -1320,6 +1366,8 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   for (int ci = 0, k = 0; ci < f->n_chunks; ++ci) {
     for (int t0 = st[ci]; t0 < st[ci + 1]; t0 += f->seg, ++k)
       if (stage_segment(f, tb, t0, std::min(f->seg, st[ci + 1] - t0), k % lh_family::kRing, cs)) return 1;
+    mark("chunk staged");
+    dmark("cs chunk copied", cs);
     LH_CUDA(cudaEventRecord(f->staged_ev[ci], cs));
     if (f->dev_plan) {
       // k_plan of the chunk on its own stream: it runs as soon as the chunk has landed, which is while
@@ -1335,7 +1383,10 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
       LH_CUDA(cudaStreamWaitEvent(f->stream, f->staged_ev[ci], 0));
     }
     if (ci == 0 && f->opt_timing) cudaEventRecord(f->ev[2], f->stream);
+    dmark("compute chunk start", f->stream);
     launch_chunk(f, ci, st[ci], st[ci + 1] - st[ci]);
+    dmark("compute chunk end", f->stream);
+    mark("chunk launched");
   }
   join_hmm_stream(f);
   if (f->opt_timing) {
@@ -1345,6 +1396,13 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   f->run_recorded = true;
   LH_CUDA(cudaGetLastError());
   const int rc = lh_batch_fetch(f, loglik, o);
+  mark("fetched");
+  for (size_t i = 0; i < dev_marks.size(); ++i) {
+    float x = 0;
+    cudaEventElapsedTime(&x, dev_marks[0].second, dev_marks[i].second);
+    fprintf(stderr, "LHTRACE dev %-20s %.3f ms\n", dev_marks[i].first, x);
+  }
+  for (auto& m : dev_marks) cudaEventDestroy(m.second);
   f->tm.ms_call = since();
   return rc;
 }

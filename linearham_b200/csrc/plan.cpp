@@ -1,6 +1,9 @@
 #include "plan.hpp"
 
+#include <emmintrin.h>
+
 #include <algorithm>
+#include <cstring>
 
 namespace lhb {
 
@@ -115,11 +118,27 @@ int plan_tree(int T, const int32_t* children, const double* blen, int32_t root_c
     const double* __restrict bl = blen;
     Step* __restrict out = steps;
     double* __restrict pb = pblen;
-    for (int pos = 0; pos < n_ops; ++pos) {
-      const int op = order[pos];
-      out[pos] = by_op[op];
-      pb[2 * pos] = bl[2 * op];
-      pb[2 * pos + 1] = bl[2 * op + 1];
+    // The destination is normally a pinned staging buffer the GPU reads next: non-temporal stores keep
+    // the lines out of this core's cache (a DMA read of dirty lines runs at a fraction of the link rate).
+    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (reinterpret_cast<uintptr_t>(pb) & 7) == 0) {
+      for (int pos = 0; pos < n_ops; ++pos) {
+        const int op = order[pos];
+        _mm_stream_si128(reinterpret_cast<__m128i*>(out + pos),
+                         _mm_loadu_si128(reinterpret_cast<const __m128i*>(by_op + op)));
+        long long l0, l1;
+        std::memcpy(&l0, bl + 2 * op, 8);
+        std::memcpy(&l1, bl + 2 * op + 1, 8);
+        _mm_stream_si64(reinterpret_cast<long long*>(pb + 2 * pos), l0);
+        _mm_stream_si64(reinterpret_cast<long long*>(pb + 2 * pos + 1), l1);
+      }
+      _mm_sfence();
+    } else {
+      for (int pos = 0; pos < n_ops; ++pos) {
+        const int op = order[pos];
+        out[pos] = by_op[op];
+        pb[2 * pos] = bl[2 * op];
+        pb[2 * pos + 1] = bl[2 * op + 1];
+      }
     }
   }
   if (max_depth > 127) return -1;
