@@ -233,7 +233,8 @@ struct lh_family {
   lhb::PruneCfg pc[2] = {};  // per column set
   lhb::EdgeCfg ec{};
   lhb::HmmOut ho{};
-  int chunk = 0, chunk_pipe = 0, wave_pipe = 0, seg = 0, occ[2] = {0, 0};
+  int chunk = 0, chunk_pipe = 0, wave_pipe = 0, wave_unit = 0, seg = 0, occ[2] = {0, 0};
+  int opt_open_unit = 1;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
   // trees that can run on site patterns (naive tip on the root edge or under the virtual root)
   std::vector<uint8_t> on_patterns;
@@ -518,6 +519,8 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_sr_arena = (int)value;
   } else if (k == "site_patterns") {
     f->opt_site_patterns = value != 0;
+  } else if (k == "open_unit") {
+    f->opt_open_unit = value != 0;
   } else if (k == "device_plan") {
     if (value < -1 || value > 1) return fail("device_plan must be -1 (auto), 0 or 1");
     f->opt_device_plan = (int)value;
@@ -773,6 +776,7 @@ int configure_batch(lh_family* f, int B, int R) {
   if (chunk > wave) chunk -= chunk % wave;
   // The pipelined call launches every `pipe_waves` waves, so its first kernels start after a
   // small part of the host planning and the copy of one chunk hides behind the kernels of another.
+  f->wave_unit = wave;
   f->wave_pipe = (std::max(wave, (resident + tiles - 1) / tiles) + wave - 1) / wave * wave;
   int chunk_pipe = std::max(1, f->opt_pipe_waves) * f->wave_pipe;
   if (f->opt_chunk_trees > 0) {
@@ -1167,8 +1171,12 @@ std::vector<int> chunk_starts(const lh_family* f, bool pipelined) {
   int t0 = 0;
   int step = pipelined ? f->chunk_pipe : f->chunk;
   if (pipelined && f->wave_pipe > 0) {
+    // The very first chunk is one item per resident CTA (`wave_unit` trees): the GPU starts after the
+    // staging of a few hundred trees; what that short launch loses is less than the lead-in it saves.
+    const int w0 = f->opt_open_unit && f->wave_unit > 0 && f->wave_unit * 2 <= f->wave_pipe ? f->wave_unit : 0;
     if (f->chunk_pipe >= 4 * f->wave_pipe && f->B >= 2 * f->chunk_pipe) {
       st.push_back(0);
+      if (w0) st.push_back(w0);
       st.push_back(f->wave_pipe);
       t0 = 3 * f->wave_pipe;
     } else {
@@ -1176,6 +1184,10 @@ std::vector<int> chunk_starts(const lh_family* f, bool pipelined) {
       // that the per-chunk launches and stream hand-offs show)
       const int floor_trees = (int)(((size_t)400 << 20) / f->rec_bytes_tree) / f->wave_pipe * f->wave_pipe;
       step = std::min(step, std::max({f->wave_pipe, f->B / 4 / f->wave_pipe * f->wave_pipe, floor_trees}));
+      if (w0 && f->B > 2 * w0) {
+        st.push_back(0);
+        t0 = w0;
+      }
     }
   }
   for (; t0 < f->B; t0 += step) st.push_back(t0);
