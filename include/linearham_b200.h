@@ -181,6 +181,8 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
  * covers 32x that many columns), "smem_slots" (-1 = auto), "smem_lo" (-1 = auto: first CLV stack level
  * of the shared-memory window), "timing" (0/1), "host_threads", "hmm_overlap" (1 = default: the forward
  * pass of a chunk runs on its own stream beside the next chunk's pruning),
+ * "chunk_growth" (1 = default: later chunks of the pipelined call grow towards the resident batch's size
+ * while the host stages faster than the GPU scores),
  * "open_unit" (1 = default: the pipelined call opens with a chunk of one work item per resident CTA),
  * "device_plan" (1: the traversal programs are built on the device by k_plan from the operation
  * lists as the caller holds them; 0: by the host planner threads; -1 = default: by the device when

@@ -234,7 +234,8 @@ struct lh_family {
   lhb::EdgeCfg ec{};
   lhb::HmmOut ho{};
   int chunk = 0, chunk_pipe = 0, wave_pipe = 0, wave_unit = 0, seg = 0, occ[2] = {0, 0};
-  int opt_open_unit = 1;
+  int opt_open_unit = 1, opt_chunk_growth = 1;
+  double stage_ratio = 1.0;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
   // trees that can run on site patterns (naive tip on the root edge or under the virtual root)
   std::vector<uint8_t> on_patterns;
@@ -519,6 +520,8 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_sr_arena = (int)value;
   } else if (k == "site_patterns") {
     f->opt_site_patterns = value != 0;
+  } else if (k == "chunk_growth") {
+    f->opt_chunk_growth = value != 0;
   } else if (k == "open_unit") {
     f->opt_open_unit = value != 0;
   } else if (k == "device_plan") {
@@ -677,6 +680,9 @@ int configure_batch(lh_family* f, int B, int R) {
     const bool small = (size_t)B * lhb::records_per_pass(T) * 20 * R * sizeof(double) <= ((size_t)1 << 30);
     const bool want = f->opt_device_plan < 0 ? (small || host_ns > 0.5 * kernel_ns) : f->opt_device_plan != 0;
     f->dev_plan = want && lhb::plan_on_device_ok(T);
+    // how much faster the host stages a tree than the GPU scores it (the device planner leaves the host
+    // a memcpy: ~6 ns per operation and thread)
+    f->stage_ratio = kernel_ns / (f->dev_plan ? 6.0 / threads : host_ns);
   }
   f->flags_pending = false;
   f->run_recorded = false;
@@ -1190,7 +1196,18 @@ std::vector<int> chunk_starts(const lh_family* f, bool pipelined) {
       }
     }
   }
-  for (; t0 < f->B; t0 += step) st.push_back(t0);
+  // Later chunks grow (up to the resident batch's 16 waves) as long as the host stages a chunk faster
+  // than the GPU scores the one before it: fewer launches and launch tails over the bulk of the batch.
+  double growth = 1.0;
+  if (pipelined && f->opt_chunk_growth && f->wave_pipe > 0 && f->opt_chunk_trees == 0)
+    growth = std::min(2.0, std::max(1.0, 0.6 * f->stage_ratio));
+  for (; t0 < f->B; t0 += step) {
+    st.push_back(t0);
+    if (growth > 1.0 && st.size() > 2) {
+      int next = (int)(step * growth) / f->wave_pipe * f->wave_pipe;
+      step = std::max(step, std::min(next, f->chunk / f->wave_pipe * f->wave_pipe));
+    }
+  }
   st.push_back(f->B);
   return st;
 }

@@ -14,7 +14,7 @@ for name, B in (("c3", 4096), ("c4", 2048), ("c4", 16384)):
 for name, (fam, tb) in cases.items():
     hs = {ou: device.Family(fam) for ou in (0, 1)}
     for ou, f in hs.items():
-        f.set_option("open_unit", ou)
+        f.set_option("chunk_growth", ou)
         if name == "c4x2048": f.set_option("host_threads", 4)
         for _ in range(3): f.score(tb)
     ts = {0: [], 1: []}
@@ -23,6 +23,6 @@ for name, (fam, tb) in cases.items():
             t0 = time.perf_counter(); f.score(tb); ts[ou].append(time.perf_counter() - t0)
     for ou in (0, 1):
         tm = hs[ou].timings()
-        print(name, "open_unit", ou, "median %.3f ms  p10 %.3f" % (1e3 * np.median(ts[ou]), 1e3 * np.percentile(ts[ou], 10)),
+        print(name, "chunk_growth", ou, "median %.3f ms  p10 %.3f" % (1e3 * np.median(ts[ou]), 1e3 * np.percentile(ts[ou], 10)),
               {k: round(tm[k], 3) for k in ("ms_plan", "ms_h2d", "ms_kernels", "kernel_launches", "device_plan")})
     for f in hs.values(): f.close()
