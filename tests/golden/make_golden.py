@@ -95,6 +95,10 @@ def main():
             fam = synth.make_family(d, genes, n, seed=seed, name=name)
             samples = synth.tree_samples(np.random.default_rng(seed + 1000), fam["tree"], B, walk="cumulative")
             bundle(name, fam["yaml_path"], os.path.join(d, "hmm"), samples, R)
+        # the smallest tree the path accepts: two observed sequences + naive = one operation (3 tips)
+        fam = synth.make_family(d, genes, 2, seed=1310, name="synth_n2")
+        samples = synth.tree_samples(np.random.default_rng(2310), fam["tree"], 5, outgroup="naive")
+        bundle("synth_n2", fam["yaml_path"], os.path.join(d, "hmm"), samples, 4)
     make_light()
 
 
