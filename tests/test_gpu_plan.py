@@ -95,3 +95,36 @@ def test_device_planner_reports_bad_trees():
     # the handle is fine afterwards
     assert rel_err(f.score(tb), exp["loglik"]) <= 1e-9
     f.close()
+
+
+def test_large_family_3000_leaves_matches_the_port():
+    """A tree far beyond BASELINE's largest (1000 leaves): CLV stack 12 deep, most levels in the L2 scratch,
+    36 KB of planner tables per tree. Emissions and scaler counts must match the port; at this size the
+    reference's own forward pass no longer yields a finite log-likelihood, and the class must agree."""
+    from linearham_b200 import host
+    from oracle import pyoracle as po
+    cfg = dict(n_leaves=3000, B=3, R=4, fam_seed=1700, tree_seed=2700, outgroup="naive")
+    with tempfile.TemporaryDirectory() as d:
+        ff = workload.write_family_files(cfg, d)
+        ph = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+        fam = ph.family()
+        ph.close()
+        tb, _, _ = workload.tree_batch(cfg, ff, 3)
+    assert fam["n_tips"] == 3001
+    pll, pout = po.port_score_batch(fam, tb, want_outputs=True)
+    hs, hp, _ = host_plan(fam["n_tips"], tb)
+    for dp in (1, 0):
+        f = device.Family(fam)
+        f.set_option("device_plan", dp)
+        ll, out = f.score(tb, outputs=True)
+        if dp:
+            f.upload(tb)
+            ds, dpb = f.fetch_plan()
+            assert np.array_equal(ds, hs) and np.array_equal(dpb, hp)
+        f.close()
+        assert np.array_equal(np.isfinite(ll), np.isfinite(pll))
+        ok = np.isfinite(pll)
+        assert rel_err(ll[ok], pll[ok]) <= 1e-9
+        assert rel_err(out["xmsa_emission"], pout["xmsa_emission"]) <= 1e-9
+        for k in ("germ_scalers", "vd_scalers", "dj_scalers"):
+            assert np.array_equal(out[k], pout[k]), k
