@@ -111,6 +111,11 @@ typedef struct lh_outputs {
   int32_t* germ_scalers;    /* [B][3] vgerm, dgerm, jgerm scaler counts       */
   int32_t* vd_scalers;      /* [B][vd_sites]                                  */
   int32_t* dj_scalers;      /* [B][dj_sites]                                  */
+  /* per rate category k and xMSA column: log( L_k(column) / pi[naive base] ), the unweighted category
+   * likelihoods whose mean is xmsa_emission. This is what the reference's ancestral-sequence step
+   * recomputes per kept tree, site and rate with phylomd (scripts/run_bootstrap_asr_ess.R:84-87) to
+   * sample the rate category of a site; -inf where the category's likelihood is not positive.       */
+  double*  site_rate_loglik; /* [B][R][S_x]                                   */
 } lh_outputs_t;
 
 typedef struct lh_timings {

@@ -52,6 +52,7 @@ class Outputs(C.Structure):
         ("xmsa_emission", _f64p), ("vgerm_forward", _f64p), ("vd_forward", _f64p),
         ("dgerm_forward", _f64p), ("dj_forward", _f64p), ("jgerm_forward", _f64p),
         ("germ_scalers", _i32p), ("vd_scalers", _i32p), ("dj_scalers", _i32p),
+        ("site_rate_loglik", _f64p),
     ]
 
 
@@ -123,7 +124,7 @@ def tree_batch(tb):
     return t, keep
 
 
-def alloc_outputs(fam, B, fields=None):
+def alloc_outputs(fam, B, fields=None, n_rates=None):
     """Allocate numpy buffers for lh_outputs_t; returns (Outputs, dict of arrays)."""
     shapes = {
         "xmsa_emission": ((B, fam["n_sites"]), np.float64),
@@ -136,6 +137,8 @@ def alloc_outputs(fam, B, fields=None):
         "vd_scalers": ((B, fam["vd_sites"]), np.int32),
         "dj_scalers": ((B, max(fam["dj_sites"], 1)), np.int32),
     }
+    if fields is not None and "site_rate_loglik" in fields:   # only on request: B x R x S_x doubles
+        shapes["site_rate_loglik"] = ((B, int(n_rates), fam["n_sites"]), np.float64)
     o = Outputs()
     arrs = {}
     for k, (shape, dt) in shapes.items():

@@ -245,7 +245,8 @@ struct lh_family {
   DevBuf d_list;                   // [B] tree indices, per chunk: pattern trees, then the others
   PinBuf h_list;
   lh_timings_t tm{};
-  bool want_tables = false;
+  bool want_tables = false, want_rate_ll = false;
+  DevBuf d_rate_ll;
   std::unique_ptr<lhb::WorkerPool> pool;  // planner threads, started on first use
   std::vector<lhb::PlanScratch> plan_scratch;
 };
@@ -272,7 +273,7 @@ void lh_family_destroy(lh_family_t* f) {
                     &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
                     &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_rs_steps,
                     &f->d_rs_idx, &f->d_rs_ecls, &f->d_rs_peak, &f->d_rs_gclv, &f->d_rs_gcnt, &f->d_counters,
-                    &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags};
+                    &f->d_rate_ll, &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags};
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
   f->h_misc.release();
@@ -832,6 +833,10 @@ int configure_batch(lh_family* f, int B, int R) {
   ec.cols_pad_pat = f->pc[1].cols_pad;
   ec.col_of_site = f->d_col_of_site;
   ec.log_threshold = std::log(1.0 / std::pow(2.0, 256));
+  if (f->want_rate_ll) {
+    if (f->d_rate_ll.reserve((size_t)B * R * S * sizeof(double))) return 1;
+    ec.rate_ll = f->d_rate_ll.as<double>();
+  }
 
   // site repeats for the trees on patterns
   f->use_sr = false;
@@ -1311,6 +1316,10 @@ int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
   if (check_flags && get(f->h_flags.as<int32_t>() + 4, f->d_flags.p, 4 * sizeof(int32_t))) return 1;
   if (o) {
     if (get(o->xmsa_emission, f->d_xe.p, (size_t)B * fd.S * 8)) return 1;
+    if (o->site_rate_loglik) {
+      if (!f->want_rate_ll) return fail("site_rate_loglik was not produced by the last run (ask for it in lh_score_batch)");
+      if (get(o->site_rate_loglik, f->d_rate_ll.p, (size_t)B * f->R * fd.S * 8)) return 1;
+    }
     const bool tables = o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
                         o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers;
     if (tables) {
@@ -1356,6 +1365,7 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   if (!f->bound) return fail("no family bound to the handle (the last lh_family_rebind failed)");
   f->want_tables = o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
                          o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers);
+  f->want_rate_ll = o && o->site_rate_loglik;
   LH_CUDA(cudaSetDevice(f->device));
   const auto call_t0 = std::chrono::steady_clock::now();
   auto since = [&]() { return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - call_t0).count(); };

@@ -1163,6 +1163,12 @@ __global__ void __launch_bounds__(128) k_edge(FamilyDev f, BatchDev b, EdgeCfg c
       const double t2 = (pi2 * mc[2]) * rg[2];
       const double t3 = (pi3 * mc[3]) * rg[3];
       double term = (t0 + t1) + (t2 + t3);
+      if (cfg.rate_ll) {
+        double v = log(term);  // -inf for 0
+        if (c) v += c * cfg.log_threshold;
+        if (code != 4) v -= eig[36 + code];
+        cfg.rate_ll[((size_t)t * R + k) * S + site] = term > 0.0 ? v : -INFINITY;
+      }
       if (term > 0.0) {  // :1225
         term *= weight;
         // bring acc and term to the smaller count (exact: powers of two)

@@ -129,6 +129,7 @@ struct EdgeCfg {
   const int32_t* col_of_site;          // [S] pattern index of each xMSA column
   const uint16_t* ecls;                // site repeats: [chunk][cols_pad_pat] class of each pattern, or null
   double log_threshold;
+  double* rate_ll;                     // optional [B][R][S]: per-category log( L_k / pi[naive] )
 };
 
 struct HmmOut {           // optional device buffers (may be null)

@@ -78,7 +78,7 @@ class Family:
         t, keep = _abi.tree_batch(tb)
         ll = np.zeros(t.n_trees)
         if outputs:
-            o, arrs = _abi.alloc_outputs(self.fam, t.n_trees, None if outputs is True else outputs)
+            o, arrs = _abi.alloc_outputs(self.fam, t.n_trees, None if outputs is True else outputs, n_rates=t.n_rates)
             self._ck(lib().lh_score_batch(self._h, C.byref(t), ll.ctypes.data_as(_f64p), C.byref(o)))
             return ll, arrs
         self._ck(lib().lh_score_batch(self._h, C.byref(t), ll.ctypes.data_as(_f64p), None))

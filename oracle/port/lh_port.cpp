@@ -391,7 +391,7 @@ static double port_score_one(const lh_family_desc_t& F, int R, const int32_t* ch
                              double* xe_out, double* vgerm_fwd_out, double* vd_fwd_out,
                              double* dgerm_fwd_out, double* dj_fwd_out,
                              double* jgerm_fwd_out, int32_t* germ_scalers_out,
-                             int32_t* vd_scalers_out, int32_t* dj_scalers_out) {
+                             int32_t* vd_scalers_out, int32_t* dj_scalers_out, double* srl_out = nullptr) {
   const int T = F.n_tips, S = F.n_sites, span = 4 * R, n_ops = T - 2;
 
   // ---- pruning: libptpll TraversalUpdate(FULL) + LogLikelihood ------------
@@ -454,6 +454,7 @@ static double port_score_one(const lh_family_desc_t& F, int R, const int32_t* ch
     const unsigned* sp = &scaler[(size_t)(n_ops - 1) * S];
     const unsigned* sc = (root_child >= T) ? &scaler[(size_t)(root_child - T) * S] : nullptr;
     const double weight = 1.0 / R;  // pll.c:746-747
+    std::vector<double> rate_term(R);
     for (int n = 0; n < S; n++) {
       double terma = 0;
       for (int k = 0; k < R; k++) {
@@ -465,9 +466,20 @@ static double port_score_one(const lh_family_desc_t& F, int R, const int32_t* ch
           terma_r += pi[i] * termb * clvp[(size_t)n * span + 4 * k + i];
         }
         if (terma_r > 0.) terma += terma_r * weight;
+        rate_term[k] = terma_r;
       }
       double site_lk = std::log(terma);
       unsigned cnt = sp[n] + (sc ? sc[n] : 0u);
+      // per-category read-out: what scripts/run_bootstrap_asr_ess.R:84-87 recomputes with phylomd
+      // (phylo.likelihood on the rate-scaled tree / pi[naive base]); the site's scaler count is shared
+      // by its categories (core_partials.c:648-659)
+      if (srl_out)
+        for (int k = 0; k < R; k++) {
+          double v = std::log(rate_term[k]);
+          if (cnt) v += cnt * std::log(kScaleThreshold);
+          if (F.tip_codes[n] != 4) v -= std::log(pi[F.tip_codes[n]]);
+          srl_out[(size_t)k * S + n] = rate_term[k] > 0. ? v : -INFINITY;
+        }
       if (cnt) site_lk += cnt * std::log(kScaleThreshold);
       // naive correction, src/PhyloHMM.cpp:228-237 (row 0 of the xMSA is the naive)
       int nb = F.tip_codes[n];
@@ -597,7 +609,8 @@ extern "C" int port_score_batch(const lh_family_desc_t* F, const lh_tree_batch_t
         (o && o->jgerm_forward) ? o->jgerm_forward + (size_t)b * F->n_j : nullptr,
         (o && o->germ_scalers) ? o->germ_scalers + 3 * b : nullptr,
         (o && o->vd_scalers) ? o->vd_scalers + (size_t)b * F->vd_sites : nullptr,
-        (o && o->dj_scalers) ? o->dj_scalers + (size_t)b * F->dj_sites : nullptr);
+        (o && o->dj_scalers) ? o->dj_scalers + (size_t)b * F->dj_sites : nullptr,
+        (o && o->site_rate_loglik) ? o->site_rate_loglik + (size_t)b * R * S : nullptr);
   }
   return 0;
 }

@@ -66,7 +66,7 @@ def port_gamma_cats(alpha, n):
     return out
 
 
-def port_score_batch(fam, tb, want_outputs=True):
+def port_score_batch(fam, tb, want_outputs=True, fields=None):
     """fam / tb: dicts as in linearham_b200._abi. Returns (loglik[B], outputs dict)."""
     from linearham_b200 import _abi
     d, k1 = _abi.family_desc(fam)
@@ -74,7 +74,7 @@ def port_score_batch(fam, tb, want_outputs=True):
     B = t.n_trees
     ll = np.zeros(B)
     if want_outputs:
-        o, arrs = _abi.alloc_outputs(fam, B)
+        o, arrs = _abi.alloc_outputs(fam, B, fields, n_rates=t.n_rates)
         port_lib().port_score_batch(C.byref(d), C.byref(t), ll.ctypes.data_as(_f64p), C.byref(o))
     else:
         arrs = {}
