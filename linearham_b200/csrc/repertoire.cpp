@@ -129,10 +129,12 @@ int lh_repertoire_score(lh_repertoire_t* r, lh_repertoire_item_t* items, int32_t
       if (!f) {
         rc = lh_family_create(&f, it.desc, r->device);
         if (!rc) rc = lh_set_option(f, "host_threads", r->host_threads);
-        // The slots share the host: between them the planner threads keep ahead of the GPU, and k_plan
-        // launches of a few hundred trees are latency-bound (measured on C5: 247 ms per pass with the
-        // host planner, 260 ms with k_plan). "device_plan" can still be set through lh_repertoire_set_option.
-        if (!rc) rc = lh_set_option(f, "device_plan", 0);
+        // The slots share the host. With two or more host threads per slot the planner threads keep
+        // ahead of the GPU and k_plan launches of a few hundred trees only add latency (C5, 16 cores, 6
+        // slots: 247 ms per pass with the host planner, 260 ms with k_plan); with one thread per slot
+        // (8 ranks on one host) the host is the bottleneck and the device plans (C5 on 4 cores: 297 ms
+        // vs 279 ms). "device_plan" can still be set through lh_repertoire_set_option.
+        if (!rc) rc = lh_set_option(f, "device_plan", r->host_threads <= 1 ? 1 : 0);
         for (const auto& kv : r->options)
           if (!rc) rc = lh_set_option(f, kv.first.c_str(), kv.second);
       } else {
