@@ -351,17 +351,39 @@ static int bind_family(lh_family* f, const lh_family_desc_t* d) {
     // CLVs away from the naive tip, so pruning visits each pattern once (first occurrence order)
     f->cols[0].n_cols = S;
     f->cols[0].codes.assign(d->tip_codes, d->tip_codes + (size_t)T * S);
+    // (columns are compared through a transposed copy: contiguous keys, one pass over the matrix)
     std::vector<int32_t> col_of_site(S), rep;
-    std::unordered_map<std::string, int32_t> seen;
-    std::string key((size_t)T - 1, '\0');
+    const int KT = T - 1;
+    std::vector<uint8_t> tr((size_t)S * KT);
+    for (int r0 = 1; r0 < T; r0 += 64)
+      for (int c = 0; c < S; ++c)
+        for (int r = r0; r < std::min(T, r0 + 64); ++r) tr[(size_t)c * KT + (r - 1)] = d->tip_codes[(size_t)r * S + c];
+    std::unordered_map<uint64_t, std::vector<int32_t>> seen;  // column hash -> pattern ids with that hash
+    seen.reserve((size_t)S * 2);
     for (int c = 0; c < S; ++c) {
-      for (int r = 1; r < T; ++r) key[r - 1] = (char)d->tip_codes[(size_t)r * S + c];
-      auto it = seen.find(key);
-      if (it == seen.end()) {
-        it = seen.emplace(key, (int32_t)rep.size()).first;
-        rep.push_back(c);
+      const uint8_t* key = &tr[(size_t)c * KT];
+      uint64_t h = 1469598103934665603ull;
+      int i = 0;
+      for (; i + 8 <= KT; i += 8) {
+        uint64_t w;
+        std::memcpy(&w, key + i, 8);
+        h = (h ^ w) * 1099511628211ull;
+        h ^= h >> 29;
       }
-      col_of_site[c] = it->second;
+      for (; i < KT; ++i) h = (h ^ key[i]) * 1099511628211ull;
+      std::vector<int32_t>& bucket = seen[h];
+      int32_t id = -1;
+      for (int32_t cand : bucket)
+        if (std::memcmp(&tr[(size_t)rep[cand] * KT], key, (size_t)KT) == 0) {
+          id = cand;
+          break;
+        }
+      if (id < 0) {
+        id = (int32_t)rep.size();
+        rep.push_back(c);
+        bucket.push_back(id);
+      }
+      col_of_site[c] = id;
     }
     const int U = (int)rep.size();
     f->cols[1].n_cols = U;
@@ -746,16 +768,16 @@ int configure_batch(lh_family* f, int B, int R) {
       const int NS = pc.sites_per_thread;
       if ((uint64_t)T * pc.n_tiles * 32 >= (1ull << 32)) return fail("tip-code table too large");  // the kernel indexes it with 32 bits
       std::vector<uint32_t> ct((size_t)T * pc.n_tiles * 32, 0u);
-      for (int r = 0; r < T; ++r)
-        for (int tile = 0; tile < pc.n_tiles; ++tile)
-          for (int lane = 0; lane < 32; ++lane) {
-            uint32_t word = 0;
-            for (int u = 0; u < NS; ++u) {
-              const int site = tile * 32 * NS + u * 32 + lane;
-              if (site < NC) word |= (uint32_t)(cset.codes[(size_t)r * NC + site] * 32u) << (8 * u);
-            }
-            ct[((size_t)r * pc.n_tiles + tile) * 32 + lane] = word;
+      for (int r = 0; r < T; ++r) {
+        const uint8_t* row = &cset.codes[(size_t)r * NC];
+        for (int tile = 0; tile < pc.n_tiles; ++tile) {
+          uint32_t* w = &ct[((size_t)r * pc.n_tiles + tile) * 32];
+          for (int u = 0; u < NS; ++u) {
+            const int s0 = tile * 32 * NS + u * 32, n = std::min(32, NC - s0);
+            for (int lane = 0; lane < n; ++lane) w[lane] |= (uint32_t)(row[s0 + lane] * 32u) << (8 * u);
           }
+        }
+      }
       LH_CUDA(cudaStreamSynchronize(f->stream));
       if (cset.d_codes_t.reserve(ct.size() * 4)) return 1;
       LH_CUDA(cudaMemcpy(cset.d_codes_t.p, ct.data(), ct.size() * 4, cudaMemcpyHostToDevice));
