@@ -401,7 +401,9 @@ def main():
         tp = os.path.join(ROOT, "profiles", f"k_prune_traffic_{args.config}.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+                # the ncu capture ran one launch of `trees_in_launch` trees: scale to this run's launch size
+                tj = json.load(open(tp))
+                traffic = tj["dram_bytes_per_launch"] / tj["trees_in_launch"] * (Bs / max(1, acc["prune_launches"] // args.steps))
             except Exception:
                 traffic = None
         if cpu_ll is not None:
@@ -415,7 +417,9 @@ def main():
             "ms_per_step": ms_kernels / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": config, "impl": "b200",
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": "k_prune", "peak_source": peak_src,
+                         "traffic": traffic, "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of one k_prune launch "
+                         "(profiles/k_prune_traffic_<config>.json), per tree x trees_per_launch",
+                         "kernel": "k_prune", "peak_source": peak_src,
                          "algorithmic_bytes_per_tree": bytes_tree, "trees_per_launch": Bs / max(1, acc["prune_launches"] // args.steps),
                          "avg_launch_ms": acc["ms_prune"] / max(1, acc["prune_launches"]),
                          "note": "inner CLVs live in registers/shared memory (on-chip stack), so DRAM traffic is far "
