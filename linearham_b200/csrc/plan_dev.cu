@@ -29,14 +29,26 @@ __device__ __forceinline__ uint32_t pack_down(uint32_t start, int want, uint32_t
   return start << 17 | (uint32_t)(want & 0xff) | level << 8 | par << 16;
 }
 
+// Shared memory through 32-bit shared-space addresses (through generic pointers every access in the
+// lane-0 sweeps rebuilt the CTA's shared window base with an S2R on the dependent chain).
+__device__ __forceinline__ uint32_t lds(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v));
+}
+
 __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
   extern __shared__ uint32_t sm[];
   const int T = p.T, n_ops = T - 2, n_nodes = T + n_ops, lane = threadIdx.x;
   // tables of the inner nodes only (a tip's `up` word is 0 and nobody reads its `down` word);
-  // node ids fit 16 bits (plan_on_device_ok)
-  uint32_t* __restrict__ up = sm;                                           // [n_ops] need | size << 8
-  uint32_t* __restrict__ dn = sm + n_ops;                                   // [n_ops] reference counts, then the down word
-  uint16_t* __restrict__ ch = reinterpret_cast<uint16_t*>(sm + 2 * n_ops);  // [2 n_ops]
+  // node ids fit 16 bits (plan_on_device_ok), so an operation's two children are one word
+  const uint32_t s_up = (uint32_t)__cvta_generic_to_shared(sm);  // [n_ops] need | size << 8
+  const uint32_t s_dn = s_up + 4u * n_ops;                       // [n_ops] reference counts, then the down word
+  const uint32_t s_ch = s_dn + 4u * n_ops;                       // [n_ops] child a | child b << 16
+  uint32_t* dn_gen = sm + n_ops;                                 // (generic view, for the atomics)
   const int t = p.tree0 + blockIdx.x;
   const int32_t* __restrict__ gch = p.children + (size_t)t * 2 * n_ops;
   const double* __restrict__ gbl = p.blen + (size_t)t * 2 * n_ops;
@@ -47,7 +59,7 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
 
   // 1. load + checks: children precede parents, every inner node is consumed exactly once
   bool neg = !(rbl >= 0.0), bad = false;
-  for (int i = lane; i < n_ops; i += 32) dn[i] = 0;
+  for (int i = lane; i < n_ops; i += 32) sts(s_dn + 4u * i, 0u);
   __syncwarp();
 #pragma unroll 4
   for (int op = lane; op < n_ops; op += 32) {
@@ -57,17 +69,16 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
     if ((uint32_t)c.x >= (uint32_t)(T + op) || (uint32_t)c.y >= (uint32_t)(T + op)) {
       bad = true;
     } else {
-      ch[2 * op] = (uint16_t)c.x;
-      ch[2 * op + 1] = (uint16_t)c.y;
-      if (c.x >= T) atomicAdd(&dn[c.x - T], 1u);
-      if (c.y >= T) atomicAdd(&dn[c.y - T], 1u);
+      sts(s_ch + 4u * op, (uint32_t)c.x | (uint32_t)c.y << 16);
+      if (c.x >= T) atomicAdd(&dn_gen[c.x - T], 1u);
+      if (c.y >= T) atomicAdd(&dn_gen[c.y - T], 1u);
     }
   }
   if (rc < 0 || rc >= n_nodes - 1) bad = true;
-  else if (lane == 0 && rc >= T) atomicAdd(&dn[rc - T], 1u);
+  else if (lane == 0 && rc >= T) atomicAdd(&dn_gen[rc - T], 1u);
   __syncwarp();
-  for (int i = lane; i < n_ops - 1; i += 32) bad |= dn[i] != 1u;
-  if (lane == 0) bad |= dn[n_ops - 1] != 0u;
+  for (int i = lane; i < n_ops - 1; i += 32) bad |= lds(s_dn + 4u * i) != 1u;
+  if (lane == 0) bad |= lds(s_dn + 4u * (n_ops - 1)) != 0u;
   neg = __any_sync(0xffffffffu, neg);
   bad = __any_sync(0xffffffffu, bad);
   if (neg || bad) {
@@ -77,15 +88,20 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
     for (int i = lane; i < 2 * n_ops + 1; i += 32) pb[i] = 0.0;
     return;
   }
-  auto up_of = [&](int id) -> uint32_t { return id >= T ? up[id - T] : 0u; };
+  auto up_of = [&](int id) -> uint32_t { return id >= T ? lds(s_up + 4u * (id - T)) : 0u; };
 
-  // 2. bottom-up: need (live CLVs, 0 for a tip) and size (inner nodes) of every subtree
+  // 2. bottom-up: need (live CLVs, 0 for a tip) and size (inner nodes) of every subtree.
+  // The children of the next operation are fetched while this one is computed: the chain through
+  // `up` is then one shared-memory load per operation.
   if (lane == 0) {
+    uint32_t c_next = lds(s_ch);
     for (int op = 0; op < n_ops; ++op) {
-      const uint32_t ua = up_of(ch[2 * op]), ub = up_of(ch[2 * op + 1]);
+      const uint32_t c = c_next;
+      if (op + 1 < n_ops) c_next = lds(s_ch + 4u * (op + 1));
+      const uint32_t ua = up_of(c & 0xffff), ub = up_of(c >> 16);
       const uint32_t na = ua & 0xff, nb = ub & 0xff;
       const uint32_t n = na == nb ? na + 1 : max(na, nb);
-      up[op] = n | ((ua >> 8) + (ub >> 8) + 1) << 8;
+      sts(s_up + 4u * op, n | ((ua >> 8) + (ub >> 8) + 1) << 8);
     }
   }
   __syncwarp();
@@ -95,27 +111,32 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
   int4 final_step = make_int4(-1, rc, -1, 0);
   int deepest = 0;
   if (rc < T) {
-    if (lane == 0) dn[root_op] = pack_down(0, -1, 0, 0);
-  } else if ((up[rc - T] & 0xff) >= (up[root_op] & 0xff)) {  // root_child first, parked in slot 0
-    final_step = make_int4(-1, -2, -1, 0);
-    if (lane == 0) {
-      dn[rc - T] = pack_down(0, 0, 0, 0);
-      dn[root_op] = pack_down(up[rc - T] >> 8, -1, 1, 0);
-    }
-    deepest = 1;
-  } else {                                                   // the virtual root first, parked in slot 0
-    final_step = make_int4(-2, -1, -1, 0);
-    if (lane == 0) {
-      dn[root_op] = pack_down(0, 0, 0, 0);
-      dn[rc - T] = pack_down(up[root_op] >> 8, -1, 1, 0);
+    if (lane == 0) sts(s_dn + 4u * root_op, pack_down(0, -1, 0, 0));
+  } else {
+    const uint32_t u_rc = lds(s_up + 4u * (rc - T)), u_root = lds(s_up + 4u * root_op);
+    if ((u_rc & 0xff) >= (u_root & 0xff)) {  // root_child first, parked in slot 0
+      final_step = make_int4(-1, -2, -1, 0);
+      if (lane == 0) {
+        sts(s_dn + 4u * (rc - T), pack_down(0, 0, 0, 0));
+        sts(s_dn + 4u * root_op, pack_down(u_rc >> 8, -1, 1, 0));
+      }
+    } else {                                 // the virtual root first, parked in slot 0
+      final_step = make_int4(-2, -1, -1, 0);
+      if (lane == 0) {
+        sts(s_dn + 4u * root_op, pack_down(0, 0, 0, 0));
+        sts(s_dn + 4u * (rc - T), pack_down(u_root >> 8, -1, 1, 0));
+      }
     }
     deepest = 1;
   }
   if (lane == 0) {
+    uint32_t c_next = lds(s_ch + 4u * (n_ops - 1));
     for (int op = n_ops - 1; op >= 0; --op) {
-      const int a = ch[2 * op], b = ch[2 * op + 1];
+      const uint32_t c = c_next;
+      if (op > 0) c_next = lds(s_ch + 4u * (op - 1));
+      const int a = c & 0xffff, b = c >> 16;
+      const uint32_t d = lds(s_dn + 4u * op);
       const uint32_t ua = up_of(a), ub = up_of(b);
-      const uint32_t d = dn[op];
       const uint32_t level = (d >> 8) & 0xff, begin = d >> 17;
       const uint32_t both = (uint32_t)(a >= T) & (uint32_t)(b >= T);
       const uint32_t a_first = (ua & 0xff) >= (ub & 0xff);
@@ -124,8 +145,8 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
       const uint32_t lo_a = base + (b_parks << 8) + (a_parks ? level : 0xffu);
       const uint32_t lo_b = base + (a_parks << 8) + (b_parks ? level : 0xffu);
       const uint32_t st_a = begin + (a_first ? 0u : ub >> 8), st_b = begin + (a_first ? ua >> 8 : 0u);
-      if (a >= T) dn[a - T] = st_a << 17 | lo_a;
-      if (b >= T) dn[b - T] = st_b << 17 | lo_b;
+      if (a >= T) sts(s_dn + 4u * (a - T), st_a << 17 | lo_a);
+      if (b >= T) sts(s_dn + 4u * (b - T), st_b << 17 | lo_b);
     }
   }
   __syncwarp();
@@ -133,11 +154,12 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
   // 4. every operation writes its step at its program position
 #pragma unroll 4
   for (int op = lane; op < n_ops; op += 32) {
-    const int a = ch[2 * op], b = ch[2 * op + 1];
+    const uint32_t c = lds(s_ch + 4u * op);
+    const int a = c & 0xffff, b = c >> 16;
     const double2 l = *reinterpret_cast<const double2*>(gbl + 2 * op);
-    const uint32_t ua = up_of(a), ub = up_of(b), d = dn[op];
+    const uint32_t ua = up_of(a), ub = up_of(b), d = lds(s_dn + 4u * op);
     const uint32_t level = (d >> 8) & 0xff, begin = d >> 17;
-    const uint32_t pos = begin + (up[op] >> 8) - 1;
+    const uint32_t pos = begin + (lds(s_up + 4u * op) >> 8) - 1;
     const uint32_t ia = a >= T, ib = b >= T, both = ia & ib;
     const uint32_t a_first = (ua & 0xff) >= (ub & 0xff);
     const uint32_t a_parks = both & a_first, b_parks = both & (a_first ^ 1u);
