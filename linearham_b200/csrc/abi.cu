@@ -137,23 +137,25 @@ int upload(const T* src, size_t n, const T** dst, ConstArena& arena) {
 // dense column-major [rows x cols] -> CSC on the device (rows ascending inside a column,
 // i.e. the order of the reference's dense dot product with the zero terms dropped)
 int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, ConstArena& owned) {
-  std::vector<int32_t> colptr(cols + 1, 0), row;
-  std::vector<double> val;
+  std::vector<int32_t> colptr(cols + 1, 0);
+  std::vector<double> ent;  // (value, row as the low word of a double) pairs
   for (int j = 0; j < cols; ++j) {
     for (int i = 0; i < rows; ++i) {
       double v = dense[(size_t)j * rows + i];
       if (v != 0.0) {
-        row.push_back(i);
-        val.push_back(v);
+        double packed = 0.0;
+        const int64_t row64 = i;
+        std::memcpy(&packed, &row64, sizeof(packed));
+        ent.push_back(v);
+        ent.push_back(packed);
       }
     }
-    colptr[j + 1] = (int32_t)row.size();
+    colptr[j + 1] = (int32_t)(ent.size() / 2);
   }
   out->rows = rows;
   out->cols = cols;
   if (upload(colptr.data(), colptr.size(), &out->colptr, owned)) return 1;
-  if (upload(row.data(), row.size(), &out->row, owned)) return 1;
-  if (upload(val.data(), val.size(), &out->val, owned)) return 1;
+  if (upload(ent.data(), ent.size(), reinterpret_cast<const double**>(&out->ent), owned)) return 1;
   return 0;
 }
 

@@ -1283,9 +1283,24 @@ __device__ __forceinline__ int fill_region(int n, const int32_t* __restrict__ of
 
 // row-vector times sparse matrix: out[j] = sum_k prev[k] * M[k][j]
 __device__ __forceinline__ double csc_dot(const CscDev& m, const double* prev, int j) {
+  // The terms are added in row order (the reference's dense dot product with the zero terms dropped);
+  // four entries and their operands are fetched ahead of the four dependent additions.
   double acc = 0.0;
   const int e = m.colptr[j + 1];
-  for (int p = m.colptr[j]; p < e; ++p) acc += prev[m.row[p]] * m.val[p];
+  int p = m.colptr[j];
+  for (; p + 4 <= e; p += 4) {
+    const double2 e0 = __ldg(m.ent + p), e1 = __ldg(m.ent + p + 1), e2 = __ldg(m.ent + p + 2), e3 = __ldg(m.ent + p + 3);
+    const double x0 = prev[__double2loint(e0.y)], x1 = prev[__double2loint(e1.y)];
+    const double x2 = prev[__double2loint(e2.y)], x3 = prev[__double2loint(e3.y)];
+    acc += x0 * e0.x;
+    acc += x1 * e1.x;
+    acc += x2 * e2.x;
+    acc += x3 * e3.x;
+  }
+  for (; p < e; ++p) {
+    const double2 en = __ldg(m.ent + p);
+    acc += prev[__double2loint(en.y)] * en.x;
+  }
   return acc;
 }
 

@@ -10,8 +10,7 @@ constexpr int kEigStride = 44;  // per tree: evals[4] evecs[16] inv_evecs[16] lo
 // Sparse column form of one HMM transition matrix (family constant).
 struct CscDev {
   const int32_t* colptr;  // [cols+1]
-  const int32_t* row;     // [nnz]
-  const double* val;      // [nnz]
+  const double2* ent;     // [nnz] x = value, low word of y = row (one 16-byte load per non-zero)
   int32_t rows, cols;
 };
 
