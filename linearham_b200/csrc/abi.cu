@@ -218,6 +218,7 @@ struct lh_family {
     int n_cols = 0;
     std::vector<uint8_t> codes;  // [T][n_cols] host copy, re-tiled per sites_per_thread
     DevBuf d_codes_t;
+    PinBuf h_codes_t;
     int codes_ns = 0;
   } cols[2];
   const int32_t* d_col_of_site = nullptr;  // [S] pattern index of each xMSA column
@@ -278,6 +279,7 @@ void lh_family_destroy(lh_family_t* f) {
                     &f->d_rate_ll, &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags};
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
+  for (auto& c : f->cols) c.h_codes_t.release();
   f->h_misc.release();
   f->h_const.release();
   f->h_flags.release();
@@ -780,9 +782,16 @@ int configure_batch(lh_family* f, int B, int R) {
           }
         }
       }
+      // The copy is ordered on the compute stream, in front of the kernels that read the table, and is
+      // waited for. (A synchronous cudaMemcpy from pageable memory returns once the data is in the
+      // driver's staging buffer; its DMA runs on the legacy stream, with which these non-blocking streams
+      // do not synchronise - with several handles keeping the copy engine busy, k_prune of a rebound
+      // handle could start on the previous family's codes.)
       LH_CUDA(cudaStreamSynchronize(f->stream));
-      if (cset.d_codes_t.reserve(ct.size() * 4)) return 1;
-      LH_CUDA(cudaMemcpy(cset.d_codes_t.p, ct.data(), ct.size() * 4, cudaMemcpyHostToDevice));
+      if (cset.d_codes_t.reserve(ct.size() * 4) || cset.h_codes_t.reserve(ct.size() * 4)) return 1;
+      stream_copy(cset.h_codes_t.p, ct.data(), ct.size() * 4);
+      LH_CUDA(cudaMemcpyAsync(cset.d_codes_t.p, cset.h_codes_t.p, ct.size() * 4, cudaMemcpyHostToDevice, f->stream));
+      LH_CUDA(cudaStreamSynchronize(f->stream));
       cset.codes_ns = NS;
     }
     pc.codes_t = cset.d_codes_t.as<uint32_t>();

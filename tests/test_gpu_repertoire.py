@@ -114,3 +114,28 @@ def test_a_bad_family_fails_alone():
     lls, st = rep.score([])
     assert lls == [] and st["n_families"] == 0
     rep.close()
+
+
+def test_many_slots_stress_is_bit_identical_to_fresh_handles():
+    """Six slots rebinding 48 families twice over, the copy engine kept busy by all of them: every family must
+    come out as from a fresh handle. (Regression: the re-tiled tip codes of a rebound handle once went up with a
+    synchronous cudaMemcpy from pageable memory, whose DMA is not ordered with the handle's non-blocking
+    streams - under load k_prune could start on the previous family's codes.)"""
+    cfg = workload.CONFIGS["c5"]
+    with tempfile.TemporaryDirectory() as d:
+        fams = workload.repertoire(cfg, d, 48, B=400, n_topo=8)
+    pairs = [(f["fam"], f["tb"]) for f in fams]
+    want = []
+    for fam, tb in pairs:
+        h = device.Family(fam)
+        want.append(h.score(tb))
+        h.close()
+    rep = device.Repertoire(n_slots=6)
+    for _ in range(2):
+        got, st = rep.score(pairs)
+        assert st["n_failed"] == 0
+        for i, (a, b) in enumerate(zip(got, want)):
+            assert _same(a, b), (i, fams[i]["n_leaves"])
+    rep.close()
+    port, _ = po.port_score_batch(pairs[0][0], {k: v[:8] for k, v in pairs[0][1].items()}, want_outputs=False)
+    assert rel_err(want[0][:8], port) <= TOL
