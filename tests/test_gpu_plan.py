@@ -128,3 +128,35 @@ def test_large_family_3000_leaves_matches_the_port():
         assert rel_err(out["xmsa_emission"], pout["xmsa_emission"]) <= 1e-9
         for k in ("germ_scalers", "vd_scalers", "dj_scalers"):
             assert np.array_equal(out[k], pout[k]), k
+
+
+def test_schedule_options_do_not_change_results():
+    """Opening unit chunk, growing chunks and either planner: a multi-chunk pipelined call gives the doubles of
+    the resident batch."""
+    from linearham_b200 import host
+    cfg = dict(workload.CONFIGS["c3"])
+    with tempfile.TemporaryDirectory() as d:
+        ff = workload.write_family_files(cfg, d)
+        ph = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+        fam = ph.family()
+        ph.close()
+        tb, _, _ = workload.tree_batch(cfg, ff, 6000, n_topo=64)
+    f = device.Family(fam)
+    f.upload(tb)
+    f.run()
+    want = f.fetch()
+    f.close()
+    assert np.isfinite(want).mean() > 0.9
+    seen = set()
+    for open_unit in (0, 1):
+        for growth in (0, 1):
+            for dp in (0, 1):
+                f = device.Family(fam)
+                f.set_option("open_unit", open_unit)
+                f.set_option("chunk_growth", growth)
+                f.set_option("device_plan", dp)
+                got = f.score(tb)
+                seen.add(f.timings()["kernel_launches"])
+                f.close()
+                assert np.array_equal(got, want, equal_nan=True), (open_unit, growth, dp)
+    assert len(seen) > 1   # the options did change the schedule
