@@ -141,10 +141,6 @@ typedef struct lh_timings {
   int32_t pattern_trees;     /* trees of the batch pruned on site patterns               */
   float ms_call;             /* wall clock of the last lh_score_batch call               */
   float ms_setup;            /* of which validation + buffer set-up before the pipeline  */
-  float ms_repeats;          /* sum over k_repeats launches                              */
-  int32_t site_repeats;      /* 1 when the pattern trees ran on site-repeat classes      */
-  int32_t sr_arena;          /* shared-memory CLV arena entries per warp (k_prune_sr)    */
-  int32_t sr_ctas_per_sm;
   float ms_plan_dev;         // sum over k_plan launches (device traversal planning)             
   int32_t device_plan;       // 1 when the batch was planned by k_plan                           
 } lh_timings_t;
@@ -195,9 +191,8 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never
  * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "pipe_waves" (default 4:
  * lh_score_batch launches a chunk's kernels every that many waves of CTAs), "stream" (a
- * caller-owned cudaStream_t cast to int64; 0 = private stream), "site_repeats" (0/1: prune the
- * pattern trees on per-node site-repeat classes, k_repeats + k_prune_sr), "sr_arena" (0 = auto:
- * shared-memory CLV entries per warp of k_prune_sr), "site_patterns" (1 =
+ * caller-owned cudaStream_t cast to int64 - 0 is the legacy default stream, i.e. torch's default
+ * stream - on which the kernels and lh_loglik_dev's buffer are then ordered; -1 = back to a private stream), "site_patterns" (1 =
  * default: trees that have the naive tip on the root edge or under the virtual root are
  * pruned on the distinct site patterns of xMSA rows 1.., and k_edge applies the naive row's
  * factor per xMSA column; other trees, and every tree when 0, are pruned on all S_x

@@ -66,8 +66,7 @@ class Timings(C.Structure):
         ("prune_slots", C.c_int32), ("prune_smem_slots", C.c_int32), ("prune_smem_lo", C.c_int32), ("prune_tile_sites", C.c_int32),
         ("prune_sites_per_thread", C.c_int32), ("prune_grid", C.c_int32), ("prune_ctas_per_sm", C.c_int32),
         ("prune_columns", C.c_int32), ("pattern_trees", C.c_int32),
-        ("ms_call", C.c_float), ("ms_setup", C.c_float), ("ms_repeats", C.c_float),
-        ("site_repeats", C.c_int32), ("sr_arena", C.c_int32), ("sr_ctas_per_sm", C.c_int32),
+        ("ms_call", C.c_float), ("ms_setup", C.c_float),
         ("ms_plan_dev", C.c_float), ("device_plan", C.c_int32),
     ]
 

@@ -208,7 +208,7 @@ struct lh_family {
   bool run_recorded = false;   // the kernels of the current batch have been queued (their chunk events exist)
   cudaEvent_t ev[8] = {};
   cudaEvent_t user_ev[8] = {};
-  std::vector<cudaEvent_t> chunk_ev;  // kChunkEvents per chunk: start, pmatrix | repeats | prune | edge ends (compute stream); hmm start, hmm end (its stream)
+  std::vector<cudaEvent_t> chunk_ev;  // kChunkEvents per chunk: start, pmatrix | (unused) | prune | edge ends (compute stream); hmm start, hmm end (its stream)
   std::vector<cudaEvent_t> staged_ev;  // per chunk: its last segment has landed in HBM
   int n_chunks = 0;
   bool own_stream = true;
@@ -224,13 +224,6 @@ struct lh_family {
   const int32_t* d_col_of_site = nullptr;  // [S] pattern index of each xMSA column
   DevBuf d_ebuf, d_ecnt, d_enaive;
   int opt_site_patterns = 1;
-  // site repeats (k_repeats + k_prune_sr) for the trees that run on site patterns
-  int opt_site_repeats = 0, opt_sr_arena = 0;
-  bool use_sr = false;
-  const uint8_t* d_pat_codes = nullptr;  // [T][U rounded up to 32] pattern codes, row-major
-  DevBuf d_rs_steps, d_rs_idx, d_rs_ecls, d_rs_peak, d_rs_gclv, d_rs_gcnt;
-  lhb::RepeatCfg rc{};
-  int sr_occ = 0;
   // launch configuration of the current batch (configure_batch)
   lhb::BatchDev bd{};
   lhb::PruneCfg pc[2] = {};  // per column set
@@ -268,14 +261,13 @@ int lh_device_count(int* n) {
 void lh_family_destroy(lh_family_t* f) {
   if (!f) return;
   cudaSetDevice(f->device);
-  if (f->stream) cudaStreamSynchronize(f->stream);
+  cudaStreamSynchronize(f->stream);  // (a null handle is the legacy default stream)
   if (f->copy_stream) cudaStreamSynchronize(f->copy_stream);
   if (f->hmm_stream) cudaStreamSynchronize(f->hmm_stream);
   DevBuf* bufs[] = {&f->d_const, &f->d_plan, &f->d_pblen, &f->d_er, &f->d_pi, &f->d_rates, &f->d_eig, &f->d_prec,
                     &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
                     &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
-                    &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_rs_steps,
-                    &f->d_rs_idx, &f->d_rs_ecls, &f->d_rs_peak, &f->d_rs_gclv, &f->d_rs_gcnt, &f->d_counters,
+                    &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_counters,
                     &f->d_rate_ll, &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags};
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
@@ -328,7 +320,6 @@ static int bind_family(lh_family* f, const lh_family_desc_t* d) {
   f->B = 0;
   f->n_chunks = 0;
   f->window_set = false;
-  f->use_sr = false;
   for (auto& c : f->cols) c.codes_ns = 0;
   auto bail = [&](int) { return 1; };
   const int T = d->n_tips, S = d->n_sites;
@@ -395,13 +386,6 @@ static int bind_family(lh_family* f, const lh_family_desc_t* d) {
     for (int r = 1; r < T; ++r)
       for (int u = 0; u < U; ++u) f->cols[1].codes[(size_t)r * U + u] = d->tip_codes[(size_t)r * S + rep[u]];
     rc |= upload(col_of_site.data(), (size_t)S, &f->d_col_of_site, own);
-    {
-      // row-major copy for k_repeats, rows padded to a multiple of 32 bytes (cp.async chunks)
-      const int up = (U + 31) / 32 * 32;
-      std::vector<uint8_t> padded((size_t)T * up, 4);
-      for (int r = 0; r < T; ++r) std::memcpy(&padded[(size_t)r * up], &f->cols[1].codes[(size_t)r * U], (size_t)U);
-      rc |= upload(padded.data(), padded.size(), &f->d_pat_codes, own);
-    }
   }
   auto region = [&](int n, const int32_t* off, const int32_t* inds, const int32_t** doff,
                     const int32_t** dinds, const char* name) {
@@ -489,6 +473,7 @@ static int bind_family(lh_family* f, const lh_family_desc_t* d) {
 
 
 int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
+  if (!out) return fail("null argument");
   *out = nullptr;
   if (check_desc(d)) return 1;
   int ndev = 0;
@@ -540,11 +525,6 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_smem_slots = (int)value;
   } else if (k == "smem_lo") {
     f->opt_smem_lo = (int)value;
-  } else if (k == "site_repeats") {
-    f->opt_site_repeats = value != 0;
-  } else if (k == "sr_arena") {
-    if (value < 0 || value > 4096) return fail("sr_arena must be 0 (auto) or a shared-memory entry count up to 4096");
-    f->opt_sr_arena = (int)value;
   } else if (k == "site_patterns") {
     f->opt_site_patterns = value != 0;
   } else if (k == "chunk_growth") {
@@ -570,12 +550,13 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
   } else if (k == "chunk_bytes") {
     f->opt_chunk_bytes = (size_t)value;
   } else if (k == "stream") {
-    // run on a caller-owned CUDA stream (e.g. torch.cuda.current_stream().cuda_stream); 0 restores
-    // a private stream
+    // run on a caller-owned CUDA stream (e.g. torch.cuda.current_stream().cuda_stream); the value is the
+    // cudaStream_t itself, so 0 is the legacy default stream (what torch's default stream is) and the
+    // kernels are then ordered with everything the caller queues there; -1 restores a private stream
     cudaSetDevice(f->device);
-    if (f->stream) cudaStreamSynchronize(f->stream);
+    cudaStreamSynchronize(f->stream);
     if (f->stream && f->own_stream) cudaStreamDestroy(f->stream);
-    if (value == 0) {
+    if (value == -1) {
       f->own_stream = true;
       if (cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking) != cudaSuccess) return fail("cudaStreamCreate failed");
     } else {
@@ -871,59 +852,6 @@ int configure_batch(lh_family* f, int B, int R) {
     ec.rate_ll = f->d_rate_ll.as<double>();
   }
 
-  // site repeats for the trees on patterns
-  f->use_sr = false;
-  if (f->opt_site_repeats && use[1]) {
-    const int U = f->cols[1].n_cols, up = (U + 31) / 32 * 32, n_bufs = f->pc[1].total_slots + 1;
-    if (U <= lhb::kRepeatMaxCols && (size_t)n_bufs * up <= 16384 && T - 1 < 65536) {
-      lhb::RepeatCfg& r = f->rc;
-      r = lhb::RepeatCfg{};
-      r.n_cols = U;
-      r.cols_pad = f->pc[1].cols_pad;
-      r.codes = f->d_pat_codes;
-      r.idx_cap = ((int64_t)(T - 1) * U + 127) / 128 * 128;
-      r.idx_ring = lhb::prune_sr_idx_ring(U);
-      r.n_bufs = n_bufs;
-      r.defer_naive = 1;
-      // shared-memory arena: small by default. Measured on B200 (C4): the kernel is bound by the
-      // latency of its dependent steps, so CTAs per SM matter more than keeping CLV entries out of
-      // L2 (64 entries, 16 CTAs/SM: 49 ms; 512 entries, 7 CTAs/SM: 72 ms; 1280 entries, 4: 99 ms)
-      int cap = f->opt_sr_arena;
-      if (cap <= 0) cap = 64;
-      cap = std::min(cap, n_bufs * up);
-      cap -= cap % 32;
-      r.arena_smem = std::max(cap, 64);
-      const int g_half = n_bufs * up;
-      r.arena_total = r.arena_smem + 2 * g_half;
-      f->sr_occ = lhb::prune_sr_max_ctas_per_sm(r.arena_smem, r.idx_ring);
-      if (f->sr_occ < 1) return fail("site-repeat kernel cannot be resident with %d arena entries", r.arena_smem);
-      r.grid = f->sr_occ * f->num_sms;
-      // the class lists are sized for the worst case (every pattern its own class at every node)
-      const size_t idx_bytes_tree = (size_t)r.idx_cap * sizeof(ushort2);
-      const int sr_chunk_max = (int)std::max<size_t>(1, ((size_t)8 << 30) / idx_bytes_tree);
-      if (f->chunk > sr_chunk_max) {
-        f->chunk = sr_chunk_max;
-        f->chunk_pipe = std::min(f->chunk_pipe, f->chunk);
-      }
-      if (f->d_rs_steps.reserve((size_t)f->chunk * (T - 1) * sizeof(int4)) ||
-          f->d_rs_idx.reserve((size_t)f->chunk * idx_bytes_tree + (size_t)r.idx_ring * sizeof(ushort2)) ||  // ring read-ahead
-          
-          f->d_rs_ecls.reserve((size_t)f->chunk * r.cols_pad * sizeof(uint16_t)) ||
-          f->d_rs_peak.reserve((size_t)f->chunk * sizeof(int32_t)) ||
-          f->d_rs_gclv.reserve((size_t)r.grid * 4 * 2 * g_half * sizeof(double)) ||
-          f->d_rs_gcnt.reserve((size_t)r.grid * 2 * g_half * sizeof(int32_t)))
-        return 1;
-      r.steps = f->d_rs_steps.as<int4>();
-      r.idx = f->d_rs_idx.as<ushort2>();
-      r.ecls = f->d_rs_ecls.as<uint16_t>();
-      r.peak = f->d_rs_peak.as<int32_t>();
-      r.g_clv = f->d_rs_gclv.as<double>();
-      r.g_cnt = f->d_rs_gcnt.as<int32_t>();
-      ec.ecls = r.ecls;
-      f->use_sr = true;
-    }
-  }
-
   // staging segments: up to ~48 MB of plan + branch lengths per ring slot, never more than a
   // pipelined chunk
   const size_t stage_bytes_tree = (size_t)(T - 1) * sizeof(lhb::Step) + (size_t)NB * sizeof(double);
@@ -962,9 +890,6 @@ int configure_batch(lh_family* f, int B, int R) {
   f->tm.prune_columns = pm.n_cols;
   f->tm.pattern_trees = f->n_pattern_trees;
   f->tm.device_plan = f->dev_plan ? 1 : 0;
-  f->tm.site_repeats = f->use_sr ? 1 : 0;
-  f->tm.sr_arena = f->use_sr ? f->rc.arena_smem : 0;
-  f->tm.sr_ctas_per_sm = f->use_sr ? f->sr_occ : 0;
   return 0;
 }
 
@@ -1137,27 +1062,14 @@ void launch_chunk(lh_family* f, int ci, int t0, int n) {
   const int n_pat = f->chunk_n_pat[ci];
   const int count[2] = {n - n_pat, n_pat};
   const int32_t* list[2] = {f->d_list.as<int32_t>() + t0 + n_pat, f->d_list.as<int32_t>() + t0};
-  const bool sr = f->use_sr && count[1] > 0;
-  if (sr) {
-    lhb::RepeatCfg r = f->rc;
-    r.tree_list = list[1];
-    lhb::launch_repeats(f->fd, f->bd, r, t0, count[1], s);
-    f->tm.kernel_launches += 1;
-  }
   if (tm) cudaEventRecord(ev[2], s);
   for (int g = 1; g >= 0; --g) {
     if (!count[g]) continue;
     lhb::PruneCfg c = f->pc[g];
     c.tree_list = list[g];
     c.work_counter = f->d_counters.as<int32_t>() + g;
-    if (g == 1 && sr) {
-      lhb::RepeatCfg r = f->rc;
-      r.tree_list = list[1];
-      lhb::launch_prune_sr(f->fd, f->bd, c, r, t0, count[1], s);
-    } else {
-      c.grid = (int)std::min<int64_t>(c.grid, (int64_t)count[g] * c.n_tiles * f->R);
-      lhb::launch_prune(f->fd, f->bd, c, t0, count[g], s);
-    }
+    c.grid = (int)std::min<int64_t>(c.grid, (int64_t)count[g] * c.n_tiles * f->R);
+    lhb::launch_prune(f->fd, f->bd, c, t0, count[g], s);
     f->tm.kernel_launches += 1;
     f->tm.prune_launches += 1;
   }
@@ -1306,7 +1218,6 @@ static int collect_run_timings(lh_family* f) {
     }
   f->tm.ms_plan_dev = sum[5];
   f->tm.ms_pmatrix = sum[0];
-  f->tm.ms_repeats = sum[1];
   f->tm.ms_prune = sum[2];
   f->tm.ms_edge = sum[3];
   f->tm.ms_hmm = sum[4];

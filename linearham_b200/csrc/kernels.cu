@@ -241,7 +241,6 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 #define LH_PRUNE_MIN_CTAS1 24
 #endif
 
-constexpr int kRecRing = 4;    // k_prune_sr: steps of branch records in flight
 constexpr int kBlk = 4;        // k_prune: steps per staged block of branch records (two blocks resident)
 constexpr int kPlanRing = 64;  // plan entries resident
 constexpr int kRecDoubles = 20;
@@ -695,417 +694,6 @@ int prune_max_ctas_per_sm(int ns, int smem_slots) {
   return n;
 }
 
-// ---------------------------------------------------------------- k_repeats ---
-// One warp per tree; topology only (no likelihood arithmetic). Walks the tree's program and
-// numbers, at every step, the classes of patterns whose two children agree: class of pattern u
-// at node v = dense id of the pair (class of u at child a, class of u at child b), a tip's
-// "class" being its code. Ids follow the first pattern of each class, so the numbering is
-// deterministic. Also lays out the CLV arena. Results must not overwrite the children they are
-// computed from, so nodes of even depth stack up from the bottom of the arena and nodes of odd
-// depth down from its top (a node's inner children are one level deeper, hence at the other end;
-// at each end the children of a step are the top-most live allocations). An allocation that would
-// make the two ends meet goes to the global part of its end instead. Arena addresses are 16 bits:
-// bit 15 = global part, else the shared-memory entry index.
-__device__ __forceinline__ unsigned repeat_hash(unsigned key) { return (key * 2654435761u) >> 21; }
-
-size_t repeats_smem_bytes(int n_cols, int n_bufs) {
-  const size_t up = ((size_t)n_cols + 31) / 32 * 32;
-  return (size_t)kRepeatTable * 8 + up * (4 + 2 + 2) + 4 * up + (size_t)n_bufs * up * 2 + (size_t)n_bufs * 8;
-}
-
-__global__ void __launch_bounds__(32) k_repeats(FamilyDev f, BatchDev b, RepeatCfg cfg, int tree0, int nlist) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int lane = threadIdx.x, T = f.T, U = cfg.n_cols, n_steps = T - 2, n_iter = T - 1;
-  const int up = (U + 31) / 32 * 32;
-  unsigned* tkey = reinterpret_cast<unsigned*>(smem_raw);          // [kRepeatTable]
-  unsigned* tmin = tkey + kRepeatTable;                            // [kRepeatTable]
-  unsigned* skey = tmin + kRepeatTable;                            // [up]
-  unsigned short* sslot = reinterpret_cast<unsigned short*>(skey + up);  // [up]
-  unsigned short* rid = sslot + up;                                // [up]
-  unsigned char* tipbuf = reinterpret_cast<unsigned char*>(rid + up);    // [2 steps][2 children][up] codes
-  unsigned short* cls = reinterpret_cast<unsigned short*>(tipbuf + 4 * up);  // [n_bufs][up]
-  int* boff = reinterpret_cast<int*>(cls + (size_t)cfg.n_bufs * up);     // [n_bufs] arena offset per buffer
-  int* bcnt = boff + cfg.n_bufs;                                   // [n_bufs] classes per buffer
-  const int reg_buf = cfg.n_bufs - 1;
-  const unsigned lt_mask = (1u << lane) - 1u;
-  constexpr unsigned kEmpty = 0xffffffffu;
-  const unsigned tipbuf_s = (unsigned)__cvta_generic_to_shared(tipbuf);
-
-  for (int i = lane; i < kRepeatTable; i += 32) { tkey[i] = kEmpty; tmin[i] = kEmpty; }
-  __syncwarp();
-
-  for (int li = blockIdx.x; li < nlist; li += gridDim.x) {
-    const int t = __ldg(cfg.tree_list + li), lt = t - tree0;
-    const int4* __restrict__ plan = b.plan + (size_t)t * (T - 1);
-    int4* steps_out = cfg.steps + (size_t)lt * (T - 1);
-    ushort2* idx_out = cfg.idx + (size_t)lt * cfg.idx_cap;
-    int stream = 0, peak = 0;
-    int stop[2] = {0, 0}, gtop[2] = {0, 0};  // entries in use at each end: shared / global part
-    // tip rows (up bytes, 16-byte chunks) of a step's children, staged one step ahead
-    auto stage_tips = [&](const int4& q, int slot) {
-      for (int c = lane; c < up / 16; c += 32) {
-        if (q.x >= 0) cp_async16(tipbuf_s + (slot * 2 + 0) * up + c * 16, cfg.codes + (size_t)q.x * up + c * 16);
-        if (q.y >= 0) cp_async16(tipbuf_s + (slot * 2 + 1) * up + c * 16, cfg.codes + (size_t)q.y * up + c * 16);
-      }
-    };
-    int4 st = __ldg(plan);
-    __syncwarp();
-    stage_tips(st, 0);
-    cp_async_commit();
-    for (int s = 0; s < n_iter; ++s) {
-      const int4 st_next = (s + 1 < n_iter) ? __ldg(plan + s + 1) : st;
-      const bool a_tip = st.x >= 0, b_tip = st.y >= 0;
-      const int buf_a = a_tip ? -1 : (st.x == -1 ? reg_buf : -2 - st.x);
-      const int buf_b = b_tip ? -1 : (st.y == -1 ? reg_buf : -2 - st.y);
-      const int buf_o = (s < n_steps && st.z >= 0) ? st.z : reg_buf;
-      const unsigned char* code_a = tipbuf + ((s & 1) * 2 + 0) * up;
-      const unsigned char* code_b = tipbuf + ((s & 1) * 2 + 1) * up;
-      const unsigned short* cls_a = cls + (size_t)(a_tip ? 0 : buf_a) * up;
-      const unsigned short* cls_b = cls + (size_t)(b_tip ? 0 : buf_b) * up;
-      __syncwarp();  // lane 0's bookkeeping of the previous step and the table reset are visible
-      if (s + 1 < n_iter) stage_tips(st_next, (s + 1) & 1);
-      cp_async_commit();
-      cp_async_wait<1>();  // this step's tip rows have landed
-      const int a_off = a_tip ? 0 : boff[buf_a], b_off = b_tip ? 0 : boff[buf_b];
-      const int a_cnt = a_tip ? 5 : bcnt[buf_a], b_cnt = b_tip ? 5 : bcnt[buf_b];
-      __syncwarp();
-      // A. one table slot per distinct pair of child classes; the smallest pattern index of a pair
-      // represents it. Small products index the table directly, large ones hash into it.
-      const bool direct = a_cnt * b_cnt <= kRepeatTable;
-      for (int u = lane; u < U; u += 32) {
-        const unsigned ca = a_tip ? (unsigned)code_a[u] : (unsigned)cls_a[u];
-        const unsigned cb = b_tip ? (unsigned)code_b[u] : (unsigned)cls_b[u];
-        const unsigned key = ca | (cb << 16);
-        unsigned h;
-        if (direct) {
-          h = ca * b_cnt + cb;
-        } else {
-          h = repeat_hash(key);
-          for (;;) {
-            const unsigned prev = atomicCAS(tkey + h, kEmpty, key);
-            if (prev == kEmpty || prev == key) break;
-            h = (h + 1) & (kRepeatTable - 1);
-          }
-        }
-        atomicMin(tmin + h, (unsigned)u);
-        skey[u] = key;
-        sslot[u] = (unsigned short)h;
-      }
-      __syncwarp();
-      // B. number the representatives in pattern order; emit their child classes
-      int n = 0;
-      for (int u0 = 0; u0 < U; u0 += 32) {
-        const int u = u0 + lane;
-        const bool rep = u < U && tmin[sslot[u < U ? u : 0]] == (unsigned)u;
-        const unsigned votes = __ballot_sync(0xffffffffu, rep);
-        if (rep) {
-          const int r = n + __popc(votes & lt_mask);
-          rid[u] = (unsigned short)r;
-          const unsigned key = skey[u];
-          idx_out[stream + r] = make_ushort2((unsigned short)(key & 0xffffu), (unsigned short)(key >> 16));
-        }
-        n += __popc(votes);
-      }
-      __syncwarp();
-      // C. class of every pattern at this node
-      unsigned short* out = (s < n_steps) ? cls + (size_t)buf_o * up : cfg.ecls + (size_t)lt * cfg.cols_pad;
-      for (int u = lane; u < U; u += 32) out[u] = rid[tmin[sslot[u]]];
-      __syncwarp();
-      for (int u = lane; u < U; u += 32) {
-        const int h = sslot[u];
-        tkey[h] = kEmpty;
-        tmin[h] = kEmpty;
-      }
-      // arena: place the result at its own end, then free the children (top-most at their end)
-      const int g_half = (cfg.arena_total - cfg.arena_smem) / 2;
-      // (inner children of a node step are one level deeper than the node; both sides of the
-      // edge step are at depth 0)
-      const int child_par = (s < n_steps) ? 1 - (st.w & 1) : 0;
-      auto release = [&](int off, int cnt) {
-        if (off & 0x8000) {
-          gtop[child_par] = min(gtop[child_par], (off & 0x7fff) - child_par * g_half);
-        } else if (child_par == 0) {          // bottom end
-          stop[0] = min(stop[0], off);
-        } else {                              // top end: the node starts at arena_smem - (in use)
-          stop[1] = min(stop[1], cfg.arena_smem - off - cnt);
-        }
-      };
-      // place the result while the children still count as live: they are read during the step
-      int out_off = 0;
-      if (s < n_steps) {
-        const int p = st.w & 1;
-        if (stop[0] + stop[1] + n <= cfg.arena_smem) {
-          out_off = p ? cfg.arena_smem - stop[1] - n : stop[0];
-          stop[p] += n;
-        } else {
-          out_off = 0x8000 | (p * g_half + gtop[p]);
-          gtop[p] += n;
-        }
-        peak = max(peak, stop[0] + stop[1] + gtop[0] + gtop[1]);
-      }
-      if (!a_tip) release(a_off, a_cnt);
-      if (!b_tip) release(b_off, b_cnt);
-      if (lane == 0) {
-        const int a_def = cfg.defer_naive && a_tip && st.x == 0, b_def = cfg.defer_naive && b_tip && st.y == 0;
-        const int flags = (a_tip ? 1 : 0) | (b_tip ? 2 : 0) | (a_def ? 4 : 0) | (b_def ? 8 : 0);
-        steps_out[s] = make_int4(stream, n, a_off | (b_off << 16), out_off | (flags << 16));
-        if (s < n_steps) {
-          boff[buf_o] = out_off;
-          bcnt[buf_o] = n;
-        }
-      }
-      stream += n;
-      st = st_next;
-    }
-    if (lane == 0) cfg.peak[lt] = peak;
-    __syncwarp();
-  }
-}
-
-void launch_repeats(const FamilyDev& f, const BatchDev& b, const RepeatCfg& r, int tree0, int nlist,
-                    cudaStream_t s) {
-  const size_t smem = repeats_smem_bytes(r.n_cols, r.n_bufs);
-  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_repeats), smem);
-  int occ = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_repeats, 32, smem);
-  int grid = std::max(1, occ) * 148;
-  if (grid > nlist) grid = nlist;
-  k_repeats<<<grid, 32, smem, s>>>(f, b, r, tree0, nlist);
-}
-
-// -------------------------------------------------------------- k_prune_sr ---
-// One warp per (tree, rate category); walks the tree's program over the site-repeat classes
-// k_repeats numbered: lane l computes the CLV entries of classes l, l+32, ... of a step from the
-// entries of its children (gathered through the class list) and stores them in the warp's arena.
-// Same arithmetic per entry as k_prune per column, so the emissions are the same doubles.
-// Staging as in k_prune: step ring 64 entries (cp.async, 32 at a time), record ring 4 steps.
-struct Arena {
-  double* s_clv;   // [4][smem_cap]
-  int* s_cnt;      // [smem_cap]
-  double* g_clv;   // [4][g_cap]
-  int* g_cnt;      // [g_cap]
-  int smem_cap, g_cap;
-  // e: arena address from k_repeats (bit 15 = global part)
-  __device__ __forceinline__ void load(int e, double (&c)[4], int& cnt) const {
-    if (!(e & 0x8000)) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) c[i] = s_clv[i * smem_cap + e];
-      cnt = s_cnt[e];
-    } else {
-      e &= 0x7fff;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) c[i] = g_clv[(size_t)i * g_cap + e];
-      cnt = g_cnt[e];
-    }
-  }
-  __device__ __forceinline__ void store(int e, const double (&c)[4], int cnt) const {
-    if (!(e & 0x8000)) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) s_clv[i * smem_cap + e] = c[i];
-      s_cnt[e] = cnt;
-    } else {
-      e &= 0x7fff;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) g_clv[(size_t)i * g_cap + e] = c[i];
-      g_cnt[e] = cnt;
-    }
-  }
-};
-
-// class-list ring: the lists of four consecutive steps (<= 4 * n_cols entries) plus one 128-entry
-// copy unit must fit: a list is issued two steps before it is read, and the copy may only overwrite
-// lists every lane is done with (those of two steps back)
-int prune_sr_idx_ring(int n_cols) { return 4 * n_cols + 128 <= 2048 ? 2048 : 4096; }
-
-size_t prune_sr_smem_bytes(int arena_smem, int idx_ring) {
-  return (size_t)kRecRing * kStepBytes + kPlanRing * sizeof(int4) + (size_t)idx_ring * sizeof(ushort2) +
-         (size_t)arena_smem * (4 * sizeof(double) + sizeof(int));
-}
-
-// message of one child for one class: tip -> column `ci` of the staged Q block; inner -> P * entry
-// (P is read from the staged record here, per class group, rather than held across the groups of a
-// step: two resident matrices cost 64 registers and four CTAs per SM)
-__device__ __forceinline__ void sr_message(bool tip, const double* rec, const Arena& ar, int off, unsigned ci,
-                                           double (&m)[4], int& cnt) {
-  if (tip) {
-    const double2 q01 = *reinterpret_cast<const double2*>(rec + ci * 4);
-    const double2 q23 = *reinterpret_cast<const double2*>(rec + ci * 4 + 2);
-    m[0] = q01.x; m[1] = q01.y; m[2] = q23.x; m[3] = q23.y;
-    cnt = 0;
-  } else {
-    double c[4];
-    ar.load(off + (int)ci, c, cnt);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const double2 p01 = *reinterpret_cast<const double2*>(rec + 4 * i);
-      const double2 p23 = *reinterpret_cast<const double2*>(rec + 4 * i + 2);
-      double acc = p01.x * c[0];
-      acc += p01.y * c[1];
-      acc += p23.x * c[2];
-      acc += p23.y * c[3];
-      m[i] = acc;
-    }
-  }
-}
-
-#ifndef LH_SR_MIN_CTAS
-#define LH_SR_MIN_CTAS 16
-#endif
-__global__ void __launch_bounds__(32, LH_SR_MIN_CTAS) k_prune_sr(FamilyDev f, BatchDev b, PruneCfg cfg, RepeatCfg rc, int tree0, int nlist) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int lane = threadIdx.x, T = f.T, R = b.R;
-  const int NB = 2 * T - 3, n_steps = T - 2, n_iter = T - 1;
-  double* ring_rec = reinterpret_cast<double*>(smem_raw);                       // [kRecRing][2][20]
-  int4* ring_step = reinterpret_cast<int4*>(smem_raw + kRecRing * kStepBytes);  // [kPlanRing]
-  ushort2* ring_idx = reinterpret_cast<ushort2*>(ring_step + kPlanRing);       // [rc.idx_ring]
-  const int ring_mask = rc.idx_ring - 1;
-  Arena ar;
-  ar.smem_cap = rc.arena_smem;
-  ar.g_cap = rc.arena_total - rc.arena_smem;
-  ar.s_clv = reinterpret_cast<double*>(ring_idx + rc.idx_ring);
-  ar.s_cnt = reinterpret_cast<int*>(ar.s_clv + (size_t)4 * ar.smem_cap);
-  ar.g_clv = rc.g_clv + (size_t)blockIdx.x * 4 * ar.g_cap;
-  ar.g_cnt = rc.g_cnt + (size_t)blockIdx.x * ar.g_cap;
-  const bool rec_lane = lane < kStepBytes / 16;
-  const unsigned ring_rec_s = (unsigned)__cvta_generic_to_shared(ring_rec) + lane * 16;
-  const unsigned ring_step_s = (unsigned)__cvta_generic_to_shared(ring_step);
-  const unsigned ring_idx_s = (unsigned)__cvta_generic_to_shared(ring_idx);
-  const size_t pass_bytes = (size_t)records_per_pass(T) * kRecDoubles * 8;  // (the closing identity record is staged, never read)
-
-  const int n_work = nlist * R;
-  for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
-    const int li = w / R, k = w - li * R;
-    const int t = __ldg(rc.tree_list + li), lt = t - tree0;
-    const int4* __restrict__ steps = rc.steps + (size_t)lt * (T - 1);
-    const ushort2* __restrict__ idx = rc.idx + (size_t)lt * rc.idx_cap;
-    const char* rec_src = reinterpret_cast<const char*>(b.prec) + ((size_t)lt * R + k) * pass_bytes + lane * 16;
-    auto stage_steps = [&](int q0) {
-      const int q = q0 + lane;
-      if (q < n_iter) cp_async16(ring_step_s + (q & (kPlanRing - 1)) * 16, steps + q);
-    };
-    auto stage_records = [&](int q) {
-      if (rec_lane && (size_t)q * kStepBytes + lane * 16 < pass_bytes)
-        cp_async16(ring_rec_s + (q & (kRecRing - 1)) * kStepBytes, rec_src + (size_t)q * kStepBytes);
-    };
-    // the class lists of the tree are one contiguous stream; copy units of 128 entries (all 32
-    // lanes x 16 bytes) keep the ring filled up to idx_ring entries past the list being read
-    int staged = 0;
-    auto stage_idx = [&](int upto) {
-      while (staged + 128 <= upto) {
-        cp_async16(ring_idx_s + ((staged + lane * 4) & ring_mask) * 4, idx + staged + lane * 4);
-        staged += 128;
-      }
-    };
-    __syncwarp();
-    stage_steps(0);
-    stage_steps(32);
-    stage_records(0);
-    stage_idx(rc.idx_ring);
-    cp_async_commit();
-    stage_records(1);
-    cp_async_commit();
-    cp_async_wait<1>();
-    __syncwarp();
-
-    int naive_br = -1;
-    int4 rs_next = ring_step[0];
-    int dead_before = 0;  // first entry of the previous step's list: everything before it is dead
-
-    for (int s = 0; s < n_iter; ++s) {
-      if ((s & 31) == 0 && s > 0) {
-        __syncwarp();
-        stage_steps(s + 32);
-      }
-      stage_records(s + 2);
-      stage_idx(dead_before + rc.idx_ring);
-      dead_before = rs_next.x;
-      cp_async_commit();
-      cp_async_wait<2>();
-      __syncwarp();  // records and class list of step s have landed; the entries step s-1 stored are visible
-      const int4 rs = rs_next;
-      if (s + 1 < n_iter) rs_next = ring_step[(s + 1) & (kPlanRing - 1)];
-      const int n = rs.y, a_off = rs.z & 0xffff, b_off = (unsigned)rs.z >> 16, out_off = rs.w & 0xffff;
-      const int flags = rs.w >> 16;
-      const bool a_tip = flags & 1, b_tip = flags & 2, a_def = flags & 4, b_def = flags & 8;
-      const double* recA = ring_rec + (s & (kRecRing - 1)) * (2 * kRecDoubles);
-      const double* recB = recA + kRecDoubles;
-      if (s < n_steps) {
-        if (a_def | b_def) naive_br = 2 * s + (a_def ? 0 : 1);
-        for (int j0 = 0; j0 < n; j0 += 32) {
-          const int j = j0 + lane;
-          if (j < n) {
-            const ushort2 ix = ring_idx[(rs.x + j) & ring_mask];
-            double ma[4], mb[4], r[4];
-            int ca, cb, cnt;
-            sr_message(a_tip, recA, ar, a_off, ix.x, ma, ca);
-            sr_message(b_tip, recB, ar, b_off, ix.y, mb, cb);
-            if (a_def) {         // the naive tip's factor is applied by k_edge
-#pragma unroll
-              for (int i = 0; i < 4; ++i) r[i] = mb[i];
-              cnt = cb;
-            } else if (b_def) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) r[i] = ma[i];
-              cnt = ca;
-            } else {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) r[i] = ma[i] * mb[i];  // core_partials.c:626
-              cnt = ca + cb;
-              const int hi = max(max(__double2hiint(r[0]), __double2hiint(r[1])),
-                                 max(__double2hiint(r[2]), __double2hiint(r[3])));
-              if (hi < kThresholdHi) {  // all four entries below 2^-256 (core_partials.c:648-659)
-#pragma unroll
-                for (int i = 0; i < 4; ++i) r[i] *= LH_SCALE_FACTOR;
-                cnt += 1;
-              }
-            }
-            ar.store(out_off + j, r, cnt);
-          }
-        }
-      } else {
-        // ---- edge step: a = the root CLV, b = the node across the edge (record in position A) ----
-        if (b_def) naive_br = 2 * n_steps;
-        double* eo = cfg.ebuf + (size_t)lt * cfg.e_stride + (size_t)k * 8 * cfg.cols_pad;
-        int* co = cfg.ecnt + (size_t)lt * cfg.c_stride + (size_t)k * cfg.cols_pad;
-        for (int j0 = 0; j0 < n; j0 += 32) {
-          const int j = j0 + lane;
-          if (j < n) {
-            const ushort2 ix = ring_idx[(rs.x + j) & ring_mask];
-            double rg[4], mc[4];
-            int ca, cb;
-            ar.load(a_off + ix.x, rg, ca);
-            sr_message(b_tip, recA, ar, b_off, ix.y, mc, cb);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              eo[(size_t)i * cfg.cols_pad + j] = mc[i];
-              eo[(size_t)(4 + i) * cfg.cols_pad + j] = rg[i];
-            }
-            co[j] = ca + cb;
-          }
-        }
-      }
-    }
-    cp_async_wait<0>();
-    if (k == 0 && lane == 0) cfg.enaive[lt] = naive_br;
-  }
-}
-
-void launch_prune_sr(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, const RepeatCfg& r, int tree0,
-                     int nlist, cudaStream_t s) {
-  const size_t smem = prune_sr_smem_bytes(r.arena_smem, r.idx_ring);
-  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_prune_sr), smem);
-  int grid = std::min(r.grid, nlist * b.R);
-  k_prune_sr<<<grid, 32, smem, s>>>(f, b, c, r, tree0, nlist);
-}
-
-int prune_sr_max_ctas_per_sm(int arena_smem, int idx_ring) {
-  const size_t smem = prune_sr_smem_bytes(arena_smem, idx_ring);
-  int n = 0;
-  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_prune_sr), smem);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_prune_sr, 32, smem);
-  return n;
-}
-
 // ------------------------------------------------------------------- k_edge ---
 // One thread per (tree, xMSA column): the edge log-likelihood of the column from the two CLV
 // messages k_prune left per category (core_likelihood_avx.c:1130-1251), the naive-sequence
@@ -1125,7 +713,6 @@ __global__ void __launch_bounds__(128) k_edge(FamilyDev f, BatchDev b, EdgeCfg c
     const int code = __ldg(f.tip_codes + site);  // xMSA row 0 is the naive sequence
     const int nbr = __ldg(cfg.enaive + lt);
     int col = nbr >= 0 ? __ldg(cfg.col_of_site + site) : site;
-    if (nbr >= 0 && cfg.ecls) col = cfg.ecls[(size_t)lt * cfg.cols_pad_pat + col];  // site-repeat class
     const size_t pitch = nbr >= 0 ? cfg.cols_pad_pat : cfg.cols_pad_all;
     const double* eig = b.eig + (size_t)t * kEigStride;
     const double pi0 = eig[40], pi1 = eig[41], pi2 = eig[42], pi3 = eig[43];

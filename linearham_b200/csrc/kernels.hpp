@@ -84,41 +84,7 @@ struct PruneCfg {
   int64_t e_stride, c_stride;
 };
 
-// Site repeats (k_repeats + k_prune_sr). At a node, patterns that agree on every tip below the
-// node share the node's CLV; k_repeats numbers these classes per node (topology only, once per
-// tree), k_prune_sr then computes one CLV entry per class instead of one per pattern.
-//   steps[lt][s] (s < T-1, the edge evaluation last):
-//     x = offset of the step's class list in idx[lt], y = number of classes,
-//     z = arena offset of child a | child b << 16 (inner children),
-//     w = arena offset of the result | flags << 16 (1: a is a tip, 2: b is a tip,
-//         4: a is the deferred naive tip, 8: b is)
-//   idx[lt][x + j] = for class j: child a's class (or tip code), child b's class (or tip code)
-//   ecls[lt][u]    = class of pattern u at the edge evaluation (k_edge reads ebuf through it)
-// CLV entries live in a per-warp arena with stack discipline: the first `arena_smem` entries in
-// shared memory, the rest in a per-CTA global scratch.
-constexpr int kRepeatMaxCols = 960;   // patterns per family the class tables are sized for
-constexpr int kRepeatTable = 2048;     // hash slots (power of two >= 2 * kRepeatMaxCols)
-struct RepeatCfg {
-  int32_t n_cols, cols_pad;   // U patterns, pitch of ecls / ebuf
-  const uint8_t* codes;       // [T][n_cols rounded up to 32] pattern codes (row 0 reads as N)
-  const int32_t* tree_list;   // trees of this launch
-  int4* steps;                // [chunk][T-1]
-  ushort2* idx;               // [chunk][idx_cap]
-  int64_t idx_cap;            // entries per tree: (T-1) * n_cols rounded up to 128
-  uint16_t* ecls;             // [chunk][cols_pad]
-  int32_t* peak;              // [chunk] peak arena entries of the tree
-  int32_t n_bufs;             // class buffers: CLV slots + the running result
-  int32_t defer_naive;
-  // k_prune_sr
-  int32_t idx_ring;           // class-list ring entries in shared memory (power of two)
-  int32_t arena_smem;         // entries held in shared memory
-  int32_t arena_total;        // entries per CTA in all (shared + global)
-  double* g_clv;              // [grid][4][arena_total - arena_smem]
-  int32_t* g_cnt;             // [grid][arena_total - arena_smem]
-  int32_t grid;
-};
-
-// k_edge reads what the k_prune / k_prune_sr launches of a chunk left behind
+// k_edge reads what the k_prune launches of a chunk left behind
 struct EdgeCfg {
   const double* ebuf;
   const int32_t* ecnt;
@@ -126,7 +92,6 @@ struct EdgeCfg {
   int64_t e_stride, c_stride;
   int32_t cols_pad_all, cols_pad_pat;  // column pitch of trees pruned on all columns / on patterns
   const int32_t* col_of_site;          // [S] pattern index of each xMSA column
-  const uint16_t* ecls;                // site repeats: [chunk][cols_pad_pat] class of each pattern, or null
   double log_threshold;
   double* rate_ll;                     // optional [B][R][S]: per-category log( L_k / pi[naive] )
 };
@@ -163,15 +128,6 @@ void launch_pmatrix(const FamilyDev& f, const BatchDev& b, int tree0, int ntrees
 // records and edge buffers are chunk-relative)
 void launch_prune(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, int tree0, int nlist,
                   cudaStream_t s);
-void launch_repeats(const FamilyDev& f, const BatchDev& b, const RepeatCfg& r, int tree0, int nlist,
-                    cudaStream_t s);
-// prunes the trees r.tree_list names over their site-repeat classes (all R categories)
-void launch_prune_sr(const FamilyDev& f, const BatchDev& b, const PruneCfg& c, const RepeatCfg& r, int tree0,
-                     int nlist, cudaStream_t s);
-size_t repeats_smem_bytes(int n_cols, int n_bufs);
-int prune_sr_idx_ring(int n_cols);
-size_t prune_sr_smem_bytes(int arena_smem, int idx_ring);
-int prune_sr_max_ctas_per_sm(int arena_smem, int idx_ring);
 void launch_edge(const FamilyDev& f, const BatchDev& b, const EdgeCfg& c, int tree0, int ntrees,
                  cudaStream_t s);
 void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, int tree0, int ntrees,

@@ -19,7 +19,7 @@ int plan_tree(int T, const int32_t* children, const double* blen, int32_t root_c
   //   need  bits 0..7   number of simultaneously live CLVs (REG included) to evaluate the node; 0 for
   //                     a tip, which makes the three cases one rule: equal needs -> one more, else the larger
   //   size  bits 8..31  inner nodes in the subtree of id (0 for a tip)
-  // uses[id] counts references: every inner node except the virtual root must be consumed
+  // uses[id] counts references: every tip and every inner node except the virtual root must be consumed
   // exactly once (root_child by the root edge).
   sc.up.assign(n_nodes, 0);
   sc.uses.assign(n_nodes, 0);
@@ -38,7 +38,7 @@ int plan_tree(int T, const int32_t* children, const double* blen, int32_t root_c
   if (root_child < 0 || root_child >= n_nodes - 1) return -1;
   uses[root_child] += uses[root_child] < 2;
   int wrong = uses[n_nodes - 1];
-  for (int id = T; id < n_nodes - 1; ++id) wrong |= uses[id] ^ 1;
+  for (int id = 0; id < n_nodes - 1; ++id) wrong |= uses[id] ^ 1;  // every tip and inner node consumed exactly once
   if (wrong) return -1;
   auto need = [&](int32_t id) { return (int)(up[id] & 0xff); };
   auto size = [&](int32_t id) { return (int)(up[id] >> 8); };
@@ -54,7 +54,7 @@ int plan_tree(int T, const int32_t* children, const double* blen, int32_t root_c
   //   level bits 8..15  stack depth when its subtree starts = the slot its first-evaluated child
   //         parks in. A parked result occupies its slot only from the moment it is produced, so
   //         the first child runs at `level`, the second at `level + 1`.
-  //   par   bit 16      parity of the node's distance from the root edge (picks the CLV arena end, k_repeats)
+  //   par   bit 16      parity of the node's distance from the root edge
   sc.down.resize(n_nodes);
   uint64_t* down = sc.down.data();
   auto pack = [](int start, int want, int level, int par) {

@@ -4,8 +4,8 @@
 // the 32 B of a planned step) and the host does no per-tree work beyond a memcpy into pinned memory.
 //
 // One warp per tree, three tables in shared memory (children, `up`, `down` of the inner nodes: 12 B each):
-//   1. all lanes: copy the operation list in, check branch lengths, count references (every inner node
-//      is consumed exactly once), check that children precede parents;
+//   1. all lanes: copy the operation list in, check branch lengths, count references (every tip and
+//      every inner node is consumed exactly once), check that children precede parents;
 //   2. lane 0: the bottom-up sweep (need, size per node) - a dependent chain through `up`;
 //   3. lane 0: the top-down sweep hands every node its block start, parking slot, level and parity;
 //   4. all lanes: every operation builds its own step from the tables and stores it at its program
@@ -49,6 +49,7 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
   const uint32_t s_dn = s_up + 4u * n_ops;                       // [n_ops] reference counts, then the down word
   const uint32_t s_ch = s_dn + 4u * n_ops;                       // [n_ops] child a | child b << 16
   uint32_t* dn_gen = sm + n_ops;                                 // (generic view, for the atomics)
+  uint32_t* tip_seen = sm + 3 * n_ops;                           // [(T+31)/32] one bit per tip: referenced
   const int t = p.tree0 + blockIdx.x;
   const int32_t* __restrict__ gch = p.children + (size_t)t * 2 * n_ops;
   const double* __restrict__ gbl = p.blen + (size_t)t * 2 * n_ops;
@@ -60,7 +61,11 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
   // 1. load + checks: children precede parents, every inner node is consumed exactly once
   bool neg = !(rbl >= 0.0), bad = false;
   for (int i = lane; i < n_ops; i += 32) sts(s_dn + 4u * i, 0u);
+  for (int i = lane; i < (T + 31) / 32; i += 32) tip_seen[i] = 0u;
   __syncwarp();
+  // a tip referenced twice shows as a bit already set; with every inner node consumed once the 2T-3
+  // references leave exactly T for the T tips, so "no tip twice" is "every tip once"
+  auto see_tip = [&](int id) { return (atomicOr(&tip_seen[id >> 5], 1u << (id & 31)) >> (id & 31)) & 1u; };
 #pragma unroll 4
   for (int op = lane; op < n_ops; op += 32) {
     const int2 c = *reinterpret_cast<const int2*>(gch + 2 * op);
@@ -70,12 +75,14 @@ __global__ void __launch_bounds__(32) k_plan(PlanDev p) {
       bad = true;
     } else {
       sts(s_ch + 4u * op, (uint32_t)c.x | (uint32_t)c.y << 16);
-      if (c.x >= T) atomicAdd(&dn_gen[c.x - T], 1u);
-      if (c.y >= T) atomicAdd(&dn_gen[c.y - T], 1u);
+      if (c.x >= T) atomicAdd(&dn_gen[c.x - T], 1u); else bad |= see_tip(c.x) != 0u;
+      if (c.y >= T) atomicAdd(&dn_gen[c.y - T], 1u); else bad |= see_tip(c.y) != 0u;
     }
   }
   if (rc < 0 || rc >= n_nodes - 1) bad = true;
-  else if (lane == 0 && rc >= T) atomicAdd(&dn_gen[rc - T], 1u);
+  else if (lane == 0) {
+    if (rc >= T) atomicAdd(&dn_gen[rc - T], 1u); else bad |= see_tip(rc) != 0u;
+  }
   __syncwarp();
   for (int i = lane; i < n_ops - 1; i += 32) bad |= lds(s_dn + 4u * i) != 1u;
   if (lane == 0) bad |= lds(s_dn + 4u * (n_ops - 1)) != 0u;
@@ -196,7 +203,9 @@ void ensure_dynamic_smem(const void* kernel, size_t bytes) {
   }
 }
 
-size_t plan_smem_bytes(int n_tips) { return (size_t)(n_tips - 2) * (2 * sizeof(uint32_t) + 2 * sizeof(uint16_t)); }
+size_t plan_smem_bytes(int n_tips) {
+  return (size_t)(n_tips - 2) * (2 * sizeof(uint32_t) + 2 * sizeof(uint16_t)) + (size_t)(n_tips + 31) / 32 * sizeof(uint32_t);
+}
 
 // The device planner packs a block start into 15 bits and keeps three tables in shared memory.
 bool plan_on_device_ok(int n_tips) { return n_tips - 2 < (1 << 15) && plan_smem_bytes(n_tips) <= (size_t)200 * 1024; }

@@ -185,40 +185,13 @@ def test_pipelined_call_matches_resident_batch():
     assert np.array_equal(a, np.tile(a[:len(tb["root_child"])], rep))
 
 
-@pytest.mark.parametrize("name", GOLDEN_NAMES)
-@pytest.mark.parametrize("arena", [0, 1024])
-def test_site_repeats_are_bit_identical(name, arena):
-    """k_repeats + k_prune_sr (one CLV entry per class of patterns that agree below a node) give the
-    same doubles as pruning every column; the default arena (64 entries) keeps most CLV entries in the global part, 1024 keeps them in shared memory."""
-    fam, tb, exp, _ = load_golden(name)
-    a, oa, ta = _score_with(fam, tb, site_repeats=1, sr_arena=arena)
-    b, ob, _ = _score_with(fam, tb, site_patterns=0)
-    if ta["pattern_trees"]:
-        assert ta["site_repeats"] == 1
-    assert np.array_equal(a, b)
-    assert np.array_equal(oa["xmsa_emission"], ob["xmsa_emission"])
-    assert rel_err(a, exp["loglik"]) <= TOL
-
-
-@pytest.mark.parametrize("name", ["synth_n12", "synth_n40"])
-def test_site_repeats_with_naive_across_the_root_edge(name):
-    fam, tb, _, _ = load_golden(name)
-    keep = [t for t in range(len(tb["root_child"])) if 0 in tb["children"][t, -1]]
-    rot = _rotate_root_to_naive({k: v[keep] for k, v in tb.items()})
-    a, oa, ta = _score_with(fam, rot, site_repeats=1)
-    b, ob, _ = _score_with(fam, rot, site_patterns=0)
-    assert ta["site_repeats"] == 1 and ta["pattern_trees"] == len(keep)
-    assert np.array_equal(a, b) and np.array_equal(oa["xmsa_emission"], ob["xmsa_emission"])
-
-
-def test_site_repeats_mixed_batch_and_chunks():
-    """Trees with the naive tip deep in the tree run on all columns next to site-repeat trees; many
-    chunks; pipelined and resident forms agree."""
+def test_mixed_pattern_batch_and_chunks():
+    """Trees with the naive tip deep in the tree run on all columns next to trees pruned on site
+    patterns; many chunks; pipelined and resident forms agree."""
     fam, tb, _, _ = load_golden("synth_n12")
     rep = 41
     big = {k: np.concatenate([v] * rep) for k, v in tb.items()}
     f = device.Family(fam)
-    f.set_option("site_repeats", 1)
     f.set_option("chunk_trees", 29)
     a = f.score(big)
     tm = f.timings()
@@ -228,7 +201,7 @@ def test_site_repeats_mixed_batch_and_chunks():
     f.set_option("site_patterns", 0)
     c = f.score(big)
     f.close()
-    assert 0 < tm["pattern_trees"] < len(a) and tm["site_repeats"] == 1
+    assert 0 < tm["pattern_trees"] < len(a)
     assert np.array_equal(a, b) and np.array_equal(a, c)
 
 

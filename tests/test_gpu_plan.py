@@ -83,6 +83,15 @@ def test_device_planner_reports_bad_trees():
     bad["children"][71, op, 1] = bad["children"][71, op, 0]   # an inner node consumed twice
     with pytest.raises(device.DeviceError, match="tree 71 is not a valid post-order"):
         f.score(bad)
+    for dp, tree in ((1, 72), (0, 73)):  # a tip referenced twice: device and host planner
+        bad = {k: v.copy() for k, v in big.items()}
+        tips = np.argwhere(bad["children"][tree] < T)
+        (o1, c1), (o2, c2) = tips[0], tips[-1]
+        bad["children"][tree, o2, c2] = bad["children"][tree, o1, c1]
+        f.set_option("device_plan", dp)
+        with pytest.raises(device.DeviceError, match=f"tree {tree} is not a valid post-order"):
+            f.score(bad)
+    f.set_option("device_plan", 1)
     bad = {k: v.copy() for k, v in big.items()}
     bad["blen"][75, 3, 1] = -0.5
     bad["blen"][79, 3, 1] = np.nan

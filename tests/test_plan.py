@@ -119,3 +119,12 @@ def test_malformed_tree_is_rejected():
     bad["children"][0, 1, 0] = bad["children"][0, 1, 1] = 4  # inner node consumed twice
     with pytest.raises(ValueError):
         plan(fam["n_tips"], bad)
+    # a tip referenced twice (and so another one never): the reference refuses a tip-set mismatch in
+    # SetTipStates (lib/libptpll/src/pll_partition.cpp:153-194)
+    bad = {k: v.copy() for k, v in tb.items()}
+    T = fam["n_tips"]
+    tips = np.argwhere(bad["children"][0] < T)
+    (o1, c1), (o2, c2) = tips[0], tips[1]
+    bad["children"][0, o2, c2] = bad["children"][0, o1, c1]
+    with pytest.raises(ValueError):
+        plan(T, bad)
