@@ -96,6 +96,23 @@ typedef struct lh_tree_batch {
   const double*  rates;       /* [B][R] discrete-Gamma category rates         */
 } lh_tree_batch_t;
 
+/* B tree samples as the RevBayes trace holds them: Newick text plus the substitution parameters of the
+ * row (src/PhyloHMM.cpp:414-426). The strings go to the device as they are; parsing
+ * (regex_replace("[&index=N]") + pll_utree_parse_newick_string + set_missing_branch_length + the
+ * post-order traversal: src/PhyloHMM.cpp:419-422, parse_utree.y:179-246, pll_util.cpp:46-62,
+ * utree.c:284-442) is a kernel there. Tip labels are matched against the family's xMSA row labels
+ * (lh_family_set_labels), as Partition::SetTipStates matches them (pll_partition.cpp:153-194).     */
+typedef struct lh_newick_batch {
+  int32_t n_trees;            /* B                                                       */
+  int32_t n_rates;            /* R                                                       */
+  const char* const* newick;  /* [B] NUL-terminated Newick strings                       */
+  const int64_t* length;      /* [B] strlen of each string, or NULL                      */
+  const double*  er;          /* [B][6]                                                  */
+  const double*  pi;          /* [B][4]                                                  */
+  const double*  rates;       /* [B][R] category rates, or NULL: computed from alpha     */
+  const double*  alpha;       /* [B] Gamma shape (pll_compute_gamma_cats, MEAN); read when rates is NULL */
+} lh_newick_batch_t;
+
 /* Optional per-tree read-outs (any pointer may be NULL). What the reference
  * exposes through accessors after LogLikelihood(): xmsa_emission()
  * (PhyloHMM.hpp:31), the forward tables and scaler counts (HMM.hpp forward
@@ -141,8 +158,10 @@ typedef struct lh_timings {
   int32_t pattern_trees;     /* trees of the batch pruned on site patterns               */
   float ms_call;             /* wall clock of the last lh_score_batch call               */
   float ms_setup;            /* of which validation + buffer set-up before the pipeline  */
-  float ms_plan_dev;         // sum over k_plan launches (device traversal planning)             
-  int32_t device_plan;       // 1 when the batch was planned by k_plan                           
+  float ms_plan_dev;         /* sum over k_plan launches (device traversal planning)     */
+  int32_t device_plan;       /* 1 when the batch was planned by k_plan                   */
+  float ms_newick;           /* sum over k_newick launches (device Newick parsing)       */
+  int32_t newick_host_trees; /* trees of an lh_score_newick call the host parser took over */
 } lh_timings_t;
 
 const char* lh_last_error(void);
@@ -162,6 +181,14 @@ int  lh_family_rebind(lh_family_t* fam, const lh_family_desc_t* desc);
 int lh_score_batch(lh_family_t* fam, const lh_tree_batch_t* trees,
                    double* loglik /* [B] */, lh_outputs_t* opt /* or NULL */);
 
+/* The same for samples given as Newick text (the batched RevBayes hook: what the loop body
+ * src/PhyloHMM.cpp:419-430 does per row, for B rows). Needs lh_family_set_labels first. A tree the
+ * device parser does not accept is parsed by the host parser (same grammar as the reference's); a
+ * malformed tree fails the call with that parser's message.                                      */
+int lh_family_set_labels(lh_family_t* fam, const char* const* labels /* [n_tips], xMSA row order */);
+int lh_score_newick(lh_family_t* fam, const lh_newick_batch_t* trees,
+                    double* loglik /* [B] */, lh_outputs_t* opt /* or NULL */);
+
 /* Split form for callers that keep a batch resident (bench `value`, pipelining):
  * upload once, run any number of times, fetch.                               */
 int lh_batch_upload(lh_family_t* fam, const lh_tree_batch_t* trees);
@@ -174,6 +201,13 @@ int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/scor
 /* Test hook: the traversal programs of the current batch as the device holds them
  * (steps [B][T-1][4] int32, pblen [B][2T-3]); compared with the host planner in the tests. */
 int lh_debug_fetch_plan(lh_family_t* fam, int32_t* steps, double* pblen);
+/* Test hook: runs only the device Newick parser (k_newick) over the batch's strings and returns what it
+ * wrote - children [B][T-2][2], blen [B][T-2][2], root_child [B], root_blen [B], whether the naive tip is on
+ * the root edge or under the virtual root, and whether the tree was left to the host parser - plus the
+ * summed kernel time; compared with lhh_newick_to_ops in the tests.                                      */
+int lh_debug_parse_newick(lh_family_t* fam, const lh_newick_batch_t* trees, int32_t* children, double* blen,
+                          int32_t* root_child, double* root_blen, uint8_t* on_patterns /* or NULL */,
+                          uint8_t* left_to_host, float* ms_kernel /* or NULL */);
 /* Diagnostic: sustained FP64 FMA rate of a register-resident DFMA loop (TFLOP/s); the
  * denominator for the FP64-pipe view of the pruning kernel (no reference counterpart). */
 int lh_measure_fp64_peak(int device, double* tflops);

@@ -39,6 +39,19 @@ int lhh_newick_to_ops(int32_t n_tips, const char* const* labels, int32_t n_trees
                       const char* const* newicks, int32_t n_threads, int32_t* children,
                       double* blen, int32_t* root_child, double* root_blen);
 
+/* The inverse, for workloads and tests: the trees of a flat batch as RevBayes-style Newick text
+ * ("[&index=N]" comments, shortest round-trip lengths); tree t is written at out + t * stride,
+ * NUL-terminated. Fails when stride is too small.                                        */
+int lhh_ops_to_newick(int32_t n_tips, const char* const* labels, int32_t n_trees, const int32_t* children,
+                      const double* blen, const int32_t* root_child, const double* root_blen,
+                      int32_t n_threads, char* out, int64_t stride);
+
+/* Test hook: the decimal -> double conversion of the device Newick parser (csrc/decimal.hpp, Eisel-Lemire),
+ * compiled for the host. n NUL-terminated strings laid end to end in buf; status 0 = converted (out is the
+ * correctly rounded double, as atof in the reference's lexer), 1 = no number, 2 = left to the host parser;
+ * consumed = characters read.                                                                    */
+int lhh_parse_decimal_buf(const char* buf, int32_t n, double* out, int32_t* status, int32_t* consumed);
+
 /* ---- linearham::PhyloHMM (linearham_b200/csrc/host/phylo_hmm.hpp), the host-side mirror of the
  * reference class (src/PhyloHMM.hpp:24-127, src/HMM.hpp:31-413), behind a C handle so that
  * non-C++ callers (the ctypes tests, bench.py) can drive it. Construction is pure host work

@@ -47,6 +47,14 @@ class TreeBatch(C.Structure):
     ]
 
 
+class NewickBatch(C.Structure):
+    _fields_ = [
+        ("n_trees", C.c_int32), ("n_rates", C.c_int32),
+        ("newick", C.POINTER(C.c_char_p)), ("length", C.POINTER(C.c_int64)),
+        ("er", _f64p), ("pi", _f64p), ("rates", _f64p), ("alpha", _f64p),
+    ]
+
+
 class Outputs(C.Structure):
     _fields_ = [
         ("xmsa_emission", _f64p), ("vgerm_forward", _f64p), ("vd_forward", _f64p),
@@ -68,6 +76,7 @@ class Timings(C.Structure):
         ("prune_columns", C.c_int32), ("pattern_trees", C.c_int32),
         ("ms_call", C.c_float), ("ms_setup", C.c_float),
         ("ms_plan_dev", C.c_float), ("device_plan", C.c_int32),
+        ("ms_newick", C.c_float), ("newick_host_trees", C.c_int32),
     ]
 
 
@@ -149,11 +158,34 @@ def alloc_outputs(fam, B, fields=None, n_rates=None):
     return o, arrs
 
 
+def newick_batch(newicks, er, pi, n_rates, alpha=None, rates=None, lengths=False):
+    """Newick strings (str or bytes) + er[B,6], pi[B,4] + alpha[B] or rates[B,R] -> (NewickBatch, keepalive)."""
+    nb = NewickBatch()
+    raw = [s if isinstance(s, bytes) else str(s).encode() for s in newicks]
+    B = len(raw)
+    arr = (C.c_char_p * max(B, 1))(*raw)
+    keep = [raw, arr]
+    nb.n_trees, nb.n_rates = B, int(n_rates)
+    nb.newick = C.cast(arr, C.POINTER(C.c_char_p))
+    if lengths:
+        ln = np.array([len(s) for s in raw], dtype=np.int64)
+        keep.append(ln)
+        nb.length = ln.ctypes.data_as(C.POINTER(C.c_int64))
+    for name, val in (("er", er), ("pi", pi), ("alpha", alpha), ("rates", rates)):
+        if val is None:
+            continue
+        a = np.ascontiguousarray(np.asarray(val, dtype=np.float64).reshape(-1))
+        keep.append(a)
+        setattr(nb, name, _ptr(a, C.c_double))
+    return nb, keep
+
+
 DEVICE_SYMBOLS = [
     "lh_last_error", "lh_version", "lh_device_count", "lh_family_create", "lh_family_destroy",
     "lh_score_batch", "lh_batch_upload", "lh_batch_run", "lh_batch_fetch", "lh_sync",
     "lh_loglik_dev", "lh_get_timings", "lh_set_option", "lh_measure_fp64_peak",
     "lh_timer_mark", "lh_timer_elapsed_ms", "lh_family_rebind", "lh_debug_fetch_plan",
+    "lh_family_set_labels", "lh_score_newick", "lh_debug_parse_newick",
     "lh_repertoire_create", "lh_repertoire_score", "lh_repertoire_destroy", "lh_repertoire_set_option", "lh_repertoire_last_error",
 ]
 
@@ -197,6 +229,10 @@ def load_library(path=None):
     lib.lh_timer_elapsed_ms.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_float)]
     lib.lh_debug_fetch_plan.argtypes = [C.c_void_p, _i32p, _f64p]
     lib.lh_family_rebind.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
+    lib.lh_family_set_labels.argtypes = [C.c_void_p, C.POINTER(C.c_char_p)]
+    lib.lh_score_newick.argtypes = [C.c_void_p, C.POINTER(NewickBatch), _f64p, C.POINTER(Outputs)]
+    lib.lh_debug_parse_newick.argtypes = [C.c_void_p, C.POINTER(NewickBatch), _i32p, _f64p, _i32p, _f64p, _u8p, _u8p,
+                                          C.POINTER(C.c_float)]
     lib.lh_repertoire_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int]
     lib.lh_repertoire_score.argtypes = [C.c_void_p, C.POINTER(RepertoireItem), C.c_int32,
                                         C.POINTER(RepertoireStats)]
@@ -210,7 +246,7 @@ def load_library(path=None):
 # ---- host-side C ABI (include/linearham_b200_host.h) ------------------------------------
 
 HOST_SYMBOLS = ["lhh_last_error", "lhh_plan_trees", "lhh_gamma_cats", "lhh_gamma_cats_batch",
-                "lhh_newick_to_ops"]
+                "lhh_newick_to_ops", "lhh_parse_decimal_buf", "lhh_ops_to_newick"]
 
 
 def bind_host(lib):
@@ -220,6 +256,9 @@ def bind_host(lib):
     lib.lhh_newick_to_ops.argtypes = [C.c_int32, C.POINTER(C.c_char_p), C.c_int32, C.POINTER(C.c_char_p),
                                       C.c_int32, _i32p, _f64p, _i32p, _f64p]
     lib.lhh_plan_trees.argtypes = [C.c_int32, C.c_int32, _i32p, _f64p, _i32p, _f64p, _i32p, _f64p, _i32p]
+    lib.lhh_parse_decimal_buf.argtypes = [C.c_char_p, C.c_int32, _f64p, _i32p, _i32p]
+    lib.lhh_ops_to_newick.argtypes = [C.c_int32, C.POINTER(C.c_char_p), C.c_int32, _i32p, _f64p, _i32p, _f64p, C.c_int32,
+                                      C.c_void_p, C.c_int64]
     return lib
 
 

@@ -19,6 +19,7 @@
 #include <emmintrin.h>
 
 #include "../../include/linearham_b200.h"
+#include "../../include/linearham_b200_host.h"
 #include "kernels.hpp"
 #include "plan.hpp"
 #include "pool.hpp"
@@ -162,6 +163,7 @@ int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, ConstA
 }  // namespace
 
 constexpr int kChunkEvents = 9;  // [7], [8]: k_plan of the chunk started / finished (plan stream)
+constexpr size_t kTextSlotBytes = (size_t)32 << 20;  // Newick text per staging segment
 
 struct lh_family {
   int device = 0;
@@ -242,7 +244,22 @@ struct lh_family {
   PinBuf h_list;
   lh_timings_t tm{};
   bool want_tables = false, want_rate_ll = false;
+  int bad_plan_tree = -1;  // set by lh_batch_fetch when k_plan refused a tree
   DevBuf d_rate_ll;
+  // Newick input (lh_score_newick): the xMSA row labels as a device hash table, a ring of text segments,
+  // and what k_newick / k_split leave per tree and per chunk
+  std::vector<std::string> labels;
+  std::vector<const char*> label_ptrs;
+  DevBuf d_label_slots, d_label_off, d_label_chars;
+  lhb::LabelTableDev lt{};
+  bool labels_set = false;
+  bool newick_mode = false;           // the current batch came in as text
+  DevBuf d_text[kRing];
+  cudaEvent_t text_copied[kRing] = {};
+  DevBuf d_on_pat, d_nw_status, d_chunk_npat;
+  PinBuf h_nw_status, h_chunk_npat;
+  std::vector<cudaEvent_t> seg_ev;    // pairs around the k_newick launches of the current call
+  int n_seg_ev = 0;
   std::unique_ptr<lhb::WorkerPool> pool;  // planner threads, started on first use
   std::vector<lhb::PlanScratch> plan_scratch;
 };
@@ -268,7 +285,10 @@ void lh_family_destroy(lh_family_t* f) {
                     &f->d_xe, &f->d_loglik, &f->d_scratch, &f->d_scratch_cnt, &f->d_vgerm, &f->d_vd,
                     &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
                     &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_counters,
-                    &f->d_rate_ll, &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags};
+                    &f->d_rate_ll, &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags,
+                    &f->d_label_slots, &f->d_label_off, &f->d_label_chars, &f->d_text[0], &f->d_text[1], &f->d_text[2],
+                    &f->d_on_pat, &f->d_nw_status, &f->d_chunk_npat};
+  static_assert(lh_family::kRing == 3, "d_text slots are listed by hand above");
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
   for (auto& c : f->cols) c.h_codes_t.release();
@@ -277,6 +297,11 @@ void lh_family_destroy(lh_family_t* f) {
   f->h_flags.release();
   f->h_list.release();
   f->h_out.release();
+  f->h_nw_status.release();
+  f->h_chunk_npat.release();
+  for (auto& e : f->text_copied)
+    if (e) cudaEventDestroy(e);
+  for (auto& e : f->seg_ev) cudaEventDestroy(e);
   for (auto& e : f->ev)
     if (e) cudaEventDestroy(e);
   for (auto& e : f->user_ev)
@@ -320,6 +345,7 @@ static int bind_family(lh_family* f, const lh_family_desc_t* d) {
   f->B = 0;
   f->n_chunks = 0;
   f->window_set = false;
+  f->labels_set = false;  // the labels belong to the family
   for (auto& c : f->cols) c.codes_ns = 0;
   auto bail = [&](int) { return 1; };
   const int T = d->n_tips, S = d->n_sites;
@@ -498,6 +524,7 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
   cudaEventCreateWithFlags(&f->hmm_done, cudaEventDisableTiming);
   if (f->d_counters.reserve(64)) return bail(1);
   for (auto& ev : f->ring_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+  for (auto& ev : f->text_copied) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&f->misc_ev, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&f->list_ev, cudaEventDisableTiming);
   for (auto& ev : f->ev) cudaEventCreate(&ev);
@@ -514,6 +541,64 @@ int lh_family_rebind(lh_family_t* f, const lh_family_desc_t* d) {
   if (check_desc(d)) return 1;
   f->bound = false;
   return bind_family(f, d);
+}
+
+// The xMSA row labels of the bound family -> the device hash table k_newick looks tips up in.
+int lh_family_set_labels(lh_family_t* f, const char* const* labels) {
+  if (!f || !labels) return fail("null argument");
+  if (!f->bound) return fail("no family bound to the handle");
+  LH_CUDA(cudaSetDevice(f->device));
+  const int T = f->fd.T;
+  if (T >= 65536) return fail("the device Newick parser takes families of up to 65535 tips (got %d)", T);
+  f->labels_set = false;
+  f->labels.assign(T, std::string());
+  f->label_ptrs.assign(T, nullptr);
+  size_t cap = 8;
+  while (cap < (size_t)T * 2) cap <<= 1;
+  std::vector<uint32_t> slots(cap * 4, 0xffffffffu), off(T, 0);
+  std::vector<char> chars;
+  for (int r = 0; r < T; ++r) {
+    if (!labels[r]) return fail("null label for row %d", r);
+    f->labels[r] = labels[r];
+    const std::string& l = f->labels[r];
+    if (l.empty() || l.size() >= 65536) return fail("label of row %d is empty or too long", r);
+    uint32_t h = 2166136261u;  // FNV-1a, as host/newick.cpp
+    uint64_t first8 = 0;
+    for (size_t i = 0; i < l.size(); ++i) {
+      h = (h ^ (unsigned char)l[i]) * 16777619u;
+      if (i < 8) first8 |= (uint64_t)(unsigned char)l[i] << (8 * i);
+    }
+    off[r] = (uint32_t)chars.size();
+    chars.insert(chars.end(), l.begin(), l.end());
+    for (uint32_t j = h & (uint32_t)(cap - 1);; j = (j + 1) & (uint32_t)(cap - 1)) {
+      uint32_t* e = &slots[(size_t)j * 4];
+      if (e[3] == 0xffffffffu) {
+        e[0] = (uint32_t)first8;
+        e[1] = (uint32_t)(first8 >> 32);
+        e[2] = h;
+        e[3] = (uint32_t)l.size() | (uint32_t)r << 16;
+        break;
+      }
+      if (f->labels[e[3] >> 16] == l) return fail("duplicate label '%s'", l.c_str());
+    }
+  }
+  for (int r = 0; r < T; ++r) f->label_ptrs[r] = f->labels[r].c_str();
+  chars.resize((chars.size() + 16) / 16 * 16, 0);
+  if (f->d_label_slots.reserve(slots.size() * 4) || f->d_label_off.reserve(off.size() * 4) || f->d_label_chars.reserve(chars.size()))
+    return 1;
+  // (ordered on the compute stream and waited for, like the tip codes: see configure_batch)
+  LH_CUDA(cudaStreamSynchronize(f->stream));
+  LH_CUDA(cudaStreamSynchronize(f->plan_stream));
+  LH_CUDA(cudaMemcpyAsync(f->d_label_slots.p, slots.data(), slots.size() * 4, cudaMemcpyHostToDevice, f->stream));
+  LH_CUDA(cudaMemcpyAsync(f->d_label_off.p, off.data(), off.size() * 4, cudaMemcpyHostToDevice, f->stream));
+  LH_CUDA(cudaMemcpyAsync(f->d_label_chars.p, chars.data(), chars.size(), cudaMemcpyHostToDevice, f->stream));
+  LH_CUDA(cudaStreamSynchronize(f->stream));
+  f->lt.slots = f->d_label_slots.as<uint4>();
+  f->lt.mask = (uint32_t)(cap - 1);
+  f->lt.long_off = f->d_label_off.as<uint32_t>();
+  f->lt.chars = f->d_label_chars.as<char>();
+  f->labels_set = true;
+  return 0;
 }
 
 int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
@@ -688,12 +773,21 @@ int configure_batch(lh_family* f, int B, int R) {
     const bool small = (size_t)B * lhb::records_per_pass(T) * 20 * R * sizeof(double) <= ((size_t)1 << 30);
     const bool want = f->opt_device_plan < 0 ? (small || host_ns > 0.5 * kernel_ns) : f->opt_device_plan != 0;
     f->dev_plan = want && lhb::plan_on_device_ok(T);
+    if (f->newick_mode) {  // k_newick feeds k_plan
+      if (!lhb::plan_on_device_ok(T)) return fail("the device Newick parser takes families of up to 32769 tips (got %d)", T);
+      f->dev_plan = true;
+    }
     // how much faster the host stages a tree than the GPU scores it (the device planner leaves the host
     // a memcpy: ~6 ns per operation and thread)
     f->stage_ratio = kernel_ns / (f->dev_plan ? 6.0 / threads : host_ns);
   }
   f->flags_pending = false;
   f->run_recorded = false;
+  if (f->newick_mode) {
+    if (f->d_on_pat.reserve((size_t)B) || f->d_nw_status.reserve((size_t)B) || f->h_nw_status.reserve((size_t)B)) return 1;
+    for (auto& d : f->d_text)
+      if (d.reserve(kTextSlotBytes)) return 1;
+  }
   if (f->dev_plan) {
     const size_t n2 = (size_t)B * (T - 2) * 2;
     if (f->d_rchildren.reserve(n2 * sizeof(int32_t)) || f->d_rblen.reserve(n2 * sizeof(double)) ||
@@ -719,7 +813,8 @@ int configure_batch(lh_family* f, int B, int R) {
   f->rec_bytes_tree = rec_bytes_tree;
   int strahler = 1;
   while ((2 << (strahler - 1)) <= T) ++strahler;  // floor(log2 T) + 1
-  const bool use[2] = {f->n_pattern_trees < B, f->n_pattern_trees > 0};
+  // (text input: which trees run on patterns is only known on the device, so both sets are made ready)
+  const bool use[2] = {f->n_pattern_trees < B || f->newick_mode, f->n_pattern_trees > 0};
   size_t scratch_bytes = 0, scratch_cnt_bytes = 0;
   for (int g = 0; g < 2; ++g) {
     lhb::PruneCfg& pc = f->pc[g];
@@ -858,7 +953,7 @@ int configure_batch(lh_family* f, int B, int R) {
   int seg = (int)std::max<size_t>(64, ((size_t)48 << 20) / stage_bytes_tree);
   f->seg = std::min(seg, f->chunk_pipe);
   for (auto& r : f->h_ring)
-    if (r.reserve((size_t)f->seg * stage_bytes_tree)) return 1;
+    if (r.reserve(f->newick_mode ? kTextSlotBytes : (size_t)f->seg * stage_bytes_tree)) return 1;
 
   lhb::HmmOut& ho = f->ho;
   ho = lhb::HmmOut{};
@@ -989,14 +1084,177 @@ int stage_segment(lh_family* f, const lh_tree_batch_t* tb, int t0, int n, int sl
   return 0;
 }
 
+void ensure_pool(lh_family* f) {
+  if (f->pool) return;
+  int nthreads = f->opt_threads > 0 ? f->opt_threads : (int)std::thread::hardware_concurrency();
+  nthreads = std::max(1, std::min(nthreads, 32));
+  f->pool.reset(new lhb::WorkerPool(nthreads - 1));  // the calling thread works too
+  f->plan_scratch.resize(nthreads);
+}
+
+// Text input, first trees of a batch: parsed and planned on the host, into a scratch, because their
+// programs choose the shared-memory window of the CLV stack (the same probe as for array input).
+int probe_window_from_text(lh_family* f, const lh_newick_batch_t* nb, int t0, int n) {
+  const int T = f->fd.T, NB = 2 * T - 3;
+  const size_t per = (size_t)(T - 2) * 2;
+  std::vector<int32_t> ch(n * per), rc(n);
+  std::vector<double> bl(n * per), rb(n);
+  if (lhh_newick_to_ops(T, f->label_ptrs.data(), n, nb->newick + t0, f->opt_threads, ch.data(), bl.data(), rc.data(), rb.data()))
+    return 0;  // a malformed tree among them: the device pass flags it and the call reports it; any window is valid
+  lh_tree_batch_t tb{};
+  tb.n_trees = n;
+  tb.children = ch.data();
+  tb.blen = bl.data();
+  tb.root_child = rc.data();
+  tb.root_blen = rb.data();
+  std::vector<lhb::Step> steps((size_t)n * (T - 1));
+  std::vector<double> pblen((size_t)n * NB);
+  int slots = 0;
+  ensure_pool(f);
+  {
+    // (plan_range reports bad trees through fail(); here they are left to the device pass)
+    std::atomic<int> bad(0);
+    lhb::PlanScratch& sc = f->plan_scratch[f->pool->workers()];
+    for (int i = 0; i < n; ++i) {
+      const int d = lhb::plan_tree(T, ch.data() + i * per, bl.data() + i * per, rc[i], rb[i], steps.data() + (size_t)i * (T - 1),
+                                   pblen.data() + (size_t)i * NB, sc);
+      if (d < 0) return 0;
+      slots = std::max(slots, d);
+    }
+  }
+  f->slots = std::max(f->slots, slots);
+  int64_t hist[32] = {};
+  for (int i = 0; i < n; ++i)
+    for (int q = 0; q < T - 2; ++q) {
+      const int dst = steps[(size_t)i * (T - 1) + q].dst;
+      if (dst >= 0 && dst < 32) ++hist[dst];
+    }
+  for (auto& pc : f->pc) {
+    int best = 0;
+    int64_t best_sum = -1;
+    for (int lo = 0; lo + pc.smem_slots <= std::max(pc.total_slots, pc.smem_slots); ++lo) {
+      int64_t sum = 0;
+      for (int k = lo; k < lo + pc.smem_slots && k < 32; ++k) sum += hist[k];
+      if (sum > best_sum) { best_sum = sum; best = lo; }
+    }
+    pc.smem_lo = f->opt_smem_lo >= 0 ? std::min(f->opt_smem_lo, std::max(0, pc.total_slots - pc.smem_slots)) : best;
+  }
+  f->tm.prune_smem_lo = f->pc[1].n_cols ? f->pc[1].smem_lo : f->pc[0].smem_lo;
+  return 0;
+}
+
+// Copies the strings of trees [t0, t0+n) (lengths len[0..n)) into ring slot `slot`, queues their copy to
+// the slot's device text buffer on `cs` and their parse (k_newick) on the plan stream.
+// Slot layout: offs [n] uint32 | pad to 16 | strings, each NUL-terminated and 16-byte aligned.
+int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n, const int64_t* len, int slot, cudaStream_t cs) {
+  if (f->ring_busy[slot]) {
+    LH_CUDA(cudaEventSynchronize(f->ring_ev[slot]));  // k_newick of the slot's previous segment has run
+    f->ring_busy[slot] = false;
+  }
+  const auto t_a = std::chrono::steady_clock::now();
+  if (!f->window_set) {
+    if (probe_window_from_text(f, nb, t0, std::min(n, 16))) return 1;
+    f->window_set = true;
+  }
+  uint8_t* base = f->h_ring[slot].as<uint8_t>();
+  uint32_t* offs = reinterpret_cast<uint32_t*>(base);
+  const size_t text0 = ((size_t)n * 4 + 15) / 16 * 16;
+  size_t at = 0;
+  for (int i = 0; i < n; ++i) {
+    offs[i] = (uint32_t)at;
+    at += ((size_t)len[i] + 1 + 15) / 16 * 16;
+  }
+  const size_t total = text0 + at;
+  ensure_pool(f);
+  constexpr int kBlock = 8;  // trees per task
+  f->pool->run((n + kBlock - 1) / kBlock, [&](int task, int) {
+    const int lo = task * kBlock, hi = std::min(n, lo + kBlock);
+    for (int i = lo; i < hi; ++i) {
+      uint8_t* dst = base + text0 + offs[i];
+      const size_t l = (size_t)len[i], padded = (l + 1 + 15) / 16 * 16;
+      const size_t body = l / 16 * 16;  // whole 16-byte blocks stream straight from the caller's string
+      stream_copy(dst, nb->newick[t0 + i], body);
+      uint8_t tail[16] = {};
+      std::memcpy(tail, nb->newick[t0 + i] + body, l - body);
+      stream_copy(dst + body, tail, 16);
+      if (padded > body + 16) std::memset(dst + body + 16, 0, padded - body - 16);
+    }
+  });
+  _mm_sfence();
+  f->tm.ms_plan += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_a).count();
+  LH_CUDA(cudaMemcpyAsync(f->d_text[slot].p, base, total, cudaMemcpyHostToDevice, cs));
+  LH_CUDA(cudaEventRecord(f->text_copied[slot], cs));
+  f->tm.h2d_bytes += (int64_t)total;
+  cudaStream_t ps = f->plan_stream;
+  LH_CUDA(cudaStreamWaitEvent(ps, f->text_copied[slot], 0));
+  lhb::NewickDev p{};
+  p.T = f->fd.T;
+  p.tree0 = t0;
+  p.n = n;
+  p.text = f->d_text[slot].as<char>() + text0;
+  p.offs = f->d_text[slot].as<uint32_t>();
+  p.labels = f->lt;
+  p.children = f->d_rchildren.as<int32_t>();
+  p.blen = f->d_rblen.as<double>();
+  p.root_child = f->d_rroot_child.as<int32_t>();
+  p.root_blen = f->d_rroot_blen.as<double>();
+  p.on_pat = f->d_on_pat.as<uint8_t>();
+  p.status = f->d_nw_status.as<uint8_t>();
+  if (f->opt_timing) {
+    while ((int)f->seg_ev.size() < f->n_seg_ev + 2) {
+      cudaEvent_t e;
+      LH_CUDA(cudaEventCreate(&e));
+      f->seg_ev.push_back(e);
+    }
+    cudaEventRecord(f->seg_ev[f->n_seg_ev], ps);
+  }
+  lhb::launch_newick(p, ps);
+  if (f->opt_timing) {
+    cudaEventRecord(f->seg_ev[f->n_seg_ev + 1], ps);
+    f->n_seg_ev += 2;
+  }
+  f->tm.kernel_launches += 1;
+  LH_CUDA(cudaEventRecord(f->ring_ev[slot], ps));
+  f->ring_busy[slot] = true;
+  return 0;
+}
+
+// The strings of trees [c0, c0+cn) -> the device, in segments of up to kTextSlotBytes; *k counts ring slots.
+int stage_text_chunk(lh_family* f, const lh_newick_batch_t* nb, int c0, int cn, int* k, cudaStream_t cs) {
+  std::vector<int64_t> lens(cn);
+  if (nb->length) {
+    std::copy(nb->length + c0, nb->length + c0 + cn, lens.begin());
+  } else {
+    ensure_pool(f);
+    f->pool->run((cn + 15) / 16, [&](int task, int) {
+      for (int i = task * 16; i < std::min(cn, task * 16 + 16); ++i) lens[i] = (int64_t)std::strlen(nb->newick[c0 + i]);
+    });
+  }
+  for (int i = 0; i < cn;) {
+    size_t bytes = 0;
+    int n = 0;
+    while (i + n < cn) {
+      const size_t add = ((size_t)lens[i + n] + 1 + 15) / 16 * 16 + 4;
+      if (n && bytes + add + 16 > kTextSlotBytes) break;
+      bytes += add;
+      ++n;
+    }
+    if (bytes + 16 > kTextSlotBytes) return fail("tree %d: a Newick string of %lld bytes is too long", c0 + i, (long long)lens[i]);
+    if (stage_text_segment(f, nb, c0 + i, n, lens.data() + i, *k % lh_family::kRing, cs)) return 1;
+    i += n;
+    ++*k;
+  }
+  return 0;
+}
+
 // Substitution parameters of the whole batch (10 + R doubles per tree) -> HBM on `s`.
-int stage_params(lh_family* f, const lh_tree_batch_t* tb, cudaStream_t s) {
+int stage_params(lh_family* f, const double* er, const double* pi, const double* rates, cudaStream_t s) {
   const size_t B = (size_t)f->B, R = (size_t)f->R;
   if (f->misc_busy) LH_CUDA(cudaEventSynchronize(f->misc_ev));
   double* misc = f->h_misc.as<double>();
-  stream_copy(misc, tb->er, sizeof(double) * 6 * B);
-  stream_copy(misc + 6 * B, tb->pi, sizeof(double) * 4 * B);
-  stream_copy(misc + 10 * B, tb->rates, sizeof(double) * R * B);
+  stream_copy(misc, er, sizeof(double) * 6 * B);
+  stream_copy(misc + 6 * B, pi, sizeof(double) * 4 * B);
+  stream_copy(misc + 10 * B, rates, sizeof(double) * R * B);
   LH_CUDA(cudaMemcpyAsync(f->d_er.p, misc, B * (10 + R) * 8, cudaMemcpyHostToDevice, s));
   LH_CUDA(cudaEventRecord(f->misc_ev, s));
   f->misc_busy = true;
@@ -1059,8 +1317,10 @@ void launch_chunk(lh_family* f, int ci, int t0, int n) {
   lhb::launch_pmatrix(f->fd, f->bd, t0, n, s);
   if (tm) cudaEventRecord(ev[1], s);
   // trees on site patterns are listed first in the chunk's part of d_list, the others after
-  const int n_pat = f->chunk_n_pat[ci];
-  const int count[2] = {n - n_pat, n_pat};
+  // (text input: the split is made on the device by k_split; both launches go out and each takes its part)
+  const bool dyn = f->newick_mode;
+  const int n_pat = dyn ? 0 : f->chunk_n_pat[ci];
+  const int count[2] = {dyn ? (f->pc[0].n_cols ? n : 0) : n - n_pat, dyn ? (f->pc[1].n_cols ? n : 0) : n_pat};
   const int32_t* list[2] = {f->d_list.as<int32_t>() + t0 + n_pat, f->d_list.as<int32_t>() + t0};
   if (tm) cudaEventRecord(ev[2], s);
   for (int g = 1; g >= 0; --g) {
@@ -1069,6 +1329,10 @@ void launch_chunk(lh_family* f, int ci, int t0, int n) {
     c.tree_list = list[g];
     c.work_counter = f->d_counters.as<int32_t>() + g;
     c.grid = (int)std::min<int64_t>(c.grid, (int64_t)count[g] * c.n_tiles * f->R);
+    if (dyn) {
+      c.dyn_n_pat = f->d_chunk_npat.as<int32_t>() + ci;
+      c.dyn_total = n;
+    }
     lhb::launch_prune(f->fd, f->bd, c, t0, count[g], s);
     f->tm.kernel_launches += 1;
     f->tm.prune_launches += 1;
@@ -1100,6 +1364,11 @@ int stage_lists(lh_family* f, std::vector<int> starts, cudaStream_t s) {
   f->starts = std::move(starts);
   f->n_chunks = (int)f->starts.size() - 1;
   f->chunk_n_pat.assign(f->n_chunks, 0);
+  if (f->newick_mode) {  // the lists are made on the device, chunk by chunk (k_split)
+    if (f->d_chunk_npat.reserve((size_t)f->n_chunks * sizeof(int32_t)) || f->h_chunk_npat.reserve((size_t)f->n_chunks * sizeof(int32_t)))
+      return 1;
+    return ensure_chunk_events(f, f->n_chunks);
+  }
   if (f->list_busy) LH_CUDA(cudaEventSynchronize(f->list_ev));
   if (f->h_list.reserve((size_t)f->B * sizeof(int32_t))) return 1;
   int32_t* l = f->h_list.as<int32_t>();
@@ -1175,7 +1444,7 @@ int lh_batch_upload(lh_family_t* f, const lh_tree_batch_t* tb) {
   if (f->B == 0) return 0;
   cudaStream_t s = f->stream;
   if (f->opt_timing) cudaEventRecord(f->ev[0], s);
-  if (stage_params(f, tb, s) || stage_flags(f, s)) return 1;
+  if (stage_params(f, tb->er, tb->pi, tb->rates, s) || stage_flags(f, s)) return 1;
   if (stage_lists(f, chunk_starts(f, false), s)) return 1;
   for (int t0 = 0, k = 0; t0 < f->B; t0 += f->seg, ++k)
     if (stage_segment(f, tb, t0, std::min(f->seg, f->B - t0), k % lh_family::kRing, s)) return 1;
@@ -1217,6 +1486,11 @@ static int collect_run_timings(lh_family* f) {
       sum[k] += x;
     }
   f->tm.ms_plan_dev = sum[5];
+  f->tm.ms_newick = 0.f;
+  for (int i = 0; i + 1 < f->n_seg_ev; i += 2) {
+    cudaEventElapsedTime(&x, f->seg_ev[i], f->seg_ev[i + 1]);
+    f->tm.ms_newick += x;
+  }
   f->tm.ms_pmatrix = sum[0];
   f->tm.ms_prune = sum[2];
   f->tm.ms_edge = sum[3];
@@ -1258,6 +1532,9 @@ int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
   if (get(f->h_out.p, f->d_loglik.p, (size_t)B * 8)) return 1;
   const bool check_flags = f->dev_plan && f->flags_pending;
   if (check_flags && get(f->h_flags.as<int32_t>() + 4, f->d_flags.p, 4 * sizeof(int32_t))) return 1;
+  if (f->newick_mode && (get(f->h_nw_status.p, f->d_nw_status.p, (size_t)B) ||
+                         get(f->h_chunk_npat.p, f->d_chunk_npat.p, (size_t)f->n_chunks * sizeof(int32_t))))
+    return 1;
   if (o) {
     if (get(o->xmsa_emission, f->d_xe.p, (size_t)B * fd.S * 8)) return 1;
     if (o->site_rate_loglik) {
@@ -1288,13 +1565,20 @@ int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
     const int32_t* fl = f->h_flags.as<int32_t>() + 4;
     f->flags_pending = false;
     if (fl[0] != INT32_MAX) return fail("tree %d: negative branch length", fl[0]);
-    if (fl[1] != INT32_MAX) return fail("tree %d is not a valid post-order operation list", fl[1]);
+    if (fl[1] != INT32_MAX) {
+      f->bad_plan_tree = fl[1];
+      return fail("tree %d is not a valid post-order operation list", fl[1]);
+    }
     f->slots = std::max(f->slots, (int)fl[2]);
     const int slot_bound = std::max(f->pc[0].total_slots, f->pc[1].total_slots);
     if (f->slots > slot_bound) return fail("internal: tree needs %d CLV slots, bound is %d", f->slots, slot_bound);
   }
   std::memcpy(loglik, f->h_out.p, (size_t)B * 8);
   f->tm.d2h_bytes = bytes;
+  if (f->newick_mode) {
+    f->tm.pattern_trees = 0;
+    for (int ci = 0; ci < f->n_chunks; ++ci) f->tm.pattern_trees += f->h_chunk_npat.as<int32_t>()[ci];
+  }
   if (f->opt_timing) {
     collect_run_timings(f);
     cudaEventElapsedTime(&f->tm.ms_h2d, f->ev[0], f->ev[1]);
@@ -1304,9 +1588,14 @@ int lh_batch_fetch(lh_family_t* f, double* loglik, lh_outputs_t* o) {
   return 0;
 }
 
-int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh_outputs_t* o) {
-  if (!f || !tb || !loglik) return fail("null argument");
-  if (!f->bound) return fail("no family bound to the handle (the last lh_family_rebind failed)");
+}  // extern "C"
+
+namespace {
+
+// The pipelined call behind lh_score_batch (tb: operation arrays) and lh_score_newick (nb: text; `rates`
+// are the category rates of its trees). Host buffers in, host results out.
+int score_call(lh_family* f, const lh_tree_batch_t* tb, const lh_newick_batch_t* nb, const double* rates,
+               double* loglik, lh_outputs_t* o) {
   f->want_tables = o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
                          o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers);
   f->want_rate_ll = o && o->site_rate_loglik;
@@ -1323,9 +1612,34 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
     cudaEventRecord(e, st_);
     dev_marks.emplace_back(what, e);
   };
-  if (check_batch(f, tb)) return 1;
+  f->newick_mode = nb != nullptr;
+  f->bad_plan_tree = -1;
+  f->n_seg_ev = 0;
+  int B, R;
+  const double *er, *pi;
+  if (nb) {
+    B = nb->n_trees;
+    R = nb->n_rates;
+    er = nb->er;
+    pi = nb->pi;
+    if (B < 0) return fail("negative batch size");
+    if (R < 1 || R > LH_MAX_RATES) return fail("n_rates %d outside 1..%d", R, LH_MAX_RATES);
+    for (int t = 0; t < B; ++t)
+      for (int i = 0; i < 4; ++i)
+        if (!(pi[4 * t + i] > 0.0)) return fail("tree %d: pi[%d] must be positive", t, i);
+    // which trees run on site patterns is found by the parser; until then every tree may
+    f->on_patterns.clear();
+    f->n_pattern_trees = (f->opt_site_patterns && f->cols[1].n_cols < f->cols[0].n_cols) ? B : 0;
+  } else {
+    if (check_batch(f, tb)) return 1;
+    B = tb->n_trees;
+    R = tb->n_rates;
+    er = tb->er;
+    pi = tb->pi;
+    rates = tb->rates;
+  }
   mark("check");
-  if (configure_batch(f, tb->n_trees, tb->n_rates)) return 1;
+  if (configure_batch(f, B, R)) return 1;
   if (f->B == 0) return 0;
   f->tm.ms_setup = since();
   mark("configure");
@@ -1337,7 +1651,7 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   LH_CUDA(cudaEventRecord(f->ev[7], f->stream));
   LH_CUDA(cudaStreamWaitEvent(cs, f->ev[7], 0));
   if (f->opt_timing) cudaEventRecord(f->ev[0], cs);
-  if (stage_params(f, tb, cs) || stage_flags(f, cs)) return 1;
+  if (stage_params(f, er, pi, rates, cs) || stage_flags(f, cs)) return 1;
   dmark("cs start", cs);
   if (stage_lists(f, chunk_starts(f, true), cs)) return 1;
   mark("params+lists");
@@ -1347,8 +1661,13 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   if (f->dev_plan) LH_CUDA(cudaStreamWaitEvent(f->plan_stream, f->ev[7], 0));
   const std::vector<int>& st = f->starts;
   for (int ci = 0, k = 0; ci < f->n_chunks; ++ci) {
-    for (int t0 = st[ci]; t0 < st[ci + 1]; t0 += f->seg, ++k)
-      if (stage_segment(f, tb, t0, std::min(f->seg, st[ci + 1] - t0), k % lh_family::kRing, cs)) return 1;
+    const int c0 = st[ci], cn = st[ci + 1] - st[ci];
+    if (nb) {
+      if (stage_text_chunk(f, nb, c0, cn, &k, cs)) return 1;
+    } else {
+      for (int t0 = c0; t0 < st[ci + 1]; t0 += f->seg, ++k)
+        if (stage_segment(f, tb, t0, std::min(f->seg, st[ci + 1] - t0), k % lh_family::kRing, cs)) return 1;
+    }
     mark("chunk staged");
     dmark("cs chunk copied", cs);
     LH_CUDA(cudaEventRecord(f->staged_ev[ci], cs));
@@ -1357,8 +1676,14 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
       // the chunk before is still in its kernels (in the space k_prune's last CTAs, k_edge and k_hmm leave)
       cudaEvent_t* pev = f->chunk_ev.data() + (size_t)kChunkEvents * ci + 7;
       LH_CUDA(cudaStreamWaitEvent(f->plan_stream, f->staged_ev[ci], 0));
+      if (nb) {
+        // (the chunk's k_newick launches are already queued on the plan stream)
+        lhb::launch_split(f->pc[1].n_cols ? f->d_on_pat.as<uint8_t>() : nullptr, c0, cn, f->d_list.as<int32_t>(),
+                          f->d_chunk_npat.as<int32_t>() + ci, f->plan_stream);
+        f->tm.kernel_launches += 1;
+      }
       LH_CUDA(cudaEventRecord(pev[0], f->plan_stream));
-      launch_plan_trees(f, st[ci], st[ci + 1] - st[ci], f->plan_stream);
+      launch_plan_trees(f, c0, cn, f->plan_stream);
       f->tm.kernel_launches += 1;
       LH_CUDA(cudaEventRecord(pev[1], f->plan_stream));
       LH_CUDA(cudaStreamWaitEvent(f->stream, pev[1], 0));
@@ -1367,7 +1692,7 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
     }
     if (ci == 0 && f->opt_timing) cudaEventRecord(f->ev[2], f->stream);
     dmark("compute chunk start", f->stream);
-    launch_chunk(f, ci, st[ci], st[ci + 1] - st[ci]);
+    launch_chunk(f, ci, c0, cn);
     dmark("compute chunk end", f->stream);
     mark("chunk launched");
   }
@@ -1388,6 +1713,160 @@ int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh
   for (auto& m : dev_marks) cudaEventDestroy(m.second);
   f->tm.ms_call = since();
   return rc;
+}
+
+// Copies row `src` of a [n][row] result of the host-parsed trees into row `dst` of the caller's array.
+template <class T>
+void put_row(T* dst_base, const std::vector<T>& src_base, size_t row, int dst, int src) {
+  if (dst_base && row) std::memcpy(dst_base + (size_t)dst * row, src_base.data() + (size_t)src * row, row * sizeof(T));
+}
+
+}  // namespace
+
+extern "C" {
+
+int lh_score_batch(lh_family_t* f, const lh_tree_batch_t* tb, double* loglik, lh_outputs_t* o) {
+  if (!f || !tb || !loglik) return fail("null argument");
+  if (!f->bound) return fail("no family bound to the handle (the last lh_family_rebind failed)");
+  return score_call(f, tb, nullptr, nullptr, loglik, o);
+}
+
+int lh_score_newick(lh_family_t* f, const lh_newick_batch_t* nb, double* loglik, lh_outputs_t* o) {
+  if (!f || !nb || !loglik) return fail("null argument");
+  if (!f->bound) return fail("no family bound to the handle (the last lh_family_rebind failed)");
+  if (!f->labels_set) return fail("lh_score_newick needs the family's row labels (lh_family_set_labels)");
+  const int B = nb->n_trees, R = nb->n_rates, T = f->fd.T;
+  if (B > 0 && (!nb->newick || !nb->er || !nb->pi || (!nb->rates && !nb->alpha))) return fail("null argument");
+  for (int t = 0; t < B; ++t)
+    if (!nb->newick[t]) return fail("tree %d: null string", t);
+  // category rates: given, or from alpha on the handle's host threads (the same doubles as
+  // pll_compute_gamma_cats, host/gamma.cpp)
+  std::vector<double> rates_buf;
+  const double* rates = nb->rates;
+  if (!rates && B > 0) {
+    if (R < 1 || R > LH_MAX_RATES) return fail("n_rates %d outside 1..%d", R, LH_MAX_RATES);
+    rates_buf.resize((size_t)B * R);
+    ensure_pool(f);
+    std::atomic<int> bad(-1);
+    std::vector<std::string> msgs((size_t)f->pool->workers() + 1);
+    f->pool->run((B + 63) / 64, [&](int task, int w) {
+      const int lo = task * 64, n = std::min(B, lo + 64) - lo;
+      if (lhh_gamma_cats_batch(n, nb->alpha + lo, R, rates_buf.data() + (size_t)lo * R)) {
+        bad.store(lo);
+        msgs[w] = lhh_last_error();
+      }
+    });
+    if (bad.load() >= 0) {
+      for (auto& m : msgs)
+        if (!m.empty()) return fail("%s (trees %d..)", m.c_str(), bad.load());
+      return fail("Gamma category rates failed");
+    }
+    rates = rates_buf.data();
+  }
+  int rc = score_call(f, nullptr, nb, rates, loglik, o);
+  f->newick_mode = false;
+  if (B == 0) return rc;
+  const lh_timings_t tm_main = f->tm;
+  auto host_parse_message = [&](int t) {
+    std::vector<int32_t> ch((size_t)(T - 2) * 2);
+    std::vector<double> bl((size_t)(T - 2) * 2);
+    int32_t rch;
+    double rbl;
+    if (lhh_newick_to_ops(T, f->label_ptrs.data(), 1, nb->newick + t, 1, ch.data(), bl.data(), &rch, &rbl)) {
+      std::string m = lhh_last_error();
+      const std::string pre = "tree 0: ";  // the host parser numbers the trees of its own call
+      if (m.compare(0, pre.size(), pre) == 0) m = m.substr(pre.size());
+      return m;
+    }
+    return std::string();
+  };
+  if (rc) {
+    // k_plan refused a tree k_newick had passed (a label twice): the host parser words the error
+    if (f->bad_plan_tree >= 0) {
+      const std::string m = host_parse_message(f->bad_plan_tree);
+      if (!m.empty()) return fail("tree %d: %s", f->bad_plan_tree, m.c_str());
+    }
+    return rc;
+  }
+  // trees the device parser left to the host: parse them there (its errors are the call's errors) and
+  // score them through the array path; their results replace the stand-ins'
+  const uint8_t* status = f->h_nw_status.as<uint8_t>();
+  std::vector<int> todo;
+  for (int t = 0; t < B; ++t)
+    if (status[t]) todo.push_back(t);
+  if (todo.empty()) return 0;
+  const int n = (int)todo.size();
+  const size_t per = (size_t)(T - 2) * 2;
+  std::vector<const char*> strs(n);
+  for (int i = 0; i < n; ++i) strs[i] = nb->newick[todo[i]];
+  std::vector<int32_t> ch(n * per), rch(n);
+  std::vector<double> bl(n * per), rbl(n), er(6 * (size_t)n), pi(4 * (size_t)n), rt((size_t)n * R), ll(n);
+  if (lhh_newick_to_ops(T, f->label_ptrs.data(), n, strs.data(), f->opt_threads, ch.data(), bl.data(), rch.data(), rbl.data())) {
+    // report the first bad tree of the batch with its own message
+    for (int i = 0; i < n; ++i) {
+      const std::string m = host_parse_message(todo[i]);
+      if (!m.empty()) return fail("tree %d: %s", todo[i], m.c_str());
+    }
+    return fail("%s", lhh_last_error());
+  }
+  for (int i = 0; i < n; ++i) {
+    std::memcpy(&er[6 * (size_t)i], nb->er + 6 * (size_t)todo[i], 6 * sizeof(double));
+    std::memcpy(&pi[4 * (size_t)i], nb->pi + 4 * (size_t)todo[i], 4 * sizeof(double));
+    std::memcpy(&rt[(size_t)R * i], rates + (size_t)R * todo[i], R * sizeof(double));
+  }
+  lh_tree_batch_t tb{n, R, ch.data(), bl.data(), rch.data(), rbl.data(), er.data(), pi.data(), rt.data()};
+  const lhb::FamilyDev& fd = f->fd;
+  const size_t S = fd.S, vd_n = (size_t)fd.vd_sites * fd.vd_states, dj_n = (size_t)fd.dj_sites * fd.dj_states;
+  std::vector<double> xe, fv, fvd, fdg, fdj, fj, rll;
+  std::vector<int32_t> gs, vds, djs;
+  lh_outputs_t o2{};
+  if (o) {
+    auto want = [&](auto* dst, auto& buf, size_t row) -> decltype(dst) {
+      if (!dst || !row) return nullptr;
+      buf.resize((size_t)n * row);
+      return buf.data();
+    };
+    o2.xmsa_emission = want(o->xmsa_emission, xe, S);
+    o2.vgerm_forward = want(o->vgerm_forward, fv, fd.n_v);
+    o2.vd_forward = want(o->vd_forward, fvd, vd_n);
+    o2.dgerm_forward = want(o->dgerm_forward, fdg, fd.n_d);
+    o2.dj_forward = want(o->dj_forward, fdj, dj_n);
+    o2.jgerm_forward = want(o->jgerm_forward, fj, fd.n_j);
+    o2.germ_scalers = want(o->germ_scalers, gs, 3);
+    o2.vd_scalers = want(o->vd_scalers, vds, fd.vd_sites);
+    o2.dj_scalers = want(o->dj_scalers, djs, fd.dj_sites);
+    o2.site_rate_loglik = want(o->site_rate_loglik, rll, (size_t)R * S);
+  }
+  rc = score_call(f, &tb, nullptr, nullptr, ll.data(), o ? &o2 : nullptr);
+  if (rc) {
+    // (an error of the array path names a tree of the small batch)
+    return fail("among the %d trees left to the host parser (first: tree %d): %s", n, todo[0], std::string(g_err).c_str());
+  }
+  for (int i = 0; i < n; ++i) {
+    const int t = todo[i];
+    loglik[t] = ll[i];
+    if (!o) continue;
+    put_row(o->xmsa_emission, xe, o2.xmsa_emission ? S : 0, t, i);
+    put_row(o->vgerm_forward, fv, o2.vgerm_forward ? (size_t)fd.n_v : 0, t, i);
+    put_row(o->vd_forward, fvd, o2.vd_forward ? vd_n : 0, t, i);
+    put_row(o->dgerm_forward, fdg, o2.dgerm_forward ? (size_t)fd.n_d : 0, t, i);
+    put_row(o->dj_forward, fdj, o2.dj_forward ? dj_n : 0, t, i);
+    put_row(o->jgerm_forward, fj, o2.jgerm_forward ? (size_t)fd.n_j : 0, t, i);
+    put_row(o->germ_scalers, gs, o2.germ_scalers ? (size_t)3 : 0, t, i);
+    put_row(o->vd_scalers, vds, o2.vd_scalers ? (size_t)fd.vd_sites : 0, t, i);
+    put_row(o->dj_scalers, djs, o2.dj_scalers ? (size_t)fd.dj_sites : 0, t, i);
+    put_row(o->site_rate_loglik, rll, o2.site_rate_loglik ? (size_t)R * S : 0, t, i);
+  }
+  // the timings the caller reads are those of the main pass
+  const int64_t h2d = f->tm.h2d_bytes, d2h = f->tm.d2h_bytes;
+  const int launches = f->tm.kernel_launches;
+  f->tm = tm_main;
+  f->tm.h2d_bytes += h2d;
+  f->tm.d2h_bytes += d2h;
+  f->tm.kernel_launches += launches;
+  f->tm.newick_host_trees = n;
+  f->run_recorded = false;  // (the chunk events now belong to the small batch)
+  return 0;
 }
 
 int lh_measure_fp64_peak(int device, double* tflops) {
@@ -1430,6 +1909,49 @@ int lh_debug_fetch_plan(lh_family_t* f, int32_t* steps, double* pblen) {
   const size_t T = f->fd.T;
   LH_CUDA(cudaMemcpy(steps, f->d_plan.p, (size_t)f->B * (T - 1) * sizeof(lhb::Step), cudaMemcpyDeviceToHost));
   LH_CUDA(cudaMemcpy(pblen, f->d_pblen.p, (size_t)f->B * (2 * T - 3) * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// Test hook: runs only the device parser over the batch's strings and returns what it wrote.
+int lh_debug_parse_newick(lh_family_t* f, const lh_newick_batch_t* nb, int32_t* children, double* blen,
+                          int32_t* root_child, double* root_blen, uint8_t* on_patterns, uint8_t* left_to_host, float* ms_kernel) {
+  if (!f || !nb || !children || !blen || !root_child || !root_blen || !left_to_host) return fail("null argument");
+  if (!f->bound || !f->labels_set) return fail("needs a bound family with labels (lh_family_set_labels)");
+  LH_CUDA(cudaSetDevice(f->device));
+  const int B = nb->n_trees;
+  if (B <= 0) return 0;
+  f->newick_mode = true;
+  f->n_seg_ev = 0;
+  f->on_patterns.clear();
+  f->n_pattern_trees = 0;
+  const int rc = configure_batch(f, B, 1);
+  f->window_set = true;  // (no pruning follows: no probe)
+  if (rc) {
+    f->newick_mode = false;
+    return 1;
+  }
+  int k = 0;
+  const int rc2 = stage_text_chunk(f, nb, 0, B, &k, f->copy_stream);
+  f->newick_mode = false;
+  if (rc2) return 1;
+  LH_CUDA(cudaStreamSynchronize(f->plan_stream));
+  for (auto& b : f->ring_busy) b = false;
+  const size_t n2 = (size_t)B * (f->fd.T - 2) * 2;
+  LH_CUDA(cudaMemcpy(children, f->d_rchildren.p, n2 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  LH_CUDA(cudaMemcpy(blen, f->d_rblen.p, n2 * sizeof(double), cudaMemcpyDeviceToHost));
+  LH_CUDA(cudaMemcpy(root_child, f->d_rroot_child.p, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  LH_CUDA(cudaMemcpy(root_blen, f->d_rroot_blen.p, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost));
+  if (on_patterns) LH_CUDA(cudaMemcpy(on_patterns, f->d_on_pat.p, (size_t)B, cudaMemcpyDeviceToHost));
+  LH_CUDA(cudaMemcpy(left_to_host, f->d_nw_status.p, (size_t)B, cudaMemcpyDeviceToHost));
+  if (ms_kernel) {
+    *ms_kernel = 0.f;
+    for (int i = 0; i + 1 < f->n_seg_ev; i += 2) {
+      float x = 0.f;
+      cudaEventElapsedTime(&x, f->seg_ev[i], f->seg_ev[i + 1]);
+      *ms_kernel += x;
+    }
+  }
+  f->B = 0;  // no batch is resident
   return 0;
 }
 

@@ -7,6 +7,7 @@
 #include <memory>
 #include <string>
 
+#include "../decimal.hpp"
 #include "../plan.hpp"
 #include "host_error.hpp"
 
@@ -42,6 +43,20 @@ int lhh_plan_trees(int32_t T, int32_t B, const int32_t* children, const double* 
     if (s > mx) mx = s;
   }
   *max_slots = mx;
+  return 0;
+}
+
+// Test hook for the decimal conversion the device Newick parser uses (decimal.hpp, compiled for the
+// host here): n NUL-terminated strings laid end to end in buf.
+int lhh_parse_decimal_buf(const char* buf, int32_t n, double* out, int32_t* status, int32_t* consumed) {
+  const char* p = buf;
+  for (int i = 0; i < n; ++i) {
+    const char* q = p;
+    out[i] = 0.0;
+    status[i] = lhb::parse_decimal([&]() { return (int)(unsigned char)*q; }, [&]() { ++q; }, &out[i]);
+    consumed[i] = (int32_t)(q - p);
+    p += std::strlen(p) + 1;
+  }
   return 0;
 }
 

@@ -263,3 +263,90 @@ extern "C" int lhh_newick_to_ops(int32_t n_tips, const char* const* labels, int3
   }
   return 0;
 }
+
+// The inverse, for workloads and tests: the trees of a flat batch written as RevBayes writes them
+// ("[&index=N]" comments, shortest round-trip branch lengths). Tree t goes to out + t * stride,
+// NUL-terminated; flattening the strings again gives the same arrays when the batch's operations are in
+// listed (post-)order. Returns 1 when `stride` is too small for some tree.
+extern "C" int lhh_ops_to_newick(int32_t n_tips, const char* const* labels, int32_t n_trees, const int32_t* children,
+                                 const double* blen, const int32_t* root_child, const double* root_blen,
+                                 int32_t n_threads, char* out, int64_t stride) {
+  using namespace lhb;
+  const int T = n_tips, n_ops = T - 2;
+  if (T < 3) return host_fail("need at least 3 tips (got %d)", T);
+  int nt = n_threads > 0 ? n_threads : (int)std::thread::hardware_concurrency();
+  nt = std::max(1, std::min(nt, std::min(64, (n_trees + 15) / 16)));
+  std::atomic<int> bad(-1);
+  auto work = [&](int tid) {
+    // iterative expansion with an explicit stack of (node, next child) frames
+    struct Frame { int32_t node; int8_t next; };
+    std::vector<Frame> stack;
+    for (int t = tid; t < n_trees; t += nt) {
+      const int32_t* ch = children + (size_t)t * n_ops * 2;
+      const double* bl = blen + (size_t)t * n_ops * 2;
+      char* const base = out + (size_t)t * stride;
+      char* p = base;
+      char* const end = base + stride - 64;  // room for one more token
+      int counter = 0;
+      bool ok = true;
+      auto put_len = [&](double v) {
+        p += std::snprintf(p, 32, "[&index=%d]:", ++counter);
+        p = std::to_chars(p, p + 32, v).ptr;
+      };
+      // node -> text, children in listed order
+      auto emit = [&](int32_t root) {
+        stack.clear();
+        stack.push_back({root, 0});
+        while (!stack.empty() && ok) {
+          Frame& f = stack.back();
+          if (p >= end) { ok = false; break; }
+          if (f.node < T) {
+            const char* l = labels[f.node];
+            const size_t n = std::strlen(l);
+            if (p + n >= end) { ok = false; break; }
+            std::memcpy(p, l, n);
+            p += n;
+            stack.pop_back();
+            continue;
+          }
+          const int op = f.node - T;
+          if (f.next == 0) {
+            *p++ = '(';
+            f.next = 1;
+            stack.push_back({ch[2 * op], 0});
+          } else if (f.next == 1) {
+            put_len(bl[2 * op]);
+            *p++ = ',';
+            f.next = 2;
+            stack.push_back({ch[2 * op + 1], 0});
+          } else {
+            put_len(bl[2 * op + 1]);
+            *p++ = ')';
+            stack.pop_back();
+          }
+        }
+      };
+      *p++ = '(';
+      emit(root_child[t]);
+      if (ok) { put_len(root_blen[t]); *p++ = ','; emit(ch[2 * (n_ops - 1)]); }
+      if (ok) { put_len(bl[2 * (n_ops - 1)]); *p++ = ','; emit(ch[2 * (n_ops - 1) + 1]); }
+      if (ok) {
+        put_len(bl[2 * (n_ops - 1) + 1]);
+        p += std::snprintf(p, 32, ")[&index=%d];", ++counter);
+        *p = '\0';
+      } else {
+        bad.store(t);
+        return;
+      }
+    }
+  };
+  if (nt == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int i = 0; i < nt; ++i) th.emplace_back(work, i);
+    for (auto& t : th) t.join();
+  }
+  if (bad.load() >= 0) return host_fail("tree %d does not fit %lld bytes", bad.load(), (long long)stride);
+  return 0;
+}

@@ -288,6 +288,9 @@ void PhyloHMM::EnsureDeviceFamily() {
   if (dev_family_) return;
   if (lh_family_create(&dev_family_, &flat_->desc, device_)) throw std::runtime_error(lh_last_error());
   if (host_threads_ > 0 && lh_set_option(dev_family_, "host_threads", host_threads_)) throw std::runtime_error(lh_last_error());
+  // the xMSA row labels, for the device Newick parser (Partition::SetTipStates matches tips by label,
+  // lib/libptpll/src/pll_partition.cpp:153-194)
+  if (lh_family_set_labels(dev_family_, flat_->label_ptrs.data())) throw std::runtime_error(lh_last_error());
 }
 
 void PhyloHMM::set_host_threads(int n) {
@@ -379,94 +382,27 @@ std::vector<double> PhyloHMM::ScoreSamples(const std::vector<std::string>& newic
   return ll;
 }
 
-// Newick ingest (host threads) of one chunk of samples overlaps the scoring of the previous chunk
-// (lh_score_batch: planner threads, copies, kernels).
+// The loop body src/PhyloHMM.cpp:419-430 for B rows of the RevBayes trace in one device call: the Newick
+// strings go to the GPU as text and are parsed there (k_newick), the discrete-Gamma rates are computed on
+// the handle's host threads (bit-identical to pll_compute_gamma_cats), planning, pruning and the forward
+// pass follow chunk by chunk while later strings are still being copied.
 void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er, const double* pi, const double* alpha,
                             int num_rates, double* loglik) {
   EnsureDeviceFamily();
   if (B <= 0) return;
-  const int T = xmsa_.rows();
-  const std::size_t per = (std::size_t)2 * (T - 2);
-  constexpr int kChunk = 1024, kBuffers = 3;
-  struct Flat {
-    std::vector<int32_t> children, root_child;
-    std::vector<double> blen, root_blen, rates;
-    int b0 = 0, n = 0;
-    std::string err;
-  } flat[kBuffers];
-  auto ingest = [&](Flat& f) {
-    const int n = f.n;
-    f.children.resize(n * per);
-    f.blen.resize(n * per);
-    f.root_child.resize(n);
-    f.root_blen.resize(n);
-    f.rates.resize((std::size_t)n * num_rates);
-    f.err.clear();
-    if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), n, newicks + f.b0, host_threads_, f.children.data(), f.blen.data(),
-                          f.root_child.data(), f.root_blen.data()) ||
-        lhh_gamma_cats_batch(n, alpha + f.b0, num_rates, f.rates.data()))
-      f.err = lhh_last_error();
-  };
-  // The ingest thread runs ahead of the device by up to kBuffers - 1 chunks; a short opening chunk gets the
-  // device started early.
-  std::mutex m;
-  std::condition_variable cv;
-  int produced = 0, consumed = 0;
-  bool stop = false;
-  std::thread producer([&] {
-    for (int b0 = 0, c = 0; b0 < B; ++c) {
-      {
-        std::unique_lock<std::mutex> lk(m);
-        cv.wait(lk, [&] { return stop || c - consumed < kBuffers; });
-        if (stop) return;
-      }
-      Flat& f = flat[c % kBuffers];
-      f.b0 = b0;
-      f.n = std::min(B - b0, c == 0 ? kChunk / 4 : kChunk);
-      ingest(f);
-      b0 += f.n;
-      const bool failed = !f.err.empty();
-      {
-        std::lock_guard<std::mutex> lk(m);
-        ++produced;
-      }
-      cv.notify_all();
-      if (failed) return;
-    }
-  });
-  std::string err;
-  bool device_failed = false;
-  for (int done = 0, c = 0; done < B; ++c) {
-    {
-      std::unique_lock<std::mutex> lk(m);
-      cv.wait(lk, [&] { return produced > c; });
-    }
-    Flat& f = flat[c % kBuffers];
-    if (!f.err.empty()) {
-      err = f.err;
-      break;
-    }
-    lh_tree_batch_t tb{f.n, num_rates, f.children.data(), f.blen.data(), f.root_child.data(), f.root_blen.data(),
-                       er + (std::size_t)6 * f.b0, pi + (std::size_t)4 * f.b0, f.rates.data()};
-    if (lh_score_batch(dev_family_, &tb, loglik + f.b0, nullptr)) {
-      device_failed = true;
-      break;
-    }
-    done += f.n;
-    {
-      std::lock_guard<std::mutex> lk(m);
-      ++consumed;
-    }
-    cv.notify_all();
+  lh_newick_batch_t nb{};
+  nb.n_trees = B;
+  nb.n_rates = num_rates;
+  nb.newick = newicks;
+  nb.er = er;
+  nb.pi = pi;
+  nb.alpha = alpha;
+  if (lh_score_newick(dev_family_, &nb, loglik, nullptr)) {
+    const std::string msg = lh_last_error();
+    // what the reference's parser / SetTipStates would refuse is the caller's mistake, the rest the device's
+    if (msg.rfind("tree ", 0) == 0 || msg.find("alpha") != std::string::npos) throw std::invalid_argument(msg);
+    throw std::runtime_error(msg);
   }
-  {
-    std::lock_guard<std::mutex> lk(m);
-    stop = true;
-  }
-  cv.notify_all();
-  producer.join();
-  if (device_failed) throw std::runtime_error(lh_last_error());
-  if (!err.empty()) throw std::invalid_argument(err);
 }
 
 // src/PhyloHMM.cpp:244-282

@@ -442,6 +442,17 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
   // work item = (tree, tile, category): the categories of a tile are independent until k_edge sums
   // them, and items this fine keep the last wave of a small batch full
   const int per_tree = cfg.n_tiles * R;
+  // text input: the chunk's list holds the pattern trees first; how many was decided on the device
+  const int32_t* tree_list = cfg.tree_list;
+  if (cfg.dyn_n_pat) {
+    const int n_pat = __ldg(cfg.dyn_n_pat);
+    if (cfg.defer_naive) {
+      ntrees = n_pat;
+    } else {
+      ntrees = cfg.dyn_total - n_pat;
+      tree_list += n_pat;
+    }
+  }
   const int n_work = ntrees * per_tree;
   for (int w = blockIdx.x; w < n_work;) {
     // claim the next item now; the answer is needed when this one is done
@@ -449,7 +460,7 @@ __global__ void __launch_bounds__(32, (NS == 4 ? LH_PRUNE_MIN_CTAS : NS == 3 ? L
     if (lane == 0) w_next = (int)gridDim.x + atomicAdd(cfg.work_counter, 1);
     const int li = w / per_tree, rem = w - li * per_tree;
     const int tile = rem / R, k = rem - tile * R;
-    const int t = __ldg(cfg.tree_list + li);
+    const int t = __ldg(tree_list + li);
     const int lt = t - tree0;
     const int4* __restrict__ plan = b.plan + (size_t)t * (T - 1);
     const unsigned* __restrict__ my_codes = cfg.codes_t + (size_t)tile * 32 + lane;

@@ -77,6 +77,11 @@ struct PruneCfg {
   // a CTA that starts late - the forward pass of the previous chunk may still hold part of an SM -
   // simply takes fewer items.
   int32_t* work_counter;
+  // Newick input: which trees of the chunk run on patterns is decided on the device (k_newick, k_split).
+  // tree_list then is the chunk's whole list (pattern trees first) and *dyn_n_pat how many of its
+  // dyn_total trees are pattern trees; the launch with defer_naive takes those, the other one the rest.
+  const int32_t* dyn_n_pat;
+  int32_t dyn_total;
   // per (chunk tree, category, column) inputs of the edge term, written by k_prune:
   double* ebuf;          // tree at e_stride doubles: [R][8][cols_pad] message across the root edge [4], root CLV [4]
   int32_t* ecnt;         // tree at c_stride ints:    [R][cols_pad] scaler count of the two
@@ -115,6 +120,36 @@ struct PlanDev {
   int32_t* flags;              // [0] min tree with a negative branch length, [1] min malformed tree
                                // (both INT_MAX when none), [2] deepest CLV stack met
 };
+// k_newick (newick_dev.cu): Newick text -> the operation arrays k_plan consumes, one thread per tree.
+// Tip labels are found through an open-addressing table on the FNV-1a hash of the label:
+//   slot = { first 8 label bytes (little-endian, zero-padded) lo, hi; hash; length | row << 16 },
+//   length | row << 16 == 0xffffffff marks an empty slot; labels longer than 8 bytes are compared
+//   against chars + long_off[row] as well.
+struct LabelTableDev {
+  const uint4* slots;
+  uint32_t mask;               // slot count - 1 (power of two)
+  const uint32_t* long_off;    // [T] offset of each label's bytes in chars
+  const char* chars;
+};
+struct NewickDev {
+  int32_t T;
+  int32_t tree0, n;            // batch index of the segment's first tree, trees in the segment
+  const char* text;            // the segment's strings, each NUL-terminated and starting on a 16-byte boundary
+  const uint32_t* offs;        // [n] start of each string in text
+  LabelTableDev labels;
+  int32_t* children;           // [B][T-2][2]   (batch arrays, as in PlanDev)
+  double* blen;                // [B][T-2][2]
+  int32_t* root_child;         // [B]
+  double* root_blen;           // [B]
+  uint8_t* on_pat;             // [B] 1: the naive tip (row 0) is on the root edge or under the virtual root
+  uint8_t* status;             // [B] 0 parsed; 1 left to the host parser (malformed, or a spelling / number
+                               //     this parser does not decide) - the tree then gets a harmless stand-in
+};
+void launch_newick(const NewickDev& p, cudaStream_t s);
+// stable partition of the chunk's trees [t0, t0+n) by on_pat into list[t0..) (pattern trees first);
+// n_pat_out[0] = how many
+void launch_split(const uint8_t* on_pat, int t0, int n, int32_t* list, int32_t* n_pat_out, cudaStream_t s);
+
 // Raises a kernel's dynamic shared-memory limit to at least `bytes`; the limit only ever grows, so
 // handles that launch the same kernel with different sizes from different host threads do not race.
 void ensure_dynamic_smem(const void* kernel, size_t bytes);

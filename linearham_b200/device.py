@@ -84,6 +84,40 @@ class Family:
         self._ck(lib().lh_score_batch(self._h, C.byref(t), ll.ctypes.data_as(_f64p), None))
         return ll
 
+    # Newick text in ------------------------------------------------------------
+    def set_labels(self, labels):
+        """xMSA row labels (row 0 = "naive") for the device Newick parser (lh_family_set_labels)."""
+        arr = (C.c_char_p * len(labels))(*[str(s).encode() for s in labels])
+        self._ck(lib().lh_family_set_labels(self._h, arr))
+
+    def score_newick(self, newicks, er, pi, n_rates, alpha=None, rates=None, outputs=False, lengths=False):
+        """Newick strings in, host results out (lh_score_newick)."""
+        nb, keep = _abi.newick_batch(newicks, er, pi, n_rates, alpha=alpha, rates=rates, lengths=lengths)
+        ll = np.zeros(nb.n_trees)
+        if outputs:
+            o, arrs = _abi.alloc_outputs(self.fam, nb.n_trees, None if outputs is True else outputs, n_rates=n_rates)
+            self._ck(lib().lh_score_newick(self._h, C.byref(nb), ll.ctypes.data_as(_f64p), C.byref(o)))
+            return ll, arrs
+        self._ck(lib().lh_score_newick(self._h, C.byref(nb), ll.ctypes.data_as(_f64p), None))
+        return ll
+
+    def parse_newick(self, newicks):
+        """Only the device parser (lh_debug_parse_newick) -> dict of the operation arrays + flags + kernel ms."""
+        B, T = len(newicks), int(self.fam["n_tips"])
+        z = np.zeros((B, 1))
+        nb, keep = _abi.newick_batch(newicks, np.zeros((B, 6)), np.ones((B, 4)), 1, rates=z)
+        out = {"children": np.zeros((B, T - 2, 2), dtype=np.int32), "blen": np.zeros((B, T - 2, 2)),
+               "root_child": np.zeros(B, dtype=np.int32), "root_blen": np.zeros(B),
+               "on_patterns": np.zeros(B, dtype=np.uint8), "left_to_host": np.zeros(B, dtype=np.uint8)}
+        ms = C.c_float()
+        i32p, u8p = C.POINTER(C.c_int32), C.POINTER(C.c_uint8)
+        self._ck(lib().lh_debug_parse_newick(
+            self._h, C.byref(nb), out["children"].ctypes.data_as(i32p), out["blen"].ctypes.data_as(_f64p),
+            out["root_child"].ctypes.data_as(i32p), out["root_blen"].ctypes.data_as(_f64p),
+            out["on_patterns"].ctypes.data_as(u8p), out["left_to_host"].ctypes.data_as(u8p), C.byref(ms)))
+        out["ms_kernel"] = ms.value
+        return out
+
     # split form --------------------------------------------------------------
     def upload(self, tb):
         t, keep = _abi.tree_batch(tb)

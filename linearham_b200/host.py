@@ -54,6 +54,39 @@ def newick_to_ops(newicks, labels, n_threads=0):
     return {"children": children, "blen": blen, "root_child": root_child, "root_blen": root_blen}
 
 
+class NewickBuffer:
+    """The trees of a flat batch as Newick text in one buffer (lhh_ops_to_newick): .ptrs is the
+    (c_char_p * B) array the text entry points take, .lengths their strlen, [i] the i-th string."""
+
+    def __init__(self, tb, labels, n_threads=0):
+        T, B = len(labels), int(np.asarray(tb["root_child"]).shape[0])
+        lab = (C.c_char_p * T)(*[str(s).encode() for s in labels])
+        stride = (max(len(str(s)) for s in labels) + 48) * 2 * T + 128
+        stride = (stride + 63) // 64 * 64
+        self.buf = np.zeros(B * stride, dtype=np.uint8)
+        arrs = [np.ascontiguousarray(tb["children"], dtype=np.int32), np.ascontiguousarray(tb["blen"], dtype=np.float64),
+                np.ascontiguousarray(tb["root_child"], dtype=np.int32), np.ascontiguousarray(tb["root_blen"], dtype=np.float64)]
+        _ck(lib().lhh_ops_to_newick(T, lab, B, arrs[0].ctypes.data_as(_abi._i32p), arrs[1].ctypes.data_as(_abi._f64p),
+                                    arrs[2].ctypes.data_as(_abi._i32p), arrs[3].ctypes.data_as(_abi._f64p), int(n_threads),
+                                    self.buf.ctypes.data, stride))
+        base = self.buf.ctypes.data
+        self.n, self.stride = B, stride
+        self.ptrs = (C.c_char_p * max(B, 1))()
+        addr = C.cast(self.ptrs, C.POINTER(C.c_void_p))
+        for i in range(B):
+            addr[i] = base + i * stride
+        self.lengths = (self.buf.reshape(B, stride) == 0).argmax(axis=1).astype(np.int64) if B else np.zeros(0, dtype=np.int64)
+
+    def __len__(self):
+        return self.n
+
+    def __getitem__(self, i):
+        return self.ptrs[i].decode()
+
+    def total_bytes(self):
+        return int(self.lengths.sum())
+
+
 def tree_batch(newicks, labels, er, pi, alpha, n_rates, n_threads=0):
     """Everything lh_score_batch needs for B samples given as the RevBayes TSV gives them
     (src/PhyloHMM.cpp:414-426): Newick, er[6], pi[4], alpha."""
