@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py - PhyloHMM tree-likelihood evaluations per second (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config c4|c3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config c4|c3|c2|c5]
 
 A step is one pass of the hot path over one batch of synthetic tree samples of a fixed clonal
 family: for every (tree, er, pi, alpha) sample, Felsenstein pruning over the xMSA + the scaled HMM
@@ -9,14 +9,24 @@ forward pass = one `InitializePhyloEmission() + LogLikelihood()` of the referenc
 (src/PhyloHMM.cpp:429-430). Default workload = BASELINE.json configs[3] ("c4": synthetic 1000-leaf
 IGH family, 400 nt, Gamma-4, batch 16384 trees sharded over the N GPUs).
 
-  value     trees/s, kernels only, batch already resident in HBM (lh_batch_upload once, then
-            lh_batch_run per step); CUDA events on the library's stream, max over ranks
-  e2e       trees/s through lh_score_batch with HOST buffers: host traversal planning, H2D from
-            pinned staging, kernels, D2H of the log-likelihoods, all inside the timed region
-  roofline  k_prune: algorithmic bytes / measured launch time vs measured HBM peak
-  cpu_baseline  the reference's own C++ (oracle/_ref) on all host cores, bounded sample (N=1 only)
+  value       trees/s, kernels only, batch already resident in HBM (lh_batch_upload once, then
+              lh_batch_run per step); CUDA events on the library's stream, max over ranks
+  e2e         trees/s through the class API a linearham user calls, PhyloHMM::ScoreSamples: NEWICK STRINGS
+              + er/pi/alpha on the host in, log-likelihoods of the whole batch on rank 0's host out. The
+              text goes to the GPU and is parsed there (k_newick); H2D, Gamma rates (host threads), parse,
+              planning, kernels, D2H and - at N > 1 - the NCCL gather are all inside the timed region. This is
+              what the reference arm times (src/PhyloHMM.cpp:419-430: parse + Gamma + emission + forward).
+  e2e_arrays  the same through lh_score_batch with pre-flattened operation arrays and pre-computed rates
+              (round 1's `e2e`)
+  roofline    k_prune against the FP64 pipe (the binding roofline: inner CLVs never leave the chip), with the
+              streaming-model HBM figure and the measured DRAM traffic beside it
+  cpu_baseline  the reference's own C++ (oracle/_ref) on all host cores, bounded sample (N=1 only), plus a
+              single-thread figure and the reference "as shipped" (-O0, SConstruct:266)
+  c3, c5      the other single-box configurations, each with its own parity check (c5 = families sharded
+              over the ranks through lh_repertoire_score)
+  parity_vs_n1  (N > 1) rank 0 re-scores a slice of every rank's shard on its own GPU: bit-identical
 
---impl reference times the reference's CPU implementation alone (rank 0 only).
+--impl reference times the reference's CPU implementation alone (rank 0 only) and loads nothing of the product.
 """
 import argparse
 import json
@@ -136,19 +146,12 @@ class CpuPool:
                 p.kill()
 
 
-def cpu_arm_setup(cfg_name, cfg, ff, fam, tb, newicks, alpha, n_sample, workdir):
-    """Writes the worker data file; returns (kind, path)."""
-    from oracle import pyoracle as po
-    path = os.path.join(workdir, "cpu_sample.npz")
-    if po.have_ref():
-        np.savez(path, yaml_path=ff["yaml_path"], hmm_dir=ff["hmm_dir"], newicks=np.array(newicks[:n_sample]),
-                 er=tb["er"][:n_sample], pi=tb["pi"][:n_sample], alpha=alpha[:n_sample], R=cfg["R"])
-        return "reference", path
-    po.build_port()
-    data = {"fam_" + k: np.asarray(v) for k, v in fam.items()}
-    data.update({"tb_" + k: v[:n_sample] for k, v in tb.items()})
-    np.savez(path, **data)
-    return "port", path
+def cpu_sample_file(ff, R, newicks, er, pi, alpha, workdir, name="cpu_sample.npz"):
+    """The worker data file of the reference kind: the family's files + the samples as the RevBayes trace holds them."""
+    path = os.path.join(workdir, name)
+    np.savez(path, yaml_path=ff["yaml_path"], hmm_dir=ff["hmm_dir"], newicks=np.array(newicks), er=np.asarray(er),
+             pi=np.asarray(pi), alpha=np.asarray(alpha), R=R)
+    return path
 
 
 def cpu_sample_size(cfg_name, cores):
@@ -157,7 +160,382 @@ def cpu_sample_size(cfg_name, cores):
     return per_core * cores
 
 
-# ------------------------------------------------------------------------------ main ---
+def reference_samples(cfg, ff, n_topo):
+    """The first n_topo samples of the configuration exactly as workload.tree_batch draws them (same generator,
+    same seed) - Newick strings, er, pi, alpha - without touching the product library."""
+    from linearham_b200 import synth  # pure Python
+    rng = np.random.default_rng(cfg["tree_seed"])
+    samples = synth.tree_samples(rng, ff["tree"], n_topo, outgroup=cfg.get("outgroup"))
+    return ([s["newick"] for s in samples], np.array([s["er"] for s in samples]), np.array([s["pi"] for s in samples]),
+            np.array([s["alpha"] for s in samples]))
+
+
+def rel_err_finite(a, b):
+    ok = np.isfinite(b)
+    worst = float(np.max(np.abs(a[ok] - b[ok]) / np.abs(b[ok]))) if ok.any() else 0.0
+    return worst, bool(np.array_equal(np.isfinite(a), ok)), int(len(b) - ok.sum())
+
+
+# ---------------------------------------------------------------------- reference arm ---
+
+def reference_arm(args):
+    from linearham_b200 import workload  # configuration table + synthetic family files (Python only)
+    from oracle import pyoracle as po
+    cfg = dict(workload.CONFIGS[args.config])
+    cores = os.cpu_count() or 1
+    workdir = tempfile.mkdtemp(prefix="lhbench_ref_")
+    ff = workload.write_family_files(cfg, workdir)
+    B_total = args.batch or cfg["B"]
+    n_topo = min(args.topologies, B_total)
+    newicks, er, pi, alpha = reference_samples(cfg, ff, n_topo)
+    if not po.have_ref():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libref_linearham.so is missing (built by "
+                          "__graft_entry__.build() where /root/reference exists)"}))
+        return 0
+    ref = po.RefPhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+    fam = ref.family()
+    ref.close()
+    config = workload_config(args, cfg, fam, B_total)
+    n_step = max(cores, min(len(newicks), {"c4": 4, "c3": 64}.get(args.config, 16) * cores))
+    path = cpu_sample_file(ff, cfg["R"], newicks[:n_step], er[:n_step], pi[:n_step], alpha[:n_step], workdir)
+    pool = CpuPool("reference", path, cores)
+    for _ in range(args.warmup):
+        pool.score(0, n_step)
+    total = 0.0
+    for _ in range(args.steps):
+        w, _, stages = pool.score(0, n_step)
+        total += w
+    pool.close()
+    v = n_step * args.steps / total
+    sample = (f"{n_step} tree samples per step (the first {n_step} of the batch), {cores} worker processes, each the "
+              "reference's loop body src/PhyloHMM.cpp:419-430 (Newick parse + Gamma rates + emission + forward); "
+              "the std::regex of :420 is built once per worker, not once per row as the reference does")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+    return 0
+
+
+def workload_config(args, cfg, fam, B_total):
+    return {"workload": f"{args.config}: {cfg['desc']}", "n_tips": int(fam["n_tips"]), "xmsa_columns": int(fam["n_sites"]),
+            "gamma_categories": cfg["R"], "global_batch": B_total, "distinct_topologies": min(args.topologies, B_total),
+            "hmm": {"vd": [int(fam["vd_sites"]), int(fam["vd_states"])], "dj": [int(fam["dj_sites"]), int(fam["dj_states"])],
+                    "genes": [int(fam["n_v"]), int(fam["n_d"]), int(fam["n_j"])]},
+            "parallelism": f"trees sharded over {args.gpus} GPU(s), no data-path collective; "
+                           "NCCL all-gather of the per-tree log-likelihoods",
+            "l2": "inputs larger than L2"}
+
+
+# -------------------------------------------------------------------------- B200 arm ---
+
+class Env:
+    """Process-wide state of the B200 arm: ranks, device, the torch stream everything is ordered on."""
+
+    def __init__(self, args):
+        import torch
+        from linearham_b200 import device
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available() or device.device_count() < 1:
+            raise RuntimeError("bench.py needs a CUDA device: linearham_b200 has no CPU fallback")
+        self.dist = None
+        self.dev = self.local_rank if self.world > 1 else 0
+        torch.cuda.set_device(self.dev)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.dev))
+            self.dist = dist
+        self.cores = os.cpu_count() or 1
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", self.world))
+        # ranks of one node share its host cores: each takes its share for staging and planning
+        self.host_threads = max(2, self.cores // local_world) if self.world > 1 else self.cores
+        # a non-default torch stream: the library runs its kernels on it (option "stream") and the NCCL gather
+        # is queued behind them on the same stream
+        self.stream = torch.cuda.Stream(device=self.dev)
+
+    def sync_all(self):
+        self.torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, values):
+        if self.dist is None:
+            return list(values)
+        t = self.torch.tensor(list(values), dtype=self.torch.float64, device=f"cuda:{self.dev}")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.tolist()
+
+    def sum_over_ranks(self, values):
+        if self.dist is None:
+            return list(values)
+        t = self.torch.tensor(list(values), dtype=self.torch.float64, device=f"cuda:{self.dev}")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return t.tolist()
+
+
+class _DevArr:
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+
+def bench_family(env, args, cfg_name, steps, warmup, full_record):
+    """One tree-batch configuration (c3 / c4) on the env's ranks -> the record of rank 0 (None elsewhere)."""
+    torch, dist = env.torch, env.dist
+    from linearham_b200 import device, host, sharding, workload
+    rank, world, dev = env.rank, env.world, env.dev
+    cfg = dict(workload.CONFIGS[cfg_name])
+    B_total = (args.batch if cfg_name == args.config else 0) or cfg["B"]
+    workdir = tempfile.mkdtemp(prefix=f"lhbench_{cfg_name}_")
+    ff = workload.write_family_files(cfg, workdir)
+    # per-family host work of the product: partis YAML + HMM parameter dir -> state space, transition
+    # matrices, xMSA (C++ linearham::PhyloHMM of this repo; bit-exact vs the reference, tests/test_host_model.py)
+    phmm = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0, device=dev)
+    fam, labels = phmm.family(), phmm.strs("xmsa_labels")
+    if labels != ff["labels"]:
+        raise RuntimeError("xMSA labels do not match the generated family")
+    T, S, R = fam["n_tips"], fam["n_sites"], cfg["R"]
+    tb, newicks, alpha = workload.tree_batch(cfg, ff, B_total, n_topo=args.topologies)
+    cores = env.cores
+    sub = argparse.Namespace(**vars(args))
+    sub.config = cfg_name
+    config = workload_config(sub, cfg, fam, B_total)
+    config["tree_samples"] = ("every tree keeps the naive tip under the virtual root (RevBayes' outgroup=naive template), so "
+                              "the whole batch is pruned on the distinct site patterns of xMSA rows 1.. (prune_columns)")
+
+    # CPU baseline first (before this process touches the GPU heavily); rank 0, N=1 only
+    cpu_baseline, parity, cpu_ll = None, None, None
+    want_cpu = rank == 0 and not args.no_cpu_baseline
+    if want_cpu:
+        from oracle import pyoracle as po
+        if po.have_ref():
+            n_cpu = min(len(newicks), cpu_sample_size(cfg_name, cores) if (world == 1 and full_record) else 256)
+            path = cpu_sample_file(ff, R, newicks[:n_cpu], tb["er"][:n_cpu], tb["pi"][:n_cpu], alpha[:n_cpu], workdir)
+            pool = CpuPool("reference", path, cores)
+            pool.score(0, cores)  # warm the workers (page in the library, first allocation)
+            w, cpu_ll, stages = pool.score(0, n_cpu)
+            pool.close()
+            cpu_baseline = {"value": n_cpu / w, "unit": UNIT, "cores": cores, "kind": "reference",
+                            "sample": f"first {n_cpu} tree samples of the batch, one worker process per core, {w:.2f} s wall",
+                            "stage_core_seconds": stages}
+            if world == 1 and full_record:
+                # one worker alone, and the reference as its own build makes it (-O0 linearham + libptpll,
+                # SConstruct:266, lib/libptpll/CMakeLists.txt:14) on all cores
+                n1 = {"c4": 6, "c3": 64}.get(cfg_name, 8)
+                p1 = CpuPool("reference", path, 1)
+                p1.score(0, 1)
+                w1, _, _ = p1.score(0, n1)
+                p1.close()
+                cpu_baseline["single_thread"] = {"value": n1 / w1, "unit": UNIT, "cores": 1, "sample": f"first {n1} tree samples, {w1:.2f} s"}
+                if os.path.exists(po.REF_LIB_SHIPPED):
+                    ns = {"c4": 1, "c3": 16}.get(cfg_name, 2) * cores
+                    ps = CpuPool("reference_shipped", path, cores)
+                    ws, _, _ = ps.score(0, min(ns, n_cpu))
+                    ps.close()
+                    cpu_baseline["as_shipped"] = {"value": min(ns, n_cpu) / ws, "unit": UNIT, "cores": cores,
+                                                  "build": "make -C oracle/refbuild FLAVOR=shipped (-O0, as SConstruct:266 builds it)",
+                                                  "sample": f"first {min(ns, n_cpu)} tree samples, one worker per core, {ws:.2f} s wall"}
+                else:
+                    cpu_baseline["as_shipped"] = None
+
+    # shard the batch: contiguous, equal chunks (trees of one family cost the same)
+    per = sharding.per_rank(B_total, world)
+    shard, lo, hi = sharding.shard_batch(tb, rank, world)
+    Bs = hi - lo
+    alpha_s = alpha[lo:hi]
+    # the shard's trees as the RevBayes trace would hold them (text), written once outside the timed regions
+    text = host.NewickBuffer(shard, labels)
+
+    f = device.Family(fam, device=dev)
+    f.set_labels(labels)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        f.set_option(k, int(v))
+        phmm.set_option(k, int(v))
+    if args.opt:
+        config["options"] = list(args.opt)
+    f.set_option("stream", env.stream.cuda_stream)
+    if world > 1:
+        f.set_option("host_threads", env.host_threads)
+        phmm.set_host_threads(env.host_threads)
+    gathered = None
+
+    def gather_dev(ptr, n):
+        """NCCL all-gather of this rank's device-resident log-likelihoods (queued on env.stream)."""
+        nonlocal gathered
+        if dist is None:
+            return None
+        local = torch.as_tensor(_DevArr(ptr, n), device=f"cuda:{dev}")
+        if gathered is None:
+            gathered = torch.empty(world * per, dtype=torch.float64, device=f"cuda:{dev}")
+        return sharding.gather_loglik(dist, local, B_total, out=gathered)
+
+    sampler = ClockSampler(dev)
+    rec = {}
+    with torch.cuda.stream(env.stream):
+        # -------- value: batch resident in HBM -------------------------------------
+        f.upload(shard)
+        for _ in range(warmup):
+            f.run()
+            gather_dev(*f.loglik_dev())
+        env.sync_all()
+        if full_record:
+            sampler.start()
+        f.mark(0)
+        acc = {"ms_prune": 0.0, "ms_pmatrix": 0.0, "ms_edge": 0.0, "ms_hmm": 0.0, "prune_launches": 0, "kernel_launches": 0}
+        for _ in range(steps):
+            f.run()
+            gather_dev(*f.loglik_dev())   # the collective is part of the step
+            tm = f.timings()
+            for k in acc:
+                acc[k] += tm[k]
+        f.mark(1)
+        env.sync_all()
+        ms_kernels = f.elapsed_ms(0, 1)
+        ll_dev = f.fetch()
+        full_value = gathered[:B_total].cpu().numpy() if gathered is not None else ll_dev
+
+        # -------- e2e_arrays: flattened host arrays in, this rank's host log-likelihoods out ----------
+        arr_s, arr_detail, h2d_a, d2h_a = None, None, 0, 0
+        if not args.no_e2e:
+            for _ in range(2):
+                f.score(shard)
+            env.sync_all()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                ll_arr = f.score(shard)
+                t2 = f.timings()
+            env.sync_all()
+            arr_s = time.perf_counter() - t0
+            h2d_a, d2h_a = t2["h2d_bytes"], t2["d2h_bytes"]
+            arr_detail = {k: t2[k] for k in ("ms_call", "ms_setup", "ms_plan", "ms_h2d", "ms_kernels", "ms_d2h", "ms_plan_dev", "device_plan")}
+            assert np.array_equal(ll_arr, ll_dev, equal_nan=True)
+
+        # -------- e2e: Newick text in through the class API, the whole batch's log-likelihoods on rank 0's host out
+        e2e_s, e2e_detail, h2d_e, d2h_e, e2e_launches, ll_host = None, None, 0, 0, 0, None
+        if not args.no_e2e:
+            stage = torch.empty(per, dtype=torch.float64, device=f"cuda:{dev}") if dist is not None else None
+
+            def e2e_step():
+                ll = phmm.ScoreSamples(text.ptrs, shard["er"], shard["pi"], alpha_s, R)
+                if dist is None:
+                    return ll
+                stage[:Bs].copy_(torch.from_numpy(ll), non_blocking=True)
+                allv = sharding.gather_loglik(dist, stage, B_total, out=gathered)
+                out = allv.cpu().numpy() if rank == 0 else None   # the job's result lands on rank 0's host
+                return out
+
+            for _ in range(2):
+                e2e_step()
+            env.sync_all()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                ll_host = e2e_step()
+                t3 = phmm.timings()
+                e2e_launches += t3["kernel_launches"]
+            env.sync_all()
+            e2e_s = time.perf_counter() - t0
+            h2d_e, d2h_e = t3["h2d_bytes"], t3["d2h_bytes"]
+            e2e_detail = {k: t3[k] for k in ("ms_call", "ms_setup", "ms_plan", "ms_h2d", "ms_kernels", "ms_d2h", "ms_plan_dev",
+                                             "ms_newick", "newick_host_trees", "pattern_trees")}
+            if rank == 0:
+                assert np.array_equal(ll_host, full_value, equal_nan=True), "text in and arrays in must give the same doubles"
+        clocks = sampler.stop() if full_record else None
+
+        # -------- N > 1: what the ranks computed equals what one GPU computes (bit for bit) ----------
+        parity_vs_n1 = None
+        if dist is not None:
+            k = max(1, 512 // world)
+            idx = np.concatenate([np.arange(r * per, min(B_total, r * per + k)) for r in range(world)])
+            if rank == 0:
+                sub_tb = {key: np.ascontiguousarray(v[idx]) for key, v in tb.items()}
+                again = f.score(sub_tb)
+                parity_vs_n1 = {"equal": bool(np.array_equal(again, full_value[idx], equal_nan=True)), "n": int(len(idx)),
+                                "how": f"rank 0 re-scored the first {k} trees of every rank's shard on its own GPU; "
+                                       "np.array_equal with the NCCL-gathered vector"}
+            env.sync_all()
+
+    # -------- max over ranks ------------------------------------------------------
+    ms_kernels, arr_max, e2e_max = env.max_over_ranks([ms_kernels, arr_s or 0.0, e2e_s or 0.0])
+    launches_total, h2d_a, d2h_a, h2d_e, d2h_e, e2e_launches = (int(x) for x in env.sum_over_ranks(
+        [acc["kernel_launches"], h2d_a, d2h_a, h2d_e, d2h_e, e2e_launches]))
+    out = None
+    if rank == 0:
+        value = B_total * steps / (ms_kernels * 1e-3)
+        peak, peak_src = measured_peaks()
+        bytes_tree = workload.bytes_per_tree(T, S, R)
+        # the kernel walks the distinct site patterns when it can; utilisation counts executed flop
+        cols = int(tm["prune_columns"])
+        flops_tree = workload.flops_per_tree(T, cols, R)
+        config["prune_columns"] = cols
+        config["pattern_trees_rank0"] = int(tm["pattern_trees"])
+        prune_s = acc["ms_prune"] * 1e-3
+        launches_per_step = max(1, acc["prune_launches"] // steps)
+        trees_per_launch = Bs / launches_per_step
+        avg_launch_ms = acc["ms_prune"] / max(1, acc["prune_launches"])
+        streaming = bytes_tree * Bs * steps / prune_s / 1e9
+        fp64_peak = device.fp64_peak_tflops(dev)
+        fp64_ach = flops_tree * Bs * steps / prune_s / 1e12
+        traffic, traffic_gbs, traffic_note = None, None, None
+        tp = os.path.join(ROOT, "profiles", f"k_prune_traffic_{cfg_name}.json")
+        if os.path.exists(tp):
+            try:
+                tj = json.load(open(tp))
+                traffic = tj["dram_bytes_per_launch"] / tj["trees_in_launch"] * trees_per_launch
+                traffic_gbs = traffic / (avg_launch_ms * 1e-3) / 1e9
+                traffic_note = (f"ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one k_prune launch of "
+                                f"{tj['trees_in_launch']} trees (profiles/k_prune_traffic_{cfg_name}.json, tag {tj.get('tag')}), "
+                                "per tree x trees_per_launch")
+            except Exception:
+                traffic = None
+        if cpu_ll is not None:
+            n = len(cpu_ll)
+            worst, cls, nonfin = rel_err_finite(full_value[:n], cpu_ll)
+            parity = {"n": int(n), "max_rel_err_vs_cpu": worst, "tolerance": 1e-9, "non_finite_class_equal": cls,
+                      "non_finite": nonfin, "checker": "oracle/_ref (the reference's own C++)"}
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms_kernels / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": config, "impl": "b200",
+            "roofline": {"bound": "fp64", "achieved": fp64_ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": fp64_ach / fp64_peak,
+                         "kernel": "k_prune", "peak_source": "lh_measure_fp64_peak (register-resident DFMA loop, this run)",
+                         "flop_model": "60 flop per inner node, pruning column and rate category (SURVEY 8(d): two 4x4 "
+                                       "mat-vecs + the product), on the prune_columns the kernel walks",
+                         "traffic": traffic, "traffic_source": traffic_note, "dram_gbs": traffic_gbs,
+                         "dram_frac_of_hbm_peak": None if traffic_gbs is None else traffic_gbs / peak,
+                         "trees_per_launch": trees_per_launch, "avg_launch_ms": avg_launch_ms,
+                         "hbm_streaming_model": {"achieved": streaming, "peak": peak, "unit": "GB/s", "ratio": streaming / peak,
+                                                 "peak_source": peak_src, "algorithmic_bytes_per_tree": bytes_tree,
+                                                 "note": "SURVEY 8(d)'s streaming-model bytes (every inner CLV written and read once) "
+                                                         "over the launch time: not a bandwidth fraction - inner CLVs live in "
+                                                         "registers / shared memory, so the ratio exceeds 1 and HBM does not bind"}},
+            "stage_ms_per_step": {"k_pmatrix": acc["ms_pmatrix"] / steps, "k_prune": acc["ms_prune"] / steps,
+                                  "k_edge": acc["ms_edge"] / steps, "k_hmm": acc["ms_hmm"] / steps, "rank": 0},
+            "cpu_baseline": cpu_baseline,
+            "e2e": None if e2e_s is None else {
+                "value": B_total * steps / e2e_max, "unit": UNIT, "h2d_bytes_per_step": h2d_e, "d2h_bytes_per_step": d2h_e,
+                "newick_bytes_per_step_rank0": text.total_bytes(), "host_threads_per_rank": env.host_threads,
+                "last_call_ms_rank0": e2e_detail, "gather_timed": world > 1,
+                "api": "PhyloHMM::ScoreSamples (Newick strings + er/pi/alpha on the host in, log-likelihoods out): text to the "
+                       "GPU, k_newick, k_plan, k_eigen, k_pmatrix, k_prune, k_edge, k_hmm; Gamma rates on the host threads"
+                       + ("; then the ranks' results gathered over NCCL onto rank 0's host" if world > 1 else "")},
+            "e2e_arrays": None if arr_s is None else {
+                "value": B_total * steps / arr_max, "unit": UNIT, "h2d_bytes_per_step": h2d_a, "d2h_bytes_per_step": d2h_a,
+                "last_call_ms_rank0": arr_detail,
+                "api": "lh_score_batch (pre-flattened operation arrays + pre-computed rates in, each rank's log-likelihoods on its host out)"},
+            "gpu_launches": launches_total + e2e_launches, "clocks": clocks, "parity": parity, "parity_vs_n1": parity_vs_n1,
+            "finite_fraction": float(np.mean(np.isfinite(full_value))),
+        }
+    f.close()
+    phmm.close()
+    return out
+
 
 def main():
     ap = argparse.ArgumentParser()
@@ -170,11 +548,10 @@ def main():
     ap.add_argument("--topologies", type=int, default=256, help="distinct tree topologies in the batch")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-newick", action="store_true", help="skip the Newick-string class-API measurement")
-    ap.add_argument("--newick-trees", type=int, default=4096, help="tree samples per step of e2e_newick")
+    ap.add_argument("--no-extras", action="store_true", help="skip the c3 / c5 records of the default run")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE",
                     help="lh_set_option on the family (e.g. pipe_waves=4); recorded in config")
-    ap.add_argument("--families", type=int, default=256, help="config c5: families scored per pass (whole job)")
+    ap.add_argument("--families", type=int, default=0, help="config c5: families scored per pass (whole job; default 1024)")
     ap.add_argument("--slots", type=int, default=6, help="config c5: device handles per GPU")
     ap.add_argument("--topologies-c5", dest="topologies_c5", type=int, default=16,
                     help="config c5: distinct topologies per family")
@@ -183,272 +560,43 @@ def main():
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus and world > 1:
         args.gpus = world
-    if args.impl == "reference" and rank != 0:
-        return 0
 
-    if args.config in ("c5", "c2"):
-        if args.impl == "reference":
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        if args.config in ("c5", "c2"):
             print(json.dumps({"impl": "reference", "unavailable": "the reference arm is timed on config c4 (bench.py default)"}))
             return 0
+        return reference_arm(args)
+
+    env = Env(args)
+    if args.config in ("c5", "c2"):
         import bench_c2
         import bench_c5
-        return (bench_c5 if args.config == "c5" else bench_c2).run(args, rank, world, local_rank)
-
-    from linearham_b200 import host, sharding, workload
-    cfg = dict(workload.CONFIGS[args.config])
-    B_total = args.batch or cfg["B"]
-    workdir = tempfile.mkdtemp(prefix="lhbench_")
-    ff = workload.write_family_files(cfg, workdir)
-    # per-family host work of the product: partis YAML + HMM parameter dir -> state space, transition
-    # matrices, xMSA (C++ linearham::PhyloHMM of this repo; bit-exact vs the reference, tests/test_host_model.py)
-    phmm = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0, device=local_rank if world > 1 else 0)
-    fam, labels = phmm.family(), phmm.strs("xmsa_labels")
-    if labels != ff["labels"]:
-        raise RuntimeError("xMSA labels do not match the generated family")
-    T, S, R = fam["n_tips"], fam["n_sites"], cfg["R"]
-    tb, newicks, alpha = workload.tree_batch(cfg, ff, B_total, n_topo=args.topologies)
-    cores = os.cpu_count() or 1
-    config = {"workload": f"{args.config}: {cfg['desc']}", "n_tips": T, "xmsa_columns": S, "gamma_categories": R,
-              "global_batch": B_total, "distinct_topologies": min(args.topologies, B_total),
-              "hmm": {"vd": [fam["vd_sites"], fam["vd_states"]], "dj": [fam["dj_sites"], fam["dj_states"]],
-                      "genes": [fam["n_v"], fam["n_d"], fam["n_j"]]},
-              "parallelism": f"trees sharded over {args.gpus} GPU(s), no data-path collective; "
-                             "NCCL all-gather of the per-tree log-likelihoods",
-              "l2": "inputs larger than L2"}
-
-    # ---------------------------------------------------------------- reference arm ---
-    if args.impl == "reference":
-        n_step = max(cores, min(len(newicks), {"c4": 4, "c3": 64}.get(args.config, 16) * cores))
-        kind, path = cpu_arm_setup(args.config, cfg, ff, fam, tb, newicks, alpha, n_step, workdir)
-        pool = CpuPool(kind, path, cores)
-        for _ in range(args.warmup):
-            pool.score(0, n_step)
-        total = 0.0
-        for _ in range(args.steps):
-            w, _, stages = pool.score(0, n_step)
-            total += w
-        pool.close()
-        v = n_step * args.steps / total
-        sample = f"{n_step} tree samples per step (the first {n_step} of the batch), {cores} worker processes"
-        print(json.dumps({
-            "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
-            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}))
-        return 0
-
-    # ------------------------------------------------------------------- B200 arm ---
-    import torch
-    from linearham_b200 import device
-    if not torch.cuda.is_available() or device.device_count() < 1:
-        raise RuntimeError("bench.py needs a CUDA device: linearham_b200 has no CPU fallback")
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    dev = local_rank if world > 1 else 0
-
-    # CPU baseline first (before this process touches the GPU heavily); rank 0, N=1 only
-    cpu_baseline, parity = None, None
-    cpu_ll = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        n_cpu = min(len(newicks), cpu_sample_size(args.config, cores))
-        kind, path = cpu_arm_setup(args.config, cfg, ff, fam, tb, newicks, alpha, n_cpu, workdir)
-        pool = CpuPool(kind, path, cores)
-        pool.score(0, cores)  # warm the workers (page in the library, first allocation)
-        w, cpu_ll, stages = pool.score(0, n_cpu)
-        pool.close()
-        cpu_baseline = {"value": n_cpu / w, "unit": UNIT, "cores": cores, "kind": kind,
-                        "sample": f"first {n_cpu} tree samples of the batch, one worker process per core, "
-                                  f"{w:.2f} s wall",
-                        "stage_core_seconds": stages}
-
-    # shard the batch: contiguous, equal chunks (trees of one family cost the same)
-    per = sharding.per_rank(B_total, world)
-    shard, lo, hi = sharding.shard_batch(tb, rank, world)
-    Bs = hi - lo
-
-    f = device.Family(fam, device=dev)
-    for kv in args.opt:
-        k, v = kv.split("=")
-        f.set_option(k, int(v))
-    if args.opt:
-        config["options"] = list(args.opt)
-    gathered = None
-    # ranks of one node share its host cores: each takes its share for traversal planning and Newick ingest
-    host_threads = max(2, cores // int(os.environ.get("LOCAL_WORLD_SIZE", world))) if world > 1 else cores
-    if world > 1:
-        f.set_option("stream", torch.cuda.current_stream().cuda_stream)
-        f.set_option("host_threads", host_threads)
-        phmm.set_host_threads(host_threads)
-
-    class _DevArr:
-        def __init__(self, ptr, n):
-            self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
-
-    def sync_all():
-        f.sync()
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    def gather_step():
-        nonlocal gathered
-        if dist is None:
-            return
-        ptr, n = f.loglik_dev()
-        local = torch.as_tensor(_DevArr(ptr, n), device=f"cuda:{dev}")
-        if gathered is None:
-            gathered = torch.empty(world * per, dtype=torch.float64, device=f"cuda:{dev}")
-        sharding.gather_loglik(dist, local, B_total, out=gathered)
-
-    sampler = ClockSampler(dev)
-    # -------- value: batch resident in HBM -------------------------------------
-    f.upload(shard)
-    for _ in range(args.warmup):
-        f.run()
-        gather_step()
-    sync_all()
-    sampler.start()
-    f.mark(0)
-    acc = {"ms_prune": 0.0, "ms_pmatrix": 0.0, "ms_repeats": 0.0, "ms_edge": 0.0, "ms_hmm": 0.0, "prune_launches": 0, "kernel_launches": 0}
-    for _ in range(args.steps):
-        f.run()
-        gather_step()
-        tm = f.timings()
-        for k in acc:
-            acc[k] += tm[k]
-    f.mark(1)
-    sync_all()
-    ms_kernels = f.elapsed_ms(0, 1)
-    ll_dev = f.fetch()
-
-    # -------- e2e: host buffers in, host log-likelihoods out --------------------
-    e2e_s, h2d, d2h, ms_plan, e2e_detail = None, 0, 0, 0.0, None
-    if not args.no_e2e:
-        for _ in range(max(1, min(args.warmup, 2))):
-            f.score(shard)
-        sync_all()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            ll_e2e = f.score(shard)
-            t2 = f.timings()
-            h2d, d2h, ms_plan = t2["h2d_bytes"], t2["d2h_bytes"], t2["ms_plan"]
-            e2e_detail = {k: t2[k] for k in ("ms_call", "ms_setup", "ms_plan", "ms_h2d", "ms_kernels", "ms_d2h",
-                                             "ms_plan_dev", "device_plan")}
-        sync_all()
-        e2e_s = time.perf_counter() - t0
-        assert np.array_equal(ll_e2e, ll_dev, equal_nan=True)
-    # -------- e2e from Newick strings: the class API a linearham user calls -------------
-    # PhyloHMM::ScoreSamples(newick strings, er, pi, alpha) -> log-likelihoods: Newick ingest on the host
-    # threads overlapped with lh_score_batch of the previous chunk. The strings are marshalled to a C array
-    # once, outside the timed region (a C++ caller holds them as char* already).
-    nw_s, nw_n = None, 0
-    if not args.no_e2e and not args.no_newick:
-        nw_n = min(Bs, args.newick_trees)
-        nt = len(newicks)
-        arr = host.encode_newicks([newicks[(lo + i) % nt] for i in range(nw_n)])
-        er_n, pi_n, al_n = shard["er"][:nw_n], shard["pi"][:nw_n], alpha[lo:lo + nw_n]
-        ll_nw = phmm.ScoreSamples(arr, er_n, pi_n, al_n, R)
-        sync_all()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            ll_nw = phmm.ScoreSamples(arr, er_n, pi_n, al_n, R)
-        sync_all()
-        nw_s = time.perf_counter() - t0
-        k = max(0, min(nw_n, nt - lo))  # samples whose branch lengths are the strings' own
-        assert np.array_equal(ll_nw[:k], ll_dev[:k], equal_nan=True)
-    clocks = sampler.stop()
-
-    # -------- max over ranks ------------------------------------------------------
-    if dist is not None:
-        t = torch.tensor([ms_kernels, e2e_s or 0.0, acc["ms_prune"], nw_s or 0.0], dtype=torch.float64, device=f"cuda:{dev}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_kernels, e2e_max, _, nw_max = t.tolist()
-        e2e_s = e2e_max if e2e_s is not None else None
-        nw_s = nw_max if nw_s is not None else None
-        full = gathered[:B_total].cpu().numpy() if gathered is not None else ll_dev
-        lt = torch.tensor([acc["kernel_launches"]], dtype=torch.float64, device=f"cuda:{dev}")
-        dist.all_reduce(lt, op=dist.ReduceOp.SUM)
-        launches_total = int(lt.item())
+        out = (bench_c5.run(env, args) if args.config == "c5" else bench_c2.run(env, args))
     else:
-        full = ll_dev
-        launches_total = acc["kernel_launches"]
-
-    if rank == 0:
-        value = B_total * args.steps / (ms_kernels * 1e-3)
-        peak, peak_src = measured_peaks()
-        bytes_tree = workload.bytes_per_tree(T, S, R)
-        # the kernel walks the distinct site patterns when it can; utilisation counts executed flop
-        cols = int(tm["prune_columns"])
-        flops_tree = workload.flops_per_tree(T, cols, R)
-        config["prune_columns"] = cols
-        config["pattern_trees_rank0"] = int(tm["pattern_trees"])
-        config["site_repeats"] = bool(tm["site_repeats"])
-        if tm["site_repeats"]:
-            config["sr_arena_entries"], config["sr_ctas_per_sm"] = int(tm["sr_arena"]), int(tm["sr_ctas_per_sm"])
-        prune_s = acc["ms_prune"] * 1e-3
-        achieved = bytes_tree * Bs * args.steps / prune_s / 1e9
-        fp64_peak = device.fp64_peak_tflops(dev)
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", f"k_prune_traffic_{args.config}.json")
-        if os.path.exists(tp):
-            try:
-                # the ncu capture ran one launch of `trees_in_launch` trees: scale to this run's launch size
-                tj = json.load(open(tp))
-                traffic = tj["dram_bytes_per_launch"] / tj["trees_in_launch"] * (Bs / max(1, acc["prune_launches"] // args.steps))
-            except Exception:
-                traffic = None
-        if cpu_ll is not None:
-            n = len(cpu_ll)
-            ok = np.isfinite(cpu_ll)
-            parity = {"n": int(n), "max_rel_err_vs_cpu": float(np.max(np.abs(full[:n][ok] - cpu_ll[ok]) / np.abs(cpu_ll[ok]))),
-                      "tolerance": 1e-9, "non_finite_class_equal": bool(np.array_equal(np.isfinite(full[:n]), ok)),
-                      "non_finite": int(n - ok.sum())}
-        out = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_kernels / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic", "config": config, "impl": "b200",
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of one k_prune launch "
-                         "(profiles/k_prune_traffic_<config>.json), per tree x trees_per_launch",
-                         "kernel": "k_prune", "peak_source": peak_src,
-                         "algorithmic_bytes_per_tree": bytes_tree, "trees_per_launch": Bs / max(1, acc["prune_launches"] // args.steps),
-                         "avg_launch_ms": acc["ms_prune"] / max(1, acc["prune_launches"]),
-                         "note": "inner CLVs live in registers/shared memory (on-chip stack), so DRAM traffic is far "
-                                 "below the streaming-model bytes and frac may exceed 1; the binding limits are the "
-                                 "FP64 pipe and the L1 data pipe. achieved counts the streaming-model bytes of all "
-                                 "xmsa_columns; fp64 counts the flop executed on prune_columns",
-                         "fp64": {"achieved_tflops": flops_tree * Bs * args.steps / prune_s / 1e12, "peak_tflops": fp64_peak,
-                                  "frac": flops_tree * Bs * args.steps / prune_s / 1e12 / fp64_peak,
-                                  "peak_source": "lh_measure_fp64_peak (DFMA loop, this run)"}},
-            "stage_ms_per_step": {"k_pmatrix": acc["ms_pmatrix"] / args.steps, "k_repeats": acc["ms_repeats"] / args.steps, "k_prune": acc["ms_prune"] / args.steps,
-                                  "k_edge": acc["ms_edge"] / args.steps, "k_hmm": acc["ms_hmm"] / args.steps, "rank": 0},
-            "cpu_baseline": cpu_baseline,
-            "e2e": None if e2e_s is None else {"value": B_total * args.steps / e2e_s, "unit": UNIT,
-                                               "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
-                                               "host_plan_ms_per_step_rank0": ms_plan, "host_threads_per_rank": host_threads, "last_call_ms_rank0": e2e_detail,
-                                               "api": "lh_score_batch (host arrays in, host log-likelihoods out)"},
-            "e2e_newick": None if nw_s is None else {
-                "value": nw_n * world * args.steps / nw_s, "unit": UNIT, "trees_per_step": nw_n * world,
-                "host_threads": host_threads,
-                "api": "PhyloHMM::ScoreSamples (Newick strings + er/pi/alpha in, log-likelihoods out; "
-                       "Newick ingest on host threads overlapped with lh_score_batch)"},
-            "gpu_launches": launches_total, "clocks": clocks, "parity": parity,
-            "finite_fraction": float(np.mean(np.isfinite(full))),
-        }
+        out = bench_family(env, args, args.config, args.steps, args.warmup, True)
+        if args.config == "c4" and not args.no_extras and not args.batch:
+            # the other single-box configurations, so that one driver-run line carries them all
+            c3 = bench_family(env, args, "c3", 3, 3, False)
+            import bench_c5
+            c5_args = argparse.Namespace(**vars(args))
+            c5_args.families = args.families or 1024
+            c5_args.steps, c5_args.warmup, c5_args.batch = 2, 3, 0
+            c5 = bench_c5.run(env, c5_args)
+            if env.rank == 0:
+                keep = ("value", "unit", "ms_per_step", "steps", "warmup", "config", "roofline", "e2e", "e2e_arrays", "parity", "cpu_baseline",
+                        "parity_vs_n1", "gpu_launches", "families_per_s", "value_is_end_to_end")
+                out["c3"] = {k: c3[k] for k in keep if k in c3}
+                out["c5"] = {k: c5[k] for k in keep if k in c5}
+                out["gpu_launches"] += c3["gpu_launches"] + c5["gpu_launches"]
+    if env.rank == 0:
         print(json.dumps(out))
-    f.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    if env.dist is not None:
+        env.dist.barrier()
+        env.dist.destroy_process_group()
     return 0
 
 

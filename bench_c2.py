@@ -13,29 +13,24 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 
 
-def run(args, rank, world, local_rank):
-    import torch
+def run(env, args):
+    """-> the record (rank 0) or None; bench.py prints it."""
     import bench as B
-    from linearham_b200 import device, sharding, workload
+    from linearham_b200 import device, host, sharding, workload
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from conftest import load_liao
-    if not torch.cuda.is_available() or device.device_count() < 1:
-        raise RuntimeError("bench.py needs a CUDA device: linearham_b200 has no CPU fallback")
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    dev = local_rank if world > 1 else 0
-    fam, tb, exp, _ = load_liao()
+    torch, dist, rank, world, dev = env.torch, env.dist, env.rank, env.world, env.dev
+    fam, tb, exp, z = load_liao()
+    labels = [str(x) for x in z["labels"]]
     T, S, R = fam["n_tips"], fam["n_sites"], int(tb["rates"].shape[1])
     Bt = int(tb["root_child"].shape[0])
     shard, lo, hi = sharding.shard_batch(tb, rank, world)
     Bs = hi - lo
     f = device.Family(fam, device=dev)
-    cores = os.cpu_count() or 1
+    f.set_labels(labels)
     if world > 1:
-        f.set_option("host_threads", max(2, cores // int(os.environ.get("LOCAL_WORLD_SIZE", world))))
+        f.set_option("host_threads", env.host_threads)
+    text = host.NewickBuffer(shard, labels)   # the shard's trees as text (the bundle stores arrays)
 
     def sync_all():
         f.sync()
@@ -44,6 +39,7 @@ def run(args, rank, world, local_rank):
             dist.barrier()
             torch.cuda.synchronize()
 
+    out = None
     f.upload(shard)
     for _ in range(max(3, args.warmup)):
         f.run()
@@ -70,12 +66,21 @@ def run(args, rank, world, local_rank):
         t2 = f.timings()
     sync_all()
     e2e_s = time.perf_counter() - t0
-    clocks = sampler.stop()
     assert np.array_equal(ll, ll_e2e, equal_nan=True)
+    # Newick text in (lh_score_newick: parsed on the device)
+    for _ in range(2):
+        f.score_newick(text.ptrs, shard["er"], shard["pi"], R, rates=shard["rates"])
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ll_text = f.score_newick(text.ptrs, shard["er"], shard["pi"], R, rates=shard["rates"])
+        t3 = f.timings()
+    sync_all()
+    text_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+    assert np.array_equal(ll, ll_text, equal_nan=True)
     if dist is not None:
-        t = torch.tensor([ms_kernels, e2e_s], dtype=torch.float64, device=f"cuda:{dev}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_kernels, e2e_s = t.tolist()
+        ms_kernels, e2e_s, text_s = env.max_over_ranks([ms_kernels, e2e_s, text_s])
         full = sharding.gather_loglik(dist, torch.from_numpy(ll).to(f"cuda:{dev}"), Bt).cpu().numpy()
     else:
         full = ll
@@ -102,7 +107,7 @@ def run(args, rank, world, local_rank):
         cols = int(tm["prune_columns"])
         fp64_peak = device.fp64_peak_tflops(dev)
         fl = workload.flops_per_tree(T, cols, R) * Bs * args.steps / prune_s / 1e12
-        print(json.dumps({
+        out = {
             "metric": B.METRIC, "value": Bt * args.steps / (ms_kernels * 1e-3), "unit": B.UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_kernels / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -114,19 +119,19 @@ def run(args, rank, world, local_rank):
                                "genes": [fam["n_v"], fam["n_d"], fam["n_j"]]},
                        "l2": "L2 flush not needed: a step reads what the step itself wrote (branch records, "
                              f"{f.timings()['prune_grid']} CTAs); inputs are {t2['h2d_bytes'] >> 20} MB"},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "k_prune", "peak_source": peak_src,
-                         "algorithmic_bytes_per_tree": bytes_tree,
+            "roofline": {"bound": "fp64", "achieved": fl, "peak": fp64_peak, "unit": "TFLOP/s", "frac": fl / fp64_peak,
+                         "traffic": None, "kernel": "k_prune", "peak_source": "lh_measure_fp64_peak (this run)",
                          "avg_launch_ms": acc["ms_prune"] / max(1, acc["prune_launches"]),
-                         "fp64": {"achieved_tflops": fl, "peak_tflops": fp64_peak, "frac": fl / fp64_peak}},
+                         "hbm_streaming_model": {"achieved": achieved, "peak": peak, "unit": "GB/s", "ratio": achieved / peak,
+                                                 "peak_source": peak_src, "algorithmic_bytes_per_tree": bytes_tree}},
             "stage_ms_per_step": {k[3:]: acc[k] / args.steps for k in ("ms_pmatrix", "ms_prune", "ms_edge", "ms_hmm")},
-            "e2e": {"value": Bt * args.steps / e2e_s, "unit": B.UNIT, "h2d_bytes_per_step": int(t2["h2d_bytes"]) * world,
-                    "d2h_bytes_per_step": int(t2["d2h_bytes"]) * world,
-                    "api": "lh_score_batch (host arrays in, host log-likelihoods out)"},
+            "e2e": {"value": Bt * args.steps / text_s, "unit": B.UNIT, "h2d_bytes_per_step": int(t3["h2d_bytes"]) * world,
+                    "d2h_bytes_per_step": int(t3["d2h_bytes"]) * world, "ms_newick_rank0": t3["ms_newick"],
+                    "api": "lh_score_newick (Newick strings in, host log-likelihoods out)"},
+            "e2e_arrays": {"value": Bt * args.steps / e2e_s, "unit": B.UNIT, "h2d_bytes_per_step": int(t2["h2d_bytes"]) * world,
+                           "d2h_bytes_per_step": int(t2["d2h_bytes"]) * world,
+                           "api": "lh_score_batch (host arrays in, host log-likelihoods out)"},
             "cpu_baseline": cpu_baseline, "parity": parity, "gpu_launches": int(acc["kernel_launches"]),
-            "clocks": clocks}))
+            "clocks": clocks}
     f.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
-    return 0
+    return out if rank == 0 else None

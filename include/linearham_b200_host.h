@@ -82,6 +82,10 @@ int lhh_phylohmm_run_pipeline(lhh_phylohmm_t* h, const char* input_path, const c
 /* The loop body :419-430 for n samples at once: log-likelihoods only.                           */
 int lhh_phylohmm_score_samples(lhh_phylohmm_t* h, int32_t n, const char* const* newicks, const double* er,
                                const double* pi, const double* alpha, int32_t num_rates, double* loglik);
+/* The device handle (include/linearham_b200.h) behind the object, created on first use: for
+ * lh_get_timings / lh_set_option / lh_loglik_dev after a scoring call. Owned by the object.       */
+struct lh_family;
+int lhh_phylohmm_device_family(lhh_phylohmm_t* h, struct lh_family** out);
 /* pll_utree_export_newick of a Newick string (libpll utree.c:148-270), as written to the output TSV. */
 int lhh_export_newick(const char* newick, char* out, int32_t cap);
 /* Named read-outs of the object's members (accessor names of src/HMM.hpp / src/PhyloHMM.hpp

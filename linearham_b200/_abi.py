@@ -161,14 +161,19 @@ def alloc_outputs(fam, B, fields=None, n_rates=None):
 def newick_batch(newicks, er, pi, n_rates, alpha=None, rates=None, lengths=False):
     """Newick strings (str or bytes) + er[B,6], pi[B,4] + alpha[B] or rates[B,R] -> (NewickBatch, keepalive)."""
     nb = NewickBatch()
-    raw = [s if isinstance(s, bytes) else str(s).encode() for s in newicks]
-    B = len(raw)
-    arr = (C.c_char_p * max(B, 1))(*raw)
+    if isinstance(newicks, C.Array):   # a (c_char_p * B) array marshalled once by the caller (host.NewickBuffer.ptrs)
+        arr, raw = newicks, None
+        B = int(np.asarray(er).reshape(-1, 6).shape[0])
+    else:
+        raw = [s if isinstance(s, bytes) else str(s).encode() for s in newicks]
+        B = len(raw)
+        arr = (C.c_char_p * max(B, 1))(*raw)
     keep = [raw, arr]
     nb.n_trees, nb.n_rates = B, int(n_rates)
     nb.newick = C.cast(arr, C.POINTER(C.c_char_p))
-    if lengths:
-        ln = np.array([len(s) for s in raw], dtype=np.int64)
+    if lengths is not None and lengths is not False:
+        ln = (np.array([len(s) for s in raw], dtype=np.int64) if lengths is True
+              else np.ascontiguousarray(lengths, dtype=np.int64))
         keep.append(ln)
         nb.length = ln.ctypes.data_as(C.POINTER(C.c_int64))
     for name, val in (("er", er), ("pi", pi), ("alpha", alpha), ("rates", rates)):
@@ -264,7 +269,7 @@ def bind_host(lib):
 
 HOST_SYMBOLS += ["lhh_phylohmm_new", "lhh_phylohmm_free", "lhh_phylohmm_set_device", "lhh_phylohmm_set_host_threads", "lhh_phylohmm_family_desc",
                  "lhh_phylohmm_init_params", "lhh_phylohmm_init_emission", "lhh_phylohmm_loglikelihood",
-                 "lhh_phylohmm_sample_naive", "lhh_phylohmm_run_pipeline", "lhh_phylohmm_score_samples",
+                 "lhh_phylohmm_sample_naive", "lhh_phylohmm_run_pipeline", "lhh_phylohmm_score_samples", "lhh_phylohmm_device_family",
                  "lhh_export_newick", "lhh_phylohmm_get_f64", "lhh_phylohmm_get_i32", "lhh_phylohmm_get_str"]
 
 
@@ -274,6 +279,7 @@ def bind_phylohmm(lib):
     lib.lhh_phylohmm_free.argtypes = [C.c_void_p]
     lib.lhh_phylohmm_free.restype = None
     lib.lhh_phylohmm_set_device.argtypes = [C.c_void_p, C.c_int32]
+    lib.lhh_phylohmm_device_family.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
     lib.lhh_phylohmm_set_host_threads.argtypes = [C.c_void_p, C.c_int32]
     lib.lhh_phylohmm_family_desc.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
     lib.lhh_phylohmm_init_params.argtypes = [C.c_void_p, C.c_char_p, _f64p, _f64p, C.c_double, C.c_int32]

@@ -149,6 +149,10 @@ int lhh_phylohmm_score_samples(lhh_phylohmm_t* h, int32_t n, const char* const* 
   });
 }
 
+int lhh_phylohmm_device_family(lhh_phylohmm_t* h, lh_family_t** out) {
+  return guarded([&] { *out = H(h).device_family(); });
+}
+
 int lhh_export_newick(const char* newick, char* out, int32_t cap) {
   return guarded([&] {
     std::string s = linearham::ExportNewick(newick);

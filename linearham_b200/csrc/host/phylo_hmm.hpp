@@ -178,6 +178,8 @@ class PhyloHMM : public HMM {
                     int num_rates, double* loglik);
 
   void set_device(int device) { device_ = device; }
+  // the device handle behind this object (created on first use); for timings and options
+  lh_family* device_family() { EnsureDeviceFamily(); return dev_family_; }
   // host threads for Newick ingest and traversal planning (0 = all hardware threads)
   void set_host_threads(int n);
 

@@ -210,6 +210,20 @@ class PhyloHMM:
         _ck(self._lib.lhh_phylohmm_run_pipeline(self._h, str(input_path).encode(), str(output_path).encode(),
                                                 int(num_rates), int(batch_size)))
 
+    def timings(self):
+        """lh_get_timings of the device handle behind the object (the last scoring call)."""
+        h, t = C.c_void_p(), _abi.Timings()
+        _ck(self._lib.lhh_phylohmm_device_family(self._h, C.byref(h)))
+        if self._lib.lh_get_timings(h, C.byref(t)):
+            raise HostError(self._lib.lh_last_error().decode())
+        return {k: getattr(t, k) for k, _ in _abi.Timings._fields_}
+
+    def set_option(self, key, value):
+        h = C.c_void_p()
+        _ck(self._lib.lhh_phylohmm_device_family(self._h, C.byref(h)))
+        if self._lib.lh_set_option(h, key.encode(), int(value)):
+            raise HostError(self._lib.lh_last_error().decode())
+
     def ScoreSamples(self, newicks, er, pi, alpha, num_rates):
         """newicks: list of str, or a ctypes array made by encode_newicks (marshalled once, reused)."""
         n = len(newicks)

@@ -22,8 +22,9 @@ def main():
     kind, path = sys.argv[1], sys.argv[2]
     z = np.load(path, allow_pickle=False)
     from oracle import pyoracle as po
-    if kind == "reference":
-        ref = po.RefPhyloHMM(str(z["yaml_path"]), 0, str(z["hmm_dir"]), 0)
+    if kind in ("reference", "reference_shipped"):  # the tuned build, or the -O0 build the reference's SConstruct makes
+        ref = po.RefPhyloHMM(str(z["yaml_path"]), 0, str(z["hmm_dir"]), 0,
+                             lib_path=po.REF_LIB_SHIPPED if kind == "reference_shipped" else None)
         newicks = [str(s) for s in z["newicks"]]
 
         def score(a, n):
