@@ -233,6 +233,7 @@ struct lh_family {
   lhb::HmmOut ho{};
   int chunk = 0, chunk_pipe = 0, wave_pipe = 0, wave_unit = 0, seg = 0, occ[2] = {0, 0};
   int opt_open_unit = 1, opt_chunk_growth = 1;
+  int opt_newick_kernel = 0;  // 0 auto, 1 k_newick (one thread per tree), 2 k_newick_cta (one CTA per tree)
   double stage_ratio = 1.0;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
   // trees that can run on site patterns (naive tip on the root edge or under the virtual root)
@@ -616,6 +617,10 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_chunk_growth = value != 0;
   } else if (k == "open_unit") {
     f->opt_open_unit = value != 0;
+  } else if (k == "newick_kernel") {
+    if (value < 0 || value > 2) return fail("newick_kernel must be 0 (auto), 1 (one thread per tree) or 2 (one CTA per tree)");
+    if (value == 2 && f->bound && !lhb::newick_cta_ok(f->fd.T)) return fail("the family is too large for the one-CTA-per-tree parser");
+    f->opt_newick_kernel = (int)value;
   } else if (k == "device_plan") {
     if (value < -1 || value > 1) return fail("device_plan must be -1 (auto), 0 or 1");
     f->opt_device_plan = (int)value;
@@ -1145,7 +1150,7 @@ int probe_window_from_text(lh_family* f, const lh_newick_batch_t* nb, int t0, in
 
 // Copies the strings of trees [t0, t0+n) (lengths len[0..n)) into ring slot `slot`, queues their copy to
 // the slot's device text buffer on `cs` and their parse (k_newick) on the plan stream.
-// Slot layout: offs [n] uint32 | pad to 16 | strings, each NUL-terminated and 16-byte aligned.
+// Slot layout: offs [n] uint32 | lens [n] uint32 | pad to 16 | strings, each NUL-terminated and 16-byte aligned.
 int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n, const int64_t* len, int slot, cudaStream_t cs) {
   if (f->ring_busy[slot]) {
     LH_CUDA(cudaEventSynchronize(f->ring_ev[slot]));  // k_newick of the slot's previous segment has run
@@ -1158,10 +1163,12 @@ int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n,
   }
   uint8_t* base = f->h_ring[slot].as<uint8_t>();
   uint32_t* offs = reinterpret_cast<uint32_t*>(base);
-  const size_t text0 = ((size_t)n * 4 + 15) / 16 * 16;
+  const size_t text0 = ((size_t)n * 8 + 15) / 16 * 16;
+  uint32_t* lens32 = offs + n;
   size_t at = 0;
   for (int i = 0; i < n; ++i) {
     offs[i] = (uint32_t)at;
+    lens32[i] = (uint32_t)len[i];
     at += ((size_t)len[i] + 1 + 15) / 16 * 16;
   }
   const size_t total = text0 + at;
@@ -1193,6 +1200,8 @@ int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n,
   p.n = n;
   p.text = f->d_text[slot].as<char>() + text0;
   p.offs = f->d_text[slot].as<uint32_t>();
+  p.lens = p.offs + n;
+  p.kernel = f->opt_newick_kernel;
   p.labels = f->lt;
   p.children = f->d_rchildren.as<int32_t>();
   p.blen = f->d_rblen.as<double>();
@@ -1234,7 +1243,7 @@ int stage_text_chunk(lh_family* f, const lh_newick_batch_t* nb, int c0, int cn, 
     size_t bytes = 0;
     int n = 0;
     while (i + n < cn) {
-      const size_t add = ((size_t)lens[i + n] + 1 + 15) / 16 * 16 + 4;
+      const size_t add = ((size_t)lens[i + n] + 1 + 15) / 16 * 16 + 8;
       if (n && bytes + add + 16 > kTextSlotBytes) break;
       bytes += add;
       ++n;

@@ -136,6 +136,8 @@ struct NewickDev {
   int32_t tree0, n;            // batch index of the segment's first tree, trees in the segment
   const char* text;            // the segment's strings, each NUL-terminated and starting on a 16-byte boundary
   const uint32_t* offs;        // [n] start of each string in text
+  const uint32_t* lens;        // [n] strlen of each string
+  int32_t kernel;              // 0: pick by family size, 1: k_newick (one thread per tree), 2: k_newick_cta
   LabelTableDev labels;
   int32_t* children;           // [B][T-2][2]   (batch arrays, as in PlanDev)
   double* blen;                // [B][T-2][2]
@@ -146,6 +148,7 @@ struct NewickDev {
                                //     this parser does not decide) - the tree then gets a harmless stand-in
 };
 void launch_newick(const NewickDev& p, cudaStream_t s);
+bool newick_cta_ok(int n_tips);  // the cooperative parser's shared-memory tables fit
 // stable partition of the chunk's trees [t0, t0+n) by on_pat into list[t0..) (pattern trees first);
 // n_pat_out[0] = how many
 void launch_split(const uint8_t* on_pat, int t0, int n, int32_t* list, int32_t* n_pat_out, cudaStream_t s);

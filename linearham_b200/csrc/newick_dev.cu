@@ -30,8 +30,9 @@ struct Reader {
   const char* s;
   uint64_t cur;
   uint32_t pos;
-  __device__ __forceinline__ explicit Reader(const char* str) : s(str), pos(0) {
-    cur = __ldg(reinterpret_cast<const unsigned long long*>(s));
+  // str is 8-byte aligned; reading starts at character p0
+  __device__ __forceinline__ explicit Reader(const char* str, uint32_t p0 = 0) : s(str), pos(p0) {
+    cur = __ldg(reinterpret_cast<const unsigned long long*>(s + (p0 & ~7u)));
   }
   __device__ __forceinline__ int peek() const { return (int)((cur >> ((pos & 7u) * 8u)) & 0xffu); }
   __device__ __forceinline__ void adv() {
@@ -207,6 +208,368 @@ __global__ void __launch_bounds__(32) k_newick(NewickDev p) {
   }
 }
 
+// ------------------------------------------------------------------ k_newick_cta ---
+// The same parse, one CTA per tree, for the latency of a call: a 1001-tip string is 73 KB and a single thread
+// needs tens of milliseconds for it (a dependent chain over the characters), which is half a C4 step in front of
+// the first pruning kernel. Here the string is cut into one slice per thread and lexed in parallel:
+//   S0  brackets: a character is inside a comment iff the nearest bracket to its left is '[' - each thread finds
+//       the last bracket of its slice, a warp ballot / per-warp summary gives every slice its state at its start;
+//   S1  every thread lexes its slice without knowing what came before it: the state (inside a word?, last token)
+//       is fixed from the first structural character on, so a slice is summarised by what it holds before that
+//       character (a word run that may continue the previous slice, at most one new word) and by its counts
+//       after it; thread 0 folds the summaries front to back (one short loop) into the exact state - last token,
+//       depth, ')' count, node count - at the start of every slice;
+//   S3  every thread lexes its slice again, now exactly: checks the token grammar and records one item per node
+//       (tip: where its label starts; ')': where it ends, which operation it is) with its depth, in text order;
+//   S5  one thread per node: label -> xMSA row (hash table), branch length -> double (Eisel-Lemire);
+//   S6  thread 0 walks the items once: a tip or a finished node is filed under its level, a ')' takes the two
+//       filed under its level as its children - the stack of the sequential parser, indexed by the depth S3 knows.
+// The grammar accepted here is the strict one - '(' item ',' item [',' item] ')' [label] [':' number], ';' at depth
+// 0, nothing after it; every other spelling the lenient host parser takes (missing commas, text after ';', ...)
+// is left to it, like everything else this kernel does not decide.
+enum : int { K_NONE = 0, K_OPEN, K_CLOSE, K_COMMA, K_COLON, K_SEMI, K_TIP, K_NUM, K_INNER, K_BAD };
+
+__device__ __forceinline__ int word_type(int last) {
+  return (last == K_OPEN || last == K_COMMA) ? K_TIP : last == K_COLON ? K_NUM : last == K_CLOSE ? K_INNER : K_BAD;
+}
+// which tokens may come before a structural token
+__device__ __forceinline__ bool may_follow(int prev, int cur) {
+  constexpr unsigned after_node = (1u << K_TIP) | (1u << K_NUM) | (1u << K_CLOSE) | (1u << K_INNER);
+  unsigned ok = 0;
+  if (cur == K_OPEN) ok = (1u << K_NONE) | (1u << K_OPEN) | (1u << K_COMMA);
+  else if (cur == K_CLOSE || cur == K_COMMA) ok = after_node;
+  else if (cur == K_COLON) ok = (1u << K_TIP) | (1u << K_INNER) | (1u << K_CLOSE);
+  else if (cur == K_SEMI) ok = (1u << K_CLOSE) | (1u << K_INNER) | (1u << K_NUM);
+  return (ok >> prev) & 1u;
+}
+__device__ __forceinline__ int structural(int c) {
+  return c == '(' ? K_OPEN : c == ')' ? K_CLOSE : c == ',' ? K_COMMA : c == ':' ? K_COLON : c == ';' ? K_SEMI : K_NONE;
+}
+__device__ __forceinline__ bool is_blank(int c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
+
+struct SliceSummary {        // what a slice says without knowing what precedes it (S1)
+  uint8_t lead_word;         // starts (outside a comment) with a word character: may continue the previous slice's word
+  uint8_t early_runs;        // word runs that start before its first structural token (0, 1, 2 = more)
+  uint8_t first_tok;         // its first structural token, K_NONE if it has none
+  uint8_t last_tok;          // its last token if that is fixed inside the slice, else K_NONE (= the early word, or nothing)
+  uint8_t in_word_out;       // its last character is a word character outside a comment
+  uint8_t nonempty;
+  uint16_t n_open, n_close, n_tips;  // after (and including) the first structural token
+};
+struct SliceStart {          // the exact lexer state at the start of a slice (thread 0's fold)
+  uint8_t in_word, last_tok;
+  uint16_t depth;
+  int32_t n_close, n_items;
+};
+
+struct CtaLayout {           // dynamic shared memory of k_newick_cta for a family of T tips
+  int n_items, n_levels;
+  size_t len, id, lvl, kind, pid, pl, cnt, sum, start, total;
+  __host__ __device__ explicit CtaLayout(int T, int nt) {
+    n_items = 2 * T - 2;     // T tips + T-2 ')'
+    n_levels = T;            // depth <= T-2
+    size_t at = 0;
+    auto take = [&](size_t bytes) { const size_t o = at; at += (bytes + 15) / 16 * 16; return o; };
+    len = take((size_t)n_items * 8);    // double: the node's branch length (before S5: the text position, low word)
+    id = take((size_t)n_items * 4);     // int32: xMSA row of a tip / operation index of a ')'
+    lvl = take((size_t)n_items * 2);    // uint16: depth of the node's parent list
+    kind = take((size_t)n_items);       // uint8: K_TIP / K_CLOSE
+    pid = take((size_t)n_levels * 8);   // int2: the two children filed under a level
+    pl = take((size_t)n_levels * 16);   // double2: their branch lengths
+    cnt = take((size_t)n_levels);       // uint8: how many are filed
+    sum = take((size_t)nt * sizeof(SliceSummary));
+    start = take((size_t)nt * sizeof(SliceStart));
+    total = at;
+  }
+};
+
+template <int NT>
+__global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
+  extern __shared__ __align__(16) unsigned char nw_smem[];
+  // s_flag[j] != 0: stage j (0 fold, 1 S3, 2 S5, 3 S6) leaves the tree to the host. One flag per stage: a stage reads
+  // only flags written before the barrier in front of it, so every thread takes the same branch around the barriers.
+  __shared__ int s_flag[4], s_warp_has[NT / 32], s_warp_open[NT / 32];
+  const int i = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int t = p.tree0 + i, T = p.T, n_ops = T - 2;
+  const CtaLayout lay(T, NT);
+  double* LEN = reinterpret_cast<double*>(nw_smem + lay.len);
+  int32_t* ID = reinterpret_cast<int32_t*>(nw_smem + lay.id);
+  uint16_t* LVL = reinterpret_cast<uint16_t*>(nw_smem + lay.lvl);
+  uint8_t* KIND = nw_smem + lay.kind;
+  int2* PID = reinterpret_cast<int2*>(nw_smem + lay.pid);
+  double2* PL = reinterpret_cast<double2*>(nw_smem + lay.pl);
+  uint8_t* CNT = nw_smem + lay.cnt;
+  SliceSummary* SUM = reinterpret_cast<SliceSummary*>(nw_smem + lay.sum);
+  SliceStart* START = reinterpret_cast<SliceStart*>(nw_smem + lay.start);
+  int2* __restrict__ ch = reinterpret_cast<int2*>(p.children) + (size_t)t * n_ops;
+  double2* __restrict__ bl = reinterpret_cast<double2*>(p.blen) + (size_t)t * n_ops;
+  const char* text = p.text + __ldg(p.offs + i);
+  const uint32_t L = __ldg(p.lens + i);
+  const uint32_t slice = ((L + NT - 1) / NT + 7u) & ~7u;          // a multiple of 8: slices start on the reader's words
+  const uint32_t a = min(L, (uint32_t)tid * slice), b = min(L, a + slice);
+  if (tid < 4) s_flag[tid] = 0;
+  for (int l = tid; l < lay.n_levels; l += NT) CNT[l] = 0;
+
+  // ---- S0: is the start of my slice inside a comment? ----
+  int my_last = 0;  // 0: no bracket in the slice, 1: its last bracket is '[', 2: ']'
+  for (uint32_t q = a; q < b; q += 8) {
+    const unsigned long long v = __ldg(reinterpret_cast<const unsigned long long*>(text + q));
+    const int n = (int)min(8u, b - q);
+    for (int j = 0; j < n; ++j) {
+      const int c = (int)((v >> (8 * j)) & 0xff);
+      if (c == '[') my_last = 1;
+      else if (c == ']') my_last = 2;
+    }
+  }
+  const unsigned has = __ballot_sync(0xffffffffu, my_last != 0), open = __ballot_sync(0xffffffffu, my_last == 1);
+  if (lane == 0) {
+    s_warp_has[wid] = has != 0;
+    s_warp_open[wid] = has ? (int)((open >> (31 - __clz(has))) & 1u) : 0;
+  }
+  __syncthreads();
+  bool in_comment = false;
+  {
+    const unsigned before = has & ((1u << lane) - 1u);
+    if (before) {
+      in_comment = (open >> (31 - __clz(before))) & 1u;
+    } else {
+      for (int w = wid - 1; w >= 0; --w)
+        if (s_warp_has[w]) {
+          in_comment = s_warp_open[w] != 0;
+          break;
+        }
+    }
+  }
+
+  // ---- S1: what my slice holds, not knowing what precedes it ----
+  {
+    SliceSummary sm{};
+    sm.nonempty = b > a;
+    bool com = in_comment, in_word = false, synced = false;
+    int last = K_NONE;  // the last token since the first structural one
+    Reader r(text, a);
+    for (uint32_t q = a; q < b; ++q, r.adv()) {
+      const int c = r.peek();
+      if (com) {
+        if (c == ']') com = false;
+        continue;
+      }
+      if (c == '[') { com = true; in_word = false; continue; }
+      if (is_blank(c)) { in_word = false; continue; }
+      const int st = structural(c);
+      if (st != K_NONE) {
+        if (!synced) { synced = true; sm.first_tok = (uint8_t)st; }
+        sm.n_open += st == K_OPEN;
+        sm.n_close += st == K_CLOSE;
+        last = st;
+        in_word = false;
+        continue;
+      }
+      if (!in_word) {  // a word starts here
+        in_word = true;
+        if (!synced) {
+          if (q == a) sm.lead_word = 1;
+          sm.early_runs = sm.early_runs < 2 ? sm.early_runs + 1 : 2;
+        } else {
+          const int wt = word_type(last);
+          sm.n_tips += wt == K_TIP;
+          last = wt;
+        }
+      }
+    }
+    sm.last_tok = (uint8_t)(synced ? last : K_NONE);
+    sm.in_word_out = in_word && !com;
+    SUM[tid] = sm;
+  }
+  __syncthreads();
+
+  // ---- thread 0 folds the summaries into the exact state at the start of every slice ----
+  if (tid == 0) {
+    int in_word = 0, last = K_NONE, depth = 0, n_close = 0, n_items = 0;
+    for (int k = 0; k < NT; ++k) {
+      SliceStart st;
+      st.in_word = (uint8_t)in_word;
+      st.last_tok = (uint8_t)last;
+      st.depth = depth;
+      st.n_close = n_close;
+      st.n_items = n_items;
+      START[k] = st;
+      const SliceSummary sm = SUM[k];
+      if (!sm.nonempty) continue;
+      const int runs = (int)sm.early_runs - ((sm.lead_word && in_word) ? 1 : 0);
+      if (runs >= 1) {  // a new word before the slice's first structural token: its kind follows from what came before
+        const int wt = word_type(last);
+        n_items += wt == K_TIP;
+        last = wt;
+      }
+      if (sm.first_tok != K_NONE) {
+        depth += (int)sm.n_open - (int)sm.n_close;
+        n_items += (int)sm.n_tips + (int)sm.n_close;
+        n_close += sm.n_close;
+        last = sm.last_tok;
+      }
+      in_word = sm.in_word_out;
+    }
+    // a tree of this family ends with ';' at depth 0 and has T tips and T-2 ')'
+    if (last != K_SEMI || depth != 0 || n_close != n_ops || n_items != lay.n_items) s_flag[0] = 1;
+  }
+  __syncthreads();
+
+  if (!s_flag[0]) {
+    // ---- S3: the exact pass: token grammar, one item per node ----
+    {
+      const SliceStart st = START[tid];
+      bool com = in_comment, in_word = st.in_word != 0, bad = false;
+      int last = st.last_tok, depth = st.depth, nc = st.n_close, ni = st.n_items;
+      Reader r(text, a);
+      for (uint32_t q = a; q < b; ++q, r.adv()) {
+        const int c = r.peek();
+        if (com) {
+          if (c == ']') com = false;
+          continue;
+        }
+        if (c == '[') { com = true; in_word = false; continue; }
+        if (is_blank(c)) { in_word = false; continue; }
+        const int stc = structural(c);
+        if (stc != K_NONE) {
+          in_word = false;
+          if (!may_follow(last, stc)) bad = true;   // (nothing may follow ';')
+          if (stc == K_OPEN) {
+            if (++depth > n_ops) bad = true;
+          } else if (stc == K_CLOSE) {
+            if (depth <= 0 || ni >= lay.n_items) {
+              bad = true;
+            } else {
+              KIND[ni] = K_CLOSE;
+              LVL[ni] = (uint16_t)depth;
+              ID[ni] = nc;
+              reinterpret_cast<uint32_t*>(LEN + ni)[0] = q + 1;
+            }
+            ++ni;
+            ++nc;
+            --depth;
+          } else if (stc == K_COMMA) {
+            if (depth <= 0) bad = true;
+          } else if (stc == K_SEMI) {
+            if (depth != 0) bad = true;
+          }
+          last = stc;
+          continue;
+        }
+        if (!in_word) {
+          in_word = true;
+          const int wt = word_type(last);
+          if (wt == K_BAD) bad = true;
+          if (wt == K_TIP) {
+            if (depth <= 0 || ni >= lay.n_items) {
+              bad = true;
+            } else {
+              KIND[ni] = K_TIP;
+              LVL[ni] = (uint16_t)depth;
+              reinterpret_cast<uint32_t*>(LEN + ni)[0] = q;
+            }
+            ++ni;
+          }
+          last = wt;
+        }
+      }
+      if (bad) s_flag[1] = 1;
+    }
+    __syncthreads();
+  }
+
+  if (!s_flag[0] && !s_flag[1]) {
+    // ---- S5: one thread per node: label -> row, branch length -> double ----
+    bool bad = false;
+    for (int it = tid; it < lay.n_items; it += NT) {
+      const uint32_t pos = reinterpret_cast<const uint32_t*>(LEN + it)[0];
+      Reader r(text, pos);
+      if (KIND[it] == K_TIP) {
+        uint32_t h = 2166136261u;
+        uint64_t first8 = 0;
+        int len = 0;
+        for (int cc = r.peek(); !is_delim(cc); cc = r.peek()) {
+          h = (h ^ (uint32_t)cc) * 16777619u;
+          if (len < 8) first8 |= (uint64_t)cc << (8 * len);
+          ++len;
+          r.adv();
+        }
+        const int row = find_label(p.labels, text, pos, len, h, first8);
+        if (row < 0) bad = true;
+        ID[it] = row;
+      } else {
+        skip(r);
+        while (!is_delim(r.peek())) r.adv();  // inner label, ignored
+      }
+      double v = 0.0;
+      if (!branch_length(r, &v)) bad = true;
+      LEN[it] = v;
+    }
+    if (bad) s_flag[2] = 1;
+    __syncthreads();
+  }
+
+  if (tid == 0 && !s_flag[0] && !s_flag[1] && !s_flag[2]) {
+    // ---- S6: children to parents, in text order ----
+    int root_child = 0, top0 = 0, top1 = 0, c1 = 0;
+    double root_blen = 0.0, topl0 = 0.0, topl1 = 0.0;
+    bool bad = false, done = false;
+    for (int it = 0; it < lay.n_items && !bad; ++it) {
+      int lvl = LVL[it], id = ID[it];
+      const double len = LEN[it];
+      if (KIND[it] == K_CLOSE) {
+        if (lvl == 1) {  // the trifurcation, last
+          if (c1 != 3 || id != n_ops - 1 || it != lay.n_items - 1) bad = true;
+          done = true;
+          break;
+        }
+        if (CNT[lvl] != 2) { bad = true; break; }
+        ch[id] = PID[lvl];
+        bl[id] = PL[lvl];
+        CNT[lvl] = 0;
+        id += T;
+        --lvl;
+      }
+      if (lvl == 1) {
+        if (c1 == 0) { root_child = id; root_blen = len; }
+        else if (c1 == 1) { top0 = id; topl0 = len; }
+        else if (c1 == 2) { top1 = id; topl1 = len; }
+        else bad = true;
+        ++c1;
+      } else {
+        const int k = CNT[lvl];
+        if (k == 0) { PID[lvl].x = id; PL[lvl].x = len; }
+        else if (k == 1) { PID[lvl].y = id; PL[lvl].y = len; }
+        else bad = true;
+        CNT[lvl] = (uint8_t)(k + 1);
+      }
+    }
+    if (bad || !done) {
+      s_flag[3] = 1;
+    } else {
+      ch[n_ops - 1] = make_int2(top0, top1);
+      bl[n_ops - 1] = make_double2(topl0, topl1);
+      p.root_child[t] = root_child;
+      p.root_blen[t] = root_blen;
+      p.on_pat[t] = (root_child == 0 || top0 == 0 || top1 == 0) ? 1 : 0;
+      p.status[t] = 0;
+    }
+  }
+  __syncthreads();
+  if (s_flag[0] | s_flag[1] | s_flag[2] | s_flag[3]) {
+    // stand-in (see k_newick): the host parser decides what the tree really is
+    for (int op = tid; op < n_ops; op += NT) {
+      ch[op] = op == 0 ? make_int2(1, 2) : make_int2(T + op - 1, op + 2);
+      bl[op] = make_double2(kEpsLen, kEpsLen);
+    }
+    if (tid == 0) {
+      p.root_child[t] = 0;
+      p.root_blen[t] = kEpsLen;
+      p.on_pat[t] = 1;
+      p.status[t] = 1;
+    }
+  }
+}
 __global__ void __launch_bounds__(32) k_split(const uint8_t* __restrict__ on_pat, int t0, int n, int32_t* __restrict__ list,
                                               int32_t* __restrict__ n_pat_out) {
   const int lane = threadIdx.x;
@@ -225,9 +588,26 @@ __global__ void __launch_bounds__(32) k_split(const uint8_t* __restrict__ on_pat
 
 }  // namespace
 
+constexpr int kCtaWide = 256, kCtaNarrow = 128;   // threads per tree: long strings get more slices
+static int cta_threads(int n_tips) { return n_tips >= 300 ? kCtaWide : kCtaNarrow; }
+bool newick_cta_ok(int n_tips) { return n_tips < 65535 && CtaLayout(n_tips, cta_threads(n_tips)).total <= (size_t)200 * 1024; }
+
 void launch_newick(const NewickDev& p, cudaStream_t s) {
   if (p.n <= 0) return;
-  k_newick<<<(p.n + 31) / 32, 32, 0, s>>>(p);
+  const bool cta = p.kernel == 2 || (p.kernel == 0 && newick_cta_ok(p.T));
+  if (!cta) {
+    k_newick<<<(p.n + 31) / 32, 32, 0, s>>>(p);
+    return;
+  }
+  const int nt = cta_threads(p.T);
+  const size_t smem = CtaLayout(p.T, nt).total;
+  if (nt == kCtaWide) {
+    ensure_dynamic_smem(reinterpret_cast<const void*>(&k_newick_cta<kCtaWide>), smem);
+    k_newick_cta<kCtaWide><<<p.n, kCtaWide, smem, s>>>(p);
+  } else {
+    ensure_dynamic_smem(reinterpret_cast<const void*>(&k_newick_cta<kCtaNarrow>), smem);
+    k_newick_cta<kCtaNarrow><<<p.n, kCtaNarrow, smem, s>>>(p);
+  }
 }
 
 void launch_split(const uint8_t* on_pat, int t0, int n, int32_t* list, int32_t* n_pat_out, cudaStream_t s) {

@@ -12,9 +12,13 @@ pytestmark = pytest.mark.gpu
 OPS = ("children", "blen", "root_child", "root_blen")
 
 
-def _family(fam, labels):
+KERNELS = [1, 2]   # k_newick (one thread per tree), k_newick_cta (one CTA per tree; the default where it fits)
+
+
+def _family(fam, labels, kernel=0):
     f = device.Family(fam)
     f.set_labels(labels)
+    f.set_option("newick_kernel", kernel)
     return f
 
 
@@ -22,11 +26,12 @@ def _on_patterns(ops):
     return ((ops["root_child"] == 0) | (ops["children"][:, -1, 0] == 0) | (ops["children"][:, -1, 1] == 0)).astype(np.uint8)
 
 
+@pytest.mark.parametrize("kernel", KERNELS)
 @pytest.mark.parametrize("name", GOLDEN_NAMES)
-def test_ops_bit_identical_on_goldens(name):
+def test_ops_bit_identical_on_goldens(name, kernel):
     fam, tb, exp, meta = load_golden(name)
     nw, labels = [str(s) for s in meta["newicks"]], [str(s) for s in meta["labels"]]
-    f = _family(fam, labels)
+    f = _family(fam, labels, kernel)
     got = f.parse_newick(nw)
     assert not got["left_to_host"].any()
     for k in OPS:
@@ -103,8 +108,9 @@ def _decorate(rng, nwk):
     return s
 
 
-@pytest.mark.parametrize("n_leaves,n_trees", [(3, 400), (7, 1500), (57, 4000), (200, 3000), (1000, 1200)])
-def test_ops_bit_identical_on_random_trees(n_leaves, n_trees):
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("n_leaves,n_trees", [(3, 400), (7, 1500), (57, 4000), (200, 3000), (1000, 1200), (3000, 64)])
+def test_ops_bit_identical_on_random_trees(n_leaves, n_trees, kernel):
     rng = np.random.default_rng(100 + n_leaves)
     labels = ["naive"] + [f"seq_{i:04d}_long" if i % 3 == 0 else str(i) for i in range(n_leaves)]
     nw = []
@@ -124,7 +130,7 @@ def test_ops_bit_identical_on_random_trees(n_leaves, n_trees):
     # ... as long as it has the right number of tips: parse_newick only reads n_tips
     fam["n_tips"] = n_leaves + 1
     fam["tip_codes"] = np.zeros((n_leaves + 1, fam["n_sites"]), dtype=np.uint8)
-    f = _family(fam, labels)
+    f = _family(fam, labels, kernel)
     got = f.parse_newick(nw)
     f.close()
     assert not got["left_to_host"].any()
@@ -133,7 +139,35 @@ def test_ops_bit_identical_on_random_trees(n_leaves, n_trees):
     assert np.array_equal(got["on_patterns"], _on_patterns(ref))
 
 
-def test_hard_spellings_go_to_the_host_parser_and_score_the_same():
+def test_lenient_spellings_are_left_to_the_host_by_the_cta_parser():
+    """What the lenient host parser takes beyond the strict grammar - a missing comma, text after ';' - the
+    one-CTA-per-tree parser declines (the one-thread-per-tree parser reads them as the host does); the call's
+    results are the host parser's either way."""
+    fam, tb, exp, meta = load_golden("synth_n12")
+    nw, labels = [str(s) for s in meta["newicks"]], [str(s) for s in meta["labels"]]
+    odd = list(nw)
+    odd[0] = nw[0] + " trailing text (ignored"
+    i = nw[1].index(",")
+    odd[1] = nw[1][:i] + " " + nw[1][i + 1:]
+    odd[2] = "  \t" + nw[2].replace(",", " ,\n", 3)          # blanks are fine everywhere
+    ref = host.newick_to_ops(odd, labels)
+    R = tb["rates"].shape[1]
+    for kernel, left in ((1, []), (2, [0, 1])):
+        f = _family(fam, labels, kernel)
+        got = f.parse_newick(odd)
+        assert np.flatnonzero(got["left_to_host"]).tolist() == left
+        keep = got["left_to_host"] == 0
+        for k in OPS:
+            assert np.array_equal(got[k][keep], ref[k][keep]), k
+        ll = f.score_newick(odd, tb["er"], tb["pi"], R, alpha=meta["alpha"])
+        assert f.timings()["newick_host_trees"] == len(left)
+        ll_arr = f.score(dict(tb, **ref))
+        f.close()
+        assert np.array_equal(ll, ll_arr, equal_nan=True)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_hard_spellings_go_to_the_host_parser_and_score_the_same(kernel):
     fam, tb, exp, meta = load_golden("synth_n12")
     nw, labels = [str(s) for s in meta["newicks"]], [str(s) for s in meta["labels"]]
     B = len(nw)
@@ -148,7 +182,7 @@ def test_hard_spellings_go_to_the_host_parser_and_score_the_same():
         return s[:i + 1] + {"long": f"{v:.30f}", "plus": "+" + repr(v), "hex": v.hex()}[how] + s[j:]
     hard[1], hard[3], hard[B - 1] = respell(nw[1], "long"), respell(nw[3], "plus"), respell(nw[B - 1], "hex")
     ref = host.newick_to_ops(hard, labels)
-    f = _family(fam, labels)
+    f = _family(fam, labels, kernel)
     got = f.parse_newick(hard)
     assert got["left_to_host"].tolist() == [1 if i in (1, 3, B - 1) else 0 for i in range(B)]
     keep = got["left_to_host"] == 0
@@ -166,11 +200,12 @@ def test_hard_spellings_go_to_the_host_parser_and_score_the_same():
         assert np.array_equal(out[k], out_arr[k], equal_nan=True), k
 
 
-def test_malformed_trees_fail_with_the_host_parsers_message():
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_malformed_trees_fail_with_the_host_parsers_message(kernel):
     fam, tb, exp, meta = load_golden("synth_n12")
     nw, labels = [str(s) for s in meta["newicks"]], [str(s) for s in meta["labels"]]
     R = tb["rates"].shape[1]
-    f = _family(fam, labels)
+    f = _family(fam, labels, kernel)
     cases = {
         "unknown": nw[2].replace("," + labels[3] + "[", ",nobody[", 1).replace("(" + labels[3] + "[", "(nobody[", 1),
         "twice": nw[2].replace("," + labels[3] + "[", "," + labels[4] + "[", 1).replace("(" + labels[3] + "[", "(" + labels[4] + "[", 1),
