@@ -222,8 +222,10 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
  * "device_plan" (1: the traversal programs are built on the device by k_plan from the operation
  * lists as the caller holds them; 0: by the host planner threads; -1 = default: by the device when
  * the handle's host threads would not keep ahead of the kernels - the programs are the same),
- * "newick_kernel" (lh_score_newick: 0 = default, the one-CTA-per-tree parser where its tables fit shared memory;
- * 1 the one-thread-per-tree parser; 2 the one-CTA-per-tree parser),
+ * "newick_kernel" (lh_score_newick: 0 / 2 = default, the one-CTA-per-tree parser, with the one-thread-per-tree
+ * parser behind it for trees nested deeper than its tables; 1 = the one-thread-per-tree parser alone),
+ * "parse_reserve" (default 1: pruning CTAs per SM given up during lh_score_newick so that the parser of the
+ * next chunk runs beside the pruning of this one),
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never
  * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "pipe_waves" (default 4:
  * lh_score_batch launches a chunk's kernels every that many waves of CTAs), "stream" (a

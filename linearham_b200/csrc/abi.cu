@@ -233,6 +233,7 @@ struct lh_family {
   lhb::HmmOut ho{};
   int chunk = 0, chunk_pipe = 0, wave_pipe = 0, wave_unit = 0, seg = 0, occ[2] = {0, 0};
   int opt_open_unit = 1, opt_chunk_growth = 1;
+  int opt_parse_reserve = 1;  // pruning CTAs per SM given up for the parser while text is coming in
   int opt_newick_kernel = 0;  // 0 auto, 1 k_newick (one thread per tree), 2 k_newick_cta (one CTA per tree)
   double stage_ratio = 1.0;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
@@ -255,8 +256,8 @@ struct lh_family {
   lhb::LabelTableDev lt{};
   bool labels_set = false;
   bool newick_mode = false;           // the current batch came in as text
-  DevBuf d_text[kRing];
-  cudaEvent_t text_copied[kRing] = {};
+  DevBuf d_textbuf[2], d_items, d_toffs, d_tlens;   // the text of a chunk (two alternate), parser scratch, string offsets / lengths
+  cudaEvent_t text_copied = nullptr, parsed_ev[2] = {};
   DevBuf d_on_pat, d_nw_status, d_chunk_npat;
   PinBuf h_nw_status, h_chunk_npat;
   std::vector<cudaEvent_t> seg_ev;    // pairs around the k_newick launches of the current call
@@ -287,9 +288,8 @@ void lh_family_destroy(lh_family_t* f) {
                     &f->d_dgerm, &f->d_dj, &f->d_jgerm, &f->d_gs, &f->d_vds, &f->d_djs, &f->cols[0].d_codes_t,
                     &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_counters,
                     &f->d_rate_ll, &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags,
-                    &f->d_label_slots, &f->d_label_off, &f->d_label_chars, &f->d_text[0], &f->d_text[1], &f->d_text[2],
+                    &f->d_label_slots, &f->d_label_off, &f->d_label_chars, &f->d_textbuf[0], &f->d_textbuf[1], &f->d_items, &f->d_toffs, &f->d_tlens,
                     &f->d_on_pat, &f->d_nw_status, &f->d_chunk_npat};
-  static_assert(lh_family::kRing == 3, "d_text slots are listed by hand above");
   for (DevBuf* b : bufs) b->release();
   for (auto& r : f->h_ring) r.release();
   for (auto& c : f->cols) c.h_codes_t.release();
@@ -300,7 +300,8 @@ void lh_family_destroy(lh_family_t* f) {
   f->h_out.release();
   f->h_nw_status.release();
   f->h_chunk_npat.release();
-  for (auto& e : f->text_copied)
+  if (f->text_copied) cudaEventDestroy(f->text_copied);
+  for (auto& e : f->parsed_ev)
     if (e) cudaEventDestroy(e);
   for (auto& e : f->seg_ev) cudaEventDestroy(e);
   for (auto& e : f->ev)
@@ -525,7 +526,8 @@ int lh_family_create(lh_family_t** out, const lh_family_desc_t* d, int device) {
   cudaEventCreateWithFlags(&f->hmm_done, cudaEventDisableTiming);
   if (f->d_counters.reserve(64)) return bail(1);
   for (auto& ev : f->ring_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
-  for (auto& ev : f->text_copied) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&f->text_copied, cudaEventDisableTiming);
+  for (auto& ev : f->parsed_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&f->misc_ev, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&f->list_ev, cudaEventDisableTiming);
   for (auto& ev : f->ev) cudaEventCreate(&ev);
@@ -617,9 +619,11 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     f->opt_chunk_growth = value != 0;
   } else if (k == "open_unit") {
     f->opt_open_unit = value != 0;
+  } else if (k == "parse_reserve") {
+    if (value < 0 || value > 3) return fail("parse_reserve must be 0..3");
+    f->opt_parse_reserve = (int)value;
   } else if (k == "newick_kernel") {
     if (value < 0 || value > 2) return fail("newick_kernel must be 0 (auto), 1 (one thread per tree) or 2 (one CTA per tree)");
-    if (value == 2 && f->bound && !lhb::newick_cta_ok(f->fd.T)) return fail("the family is too large for the one-CTA-per-tree parser");
     f->opt_newick_kernel = (int)value;
   } else if (k == "device_plan") {
     if (value < -1 || value > 1) return fail("device_plan must be -1 (auto), 0 or 1");
@@ -790,8 +794,7 @@ int configure_batch(lh_family* f, int B, int R) {
   f->run_recorded = false;
   if (f->newick_mode) {
     if (f->d_on_pat.reserve((size_t)B) || f->d_nw_status.reserve((size_t)B) || f->h_nw_status.reserve((size_t)B)) return 1;
-    for (auto& d : f->d_text)
-      if (d.reserve(kTextSlotBytes)) return 1;
+    if (f->d_toffs.reserve((size_t)B * 8) || f->d_tlens.reserve((size_t)B * 4)) return 1;
   }
   if (f->dev_plan) {
     const size_t n2 = (size_t)B * (T - 2) * 2;
@@ -847,6 +850,9 @@ int configure_batch(lh_family* f, int B, int R) {
     pc.smem_slots = smem_slots;
     f->occ[g] = lhb::prune_max_ctas_per_sm(pc.sites_per_thread, pc.smem_slots);
     if (f->occ[g] < 1) return fail("pruning kernel cannot be resident with %d shared-memory slots", pc.smem_slots);
+    // Text input: the parser (k_newick_cta, 128 threads) of the next chunks runs beside the persistent pruning
+    // CTAs, which otherwise hold every register of an SM until their launch ends: leave it room.
+    if (f->newick_mode && f->occ[g] >= 4) f->occ[g] -= f->opt_parse_reserve;
     pc.log_threshold = std::log(1.0 / std::pow(2.0, 256));
     if (cset.codes_ns != pc.sites_per_thread) {
       // re-tile the tip codes for this NS (once per family, column set and NS)
@@ -1148,12 +1154,14 @@ int probe_window_from_text(lh_family* f, const lh_newick_batch_t* nb, int t0, in
   return 0;
 }
 
-// Copies the strings of trees [t0, t0+n) (lengths len[0..n)) into ring slot `slot`, queues their copy to
-// the slot's device text buffer on `cs` and their parse (k_newick) on the plan stream.
-// Slot layout: offs [n] uint32 | lens [n] uint32 | pad to 16 | strings, each NUL-terminated and 16-byte aligned.
-int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n, const int64_t* len, int slot, cudaStream_t cs) {
+// Copies the strings of trees [t0, t0+n) (lengths len[0..n)) into ring slot `slot` and queues their copy on `cs`
+// into the chunk's device text buffer at byte `text_at` (returns the bytes used through *used).
+// Slot layout: offs [n] uint64 (into the chunk's text buffer) | lens [n] uint32 | pad to 16 | strings, each
+// NUL-terminated and 16-byte aligned.
+int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n, const int64_t* len, int slot,
+                       char* d_chunk_text, size_t text_at, size_t* used, cudaStream_t cs) {
   if (f->ring_busy[slot]) {
-    LH_CUDA(cudaEventSynchronize(f->ring_ev[slot]));  // k_newick of the slot's previous segment has run
+    LH_CUDA(cudaEventSynchronize(f->ring_ev[slot]));  // the slot's previous segment has been copied
     f->ring_busy[slot] = false;
   }
   const auto t_a = std::chrono::steady_clock::now();
@@ -1162,46 +1170,102 @@ int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n,
     f->window_set = true;
   }
   uint8_t* base = f->h_ring[slot].as<uint8_t>();
-  uint32_t* offs = reinterpret_cast<uint32_t*>(base);
-  const size_t text0 = ((size_t)n * 8 + 15) / 16 * 16;
-  uint32_t* lens32 = offs + n;
+  uint64_t* offs = reinterpret_cast<uint64_t*>(base);
+  uint32_t* lens32 = reinterpret_cast<uint32_t*>(offs + n);
+  const size_t text0 = ((size_t)n * 12 + 15) / 16 * 16;
   size_t at = 0;
   for (int i = 0; i < n; ++i) {
-    offs[i] = (uint32_t)at;
+    offs[i] = (uint64_t)(text_at + at);
     lens32[i] = (uint32_t)len[i];
     at += ((size_t)len[i] + 1 + 15) / 16 * 16;
   }
-  const size_t total = text0 + at;
   ensure_pool(f);
   constexpr int kBlock = 8;  // trees per task
   f->pool->run((n + kBlock - 1) / kBlock, [&](int task, int) {
     const int lo = task * kBlock, hi = std::min(n, lo + kBlock);
     for (int i = lo; i < hi; ++i) {
-      uint8_t* dst = base + text0 + offs[i];
-      const size_t l = (size_t)len[i], padded = (l + 1 + 15) / 16 * 16;
+      uint8_t* dst = base + text0 + (size_t)(offs[i] - text_at);
+      const size_t l = (size_t)len[i];
       const size_t body = l / 16 * 16;  // whole 16-byte blocks stream straight from the caller's string
       stream_copy(dst, nb->newick[t0 + i], body);
       uint8_t tail[16] = {};
-      std::memcpy(tail, nb->newick[t0 + i] + body, l - body);
+      std::memcpy(tail, nb->newick[t0 + i] + body, l - body);   // the NUL and the padding come with it
       stream_copy(dst + body, tail, 16);
-      if (padded > body + 16) std::memset(dst + body + 16, 0, padded - body - 16);
     }
   });
   _mm_sfence();
   f->tm.ms_plan += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_a).count();
-  LH_CUDA(cudaMemcpyAsync(f->d_text[slot].p, base, total, cudaMemcpyHostToDevice, cs));
-  LH_CUDA(cudaEventRecord(f->text_copied[slot], cs));
-  f->tm.h2d_bytes += (int64_t)total;
+  LH_CUDA(cudaMemcpyAsync(d_chunk_text + text_at, base + text0, at, cudaMemcpyHostToDevice, cs));
+  LH_CUDA(cudaMemcpyAsync(f->d_toffs.as<uint64_t>() + t0, offs, (size_t)n * 8, cudaMemcpyHostToDevice, cs));
+  LH_CUDA(cudaMemcpyAsync(f->d_tlens.as<uint32_t>() + t0, lens32, (size_t)n * 4, cudaMemcpyHostToDevice, cs));
+  LH_CUDA(cudaEventRecord(f->ring_ev[slot], cs));
+  f->ring_busy[slot] = true;
+  f->tm.h2d_bytes += (int64_t)(at + (size_t)n * 12);
+  *used = at;
+  return 0;
+}
+
+// The strings of the chunk's trees [c0, c0+cn) -> one device text buffer (two alternate between chunks), in
+// segments of up to kTextSlotBytes through the pinned ring, then ONE parse of the whole chunk on the plan
+// stream: a launch of a few hundred trees leaves most of the GPU idle, and the parser of a chunk can only run
+// in the gaps the persistent pruning CTAs of the chunk before leave anyway. *k counts ring slots.
+int stage_text_chunk(lh_family* f, const lh_newick_batch_t* nb, int ci, int c0, int cn, int* k, cudaStream_t cs) {
+  std::vector<int64_t> lens(cn);
+  if (nb->length) {
+    std::copy(nb->length + c0, nb->length + c0 + cn, lens.begin());
+  } else {
+    ensure_pool(f);
+    f->pool->run((cn + 15) / 16, [&](int task, int) {
+      for (int i = task * 16; i < std::min(cn, task * 16 + 16); ++i) lens[i] = (int64_t)std::strlen(nb->newick[c0 + i]);
+    });
+  }
+  size_t chunk_bytes = 0;
+  for (int i = 0; i < cn; ++i) {
+    if (lens[i] < 0 || (uint64_t)lens[i] + 64 > kTextSlotBytes)
+      return fail("tree %d: a Newick string of %lld bytes is too long", c0 + i, (long long)lens[i]);
+    chunk_bytes += ((size_t)lens[i] + 1 + 15) / 16 * 16;
+  }
+  DevBuf& buf = f->d_textbuf[ci & 1];
   cudaStream_t ps = f->plan_stream;
-  LH_CUDA(cudaStreamWaitEvent(ps, f->text_copied[slot], 0));
+  // the buffer's previous chunk (ci - 2) must have been parsed before it is overwritten - or freed
+  if (ci >= 2) {
+    if (chunk_bytes > buf.cap) LH_CUDA(cudaEventSynchronize(f->parsed_ev[ci & 1]));
+    else LH_CUDA(cudaStreamWaitEvent(cs, f->parsed_ev[ci & 1], 0));
+  }
+  if (buf.reserve(chunk_bytes + 64)) return 1;
+  size_t text_at = 0;
+  for (int i = 0; i < cn;) {
+    size_t bytes = 0;
+    int n = 0;
+    while (i + n < cn) {
+      const size_t add = ((size_t)lens[i + n] + 1 + 15) / 16 * 16 + 12;
+      if (n && bytes + add + 16 > kTextSlotBytes) break;
+      bytes += add;
+      ++n;
+    }
+    size_t used = 0;
+    if (stage_text_segment(f, nb, c0 + i, n, lens.data() + i, *k % lh_family::kRing, buf.as<char>(), text_at, &used, cs)) return 1;
+    text_at += used;
+    i += n;
+    ++*k;
+  }
+  LH_CUDA(cudaEventRecord(f->text_copied, cs));
+  LH_CUDA(cudaStreamWaitEvent(ps, f->text_copied, 0));
   lhb::NewickDev p{};
   p.T = f->fd.T;
-  p.tree0 = t0;
-  p.n = n;
-  p.text = f->d_text[slot].as<char>() + text0;
-  p.offs = f->d_text[slot].as<uint32_t>();
-  p.lens = p.offs + n;
+  p.tree0 = c0;
+  p.n = cn;
+  p.text = buf.as<char>();
+  p.offs = f->d_toffs.as<uint64_t>() + c0;
+  p.lens = f->d_tlens.as<uint32_t>() + c0;
   p.kernel = f->opt_newick_kernel;
+  if (p.kernel != 1) {
+    // (one scratch: the parses of a call run one after the other on the plan stream; growing it waits for them)
+    const size_t need = lhb::newick_items_bytes(p.T, cn);
+    if (need > f->d_items.cap) LH_CUDA(cudaStreamSynchronize(ps));
+    if (f->d_items.reserve(need)) return 1;
+    p.items = f->d_items.as<unsigned char>();
+  }
   p.labels = f->lt;
   p.children = f->d_rchildren.as<int32_t>();
   p.blen = f->d_rblen.as<double>();
@@ -1222,37 +1286,8 @@ int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n,
     cudaEventRecord(f->seg_ev[f->n_seg_ev + 1], ps);
     f->n_seg_ev += 2;
   }
-  f->tm.kernel_launches += 1;
-  LH_CUDA(cudaEventRecord(f->ring_ev[slot], ps));
-  f->ring_busy[slot] = true;
-  return 0;
-}
-
-// The strings of trees [c0, c0+cn) -> the device, in segments of up to kTextSlotBytes; *k counts ring slots.
-int stage_text_chunk(lh_family* f, const lh_newick_batch_t* nb, int c0, int cn, int* k, cudaStream_t cs) {
-  std::vector<int64_t> lens(cn);
-  if (nb->length) {
-    std::copy(nb->length + c0, nb->length + c0 + cn, lens.begin());
-  } else {
-    ensure_pool(f);
-    f->pool->run((cn + 15) / 16, [&](int task, int) {
-      for (int i = task * 16; i < std::min(cn, task * 16 + 16); ++i) lens[i] = (int64_t)std::strlen(nb->newick[c0 + i]);
-    });
-  }
-  for (int i = 0; i < cn;) {
-    size_t bytes = 0;
-    int n = 0;
-    while (i + n < cn) {
-      const size_t add = ((size_t)lens[i + n] + 1 + 15) / 16 * 16 + 8;
-      if (n && bytes + add + 16 > kTextSlotBytes) break;
-      bytes += add;
-      ++n;
-    }
-    if (bytes + 16 > kTextSlotBytes) return fail("tree %d: a Newick string of %lld bytes is too long", c0 + i, (long long)lens[i]);
-    if (stage_text_segment(f, nb, c0 + i, n, lens.data() + i, *k % lh_family::kRing, cs)) return 1;
-    i += n;
-    ++*k;
-  }
+  f->tm.kernel_launches += p.kernel != 1 ? 2 : 1;
+  LH_CUDA(cudaEventRecord(f->parsed_ev[ci & 1], ps));
   return 0;
 }
 
@@ -1672,7 +1707,7 @@ int score_call(lh_family* f, const lh_tree_batch_t* tb, const lh_newick_batch_t*
   for (int ci = 0, k = 0; ci < f->n_chunks; ++ci) {
     const int c0 = st[ci], cn = st[ci + 1] - st[ci];
     if (nb) {
-      if (stage_text_chunk(f, nb, c0, cn, &k, cs)) return 1;
+      if (stage_text_chunk(f, nb, ci, c0, cn, &k, cs)) return 1;
     } else {
       for (int t0 = c0; t0 < st[ci + 1]; t0 += f->seg, ++k)
         if (stage_segment(f, tb, t0, std::min(f->seg, st[ci + 1] - t0), k % lh_family::kRing, cs)) return 1;
@@ -1940,7 +1975,7 @@ int lh_debug_parse_newick(lh_family_t* f, const lh_newick_batch_t* nb, int32_t* 
     return 1;
   }
   int k = 0;
-  const int rc2 = stage_text_chunk(f, nb, 0, B, &k, f->copy_stream);
+  const int rc2 = stage_text_chunk(f, nb, 0, 0, B, &k, f->copy_stream);
   f->newick_mode = false;
   if (rc2) return 1;
   LH_CUDA(cudaStreamSynchronize(f->plan_stream));

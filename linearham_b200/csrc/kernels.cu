@@ -780,7 +780,11 @@ __global__ void __launch_bounds__(128) k_edge(FamilyDev f, BatchDev b, EdgeCfg c
     if (acc_cnt) site_lk += acc_cnt * cfg.log_threshold;   // :1247-1251
     // naive-sequence correction (src/PhyloHMM.cpp:229-237)
     if (code != 4) site_lk -= eig[36 + code];
-    b.xe[(size_t)t * S + site] = exp(site_lk);
+    // xmsa_emission_.array().exp() (src/PhyloHMM.cpp:239) is Eigen's packet exp (pexp_double; SSE2 Packet2d in the
+    // reference's build): 2^n * exp(g) with n = floor(x log2(e) + 1/2), which is 0 once n <= -1023 - where libm
+    // returns a subnormal; the odd last element of the vector goes through libm
+    const bool flush = site < (S & ~1) && floor(fma(site_lk, 1.4426950408889634073599, 0.5)) <= -1023.0;
+    b.xe[(size_t)t * S + site] = flush ? 0.0 : exp(site_lk);
   }
 }
 
@@ -902,6 +906,26 @@ __device__ __forceinline__ double csc_dot(const CscDev& m, const double* prev, i
   return acc;
 }
 
+// The same dot product with the zero terms kept, for a previous row that holds an infinity or a NaN (ScaleMatrix
+// multiplies a whole row by 2^256 while ANY entry is below 2^-256, so in the underflow regime the large entries
+// overflow): the reference's dense product then meets inf * 0 = NaN, which dropping the zero terms would hide.
+__device__ double csc_dot_dense(const CscDev& m, const double* prev, int j) {
+  double acc = 0.0;
+  int p = m.colptr[j];
+  const int e = m.colptr[j + 1];
+  int next_row = p < e ? __double2loint(__ldg(m.ent + p).y) : -1;
+  for (int k = 0; k < m.rows; ++k) {
+    double coef = 0.0;
+    if (k == next_row) {
+      coef = __ldg(m.ent + p).x;
+      ++p;
+      next_row = p < e ? __double2loint(__ldg(m.ent + p).y) : -1;
+    }
+    acc += prev[k] * coef;
+  }
+  return acc;
+}
+
 // ComputeJunctionForwardProbabilities (src/HMM.cpp:1107-1139). Most (state, site) pairs of a junction
 // are silent - the state cannot emit at the site, its emission is 0 (FillJunctionEmission) - and their
 // value is (dot product) * 0. While the previous row is tame (finite, <= 1e150; the matrices are checked
@@ -910,7 +934,7 @@ __device__ __forceinline__ double csc_dot(const CscDev& m, const double* prev, i
 __device__ int junction_forward(const FamilyDev& f, const CscDev& t_in, const CscDev& t_jj,
                                 const int32_t* __restrict__ inds_rm, const int32_t* __restrict__ valid_off,
                                 const int2* __restrict__ valid, int L, int Sj, const double* __restrict__ xe,
-                                double*& prev, double*& cur, int count, bool tame, double* fwd_out,
+                                double*& prev, double*& cur, int count, bool& tame, double* fwd_out,
                                 int32_t* cnt_out, int lane) {
   for (int i = 0; i < L; ++i) {
     const CscDev& m = (i == 0) ? t_in : t_jj;
@@ -924,7 +948,7 @@ __device__ int junction_forward(const FamilyDev& f, const CscDev& t_in, const Cs
       }
     } else {
       for (int j = lane; j < Sj; j += 32) {
-        double acc = csc_dot(m, prev, j);
+        double acc = tame ? csc_dot(m, prev, j) : csc_dot_dense(m, prev, j);
         const int idx = inds_rm[(size_t)i * Sj + j];
         acc *= (idx < 0) ? 0.0 : xe[idx];   // FillJunctionEmission: 0 where idx == -1
         cur[j] = acc;
@@ -989,7 +1013,7 @@ __global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o, 
     if (f.has_d) {
       // ComputeGermlineForwardProbabilities for D (src/HMM.cpp:1160-1177; padding terms are ones)
       for (int g = lane; g < f.n_d; g += 32) {
-        double v = csc_dot(f.t_vd_d, prev, g);
+        double v = tame ? csc_dot(f.t_vd_d, prev, g) : csc_dot_dense(f.t_vd_d, prev, g);
         v *= e_dgerm[g];
         cur[g] = v;
       }
@@ -1005,7 +1029,7 @@ __global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o, 
     }
     const CscDev& t_out = f.has_d ? f.t_dj_j : f.t_vd_d;
     for (int g = lane; g < f.n_j; g += 32) {
-      double v = csc_dot(t_out, prev, g);
+      double v = tame ? csc_dot(t_out, prev, g) : csc_dot_dense(t_out, prev, g);
       v *= e_jgerm[g];
       v *= f.jpad_trans[g];
       v *= e_jpad[g];

@@ -133,11 +133,14 @@ struct LabelTableDev {
 };
 struct NewickDev {
   int32_t T;
-  int32_t tree0, n;            // batch index of the segment's first tree, trees in the segment
-  const char* text;            // the segment's strings, each NUL-terminated and starting on a 16-byte boundary
-  const uint32_t* offs;        // [n] start of each string in text
+  int32_t tree0, n;            // batch index of the chunk's first tree, trees in the chunk
+  const char* text;            // the chunk's strings, each NUL-terminated and starting on a 16-byte boundary
+  const uint64_t* offs;        // [n] start of each string in text
   const uint32_t* lens;        // [n] strlen of each string
-  int32_t kernel;              // 0: pick by family size, 1: k_newick (one thread per tree), 2: k_newick_cta
+  int32_t kernel;              // 0 / 2: k_newick_cta (one CTA per tree), then k_newick for the trees too deep for
+                               //        its tables; 1: k_newick alone (one thread per tree)
+  unsigned char* items;        // k_newick_cta scratch: newick_items_bytes(T, n)
+  int32_t only_deferred;       // (set by launch_newick) k_newick takes only the trees k_newick_cta marked status 2
   LabelTableDev labels;
   int32_t* children;           // [B][T-2][2]   (batch arrays, as in PlanDev)
   double* blen;                // [B][T-2][2]
@@ -148,7 +151,7 @@ struct NewickDev {
                                //     this parser does not decide) - the tree then gets a harmless stand-in
 };
 void launch_newick(const NewickDev& p, cudaStream_t s);
-bool newick_cta_ok(int n_tips);  // the cooperative parser's shared-memory tables fit
+size_t newick_items_bytes(int n_tips, int n_trees);
 // stable partition of the chunk's trees [t0, t0+n) by on_pat into list[t0..) (pattern trees first);
 // n_pat_out[0] = how many
 void launch_split(const uint8_t* on_pat, int t0, int n, int32_t* list, int32_t* n_pat_out, cudaStream_t s);

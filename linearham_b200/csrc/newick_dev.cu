@@ -100,6 +100,7 @@ __global__ void __launch_bounds__(32) k_newick(NewickDev p) {
   const int i = blockIdx.x * 32 + threadIdx.x;
   if (i >= p.n) return;
   const int t = p.tree0 + i, T = p.T, n_ops = T - 2;
+  if (p.only_deferred && p.status[t] != 2) return;   // second pass behind k_newick_cta: the trees it found too deep
   int2* __restrict__ ch = reinterpret_cast<int2*>(p.children) + (size_t)t * n_ops;
   double2* __restrict__ bl = reinterpret_cast<double2*>(p.blen) + (size_t)t * n_ops;
   const char* text = p.text + __ldg(p.offs + i);
@@ -262,21 +263,19 @@ struct SliceStart {          // the exact lexer state at the start of a slice (t
   int32_t n_close, n_items;
 };
 
-struct CtaLayout {           // dynamic shared memory of k_newick_cta for a family of T tips
-  int n_items, n_levels;
-  size_t len, id, lvl, kind, pid, pl, cnt, sum, start, total;
-  __host__ __device__ explicit CtaLayout(int T, int nt) {
-    n_items = 2 * T - 2;     // T tips + T-2 ')'
-    n_levels = T;            // depth <= T-2
+constexpr int kCtaLevels = 256;   // depth the per-level tables are sized for; deeper trees go to k_newick
+// Per-tree item arrays (global scratch, L2-resident: written in S3/S5, read in S5/S6 by the same CTA):
+//   len [N] double (before S5: the text position in the low word) | id [N] int32 (xMSA row of a tip /
+//   operation index of a ')') | lvl [N] uint16 (depth of the parent's child list; bit 15: the node is a ')')
+__host__ __device__ inline size_t cta_items_stride(int n_tips) { return ((size_t)(2 * n_tips - 2) * 14 + 15) / 16 * 16; }
+struct CtaLayout {           // dynamic shared memory of k_newick_cta
+  size_t pid, pl, cnt, sum, start, total;
+  __host__ __device__ explicit CtaLayout(int nt) {
     size_t at = 0;
     auto take = [&](size_t bytes) { const size_t o = at; at += (bytes + 15) / 16 * 16; return o; };
-    len = take((size_t)n_items * 8);    // double: the node's branch length (before S5: the text position, low word)
-    id = take((size_t)n_items * 4);     // int32: xMSA row of a tip / operation index of a ')'
-    lvl = take((size_t)n_items * 2);    // uint16: depth of the node's parent list
-    kind = take((size_t)n_items);       // uint8: K_TIP / K_CLOSE
-    pid = take((size_t)n_levels * 8);   // int2: the two children filed under a level
-    pl = take((size_t)n_levels * 16);   // double2: their branch lengths
-    cnt = take((size_t)n_levels);       // uint8: how many are filed
+    pid = take((size_t)(kCtaLevels + 1) * 8);   // int2: the two children filed under a level
+    pl = take((size_t)(kCtaLevels + 1) * 16);   // double2: their branch lengths
+    cnt = take((size_t)(kCtaLevels + 1));       // uint8: how many are filed
     sum = take((size_t)nt * sizeof(SliceSummary));
     start = take((size_t)nt * sizeof(SliceStart));
     total = at;
@@ -288,14 +287,15 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
   extern __shared__ __align__(16) unsigned char nw_smem[];
   // s_flag[j] != 0: stage j (0 fold, 1 S3, 2 S5, 3 S6) leaves the tree to the host. One flag per stage: a stage reads
   // only flags written before the barrier in front of it, so every thread takes the same branch around the barriers.
-  __shared__ int s_flag[4], s_warp_has[NT / 32], s_warp_open[NT / 32];
+  __shared__ int s_flag[4], s_deep, s_warp_has[NT / 32], s_warp_open[NT / 32];
   const int i = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int t = p.tree0 + i, T = p.T, n_ops = T - 2;
-  const CtaLayout lay(T, NT);
-  double* LEN = reinterpret_cast<double*>(nw_smem + lay.len);
-  int32_t* ID = reinterpret_cast<int32_t*>(nw_smem + lay.id);
-  uint16_t* LVL = reinterpret_cast<uint16_t*>(nw_smem + lay.lvl);
-  uint8_t* KIND = nw_smem + lay.kind;
+  const CtaLayout lay(NT);
+  const int n_items = 2 * T - 2;   // T tips + T-2 ')'
+  unsigned char* items = p.items + (size_t)i * cta_items_stride(T);
+  double* LEN = reinterpret_cast<double*>(items);
+  int32_t* ID = reinterpret_cast<int32_t*>(items + (size_t)n_items * 8);
+  uint16_t* LVL = reinterpret_cast<uint16_t*>(items + (size_t)n_items * 12);
   int2* PID = reinterpret_cast<int2*>(nw_smem + lay.pid);
   double2* PL = reinterpret_cast<double2*>(nw_smem + lay.pl);
   uint8_t* CNT = nw_smem + lay.cnt;
@@ -307,8 +307,14 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
   const uint32_t L = __ldg(p.lens + i);
   const uint32_t slice = ((L + NT - 1) / NT + 7u) & ~7u;          // a multiple of 8: slices start on the reader's words
   const uint32_t a = min(L, (uint32_t)tid * slice), b = min(L, a + slice);
+  // character classes, one shared-memory look-up per character instead of a dozen compares: 0 word character,
+  // K_OPEN..K_SEMI the structural ones, 6 '[', 7 ']' (a word character unless it closes a comment), 8 blank / NUL
+  __shared__ uint8_t s_cls[256];
+  for (int c = tid; c < 256; c += NT)
+    s_cls[c] = (uint8_t)(c == '[' ? 6 : c == ']' ? 7 : (c == 0 || is_blank(c)) ? 8 : structural(c));
   if (tid < 4) s_flag[tid] = 0;
-  for (int l = tid; l < lay.n_levels; l += NT) CNT[l] = 0;
+  if (tid == 4) s_deep = 0;
+  for (int l = tid; l <= kCtaLevels; l += NT) CNT[l] = 0;
 
   // ---- S0: is the start of my slice inside a comment? ----
   int my_last = 0;  // 0: no bracket in the slice, 1: its last bracket is '[', 2: ']'
@@ -349,14 +355,17 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
     int last = K_NONE;  // the last token since the first structural one
     Reader r(text, a);
     for (uint32_t q = a; q < b; ++q, r.adv()) {
-      const int c = r.peek();
+      const int cls = s_cls[r.peek()];
       if (com) {
-        if (c == ']') com = false;
+        com = cls != 7;
         continue;
       }
-      if (c == '[') { com = true; in_word = false; continue; }
-      if (is_blank(c)) { in_word = false; continue; }
-      const int st = structural(c);
+      if (cls >= 6 && cls != 7) {  // '[' or a blank: either ends a word
+        com = cls == 6;
+        in_word = false;
+        continue;
+      }
+      const int st = cls == 7 ? K_NONE : cls;
       if (st != K_NONE) {
         if (!synced) { synced = true; sm.first_tok = (uint8_t)st; }
         sm.n_open += st == K_OPEN;
@@ -411,7 +420,7 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
       in_word = sm.in_word_out;
     }
     // a tree of this family ends with ';' at depth 0 and has T tips and T-2 ')'
-    if (last != K_SEMI || depth != 0 || n_close != n_ops || n_items != lay.n_items) s_flag[0] = 1;
+    if (last != K_SEMI || depth != 0 || n_close != n_ops || n_items != n_items) s_flag[0] = 1;
   }
   __syncthreads();
 
@@ -423,25 +432,27 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
       int last = st.last_tok, depth = st.depth, nc = st.n_close, ni = st.n_items;
       Reader r(text, a);
       for (uint32_t q = a; q < b; ++q, r.adv()) {
-        const int c = r.peek();
+        const int cls = s_cls[r.peek()];
         if (com) {
-          if (c == ']') com = false;
+          com = cls != 7;
           continue;
         }
-        if (c == '[') { com = true; in_word = false; continue; }
-        if (is_blank(c)) { in_word = false; continue; }
-        const int stc = structural(c);
+        if (cls >= 6 && cls != 7) {
+          com = cls == 6;
+          in_word = false;
+          continue;
+        }
+        const int stc = cls == 7 ? K_NONE : cls;
         if (stc != K_NONE) {
           in_word = false;
           if (!may_follow(last, stc)) bad = true;   // (nothing may follow ';')
           if (stc == K_OPEN) {
-            if (++depth > n_ops) bad = true;
+            if (++depth > kCtaLevels) { bad = true; s_deep = 1; }
           } else if (stc == K_CLOSE) {
-            if (depth <= 0 || ni >= lay.n_items) {
+            if (depth <= 0 || ni >= n_items) {
               bad = true;
             } else {
-              KIND[ni] = K_CLOSE;
-              LVL[ni] = (uint16_t)depth;
+              LVL[ni] = (uint16_t)(depth | 0x8000);
               ID[ni] = nc;
               reinterpret_cast<uint32_t*>(LEN + ni)[0] = q + 1;
             }
@@ -461,10 +472,9 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
           const int wt = word_type(last);
           if (wt == K_BAD) bad = true;
           if (wt == K_TIP) {
-            if (depth <= 0 || ni >= lay.n_items) {
+            if (depth <= 0 || ni >= n_items) {
               bad = true;
             } else {
-              KIND[ni] = K_TIP;
               LVL[ni] = (uint16_t)depth;
               reinterpret_cast<uint32_t*>(LEN + ni)[0] = q;
             }
@@ -481,10 +491,10 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
   if (!s_flag[0] && !s_flag[1]) {
     // ---- S5: one thread per node: label -> row, branch length -> double ----
     bool bad = false;
-    for (int it = tid; it < lay.n_items; it += NT) {
-      const uint32_t pos = reinterpret_cast<const uint32_t*>(LEN + it)[0];
+    for (int it = tid; it < n_items; it += NT) {
+      const uint32_t pos = __ldcg(reinterpret_cast<const uint32_t*>(LEN + it));
       Reader r(text, pos);
-      if (KIND[it] == K_TIP) {
+      if ((__ldcg(LVL + it) & 0x8000u) == 0) {
         uint32_t h = 2166136261u;
         uint64_t first8 = 0;
         int len = 0;
@@ -514,34 +524,50 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
     int root_child = 0, top0 = 0, top1 = 0, c1 = 0;
     double root_blen = 0.0, topl0 = 0.0, topl1 = 0.0;
     bool bad = false, done = false;
-    for (int it = 0; it < lay.n_items && !bad; ++it) {
-      int lvl = LVL[it], id = ID[it];
-      const double len = LEN[it];
-      if (KIND[it] == K_CLOSE) {
-        if (lvl == 1) {  // the trifurcation, last
-          if (c1 != 3 || id != n_ops - 1 || it != lay.n_items - 1) bad = true;
-          done = true;
-          break;
-        }
-        if (CNT[lvl] != 2) { bad = true; break; }
-        ch[id] = PID[lvl];
-        bl[id] = PL[lvl];
-        CNT[lvl] = 0;
-        id += T;
-        --lvl;
+    for (int base = 0; base < n_items && !bad && !done; base += 4) {
+      // (the items come from L2: four at a time, so that their latency is paid once per four)
+      unsigned lv4[4];
+      int id4[4];
+      double len4[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int it = min(base + j, n_items - 1);
+        lv4[j] = __ldcg(LVL + it);
+        id4[j] = __ldcg(ID + it);
+        len4[j] = __ldcg(LEN + it);
       }
-      if (lvl == 1) {
-        if (c1 == 0) { root_child = id; root_blen = len; }
-        else if (c1 == 1) { top0 = id; topl0 = len; }
-        else if (c1 == 2) { top1 = id; topl1 = len; }
-        else bad = true;
-        ++c1;
-      } else {
-        const int k = CNT[lvl];
-        if (k == 0) { PID[lvl].x = id; PL[lvl].x = len; }
-        else if (k == 1) { PID[lvl].y = id; PL[lvl].y = len; }
-        else bad = true;
-        CNT[lvl] = (uint8_t)(k + 1);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int it = base + j;
+        if (it >= n_items || bad || done) break;
+        int lvl = (int)(lv4[j] & 0x7fffu), id = id4[j];
+        const double len = len4[j];
+        if (lv4[j] & 0x8000u) {
+          if (lvl == 1) {  // the trifurcation, last
+            if (c1 != 3 || id != n_ops - 1 || it != n_items - 1) bad = true;
+            done = true;
+            break;
+          }
+          if (CNT[lvl] != 2) { bad = true; break; }
+          ch[id] = PID[lvl];
+          bl[id] = PL[lvl];
+          CNT[lvl] = 0;
+          id += T;
+          --lvl;
+        }
+        if (lvl == 1) {
+          if (c1 == 0) { root_child = id; root_blen = len; }
+          else if (c1 == 1) { top0 = id; topl0 = len; }
+          else if (c1 == 2) { top1 = id; topl1 = len; }
+          else bad = true;
+          ++c1;
+        } else {
+          const int k = CNT[lvl];
+          if (k == 0) { PID[lvl].x = id; PL[lvl].x = len; }
+          else if (k == 1) { PID[lvl].y = id; PL[lvl].y = len; }
+          else bad = true;
+          CNT[lvl] = (uint8_t)(k + 1);
+        }
       }
     }
     if (bad || !done) {
@@ -566,7 +592,7 @@ __global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
       p.root_child[t] = 0;
       p.root_blen[t] = kEpsLen;
       p.on_pat[t] = 1;
-      p.status[t] = 1;
+      p.status[t] = s_deep ? 2 : 1;   // 2: deeper than this kernel's tables - k_newick takes the tree
     }
   }
 }
@@ -588,26 +614,19 @@ __global__ void __launch_bounds__(32) k_split(const uint8_t* __restrict__ on_pat
 
 }  // namespace
 
-constexpr int kCtaWide = 256, kCtaNarrow = 128;   // threads per tree: long strings get more slices
-static int cta_threads(int n_tips) { return n_tips >= 300 ? kCtaWide : kCtaNarrow; }
-bool newick_cta_ok(int n_tips) { return n_tips < 65535 && CtaLayout(n_tips, cta_threads(n_tips)).total <= (size_t)200 * 1024; }
+constexpr int kCtaThreads = 128;
+size_t newick_items_bytes(int n_tips, int n_trees) { return cta_items_stride(n_tips) * (size_t)n_trees; }
 
 void launch_newick(const NewickDev& p, cudaStream_t s) {
   if (p.n <= 0) return;
-  const bool cta = p.kernel == 2 || (p.kernel == 0 && newick_cta_ok(p.T));
-  if (!cta) {
-    k_newick<<<(p.n + 31) / 32, 32, 0, s>>>(p);
-    return;
+  const bool cta = p.kernel != 1 && p.T < 32768 && p.items != nullptr;
+  if (cta) {
+    const size_t smem = CtaLayout(kCtaThreads).total;
+    k_newick_cta<kCtaThreads><<<p.n, kCtaThreads, smem, s>>>(p);
   }
-  const int nt = cta_threads(p.T);
-  const size_t smem = CtaLayout(p.T, nt).total;
-  if (nt == kCtaWide) {
-    ensure_dynamic_smem(reinterpret_cast<const void*>(&k_newick_cta<kCtaWide>), smem);
-    k_newick_cta<kCtaWide><<<p.n, kCtaWide, smem, s>>>(p);
-  } else {
-    ensure_dynamic_smem(reinterpret_cast<const void*>(&k_newick_cta<kCtaNarrow>), smem);
-    k_newick_cta<kCtaNarrow><<<p.n, kCtaNarrow, smem, s>>>(p);
-  }
+  NewickDev q = p;
+  q.only_deferred = cta ? 1 : 0;
+  k_newick<<<(p.n + 31) / 32, 32, 0, s>>>(q);
 }
 
 void launch_split(const uint8_t* on_pat, int t0, int n, int32_t* list, int32_t* n_pat_out, cudaStream_t s) {

@@ -165,6 +165,8 @@ class Tree:
         return t
 
     def newick(self, with_index=False):
+        import sys
+        sys.setrecursionlimit(max(sys.getrecursionlimit(), 4 * len(self.parent) + 1000))
         out = []
         counter = [0]
 
@@ -234,6 +236,25 @@ def random_tree(rng, n_leaves, blen_mean=0.01):
     t.add(0, 0.002, "naive")
     if n_leaves == 1:
         raise ValueError("need at least 2 observed sequences")
+    return t
+
+
+def caterpillar_tree(rng, n_leaves, blen=0.05):
+    """A ladder: tip 0 and tip 1 deepest, every further tip one node up; the naive tip and the last tip hang under
+    the trifurcation. Depth n_leaves - 2: the shape of libpll's own scaling test (test/out/scaling.out)."""
+    t = Tree()
+    chain = [t.add(0, blen) for _ in range(1)]
+    for _ in range(n_leaves - 3):
+        chain.append(t.add(chain[-1], blen))
+    # chain[k] is an inner node; its second child is tip (n_leaves - 2 - k); the deepest holds tips 0 and 1
+    for k, node in enumerate(chain):
+        tip = t.add(node, blen)
+        t.label[tip] = str(n_leaves - 2 - k)
+    last = t.add(chain[-1], blen)
+    t.label[last] = "0"
+    top = t.add(0, blen)
+    t.label[top] = str(n_leaves - 1)
+    t.add(0, 0.002, "naive")
     return t
 
 
@@ -340,8 +361,10 @@ def make_light_family(outdir, genes, n_leaves, seed, L=400, name="family", locus
             "flexbounds": flex, "relpos": relpos}
 
 
-def make_family(outdir, genes, n_leaves, seed, L=400, name="family"):
-    """Writes <outdir>/<name>.yaml; returns dict(yaml_path, tree, labels, naive)."""
+def make_family(outdir, genes, n_leaves, seed, L=400, name="family", tree_fn=None, evolve_fn=None):
+    """Writes <outdir>/<name>.yaml; returns dict(yaml_path, tree, labels, naive).
+    tree_fn(rng, n_leaves) / evolve_fn(rng, tree, naive) replace random_tree / evolve (test families with a
+    chosen shape and chosen sequences)."""
     rng = np.random.default_rng(seed)
     vs = [g for g, (t, _) in genes.items() if t == "V"]
     ds = [g for g, (t, _) in genes.items() if t == "D"]
@@ -373,8 +396,8 @@ def make_family(outdir, genes, n_leaves, seed, L=400, name="family"):
         lo = max(flex["d_r"][0] - n + 1, flex["v_r"][0] + 1)
         hi = min(dl2 - 1, dl2)
         relpos[d] = int(rng.integers(min(lo, hi), hi + 1))
-    tree = random_tree(rng, n_leaves)
-    seqs = evolve(rng, tree, naive)
+    tree = (tree_fn or random_tree)(rng, n_leaves)
+    seqs = (evolve_fn or evolve)(rng, tree, naive)
     ids = [str(i) for i in range(n_leaves)]
     import json
     doc = {"germline-info": {"locus": "igh"},

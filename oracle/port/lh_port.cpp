@@ -17,6 +17,7 @@
 // place (oracle/_ref, built by oracle/refbuild/Makefile) in
 // tests/test_oracle_port.py and through the golden vectors in tests/golden/.
 #include <cmath>
+#include <cstdlib>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -398,8 +399,12 @@ static double port_score_one(const lh_family_desc_t& F, int R, const int32_t* ch
   GtrEigen eig;
   gtr_eigen(er, pi, &eig);
 
+  // LH_PORT_RATE_SCALERS=1 (experiments only, tests/ never set it): scale every rate category on its own count, the
+  // way the CUDA kernels did before they took libpll's all-categories rule; used to find inputs that tell the two apart
+  static const bool rate_scalers = getenv("LH_PORT_RATE_SCALERS") != nullptr;
   std::vector<double> clv((size_t)(2 * T - 2) * S * span);
   std::vector<unsigned> scaler((size_t)n_ops * S, 0u);
+  std::vector<unsigned> rscaler(rate_scalers ? (size_t)n_ops * S * R : 0, 0u);
   for (int t = 0; t < T; t++)
     for (int n = 0; n < S; n++)
       tip_clv(F.tip_codes[(size_t)t * S + n], R, &clv[((size_t)t * S + n) * span]);
@@ -436,10 +441,21 @@ static double port_score_one(const lh_family_desc_t& F, int R, const int32_t* ch
         }
         site_scale = site_scale && rate_scale;
       }
-      if (site_scale) {
+      if (site_scale && !rate_scalers) {
         for (int i = 0; i < span; i++) parent[(size_t)n * span + i] *= kScaleFactor;
         ps[n] += 1;
       }
+      if (rate_scalers)
+        for (int k = 0; k < R; k++) {
+          unsigned& c = rscaler[((size_t)op * S + n) * R + k];
+          c = (c1 >= T ? rscaler[((size_t)(c1 - T) * S + n) * R + k] : 0u) + (c2 >= T ? rscaler[((size_t)(c2 - T) * S + n) * R + k] : 0u);
+          bool small = true;
+          for (int i = 0; i < 4; i++) small = small && parent[(size_t)n * span + 4 * k + i] < kScaleThreshold;
+          if (small) {
+            for (int i = 0; i < 4; i++) parent[(size_t)n * span + 4 * k + i] *= kScaleFactor;
+            c += 1;
+          }
+        }
     }
   }
 
@@ -465,11 +481,27 @@ static double port_score_one(const lh_family_desc_t& F, int R, const int32_t* ch
             termb += pm[16 * k + 4 * i + j] * clvc[(size_t)n * span + 4 * k + j];
           terma_r += pi[i] * termb * clvp[(size_t)n * span + 4 * k + i];
         }
-        if (terma_r > 0.) terma += terma_r * weight;
+        if (terma_r > 0. && !rate_scalers) terma += terma_r * weight;
         rate_term[k] = terma_r;
       }
-      double site_lk = std::log(terma);
       unsigned cnt = sp[n] + (sc ? sc[n] : 0u);
+      if (rate_scalers) {  // sum the categories at the smallest count (exact: powers of two)
+        double acc = 0.0;
+        unsigned acc_cnt = 0;
+        for (int k = 0; k < R; k++) {
+          double term = rate_term[k];
+          unsigned c = rscaler[((size_t)(n_ops - 1) * S + n) * R + k] + (root_child >= T ? rscaler[((size_t)(root_child - T) * S + n) * R + k] : 0u);
+          if (!(term > 0.)) continue;
+          term *= weight;
+          if (acc == 0.0) acc_cnt = c;
+          while (c > acc_cnt) { term *= kScaleThreshold; --c; if (term == 0.0) c = acc_cnt; }
+          while (acc_cnt > c) { acc *= kScaleThreshold; --acc_cnt; if (acc == 0.0) acc_cnt = c; }
+          acc += term;
+        }
+        terma = acc;
+        cnt = acc_cnt;
+      }
+      double site_lk = std::log(terma);
       // per-category read-out: what scripts/run_bootstrap_asr_ess.R:84-87 recomputes with phylomd
       // (phylo.likelihood on the rate-scaled tree / pi[naive base]); the site's scaler count is shared
       // by its categories (core_partials.c:648-659)
@@ -484,7 +516,11 @@ static double port_score_one(const lh_family_desc_t& F, int R, const int32_t* ch
       // naive correction, src/PhyloHMM.cpp:228-237 (row 0 of the xMSA is the naive)
       int nb = F.tip_codes[n];
       if (nb != 4) site_lk -= std::log(pi[nb]);
-      xe[n] = std::exp(site_lk);
+      // xmsa_emission_.array().exp() (src/PhyloHMM.cpp:239) is Eigen's packet exp (pexp_double, SSE2 Packet2d in the
+      // reference's build): 2^n * exp(g) with n = floor(x log2(e) + 1/2), which is 0 once n <= -1023; the odd last
+      // element of the vector goes through libm
+      const bool packet = n < (S & ~1);
+      xe[n] = (packet && std::floor(site_lk * 1.4426950408889634073599 + 0.5) <= -1023.0) ? 0.0 : std::exp(site_lk);
     }
   }
   if (xe_out) std::memcpy(xe_out, xe.data(), sizeof(double) * S);

@@ -13,7 +13,31 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 # sample bundles (family + tree batch + reference outputs); family_*.npz hold a family description only
 GOLDEN_NAMES = sorted(n for n in (os.path.splitext(os.path.basename(p))[0]
                                   for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-                      if not n.startswith(("family_", "pipeline_", "liao_")))
+                      if not n.startswith(("family_", "pipeline_", "liao_", "scaling_")))
+# underflow-regime families scored by the reference (scripts/make_scaling_goldens.py)
+SCALING_NAMES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "scaling_*.npz")))
+
+
+def compare_in_underflow_regime(got_ll, got, exp, tol=1e-9):
+    """xmsa_emission / log-likelihood: within tol where the reference's value is finite and non-zero, the same
+    class (zero, +-inf, nan) where it is not; every scaler count exact for the samples whose reference
+    log-likelihood is finite (past a NaN the reference's own counts are the residue of comparisons with NaN)."""
+    xe, rxe = np.asarray(got["xmsa_emission"]), np.asarray(exp["xmsa_emission"])
+    ok = np.isfinite(rxe) & (np.abs(rxe) >= np.finfo(np.float64).tiny)   # (a subnormal has no 1e-9 to offer)
+    sub = np.isfinite(rxe) & (rxe != 0) & ~ok
+    assert np.array_equal(np.isnan(xe), np.isnan(rxe)) and np.array_equal(xe == 0, rxe == 0)
+    assert np.all(np.abs(xe[sub]) < np.finfo(np.float64).tiny)
+    assert np.array_equal(np.isinf(xe), np.isinf(rxe))
+    worst = float(np.max(np.abs(xe[ok] - rxe[ok]) / np.abs(rxe[ok]))) if ok.any() else 0.0
+    assert worst <= tol, worst
+    rll = np.asarray(exp["loglik"])
+    fin = np.isfinite(rll)
+    assert np.array_equal(np.isnan(got_ll), np.isnan(rll)) and np.array_equal(np.isinf(got_ll), np.isinf(rll))
+    if fin.any():
+        assert float(np.max(np.abs(got_ll[fin] - rll[fin]) / np.abs(rll[fin]))) <= tol
+        for k in ("germ_scalers", "vd_scalers", "dj_scalers"):
+            assert np.array_equal(np.asarray(got[k])[fin], np.asarray(exp[k])[fin]), k
+    return worst
 
 
 def pytest_configure(config):

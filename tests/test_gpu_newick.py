@@ -139,6 +139,34 @@ def test_ops_bit_identical_on_random_trees(n_leaves, n_trees, kernel):
     assert np.array_equal(got["on_patterns"], _on_patterns(ref))
 
 
+def test_deep_caterpillar_goes_through_the_second_device_pass():
+    """A caterpillar of 600 tips nests 598 deep - beyond the per-level tables of k_newick_cta (256): the tree is
+    handed to k_newick on the device, not to the host, and comes out the same."""
+    T = 601
+    labels = ["naive"] + [f"t{i}" for i in range(1, T)]
+    n_ops = T - 2
+    ch = np.zeros((3, n_ops, 2), dtype=np.int32)
+    ch[:, 0] = (1, 2)
+    for op in range(1, n_ops - 1):
+        ch[:, op] = (T + op - 1, op + 2)
+    ch[:, n_ops - 1] = (T + n_ops - 2, T - 1)
+    rng = np.random.default_rng(5)
+    tb = {"children": ch, "blen": rng.uniform(1e-4, 0.1, (3, n_ops, 2)), "root_child": np.zeros(3, dtype=np.int32),
+          "root_blen": rng.uniform(1e-4, 0.1, 3)}
+    text = host.NewickBuffer(tb, labels)
+    nw = [text[i] for i in range(3)]
+    ref = host.newick_to_ops(nw, labels)
+    fam = dict(load_golden("synth_n12")[0])
+    fam["n_tips"] = T
+    fam["tip_codes"] = np.zeros((T, fam["n_sites"]), dtype=np.uint8)
+    f = _family(fam, labels, 2)
+    got = f.parse_newick(nw)
+    f.close()
+    assert not got["left_to_host"].any()
+    for k in OPS:
+        assert np.array_equal(got[k], ref[k]), k
+
+
 def test_lenient_spellings_are_left_to_the_host_by_the_cta_parser():
     """What the lenient host parser takes beyond the strict grammar - a missing comma, text after ';' - the
     one-CTA-per-tree parser declines (the one-thread-per-tree parser reads them as the host does); the call's
