@@ -571,6 +571,11 @@ def main():
             return 0
         return reference_arm(args)
 
+    # stdout carries the ONE JSON line and nothing else: whatever the libraries print there (NCCL's version banner,
+    # ...) goes to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     env = Env(args)
     if args.config in ("c5", "c2"):
         import bench_c2
@@ -593,7 +598,8 @@ def main():
                 out["c5"] = {k: c5[k] for k in keep if k in c5}
                 out["gpu_launches"] += c3["gpu_launches"] + c5["gpu_launches"]
     if env.rank == 0:
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     if env.dist is not None:
         env.dist.barrier()
         env.dist.destroy_process_group()

@@ -224,7 +224,7 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
  * the handle's host threads would not keep ahead of the kernels - the programs are the same),
  * "newick_kernel" (lh_score_newick: 0 / 2 = default, the one-CTA-per-tree parser, with the one-thread-per-tree
  * parser behind it for trees nested deeper than its tables; 1 = the one-thread-per-tree parser alone),
- * "parse_reserve" (default 1: pruning CTAs per SM given up during lh_score_newick so that the parser of the
+ * "parse_reserve" (default 0: pruning CTAs per SM given up during lh_score_newick so that the parser of the
  * next chunk runs beside the pruning of this one),
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never
  * smaller than 16 waves of CTAs), "chunk_trees" (0 = auto; trees per chunk, overrides), "pipe_waves" (default 4:
@@ -240,6 +240,25 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
  * lh_batch_run calls on the stream the kernels are launched on.                          */
 int lh_timer_mark(lh_family_t* fam, int32_t slot);
 int lh_timer_elapsed_ms(lh_family_t* fam, int32_t from_slot, int32_t to_slot, float* ms);
+
+/* ---- group: one clonal family on several GPUs of one box, inside one process ----
+ * The reference has no counterpart (one CPU process per cluster). The trees of a call are cut into contiguous,
+ * equal shards, one per device; the family constants are replicated; each member is an lh_family_t driven by
+ * its own host thread; results are written into the caller's single host arrays. The doubles do not depend on
+ * the number of devices. A group of one device is an lh_family_t with another name.                       */
+typedef struct lh_group lh_group_t;
+int  lh_group_create(lh_group_t** out, const lh_family_desc_t* desc, const int* devices, int n_devices);
+void lh_group_destroy(lh_group_t* grp);
+int  lh_group_size(const lh_group_t* grp);
+lh_family_t* lh_group_member(lh_group_t* grp, int member);            /* owned by the group */
+int  lh_group_set_labels(lh_group_t* grp, const char* const* labels);
+int  lh_group_set_option(lh_group_t* grp, const char* key, int64_t value);   /* lh_set_option on every member */
+int  lh_group_score_batch(lh_group_t* grp, const lh_tree_batch_t* trees, double* loglik, lh_outputs_t* opt);
+int  lh_group_score_newick(lh_group_t* grp, const lh_newick_batch_t* trees, double* loglik, lh_outputs_t* opt);
+int  lh_group_get_timings(lh_group_t* grp, int member /* -1: summed counts, slowest member's times */, lh_timings_t* out);
+const char* lh_group_last_error(void);
+/* "0-3", "0,2,5", "1" -> device ordinals: the CLI's --devices flag and the LINEARHAM_DEVICES variable */
+int  lh_parse_devices(const char* spec, int* out, int cap, int* n_out);
 
 /* ---- repertoire: many independent clonal families on one device (BASELINE config 5) --------
  * The reference runs one linearham process per cluster (SConstruct:344-352, 428-447;
@@ -262,6 +281,10 @@ typedef struct lh_repertoire_stats {
   int64_t kernel_launches, h2d_bytes, d2h_bytes;
 } lh_repertoire_stats_t;
 int  lh_repertoire_create(lh_repertoire_t** out, int device, int n_slots, int host_threads /*0 = cores / n_slots*/);
+/* the same over several devices of the box: n_slots handles on each, ONE queue (largest family first) that
+ * every slot of every device pulls from                                                          */
+int  lh_repertoire_create_multi(lh_repertoire_t** out, const int* devices, int n_devices, int n_slots,
+                                int host_threads /*0 = cores / (n_devices * n_slots)*/);
 int  lh_repertoire_score(lh_repertoire_t* rep, lh_repertoire_item_t* items, int32_t n_items,
                          lh_repertoire_stats_t* stats /* or NULL */);
 int  lh_repertoire_set_option(lh_repertoire_t* rep, const char* key, int64_t value); /* lh_set_option on every slot */

@@ -64,6 +64,9 @@ typedef struct lhh_phylohmm lhh_phylohmm_t;
 lhh_phylohmm_t* lhh_phylohmm_new(const char* yaml_path, int32_t cluster_ind, const char* hmm_param_dir, int32_t seed);
 void lhh_phylohmm_free(lhh_phylohmm_t* h);
 int lhh_phylohmm_set_device(lhh_phylohmm_t* h, int32_t device);
+/* Several GPUs of the box (before the first scoring call): the batched calls - score_samples, run_pipeline - cut
+ * their trees into one shard per device (lh_group_t, include/linearham_b200.h); results do not depend on it. */
+int lhh_phylohmm_set_devices(lhh_phylohmm_t* h, const int32_t* devices, int32_t n_devices);
 /* Host threads this object may use (Newick ingest and traversal planning); 0 = all hardware threads.
  * A job with several ranks per node gives each rank its share. */
 int lhh_phylohmm_set_host_threads(lhh_phylohmm_t* h, int32_t n_threads);

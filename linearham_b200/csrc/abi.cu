@@ -233,7 +233,7 @@ struct lh_family {
   lhb::HmmOut ho{};
   int chunk = 0, chunk_pipe = 0, wave_pipe = 0, wave_unit = 0, seg = 0, occ[2] = {0, 0};
   int opt_open_unit = 1, opt_chunk_growth = 1;
-  int opt_parse_reserve = 1;  // pruning CTAs per SM given up for the parser while text is coming in
+  int opt_parse_reserve = 0;  // pruning CTAs per SM given up for the parser while text is coming in (measured: no gain, the parser of a chunk runs between the pruning launches either way)
   int opt_newick_kernel = 0;  // 0 auto, 1 k_newick (one thread per tree), 2 k_newick_cta (one CTA per tree)
   double stage_ratio = 1.0;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories

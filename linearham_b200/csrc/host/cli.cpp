@@ -18,6 +18,7 @@
 #include <string>
 #include <vector>
 
+#include "../../../include/linearham_b200.h"
 #include "phylo_hmm.hpp"
 
 namespace {
@@ -36,6 +37,7 @@ const Flag kCommon[] = {
     {"seed", false, false, "0", "The RNG seed."},
     {"num-rates", false, false, "1", "The number of gamma rate categories."},
     {"device", false, false, "0", "The CUDA device ordinal."},
+    {"devices", false, false, "", "CUDA devices to spread the batched work over, e.g. 0-7 or 0,2,4 (default: $LINEARHAM_DEVICES, else --device)."},
 };
 const Flag kTree[] = {
     {"newick-path", true, false, "", "The Newick tree file path."},
@@ -143,7 +145,16 @@ bool wants_help(const std::vector<std::string>& argv, size_t first) {
 linearham::PhyloHMMPtr make_model(const Args& a) {
   auto p = std::make_shared<linearham::PhyloHMM>(a.str("yaml-path"), a.integer("cluster-ind"), a.str("hmm-param-dir"),
                                                  a.integer("seed"));
-  p->set_device(a.integer("device"));
+  // --devices, else LINEARHAM_DEVICES, else --device
+  std::string spec = a.str("devices");
+  if (spec.empty() && std::getenv("LINEARHAM_DEVICES")) spec = std::getenv("LINEARHAM_DEVICES");
+  if (spec.empty()) {
+    p->set_device(a.integer("device"));
+  } else {
+    int dev[64], n = 0;
+    if (lh_parse_devices(spec.c_str(), dev, 64, &n)) throw std::invalid_argument(lh_group_last_error());
+    p->set_devices(std::vector<int>(dev, dev + n));
+  }
   return p;
 }
 

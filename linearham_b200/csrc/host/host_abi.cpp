@@ -106,6 +106,9 @@ void lhh_phylohmm_free(lhh_phylohmm_t* h) { delete reinterpret_cast<Handle*>(h);
 int lhh_phylohmm_set_device(lhh_phylohmm_t* h, int32_t device) {
   return guarded([&] { H(h).set_device(device); });
 }
+int lhh_phylohmm_set_devices(lhh_phylohmm_t* h, const int32_t* devices, int32_t n_devices) {
+  return guarded([&] { H(h).set_devices(std::vector<int>(devices, devices + n_devices)); });
+}
 int lhh_phylohmm_set_host_threads(lhh_phylohmm_t* h, int32_t n_threads) {
   return guarded([&] { H(h).set_host_threads(n_threads); });
 }

@@ -183,7 +183,8 @@ PhyloHMM::PhyloHMM(const std::string& yaml_path, int cluster_ind, const std::str
 }
 
 PhyloHMM::~PhyloHMM() {
-  if (dev_family_) lh_family_destroy(dev_family_);
+  if (dev_group_) lh_group_destroy(dev_group_);   // (owns its members)
+  else if (dev_family_) lh_family_destroy(dev_family_);
 }
 
 // src/PhyloHMM.cpp:45-89, 123-144
@@ -286,17 +287,35 @@ const lh_family_desc& PhyloHMM::family_desc() const { return flat_->desc; }
 
 void PhyloHMM::EnsureDeviceFamily() {
   if (dev_family_) return;
-  if (lh_family_create(&dev_family_, &flat_->desc, device_)) throw std::runtime_error(lh_last_error());
+  if (devices_.size() > 1) {
+    if (lh_group_create(&dev_group_, &flat_->desc, devices_.data(), (int)devices_.size())) throw std::runtime_error(lh_group_last_error());
+    dev_family_ = lh_group_member(dev_group_, 0);
+    if (host_threads_ > 0 && lh_group_set_option(dev_group_, "host_threads", std::max(1, host_threads_ / (int)devices_.size())))
+      throw std::runtime_error(lh_group_last_error());
+    if (lh_group_set_labels(dev_group_, flat_->label_ptrs.data())) throw std::runtime_error(lh_group_last_error());
+    return;
+  }
+  if (lh_family_create(&dev_family_, &flat_->desc, devices_[0])) throw std::runtime_error(lh_last_error());
   if (host_threads_ > 0 && lh_set_option(dev_family_, "host_threads", host_threads_)) throw std::runtime_error(lh_last_error());
   // the xMSA row labels, for the device Newick parser (Partition::SetTipStates matches tips by label,
   // lib/libptpll/src/pll_partition.cpp:153-194)
   if (lh_family_set_labels(dev_family_, flat_->label_ptrs.data())) throw std::runtime_error(lh_last_error());
 }
 
+void PhyloHMM::set_devices(const std::vector<int>& devices) {
+  if (devices.empty()) throw std::invalid_argument("empty device list");
+  if (dev_family_) throw std::logic_error("set_devices() must come before the first scoring call");
+  devices_ = devices;
+}
+
 void PhyloHMM::set_host_threads(int n) {
   if (n < 0) throw std::invalid_argument("host thread count must not be negative");
   host_threads_ = n;
-  if (dev_family_ && n > 0 && lh_set_option(dev_family_, "host_threads", n)) throw std::runtime_error(lh_last_error());
+  if (dev_group_ && n > 0) {
+    if (lh_group_set_option(dev_group_, "host_threads", std::max(1, n / (int)devices_.size()))) throw std::runtime_error(lh_group_last_error());
+  } else if (dev_family_ && n > 0 && lh_set_option(dev_family_, "host_threads", n)) {
+    throw std::runtime_error(lh_last_error());
+  }
 }
 
 // src/PhyloHMM.cpp:350-361
@@ -397,8 +416,9 @@ void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er,
   nb.er = er;
   nb.pi = pi;
   nb.alpha = alpha;
-  if (lh_score_newick(dev_family_, &nb, loglik, nullptr)) {
-    const std::string msg = lh_last_error();
+  const int rc = dev_group_ ? lh_group_score_newick(dev_group_, &nb, loglik, nullptr) : lh_score_newick(dev_family_, &nb, loglik, nullptr);
+  if (rc) {
+    const std::string msg = dev_group_ ? lh_group_last_error() : lh_last_error();
     // what the reference's parser / SetTipStates would refuse is the caller's mistake, the rest the device's
     if (msg.rfind("tree ", 0) == 0 || msg.find("alpha") != std::string::npos) throw std::invalid_argument(msg);
     throw std::runtime_error(msg);
@@ -510,7 +530,8 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
         fdj(B * std::max<std::size_t>(dj_n, 1)), fj((std::size_t)B * d.n_j);
     std::vector<int32_t> gs((std::size_t)B * 3), vds((std::size_t)B * d.vd_sites), djs((std::size_t)B * std::max(d.dj_sites, 1));
     lh_outputs_t o{xe.data(), fv.data(), fvd.data(), fd.data(), fdj.data(), fj.data(), gs.data(), vds.data(), djs.data()};
-    if (lh_score_batch(dev_family_, &tb, ll.data(), &o)) throw std::runtime_error(lh_last_error());
+    if (dev_group_ ? lh_group_score_batch(dev_group_, &tb, ll.data(), &o) : lh_score_batch(dev_family_, &tb, ll.data(), &o))
+      throw std::runtime_error(dev_group_ ? lh_group_last_error() : lh_last_error());
 
     for (int b = 0; b < B; ++b) {
       const Row& r = rows[b];

@@ -22,7 +22,8 @@
 #include "germline.hpp"
 #include "yaml_lite.hpp"
 
-struct lh_family;       // include/linearham_b200.h
+struct lh_family;
+struct lh_group;       // include/linearham_b200.h
 struct lh_family_desc;  // include/linearham_b200.h
 
 namespace linearham {
@@ -177,7 +178,10 @@ class PhyloHMM : public HMM {
   void ScoreSamples(int n, const char* const* newicks, const double* er, const double* pi, const double* alpha,
                     int num_rates, double* loglik);
 
-  void set_device(int device) { device_ = device; }
+  void set_device(int device) { devices_.assign(1, device); }
+  // several GPUs of the box: every batched call (ScoreSamples, RunPipeline) cuts its trees into one shard per
+  // device (lh_group_t); must be called before the first scoring call
+  void set_devices(const std::vector<int>& devices);
   // the device handle behind this object (created on first use); for timings and options
   lh_family* device_family() { EnsureDeviceFamily(); return dev_family_; }
   // host threads for Newick ingest and traversal planning (0 = all hardware threads)
@@ -234,8 +238,10 @@ class PhyloHMM : public HMM {
   double loglik_cached_ = 0;
 
   std::unique_ptr<FlatFamily> flat_;
-  lh_family* dev_family_ = nullptr;
-  int device_ = 0, host_threads_ = 0;
+  lh_family* dev_family_ = nullptr;   // the device handle (member 0 of the group when there are several devices)
+  lh_group* dev_group_ = nullptr;
+  std::vector<int> devices_{0};
+  int host_threads_ = 0;
 };
 
 typedef std::shared_ptr<PhyloHMM> PhyloHMMPtr;

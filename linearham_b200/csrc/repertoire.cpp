@@ -25,7 +25,7 @@
 #include "../../include/linearham_b200.h"
 
 struct lh_repertoire {
-  int device = 0;
+  std::vector<int> slot_device;  // the device of every slot (slots of the devices interleaved)
   int host_threads = 0;  // planner threads per slot
   std::vector<lh_family_t*> slots;
   std::vector<std::pair<std::string, int64_t>> options;  // lh_set_option on every slot handle
@@ -48,24 +48,30 @@ extern "C" {
 
 const char* lh_repertoire_last_error(void) { return g_rep_err.c_str(); }
 
-int lh_repertoire_create(lh_repertoire_t** out, int device, int n_slots, int host_threads) {
-  if (!out) return rep_fail("null argument");
+int lh_repertoire_create_multi(lh_repertoire_t** out, const int* devices, int n_devices, int n_slots, int host_threads) {
+  if (!out || !devices) return rep_fail("null argument");
   *out = nullptr;
   int ndev = 0;
   if (lh_device_count(&ndev) || ndev == 0)
     return rep_fail(std::string("no CUDA device available; linearham_b200 has no CPU fallback (") + lh_last_error() + ")");
-  if (device < 0 || device >= ndev) return rep_fail("device " + std::to_string(device) + " out of range");
+  if (n_devices < 1 || n_devices > 64) return rep_fail("need 1..64 devices");
+  for (int i = 0; i < n_devices; ++i)
+    if (devices[i] < 0 || devices[i] >= ndev) return rep_fail("device " + std::to_string(devices[i]) + " out of range");
   if (n_slots < 1 || n_slots > 16) return rep_fail("n_slots must be 1..16");
   lh_repertoire* r = new lh_repertoire;
-  r->device = device;
   if (host_threads <= 0) {
     const int hw = std::max(1u, std::thread::hardware_concurrency());
-    host_threads = std::max(1, hw / n_slots);
+    host_threads = std::max(1, hw / (n_slots * n_devices));
   }
   r->host_threads = host_threads;
-  r->slots.assign(n_slots, nullptr);  // handles are created by the first family a slot scores
+  r->slots.assign((size_t)n_slots * n_devices, nullptr);  // handles are created by the first family a slot scores
+  for (int si = 0; si < n_slots * n_devices; ++si) r->slot_device.push_back(devices[si % n_devices]);
   *out = r;
   return 0;
+}
+
+int lh_repertoire_create(lh_repertoire_t** out, int device, int n_slots, int host_threads) {
+  return lh_repertoire_create_multi(out, &device, 1, n_slots, host_threads);
 }
 
 // lh_set_option on every slot handle, present and future ("host_threads" also sets the per-slot share).
@@ -127,7 +133,7 @@ int lh_repertoire_score(lh_repertoire_t* r, lh_repertoire_item_t* items, int32_t
       lh_family_t*& f = r->slots[si];
       int rc;
       if (!f) {
-        rc = lh_family_create(&f, it.desc, r->device);
+        rc = lh_family_create(&f, it.desc, r->slot_device[si]);
         if (!rc) rc = lh_set_option(f, "host_threads", r->host_threads);
         // The slots share the host. With two or more host threads per slot the planner threads keep
         // ahead of the GPU and k_plan launches of a few hundred trees only add latency (C5, 16 cores, 6

@@ -165,13 +165,87 @@ class Family:
         return {k: getattr(t, k) for k, _ in _abi.Timings._fields_}
 
 
+def parse_devices(spec):
+    """"0-3", "0,2,5" -> [0, 1, 2, 3] (lh_parse_devices: the --devices flag / LINEARHAM_DEVICES)."""
+    out, n = (C.c_int * 64)(), C.c_int()
+    if lib().lh_parse_devices(str(spec).encode(), out, 64, C.byref(n)):
+        raise DeviceError(lib().lh_group_last_error().decode())
+    return [out[i] for i in range(n.value)]
+
+
+class Group:
+    """One clonal family on several GPUs of the box, inside this process (lh_group_t): contiguous shards of the
+    trees of a call, one per device; results in one host array."""
+
+    def __init__(self, fam, devices):
+        self.fam = fam
+        self._h = C.c_void_p()
+        d, keep = _abi.family_desc(fam)
+        dev = (C.c_int * len(devices))(*[int(x) for x in devices])
+        if lib().lh_group_create(C.byref(self._h), C.byref(d), dev, len(devices)):
+            raise DeviceError(lib().lh_group_last_error().decode())
+
+    def close(self):
+        if self._h:
+            lib().lh_group_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc:
+            raise DeviceError(lib().lh_group_last_error().decode())
+
+    def size(self):
+        return lib().lh_group_size(self._h)
+
+    def set_option(self, key, value):
+        self._ck(lib().lh_group_set_option(self._h, key.encode(), int(value)))
+
+    def set_labels(self, labels):
+        arr = (C.c_char_p * len(labels))(*[str(s).encode() for s in labels])
+        self._ck(lib().lh_group_set_labels(self._h, arr))
+
+    def score(self, tb, outputs=False):
+        t, keep = _abi.tree_batch(tb)
+        ll = np.zeros(t.n_trees)
+        if outputs:
+            o, arrs = _abi.alloc_outputs(self.fam, t.n_trees, None if outputs is True else outputs, n_rates=t.n_rates)
+            self._ck(lib().lh_group_score_batch(self._h, C.byref(t), ll.ctypes.data_as(_f64p), C.byref(o)))
+            return ll, arrs
+        self._ck(lib().lh_group_score_batch(self._h, C.byref(t), ll.ctypes.data_as(_f64p), None))
+        return ll
+
+    def score_newick(self, newicks, er, pi, n_rates, alpha=None, rates=None, outputs=False, lengths=False):
+        nb, keep = _abi.newick_batch(newicks, er, pi, n_rates, alpha=alpha, rates=rates, lengths=lengths)
+        ll = np.zeros(nb.n_trees)
+        if outputs:
+            o, arrs = _abi.alloc_outputs(self.fam, nb.n_trees, None if outputs is True else outputs, n_rates=n_rates)
+            self._ck(lib().lh_group_score_newick(self._h, C.byref(nb), ll.ctypes.data_as(_f64p), C.byref(o)))
+            return ll, arrs
+        self._ck(lib().lh_group_score_newick(self._h, C.byref(nb), ll.ctypes.data_as(_f64p), None))
+        return ll
+
+    def timings(self, member=-1):
+        t = _abi.Timings()
+        self._ck(lib().lh_group_get_timings(self._h, int(member), C.byref(t)))
+        return {k: getattr(t, k) for k, _ in _abi.Timings._fields_}
+
+
 class Repertoire:
     """Many independent clonal families on one device (lh_repertoire_t): n_slots device handles, one
     host thread per slot."""
 
-    def __init__(self, device=0, n_slots=3, host_threads=0):
+    def __init__(self, device=0, n_slots=3, host_threads=0, devices=None):
+        """devices: several GPUs (n_slots handles on each, one queue); else the one `device`."""
         self._h = C.c_void_p()
-        if lib().lh_repertoire_create(C.byref(self._h), int(device), int(n_slots), int(host_threads)):
+        devs = [int(device)] if devices is None else [int(x) for x in devices]
+        arr = (C.c_int * len(devs))(*devs)
+        if lib().lh_repertoire_create_multi(C.byref(self._h), arr, len(devs), int(n_slots), int(host_threads)):
             raise DeviceError(lib().lh_repertoire_last_error().decode())
 
     def close(self):

@@ -117,6 +117,11 @@ class PhyloHMM:
             raise HostError(self._lib.lhh_last_error().decode())
         _ck(self._lib.lhh_phylohmm_set_device(self._h, int(device)))
 
+    def set_devices(self, devices):
+        """several GPUs of the box for the batched calls (before the first scoring call)"""
+        arr = np.ascontiguousarray(devices, dtype=np.int32)
+        _ck(self._lib.lhh_phylohmm_set_devices(self._h, arr.ctypes.data_as(_abi._i32p), len(arr)))
+
     def set_host_threads(self, n):
         """host threads for Newick ingest and traversal planning (0 = all hardware threads)"""
         _ck(self._lib.lhh_phylohmm_set_host_threads(self._h, int(n)))
