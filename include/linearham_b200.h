@@ -208,6 +208,29 @@ int lh_debug_fetch_plan(lh_family_t* fam, int32_t* steps, double* pblen);
 int lh_debug_parse_newick(lh_family_t* fam, const lh_newick_batch_t* trees, int32_t* children, double* blen,
                           int32_t* root_child, double* root_blen, uint8_t* on_patterns /* or NULL */,
                           uint8_t* left_to_host, float* ms_kernel /* or NULL */);
+/* The device Newick parser (k_newick_cta + k_newick) for callers that cannot allocate - code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc. This entry point has NO counterpart in the
+ * reference. It calls no cudaMalloc / cudaFree or any other
+ * allocating routine: the parser's per-tree scratch lives in a static device array of
+ * LH_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit, and all inputs and outputs are
+ * the caller's DEVICE buffers:
+ *   text_dev   the strings, each NUL-terminated, starting on a 16-byte boundary and padded with NULs to one
+ *   offs_dev   [n_trees] start of each string in text_dev;  lens_dev [n_trees] its strlen
+ *   children_dev [n][T-2][2], blen_dev [n][T-2][2], root_child_dev [n], root_blen_dev [n]  as lh_tree_batch_t
+ *   on_patterns_dev [n] 1: naive tip on the root edge or under the virtual root
+ *   status_dev [n] 0 parsed; non-zero: not decided here (malformed, or a spelling left to the host parser) -
+ *              the tree's rows then hold a harmless stand-in
+ * The family needs lh_family_set_labels (set-up; that call does allocate). The two kernels are queued on `stream`
+ * (a cudaStream_t; NULL = the legacy default stream) and the call returns without waiting. Limit: n_trees *
+ * ((2T-2)*14 rounded up to 16) bytes <= LH_NOALLOC_SCRATCH_BYTES, T < 32768 - lh_newick_parse_noalloc_max_trees(T)
+ * trees per call (599 for 1001 tips); more is refused with an error. Every call shares the one array per GPU: it
+ * keeps the last call's contents (the kernel writes every item before reading it, so nothing needs clearing), and
+ * calls that overlap on one GPU - two streams, two threads, two handles - race on it.                         */
+#define LH_NOALLOC_SCRATCH_BYTES (16u << 20)
+int lh_newick_parse_noalloc(lh_family_t* fam, int32_t n_trees, const char* text_dev, const uint64_t* offs_dev,
+                            const uint32_t* lens_dev, int32_t* children_dev, double* blen_dev, int32_t* root_child_dev,
+                            double* root_blen_dev, uint8_t* on_patterns_dev, uint8_t* status_dev, void* stream);
+int32_t lh_newick_parse_noalloc_max_trees(int32_t n_tips);
 /* Diagnostic: sustained FP64 FMA rate of a register-resident DFMA loop (TFLOP/s); the
  * denominator for the FP64-pipe view of the pruning kernel (no reference counterpart). */
 int lh_measure_fp64_peak(int device, double* tflops);

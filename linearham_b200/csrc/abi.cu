@@ -1999,6 +1999,46 @@ int lh_debug_parse_newick(lh_family_t* f, const lh_newick_batch_t* nb, int32_t* 
   return 0;
 }
 
+// The device Newick parser on caller-owned device buffers, with its scratch in a static device array: calls no
+// cudaMalloc / cudaFree (nor anything else that allocates) and only queues two kernels on `stream`.
+int lh_newick_parse_noalloc(lh_family_t* f, int32_t n_trees, const char* text_dev, const uint64_t* offs_dev,
+                            const uint32_t* lens_dev, int32_t* children_dev, double* blen_dev, int32_t* root_child_dev,
+                            double* root_blen_dev, uint8_t* on_patterns_dev, uint8_t* status_dev, void* stream) {
+  if (!f) return fail("null family");
+  if (!f->bound || !f->labels_set) return fail("lh_newick_parse_noalloc needs a bound family with labels (lh_family_set_labels)");
+  if (n_trees < 0) return fail("negative tree count");
+  const int max_trees = lhb::newick_noalloc_max_trees(f->fd.T);
+  if (max_trees == 0) return fail("lh_newick_parse_noalloc: a family of %d tips is beyond the static scratch", f->fd.T);
+  if (n_trees > max_trees)
+    return fail("lh_newick_parse_noalloc: %d trees of %d tips need more than the %zu-byte static scratch (at most %d trees per call)",
+                n_trees, f->fd.T, (size_t)lhb::kNoAllocScratchBytes, max_trees);
+  if (n_trees == 0) return 0;
+  if (!text_dev || !offs_dev || !lens_dev || !children_dev || !blen_dev || !root_child_dev || !root_blen_dev ||
+      !on_patterns_dev || !status_dev)
+    return fail("null argument");
+  LH_CUDA(cudaSetDevice(f->device));
+  lhb::NewickDev p{};
+  p.T = f->fd.T;
+  p.tree0 = 0;
+  p.n = n_trees;
+  p.text = text_dev;
+  p.offs = offs_dev;
+  p.lens = lens_dev;
+  p.kernel = 2;
+  p.labels = f->lt;
+  p.children = children_dev;
+  p.blen = blen_dev;
+  p.root_child = root_child_dev;
+  p.root_blen = root_blen_dev;
+  p.on_pat = on_patterns_dev;
+  p.status = status_dev;
+  const int rc = lhb::launch_newick_noalloc(p, f->device, static_cast<cudaStream_t>(stream));
+  if (rc) return fail("lh_newick_parse_noalloc: %s", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+  return 0;
+}
+
+int32_t lh_newick_parse_noalloc_max_trees(int32_t n_tips) { return lhb::newick_noalloc_max_trees(n_tips); }
+
 int lh_get_timings(lh_family_t* f, lh_timings_t* out) {
   if (!f || !out) return fail("null argument");
   LH_CUDA(cudaSetDevice(f->device));

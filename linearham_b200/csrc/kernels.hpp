@@ -152,6 +152,10 @@ struct NewickDev {
 };
 void launch_newick(const NewickDev& p, cudaStream_t s);
 size_t newick_items_bytes(int n_tips, int n_trees);
+// the no-allocation variant: k_newick_cta's scratch in a static device array of this size (newick_dev.cu)
+constexpr size_t kNoAllocScratchBytes = (size_t)16 << 20;
+int newick_noalloc_max_trees(int n_tips);   // trees per call the static scratch holds (0: family too large)
+int launch_newick_noalloc(NewickDev p, int device, cudaStream_t s);   // 0 or a cudaError_t
 // stable partition of the chunk's trees [t0, t0+n) by on_pat into list[t0..) (pattern trees first);
 // n_pat_out[0] = how many
 void launch_split(const uint8_t* on_pat, int t0, int n, int32_t* list, int32_t* n_pat_out, cudaStream_t s);

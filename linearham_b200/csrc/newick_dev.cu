@@ -16,7 +16,9 @@
 // the same doubles as atof / from_chars.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
+#include <mutex>
 
 #include "decimal.hpp"
 #include "kernels.hpp"
@@ -627,6 +629,60 @@ void launch_newick(const NewickDev& p, cudaStream_t s) {
   NewickDev q = p;
   q.only_deferred = cta ? 1 : 0;
   k_newick<<<(p.n + 31) / 32, 32, 0, s>>>(q);
+}
+
+// ---- the no-allocation variant (lh_newick_parse_noalloc; no counterpart in the reference) -----------------------
+// k_newick_cta's per-tree item scratch in a file-scope device array instead of a cudaMalloc'ed buffer: every GPU
+// that loads the library holds kNoAllocScratchBytes until exit. Every call shares the array; the kernel writes an
+// item before it reads it (S3 before S5 / S6), so nothing in it has to start at zero and nothing is cleared - but
+// two calls that overlap on one GPU race on it.
+static __device__ __align__(256) unsigned char g_newick_static_scratch[kNoAllocScratchBytes];
+
+int newick_noalloc_max_trees(int n_tips) {
+  if (n_tips < 3 || n_tips >= 32768) return 0;
+  return (int)std::min<size_t>((size_t)1 << 30, (size_t)kNoAllocScratchBytes / cta_items_stride(n_tips));
+}
+
+// `scratch` in host code is a host-side stand-in for the array, not its device address: the address is asked for
+// once per device, with that device current. Returns nullptr (and the CUDA error through *err) on failure.
+static unsigned char* static_scratch_address(int device, cudaError_t* err) {
+  static std::mutex mu;
+  static unsigned char* addr[64] = {};
+  *err = cudaSuccess;
+  if (device < 0 || device >= 64) {
+    *err = cudaErrorInvalidDevice;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> g(mu);
+  if (!addr[device]) {
+    int cur = -1;
+    *err = cudaGetDevice(&cur);
+    if (*err != cudaSuccess) return nullptr;
+    if (cur != device) {
+      *err = cudaErrorInvalidDevice;   // the caller makes the device current first
+      return nullptr;
+    }
+    void* ptr = nullptr;
+    *err = cudaGetSymbolAddress(&ptr, g_newick_static_scratch);
+    if (*err != cudaSuccess) return nullptr;
+    addr[device] = static_cast<unsigned char*>(ptr);
+  }
+  return addr[device];
+}
+
+// Launches k_newick_cta (and k_newick behind it for trees nested deeper than its tables) over p.n trees with the
+// static scratch; allocates nothing. `device` must be current. 0, or the CUDA error code.
+int launch_newick_noalloc(NewickDev p, int device, cudaStream_t s) {
+  cudaError_t e;
+  unsigned char* scratch = static_scratch_address(device, &e);
+  if (!scratch) return (int)e;
+  if (p.n <= 0) return 0;
+  p.items = scratch;
+  p.only_deferred = 0;
+  k_newick_cta<kCtaThreads><<<p.n, kCtaThreads, CtaLayout(kCtaThreads).total, s>>>(p);
+  p.only_deferred = 1;
+  k_newick<<<(p.n + 31) / 32, 32, 0, s>>>(p);
+  return (int)cudaGetLastError();
 }
 
 void launch_split(const uint8_t* on_pat, int t0, int n, int32_t* list, int32_t* n_pat_out, cudaStream_t s) {
