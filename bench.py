@@ -366,15 +366,32 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
         phmm.set_host_threads(env.host_threads)
     gathered = None
 
+    side = torch.cuda.Stream(device=dev) if dist is not None else None
+    stage_v = torch.zeros(per, dtype=torch.float64, device=f"cuda:{dev}") if dist is not None else None
+    ev_ready, ev_done = (torch.cuda.Event(), torch.cuda.Event()) if dist is not None else (None, None)
+    gathers = 0
+
     def gather_dev(ptr, n):
-        """NCCL all-gather of this rank's device-resident log-likelihoods (queued on env.stream)."""
-        nonlocal gathered
+        """NCCL all-gather of this rank's device-resident log-likelihoods. The rank's vector is copied (16 KB, on the
+        kernels' stream, behind k_hmm) into a staging tensor and gathered from there on a side stream, so that the
+        next step's kernels do not wait for the slowest rank; the staging tensor is not rewritten before the gather
+        that reads it is done. Everything is inside the timed region and complete at its closing synchronize."""
+        nonlocal gathered, gathers
         if dist is None:
             return None
         local = torch.as_tensor(_DevArr(ptr, n), device=f"cuda:{dev}")
         if gathered is None:
             gathered = torch.empty(world * per, dtype=torch.float64, device=f"cuda:{dev}")
-        return sharding.gather_loglik(dist, local, B_total, out=gathered)
+        if gathers:
+            env.stream.wait_event(ev_done)
+        stage_v[:n].copy_(local)
+        ev_ready.record(env.stream)
+        with torch.cuda.stream(side):
+            side.wait_event(ev_ready)
+            sharding.gather_loglik(dist, stage_v, B_total, out=gathered)
+            ev_done.record(side)
+        gathers += 1
+        return gathered[:B_total]
 
     sampler = ClockSampler(dev)
     rec = {}
@@ -446,6 +463,39 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
                                              "ms_newick", "newick_host_trees", "pattern_trees")}
             if rank == 0:
                 assert np.array_equal(ll_host, full_value, equal_nan=True), "text in and arrays in must give the same doubles"
+        # -------- e2e_pipeline: the product's real entry point, RunPipeline (src/PhyloHMM.cpp:393-446): RevBayes trace TSV in,
+        # linearham TSV out (scoring + one SampleNaiveSequence per row), on c3; beside it the reference's own RunPipeline
+        pipe = None
+        if cfg_name == "c3" and world == 1 and not args.no_e2e:
+            from linearham_b200 import synth
+            rows = [{"newick": text[i], "er": shard["er"][i], "pi": shard["pi"][i], "alpha": float(alpha_s[i])} for i in range(Bs)]
+            tsv_all, tsv_small = os.path.join(workdir, "trace.tsv"), os.path.join(workdir, "trace64.tsv")
+            synth.write_tsv(tsv_all, rows)
+            synth.write_tsv(tsv_small, rows[:64])
+            out_tsv = os.path.join(workdir, "lh_out.tsv")
+            ours = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0, device=dev)
+            ours.RunPipeline(tsv_small, out_tsv, R, 1024)      # fresh object, seed 0: comparable with the reference's run
+            ours_small = open(out_tsv).read()
+            ours.RunPipeline(tsv_all, out_tsv, R, 1024)         # warm-up
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                ours.RunPipeline(tsv_all, out_tsv, R, 1024)
+            pipe_s = time.perf_counter() - t0
+            ours.close()
+            pipe = {"value": Bs * steps / pipe_s, "unit": "rows/s", "rows_per_run": Bs, "batch_size": 1024,
+                    "tsv_bytes": os.path.getsize(tsv_all),
+                    "api": "PhyloHMM::RunPipeline (TSV in -> TSV out; reader thread | device scoring from Newick text | "
+                           "SampleNaiveSequence + output line in file order, overlapped)"}
+            if want_cpu and po.have_ref():
+                ref = po.RefPhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+                ref_out = os.path.join(workdir, "ref_out.tsv")
+                t0 = time.perf_counter()
+                ref.run_pipeline(tsv_small, ref_out, R)
+                ref_s = time.perf_counter() - t0
+                ref.close()
+                pipe["reference"] = {"value": 64 / ref_s, "unit": "rows/s", "cores": 1, "sample": f"first 64 rows, {ref_s:.2f} s, "
+                                     "the reference's own RunPipeline (oracle/_ref), one thread as the reference runs it"}
+                pipe["output_identical_to_reference_on_sample"] = open(ref_out).read() == ours_small
         clocks = sampler.stop() if full_record else None
 
         # -------- N > 1: what the ranks computed equals what one GPU computes (bit for bit) ----------
@@ -529,6 +579,7 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
                 "value": B_total * steps / arr_max, "unit": UNIT, "h2d_bytes_per_step": h2d_a, "d2h_bytes_per_step": d2h_a,
                 "last_call_ms_rank0": arr_detail,
                 "api": "lh_score_batch (pre-flattened operation arrays + pre-computed rates in, each rank's log-likelihoods on its host out)"},
+            "e2e_pipeline": pipe,
             "gpu_launches": launches_total + e2e_launches, "clocks": clocks, "parity": parity, "parity_vs_n1": parity_vs_n1,
             "finite_fraction": float(np.mean(np.isfinite(full_value))),
         }
@@ -592,7 +643,7 @@ def main():
             c5_args.steps, c5_args.warmup, c5_args.batch = 2, 3, 0
             c5 = bench_c5.run(env, c5_args)
             if env.rank == 0:
-                keep = ("value", "unit", "ms_per_step", "steps", "warmup", "config", "roofline", "e2e", "e2e_arrays", "parity", "cpu_baseline",
+                keep = ("value", "unit", "ms_per_step", "steps", "warmup", "config", "roofline", "e2e", "e2e_arrays", "e2e_pipeline", "parity", "cpu_baseline",
                         "parity_vs_n1", "gpu_launches", "families_per_s", "value_is_end_to_end")
                 out["c3"] = {k: c3[k] for k in keep if k in c3}
                 out["c5"] = {k: c5[k] for k in keep if k in c5}

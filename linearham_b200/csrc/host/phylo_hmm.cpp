@@ -3,6 +3,10 @@
 // and the batched RunPipeline (src/PhyloHMM.cpp:393-446 with B rows per device call).
 #include "phylo_hmm.hpp"
 
+#include <charconv>
+#include <chrono>
+#include <cstdlib>
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -94,76 +98,99 @@ double to_double(const std::string& s, const std::string& what) {
 }
 
 // ---- Newick re-export (pll_utree_export_newick, utree.c:148-270) ----------------------------
-struct NwParser {
-  const std::string& s;
-  std::size_t p = 0;
-  explicit NwParser(const std::string& str) : s(str) {}
-  void skip() {
-    for (;;) {
-      while (p < s.size() && (s[p] == ' ' || s[p] == '\t' || s[p] == '\n' || s[p] == '\r')) ++p;
-      if (p < s.size() && s[p] == '[') {
-        while (p < s.size() && s[p] != ']') ++p;
-        if (p < s.size()) ++p;
-      } else {
-        return;
-      }
-    }
+// The exported text lists the nodes in the order the input does, so the export is one streaming pass over the
+// characters: comments and blanks go, every length becomes "%f" of the parsed value (a missing or zero length EPS,
+// src/PhyloHMM.cpp:422), the trifurcation ends in ":0.0;". std::to_chars(fixed, 6) prints the digits printf's "%f"
+// prints (both round the exact binary value). A 9 KB string took 218 us when the text was assembled subtree by
+// subtree; this pass takes a tenth of that, which matters because RunPipeline's reader does it for every row.
+inline bool nw_delim(char c) {
+  return c == '(' || c == ')' || c == ',' || c == ':' || c == ';' || c == '[' || c == ' ' || c == '\t' || c == '\n' ||
+         c == '\r' || c == '\0';
+}
+inline const char* nw_skip(const char* p) {
+  for (;;) {
+    while (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r') ++p;
+    if (*p != '[') return p;
+    while (*p != ']' && *p) ++p;
+    if (*p) ++p;
   }
-  std::string label() {
-    skip();
-    const std::size_t b = p;
-    while (p < s.size() && std::strchr("(),:;[ \t\n\r", s[p]) == nullptr) ++p;
-    return s.substr(b, p - b);
+}
+// optional ":number" -> its value (0 when absent); the reference reads it with atof
+inline const char* nw_length(const char* p, const char* end, double* out) {
+  p = nw_skip(p);
+  *out = 0.0;
+  if (*p != ':') return p;
+  p = nw_skip(p + 1);
+  if ((*p >= '0' && *p <= '9') || *p == '-' || *p == '.') {
+    const auto r = std::from_chars(p, end, *out);
+    if (r.ec == std::errc() && nw_delim(*r.ptr)) return r.ptr;
   }
-  double length() {
-    skip();
-    double v = 0.0;
-    if (p < s.size() && s[p] == ':') {
-      ++p;
-      skip();
-      char* end = nullptr;
-      v = std::strtod(s.c_str() + p, &end);
-      if (end == s.c_str() + p) throw std::invalid_argument("malformed branch length in Newick string");
-      p = end - s.c_str();
-    }
-    return v ? v : kEps;
-  }
-  std::string subtree(bool top) {
-    skip();
-    char buf[64];
-    if (p < s.size() && s[p] == '(') {
-      ++p;
-      std::vector<std::string> kids;
-      kids.push_back(subtree(false));
-      skip();
-      while (p < s.size() && s[p] == ',') {
-        ++p;
-        kids.push_back(subtree(false));
-        skip();
-      }
-      if (p >= s.size() || s[p] != ')') throw std::invalid_argument("unbalanced Newick string");
-      ++p;
-      const std::string lab = label();
-      const double len = length();
-      if (kids.size() != (top ? 3u : 2u)) throw std::invalid_argument("Newick tree is not an unrooted binary tree");
-      std::string out = "(" + kids[0];
-      for (std::size_t i = 1; i < kids.size(); ++i) out += "," + kids[i];
-      if (top) return out + ")" + lab + ":0.0;";
-      std::snprintf(buf, sizeof(buf), ":%f", len);
-      return out + ")" + lab + buf;
-    }
-    const std::string lab = label();
-    if (lab.empty()) throw std::invalid_argument("empty tip label in Newick string");
-    std::snprintf(buf, sizeof(buf), ":%f", length());
-    return lab + buf;
-  }
-};
+  char* stop = nullptr;
+  *out = std::strtod(p, &stop);
+  if (stop == p) throw std::invalid_argument("malformed branch length in Newick string");
+  return stop;
+}
+inline void nw_put_length(std::string& out, double v) {
+  char buf[512];  // "%f" of 1e308 has 316 characters
+  out.push_back(':');
+  const auto r = std::to_chars(buf, buf + sizeof(buf), v ? v : kEps, std::chars_format::fixed, 6);
+  out.append(buf, r.ptr);
+}
 
 }  // namespace
 
 std::string ExportNewick(const std::string& newick) {
-  NwParser ps(newick);
-  return ps.subtree(true);
+  const char* p = newick.c_str();
+  const char* const end = p + newick.size();
+  std::string out;
+  out.reserve(newick.size());
+  std::vector<int> kids;  // children finished so far, per open node
+  bool want_item = true;
+  for (;;) {
+    p = nw_skip(p);
+    if (want_item) {
+      if (*p == '(') {
+        out.push_back('(');
+        kids.push_back(0);
+        ++p;
+        continue;
+      }
+      const char* b = p;
+      while (!nw_delim(*p)) ++p;
+      if (p == b) throw std::invalid_argument("empty tip label in Newick string");
+      out.append(b, p);
+      double len;
+      p = nw_length(p, end, &len);
+      nw_put_length(out, len);
+      if (kids.empty()) return out;  // a single tip
+      ++kids.back();
+      want_item = false;
+    } else if (*p == ',') {
+      out.push_back(',');
+      ++p;
+      want_item = true;
+    } else if (*p == ')') {
+      ++p;
+      out.push_back(')');
+      p = nw_skip(p);
+      const char* b = p;
+      while (!nw_delim(*p)) ++p;
+      out.append(b, p);
+      double len;
+      p = nw_length(p, end, &len);
+      const bool top = kids.size() == 1;
+      if (kids.back() != (top ? 3 : 2)) throw std::invalid_argument("Newick tree is not an unrooted binary tree");
+      kids.pop_back();
+      if (top) {
+        out.append(":0.0;");
+        return out;
+      }
+      nw_put_length(out, len);
+      ++kids.back();
+    } else {
+      throw std::invalid_argument("unbalanced Newick string");
+    }
+  }
 }
 
 // flat arrays behind lh_family_desc_t
@@ -443,7 +470,7 @@ void PhyloHMM::WriteOutputLine(std::ostream& out) const {
   out << iteration_ << "\t" << rb_loglikelihood_ << "\t" << prior_ << "\t" << alpha_ << "\t";
   for (double v : er_) out << v << "\t";
   for (double v : pi_) out << v << "\t";
-  out << ExportNewick(tree_) << "\t";
+  out << (tree_export_cache_.empty() ? ExportNewick(tree_) : tree_export_cache_) << "\t";
   for (double v : sr_) out << v << "\t";
   out << lh_loglikelihood_ << "\t" << logweight_ << "\t" << naive_sequence_ << "\t";
   out << vgerm_state_str_samp_ << "\t" << vgerm_left_del_samp_ << "\t" << vgerm_right_del_samp_ << "\t"
@@ -458,16 +485,39 @@ void PhyloHMM::WriteOutputLine(std::ostream& out) const {
       << jgerm_right_insertion_samp_ << "\n";
 }
 
-// src/PhyloHMM.cpp:393-446, batched: read up to batch_size rows, score them in one device call with
-// the forward tables returned, then finish every row on the host in file order (the RNG advances
-// exactly as in the reference: one SampleNaiveSequence per row).
+// src/PhyloHMM.cpp:393-446, batched and pipelined. Three stages run side by side over a ring of three batches:
+//   reader  (a thread)   reads up to batch_size rows of the RevBayes trace, converts their numbers, computes the
+//                        discrete-Gamma rates (bit-identical to pll_compute_gamma_cats) and the exported tree text
+//   scorer  (a thread)   one device call per batch, Newick text in (parsed on the GPU), forward tables out
+//   sampler (the caller) finishes every row in file order: SampleNaiveSequence + the output line. The RNG
+//                        advances exactly as in the reference: one std::mt19937 walked row by row
+//                        (src/HMM.cpp:325-329, 1252-1257).
+// So the TSV read / ingest of batch b+1, the device scoring of b and the host sampling of b-1 overlap.
+namespace {
+struct PipeRow {
+  int iteration;
+  double rb, prior, alpha, er[6], pi[4];
+  std::string tree, exported;
+};
+struct PipeBatch {
+  std::vector<PipeRow> rows;
+  std::vector<const char*> nw;
+  std::vector<int64_t> len;
+  std::vector<double> er, pi, alpha, rates, ll, xe, fv, fvd, fd, fdj, fj;
+  std::vector<int32_t> gs, vds, djs;
+  std::string err;          // a stage's failure, reported by the sampler in file order
+  bool err_is_input = false;
+  int state = 0;            // 0 free, 1 read, 2 scored
+};
+}  // namespace
+
 void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& output_path, int num_rates, int batch_size) {
   if (batch_size < 1) throw std::invalid_argument("batch_size must be positive");
   std::ifstream in(input_path);
   if (!in) throw std::runtime_error("cannot open " + input_path);
-  std::string line;
-  if (!std::getline(in, line)) throw std::runtime_error(input_path + " is empty");
-  const std::vector<std::string> header = split_tsv(line);
+  std::string header_line;
+  if (!std::getline(in, header_line)) throw std::runtime_error(input_path + " is empty");
+  const std::vector<std::string> header = split_tsv(header_line);
   static const char* kCols[15] = {"Iteration", "Likelihood", "Prior", "alpha", "er[1]", "er[2]", "er[3]", "er[4]",
                                   "er[5]", "er[6]", "pi[1]", "pi[2]", "pi[3]", "pi[4]", "tree"};
   int col[15];
@@ -481,97 +531,249 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
   if (!outfile) throw std::runtime_error("cannot open " + output_path);
   EnsureDeviceFamily();
   const lh_family_desc_t& d = flat_->desc;
-  const int T = xmsa_.rows();
   const std::size_t vd_n = (std::size_t)d.vd_sites * d.vd_states, dj_n = (std::size_t)d.dj_sites * d.dj_states;
   sr_.assign(num_rates, 0.0);
-  bool first = true;
 
-  struct Row {
-    int iteration;
-    double rb, prior, alpha, er[6], pi[4];
-    std::string tree;
+  constexpr int kRing = 3;
+  PipeBatch ring[kRing];
+  std::mutex m;
+  std::condition_variable cv;
+  int n_read = 0;           // batches the reader has handed over; -1 - n: the input ended after n batches
+  bool input_done = false, abort = false;
+  auto wait_for = [&](PipeBatch& b, int state) {  // false: the pipeline is being torn down
+    std::unique_lock<std::mutex> lk(m);
+    cv.wait(lk, [&] { return abort || b.state == state; });
+    return !abort;
   };
-  std::vector<Row> rows;
-  bool eof = false;
-  while (!eof) {
-    rows.clear();
-    while ((int)rows.size() < batch_size) {
-      if (!std::getline(in, line)) { eof = true; break; }
-      if (line.empty()) continue;
-      const std::vector<std::string> f = split_tsv(line);
-      if ((int)f.size() < (int)header.size()) throw std::runtime_error("too few columns in a row of " + input_path);
-      Row r;
-      r.iteration = (int)to_double(f[col[0]], "Iteration");
-      r.rb = to_double(f[col[1]], "Likelihood");
-      r.prior = to_double(f[col[2]], "Prior");
-      r.alpha = to_double(f[col[3]], "alpha");
-      for (int k = 0; k < 6; ++k) r.er[k] = to_double(f[col[4 + k]], "er");
-      for (int k = 0; k < 4; ++k) r.pi[k] = to_double(f[col[10 + k]], "pi");
-      r.tree = f[col[14]];
-      rows.push_back(r);
+  auto hand_over = [&](PipeBatch& b, int state) {
+    {
+      std::lock_guard<std::mutex> lk(m);
+      b.state = state;
     }
-    const int B = (int)rows.size();
-    if (B == 0) break;
-    std::vector<const char*> nw(B);
-    std::vector<double> er(6 * (std::size_t)B), pi(4 * (std::size_t)B), alpha(B), rates((std::size_t)B * num_rates), ll(B);
-    for (int b = 0; b < B; ++b) {
-      nw[b] = rows[b].tree.c_str();
-      std::memcpy(&er[6 * b], rows[b].er, sizeof(double) * 6);
-      std::memcpy(&pi[4 * b], rows[b].pi, sizeof(double) * 4);
-      alpha[b] = rows[b].alpha;
-    }
-    std::vector<int32_t> children((std::size_t)B * 2 * (T - 2)), root_child(B);
-    std::vector<double> blen((std::size_t)B * 2 * (T - 2)), root_blen(B);
-    if (lhh_newick_to_ops(T, flat_->label_ptrs.data(), B, nw.data(), 0, children.data(), blen.data(), root_child.data(), root_blen.data()))
-      throw std::invalid_argument(lhh_last_error());
-    if (lhh_gamma_cats_batch(B, alpha.data(), num_rates, rates.data())) throw std::invalid_argument(lhh_last_error());
-    lh_tree_batch_t tb{B, num_rates, children.data(), blen.data(), root_child.data(), root_blen.data(), er.data(), pi.data(), rates.data()};
-    std::vector<double> xe((std::size_t)B * d.n_sites), fv((std::size_t)B * d.n_v), fvd(B * vd_n), fd((std::size_t)B * std::max(d.n_d, 1)),
-        fdj(B * std::max<std::size_t>(dj_n, 1)), fj((std::size_t)B * d.n_j);
-    std::vector<int32_t> gs((std::size_t)B * 3), vds((std::size_t)B * d.vd_sites), djs((std::size_t)B * std::max(d.dj_sites, 1));
-    lh_outputs_t o{xe.data(), fv.data(), fvd.data(), fd.data(), fdj.data(), fj.data(), gs.data(), vds.data(), djs.data()};
-    if (dev_group_ ? lh_group_score_batch(dev_group_, &tb, ll.data(), &o) : lh_score_batch(dev_family_, &tb, ll.data(), &o))
-      throw std::runtime_error(dev_group_ ? lh_group_last_error() : lh_last_error());
+    cv.notify_all();
+  };
 
-    for (int b = 0; b < B; ++b) {
-      const Row& r = rows[b];
-      iteration_ = r.iteration;
-      rb_loglikelihood_ = r.rb;
-      prior_ = r.prior;
-      alpha_ = r.alpha;
-      er_.assign(r.er, r.er + 6);
-      pi_.assign(r.pi, r.pi + 4);
-      tree_ = r.tree;
-      sr_.assign(rates.begin() + (std::size_t)b * num_rates, rates.begin() + (std::size_t)(b + 1) * num_rates);
-      xmsa_emission_.assign(xe.begin() + (std::size_t)b * d.n_sites, xe.begin() + (std::size_t)(b + 1) * d.n_sites);
-      vgerm_.forward.assign(fv.begin() + (std::size_t)b * d.n_v, fv.begin() + (std::size_t)(b + 1) * d.n_v);
-      jgerm_.forward.assign(fj.begin() + (std::size_t)b * d.n_j, fj.begin() + (std::size_t)(b + 1) * d.n_j);
-      vd_junction_.forward.assign(d.vd_sites, d.vd_states, 0.0);
-      std::memcpy(vd_junction_.forward.data(), &fvd[b * vd_n], vd_n * sizeof(double));
-      vd_junction_.scaler_counts.assign(vds.begin() + (std::size_t)b * d.vd_sites, vds.begin() + (std::size_t)(b + 1) * d.vd_sites);
-      if (d.has_d) {
-        dgerm_.forward.assign(fd.begin() + (std::size_t)b * d.n_d, fd.begin() + (std::size_t)(b + 1) * d.n_d);
-        dj_junction_.forward.assign(d.dj_sites, d.dj_states, 0.0);
-        std::memcpy(dj_junction_.forward.data(), &fdj[b * dj_n], dj_n * sizeof(double));
-        dj_junction_.scaler_counts.assign(djs.begin() + (std::size_t)b * d.dj_sites, djs.begin() + (std::size_t)(b + 1) * d.dj_sites);
+  // ---- reader -----------------------------------------------------------------------------------------------
+  double ms_reader = 0.0, ms_scorer = 0.0, ms_sampler = 0.0;   // busy time of the three stages (LH_TRACE)
+  const int hw = host_threads_ > 0 ? host_threads_ : (int)std::max(1u, std::thread::hardware_concurrency());
+  const int reader_threads = std::max(1, hw / 2);
+  std::thread reader([&] {
+    std::string line;
+    std::vector<std::string> lines;
+    bool eof = false;
+    for (int bi = 0; !eof; ++bi) {
+      PipeBatch& b = ring[bi % kRing];
+      if (!wait_for(b, 0)) return;
+      b.rows.clear();
+      b.err.clear();
+      try {
+        const auto t_r0 = std::chrono::steady_clock::now();
+        // the lines are read one after the other; their fields (15 numbers, a tree of several KB to re-export)
+        // are independent and are worked on by a few threads
+        lines.clear();
+        while ((int)lines.size() < batch_size) {
+          if (!std::getline(in, line)) { eof = true; break; }
+          if (line.empty()) continue;
+          lines.emplace_back(std::move(line));
+        }
+        const int n_lines = (int)lines.size();
+        b.rows.assign(n_lines, PipeRow{});
+        std::vector<std::string> row_err(n_lines);
+        auto parse_rows = [&](int w, int nw) {
+          for (int i = w; i < n_lines; i += nw) {
+            try {
+              const std::vector<std::string> f = split_tsv(lines[i]);
+              if ((int)f.size() < (int)header.size()) throw std::runtime_error("too few columns in a row of " + input_path);
+              PipeRow& r = b.rows[i];
+              r.iteration = (int)to_double(f[col[0]], "Iteration");
+              r.rb = to_double(f[col[1]], "Likelihood");
+              r.prior = to_double(f[col[2]], "Prior");
+              r.alpha = to_double(f[col[3]], "alpha");
+              for (int k = 0; k < 6; ++k) r.er[k] = to_double(f[col[4 + k]], "er");
+              for (int k = 0; k < 4; ++k) r.pi[k] = to_double(f[col[10 + k]], "pi");
+              r.tree = f[col[14]];
+              // the exported tree text of the output line (pll_utree_export_newick of the parsed tree; text work
+              // only). A string it cannot read is left to the device call, whose parser words the error.
+              try {
+                r.exported = ExportNewick(r.tree);
+              } catch (const std::exception&) {
+                r.exported.clear();
+              }
+            } catch (const std::exception& e) {
+              row_err[i] = e.what();
+            }
+          }
+        };
+        const int n_workers = std::max(1, std::min({reader_threads, n_lines / 16, 16}));
+        std::vector<std::thread> team;
+        for (int w = 1; w < n_workers; ++w) team.emplace_back(parse_rows, w, n_workers);
+        parse_rows(0, n_workers);
+        for (auto& t : team) t.join();
+        for (int i = 0; i < n_lines; ++i)
+          if (!row_err[i].empty()) throw std::runtime_error(row_err[i]);   // the first bad row, in file order
+        ms_reader += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_r0).count();
+        const std::size_t B = b.rows.size();
+        b.nw.resize(B);
+        b.len.resize(B);
+        b.er.resize(6 * B);
+        b.pi.resize(4 * B);
+        b.alpha.resize(B);
+        b.rates.resize(B * (std::size_t)num_rates);
+        for (std::size_t i = 0; i < B; ++i) {
+          b.nw[i] = b.rows[i].tree.c_str();
+          b.len[i] = (int64_t)b.rows[i].tree.size();
+          std::memcpy(&b.er[6 * i], b.rows[i].er, sizeof(double) * 6);
+          std::memcpy(&b.pi[4 * i], b.rows[i].pi, sizeof(double) * 4);
+          b.alpha[i] = b.rows[i].alpha;
+        }
+        if (B && lhh_gamma_cats_batch((int)B, b.alpha.data(), num_rates, b.rates.data())) {
+          b.err = lhh_last_error();
+          b.err_is_input = true;
+        }
+      } catch (const std::exception& e) {
+        b.err = e.what();
+        eof = true;
       }
-      vgerm_.scaler_count = gs[3 * b];
-      dgerm_.scaler_count = gs[3 * b + 1];
-      jgerm_.scaler_count = gs[3 * b + 2];
-      loglik_cached_ = ll[b];
-      cache_forward_ = false;
-      lh_loglikelihood_ = ll[b];
-      logweight_ = lh_loglikelihood_ - rb_loglikelihood_;
-      naive_sequence_ = SampleNaiveSequence();
-      if (first) {
-        WriteOutputHeaders(outfile);
-        first = false;
+      {
+        std::lock_guard<std::mutex> lk(m);
+        b.state = 1;
+        ++n_read;
+        if (eof) input_done = true;
       }
-      WriteOutputLine(outfile);
+      cv.notify_all();
     }
+  });
+
+  // ---- scorer -----------------------------------------------------------------------------------------------
+  std::thread scorer([&] {
+    for (int bi = 0;; ++bi) {
+      {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return abort || n_read > bi || input_done; });
+        if (abort || n_read <= bi) return;   // torn down, or the input ended before this batch
+      }
+      PipeBatch& b = ring[bi % kRing];
+      const std::size_t B = b.rows.size();
+      if (B && b.err.empty()) {
+        b.ll.resize(B);
+        b.xe.resize(B * (std::size_t)d.n_sites);
+        b.fv.resize(B * (std::size_t)d.n_v);
+        b.fvd.resize(B * vd_n);
+        b.fd.resize(B * (std::size_t)std::max(d.n_d, 1));
+        b.fdj.resize(B * std::max<std::size_t>(dj_n, 1));
+        b.fj.resize(B * (std::size_t)d.n_j);
+        b.gs.resize(B * 3);
+        b.vds.resize(B * (std::size_t)d.vd_sites);
+        b.djs.resize(B * (std::size_t)std::max(d.dj_sites, 1));
+        lh_newick_batch_t nb{};
+        nb.n_trees = (int)B;
+        nb.n_rates = num_rates;
+        nb.newick = b.nw.data();
+        nb.length = b.len.data();
+        nb.er = b.er.data();
+        nb.pi = b.pi.data();
+        nb.rates = b.rates.data();
+        lh_outputs_t o{b.xe.data(), b.fv.data(), b.fvd.data(), b.fd.data(), b.fdj.data(), b.fj.data(),
+                       b.gs.data(), b.vds.data(), b.djs.data(), nullptr};
+        const auto t_s0 = std::chrono::steady_clock::now();
+        const int rc = dev_group_ ? lh_group_score_newick(dev_group_, &nb, b.ll.data(), &o)
+                                  : lh_score_newick(dev_family_, &nb, b.ll.data(), &o);
+        ms_scorer += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_s0).count();
+        if (rc) {
+          b.err = dev_group_ ? lh_group_last_error() : lh_last_error();
+          b.err_is_input = b.err.rfind("tree ", 0) == 0;   // what the reference's parser / SetTipStates would refuse
+        }
+      }
+      hand_over(b, 2);
+    }
+  });
+
+  // ---- sampler (this thread), in file order -------------------------------------------------------------------
+  std::string failure;
+  bool failure_is_input = false, first = true;
+  try {
+    for (int bi = 0;; ++bi) {
+      {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return ring[bi % kRing].state == 2 || (input_done && n_read <= bi); });
+        if (ring[bi % kRing].state != 2) break;   // the input ended before this batch
+      }
+      PipeBatch& b = ring[bi % kRing];
+      if (!b.err.empty()) {
+        failure = b.err;
+        failure_is_input = b.err_is_input;
+        break;
+      }
+      const int B = (int)b.rows.size();
+      const auto t_w0 = std::chrono::steady_clock::now();
+      for (int i = 0; i < B; ++i) {
+        const PipeRow& r = b.rows[i];
+        iteration_ = r.iteration;
+        rb_loglikelihood_ = r.rb;
+        prior_ = r.prior;
+        alpha_ = r.alpha;
+        er_.assign(r.er, r.er + 6);
+        pi_.assign(r.pi, r.pi + 4);
+        tree_ = r.tree;
+        tree_export_cache_ = r.exported;
+        sr_.assign(b.rates.begin() + (std::size_t)i * num_rates, b.rates.begin() + (std::size_t)(i + 1) * num_rates);
+        xmsa_emission_.assign(b.xe.begin() + (std::size_t)i * d.n_sites, b.xe.begin() + (std::size_t)(i + 1) * d.n_sites);
+        vgerm_.forward.assign(b.fv.begin() + (std::size_t)i * d.n_v, b.fv.begin() + (std::size_t)(i + 1) * d.n_v);
+        jgerm_.forward.assign(b.fj.begin() + (std::size_t)i * d.n_j, b.fj.begin() + (std::size_t)(i + 1) * d.n_j);
+        vd_junction_.forward.assign(d.vd_sites, d.vd_states, 0.0);
+        std::memcpy(vd_junction_.forward.data(), &b.fvd[i * vd_n], vd_n * sizeof(double));
+        vd_junction_.scaler_counts.assign(b.vds.begin() + (std::size_t)i * d.vd_sites, b.vds.begin() + (std::size_t)(i + 1) * d.vd_sites);
+        if (d.has_d) {
+          dgerm_.forward.assign(b.fd.begin() + (std::size_t)i * d.n_d, b.fd.begin() + (std::size_t)(i + 1) * d.n_d);
+          dj_junction_.forward.assign(d.dj_sites, d.dj_states, 0.0);
+          std::memcpy(dj_junction_.forward.data(), &b.fdj[i * dj_n], dj_n * sizeof(double));
+          dj_junction_.scaler_counts.assign(b.djs.begin() + (std::size_t)i * d.dj_sites, b.djs.begin() + (std::size_t)(i + 1) * d.dj_sites);
+        }
+        vgerm_.scaler_count = b.gs[3 * i];
+        dgerm_.scaler_count = b.gs[3 * i + 1];
+        jgerm_.scaler_count = b.gs[3 * i + 2];
+        loglik_cached_ = b.ll[i];
+        cache_forward_ = false;
+        lh_loglikelihood_ = b.ll[i];
+        logweight_ = lh_loglikelihood_ - rb_loglikelihood_;
+        naive_sequence_ = SampleNaiveSequence();
+        if (first) {
+          WriteOutputHeaders(outfile);
+          first = false;
+        }
+        WriteOutputLine(outfile);
+      }
+      ms_sampler += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_w0).count();
+      hand_over(b, 0);
+    }
+  } catch (...) {
+    {
+      std::lock_guard<std::mutex> lk(m);
+      abort = true;
+    }
+    cv.notify_all();
+    reader.join();
+    scorer.join();
+    tree_export_cache_.clear();
+    throw;
   }
+  {
+    std::lock_guard<std::mutex> lk(m);
+    abort = true;
+  }
+  cv.notify_all();
+  reader.join();
+  scorer.join();
   tree_.clear();
+  tree_export_cache_.clear();
   outfile.close();
+  if (std::getenv("LH_TRACE"))
+    std::fprintf(stderr, "LHTRACE RunPipeline busy ms: reader %.1f (%d threads)  scorer %.1f  sampler+writer %.1f\n", ms_reader,
+                 reader_threads, ms_scorer, ms_sampler);
+  if (!failure.empty()) {
+    if (failure_is_input) throw std::invalid_argument(failure);
+    throw std::runtime_error(failure);
+  }
 }
 
 }  // namespace linearham

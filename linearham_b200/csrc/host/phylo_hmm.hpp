@@ -238,6 +238,7 @@ class PhyloHMM : public HMM {
   double loglik_cached_ = 0;
 
   std::unique_ptr<FlatFamily> flat_;
+  std::string tree_export_cache_;     // RunPipeline: ExportNewick(tree_) made ahead by the reader stage (else empty)
   lh_family* dev_family_ = nullptr;   // the device handle (member 0 of the group when there are several devices)
   lh_group* dev_group_ = nullptr;
   std::vector<int> devices_{0};

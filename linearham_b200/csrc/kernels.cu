@@ -710,8 +710,10 @@ int prune_max_ctas_per_sm(int ns, int smem_slots) {
 // messages k_prune left per category (core_likelihood_avx.c:1130-1251), the naive-sequence
 // correction and the exponential (src/PhyloHMM.cpp:219-240). When the pruning ran on site
 // patterns, the naive tip's factor - column `code` of its branch's Q block - is multiplied in
-// here, with the node's rescaling test (core_partials.c:648-659) applied to the product as the
-// reference applies it.
+// here, with the node's rescaling test applied to the product - per rate category (this kernel's rule;
+// libpll tests all 4R entries of the site at once, core_partials.c:648-659), the counts being reconciled
+// exactly when the categories are summed. tests/test_scaling_regime.py pins the results in the underflow
+// regime to the reference's.
 __global__ void __launch_bounds__(128) k_edge(FamilyDev f, BatchDev b, EdgeCfg cfg, int tree0, int ntrees) {
   const int S = f.S, R = b.R, NB = 2 * f.T - 3, edge_br = NB - 1;
   const double weight = 1.0 / R;  // pll.c:746-747
@@ -906,23 +908,30 @@ __device__ __forceinline__ double csc_dot(const CscDev& m, const double* prev, i
   return acc;
 }
 
-// The same dot product with the zero terms kept, for a previous row that holds an infinity or a NaN (ScaleMatrix
-// multiplies a whole row by 2^256 while ANY entry is below 2^-256, so in the underflow regime the large entries
-// overflow): the reference's dense product then meets inf * 0 = NaN, which dropping the zero terms would hide.
-__device__ double csc_dot_dense(const CscDev& m, const double* prev, int j) {
+// The reference's dot product is dense. Dropping its zero terms changes nothing but this: an infinity or a NaN
+// in the previous row (ScaleMatrix multiplies a whole row by 2^256 while ANY entry is below 2^-256, so in the
+// underflow regime the large entries overflow) times a zero coefficient is NaN, and a NaN term makes the sum NaN.
+// So for a row that is not tame the sparse product is kept and the sum is poisoned exactly when some non-finite
+// entry of `prev` falls outside the column's non-zero rows: `nf_total` non-finite entries in all (counted once
+// per row by the warp), of which the loop below meets `nf_seen`. (finite * 0 = +-0 leaves every sum as it is.)
+__device__ __forceinline__ int warp_count_nonfinite(const double* prev, int n, int lane) {
+  int c = 0;
+  for (int k = lane; k < n; k += 32) c += !(fabs(prev[k]) <= DBL_MAX);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  return c;
+}
+__device__ double csc_dot_dense(const CscDev& m, const double* prev, int j, int nf_total) {
   double acc = 0.0;
-  int p = m.colptr[j];
+  int nf_seen = 0;
   const int e = m.colptr[j + 1];
-  int next_row = p < e ? __double2loint(__ldg(m.ent + p).y) : -1;
-  for (int k = 0; k < m.rows; ++k) {
-    double coef = 0.0;
-    if (k == next_row) {
-      coef = __ldg(m.ent + p).x;
-      ++p;
-      next_row = p < e ? __double2loint(__ldg(m.ent + p).y) : -1;
-    }
-    acc += prev[k] * coef;
+  for (int p = m.colptr[j]; p < e; ++p) {
+    const double2 en = __ldg(m.ent + p);
+    const double x = prev[__double2loint(en.y)];
+    nf_seen += !(fabs(x) <= DBL_MAX);
+    acc += x * en.x;
   }
+  if (nf_total > nf_seen) acc += __longlong_as_double(0x7ff8000000000000ll);  // inf * 0 somewhere in the dense sum
   return acc;
 }
 
@@ -947,8 +956,9 @@ __device__ int junction_forward(const FamilyDev& f, const CscDev& t_in, const Cs
         cur[sv.x] = csc_dot(m, prev, sv.x) * xe[sv.y];
       }
     } else {
+      const int nf = tame ? 0 : warp_count_nonfinite(prev, m.rows, lane);
       for (int j = lane; j < Sj; j += 32) {
-        double acc = tame ? csc_dot(m, prev, j) : csc_dot_dense(m, prev, j);
+        double acc = tame ? csc_dot(m, prev, j) : csc_dot_dense(m, prev, j, nf);
         const int idx = inds_rm[(size_t)i * Sj + j];
         acc *= (idx < 0) ? 0.0 : xe[idx];   // FillJunctionEmission: 0 where idx == -1
         cur[j] = acc;
@@ -1012,8 +1022,9 @@ __global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o, 
                                o.vd_scalers ? o.vd_scalers + (size_t)t * f.vd_sites : nullptr, lane);
     if (f.has_d) {
       // ComputeGermlineForwardProbabilities for D (src/HMM.cpp:1160-1177; padding terms are ones)
+      const int nf_d = tame ? 0 : warp_count_nonfinite(prev, f.t_vd_d.rows, lane);
       for (int g = lane; g < f.n_d; g += 32) {
-        double v = tame ? csc_dot(f.t_vd_d, prev, g) : csc_dot_dense(f.t_vd_d, prev, g);
+        double v = tame ? csc_dot(f.t_vd_d, prev, g) : csc_dot_dense(f.t_vd_d, prev, g, nf_d);
         v *= e_dgerm[g];
         cur[g] = v;
       }
@@ -1028,8 +1039,9 @@ __global__ void __launch_bounds__(128) k_hmm(FamilyDev f, BatchDev b, HmmOut o, 
                              o.dj_scalers ? o.dj_scalers + (size_t)t * f.dj_sites : nullptr, lane);
     }
     const CscDev& t_out = f.has_d ? f.t_dj_j : f.t_vd_d;
+    const int nf_j = tame ? 0 : warp_count_nonfinite(prev, t_out.rows, lane);
     for (int g = lane; g < f.n_j; g += 32) {
-      double v = tame ? csc_dot(t_out, prev, g) : csc_dot_dense(t_out, prev, g);
+      double v = tame ? csc_dot(t_out, prev, g) : csc_dot_dense(t_out, prev, g, nf_j);
       v *= e_jgerm[g];
       v *= f.jpad_trans[g];
       v *= e_jpad[g];
