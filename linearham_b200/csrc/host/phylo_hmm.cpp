@@ -465,24 +465,43 @@ void PhyloHMM::WriteOutputHeaders(std::ostream& out) const {
   out << "JGene\tJ5pDel\tJ3pDel\tJFwkInsertion\n";
 }
 
-// src/PhyloHMM.cpp:288-327
-void PhyloHMM::WriteOutputLine(std::ostream& out) const {
-  out << iteration_ << "\t" << rb_loglikelihood_ << "\t" << prior_ << "\t" << alpha_ << "\t";
-  for (double v : er_) out << v << "\t";
-  for (double v : pi_) out << v << "\t";
-  out << (tree_export_cache_.empty() ? ExportNewick(tree_) : tree_export_cache_) << "\t";
-  for (double v : sr_) out << v << "\t";
-  out << lh_loglikelihood_ << "\t" << logweight_ << "\t" << naive_sequence_ << "\t";
-  out << vgerm_state_str_samp_ << "\t" << vgerm_left_del_samp_ << "\t" << vgerm_right_del_samp_ << "\t"
-      << vgerm_left_insertion_samp_ << "\t";
-  if (locus_ == "igh") {
-    out << vd_junction_insertion_samp_ << "\t" << dgerm_state_str_samp_ << "\t" << dgerm_left_del_samp_ << "\t"
-        << dgerm_right_del_samp_ << "\t" << dj_junction_insertion_samp_ << "\t";
+// src/PhyloHMM.cpp:288-327. One output line from the row's values and the annotation `h` sampled last
+// (a free function so that RunPipeline's sampling clones format their rows with the very same code).
+namespace {
+struct LineFields {
+  int iteration;
+  double rb, prior, alpha;
+  const double *er, *pi, *sr;
+  int n_er, n_pi, n_sr;
+  const std::string* tree_text;   // already exported (pll_utree_export_newick)
+  double lh, logweight;
+  const std::string* naive;
+};
+void write_output_line(std::ostream& out, const LineFields& f, const HMM& h) {
+  out << f.iteration << "\t" << f.rb << "\t" << f.prior << "\t" << f.alpha << "\t";
+  for (int i = 0; i < f.n_er; ++i) out << f.er[i] << "\t";
+  for (int i = 0; i < f.n_pi; ++i) out << f.pi[i] << "\t";
+  out << *f.tree_text << "\t";
+  for (int i = 0; i < f.n_sr; ++i) out << f.sr[i] << "\t";
+  out << f.lh << "\t" << f.logweight << "\t" << *f.naive << "\t";
+  out << h.vgerm_state_str_samp() << "\t" << h.vgerm_left_del_samp() << "\t" << h.vgerm_right_del_samp() << "\t"
+      << h.vgerm_left_insertion_samp() << "\t";
+  if (h.locus() == "igh") {
+    out << h.vd_junction_insertion_samp() << "\t" << h.dgerm_state_str_samp() << "\t" << h.dgerm_left_del_samp() << "\t"
+        << h.dgerm_right_del_samp() << "\t" << h.dj_junction_insertion_samp() << "\t";
   } else {
-    out << vd_junction_insertion_samp_ << "\t";
+    out << h.vd_junction_insertion_samp() << "\t";
   }
-  out << jgerm_state_str_samp_ << "\t" << jgerm_left_del_samp_ << "\t" << jgerm_right_del_samp_ << "\t"
-      << jgerm_right_insertion_samp_ << "\n";
+  out << h.jgerm_state_str_samp() << "\t" << h.jgerm_left_del_samp() << "\t" << h.jgerm_right_del_samp() << "\t"
+      << h.jgerm_right_insertion_samp() << "\n";
+}
+}  // namespace
+
+void PhyloHMM::WriteOutputLine(std::ostream& out) const {
+  const std::string exported = tree_export_cache_.empty() ? ExportNewick(tree_) : tree_export_cache_;
+  const LineFields f{iteration_, rb_loglikelihood_, prior_, alpha_, er_.data(), pi_.data(), sr_.data(), (int)er_.size(),
+                     (int)pi_.size(), (int)sr_.size(), &exported, lh_loglikelihood_, logweight_, &naive_sequence_};
+  write_output_line(out, f, *this);
 }
 
 // src/PhyloHMM.cpp:393-446, batched and pipelined. Three stages run side by side over a ring of three batches:
@@ -509,6 +528,47 @@ struct PipeBatch {
   bool err_is_input = false;
   int state = 0;            // 0 free, 1 read, 2 scored
 };
+
+// A copy of what SampleNaiveSequence reads and writes - state space, transitions, forward tables, the sampled
+// annotation, the RNG - so that RunPipeline can sample the rows of a batch on several threads. The reference draws
+// every row from ONE std::mt19937 in file order (src/HMM.cpp:325-329, 1252-1257); a row consumes a fixed number of
+// its outputs (one std::discrete_distribution draw per germline region and junction site, each over a weight vector
+// whose length the family fixes), so the generator's state at the start of row i is the batch's start state advanced
+// by i times that number (std::mt19937::discard), and the rows come out exactly as the serial walk gives them. The
+// block ends are checked against the next block's start; a mismatch sends the batch through the serial path.
+class SamplerClone : public HMM {
+ public:
+  explicit SamplerClone(const HMM& h) : HMM(h) { cache_forward_ = false; }
+  double LogLikelihood() override { return 0.0; }
+  std::mt19937& rng() { return rng_; }
+  void Load(const PipeBatch& b, int i, const lh_family_desc_t& d) {
+    const std::size_t vd_n = (std::size_t)d.vd_sites * d.vd_states, dj_n = (std::size_t)d.dj_sites * d.dj_states;
+    vgerm_.forward.assign(b.fv.begin() + (std::size_t)i * d.n_v, b.fv.begin() + (std::size_t)(i + 1) * d.n_v);
+    jgerm_.forward.assign(b.fj.begin() + (std::size_t)i * d.n_j, b.fj.begin() + (std::size_t)(i + 1) * d.n_j);
+    vd_junction_.forward.r = d.vd_sites;
+    vd_junction_.forward.c = d.vd_states;
+    vd_junction_.forward.v.assign(b.fvd.begin() + i * vd_n, b.fvd.begin() + (i + 1) * vd_n);
+    if (d.has_d) {
+      dgerm_.forward.assign(b.fd.begin() + (std::size_t)i * d.n_d, b.fd.begin() + (std::size_t)(i + 1) * d.n_d);
+      dj_junction_.forward.r = d.dj_sites;
+      dj_junction_.forward.c = d.dj_states;
+      dj_junction_.forward.v.assign(b.fdj.begin() + i * dj_n, b.fdj.begin() + (i + 1) * dj_n);
+    }
+    cache_forward_ = false;
+  }
+
+ protected:
+  void RunForwardAlgorithm() override {}
+};
+
+// outputs of the generator one row's sampling consumes: libstdc++'s discrete_distribution draws one
+// generate_canonical<double, 53> (two 32-bit outputs) unless it has fewer than two weights (then none)
+unsigned long long rng_outputs_per_row(const lh_family_desc_t& d) {
+  auto draws = [](int n_weights, int calls) { return n_weights >= 2 ? 2ull * calls : 0ull; };
+  unsigned long long n = draws(d.n_j, 1) + draws(d.vd_states, d.vd_sites) + draws(d.n_v, 1);
+  if (d.has_d) n += draws(d.dj_states, d.dj_sites) + draws(d.n_d, 1);
+  return n;
+}
 }  // namespace
 
 void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& output_path, int num_rates, int batch_size) {
@@ -691,6 +751,10 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
   // ---- sampler (this thread), in file order -------------------------------------------------------------------
   std::string failure;
   bool failure_is_input = false, first = true;
+  const unsigned long long per_row = rng_outputs_per_row(d);
+  const int sampler_threads = std::max(1, std::min(hw / 2, 16));
+  std::vector<std::unique_ptr<SamplerClone>> clones;
+  int last_clone = -1, last_batch = -1;   // where the last row's sampled state lives when a clone sampled it
   try {
     for (int bi = 0;; ++bi) {
       {
@@ -706,42 +770,91 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
       }
       const int B = (int)b.rows.size();
       const auto t_w0 = std::chrono::steady_clock::now();
-      for (int i = 0; i < B; ++i) {
-        const PipeRow& r = b.rows[i];
-        iteration_ = r.iteration;
-        rb_loglikelihood_ = r.rb;
-        prior_ = r.prior;
-        alpha_ = r.alpha;
-        er_.assign(r.er, r.er + 6);
-        pi_.assign(r.pi, r.pi + 4);
-        tree_ = r.tree;
-        tree_export_cache_ = r.exported;
-        sr_.assign(b.rates.begin() + (std::size_t)i * num_rates, b.rates.begin() + (std::size_t)(i + 1) * num_rates);
-        xmsa_emission_.assign(b.xe.begin() + (std::size_t)i * d.n_sites, b.xe.begin() + (std::size_t)(i + 1) * d.n_sites);
-        vgerm_.forward.assign(b.fv.begin() + (std::size_t)i * d.n_v, b.fv.begin() + (std::size_t)(i + 1) * d.n_v);
-        jgerm_.forward.assign(b.fj.begin() + (std::size_t)i * d.n_j, b.fj.begin() + (std::size_t)(i + 1) * d.n_j);
-        vd_junction_.forward.assign(d.vd_sites, d.vd_states, 0.0);
-        std::memcpy(vd_junction_.forward.data(), &b.fvd[i * vd_n], vd_n * sizeof(double));
-        vd_junction_.scaler_counts.assign(b.vds.begin() + (std::size_t)i * d.vd_sites, b.vds.begin() + (std::size_t)(i + 1) * d.vd_sites);
-        if (d.has_d) {
-          dgerm_.forward.assign(b.fd.begin() + (std::size_t)i * d.n_d, b.fd.begin() + (std::size_t)(i + 1) * d.n_d);
-          dj_junction_.forward.assign(d.dj_sites, d.dj_states, 0.0);
-          std::memcpy(dj_junction_.forward.data(), &b.fdj[i * dj_n], dj_n * sizeof(double));
-          dj_junction_.scaler_counts.assign(b.djs.begin() + (std::size_t)i * d.dj_sites, b.djs.begin() + (std::size_t)(i + 1) * d.dj_sites);
+      // ---- the rows of the batch on several threads (see SamplerClone); the lines are written in file order ----
+      bool sampled = false;
+      const int n_blocks = std::min(sampler_threads, B / 32);
+      if (n_blocks >= 2 && per_row > 0) {
+        while ((int)clones.size() < n_blocks) clones.emplace_back(new SamplerClone(*this));
+        std::vector<std::string> text(n_blocks);
+        std::vector<std::mt19937> start(n_blocks + 1, rng_), finish(n_blocks, rng_);
+        const int per_block = (B + n_blocks - 1) / n_blocks;
+        auto sample_block = [&](int t) {
+          const int lo = std::min(B, t * per_block), hi = std::min(B, lo + per_block);
+          start[t].discard(per_row * (unsigned long long)lo);
+          SamplerClone& c = *clones[t];
+          c.rng() = start[t];
+          std::ostringstream os;
+          for (int i = lo; i < hi; ++i) {
+            const PipeRow& r = b.rows[i];
+            c.Load(b, i, d);
+            const std::string naive = c.SampleNaiveSequence();
+            const std::string exported = r.exported.empty() ? ExportNewick(r.tree) : r.exported;
+            const LineFields f{r.iteration, r.rb, r.prior, r.alpha, r.er, r.pi, &b.rates[(std::size_t)i * num_rates], 6, 4, num_rates,
+                               &exported, b.ll[i], b.ll[i] - r.rb, &naive};
+            write_output_line(os, f, c);
+          }
+          finish[t] = c.rng();
+          text[t] = os.str();
+        };
+        std::vector<std::thread> team;
+        for (int t = 1; t < n_blocks; ++t) team.emplace_back(sample_block, t);
+        sample_block(0);
+        for (auto& th : team) th.join();
+        start[n_blocks].discard(per_row * (unsigned long long)B);
+        sampled = true;
+        for (int t = 0; t < n_blocks; ++t) sampled = sampled && finish[t] == start[t + 1];
+        if (sampled) {
+          if (first) {
+            er_.assign(b.rows[0].er, b.rows[0].er + 6);   // (the header names one column per rate and frequency)
+            pi_.assign(b.rows[0].pi, b.rows[0].pi + 4);
+            WriteOutputHeaders(outfile);
+            first = false;
+          }
+          for (const std::string& block : text) outfile << block;
+          rng_ = finish[n_blocks - 1];
+          last_clone = n_blocks - 1;
+          last_batch = bi % kRing;
         }
-        vgerm_.scaler_count = b.gs[3 * i];
-        dgerm_.scaler_count = b.gs[3 * i + 1];
-        jgerm_.scaler_count = b.gs[3 * i + 2];
-        loglik_cached_ = b.ll[i];
-        cache_forward_ = false;
-        lh_loglikelihood_ = b.ll[i];
-        logweight_ = lh_loglikelihood_ - rb_loglikelihood_;
-        naive_sequence_ = SampleNaiveSequence();
-        if (first) {
-          WriteOutputHeaders(outfile);
-          first = false;
+      }
+      if (!sampled) {
+        if (B) last_clone = -1;
+        for (int i = 0; i < B; ++i) {
+          const PipeRow& r = b.rows[i];
+          iteration_ = r.iteration;
+          rb_loglikelihood_ = r.rb;
+          prior_ = r.prior;
+          alpha_ = r.alpha;
+          er_.assign(r.er, r.er + 6);
+          pi_.assign(r.pi, r.pi + 4);
+          tree_ = r.tree;
+          tree_export_cache_ = r.exported;
+          sr_.assign(b.rates.begin() + (std::size_t)i * num_rates, b.rates.begin() + (std::size_t)(i + 1) * num_rates);
+          xmsa_emission_.assign(b.xe.begin() + (std::size_t)i * d.n_sites, b.xe.begin() + (std::size_t)(i + 1) * d.n_sites);
+          vgerm_.forward.assign(b.fv.begin() + (std::size_t)i * d.n_v, b.fv.begin() + (std::size_t)(i + 1) * d.n_v);
+          jgerm_.forward.assign(b.fj.begin() + (std::size_t)i * d.n_j, b.fj.begin() + (std::size_t)(i + 1) * d.n_j);
+          vd_junction_.forward.assign(d.vd_sites, d.vd_states, 0.0);
+          std::memcpy(vd_junction_.forward.data(), &b.fvd[i * vd_n], vd_n * sizeof(double));
+          vd_junction_.scaler_counts.assign(b.vds.begin() + (std::size_t)i * d.vd_sites, b.vds.begin() + (std::size_t)(i + 1) * d.vd_sites);
+          if (d.has_d) {
+            dgerm_.forward.assign(b.fd.begin() + (std::size_t)i * d.n_d, b.fd.begin() + (std::size_t)(i + 1) * d.n_d);
+            dj_junction_.forward.assign(d.dj_sites, d.dj_states, 0.0);
+            std::memcpy(dj_junction_.forward.data(), &b.fdj[i * dj_n], dj_n * sizeof(double));
+            dj_junction_.scaler_counts.assign(b.djs.begin() + (std::size_t)i * d.dj_sites, b.djs.begin() + (std::size_t)(i + 1) * d.dj_sites);
+          }
+          vgerm_.scaler_count = b.gs[3 * i];
+          dgerm_.scaler_count = b.gs[3 * i + 1];
+          jgerm_.scaler_count = b.gs[3 * i + 2];
+          loglik_cached_ = b.ll[i];
+          cache_forward_ = false;
+          lh_loglikelihood_ = b.ll[i];
+          logweight_ = lh_loglikelihood_ - rb_loglikelihood_;
+          naive_sequence_ = SampleNaiveSequence();
+          if (first) {
+            WriteOutputHeaders(outfile);
+            first = false;
+          }
+          WriteOutputLine(outfile);
         }
-        WriteOutputLine(outfile);
       }
       ms_sampler += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_w0).count();
       hand_over(b, 0);
@@ -764,6 +877,32 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
   cv.notify_all();
   reader.join();
   scorer.join();
+  if (last_clone >= 0) {
+    // the object ends as the reference's does, holding the last row: its forward tables and sampled annotation come
+    // from the clone that sampled it (with the generator where the walk ended), the rest from the batch
+    const PipeBatch& b = ring[last_batch];
+    const int i = (int)b.rows.size() - 1;
+    const PipeRow& r = b.rows[i];
+    static_cast<HMM&>(*this) = *clones[last_clone];
+    iteration_ = r.iteration;
+    rb_loglikelihood_ = r.rb;
+    prior_ = r.prior;
+    alpha_ = r.alpha;
+    er_.assign(r.er, r.er + 6);
+    pi_.assign(r.pi, r.pi + 4);
+    sr_.assign(b.rates.begin() + (std::size_t)i * num_rates, b.rates.begin() + (std::size_t)(i + 1) * num_rates);
+    xmsa_emission_.assign(b.xe.begin() + (std::size_t)i * d.n_sites, b.xe.begin() + (std::size_t)(i + 1) * d.n_sites);
+    vd_junction_.scaler_counts.assign(b.vds.begin() + (std::size_t)i * d.vd_sites, b.vds.begin() + (std::size_t)(i + 1) * d.vd_sites);
+    if (d.has_d)
+      dj_junction_.scaler_counts.assign(b.djs.begin() + (std::size_t)i * d.dj_sites, b.djs.begin() + (std::size_t)(i + 1) * d.dj_sites);
+    vgerm_.scaler_count = b.gs[3 * i];
+    dgerm_.scaler_count = b.gs[3 * i + 1];
+    jgerm_.scaler_count = b.gs[3 * i + 2];
+    loglik_cached_ = lh_loglikelihood_ = b.ll[i];
+    logweight_ = lh_loglikelihood_ - rb_loglikelihood_;
+    naive_sequence_ = naive_seq_samp_;
+    cache_forward_ = false;
+  }
   tree_.clear();
   tree_export_cache_.clear();
   outfile.close();

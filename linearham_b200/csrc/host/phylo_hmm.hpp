@@ -114,6 +114,16 @@ class HMM {
   const std::vector<std::string>& vd_junction_state_str_samps() const { return vd_junction_state_str_samps_; }
   const std::vector<std::string>& dj_junction_state_str_samps() const { return dj_junction_state_str_samps_; }
   const std::string& naive_seq_samp() const { return naive_seq_samp_; }
+  int vgerm_left_del_samp() const { return vgerm_left_del_samp_; }
+  int vgerm_right_del_samp() const { return vgerm_right_del_samp_; }
+  int dgerm_left_del_samp() const { return dgerm_left_del_samp_; }
+  int dgerm_right_del_samp() const { return dgerm_right_del_samp_; }
+  int jgerm_left_del_samp() const { return jgerm_left_del_samp_; }
+  int jgerm_right_del_samp() const { return jgerm_right_del_samp_; }
+  const std::string& vgerm_left_insertion_samp() const { return vgerm_left_insertion_samp_; }
+  const std::string& vd_junction_insertion_samp() const { return vd_junction_insertion_samp_; }
+  const std::string& dj_junction_insertion_samp() const { return dj_junction_insertion_samp_; }
+  const std::string& jgerm_right_insertion_samp() const { return jgerm_right_insertion_samp_; }
 
  protected:
   // partis YAML

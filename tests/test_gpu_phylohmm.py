@@ -184,3 +184,28 @@ def test_cli_reports_errors_like_the_reference(tiny):
     r = _cli("--compute-logl", *common, "--newick-path", bad, *sum((["--er", 1] for _ in range(6)), []),
              *sum((["--pi", 0.25] for _ in range(4)), []))
     assert r.returncode == 1 and r.stderr.startswith("ERROR: ") and r.stdout == ""
+
+
+def test_run_pipeline_parallel_sampler_equals_the_serial_walk(tiny):
+    """RunPipeline samples the rows of a batch on several threads, each starting from the one generator's state
+    advanced to its first row (std::mt19937::discard): the output must be what the serial, file-order walk of the
+    reference gives (src/HMM.cpp:325-329, 1252-1257) - compared here with the same code on one host thread, which
+    takes the serial path - and the object must end in the same state (next draws equal)."""
+    import numpy as np
+    from linearham_b200 import synth
+    z, ff, d = tiny
+    samples = synth.tree_samples(np.random.default_rng(77), ff["tree"], 300, outgroup="naive")
+    tin = os.path.join(d, "in300.trees")
+    synth.write_tsv(tin, samples)
+    outs, draws = [], []
+    for threads, batch in ((1, 128), (0, 128), (0, 1024)):
+        tout = os.path.join(d, f"out300_{threads}_{batch}.trees")
+        h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
+        h.set_host_threads(threads)
+        h.RunPipeline(tin, tout, int(z["num_rates"]), batch_size=batch)
+        draws.append([h.SampleNaiveSequence() for _ in range(3)])   # continues the generator where the run left it
+        h.close()
+        outs.append(open(tout).read())
+    assert outs[0].count("\n") == 301
+    assert outs[1] == outs[0] and outs[2] == outs[0]
+    assert draws[1] == draws[0] and draws[2] == draws[0]
