@@ -284,8 +284,13 @@ struct CtaLayout {           // dynamic shared memory of k_newick_cta
   }
 };
 
+// (at most 40 registers - 22 bytes of spills, 14.3 ms instead of 14.8 per 16 384 C4 trees. 128 x 40 = 5 K registers
+// is also what one k_prune CTA of 32 x 164 leaves free when it steps aside - option "parse_reserve" - so that the
+// parser of the next chunk can run beside the pruning of this one. Measured (r4i, C4): that buys nothing, 160 k
+// trees/s with 0 CTAs reserved, 157 k with 1, 150 k with 2 - the GPU is busy either way and the parser's SM time is
+// paid beside k_prune or between its launches - so the option stays 0.)
 template <int NT>
-__global__ void __launch_bounds__(NT) k_newick_cta(NewickDev p) {
+__global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
   extern __shared__ __align__(16) unsigned char nw_smem[];
   // s_flag[j] != 0: stage j (0 fold, 1 S3, 2 S5, 3 S6) leaves the tree to the host. One flag per stage: a stage reads
   // only flags written before the barrier in front of it, so every thread takes the same branch around the barriers.
