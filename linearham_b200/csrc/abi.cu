@@ -163,7 +163,10 @@ int upload_csc(const double* dense, int rows, int cols, lhb::CscDev* out, ConstA
 }  // namespace
 
 constexpr int kChunkEvents = 9;  // [7], [8]: k_plan of the chunk started / finished (plan stream)
-constexpr size_t kTextSlotBytes = (size_t)32 << 20;  // Newick text per staging segment
+constexpr size_t kTextSlotBytes = (size_t)32 << 20;  // a pinned ring slot for Newick text (the longest string it takes)
+// ... filled only this far unless one string is longer: the copy of a segment overlaps the staging of the next, and
+// with few host threads per GPU (8 ranks on one host) a chunk's text is otherwise staged, then copied, in turn
+constexpr size_t kTextSegBytes = (size_t)6 << 20;
 
 struct lh_family {
   int device = 0;
@@ -176,6 +179,10 @@ struct lh_family {
   // options
   int opt_sites_per_thread = 0, opt_smem_slots = -1, opt_smem_lo = -1, opt_timing = 1, opt_threads = 0;
   bool window_set = false;  // smem_lo of the batch has been chosen
+  struct WindowCache {      // ... and what lh_score_newick chose for this family last time
+    bool valid = false;
+    int opt_lo = -1, lo[2] = {0, 0}, smem_slots[2] = {0, 0}, total_slots[2] = {0, 0}, slots = 0;
+  } win_cache;
   size_t opt_chunk_bytes = 48u << 20;
   int opt_chunk_trees = 0, opt_pipe_waves = 4;
   // batch state
@@ -348,6 +355,7 @@ static int bind_family(lh_family* f, const lh_family_desc_t* d) {
   f->n_chunks = 0;
   f->window_set = false;
   f->labels_set = false;  // the labels belong to the family
+  f->win_cache.valid = false;
   for (auto& c : f->cols) c.codes_ns = 0;
   auto bail = [&](int) { return 1; };
   const int T = d->n_tips, S = d->n_sites;
@@ -1166,7 +1174,29 @@ int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n,
   }
   const auto t_a = std::chrono::steady_clock::now();
   if (!f->window_set) {
-    if (probe_window_from_text(f, nb, t0, std::min(n, 16))) return 1;
+    // The window is a placement choice (results do not depend on it) made from the shapes of the first trees.
+    // Parsing them on the host costs 0.16 ms per 1001-tip string, serially, in front of the call's first kernel:
+    // the choice is kept for the bound family while the stack geometry is the same, and the probe is short.
+    lh_family::WindowCache& wc = f->win_cache;
+    const bool hit = wc.valid && wc.opt_lo == f->opt_smem_lo && wc.smem_slots[0] == f->pc[0].smem_slots &&
+                     wc.smem_slots[1] == f->pc[1].smem_slots && wc.total_slots[0] == f->pc[0].total_slots &&
+                     wc.total_slots[1] == f->pc[1].total_slots;
+    if (hit) {
+      f->pc[0].smem_lo = wc.lo[0];
+      f->pc[1].smem_lo = wc.lo[1];
+      f->slots = std::max(f->slots, wc.slots);
+      f->tm.prune_smem_lo = f->pc[1].n_cols ? f->pc[1].smem_lo : f->pc[0].smem_lo;
+    } else {
+      if (probe_window_from_text(f, nb, t0, std::min(n, 8))) return 1;
+      wc.valid = true;
+      wc.opt_lo = f->opt_smem_lo;
+      for (int g = 0; g < 2; ++g) {
+        wc.lo[g] = f->pc[g].smem_lo;
+        wc.smem_slots[g] = f->pc[g].smem_slots;
+        wc.total_slots[g] = f->pc[g].total_slots;
+      }
+      wc.slots = f->slots;
+    }
     f->window_set = true;
   }
   uint8_t* base = f->h_ring[slot].as<uint8_t>();
@@ -1239,7 +1269,7 @@ int stage_text_chunk(lh_family* f, const lh_newick_batch_t* nb, int ci, int c0, 
     int n = 0;
     while (i + n < cn) {
       const size_t add = ((size_t)lens[i + n] + 1 + 15) / 16 * 16 + 12;
-      if (n && bytes + add + 16 > kTextSlotBytes) break;
+      if (n && bytes + add + 16 > kTextSegBytes) break;
       bytes += add;
       ++n;
     }
@@ -1298,11 +1328,41 @@ int stage_params(lh_family* f, const double* er, const double* pi, const double*
   double* misc = f->h_misc.as<double>();
   stream_copy(misc, er, sizeof(double) * 6 * B);
   stream_copy(misc + 6 * B, pi, sizeof(double) * 4 * B);
-  stream_copy(misc + 10 * B, rates, sizeof(double) * R * B);
-  LH_CUDA(cudaMemcpyAsync(f->d_er.p, misc, B * (10 + R) * 8, cudaMemcpyHostToDevice, s));
+  // (rates == nullptr: they are computed and copied chunk by chunk, stage_chunk_rates)
+  if (rates) stream_copy(misc + 10 * B, rates, sizeof(double) * R * B);
+  const size_t n = rates ? B * (10 + R) : B * 10;
+  LH_CUDA(cudaMemcpyAsync(f->d_er.p, misc, n * 8, cudaMemcpyHostToDevice, s));
   LH_CUDA(cudaEventRecord(f->misc_ev, s));
   f->misc_busy = true;
-  f->tm.h2d_bytes += (int64_t)(B * (10 + R) * 8);
+  f->tm.h2d_bytes += (int64_t)(n * 8);
+  return 0;
+}
+
+// Discrete-Gamma category rates of trees [c0, c0 + cn) from their alpha, on the handle's host threads (the same
+// doubles as pll_compute_gamma_cats, host/gamma.cpp; src/PhyloHMM.cpp:425-426), into `rates` and on to the device:
+// done chunk by chunk so that it overlaps the kernels of the chunks before instead of standing in front of the call.
+int stage_chunk_rates(lh_family* f, const double* alpha, double* rates, int c0, int cn, cudaStream_t s) {
+  const size_t B = (size_t)f->B, R = (size_t)f->R;
+  ensure_pool(f);
+  std::atomic<int> bad(-1);
+  std::vector<std::string> msgs((size_t)f->pool->workers() + 1);
+  f->pool->run((cn + 63) / 64, [&](int task, int w) {
+    const int lo = c0 + task * 64, n = std::min(c0 + cn, lo + 64) - lo;
+    if (lhh_gamma_cats_batch(n, alpha + lo, (int)R, rates + (size_t)lo * R)) {
+      bad.store(lo);
+      msgs[w] = lhh_last_error();
+    }
+  });
+  if (bad.load() >= 0) {
+    for (auto& m : msgs)
+      if (!m.empty()) return fail("%s (trees %d..)", m.c_str(), bad.load());
+    return fail("Gamma category rates failed");
+  }
+  double* misc = f->h_misc.as<double>() + 10 * B + (size_t)c0 * R;   // (the call's stage_params waited for the buffer)
+  stream_copy(misc, rates + (size_t)c0 * R, sizeof(double) * R * cn);
+  LH_CUDA(cudaMemcpyAsync(f->d_er.as<double>() + 10 * B + (size_t)c0 * R, misc, sizeof(double) * R * cn, cudaMemcpyHostToDevice, s));
+  LH_CUDA(cudaEventRecord(f->misc_ev, s));
+  f->tm.h2d_bytes += (int64_t)(sizeof(double) * R * cn);
   return 0;
 }
 
@@ -1639,7 +1699,7 @@ namespace {
 // The pipelined call behind lh_score_batch (tb: operation arrays) and lh_score_newick (nb: text; `rates`
 // are the category rates of its trees). Host buffers in, host results out.
 int score_call(lh_family* f, const lh_tree_batch_t* tb, const lh_newick_batch_t* nb, const double* rates,
-               double* loglik, lh_outputs_t* o) {
+               double* loglik, lh_outputs_t* o, double* lazy_rates = nullptr) {  // lazy_rates: [B][R] to fill from nb->alpha
   f->want_tables = o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
                          o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers);
   f->want_rate_ll = o && o->site_rate_loglik;
@@ -1707,6 +1767,7 @@ int score_call(lh_family* f, const lh_tree_batch_t* tb, const lh_newick_batch_t*
   for (int ci = 0, k = 0; ci < f->n_chunks; ++ci) {
     const int c0 = st[ci], cn = st[ci + 1] - st[ci];
     if (nb) {
+      if (lazy_rates && stage_chunk_rates(f, nb->alpha, lazy_rates, c0, cn, cs)) return 1;
       if (stage_text_chunk(f, nb, ci, c0, cn, &k, cs)) return 1;
     } else {
       for (int t0 = c0; t0 < st[ci + 1]; t0 += f->seg, ++k)
@@ -1789,25 +1850,10 @@ int lh_score_newick(lh_family_t* f, const lh_newick_batch_t* nb, double* loglik,
   const double* rates = nb->rates;
   if (!rates && B > 0) {
     if (R < 1 || R > LH_MAX_RATES) return fail("n_rates %d outside 1..%d", R, LH_MAX_RATES);
-    rates_buf.resize((size_t)B * R);
-    ensure_pool(f);
-    std::atomic<int> bad(-1);
-    std::vector<std::string> msgs((size_t)f->pool->workers() + 1);
-    f->pool->run((B + 63) / 64, [&](int task, int w) {
-      const int lo = task * 64, n = std::min(B, lo + 64) - lo;
-      if (lhh_gamma_cats_batch(n, nb->alpha + lo, R, rates_buf.data() + (size_t)lo * R)) {
-        bad.store(lo);
-        msgs[w] = lhh_last_error();
-      }
-    });
-    if (bad.load() >= 0) {
-      for (auto& m : msgs)
-        if (!m.empty()) return fail("%s (trees %d..)", m.c_str(), bad.load());
-      return fail("Gamma category rates failed");
-    }
-    rates = rates_buf.data();
+    rates_buf.resize((size_t)B * R);   // filled chunk by chunk inside the pipeline (stage_chunk_rates)
   }
-  int rc = score_call(f, nullptr, nb, rates, loglik, o);
+  int rc = score_call(f, nullptr, nb, rates, loglik, o, rates ? nullptr : rates_buf.data());
+  if (!rates) rates = rates_buf.data();
   f->newick_mode = false;
   if (B == 0) return rc;
   const lh_timings_t tm_main = f->tm;
