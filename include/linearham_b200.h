@@ -246,7 +246,8 @@ int lh_set_option(lh_family_t* fam, const char* key, int64_t value);
  * lists as the caller holds them; 0: by the host planner threads; -1 = default: by the device when
  * the handle's host threads would not keep ahead of the kernels - the programs are the same),
  * "newick_kernel" (lh_score_newick: 0 / 2 = default, the one-CTA-per-tree parser, with the one-thread-per-tree
- * parser behind it for trees nested deeper than its tables; 1 = the one-thread-per-tree parser alone),
+ * parser behind it for trees nested deeper than its tables; 3 = the one-warp-per-tree parser (ballot lexing) in its
+ * place; 1 = the one-thread-per-tree parser alone - the three write the same bits),
  * "parse_reserve" (default 0: pruning CTAs per SM given up during lh_score_newick so that the parser of the
  * next chunk runs beside the pruning of this one),
  * "chunk_bytes" (branch-record bytes per k_pmatrix/k_prune launch pair; the chunk is never

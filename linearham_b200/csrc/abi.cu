@@ -241,7 +241,7 @@ struct lh_family {
   int chunk = 0, chunk_pipe = 0, wave_pipe = 0, wave_unit = 0, seg = 0, occ[2] = {0, 0};
   int opt_open_unit = 1, opt_chunk_growth = 1;
   int opt_parse_reserve = 0;  // pruning CTAs per SM given up for the parser while text is coming in (measured: no gain, the parser of a chunk runs between the pruning launches either way)
-  int opt_newick_kernel = 0;  // 0 auto, 1 k_newick (one thread per tree), 2 k_newick_cta (one CTA per tree)
+  int opt_newick_kernel = 0;  // 0 / 2 k_newick_cta (one CTA per tree), 1 k_newick (one thread per tree), 3 k_newick_warp (one warp per tree)
   double stage_ratio = 1.0;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
   // trees that can run on site patterns (naive tip on the root edge or under the virtual root)
@@ -631,7 +631,7 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
     if (value < 0 || value > 3) return fail("parse_reserve must be 0..3");
     f->opt_parse_reserve = (int)value;
   } else if (k == "newick_kernel") {
-    if (value < 0 || value > 2) return fail("newick_kernel must be 0 (auto), 1 (one thread per tree) or 2 (one CTA per tree)");
+    if (value < 0 || value > 3) return fail("newick_kernel must be 0 (default) / 2 (one CTA per tree), 1 (one thread per tree) or 3 (one warp per tree)");
     f->opt_newick_kernel = (int)value;
   } else if (k == "device_plan") {
     if (value < -1 || value > 1) return fail("device_plan must be -1 (auto), 0 or 1");

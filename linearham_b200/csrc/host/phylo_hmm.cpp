@@ -350,6 +350,7 @@ void PhyloHMM::InitializePhyloParameters(const std::string& newick_path, const s
                                          const std::vector<double>& pi, double alpha, int num_rates) {
   if (er.size() != 6 || pi.size() != 4) throw std::invalid_argument("er must have 6 and pi 4 entries");
   tree_ = read_file(newick_path);
+  forward_ready_ = false;
   er_ = er;
   pi_ = pi;
   alpha_ = alpha;
@@ -398,14 +399,21 @@ void PhyloHMM::ScoreCurrentSample() {
   jgerm_.scaler_count = gs[2];
   loglik_cached_ = ll;
   cache_forward_ = false;
+  forward_ready_ = true;
 }
 
+// src/PhyloHMM.cpp:366-383. The device call fills the emissions and runs the forward pass in one go; the flag a
+// caller can observe still says, as in the reference, that the forward pass is due (cache_forward() == true until
+// the first LogLikelihood / SampleNaiveSequence, test/test.cpp:966), and RunForwardAlgorithm then finds it done.
 void PhyloHMM::InitializePhyloEmission() {
   if (tree_.empty()) throw std::runtime_error("InitializePhyloEmission() called before a tree was set");
   ScoreCurrentSample();
+  cache_forward_ = true;
 }
 
-void PhyloHMM::RunForwardAlgorithm() { ScoreCurrentSample(); }
+void PhyloHMM::RunForwardAlgorithm() {
+  if (!forward_ready_) ScoreCurrentSample();
+}
 
 // src/HMM.cpp:345-354
 double PhyloHMM::LogLikelihood() {

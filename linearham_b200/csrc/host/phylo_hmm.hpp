@@ -246,6 +246,7 @@ class PhyloHMM : public HMM {
   std::vector<double> er_, pi_, sr_;
   std::string tree_, naive_sequence_;
   double loglik_cached_ = 0;
+  bool forward_ready_ = false;        // the forward tables of the current sample are in place (ScoreCurrentSample ran)
 
   std::unique_ptr<FlatFamily> flat_;
   std::string tree_export_cache_;     // RunPipeline: ExportNewick(tree_) made ahead by the reader stage (else empty)

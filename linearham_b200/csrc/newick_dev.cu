@@ -245,6 +245,22 @@ __device__ __forceinline__ bool may_follow(int prev, int cur) {
   else if (cur == K_SEMI) ok = (1u << K_CLOSE) | (1u << K_INNER) | (1u << K_NUM);
   return (ok >> prev) & 1u;
 }
+// the same two tables packed into constants (k_newick_warp looks them up for every character)
+__device__ __forceinline__ int word_type_packed(int last) {
+  constexpr unsigned long long tbl = (unsigned long long)K_BAD * 0x1111111111ull                       // ten entries of four bits
+      ^ ((unsigned long long)(K_BAD ^ K_TIP) << (4 * K_OPEN)) ^ ((unsigned long long)(K_BAD ^ K_TIP) << (4 * K_COMMA))
+      ^ ((unsigned long long)(K_BAD ^ K_NUM) << (4 * K_COLON)) ^ ((unsigned long long)(K_BAD ^ K_INNER) << (4 * K_CLOSE));
+  return (int)((tbl >> (4 * last)) & 15ull);
+}
+__device__ __forceinline__ bool may_follow_packed(int prev, int cur) {   // cur: K_OPEN..K_SEMI
+  constexpr unsigned long long after_node = (1u << K_TIP) | (1u << K_NUM) | (1u << K_CLOSE) | (1u << K_INNER);
+  constexpr unsigned long long tbl =
+      ((unsigned long long)((1u << K_NONE) | (1u << K_OPEN) | (1u << K_COMMA)) << (10 * (K_OPEN - 1))) |
+      (after_node << (10 * (K_CLOSE - 1))) | (after_node << (10 * (K_COMMA - 1))) |
+      ((unsigned long long)((1u << K_TIP) | (1u << K_INNER) | (1u << K_CLOSE)) << (10 * (K_COLON - 1))) |
+      ((unsigned long long)((1u << K_CLOSE) | (1u << K_INNER) | (1u << K_NUM)) << (10 * (K_SEMI - 1)));
+  return (tbl >> (10 * (cur - 1) + prev)) & 1ull;
+}
 __device__ __forceinline__ int structural(int c) {
   return c == '(' ? K_OPEN : c == ')' ? K_CLOSE : c == ',' ? K_COMMA : c == ':' ? K_COLON : c == ';' ? K_SEMI : K_NONE;
 }
@@ -427,7 +443,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
       in_word = sm.in_word_out;
     }
     // a tree of this family ends with ';' at depth 0 and has T tips and T-2 ')'
-    if (last != K_SEMI || depth != 0 || n_close != n_ops || n_items != n_items) s_flag[0] = 1;
+    if (last != K_SEMI || depth != 0 || n_close != n_ops || n_items != 2 * T - 2) s_flag[0] = 1;
   }
   __syncthreads();
 
@@ -603,6 +619,226 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
     }
   }
 }
+// ------------------------------------------------------------------ k_newick_warp ---
+// One warp per tree, the lexing data-parallel over the characters instead of over slices: the warp reads 32
+// consecutive characters per step (one 32-byte sector, coalesced) and every lane classifies its own; what a
+// sequential lexer carries from character to character becomes warp-wide bit arithmetic on ballot masks -
+//   comments   the bracket masks are walked once per window (a loop over their set bits, the same in every lane):
+//              '[' outside a comment opens one, the next ']' closes it, ']' outside one is a word character;
+//   words      W = word characters outside comments; a word starts where W has a bit and its left neighbour has not;
+//   tokens     T = structural characters | word starts; the kind of a word follows from the token before it (its
+//              lane is the highest bit of T below mine, read with one shuffle), the grammar check from that token's
+//              kind (a second shuffle);
+//   counters   depth, node index and ')' index of a lane = the carried value + popcounts of the masks below it.
+// Every lane is busy on every step and no lane diverges, so a 73 KB string costs ~2300 steps of ~70 instructions
+// instead of two divergent byte loops per thread, and there is nothing to summarise and fold: the state at the end
+// of a window (in a comment?, in a word?, last token, depth, counts) is carried in registers to the next. S5 (label
+// -> row, branch length -> double, one lane per node) and S6 (children to parents) are k_newick_cta's.
+__global__ void __launch_bounds__(32, 24) k_newick_warp(NewickDev p) {
+  __shared__ int2 PID[kCtaLevels + 1];
+  __shared__ double2 PL[kCtaLevels + 1];
+  __shared__ uint8_t CNT[kCtaLevels + 1];
+  __shared__ uint8_t s_cls[256];
+  constexpr unsigned FULL = 0xffffffffu;
+  const int i = blockIdx.x, lane = threadIdx.x;
+  const int t = p.tree0 + i, T = p.T, n_ops = T - 2;
+  const int n_items = 2 * T - 2;   // T tips + T-2 ')'
+  unsigned char* items = p.items + (size_t)i * cta_items_stride(T);
+  double* LEN = reinterpret_cast<double*>(items);
+  int32_t* ID = reinterpret_cast<int32_t*>(items + (size_t)n_items * 8);
+  uint16_t* LVL = reinterpret_cast<uint16_t*>(items + (size_t)n_items * 12);
+  int2* __restrict__ ch = reinterpret_cast<int2*>(p.children) + (size_t)t * n_ops;
+  double2* __restrict__ bl = reinterpret_cast<double2*>(p.blen) + (size_t)t * n_ops;
+  const char* text = p.text + __ldg(p.offs + i);
+  const uint32_t L = __ldg(p.lens + i);
+  for (int c = lane; c < 256; c += 32)
+    s_cls[c] = (uint8_t)(c == '[' ? 6 : c == ']' ? 7 : (c == 0 || is_blank(c)) ? 8 : structural(c));
+  for (int l = lane; l <= kCtaLevels; l += 32) CNT[l] = 0;
+  __syncwarp();
+
+  // ---- lexing: token grammar, one item per node (what S0-S3 of k_newick_cta do in four passes) ----
+  bool bad = false, deep = false;
+  {
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned com = 0;              // the window starts inside a comment
+    unsigned in_word = 0;          // the character before the window is a word character
+    int last = K_NONE, depth = 0, ni = 0, nc = 0;
+    const unsigned char* tx = reinterpret_cast<const unsigned char*>(text);
+    int c_next = lane < L ? (int)__ldg(tx + lane) : ' ';
+    for (uint32_t base = 0; base < L; base += 32) {
+      const uint32_t q = base + lane;
+      const int cls = s_cls[c_next];
+      c_next = q + 32 < L ? (int)__ldg(tx + q + 32) : ' ';   // (the next window's load is in flight during this one)
+      // the four bits of every lane's class: all class masks follow from them, the same in every lane
+      const unsigned b0 = __ballot_sync(FULL, cls & 1), b1 = __ballot_sync(FULL, cls & 2);
+      const unsigned b2 = __ballot_sync(FULL, cls & 4), b3 = __ballot_sync(FULL, cls & 8);
+      const unsigned m_ob = b1 & b2 & ~b0, m_cb = b0 & b1 & b2;          // '[' (6), ']' (7)
+      // Comments. After a '[' the text is inside a comment whatever it was before, after a ']' outside one: a
+      // character is inside iff the nearest bracket to its left is '['. Adding a one above every '[' to the mask of
+      // non-brackets lets the carry run up to the next bracket; the bits the addition changes are that stretch.
+      const unsigned nb = ~(m_ob | m_cb);
+      const unsigned com_mask = ((nb + ((m_ob << 1) | com)) ^ nb) | m_ob;
+      if (~nb) com = (m_ob >> (31 - __clz(~nb))) & 1u;
+      const unsigned U = (b0 | b1 | b2) & ~(b1 & b2) & ~com_mask;         // structural characters (1..5)
+      const unsigned W = (~(b0 | b1 | b2 | b3) | m_cb) & ~com_mask;       // word characters (0; ']' outside a comment)
+      const unsigned MO = b0 & ~b1 & ~b2 & ~com_mask, MC = b1 & ~b0 & ~b2 & ~com_mask;   // '(' (1), ')' (2)
+      const unsigned WS = W & ~((W << 1) | in_word);
+      const unsigned TK = U | WS;
+      const int st = ((U >> lane) & 1u) ? cls : K_NONE;
+      const unsigned below = TK & lt;
+      const int pidx = below ? 31 - __clz(below) : 0;
+      const int st_prev = __shfl_sync(FULL, st, pidx);
+      const bool word_start = (WS >> lane) & 1u;
+      int tok = st;
+      if (word_start) tok = below ? word_type_packed(st_prev) : word_type_packed(last);   // (after a word: K_BAD)
+      const int tok_prev = __shfl_sync(FULL, tok, pidx);
+      const int prev = below ? tok_prev : last;
+      const bool is_tip = word_start && tok == K_TIP;
+      const unsigned IT = __ballot_sync(FULL, is_tip) | MC;
+      const int d = depth + __popc(MO & lt) - __popc(MC & lt);   // the depth in front of my character
+      const int my = ni + __popc(IT & lt);
+      if (st != K_NONE) {
+        if (!may_follow_packed(prev, st)) bad = true;   // (nothing may follow ';')
+        if (st == K_OPEN) {
+          if (d + 1 > kCtaLevels) { bad = true; deep = true; }
+        } else if (st == K_SEMI) {
+          if (d != 0) bad = true;
+        } else if (st != K_COLON && d <= 0) {           // ')' and ','
+          bad = true;
+        }
+      } else if (word_start && tok == K_BAD) {
+        bad = true;
+      }
+      if ((IT >> lane) & 1u) {
+        if (d <= 0 || my >= n_items) {
+          bad = true;
+        } else {
+          LVL[my] = (uint16_t)(is_tip ? d : (d | 0x8000));
+          if (!is_tip) ID[my] = nc + __popc(MC & lt);
+          reinterpret_cast<uint32_t*>(LEN + my)[0] = is_tip ? q : q + 1;
+        }
+      }
+      depth += __popc(MO) - __popc(MC);
+      ni += __popc(IT);
+      nc += __popc(MC);
+      in_word = W >> 31;
+      if (TK) last = __shfl_sync(FULL, tok, 31 - __clz(TK));
+    }
+    // a tree of this family ends with ';' at depth 0 and has T tips and T-2 ')'
+    if (last != K_SEMI || depth != 0 || nc != n_ops || ni != n_items) bad = true;
+    bad = __any_sync(FULL, bad);
+    deep = __any_sync(FULL, deep);
+  }
+  __syncwarp();
+
+  if (!bad) {
+    // ---- S5: one lane per node: label -> row, branch length -> double ----
+    for (int it = lane; it < n_items; it += 32) {
+      const uint32_t pos = __ldcg(reinterpret_cast<const uint32_t*>(LEN + it));
+      Reader r(text, pos);
+      if ((__ldcg(LVL + it) & 0x8000u) == 0) {
+        uint32_t h = 2166136261u;
+        uint64_t first8 = 0;
+        int len = 0;
+        for (int cc = r.peek(); !is_delim(cc); cc = r.peek()) {
+          h = (h ^ (uint32_t)cc) * 16777619u;
+          if (len < 8) first8 |= (uint64_t)cc << (8 * len);
+          ++len;
+          r.adv();
+        }
+        const int row = find_label(p.labels, text, pos, len, h, first8);
+        if (row < 0) bad = true;
+        ID[it] = row;
+      } else {
+        skip(r);
+        while (!is_delim(r.peek())) r.adv();  // inner label, ignored
+      }
+      double v = 0.0;
+      if (!branch_length(r, &v)) bad = true;
+      LEN[it] = v;
+    }
+    bad = __any_sync(FULL, bad);
+    __syncwarp();
+  }
+
+  if (!bad) {
+    // ---- S6: children to parents, in text order ----
+    if (lane == 0) {
+      int root_child = 0, top0 = 0, top1 = 0, c1 = 0;
+      double root_blen = 0.0, topl0 = 0.0, topl1 = 0.0;
+      bool done = false;
+      for (int base = 0; base < n_items && !bad && !done; base += 4) {
+        unsigned lv4[4];
+        int id4[4];
+        double len4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int it = min(base + j, n_items - 1);
+          lv4[j] = __ldcg(LVL + it);
+          id4[j] = __ldcg(ID + it);
+          len4[j] = __ldcg(LEN + it);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int it = base + j;
+          if (it >= n_items || bad || done) break;
+          int lvl = (int)(lv4[j] & 0x7fffu), id = id4[j];
+          const double len = len4[j];
+          if (lv4[j] & 0x8000u) {
+            if (lvl == 1) {  // the trifurcation, last
+              if (c1 != 3 || id != n_ops - 1 || it != n_items - 1) bad = true;
+              done = true;
+              break;
+            }
+            if (CNT[lvl] != 2) { bad = true; break; }
+            ch[id] = PID[lvl];
+            bl[id] = PL[lvl];
+            CNT[lvl] = 0;
+            id += T;
+            --lvl;
+          }
+          if (lvl == 1) {
+            if (c1 == 0) { root_child = id; root_blen = len; }
+            else if (c1 == 1) { top0 = id; topl0 = len; }
+            else if (c1 == 2) { top1 = id; topl1 = len; }
+            else bad = true;
+            ++c1;
+          } else {
+            const int k = CNT[lvl];
+            if (k == 0) { PID[lvl].x = id; PL[lvl].x = len; }
+            else if (k == 1) { PID[lvl].y = id; PL[lvl].y = len; }
+            else bad = true;
+            CNT[lvl] = (uint8_t)(k + 1);
+          }
+        }
+      }
+      if (!done) bad = true;
+      if (!bad) {
+        ch[n_ops - 1] = make_int2(top0, top1);
+        bl[n_ops - 1] = make_double2(topl0, topl1);
+        p.root_child[t] = root_child;
+        p.root_blen[t] = root_blen;
+        p.on_pat[t] = (root_child == 0 || top0 == 0 || top1 == 0) ? 1 : 0;
+        p.status[t] = 0;
+      }
+    }
+    bad = __shfl_sync(FULL, bad, 0);
+  }
+  if (bad) {
+    // stand-in (see k_newick): the host parser decides what the tree really is
+    for (int op = lane; op < n_ops; op += 32) {
+      ch[op] = op == 0 ? make_int2(1, 2) : make_int2(T + op - 1, op + 2);
+      bl[op] = make_double2(kEpsLen, kEpsLen);
+    }
+    if (lane == 0) {
+      p.root_child[t] = 0;
+      p.root_blen[t] = kEpsLen;
+      p.on_pat[t] = 1;
+      p.status[t] = deep ? 2 : 1;   // 2: deeper than this kernel's tables - k_newick takes the tree
+    }
+  }
+}
+
 __global__ void __launch_bounds__(32) k_split(const uint8_t* __restrict__ on_pat, int t0, int n, int32_t* __restrict__ list,
                                               int32_t* __restrict__ n_pat_out) {
   const int lane = threadIdx.x;
@@ -627,7 +863,9 @@ size_t newick_items_bytes(int n_tips, int n_trees) { return cta_items_stride(n_t
 void launch_newick(const NewickDev& p, cudaStream_t s) {
   if (p.n <= 0) return;
   const bool cta = p.kernel != 1 && p.T < 32768 && p.items != nullptr;
-  if (cta) {
+  if (cta && p.kernel == 3) {
+    k_newick_warp<<<p.n, 32, 0, s>>>(p);
+  } else if (cta) {
     const size_t smem = CtaLayout(kCtaThreads).total;
     k_newick_cta<kCtaThreads><<<p.n, kCtaThreads, smem, s>>>(p);
   }

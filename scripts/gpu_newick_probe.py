@@ -12,7 +12,7 @@ tb, newicks, alpha = workload.tree_batch(cfg, ff, B, n_topo=256)
 text = host.NewickBuffer(tb, labels)
 f = device.Family(fam)
 f.set_labels(labels)
-for kernel in (2, 1):
+for kernel in (3, 2, 1):
     f.set_option("newick_kernel", kernel)
     for rep in range(3):
         t0 = time.perf_counter()

@@ -2,6 +2,8 @@
 (host/newick.cpp - itself pinned to the compiled reference's flattened trees, test_host_ingest.py): the
 operation arrays must be bit-identical, trees the device leaves to the host must come out the same, and a
 malformed tree must fail the call with the host parser's message."""
+import re
+
 import numpy as np
 import pytest
 
@@ -12,7 +14,8 @@ pytestmark = pytest.mark.gpu
 OPS = ("children", "blen", "root_child", "root_blen")
 
 
-KERNELS = [1, 2]   # k_newick (one thread per tree), k_newick_cta (one CTA per tree; the default where it fits)
+KERNELS = [1, 2, 3]   # k_newick (one thread per tree), k_newick_cta (one CTA per tree; the default where it fits),
+                      # k_newick_warp (one warp per tree)
 
 
 def _family(fam, labels, kernel=0):
@@ -91,6 +94,8 @@ def _decorate(rng, nwk):
                 s = ":" + repr(v)
             if rng.random() < 0.2:
                 s = f"[&index={int(rng.integers(0, 999))}]" + s
+            elif rng.random() < 0.04:   # a long comment holding everything a lexer could trip over, '[' included
+                s = "[&note=((a:1,b:2)x:3,[c);" + " pad" * int(rng.integers(0, 30)) + "]" + s
             if rng.random() < 0.05 and s:
                 s = s[0] + " " + s[1:]
             out.append(s)
@@ -180,7 +185,7 @@ def test_lenient_spellings_are_left_to_the_host_by_the_cta_parser():
     odd[2] = "  \t" + nw[2].replace(",", " ,\n", 3)          # blanks are fine everywhere
     ref = host.newick_to_ops(odd, labels)
     R = tb["rates"].shape[1]
-    for kernel, left in ((1, []), (2, [0, 1])):
+    for kernel, left in ((1, []), (2, [0, 1]), (3, [0, 1])):
         f = _family(fam, labels, kernel)
         got = f.parse_newick(odd)
         assert np.flatnonzero(got["left_to_host"]).tolist() == left
@@ -240,6 +245,9 @@ def test_malformed_trees_fail_with_the_host_parsers_message(kernel):
         "nosemi": nw[2].rstrip(";"),
         "badlen": nw[2].replace(":", ":x", 1),
         "unbalanced": nw[2].replace("(", "", 1),
+        # the right number of ')' but a tip short (a unary node): the item list is one short of what S5 / S6 expect
+        "unary": re.sub(r",[^,():;\[\]\s]+(\[[^\]]*\])?(:[0-9.eE+-]+)?\)", ")", nw[2], count=1),
+        "two_words": nw[2].replace("naive[", "na[x]ive[", 1),
         "empty": "",
         "negative": None,
     }
