@@ -197,6 +197,33 @@ int lh_batch_fetch(lh_family_t* fam, double* loglik, lh_outputs_t* opt); /* sync
 int lh_sync(lh_family_t* fam);
 int lh_loglik_dev(lh_family_t* fam, const double** loglik_dev, int32_t* n); /* device ptr of the last run */
 
+/* Ancestral-state sampling: the second half of the reference's R step
+ * (scripts/run_bootstrap_asr_ess.R:81-89 - per kept tree and alignment site, the rate category drawn in proportion
+ * to phylomd::phylo.likelihood on the rate-scaled tree, then phylomd::asr.sim on that tree:
+ * lib/phylomd/src/simulation_functions.cpp:57-117). The alignment is the family's MSA - not the xMSA - with the
+ * "naive" row replaced by the sample's NaiveSequence (R:66-67): msa_codes holds the rows in the family's tip order
+ * (codes A,C,G,T = 0..3, 4 = N / gap), row naive_row of it is ignored and read from naive_codes per tree
+ * (naive_row = -1: no row is replaced). Trees and substitution parameters as for lh_score_batch.
+ * Outputs: node_states [B][T-2][n_sites], the sampled base (0..3; 4 where the site has no positive likelihood) of
+ * inner node T + op for every operation op of the tree (the last one is the trifurcation next to root_child, which is
+ * the script's root when the tree is rooted at the naive outgroup); site_rate [B][n_sites], the sampled category
+ * (n_rates where none has a positive likelihood); site_rate_loglik [B][R][n_sites] or NULL,
+ * log( L_k(site) / pi[naive base] ) as R:85 forms it (pi = 1 for an N).
+ * Draws come from Philox4x32-10 keyed by `seed` with counter (tree, site, draw): the result depends on nothing but
+ * the arguments. The reference draws with R's generator on a worker cluster, which nothing outside R reproduces;
+ * parity with it is distributional, parity with oracle/asr_oracle.py exact (tests/test_gpu_asr.py). Synchronous;
+ * allocates its own buffers per call (option "asr_scratch_mb": CLV scratch per chunk of trees, default 4096).   */
+typedef struct lh_asr_batch {
+  const lh_tree_batch_t* trees;
+  int32_t n_sites;
+  int32_t naive_row;
+  const uint8_t* msa_codes;    /* [T][n_sites]                                           */
+  const uint8_t* naive_codes;  /* [B][n_sites]                                           */
+  uint64_t seed;
+} lh_asr_batch_t;
+int lh_asr_sample(lh_family_t* fam, const lh_asr_batch_t* batch, uint8_t* node_states, uint8_t* site_rate,
+                  double* site_rate_loglik);
+
 int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/score */
 /* Test hook: the traversal programs of the current batch as the device holds them
  * (steps [B][T-1][4] int32, pblen [B][2T-3]); compared with the host planner in the tests. */

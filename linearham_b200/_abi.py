@@ -47,6 +47,11 @@ class TreeBatch(C.Structure):
     ]
 
 
+class AsrBatch(C.Structure):
+    _fields_ = [("trees", C.POINTER(TreeBatch)), ("n_sites", C.c_int32), ("naive_row", C.c_int32),
+                ("msa_codes", C.POINTER(C.c_uint8)), ("naive_codes", C.POINTER(C.c_uint8)), ("seed", C.c_uint64)]
+
+
 class NewickBatch(C.Structure):
     _fields_ = [
         ("n_trees", C.c_int32), ("n_rates", C.c_int32),
@@ -191,7 +196,7 @@ DEVICE_SYMBOLS = [
     "lh_loglik_dev", "lh_get_timings", "lh_set_option", "lh_measure_fp64_peak",
     "lh_timer_mark", "lh_timer_elapsed_ms", "lh_family_rebind", "lh_debug_fetch_plan",
     "lh_family_set_labels", "lh_score_newick", "lh_debug_parse_newick", "lh_newick_parse_noalloc",
-    "lh_newick_parse_noalloc_max_trees",
+    "lh_newick_parse_noalloc_max_trees", "lh_asr_sample",
     "lh_group_create", "lh_group_destroy", "lh_group_size", "lh_group_member", "lh_group_set_labels", "lh_group_set_option",
     "lh_group_score_batch", "lh_group_score_newick", "lh_group_get_timings", "lh_group_last_error", "lh_parse_devices",
     "lh_repertoire_create_multi", "lh_repertoire_create", "lh_repertoire_score", "lh_repertoire_destroy", "lh_repertoire_set_option", "lh_repertoire_last_error",
@@ -238,6 +243,7 @@ def load_library(path=None):
     lib.lh_debug_fetch_plan.argtypes = [C.c_void_p, _i32p, _f64p]
     lib.lh_family_rebind.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
     lib.lh_family_set_labels.argtypes = [C.c_void_p, C.POINTER(C.c_char_p)]
+    lib.lh_asr_sample.argtypes = [C.c_void_p, C.POINTER(AsrBatch), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8), _f64p]
     lib.lh_newick_parse_noalloc.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 10
     lib.lh_newick_parse_noalloc_max_trees.argtypes = [C.c_int32]
     lib.lh_newick_parse_noalloc_max_trees.restype = C.c_int32

@@ -241,6 +241,7 @@ struct lh_family {
   int chunk = 0, chunk_pipe = 0, wave_pipe = 0, wave_unit = 0, seg = 0, occ[2] = {0, 0};
   int opt_open_unit = 1, opt_chunk_growth = 1;
   int opt_parse_reserve = 0;  // pruning CTAs per SM given up for the parser while text is coming in (measured: no gain, the parser of a chunk runs between the pruning launches either way)
+  int opt_asr_scratch_mb = 0; // lh_asr_sample: CLV scratch per chunk of trees (0 = 4096 MB)
   int opt_newick_kernel = 0;  // 0 / 2 k_newick_cta (one CTA per tree), 1 k_newick (one thread per tree), 3 k_newick_warp (one warp per tree)
   double stage_ratio = 1.0;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
@@ -630,6 +631,9 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
   } else if (k == "parse_reserve") {
     if (value < 0 || value > 3) return fail("parse_reserve must be 0..3");
     f->opt_parse_reserve = (int)value;
+  } else if (k == "asr_scratch_mb") {
+    if (value < 0) return fail("asr_scratch_mb must be >= 0 (0 = default, 4096)");
+    f->opt_asr_scratch_mb = (int)value;
   } else if (k == "newick_kernel") {
     if (value < 0 || value > 3) return fail("newick_kernel must be 0 (default) / 2 (one CTA per tree), 1 (one thread per tree) or 3 (one warp per tree)");
     f->opt_newick_kernel = (int)value;
@@ -2084,6 +2088,46 @@ int lh_newick_parse_noalloc(lh_family_t* f, int32_t n_trees, const char* text_de
 }
 
 int32_t lh_newick_parse_noalloc_max_trees(int32_t n_tips) { return lhb::newick_noalloc_max_trees(n_tips); }
+
+// Ancestral-state sampling (asr.cu): the family handle names the device and the tip count; the alignment is the
+// caller's (the MSA with the naive row replaced per sample, not the xMSA).
+int lh_asr_sample(lh_family_t* f, const lh_asr_batch_t* a, uint8_t* node_states, uint8_t* site_rate,
+                  double* site_rate_loglik) {
+  if (!f || !a || !a->trees) return fail("null argument");
+  if (!f->bound) return fail("lh_asr_sample needs a bound family");
+  const lh_tree_batch_t* tb = a->trees;
+  const int T = f->fd.T, B = tb->n_trees, R = tb->n_rates, S = a->n_sites;
+  if (B < 0 || S < 0) return fail("negative tree or site count");
+  if (R < 1 || R > LH_MAX_RATES) return fail("n_rates %d outside 1..%d", R, LH_MAX_RATES);
+  if (B == 0 || S == 0) return 0;
+  if (!tb->children || !tb->blen || !tb->root_child || !tb->root_blen || !tb->er || !tb->pi || !tb->rates ||
+      !a->msa_codes || !a->naive_codes || !node_states || !site_rate)
+    return fail("null argument");
+  if (a->naive_row < -1 || a->naive_row >= T) return fail("naive_row %d outside -1..%d", a->naive_row, T - 1);
+  const int n_ops = T - 2;
+  for (int b = 0; b < B; ++b) {
+    // children before parents, every inner node used once: what the kernel's single forward loop relies on
+    const int32_t* ch = tb->children + (size_t)b * n_ops * 2;
+    for (int op = 0; op < n_ops; ++op)
+      for (int c = 0; c < 2; ++c) {
+        const int id = ch[2 * op + c];
+        if (id < 0 || id >= T + op) return fail("tree %d: operation %d refers to node %d before it is computed", b, op, id);
+      }
+    const int rc = tb->root_child[b];
+    if (rc < 0 || rc >= T + n_ops - 1) return fail("tree %d: root_child %d out of range", b, rc);
+    for (int i = 0; i < 2 * n_ops; ++i)
+      if (!(tb->blen[(size_t)b * n_ops * 2 + i] >= 0.0)) return fail("tree %d: negative branch length", b);
+    if (!(tb->root_blen[b] >= 0.0)) return fail("tree %d: negative branch length", b);
+  }
+  LH_CUDA(cudaSetDevice(f->device));
+  std::string err;
+  const size_t scratch = f->opt_asr_scratch_mb > 0 ? (size_t)f->opt_asr_scratch_mb << 20 : (size_t)4 << 30;
+  if (lhb::asr_sample(T, B, R, tb->children, tb->blen, tb->root_child, tb->root_blen, tb->er, tb->pi, tb->rates, S,
+                      a->msa_codes, a->naive_row, a->naive_codes, a->seed, scratch, node_states, site_rate,
+                      site_rate_loglik, &err))
+    return fail("%s", err.c_str());
+  return 0;
+}
 
 int lh_get_timings(lh_family_t* f, lh_timings_t* out) {
   if (!f || !out) return fail("null argument");

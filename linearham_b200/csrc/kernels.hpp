@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <string>
 
 namespace lhb {
 
@@ -182,5 +183,12 @@ int prune_max_ctas_per_sm(int sites_per_thread, int smem_slots);
 size_t hmm_smem_bytes(const FamilyDev& f, int warps);
 // launches the DFMA diagnostic kernel; returns the flop count of the launch
 double fp64_peak_flops_per_launch(double* scratch, int blocks, int iters, cudaStream_t s);
+
+// asr.cu: ancestral-state sampling (lh_asr_sample); synchronous, own buffers. 0, or 1 with *err set.
+int asr_sample(int n_tips, int n_trees, int n_rates, const int32_t* children, const double* blen,
+               const int32_t* root_child, const double* root_blen, const double* er, const double* pi,
+               const double* rates, int n_sites, const uint8_t* msa, int naive_row, const uint8_t* naive,
+               uint64_t seed, size_t scratch_bytes, uint8_t* node_states, uint8_t* site_rate, double* site_rate_loglik,
+               std::string* err);
 
 }  // namespace lhb

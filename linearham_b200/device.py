@@ -84,6 +84,26 @@ class Family:
         self._ck(lib().lh_score_batch(self._h, C.byref(t), ll.ctypes.data_as(_f64p), None))
         return ll
 
+    def asr_sample(self, tb, msa_codes, naive_codes, naive_row=0, seed=0, loglik=False):
+        """Ancestral-state sampling (lh_asr_sample): per tree and alignment site the rate category, then the base of
+        every inner node. msa_codes [T][S] uint8 (row naive_row ignored), naive_codes [B][S] uint8.
+        -> dict(node_states [B][T-2][S], site_rate [B][S] (, site_rate_loglik [B][R][S]))."""
+        t, keep = _abi.tree_batch(tb)
+        msa = np.ascontiguousarray(msa_codes, dtype=np.uint8)
+        naive = np.ascontiguousarray(naive_codes, dtype=np.uint8)
+        B, T, S = t.n_trees, int(self.fam["n_tips"]), msa.shape[1]
+        assert msa.shape == (T, S) and naive.shape == (B, S)
+        u8p = C.POINTER(C.c_uint8)
+        a = _abi.AsrBatch(C.pointer(t), S, int(naive_row), msa.ctypes.data_as(u8p), naive.ctypes.data_as(u8p), int(seed))
+        out = {"node_states": np.zeros((B, T - 2, S), dtype=np.uint8), "site_rate": np.zeros((B, S), dtype=np.uint8)}
+        srl = None
+        if loglik:
+            out["site_rate_loglik"] = np.zeros((B, t.n_rates, S))
+            srl = out["site_rate_loglik"].ctypes.data_as(_f64p)
+        self._ck(lib().lh_asr_sample(self._h, C.byref(a), out["node_states"].ctypes.data_as(u8p),
+                                     out["site_rate"].ctypes.data_as(u8p), srl))
+        return out
+
     # Newick text in ------------------------------------------------------------
     def set_labels(self, labels):
         """xMSA row labels (row 0 = "naive") for the device Newick parser (lh_family_set_labels)."""

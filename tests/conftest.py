@@ -13,7 +13,7 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 # sample bundles (family + tree batch + reference outputs); family_*.npz hold a family description only
 GOLDEN_NAMES = sorted(n for n in (os.path.splitext(os.path.basename(p))[0]
                                   for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-                      if not n.startswith(("family_", "pipeline_", "liao_", "scaling_")))
+                      if not n.startswith(("family_", "pipeline_", "liao_", "scaling_", "fixture_")))
 # underflow-regime families scored by the reference (scripts/make_scaling_goldens.py)
 SCALING_NAMES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "scaling_*.npz")))
 

@@ -19,7 +19,7 @@ HAVE_REF = os.path.isfile("/root/reference/test/test.cpp")
 
 
 def _data_dir():
-    z = np.load(os.path.join(GOLDEN_DIR, "catch_data.npz"), allow_pickle=False)
+    z = np.load(os.path.join(GOLDEN_DIR, "fixture_catch_files.npz"), allow_pickle=False)
     d = tempfile.mkdtemp(prefix="lh_catch_")
     for name, text in zip(z["names"], z["texts"]):
         path = os.path.join(d, "data", str(name))
