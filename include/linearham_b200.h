@@ -250,7 +250,7 @@ int lh_debug_parse_newick(lh_family_t* fam, const lh_newick_batch_t* trees, int3
  * The family needs lh_family_set_labels (set-up; that call does allocate). The two kernels are queued on `stream`
  * (a cudaStream_t; NULL = the legacy default stream) and the call returns without waiting. Limit: n_trees *
  * ((2T-2)*14 rounded up to 16) bytes <= LH_NOALLOC_SCRATCH_BYTES, T < 32768 - lh_newick_parse_noalloc_max_trees(T)
- * trees per call (599 for 1001 tips); more is refused with an error. Every call shares the one array per GPU: it
+ * trees per call (466 for 1001 tips); more is refused with an error. Every call shares the one array per GPU: it
  * keeps the last call's contents (the kernel writes every item before reading it, so nothing needs clearing), and
  * calls that overlap on one GPU - two streams, two threads, two handles - race on it.                         */
 #define LH_NOALLOC_SCRATCH_BYTES (16u << 20)

@@ -285,20 +285,143 @@ constexpr int kCtaLevels = 256;   // depth the per-level tables are sized for; d
 // Per-tree item arrays (global scratch, L2-resident: written in S3/S5, read in S5/S6 by the same CTA):
 //   len [N] double (before S5: the text position in the low word) | id [N] int32 (xMSA row of a tip /
 //   operation index of a ')') | lvl [N] uint16 (depth of the parent's child list; bit 15: the node is a ')')
-__host__ __device__ inline size_t cta_items_stride(int n_tips) { return ((size_t)(2 * n_tips - 2) * 14 + 15) / 16 * 16; }
+//   rnk [N] uint16 (S6: the node's rank among the nodes filed under its level) | tab [T-2] int32 (S6: the ')' items
+//   grouped by level, in text order)
+__host__ __device__ inline size_t cta_items_stride(int n_tips) {
+  return ((size_t)(2 * n_tips - 2) * 16 + (size_t)(n_tips - 2) * 4 + 15) / 16 * 16;
+}
+struct LevelTables {         // S6, per level: ')' of that level, where its group starts in tab, running ranks
+  int n_close[kCtaLevels + 1], start[kCtaLevels + 1], run_filed[kCtaLevels + 1], run_close[kCtaLevels + 1];
+};
 struct CtaLayout {           // dynamic shared memory of k_newick_cta
-  size_t pid, pl, cnt, sum, start, total;
+  size_t lev, sum, start, total;
   __host__ __device__ explicit CtaLayout(int nt) {
     size_t at = 0;
     auto take = [&](size_t bytes) { const size_t o = at; at += (bytes + 15) / 16 * 16; return o; };
-    pid = take((size_t)(kCtaLevels + 1) * 8);   // int2: the two children filed under a level
-    pl = take((size_t)(kCtaLevels + 1) * 16);   // double2: their branch lengths
-    cnt = take((size_t)(kCtaLevels + 1));       // uint8: how many are filed
+    lev = take(sizeof(LevelTables));
     sum = take((size_t)nt * sizeof(SliceSummary));
     start = take((size_t)nt * sizeof(SliceStart));
     total = at;
   }
 };
+
+// ---- S6: children to parents, in parallel -------------------------------------------------------------------------
+// A tip is filed under the level of the list it stands in, a ')' under the level below the list it closes, and a ')'
+// takes the two nodes filed under its own level since the previous ')' of that level: per level the text reads
+// (F F C)*. So the k-th ')' of level l (in text order) owns the nodes of rank 2k and 2k+1 among those filed under l.
+// The ranks are stable counting-sort ranks: one warp walks the items in text order, 32 at a time, and ranks a window
+// with __match_any_sync plus a running count per level; the ')' items are scattered into `tab`, grouped by level.
+// Then every node finds its parent on its own - rank >> 1 names the ')' - and checks that it stands between that ')'
+// and the one before it; with "filed = 2 x closes" per level that is exactly the (F F C)* pattern. Level 1 is the
+// root's list: three nodes (root_child, then the two kept in the last operation) and one ')' that must be the last
+// item. NT threads (a CTA, or one warp) call this together; returns false (to every thread) if the tree is not of
+// that shape. The serial walk this replaces took ~0.8 ms per 1001-tip tree (2000 dependent steps over L2-resident
+// items): the latency of a small chunk's parse, which is what stands in front of its pruning kernel.
+template <int NT>
+__device__ __forceinline__ void group_sync() {
+  if (NT == 32) __syncwarp();
+  else __syncthreads();
+}
+template <int NT>
+__device__ bool link_items(const NewickDev& p, int t, int T, int n_items, const double* LEN, const int32_t* ID,
+                           const uint16_t* LVL, uint16_t* RNK, int32_t* TAB, LevelTables& lev, int* s_bad, int* s_on_pat,
+                           int2* __restrict__ ch, double2* __restrict__ bl) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, lane = tid & 31, n_ops = T - 2;
+  for (int l = tid; l <= kCtaLevels; l += NT) lev.n_close[l] = lev.run_filed[l] = lev.run_close[l] = 0;
+  if (tid == 0) *s_bad = *s_on_pat = 0;
+  group_sync<NT>();
+  for (int it = tid; it < n_items; it += NT) {
+    const unsigned lv = __ldcg(LVL + it);
+    if (lv & 0x8000u) atomicAdd(&lev.n_close[lv & 0x7fffu], 1);
+  }
+  group_sync<NT>();
+  if (tid < 32) {   // exclusive scan over the levels
+    int carry = 0;
+    for (int base = 0; base <= kCtaLevels; base += 32) {
+      const int l = base + lane, v = l <= kCtaLevels ? lev.n_close[l] : 0;
+      int inc = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int up = __shfl_up_sync(FULL, inc, d);
+        if (lane >= d) inc += up;
+      }
+      if (l <= kCtaLevels) lev.start[l] = carry + inc - v;
+      carry += __shfl_sync(FULL, inc, 31);
+    }
+    __syncwarp();
+    // stable ranks, in text order
+    const unsigned lt = (1u << lane) - 1u;
+    for (int base = 0; base < n_items; base += 32) {
+      const int it = base + lane;
+      const bool valid = it < n_items;
+      const unsigned lv = valid ? __ldcg(LVL + it) : 0u;
+      const bool close = (lv & 0x8000u) != 0;
+      const int lvl = (int)(lv & 0x7fffu);
+      const int filed = valid ? (close ? lvl - 1 : lvl) : 0x10000 + lane;     // (an idle lane groups with nobody)
+      const int closed = (valid && close) ? lvl : 0x10000 + lane;
+      const unsigned mf = __match_any_sync(FULL, filed), mc = __match_any_sync(FULL, closed);
+      int rf = 0, rc = 0;
+      if (valid) rf = lev.run_filed[filed] + __popc(mf & lt);
+      if (valid && close) rc = lev.run_close[lvl] + __popc(mc & lt);
+      __syncwarp();
+      if (valid && lane == 31 - __clz(mf)) lev.run_filed[filed] += __popc(mf);
+      if (valid && close && lane == 31 - __clz(mc)) lev.run_close[lvl] += __popc(mc);
+      __syncwarp();
+      if (valid) RNK[it] = (uint16_t)rf;
+      if (valid && close) TAB[lev.start[lvl] + rc] = it;
+    }
+  }
+  group_sync<NT>();
+  bool bad = false;
+  for (int l = tid; l <= kCtaLevels; l += NT) {
+    if (l >= 2 && lev.run_filed[l] != 2 * lev.n_close[l]) bad = true;
+    if (l == 1 && (lev.run_filed[1] != 3 || lev.n_close[1] != 1)) bad = true;
+  }
+  for (int it = tid; it < n_items; it += NT) {
+    const unsigned lv = __ldcg(LVL + it);
+    const bool close = (lv & 0x8000u) != 0;
+    const int lvl = (int)(lv & 0x7fffu), filed = close ? lvl - 1 : lvl, r = __ldcg(RNK + it);
+    const int own = __ldcg(ID + it), id = close ? T + own : own;
+    const double len = __ldcg(LEN + it);
+    if (filed == 0) {   // the ')' of the root's list: the last item, the last operation
+      if (it != n_items - 1 || own != n_ops - 1) bad = true;
+      continue;
+    }
+    if (filed == 1) {
+      if (r == 0) {
+        p.root_child[t] = id;
+        p.root_blen[t] = len;
+      } else if (r == 1) {
+        ch[n_ops - 1].x = id;
+        bl[n_ops - 1].x = len;
+      } else if (r == 2) {
+        ch[n_ops - 1].y = id;
+        bl[n_ops - 1].y = len;
+      } else {
+        bad = true;
+      }
+      if (id == 0) *s_on_pat = 1;   // the naive tip under the root: the tree runs on site patterns
+      continue;
+    }
+    const int k = r >> 1;
+    if (k >= lev.n_close[filed]) { bad = true; continue; }
+    const int32_t* grp = TAB + lev.start[filed];
+    const int parent = __ldcg(grp + k);
+    if (it > parent || (k > 0 && it < __ldcg(grp + k - 1))) { bad = true; continue; }
+    const int op = __ldcg(ID + parent);
+    if (r & 1) {
+      ch[op].y = id;
+      bl[op].y = len;
+    } else {
+      ch[op].x = id;
+      bl[op].x = len;
+    }
+  }
+  if (bad) *s_bad = 1;
+  group_sync<NT>();
+  return *s_bad == 0;
+}
 
 // (at most 40 registers - 22 bytes of spills, 14.3 ms instead of 14.8 per 16 384 C4 trees. 128 x 40 = 5 K registers
 // is also what one k_prune CTA of 32 x 164 leaves free when it steps aside - option "parse_reserve" - so that the
@@ -319,9 +442,9 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
   double* LEN = reinterpret_cast<double*>(items);
   int32_t* ID = reinterpret_cast<int32_t*>(items + (size_t)n_items * 8);
   uint16_t* LVL = reinterpret_cast<uint16_t*>(items + (size_t)n_items * 12);
-  int2* PID = reinterpret_cast<int2*>(nw_smem + lay.pid);
-  double2* PL = reinterpret_cast<double2*>(nw_smem + lay.pl);
-  uint8_t* CNT = nw_smem + lay.cnt;
+  uint16_t* RNK = reinterpret_cast<uint16_t*>(items + (size_t)n_items * 14);
+  int32_t* TAB = reinterpret_cast<int32_t*>(items + (size_t)n_items * 16);
+  LevelTables& lev = *reinterpret_cast<LevelTables*>(nw_smem + lay.lev);
   SliceSummary* SUM = reinterpret_cast<SliceSummary*>(nw_smem + lay.sum);
   SliceStart* START = reinterpret_cast<SliceStart*>(nw_smem + lay.start);
   int2* __restrict__ ch = reinterpret_cast<int2*>(p.children) + (size_t)t * n_ops;
@@ -337,7 +460,6 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
     s_cls[c] = (uint8_t)(c == '[' ? 6 : c == ']' ? 7 : (c == 0 || is_blank(c)) ? 8 : structural(c));
   if (tid < 4) s_flag[tid] = 0;
   if (tid == 4) s_deep = 0;
-  for (int l = tid; l <= kCtaLevels; l += NT) CNT[l] = 0;
 
   // ---- S0: is the start of my slice inside a comment? ----
   int my_last = 0;  // 0: no bracket in the slice, 1: its last bracket is '[', 2: ']'
@@ -542,66 +664,17 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
     __syncthreads();
   }
 
-  if (tid == 0 && !s_flag[0] && !s_flag[1] && !s_flag[2]) {
-    // ---- S6: children to parents, in text order ----
-    int root_child = 0, top0 = 0, top1 = 0, c1 = 0;
-    double root_blen = 0.0, topl0 = 0.0, topl1 = 0.0;
-    bool bad = false, done = false;
-    for (int base = 0; base < n_items && !bad && !done; base += 4) {
-      // (the items come from L2: four at a time, so that their latency is paid once per four)
-      unsigned lv4[4];
-      int id4[4];
-      double len4[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int it = min(base + j, n_items - 1);
-        lv4[j] = __ldcg(LVL + it);
-        id4[j] = __ldcg(ID + it);
-        len4[j] = __ldcg(LEN + it);
+  if (!s_flag[0] && !s_flag[1] && !s_flag[2]) {
+    // ---- S6: children to parents ----
+    __shared__ int s_bad, s_on_pat;
+    const bool ok = link_items<NT>(p, t, T, n_items, LEN, ID, LVL, RNK, TAB, lev, &s_bad, &s_on_pat, ch, bl);
+    if (tid == 0) {
+      if (ok) {
+        p.on_pat[t] = s_on_pat ? 1 : 0;
+        p.status[t] = 0;
+      } else {
+        s_flag[3] = 1;
       }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int it = base + j;
-        if (it >= n_items || bad || done) break;
-        int lvl = (int)(lv4[j] & 0x7fffu), id = id4[j];
-        const double len = len4[j];
-        if (lv4[j] & 0x8000u) {
-          if (lvl == 1) {  // the trifurcation, last
-            if (c1 != 3 || id != n_ops - 1 || it != n_items - 1) bad = true;
-            done = true;
-            break;
-          }
-          if (CNT[lvl] != 2) { bad = true; break; }
-          ch[id] = PID[lvl];
-          bl[id] = PL[lvl];
-          CNT[lvl] = 0;
-          id += T;
-          --lvl;
-        }
-        if (lvl == 1) {
-          if (c1 == 0) { root_child = id; root_blen = len; }
-          else if (c1 == 1) { top0 = id; topl0 = len; }
-          else if (c1 == 2) { top1 = id; topl1 = len; }
-          else bad = true;
-          ++c1;
-        } else {
-          const int k = CNT[lvl];
-          if (k == 0) { PID[lvl].x = id; PL[lvl].x = len; }
-          else if (k == 1) { PID[lvl].y = id; PL[lvl].y = len; }
-          else bad = true;
-          CNT[lvl] = (uint8_t)(k + 1);
-        }
-      }
-    }
-    if (bad || !done) {
-      s_flag[3] = 1;
-    } else {
-      ch[n_ops - 1] = make_int2(top0, top1);
-      bl[n_ops - 1] = make_double2(topl0, topl1);
-      p.root_child[t] = root_child;
-      p.root_blen[t] = root_blen;
-      p.on_pat[t] = (root_child == 0 || top0 == 0 || top1 == 0) ? 1 : 0;
-      p.status[t] = 0;
     }
   }
   __syncthreads();
@@ -635,9 +708,8 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
 // of a window (in a comment?, in a word?, last token, depth, counts) is carried in registers to the next. S5 (label
 // -> row, branch length -> double, one lane per node) and S6 (children to parents) are k_newick_cta's.
 __global__ void __launch_bounds__(32, 24) k_newick_warp(NewickDev p) {
-  __shared__ int2 PID[kCtaLevels + 1];
-  __shared__ double2 PL[kCtaLevels + 1];
-  __shared__ uint8_t CNT[kCtaLevels + 1];
+  __shared__ LevelTables lev;
+  __shared__ int s_bad, s_on_pat;
   __shared__ uint8_t s_cls[256];
   constexpr unsigned FULL = 0xffffffffu;
   const int i = blockIdx.x, lane = threadIdx.x;
@@ -647,13 +719,14 @@ __global__ void __launch_bounds__(32, 24) k_newick_warp(NewickDev p) {
   double* LEN = reinterpret_cast<double*>(items);
   int32_t* ID = reinterpret_cast<int32_t*>(items + (size_t)n_items * 8);
   uint16_t* LVL = reinterpret_cast<uint16_t*>(items + (size_t)n_items * 12);
+  uint16_t* RNK = reinterpret_cast<uint16_t*>(items + (size_t)n_items * 14);
+  int32_t* TAB = reinterpret_cast<int32_t*>(items + (size_t)n_items * 16);
   int2* __restrict__ ch = reinterpret_cast<int2*>(p.children) + (size_t)t * n_ops;
   double2* __restrict__ bl = reinterpret_cast<double2*>(p.blen) + (size_t)t * n_ops;
   const char* text = p.text + __ldg(p.offs + i);
   const uint32_t L = __ldg(p.lens + i);
   for (int c = lane; c < 256; c += 32)
     s_cls[c] = (uint8_t)(c == '[' ? 6 : c == ']' ? 7 : (c == 0 || is_blank(c)) ? 8 : structural(c));
-  for (int l = lane; l <= kCtaLevels; l += 32) CNT[l] = 0;
   __syncwarp();
 
   // ---- lexing: token grammar, one item per node (what S0-S3 of k_newick_cta do in four passes) ----
@@ -762,67 +835,15 @@ __global__ void __launch_bounds__(32, 24) k_newick_warp(NewickDev p) {
   }
 
   if (!bad) {
-    // ---- S6: children to parents, in text order ----
-    if (lane == 0) {
-      int root_child = 0, top0 = 0, top1 = 0, c1 = 0;
-      double root_blen = 0.0, topl0 = 0.0, topl1 = 0.0;
-      bool done = false;
-      for (int base = 0; base < n_items && !bad && !done; base += 4) {
-        unsigned lv4[4];
-        int id4[4];
-        double len4[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int it = min(base + j, n_items - 1);
-          lv4[j] = __ldcg(LVL + it);
-          id4[j] = __ldcg(ID + it);
-          len4[j] = __ldcg(LEN + it);
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int it = base + j;
-          if (it >= n_items || bad || done) break;
-          int lvl = (int)(lv4[j] & 0x7fffu), id = id4[j];
-          const double len = len4[j];
-          if (lv4[j] & 0x8000u) {
-            if (lvl == 1) {  // the trifurcation, last
-              if (c1 != 3 || id != n_ops - 1 || it != n_items - 1) bad = true;
-              done = true;
-              break;
-            }
-            if (CNT[lvl] != 2) { bad = true; break; }
-            ch[id] = PID[lvl];
-            bl[id] = PL[lvl];
-            CNT[lvl] = 0;
-            id += T;
-            --lvl;
-          }
-          if (lvl == 1) {
-            if (c1 == 0) { root_child = id; root_blen = len; }
-            else if (c1 == 1) { top0 = id; topl0 = len; }
-            else if (c1 == 2) { top1 = id; topl1 = len; }
-            else bad = true;
-            ++c1;
-          } else {
-            const int k = CNT[lvl];
-            if (k == 0) { PID[lvl].x = id; PL[lvl].x = len; }
-            else if (k == 1) { PID[lvl].y = id; PL[lvl].y = len; }
-            else bad = true;
-            CNT[lvl] = (uint8_t)(k + 1);
-          }
-        }
-      }
-      if (!done) bad = true;
-      if (!bad) {
-        ch[n_ops - 1] = make_int2(top0, top1);
-        bl[n_ops - 1] = make_double2(topl0, topl1);
-        p.root_child[t] = root_child;
-        p.root_blen[t] = root_blen;
-        p.on_pat[t] = (root_child == 0 || top0 == 0 || top1 == 0) ? 1 : 0;
+    // ---- S6: children to parents ----
+    if (link_items<32>(p, t, T, n_items, LEN, ID, LVL, RNK, TAB, lev, &s_bad, &s_on_pat, ch, bl)) {
+      if (lane == 0) {
+        p.on_pat[t] = s_on_pat ? 1 : 0;
         p.status[t] = 0;
       }
+    } else {
+      bad = true;
     }
-    bad = __shfl_sync(FULL, bad, 0);
   }
   if (bad) {
     // stand-in (see k_newick): the host parser decides what the tree really is
