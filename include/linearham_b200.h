@@ -212,7 +212,7 @@ int lh_loglik_dev(lh_family_t* fam, const double** loglik_dev, int32_t* n); /* d
  * Draws come from Philox4x32-10 keyed by `seed` with counter (tree, site, draw): the result depends on nothing but
  * the arguments. The reference draws with R's generator on a worker cluster, which nothing outside R reproduces;
  * parity with it is distributional, parity with oracle/asr_oracle.py exact (tests/test_gpu_asr.py). Synchronous;
- * allocates its own buffers per call (option "asr_scratch_mb": CLV scratch per chunk of trees, default 4096).   */
+ * keeps one device pool per handle between calls (option "asr_scratch_mb": CLV scratch per chunk of trees, default 4096).   */
 typedef struct lh_asr_batch {
   const lh_tree_batch_t* trees;
   int32_t n_sites;

@@ -242,6 +242,7 @@ struct lh_family {
   int opt_open_unit = 1, opt_chunk_growth = 1;
   int opt_parse_reserve = 0;  // pruning CTAs per SM given up for the parser while text is coming in (measured: no gain, the parser of a chunk runs between the pruning launches either way)
   int opt_asr_scratch_mb = 0; // lh_asr_sample: CLV scratch per chunk of trees (0 = 4096 MB)
+  void* asr_cache = nullptr;  // lh_asr_sample's device pool, kept between calls (lhb::asr_cache_free)
   int opt_newick_kernel = 0;  // 0 / 2 k_newick_cta (one CTA per tree), 1 k_newick (one thread per tree), 3 k_newick_warp (one warp per tree)
   double stage_ratio = 1.0;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
@@ -299,6 +300,8 @@ void lh_family_destroy(lh_family_t* f) {
                     &f->d_label_slots, &f->d_label_off, &f->d_label_chars, &f->d_textbuf[0], &f->d_textbuf[1], &f->d_items, &f->d_toffs, &f->d_tlens,
                     &f->d_on_pat, &f->d_nw_status, &f->d_chunk_npat};
   for (DevBuf* b : bufs) b->release();
+  lhb::asr_cache_free(f->asr_cache);
+  f->asr_cache = nullptr;
   for (auto& r : f->h_ring) r.release();
   for (auto& c : f->cols) c.h_codes_t.release();
   f->h_misc.release();
@@ -2122,7 +2125,7 @@ int lh_asr_sample(lh_family_t* f, const lh_asr_batch_t* a, uint8_t* node_states,
   LH_CUDA(cudaSetDevice(f->device));
   std::string err;
   const size_t scratch = f->opt_asr_scratch_mb > 0 ? (size_t)f->opt_asr_scratch_mb << 20 : (size_t)4 << 30;
-  if (lhb::asr_sample(T, B, R, tb->children, tb->blen, tb->root_child, tb->root_blen, tb->er, tb->pi, tb->rates, S,
+  if (lhb::asr_sample(&f->asr_cache, T, B, R, tb->children, tb->blen, tb->root_child, tb->root_blen, tb->er, tb->pi, tb->rates, S,
                       a->msa_codes, a->naive_row, a->naive_codes, a->seed, scratch, node_states, site_rate,
                       site_rate_loglik, &err))
     return fail("%s", err.c_str());

@@ -241,12 +241,16 @@ __global__ void __launch_bounds__(128) k_asr(AsrDev a) {
   }
 }
 
-template <class T>
-struct DevBuf {
-  T* p = nullptr;
-  cudaError_t alloc(size_t n) { return cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)); }
-  ~DevBuf() {
-    if (p) cudaFree(p);
+// One device allocation per handle, kept between calls and carved into the call's buffers (a call used to spend
+// more time in cudaMalloc / cudaFree of its 3 GB scratch than in its kernels).
+struct AsrPool {
+  unsigned char* base = nullptr;
+  size_t cap = 0, at = 0;
+  template <class T>
+  T* take(size_t n) {
+    T* p = reinterpret_cast<T*>(base + at);
+    at += (std::max<size_t>(n, 1) * sizeof(T) + 255) / 256 * 256;
+    return p;
   }
 };
 
@@ -261,8 +265,16 @@ struct DevBuf {
     }                                                                                   \
   } while (0)
 
-// Host driver: chunks of trees sized so that the CLV scratch stays below `scratch_bytes`; synchronous.
-int asr_sample(int n_tips, int n_trees, int n_rates, const int32_t* children, const double* blen,
+void asr_cache_free(void* cache) {
+  AsrPool* pool = static_cast<AsrPool*>(cache);
+  if (!pool) return;
+  if (pool->base) cudaFree(pool->base);
+  delete pool;
+}
+
+// Host driver: chunks of trees sized so that the CLV scratch stays below `scratch_bytes`; synchronous. *cache holds
+// the device pool between calls (owned by the family handle, released with asr_cache_free).
+int asr_sample(void** cache, int n_tips, int n_trees, int n_rates, const int32_t* children, const double* blen,
                const int32_t* root_child, const double* root_blen, const double* er, const double* pi,
                const double* rates, int n_sites, const uint8_t* msa, int naive_row, const uint8_t* naive,
                uint64_t seed, size_t scratch_bytes, uint8_t* node_states, uint8_t* site_rate, double* site_rate_loglik,
@@ -270,24 +282,36 @@ int asr_sample(int n_tips, int n_trees, int n_rates, const int32_t* children, co
   const int T = n_tips, S = n_sites, R = n_rates, n_ops = T - 2, NB = 2 * T - 3;
   const size_t per_tree = (size_t)n_ops * 4 * S * sizeof(double);
   const int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_trees, scratch_bytes / std::max<size_t>(per_tree, 1)));
-  DevBuf<int32_t> d_children, d_root_child;
-  DevBuf<double> d_blen, d_root_blen, d_er, d_pi, d_rates, d_eig, d_pm, d_clv, d_srl;
-  DevBuf<uint8_t> d_msa, d_naive, d_states, d_site_rate;
-  LH_ASR_CK(d_children.alloc((size_t)chunk * n_ops * 2));
-  LH_ASR_CK(d_blen.alloc((size_t)chunk * n_ops * 2));
-  LH_ASR_CK(d_root_child.alloc(chunk));
-  LH_ASR_CK(d_root_blen.alloc(chunk));
-  LH_ASR_CK(d_er.alloc((size_t)chunk * 6));
-  LH_ASR_CK(d_pi.alloc((size_t)chunk * 4));
-  LH_ASR_CK(d_rates.alloc((size_t)chunk * R));
-  LH_ASR_CK(d_eig.alloc((size_t)chunk * kEigStride));
-  LH_ASR_CK(d_pm.alloc((size_t)chunk * NB * R * 16));
-  LH_ASR_CK(d_clv.alloc((size_t)chunk * n_ops * 4 * S));
-  LH_ASR_CK(d_msa.alloc((size_t)T * S));
-  LH_ASR_CK(d_naive.alloc((size_t)chunk * S));
-  LH_ASR_CK(d_states.alloc((size_t)chunk * n_ops * S));
-  LH_ASR_CK(d_site_rate.alloc((size_t)chunk * S));
-  if (site_rate_loglik) LH_ASR_CK(d_srl.alloc((size_t)chunk * R * S));
+  if (!*cache) *cache = new AsrPool();
+  AsrPool& pool = *static_cast<AsrPool*>(*cache);
+  struct { int32_t *p; } d_children, d_root_child;
+  struct { double* p; } d_blen, d_root_blen, d_er, d_pi, d_rates, d_eig, d_pm, d_clv, d_srl;
+  struct { uint8_t* p; } d_msa, d_naive, d_states, d_site_rate;
+  for (int pass = 0; pass < 2; ++pass) {   // pass 0 measures, pass 1 carves
+    pool.at = 0;
+    d_children.p = pool.take<int32_t>((size_t)chunk * n_ops * 2);
+    d_blen.p = pool.take<double>((size_t)chunk * n_ops * 2);
+    d_root_child.p = pool.take<int32_t>(chunk);
+    d_root_blen.p = pool.take<double>(chunk);
+    d_er.p = pool.take<double>((size_t)chunk * 6);
+    d_pi.p = pool.take<double>((size_t)chunk * 4);
+    d_rates.p = pool.take<double>((size_t)chunk * R);
+    d_eig.p = pool.take<double>((size_t)chunk * kEigStride);
+    d_pm.p = pool.take<double>((size_t)chunk * NB * R * 16);
+    d_clv.p = pool.take<double>((size_t)chunk * n_ops * 4 * S);
+    d_msa.p = pool.take<uint8_t>((size_t)T * S);
+    d_naive.p = pool.take<uint8_t>((size_t)chunk * S);
+    d_states.p = pool.take<uint8_t>((size_t)chunk * n_ops * S);
+    d_site_rate.p = pool.take<uint8_t>((size_t)chunk * S);
+    d_srl.p = site_rate_loglik ? pool.take<double>((size_t)chunk * R * S) : nullptr;
+    if (pass == 0 && pool.at > pool.cap) {
+      if (pool.base) LH_ASR_CK(cudaFree(pool.base));
+      pool.base = nullptr;
+      pool.cap = 0;
+      LH_ASR_CK(cudaMalloc(&pool.base, pool.at));
+      pool.cap = pool.at;
+    }
+  }
   LH_ASR_CK(cudaMemcpy(d_msa.p, msa, (size_t)T * S, cudaMemcpyHostToDevice));
   for (int t0 = 0; t0 < n_trees; t0 += chunk) {
     const int n = std::min(chunk, n_trees - t0);

@@ -184,8 +184,10 @@ size_t hmm_smem_bytes(const FamilyDev& f, int warps);
 // launches the DFMA diagnostic kernel; returns the flop count of the launch
 double fp64_peak_flops_per_launch(double* scratch, int blocks, int iters, cudaStream_t s);
 
-// asr.cu: ancestral-state sampling (lh_asr_sample); synchronous, own buffers. 0, or 1 with *err set.
-int asr_sample(int n_tips, int n_trees, int n_rates, const int32_t* children, const double* blen,
+// asr.cu: ancestral-state sampling (lh_asr_sample); synchronous; *cache keeps its device pool between calls
+// (nullptr at first, released with asr_cache_free). 0, or 1 with *err set.
+void asr_cache_free(void* cache);
+int asr_sample(void** cache, int n_tips, int n_trees, int n_rates, const int32_t* children, const double* blen,
                const int32_t* root_child, const double* root_blen, const double* er, const double* pi,
                const double* rates, int n_sites, const uint8_t* msa, int naive_row, const uint8_t* naive,
                uint64_t seed, size_t scratch_bytes, uint8_t* node_states, uint8_t* site_rate, double* site_rate_loglik,
