@@ -350,7 +350,9 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
     Bs = hi - lo
     alpha_s = alpha[lo:hi]
     # the shard's trees as the RevBayes trace would hold them (text), written once outside the timed regions
-    text = host.NewickBuffer(shard, labels)
+    # (in pinned host memory - the contract's "inputs from pinned host memory": the library then copies the strings to
+    # the device where they lie; --pageable-text puts them in ordinary memory, staged through the library's pinned ring)
+    text = host.NewickBuffer(shard, labels, pinned=not args.pageable_text)
 
     f = device.Family(fam, device=dev)
     f.set_labels(labels)
@@ -440,7 +442,7 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
             stage = torch.empty(per, dtype=torch.float64, device=f"cuda:{dev}") if dist is not None else None
 
             def e2e_step():
-                ll = phmm.ScoreSamples(text.ptrs, shard["er"], shard["pi"], alpha_s, R)
+                ll = phmm.ScoreSamples(text, shard["er"], shard["pi"], alpha_s, R)
                 if dist is None:
                     return ll
                 stage[:Bs].copy_(torch.from_numpy(ll), non_blocking=True)
@@ -460,7 +462,7 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
             e2e_s = time.perf_counter() - t0
             h2d_e, d2h_e = t3["h2d_bytes"], t3["d2h_bytes"]
             e2e_detail = {k: t3[k] for k in ("ms_call", "ms_setup", "ms_plan", "ms_h2d", "ms_kernels", "ms_d2h", "ms_plan_dev",
-                                             "ms_newick", "newick_host_trees", "pattern_trees")}
+                                             "ms_newick", "newick_host_trees", "pattern_trees", "text_direct")}
             if rank == 0:
                 assert np.array_equal(ll_host, full_value, equal_nan=True), "text in and arrays in must give the same doubles"
         # -------- e2e_pipeline: the product's real entry point, RunPipeline (src/PhyloHMM.cpp:393-446): RevBayes trace TSV in,
@@ -571,6 +573,7 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
             "e2e": None if e2e_s is None else {
                 "value": B_total * steps / e2e_max, "unit": UNIT, "h2d_bytes_per_step": h2d_e, "d2h_bytes_per_step": d2h_e,
                 "newick_bytes_per_step_rank0": text.total_bytes(), "host_threads_per_rank": env.host_threads,
+                "text_memory": "pinned (copied in place, 2-D copy per chunk)" if text.pinned else "pageable (staged through the pinned ring)",
                 "last_call_ms_rank0": e2e_detail, "gather_timed": world > 1,
                 "api": "PhyloHMM::ScoreSamples (Newick strings + er/pi/alpha on the host in, log-likelihoods out): text to the "
                        "GPU, k_newick, k_plan, k_eigen, k_pmatrix, k_prune, k_edge, k_hmm; Gamma rates on the host threads"
@@ -599,6 +602,8 @@ def main():
     ap.add_argument("--topologies", type=int, default=256, help="distinct tree topologies in the batch")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--pageable-text", dest="pageable_text", action="store_true",
+                    help="e2e: hold the Newick text in pageable instead of pinned host memory")
     ap.add_argument("--no-extras", action="store_true", help="skip the c3 / c5 records of the default run")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE",
                     help="lh_set_option on the family (e.g. pipe_waves=4); recorded in config")

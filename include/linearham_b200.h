@@ -162,6 +162,8 @@ typedef struct lh_timings {
   int32_t device_plan;       /* 1 when the batch was planned by k_plan                   */
   float ms_newick;           /* sum over k_newick launches (device Newick parsing)       */
   int32_t newick_host_trees; /* trees of an lh_score_newick call the host parser took over */
+  int32_t text_direct;       /* chunks of an lh_score_newick call whose text was copied in place from the caller's
+                              * pinned memory (one 2-D copy) instead of being staged through the pinned ring   */
 } lh_timings_t;
 
 const char* lh_last_error(void);
@@ -224,6 +226,13 @@ typedef struct lh_asr_batch {
 int lh_asr_sample(lh_family_t* fam, const lh_asr_batch_t* batch, uint8_t* node_states, uint8_t* site_rate,
                   double* site_rate_loglik);
 
+/* Page-lock a range of the caller's own memory for every device of the process (cudaHostRegister). Newick text
+ * that lh_score_newick finds in pinned memory, with its lengths given and one string every constant number of bytes
+ * (8-byte aligned), is copied to the device where it lies - one 2-D copy per chunk, no staging pass of the host over
+ * the bytes (lh_timings_t.text_direct counts those chunks; option "text_direct" = 0 turns it off). Memory from
+ * cudaHostAlloc / torch pin_memory qualifies as it is.                                                         */
+int lh_pin_host(void* ptr, size_t bytes);
+int lh_unpin_host(void* ptr);
 int lh_get_timings(lh_family_t* fam, lh_timings_t* out); /* of the last run/score */
 /* Test hook: the traversal programs of the current batch as the device holds them
  * (steps [B][T-1][4] int32, pblen [B][2T-3]); compared with the host planner in the tests. */

@@ -85,6 +85,11 @@ int lhh_phylohmm_run_pipeline(lhh_phylohmm_t* h, const char* input_path, const c
 /* The loop body :419-430 for n samples at once: log-likelihoods only.                           */
 int lhh_phylohmm_score_samples(lhh_phylohmm_t* h, int32_t n, const char* const* newicks, const double* er,
                                const double* pi, const double* alpha, int32_t num_rates, double* loglik);
+/* The same with the strings' lengths (NULL: as above). Strings in pinned memory (lh_pin_host), one every constant
+ * number of bytes, are copied to the device where they lie.                                      */
+int lhh_phylohmm_score_samples_len(lhh_phylohmm_t* h, int32_t n, const char* const* newicks, const int64_t* lengths,
+                                   const double* er, const double* pi, const double* alpha, int32_t num_rates,
+                                   double* loglik);
 /* The device handle (include/linearham_b200.h) behind the object, created on first use: for
  * lh_get_timings / lh_set_option / lh_loglik_dev after a scoring call. Owned by the object.       */
 struct lh_family;

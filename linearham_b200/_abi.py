@@ -81,7 +81,7 @@ class Timings(C.Structure):
         ("prune_columns", C.c_int32), ("pattern_trees", C.c_int32),
         ("ms_call", C.c_float), ("ms_setup", C.c_float),
         ("ms_plan_dev", C.c_float), ("device_plan", C.c_int32),
-        ("ms_newick", C.c_float), ("newick_host_trees", C.c_int32),
+        ("ms_newick", C.c_float), ("newick_host_trees", C.c_int32), ("text_direct", C.c_int32),
     ]
 
 
@@ -196,7 +196,7 @@ DEVICE_SYMBOLS = [
     "lh_loglik_dev", "lh_get_timings", "lh_set_option", "lh_measure_fp64_peak",
     "lh_timer_mark", "lh_timer_elapsed_ms", "lh_family_rebind", "lh_debug_fetch_plan",
     "lh_family_set_labels", "lh_score_newick", "lh_debug_parse_newick", "lh_newick_parse_noalloc",
-    "lh_newick_parse_noalloc_max_trees", "lh_asr_sample",
+    "lh_newick_parse_noalloc_max_trees", "lh_asr_sample", "lh_pin_host", "lh_unpin_host",
     "lh_group_create", "lh_group_destroy", "lh_group_size", "lh_group_member", "lh_group_set_labels", "lh_group_set_option",
     "lh_group_score_batch", "lh_group_score_newick", "lh_group_get_timings", "lh_group_last_error", "lh_parse_devices",
     "lh_repertoire_create_multi", "lh_repertoire_create", "lh_repertoire_score", "lh_repertoire_destroy", "lh_repertoire_set_option", "lh_repertoire_last_error",
@@ -243,6 +243,8 @@ def load_library(path=None):
     lib.lh_debug_fetch_plan.argtypes = [C.c_void_p, _i32p, _f64p]
     lib.lh_family_rebind.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
     lib.lh_family_set_labels.argtypes = [C.c_void_p, C.POINTER(C.c_char_p)]
+    lib.lh_pin_host.argtypes = [C.c_void_p, C.c_size_t]
+    lib.lh_unpin_host.argtypes = [C.c_void_p]
     lib.lh_asr_sample.argtypes = [C.c_void_p, C.POINTER(AsrBatch), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8), _f64p]
     lib.lh_newick_parse_noalloc.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 10
     lib.lh_newick_parse_noalloc_max_trees.argtypes = [C.c_int32]
@@ -295,7 +297,7 @@ def bind_host(lib):
 
 HOST_SYMBOLS += ["lhh_phylohmm_new", "lhh_phylohmm_free", "lhh_phylohmm_set_device", "lhh_phylohmm_set_devices", "lhh_phylohmm_set_host_threads", "lhh_phylohmm_family_desc",
                  "lhh_phylohmm_init_params", "lhh_phylohmm_init_emission", "lhh_phylohmm_loglikelihood",
-                 "lhh_phylohmm_sample_naive", "lhh_phylohmm_run_pipeline", "lhh_phylohmm_score_samples", "lhh_phylohmm_device_family",
+                 "lhh_phylohmm_sample_naive", "lhh_phylohmm_run_pipeline", "lhh_phylohmm_score_samples", "lhh_phylohmm_score_samples_len", "lhh_phylohmm_device_family",
                  "lhh_export_newick", "lhh_phylohmm_get_f64", "lhh_phylohmm_get_i32", "lhh_phylohmm_get_str"]
 
 
@@ -316,6 +318,8 @@ def bind_phylohmm(lib):
     lib.lhh_phylohmm_run_pipeline.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32]
     lib.lhh_phylohmm_score_samples.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), _f64p, _f64p, _f64p,
                                                C.c_int32, _f64p]
+    lib.lhh_phylohmm_score_samples_len.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), _f64p,
+                                                   _f64p, _f64p, C.c_int32, _f64p]
     lib.lhh_export_newick.argtypes = [C.c_char_p, C.c_char_p, C.c_int32]
     lib.lhh_phylohmm_get_f64.argtypes = [C.c_void_p, C.c_char_p, _f64p, _i32p, _i32p]
     lib.lhh_phylohmm_get_i32.argtypes = [C.c_void_p, C.c_char_p, _i32p, _i32p, _i32p]

@@ -243,6 +243,8 @@ struct lh_family {
   int opt_parse_reserve = 0;  // pruning CTAs per SM given up for the parser while text is coming in (measured: no gain, the parser of a chunk runs between the pruning launches either way)
   int opt_asr_scratch_mb = 0; // lh_asr_sample: CLV scratch per chunk of trees (0 = 4096 MB)
   void* asr_cache = nullptr;  // lh_asr_sample's device pool, kept between calls (lhb::asr_cache_free)
+  int opt_text_direct = 1;    // lh_score_newick: copy text the caller holds in pinned memory in place (0: always stage it)
+  bool text_direct_call = false;  // this call's text is pinned and comes with its lengths
   int opt_newick_kernel = 0;  // 0 / 2 k_newick_cta (one CTA per tree), 1 k_newick (one thread per tree), 3 k_newick_warp (one warp per tree)
   double stage_ratio = 1.0;
   size_t rec_bytes_tree = 1;  // branch records of one tree, all categories
@@ -634,6 +636,9 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
   } else if (k == "parse_reserve") {
     if (value < 0 || value > 3) return fail("parse_reserve must be 0..3");
     f->opt_parse_reserve = (int)value;
+  } else if (k == "text_direct") {
+    if (value != 0 && value != 1) return fail("text_direct must be 0 or 1");
+    f->opt_text_direct = (int)value;
   } else if (k == "asr_scratch_mb") {
     if (value < 0) return fail("asr_scratch_mb must be >= 0 (0 = default, 4096)");
     f->opt_asr_scratch_mb = (int)value;
@@ -1171,15 +1176,8 @@ int probe_window_from_text(lh_family* f, const lh_newick_batch_t* nb, int t0, in
 
 // Copies the strings of trees [t0, t0+n) (lengths len[0..n)) into ring slot `slot` and queues their copy on `cs`
 // into the chunk's device text buffer at byte `text_at` (returns the bytes used through *used).
-// Slot layout: offs [n] uint64 (into the chunk's text buffer) | lens [n] uint32 | pad to 16 | strings, each
-// NUL-terminated and 16-byte aligned.
-int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n, const int64_t* len, int slot,
-                       char* d_chunk_text, size_t text_at, size_t* used, cudaStream_t cs) {
-  if (f->ring_busy[slot]) {
-    LH_CUDA(cudaEventSynchronize(f->ring_ev[slot]));  // the slot's previous segment has been copied
-    f->ring_busy[slot] = false;
-  }
-  const auto t_a = std::chrono::steady_clock::now();
+// The shared-memory window of the CLV stack for a text call, from the shapes of the first trees (once per call).
+int choose_window_from_text(lh_family* f, const lh_newick_batch_t* nb, int t0, int n) {
   if (!f->window_set) {
     // The window is a placement choice (results do not depend on it) made from the shapes of the first trees.
     // Parsing them on the host costs 0.16 ms per 1001-tip string, serially, in front of the call's first kernel:
@@ -1206,6 +1204,19 @@ int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n,
     }
     f->window_set = true;
   }
+  return 0;
+}
+
+// Slot layout: offs [n] uint64 (into the chunk's text buffer) | lens [n] uint32 | pad to 16 | strings, each
+// NUL-terminated and 16-byte aligned.
+int stage_text_segment(lh_family* f, const lh_newick_batch_t* nb, int t0, int n, const int64_t* len, int slot,
+                       char* d_chunk_text, size_t text_at, size_t* used, cudaStream_t cs) {
+  if (f->ring_busy[slot]) {
+    LH_CUDA(cudaEventSynchronize(f->ring_ev[slot]));  // the slot's previous segment has been copied
+    f->ring_busy[slot] = false;
+  }
+  const auto t_a = std::chrono::steady_clock::now();
+  if (choose_window_from_text(f, nb, t0, n)) return 1;
   uint8_t* base = f->h_ring[slot].as<uint8_t>();
   uint64_t* offs = reinterpret_cast<uint64_t*>(base);
   uint32_t* lens32 = reinterpret_cast<uint32_t*>(offs + n);
@@ -1262,6 +1273,23 @@ int stage_text_chunk(lh_family* f, const lh_newick_batch_t* nb, int ci, int c0, 
       return fail("tree %d: a Newick string of %lld bytes is too long", c0 + i, (long long)lens[i]);
     chunk_bytes += ((size_t)lens[i] + 1 + 15) / 16 * 16;
   }
+  // Text the caller holds in pinned memory at a constant stride (one buffer, a string every `stride` bytes - how a
+  // reader that knows the longest row lays them out, and how host.NewickBuffer does) is copied in place: one 2-D
+  // copy per chunk, `width` = the chunk's longest string, no pass of the host over the bytes. Anything else goes
+  // through the pinned ring below.
+  bool direct = f->text_direct_call && ((uintptr_t)nb->newick[c0] & 7u) == 0;
+  int64_t stride = 0;
+  size_t width = 0;
+  if (direct) {
+    int64_t maxlen = 0;
+    for (int i = 0; i < cn; ++i) maxlen = std::max(maxlen, lens[i]);
+    width = ((size_t)maxlen + 1 + 15) / 16 * 16;
+    stride = cn > 1 ? (int64_t)(nb->newick[c0 + 1] - nb->newick[c0]) : (int64_t)width;
+    if (cn == 1) width = (size_t)maxlen + 1;   // (a single string: nothing may be read behind its NUL)
+    direct = stride > 0 && (stride & 7) == 0 && (int64_t)width <= stride;
+    for (int i = 0; direct && i + 1 < cn; ++i) direct = nb->newick[c0 + i + 1] - nb->newick[c0 + i] == stride;
+    if (direct) chunk_bytes = (size_t)cn * ((width + 15) / 16 * 16);
+  }
   DevBuf& buf = f->d_textbuf[ci & 1];
   cudaStream_t ps = f->plan_stream;
   // the buffer's previous chunk (ci - 2) must have been parsed before it is overwritten - or freed
@@ -1271,7 +1299,31 @@ int stage_text_chunk(lh_family* f, const lh_newick_batch_t* nb, int ci, int c0, 
   }
   if (buf.reserve(chunk_bytes + 64)) return 1;
   size_t text_at = 0;
-  for (int i = 0; i < cn;) {
+  if (direct) {
+    const int slot = *k % lh_family::kRing;
+    if (f->ring_busy[slot]) {
+      LH_CUDA(cudaEventSynchronize(f->ring_ev[slot]));
+      f->ring_busy[slot] = false;
+    }
+    if (choose_window_from_text(f, nb, c0, cn)) return 1;
+    const size_t dpitch = (width + 15) / 16 * 16;
+    uint64_t* offs = f->h_ring[slot].as<uint64_t>();
+    uint32_t* lens32 = reinterpret_cast<uint32_t*>(offs + cn);
+    for (int i = 0; i < cn; ++i) {
+      offs[i] = (uint64_t)i * dpitch;
+      lens32[i] = (uint32_t)lens[i];
+    }
+    LH_CUDA(cudaMemcpy2DAsync(buf.as<char>(), dpitch, nb->newick[c0], (size_t)stride, width, (size_t)cn,
+                              cudaMemcpyHostToDevice, cs));
+    LH_CUDA(cudaMemcpyAsync(f->d_toffs.as<uint64_t>() + c0, offs, (size_t)cn * 8, cudaMemcpyHostToDevice, cs));
+    LH_CUDA(cudaMemcpyAsync(f->d_tlens.as<uint32_t>() + c0, lens32, (size_t)cn * 4, cudaMemcpyHostToDevice, cs));
+    LH_CUDA(cudaEventRecord(f->ring_ev[slot], cs));
+    f->ring_busy[slot] = true;
+    f->tm.h2d_bytes += (int64_t)((size_t)cn * width + (size_t)cn * 12);
+    ++f->tm.text_direct;
+    ++*k;
+  }
+  for (int i = direct ? cn : 0; i < cn;) {
     size_t bytes = 0;
     int n = 0;
     while (i + n < cn) {
@@ -1859,6 +1911,20 @@ int lh_score_newick(lh_family_t* f, const lh_newick_batch_t* nb, double* loglik,
     if (R < 1 || R > LH_MAX_RATES) return fail("n_rates %d outside 1..%d", R, LH_MAX_RATES);
     rates_buf.resize((size_t)B * R);   // filled chunk by chunk inside the pipeline (stage_chunk_rates)
   }
+  // text in pinned (or registered) host memory that comes with its lengths can be copied where it lies
+  f->text_direct_call = false;
+  if (f->opt_text_direct && nb->length && B > 0) {
+    LH_CUDA(cudaSetDevice(f->device));
+    auto pinned = [](const void* p) {
+      cudaPointerAttributes a;
+      if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+      }
+      return a.type == cudaMemoryTypeHost;
+    };
+    f->text_direct_call = pinned(nb->newick[0]) && pinned(nb->newick[B - 1] + nb->length[B - 1]);
+  }
   int rc = score_call(f, nullptr, nb, rates, loglik, o, rates ? nullptr : rates_buf.data());
   if (!rates) rates = rates_buf.data();
   f->newick_mode = false;
@@ -2129,6 +2195,19 @@ int lh_asr_sample(lh_family_t* f, const lh_asr_batch_t* a, uint8_t* node_states,
                       a->msa_codes, a->naive_row, a->naive_codes, a->seed, scratch, node_states, site_rate,
                       site_rate_loglik, &err))
     return fail("%s", err.c_str());
+  return 0;
+}
+
+// Page-lock memory the caller already holds (cudaHostRegister, portable: every device of the process may copy from
+// it): text in it is copied in place by lh_score_newick. Costs ~0.1 ms per MB once; undo with lh_unpin_host.
+int lh_pin_host(void* ptr, size_t bytes) {
+  if (!ptr || bytes == 0) return fail("lh_pin_host: null or empty range");
+  LH_CUDA(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+  return 0;
+}
+int lh_unpin_host(void* ptr) {
+  if (!ptr) return fail("lh_unpin_host: null pointer");
+  LH_CUDA(cudaHostUnregister(ptr));
   return 0;
 }
 

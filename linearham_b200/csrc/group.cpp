@@ -241,10 +241,10 @@ int lh_group_get_timings(lh_group_t* g, int m, lh_timings_t* out) {
     if (lh_get_timings(g->members[i], &t)) return grp_fail(lh_last_error());
     if (t.ms_call >= sum.ms_call) {
       const int64_t h = sum.h2d_bytes, d = sum.d2h_bytes;
-      const int l = sum.kernel_launches, pl = sum.prune_launches, n = sum.n_trees, pt = sum.pattern_trees, nh = sum.newick_host_trees;
+      const int l = sum.kernel_launches, pl = sum.prune_launches, n = sum.n_trees, pt = sum.pattern_trees, nh = sum.newick_host_trees, td = sum.text_direct;
       sum = t;
       sum.h2d_bytes = h; sum.d2h_bytes = d; sum.kernel_launches = l; sum.prune_launches = pl; sum.n_trees = n;
-      sum.pattern_trees = pt; sum.newick_host_trees = nh;
+      sum.pattern_trees = pt; sum.newick_host_trees = nh; sum.text_direct = td;
     }
     sum.h2d_bytes += t.h2d_bytes;
     sum.d2h_bytes += t.d2h_bytes;
@@ -253,6 +253,7 @@ int lh_group_get_timings(lh_group_t* g, int m, lh_timings_t* out) {
     sum.n_trees += t.n_trees;
     sum.pattern_trees += t.pattern_trees;
     sum.newick_host_trees += t.newick_host_trees;
+    sum.text_direct += t.text_direct;
   }
   *out = sum;
   return 0;

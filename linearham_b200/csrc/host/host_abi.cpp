@@ -152,6 +152,14 @@ int lhh_phylohmm_score_samples(lhh_phylohmm_t* h, int32_t n, const char* const* 
   });
 }
 
+int lhh_phylohmm_score_samples_len(lhh_phylohmm_t* h, int32_t n, const char* const* newicks, const int64_t* lengths,
+                                   const double* er, const double* pi, const double* alpha, int32_t num_rates,
+                                   double* loglik) {
+  return guarded([&] {
+    H(h).ScoreSamples(n, newicks, lengths, er, pi, alpha, num_rates, loglik);
+  });
+}
+
 int lhh_phylohmm_device_family(lhh_phylohmm_t* h, lh_family_t** out) {
   return guarded([&] { *out = H(h).device_family(); });
 }

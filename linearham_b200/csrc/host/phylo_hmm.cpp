@@ -442,12 +442,18 @@ std::vector<double> PhyloHMM::ScoreSamples(const std::vector<std::string>& newic
 // pass follow chunk by chunk while later strings are still being copied.
 void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const double* er, const double* pi, const double* alpha,
                             int num_rates, double* loglik) {
+  ScoreSamples(B, newicks, nullptr, er, pi, alpha, num_rates, loglik);
+}
+
+void PhyloHMM::ScoreSamples(int B, const char* const* newicks, const int64_t* lengths, const double* er, const double* pi,
+                            const double* alpha, int num_rates, double* loglik) {
   EnsureDeviceFamily();
   if (B <= 0) return;
   lh_newick_batch_t nb{};
   nb.n_trees = B;
   nb.n_rates = num_rates;
   nb.newick = newicks;
+  nb.length = lengths;
   nb.er = er;
   nb.pi = pi;
   nb.alpha = alpha;

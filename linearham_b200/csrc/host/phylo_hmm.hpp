@@ -187,6 +187,10 @@ class PhyloHMM : public HMM {
   // pointer form: nothing is copied; Newick ingest of one chunk overlaps the scoring of the previous one
   void ScoreSamples(int n, const char* const* newicks, const double* er, const double* pi, const double* alpha,
                     int num_rates, double* loglik);
+  // the same with the strings' lengths (a reader knows them): strings held in pinned memory, one every constant
+  // number of bytes, are then copied to the device where they lie (lh_pin_host, include/linearham_b200.h)
+  void ScoreSamples(int n, const char* const* newicks, const int64_t* lengths, const double* er, const double* pi,
+                    const double* alpha, int num_rates, double* loglik);
 
   void set_device(int device) { devices_.assign(1, device); }
   // several GPUs of the box: every batched call (ScoreSamples, RunPipeline) cuts its trees into one shard per

@@ -58,7 +58,8 @@ class NewickBuffer:
     """The trees of a flat batch as Newick text in one buffer (lhh_ops_to_newick): .ptrs is the
     (c_char_p * B) array the text entry points take, .lengths their strlen, [i] the i-th string."""
 
-    def __init__(self, tb, labels, n_threads=0):
+    def __init__(self, tb, labels, n_threads=0, pinned=False):
+        """pinned: page-lock the buffer (lh_pin_host) - the text calls then copy it to the device where it lies."""
         T, B = len(labels), int(np.asarray(tb["root_child"]).shape[0])
         lab = (C.c_char_p * T)(*[str(s).encode() for s in labels])
         stride = (max(len(str(s)) for s in labels) + 48) * 2 * T + 128
@@ -76,6 +77,21 @@ class NewickBuffer:
         for i in range(B):
             addr[i] = base + i * stride
         self.lengths = (self.buf.reshape(B, stride) == 0).argmax(axis=1).astype(np.int64) if B else np.zeros(0, dtype=np.int64)
+        self.pinned = False
+        if pinned and B:
+            from . import device
+            if device.lib().lh_pin_host(self.buf.ctypes.data, self.buf.nbytes):
+                raise HostError(device.lib().lh_last_error().decode())
+            self.pinned = True
+
+    def __del__(self):
+        if getattr(self, "pinned", False):
+            self.pinned = False
+            try:
+                from . import device
+                device.lib().lh_unpin_host(self.buf.ctypes.data)
+            except Exception:   # (interpreter shutdown: the library may be gone; the process's pages go with it)
+                pass
 
     def __len__(self):
         return self.n
@@ -232,11 +248,16 @@ class PhyloHMM:
     def ScoreSamples(self, newicks, er, pi, alpha, num_rates):
         """newicks: list of str, or a ctypes array made by encode_newicks (marshalled once, reused)."""
         n = len(newicks)
-        arr = newicks if isinstance(newicks, C.Array) else encode_newicks(newicks)
         er = np.ascontiguousarray(er, dtype=np.float64).reshape(n, 6)
         pi = np.ascontiguousarray(pi, dtype=np.float64).reshape(n, 4)
         alpha = np.ascontiguousarray(alpha, dtype=np.float64).reshape(n)
         ll = np.zeros(n)
+        if isinstance(newicks, NewickBuffer):   # the strings where they lie, with their lengths
+            _ck(self._lib.lhh_phylohmm_score_samples_len(
+                self._h, n, newicks.ptrs, newicks.lengths.ctypes.data_as(C.POINTER(C.c_int64)), er.ctypes.data_as(_abi._f64p),
+                pi.ctypes.data_as(_abi._f64p), alpha.ctypes.data_as(_abi._f64p), int(num_rates), ll.ctypes.data_as(_abi._f64p)))
+            return ll
+        arr = newicks if isinstance(newicks, C.Array) else encode_newicks(newicks)
         _ck(self._lib.lhh_phylohmm_score_samples(self._h, n, arr, er.ctypes.data_as(_abi._f64p), pi.ctypes.data_as(_abi._f64p),
                                                  alpha.ctypes.data_as(_abi._f64p), int(num_rates), ll.ctypes.data_as(_abi._f64p)))
         return ll

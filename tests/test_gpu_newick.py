@@ -292,3 +292,44 @@ def test_many_chunks_and_segments_match_the_array_path():
     assert tm["prune_launches"] >= 6 and tm["pattern_trees"] == tm_b["pattern_trees"]
     assert np.array_equal(a, b, equal_nan=True)
     assert rel_err(a[:len(nw)], exp["loglik"]) <= 1e-9
+
+
+def test_pinned_text_is_copied_in_place_and_scores_the_same():
+    """Strings the caller holds in pinned memory at a constant stride, with their lengths (host.NewickBuffer(pinned=
+    True)), go to the device with one 2-D copy per chunk instead of through the pinned ring: the same doubles, through
+    lh_score_newick and through PhyloHMM::ScoreSamples, and lh_timings_t.text_direct says which way was taken."""
+    fam, tb, exp, meta = load_golden("synth_n40")
+    labels = [str(s) for s in meta["labels"]]
+    rep = 40
+    big = {k: np.concatenate([v] * rep) for k, v in tb.items()}
+    R = tb["rates"].shape[1]
+    f = _family(fam, labels)
+    ll_arr = f.score(big)
+    for pinned in (False, True):
+        text = host.NewickBuffer(big, labels, pinned=pinned)
+        assert text.pinned == pinned
+        ll = f.score_newick(text.ptrs, big["er"], big["pi"], R, rates=big["rates"], lengths=text.lengths)
+        tm = f.timings()
+        assert np.array_equal(ll, ll_arr, equal_nan=True)
+        assert (tm["text_direct"] > 0) == pinned and tm["newick_host_trees"] == 0
+        if pinned:
+            f.set_option("text_direct", 0)
+            ll = f.score_newick(text.ptrs, big["er"], big["pi"], R, rates=big["rates"], lengths=text.lengths)
+            assert np.array_equal(ll, ll_arr, equal_nan=True) and f.timings()["text_direct"] == 0
+            f.set_option("text_direct", 1)
+            # without the lengths the strings are staged (the library would have to read them to find their ends)
+            ll = f.score_newick(text.ptrs, big["er"], big["pi"], R, rates=big["rates"])
+            assert np.array_equal(ll, ll_arr, equal_nan=True) and f.timings()["text_direct"] == 0
+            # pinned, but not at a constant stride: staged
+            order = np.arange(len(text))
+            order[[3, 7]] = order[[7, 3]]
+            ptrs = (type(text.ptrs))()
+            import ctypes as C
+            src, dst = C.cast(text.ptrs, C.POINTER(C.c_void_p)), C.cast(ptrs, C.POINTER(C.c_void_p))
+            for i, j in enumerate(order):
+                dst[i] = src[int(j)]
+            shuffled = {k: v[order] for k, v in big.items()}
+            ll = f.score_newick(ptrs, shuffled["er"], shuffled["pi"], R, rates=shuffled["rates"], lengths=text.lengths[order])
+            assert np.array_equal(ll, ll_arr[order], equal_nan=True)
+        del text
+    f.close()
