@@ -352,7 +352,11 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
     # the shard's trees as the RevBayes trace would hold them (text), written once outside the timed regions
     # (in pinned host memory - the contract's "inputs from pinned host memory": the library then copies the strings to
     # the device where they lie; --pageable-text puts them in ordinary memory, staged through the library's pinned ring)
-    text = host.NewickBuffer(shard, labels, pinned=not args.pageable_text)
+    try:
+        text = host.NewickBuffer(shard, labels, pinned=not args.pageable_text)
+    except host.HostError as e:   # (a box that refuses to page-lock that much: the text is staged instead)
+        print(f"[bench] pinning the text failed ({e}); using pageable memory", file=sys.stderr)
+        text = host.NewickBuffer(shard, labels, pinned=False)
 
     f = device.Family(fam, device=dev)
     f.set_labels(labels)
