@@ -525,7 +525,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
           if (q == a) sm.lead_word = 1;
           sm.early_runs = sm.early_runs < 2 ? sm.early_runs + 1 : 2;
         } else {
-          const int wt = word_type(last);
+          const int wt = word_type_packed(last);
           sm.n_tips += wt == K_TIP;
           last = wt;
         }
@@ -552,7 +552,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
       if (!sm.nonempty) continue;
       const int runs = (int)sm.early_runs - ((sm.lead_word && in_word) ? 1 : 0);
       if (runs >= 1) {  // a new word before the slice's first structural token: its kind follows from what came before
-        const int wt = word_type(last);
+        const int wt = word_type_packed(last);
         n_items += wt == K_TIP;
         last = wt;
       }
@@ -590,7 +590,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
         const int stc = cls == 7 ? K_NONE : cls;
         if (stc != K_NONE) {
           in_word = false;
-          if (!may_follow(last, stc)) bad = true;   // (nothing may follow ';')
+          if (!may_follow_packed(last, stc)) bad = true;   // (nothing may follow ';')
           if (stc == K_OPEN) {
             if (++depth > kCtaLevels) { bad = true; s_deep = 1; }
           } else if (stc == K_CLOSE) {
@@ -614,7 +614,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
         }
         if (!in_word) {
           in_word = true;
-          const int wt = word_type(last);
+          const int wt = word_type_packed(last);
           if (wt == K_BAD) bad = true;
           if (wt == K_TIP) {
             if (depth <= 0 || ni >= n_items) {
