@@ -480,15 +480,16 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
             synth.write_tsv(tsv_small, rows[:64])
             out_tsv = os.path.join(workdir, "lh_out.tsv")
             ours = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0, device=dev)
-            ours.RunPipeline(tsv_small, out_tsv, R, 1024)      # fresh object, seed 0: comparable with the reference's run
+            PIPE_BATCH = 256   # RunPipeline's default: rows per device call
+            ours.RunPipeline(tsv_small, out_tsv, R, PIPE_BATCH)      # fresh object, seed 0: comparable with the reference's run
             ours_small = open(out_tsv).read()
-            ours.RunPipeline(tsv_all, out_tsv, R, 1024)         # warm-up
+            ours.RunPipeline(tsv_all, out_tsv, R, PIPE_BATCH)         # warm-up
             t0 = time.perf_counter()
             for _ in range(steps):
-                ours.RunPipeline(tsv_all, out_tsv, R, 1024)
+                ours.RunPipeline(tsv_all, out_tsv, R, PIPE_BATCH)
             pipe_s = time.perf_counter() - t0
             ours.close()
-            pipe = {"value": Bs * steps / pipe_s, "unit": "rows/s", "rows_per_run": Bs, "batch_size": 1024,
+            pipe = {"value": Bs * steps / pipe_s, "unit": "rows/s", "rows_per_run": Bs, "batch_size": PIPE_BATCH,
                     "tsv_bytes": os.path.getsize(tsv_all),
                     "api": "PhyloHMM::RunPipeline (TSV in -> TSV out; reader thread | device scoring from Newick text | "
                            "SampleNaiveSequence + output line in file order, overlapped)"}

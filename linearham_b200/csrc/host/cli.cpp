@@ -49,7 +49,7 @@ const Flag kSample[] = {{"N", false, false, "1", "How many naive sequences shoul
 const Flag kPipeline[] = {
     {"input-path", true, false, "", "The RevBayes output TSV file path."},
     {"output-path", true, false, "", "The linearham output TSV file path."},
-    {"batch-size", false, false, "1024", "RevBayes samples scored per device call."},
+    {"batch-size", false, false, "256", "RevBayes samples scored per device call."},
 };
 
 class Args {

@@ -645,7 +645,11 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
         // the lines are read one after the other; their fields (15 numbers, a tree of several KB to re-export)
         // are independent and are worked on by a few threads
         lines.clear();
-        while ((int)lines.size() < batch_size) {
+        // (the first batches are short - 128 rows, then twice as many each time up to batch_size - so that the
+        // scorer and the sampler start after 128 rows have been read, not after batch_size: on a trace of a few
+        // thousand rows the fill of a three-stage pipeline is otherwise a third of the run)
+        const int want_rows = std::min<long long>(batch_size, 128LL << std::min(bi, 20));
+        while ((int)lines.size() < want_rows) {
           if (!std::getline(in, line)) { eof = true; break; }
           if (line.empty()) continue;
           lines.emplace_back(std::move(line));

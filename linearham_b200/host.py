@@ -227,7 +227,7 @@ class PhyloHMM:
         _ck(self._lib.lhh_phylohmm_sample_naive(self._h, buf, len(buf)))
         return buf.value.decode()
 
-    def RunPipeline(self, input_path, output_path, num_rates, batch_size=1024):
+    def RunPipeline(self, input_path, output_path, num_rates, batch_size=256):
         _ck(self._lib.lhh_phylohmm_run_pipeline(self._h, str(input_path).encode(), str(output_path).encode(),
                                                 int(num_rates), int(batch_size)))
 
