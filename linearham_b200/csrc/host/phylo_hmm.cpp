@@ -137,6 +137,70 @@ inline void nw_put_length(std::string& out, double v) {
   out.append(buf, r.ptr);
 }
 
+// ":number" -> ":%f" of it, appended to `out`; returns the pointer behind the number. The common spelling - up to
+// three integer digits, a point, digits - is rounded to six places on the digits themselves: "%f" rounds the exact
+// value of the nearest double, which lies within 1000 * 2^-53 = 1.2e-13 of the decimal text, so the two roundings
+// can only differ when the discarded digits are that close to a tie - they start "5" + five zeros or "4" + five
+// nines - and those (and zero, which becomes EPS, and every other spelling) take the parse-and-print path.
+inline const char* nw_copy_length(const char* p, const char* end, std::string& out) {
+  const char* q = nw_skip(p);
+  if (*q == ':') {
+    const char* b = nw_skip(q + 1);
+    const char* s = b;
+    while (*s >= '0' && *s <= '9') ++s;
+    const int ni = (int)(s - b);
+    if (ni >= 1 && ni <= 3 && (ni == 1 || *b != '0') && *s == '.') {
+      const char* f = s + 1;
+      const char* e = f;
+      while (*e >= '0' && *e <= '9') ++e;
+      const int nf = (int)(e - f);
+      if (nf >= 1 && nw_delim(*e)) {
+        bool nonzero = false;
+        for (const char* c = b; c < e && !nonzero; ++c) nonzero = *c != '0' && *c != '.';
+        bool decided = nonzero, up = false;
+        if (decided && nf > 6) {
+          const char r0 = f[6];
+          if (r0 == '4' || r0 == '5') {
+            const char near_tie = r0 == '4' ? '9' : '0';
+            bool all = true;
+            for (int k = 7; k < 12 && all; ++k) all = (k < nf ? f[k] : '0') == near_tie;
+            decided = !all;
+          }
+          up = r0 >= '5';
+        }
+        if (decided) {
+          char buf[16];
+          int n = 0;
+          buf[n++] = '0';   // room for a carry out of the integer part
+          for (int k = 0; k < ni; ++k) buf[n++] = b[k];
+          buf[n++] = '.';
+          for (int k = 0; k < 6; ++k) buf[n++] = k < nf ? f[k] : '0';
+          if (up) {
+            int k = n - 1;
+            for (;; --k) {
+              if (buf[k] == '.') continue;
+              if (buf[k] == '9') {
+                buf[k] = '0';
+              } else {
+                ++buf[k];
+                break;
+              }
+            }
+          }
+          out.push_back(':');
+          const int from = buf[0] == '0' ? 1 : 0;
+          out.append(buf + from, (std::size_t)(n - from));
+          return e;
+        }
+      }
+    }
+  }
+  double len;
+  p = nw_length(p, end, &len);
+  nw_put_length(out, len);
+  return p;
+}
+
 }  // namespace
 
 std::string ExportNewick(const std::string& newick) {
@@ -159,9 +223,7 @@ std::string ExportNewick(const std::string& newick) {
       while (!nw_delim(*p)) ++p;
       if (p == b) throw std::invalid_argument("empty tip label in Newick string");
       out.append(b, p);
-      double len;
-      p = nw_length(p, end, &len);
-      nw_put_length(out, len);
+      p = nw_copy_length(p, end, out);
       if (kids.empty()) return out;  // a single tip
       ++kids.back();
       want_item = false;
@@ -176,16 +238,16 @@ std::string ExportNewick(const std::string& newick) {
       const char* b = p;
       while (!nw_delim(*p)) ++p;
       out.append(b, p);
-      double len;
-      p = nw_length(p, end, &len);
+      const std::size_t before_length = out.size();
+      p = nw_copy_length(p, end, out);   // (read first, as before: a malformed length is reported before the shape)
       const bool top = kids.size() == 1;
       if (kids.back() != (top ? 3 : 2)) throw std::invalid_argument("Newick tree is not an unrooted binary tree");
       kids.pop_back();
       if (top) {
+        out.resize(before_length);       // a length on the trifurcation is dropped
         out.append(":0.0;");
         return out;
       }
-      nw_put_length(out, len);
       ++kids.back();
     } else {
       throw std::invalid_argument("unbalanced Newick string");
