@@ -225,34 +225,27 @@ __global__ void __launch_bounds__(32) k_newick(NewickDev p) {
 //   S3  every thread lexes its slice again, now exactly: checks the token grammar and records one item per node
 //       (tip: where its label starts; ')': where it ends, which operation it is) with its depth, in text order;
 //   S5  one thread per node: label -> xMSA row (hash table), branch length -> double (Eisel-Lemire);
-//   S6  thread 0 walks the items once: a tip or a finished node is filed under its level, a ')' takes the two
-//       filed under its level as its children - the stack of the sequential parser, indexed by the depth S3 knows.
+//   S6  children to parents, in parallel (link_items below): a tip or a finished node is filed under its level, a ')'
+//       takes the two filed under its level as its children - the stack of the sequential parser, indexed by the
+//       depth S3 knows, and resolved with stable ranks per level instead of a walk.
 // The grammar accepted here is the strict one - '(' item ',' item [',' item] ')' [label] [':' number], ';' at depth
 // 0, nothing after it; every other spelling the lenient host parser takes (missing commas, text after ';', ...)
 // is left to it, like everything else this kernel does not decide.
 enum : int { K_NONE = 0, K_OPEN, K_CLOSE, K_COMMA, K_COLON, K_SEMI, K_TIP, K_NUM, K_INNER, K_BAD };
 
+// The kind of a word follows from the token before it, and which tokens may come before a structural token is a
+// 5 x 10 table; both are looked up for every character, as shifts of 64-bit constants (written as chained
+// comparisons they were 15 % of the kernel's instructions).
+//   word after '(' or ','  -> tip label;  after ':' -> number;  after ')' -> inner label;  anything else -> K_BAD
 __device__ __forceinline__ int word_type(int last) {
-  return (last == K_OPEN || last == K_COMMA) ? K_TIP : last == K_COLON ? K_NUM : last == K_CLOSE ? K_INNER : K_BAD;
-}
-// which tokens may come before a structural token
-__device__ __forceinline__ bool may_follow(int prev, int cur) {
-  constexpr unsigned after_node = (1u << K_TIP) | (1u << K_NUM) | (1u << K_CLOSE) | (1u << K_INNER);
-  unsigned ok = 0;
-  if (cur == K_OPEN) ok = (1u << K_NONE) | (1u << K_OPEN) | (1u << K_COMMA);
-  else if (cur == K_CLOSE || cur == K_COMMA) ok = after_node;
-  else if (cur == K_COLON) ok = (1u << K_TIP) | (1u << K_INNER) | (1u << K_CLOSE);
-  else if (cur == K_SEMI) ok = (1u << K_CLOSE) | (1u << K_INNER) | (1u << K_NUM);
-  return (ok >> prev) & 1u;
-}
-// the same two tables packed into constants (k_newick_warp looks them up for every character)
-__device__ __forceinline__ int word_type_packed(int last) {
   constexpr unsigned long long tbl = (unsigned long long)K_BAD * 0x1111111111ull                       // ten entries of four bits
       ^ ((unsigned long long)(K_BAD ^ K_TIP) << (4 * K_OPEN)) ^ ((unsigned long long)(K_BAD ^ K_TIP) << (4 * K_COMMA))
       ^ ((unsigned long long)(K_BAD ^ K_NUM) << (4 * K_COLON)) ^ ((unsigned long long)(K_BAD ^ K_INNER) << (4 * K_CLOSE));
   return (int)((tbl >> (4 * last)) & 15ull);
 }
-__device__ __forceinline__ bool may_follow_packed(int prev, int cur) {   // cur: K_OPEN..K_SEMI
+//   '(' after nothing, '(' or ',';  ')' and ',' after a node (tip, number, ')', inner label);  ':' after a tip, an
+//   inner label or ')';  ';' after ')', an inner label or a number;  nothing after ';'
+__device__ __forceinline__ bool may_follow(int prev, int cur) {   // cur: K_OPEN..K_SEMI
   constexpr unsigned long long after_node = (1u << K_TIP) | (1u << K_NUM) | (1u << K_CLOSE) | (1u << K_INNER);
   constexpr unsigned long long tbl =
       ((unsigned long long)((1u << K_NONE) | (1u << K_OPEN) | (1u << K_COMMA)) << (10 * (K_OPEN - 1))) |
@@ -525,7 +518,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
           if (q == a) sm.lead_word = 1;
           sm.early_runs = sm.early_runs < 2 ? sm.early_runs + 1 : 2;
         } else {
-          const int wt = word_type_packed(last);
+          const int wt = word_type(last);
           sm.n_tips += wt == K_TIP;
           last = wt;
         }
@@ -552,7 +545,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
       if (!sm.nonempty) continue;
       const int runs = (int)sm.early_runs - ((sm.lead_word && in_word) ? 1 : 0);
       if (runs >= 1) {  // a new word before the slice's first structural token: its kind follows from what came before
-        const int wt = word_type_packed(last);
+        const int wt = word_type(last);
         n_items += wt == K_TIP;
         last = wt;
       }
@@ -590,7 +583,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
         const int stc = cls == 7 ? K_NONE : cls;
         if (stc != K_NONE) {
           in_word = false;
-          if (!may_follow_packed(last, stc)) bad = true;   // (nothing may follow ';')
+          if (!may_follow(last, stc)) bad = true;   // (nothing may follow ';')
           if (stc == K_OPEN) {
             if (++depth > kCtaLevels) { bad = true; s_deep = 1; }
           } else if (stc == K_CLOSE) {
@@ -614,7 +607,7 @@ __global__ void __launch_bounds__(NT, 12) k_newick_cta(NewickDev p) {
         }
         if (!in_word) {
           in_word = true;
-          const int wt = word_type_packed(last);
+          const int wt = word_type(last);
           if (wt == K_BAD) bad = true;
           if (wt == K_TIP) {
             if (depth <= 0 || ni >= n_items) {
@@ -763,7 +756,7 @@ __global__ void __launch_bounds__(32, 24) k_newick_warp(NewickDev p) {
       const int st_prev = __shfl_sync(FULL, st, pidx);
       const bool word_start = (WS >> lane) & 1u;
       int tok = st;
-      if (word_start) tok = below ? word_type_packed(st_prev) : word_type_packed(last);   // (after a word: K_BAD)
+      if (word_start) tok = below ? word_type(st_prev) : word_type(last);   // (after a word: K_BAD)
       const int tok_prev = __shfl_sync(FULL, tok, pidx);
       const int prev = below ? tok_prev : last;
       const bool is_tip = word_start && tok == K_TIP;
@@ -771,7 +764,7 @@ __global__ void __launch_bounds__(32, 24) k_newick_warp(NewickDev p) {
       const int d = depth + __popc(MO & lt) - __popc(MC & lt);   // the depth in front of my character
       const int my = ni + __popc(IT & lt);
       if (st != K_NONE) {
-        if (!may_follow_packed(prev, st)) bad = true;   // (nothing may follow ';')
+        if (!may_follow(prev, st)) bad = true;   // (nothing may follow ';')
         if (st == K_OPEN) {
           if (d + 1 > kCtaLevels) { bad = true; deep = true; }
         } else if (st == K_SEMI) {
