@@ -226,6 +226,19 @@ typedef struct lh_asr_batch {
 int lh_asr_sample(lh_family_t* fam, const lh_asr_batch_t* batch, uint8_t* node_states, uint8_t* site_rate,
                   double* site_rate_loglik);
 
+/* The random draws of HMM::SampleNaiveSequence (src/HMM.cpp:323-341, 1222-1353) for every tree of the batch the
+ * handle scored last, on the device: the J gene, the D-J junction states from the last site to the first, the D gene,
+ * the V-D junction states, the V gene - each a std::discrete_distribution draw over (transition column of the state
+ * drawn before) x (forward row), reproduced operation by operation as libstdc++ computes it. The forward tables must
+ * still be on the device: set option "keep_tables" = 1 before the scoring call (or request them as read-outs).
+ * words [B][n_words]: the raw 32-bit outputs of the run's std::mt19937 in the order the draws consume them - two per
+ * draw over two or more weights, so n_words = 2 * (1 + dj_sites + 1 + vd_sites + 1) for a heavy chain with more than
+ * one candidate everywhere; the call checks the count. idx [B][n_idx]: J gene | D-J states (site 0 first) | D gene |
+ * V-D states | V gene (light chains: J gene | V-J states | V gene). flags [B]: 1 where the tree must be sampled by
+ * the host code instead (a non-finite forward entry, weights that do not sum to a positive finite number).        */
+int lh_sample_paths(lh_family_t* fam, int32_t n_trees, const uint32_t* words, int32_t n_words, int32_t* idx,
+                    int32_t n_idx, uint8_t* flags);
+
 /* Page-lock a range of the caller's own memory for every device of the process (cudaHostRegister). Newick text
  * that lh_score_newick finds in pinned memory, with its lengths given and one string every constant number of bytes
  * (8-byte aligned), is copied to the device where it lies - one 2-D copy per chunk, no staging pass of the host over

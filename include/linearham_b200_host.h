@@ -70,6 +70,9 @@ int lhh_phylohmm_set_devices(lhh_phylohmm_t* h, const int32_t* devices, int32_t 
 /* Host threads this object may use (Newick ingest and traversal planning); 0 = all hardware threads.
  * A job with several ranks per node gives each rank its share. */
 int lhh_phylohmm_set_host_threads(lhh_phylohmm_t* h, int32_t n_threads);
+/* run_pipeline: 1 (default) = the states of every row's annotation are drawn on the device from the forward tables
+ * left there (lh_sample_paths; one device only), 0 = by the host's SampleNaiveSequence; the output is the same.   */
+int lhh_phylohmm_set_device_sampler(lhh_phylohmm_t* h, int32_t on);
 /* The flat family description for lh_family_create; pointers live as long as the handle. */
 int lhh_phylohmm_family_desc(lhh_phylohmm_t* h, struct lh_family_desc* out);
 /* InitializePhyloParameters(newick_path, er, pi, alpha, num_rates) - src/PhyloHMM.cpp:350-361 */

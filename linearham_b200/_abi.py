@@ -196,7 +196,7 @@ DEVICE_SYMBOLS = [
     "lh_loglik_dev", "lh_get_timings", "lh_set_option", "lh_measure_fp64_peak",
     "lh_timer_mark", "lh_timer_elapsed_ms", "lh_family_rebind", "lh_debug_fetch_plan",
     "lh_family_set_labels", "lh_score_newick", "lh_debug_parse_newick", "lh_newick_parse_noalloc",
-    "lh_newick_parse_noalloc_max_trees", "lh_asr_sample", "lh_pin_host", "lh_unpin_host",
+    "lh_newick_parse_noalloc_max_trees", "lh_asr_sample", "lh_pin_host", "lh_unpin_host", "lh_sample_paths",
     "lh_group_create", "lh_group_destroy", "lh_group_size", "lh_group_member", "lh_group_set_labels", "lh_group_set_option",
     "lh_group_score_batch", "lh_group_score_newick", "lh_group_get_timings", "lh_group_last_error", "lh_parse_devices",
     "lh_repertoire_create_multi", "lh_repertoire_create", "lh_repertoire_score", "lh_repertoire_destroy", "lh_repertoire_set_option", "lh_repertoire_last_error",
@@ -295,7 +295,7 @@ def bind_host(lib):
     return lib
 
 
-HOST_SYMBOLS += ["lhh_phylohmm_new", "lhh_phylohmm_free", "lhh_phylohmm_set_device", "lhh_phylohmm_set_devices", "lhh_phylohmm_set_host_threads", "lhh_phylohmm_family_desc",
+HOST_SYMBOLS += ["lhh_phylohmm_new", "lhh_phylohmm_free", "lhh_phylohmm_set_device", "lhh_phylohmm_set_devices", "lhh_phylohmm_set_host_threads", "lhh_phylohmm_set_device_sampler", "lhh_phylohmm_family_desc",
                  "lhh_phylohmm_init_params", "lhh_phylohmm_init_emission", "lhh_phylohmm_loglikelihood",
                  "lhh_phylohmm_sample_naive", "lhh_phylohmm_run_pipeline", "lhh_phylohmm_score_samples", "lhh_phylohmm_score_samples_len", "lhh_phylohmm_device_family",
                  "lhh_export_newick", "lhh_phylohmm_get_f64", "lhh_phylohmm_get_i32", "lhh_phylohmm_get_str"]
@@ -310,6 +310,7 @@ def bind_phylohmm(lib):
     lib.lhh_phylohmm_set_devices.argtypes = [C.c_void_p, _i32p, C.c_int32]
     lib.lhh_phylohmm_device_family.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
     lib.lhh_phylohmm_set_host_threads.argtypes = [C.c_void_p, C.c_int32]
+    lib.lhh_phylohmm_set_device_sampler.argtypes = [C.c_void_p, C.c_int32]
     lib.lhh_phylohmm_family_desc.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
     lib.lhh_phylohmm_init_params.argtypes = [C.c_void_p, C.c_char_p, _f64p, _f64p, C.c_double, C.c_int32]
     lib.lhh_phylohmm_init_emission.argtypes = [C.c_void_p]

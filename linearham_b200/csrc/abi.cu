@@ -243,6 +243,8 @@ struct lh_family {
   int opt_parse_reserve = 0;  // pruning CTAs per SM given up for the parser while text is coming in (measured: no gain, the parser of a chunk runs between the pruning launches either way)
   int opt_asr_scratch_mb = 0; // lh_asr_sample: CLV scratch per chunk of trees (0 = 4096 MB)
   void* asr_cache = nullptr;  // lh_asr_sample's device pool, kept between calls (lhb::asr_cache_free)
+  int opt_keep_tables = 0;    // forward tables stay on the device after a run although nobody fetches them (lh_sample_paths)
+  DevBuf d_words, d_sidx, d_sflag;   // lh_sample_paths: raw generator outputs in, drawn indices and flags out
   int opt_text_direct = 1;    // lh_score_newick: copy text the caller holds in pinned memory in place (0: always stage it)
   bool text_direct_call = false;  // this call's text is pinned and comes with its lengths
   int opt_newick_kernel = 0;  // 0 / 2 k_newick_cta (one CTA per tree), 1 k_newick (one thread per tree), 3 k_newick_warp (one warp per tree)
@@ -300,7 +302,7 @@ void lh_family_destroy(lh_family_t* f) {
                     &f->cols[1].d_codes_t, &f->d_ebuf, &f->d_ecnt, &f->d_enaive, &f->d_list, &f->d_counters,
                     &f->d_rate_ll, &f->d_rchildren, &f->d_rblen, &f->d_rroot_child, &f->d_rroot_blen, &f->d_flags,
                     &f->d_label_slots, &f->d_label_off, &f->d_label_chars, &f->d_textbuf[0], &f->d_textbuf[1], &f->d_items, &f->d_toffs, &f->d_tlens,
-                    &f->d_on_pat, &f->d_nw_status, &f->d_chunk_npat};
+                    &f->d_on_pat, &f->d_nw_status, &f->d_chunk_npat, &f->d_words, &f->d_sidx, &f->d_sflag};
   for (DevBuf* b : bufs) b->release();
   lhb::asr_cache_free(f->asr_cache);
   f->asr_cache = nullptr;
@@ -636,6 +638,9 @@ int lh_set_option(lh_family_t* f, const char* key, int64_t value) {
   } else if (k == "parse_reserve") {
     if (value < 0 || value > 3) return fail("parse_reserve must be 0..3");
     f->opt_parse_reserve = (int)value;
+  } else if (k == "keep_tables") {
+    if (value != 0 && value != 1) return fail("keep_tables must be 0 or 1");
+    f->opt_keep_tables = (int)value;
   } else if (k == "text_direct") {
     if (value != 0 && value != 1) return fail("text_direct must be 0 or 1");
     f->opt_text_direct = (int)value;
@@ -1763,8 +1768,9 @@ namespace {
 // are the category rates of its trees). Host buffers in, host results out.
 int score_call(lh_family* f, const lh_tree_batch_t* tb, const lh_newick_batch_t* nb, const double* rates,
                double* loglik, lh_outputs_t* o, double* lazy_rates = nullptr) {  // lazy_rates: [B][R] to fill from nb->alpha
-  f->want_tables = o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
-                         o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers);
+  f->want_tables = f->opt_keep_tables ||
+                   (o && (o->vgerm_forward || o->vd_forward || o->dgerm_forward || o->dj_forward ||
+                          o->jgerm_forward || o->germ_scalers || o->vd_scalers || o->dj_scalers));
   f->want_rate_ll = o && o->site_rate_loglik;
   LH_CUDA(cudaSetDevice(f->device));
   const auto call_t0 = std::chrono::steady_clock::now();
@@ -2199,6 +2205,41 @@ int lh_asr_sample(lh_family_t* f, const lh_asr_batch_t* a, uint8_t* node_states,
                       a->msa_codes, a->naive_row, a->naive_codes, a->seed, scratch, node_states, site_rate,
                       site_rate_loglik, &err))
     return fail("%s", err.c_str());
+  return 0;
+}
+
+// The index draws of SampleNaiveSequence for every tree of the batch scored last (k_sample), from the forward tables
+// that run left on the device (option "keep_tables", or read-outs requested from it).
+int lh_sample_paths(lh_family_t* f, int32_t n_trees, const uint32_t* words, int32_t n_words, int32_t* idx, int32_t n_idx,
+                    uint8_t* flags) {
+  if (!f || !words || !idx || !flags) return fail("null argument");
+  if (!f->bound) return fail("no family bound to the handle");
+  if (!f->want_tables || f->B != n_trees)
+    return fail("lh_sample_paths: the last run of the handle did not keep the forward tables of %d trees (option keep_tables)", n_trees);
+  const lhb::FamilyDev& fd = f->fd;
+  auto draw_words = [](int n_weights, int calls) { return n_weights >= 2 ? 2 * calls : 0; };
+  int want_words = draw_words(fd.n_j, 1) + draw_words(fd.vd_states, fd.vd_sites) + draw_words(fd.n_v, 1);
+  int want_idx = 2 + fd.vd_sites;
+  if (fd.has_d) {
+    want_words += draw_words(fd.dj_states, fd.dj_sites) + draw_words(fd.n_d, 1);
+    want_idx += 1 + fd.dj_sites;
+  }
+  if (n_words != want_words || n_idx != want_idx)
+    return fail("lh_sample_paths: this family draws %d generator outputs and %d indices per tree (got %d, %d)", want_words,
+                want_idx, n_words, n_idx);
+  if (n_trees == 0) return 0;
+  LH_CUDA(cudaSetDevice(f->device));
+  const size_t B = (size_t)n_trees;
+  if (f->d_words.reserve(B * std::max(n_words, 1) * 4) || f->d_sidx.reserve(B * n_idx * 4) || f->d_sflag.reserve(B)) return 1;
+  cudaStream_t s = f->stream;
+  if (n_words) LH_CUDA(cudaMemcpyAsync(f->d_words.p, words, B * n_words * 4, cudaMemcpyHostToDevice, s));
+  lhb::launch_sample(fd, f->d_vgerm.as<double>(), f->d_vd.as<double>(), f->d_dgerm.as<double>(), f->d_dj.as<double>(),
+                     f->d_jgerm.as<double>(), f->d_words.as<uint32_t>(), n_words, f->d_sidx.as<int32_t>(), n_idx,
+                     f->d_sflag.as<uint8_t>(), n_trees, s);
+  LH_CUDA(cudaGetLastError());
+  LH_CUDA(cudaMemcpyAsync(idx, f->d_sidx.p, B * n_idx * 4, cudaMemcpyDeviceToHost, s));
+  LH_CUDA(cudaMemcpyAsync(flags, f->d_sflag.p, B, cudaMemcpyDeviceToHost, s));
+  LH_CUDA(cudaStreamSynchronize(s));
   return 0;
 }
 

@@ -256,19 +256,25 @@ void SampleJunctionStates(int germ_state_ind, const MatrixXd& junction_germ_T, c
                           const MatrixXd& junction_T, char left_gtype, char right_gtype, int site_start,
                           const std::string& alphabet, std::mt19937& rng, std::discrete_distribution<int>& distr,
                           std::string& naive, int& germ_left_del, std::vector<std::string>& strs, std::vector<int>& inds,
-                          std::string& insertion, int& germ_right_del) {
-  const int L = J.forward.rows(), S = J.forward.cols();
+                          std::string& insertion, int& germ_right_del, const int32_t* preset = nullptr) {
+  // preset: the states drawn elsewhere (k_sample, lh_sample_paths), site 0 first - everything but the draws runs here
+  const int L = preset ? J.xmsa_inds.rows() : J.forward.rows(), S = preset ? 0 : J.forward.cols();
   strs.assign(L, "");
   inds.assign(L, -1);
   insertion.clear();
   germ_right_del = -1;
   std::vector<double> probs(S);
   for (int i = L - 1; i >= 0; --i) {
-    const double* column = (i == L - 1) ? junction_germ_T.data() + (std::size_t)germ_state_ind * junction_germ_T.rows()
-                                        : junction_T.data() + (std::size_t)inds[i + 1] * junction_T.rows();
-    for (int j = 0; j < S; ++j) probs[j] = column[j] * J.forward(i, j);
-    distr.param(std::discrete_distribution<int>::param_type(probs.begin(), probs.end()));
-    const int k = distr(rng);
+    int k;
+    if (preset) {
+      k = preset[i];
+    } else {
+      const double* column = (i == L - 1) ? junction_germ_T.data() + (std::size_t)germ_state_ind * junction_germ_T.rows()
+                                          : junction_T.data() + (std::size_t)inds[i + 1] * junction_T.rows();
+      for (int j = 0; j < S; ++j) probs[j] = column[j] * J.forward(i, j);
+      distr.param(std::discrete_distribution<int>::param_type(probs.begin(), probs.end()));
+      k = distr(rng);
+    }
     inds[i] = k;
     strs[i] = J.state_strs[k];
     naive[site_start + i] = alphabet[J.naive_bases[k]];
@@ -283,13 +289,18 @@ void SampleJunctionStates(int germ_state_ind, const MatrixXd& junction_germ_T, c
 
 void SampleGermlineState(const std::vector<int>& junction_inds, const MatrixXd& germ_junction_T, const GermlineRegion& G,
                          const std::string& alphabet, std::mt19937& rng, std::discrete_distribution<int>& distr,
-                         std::string& naive, std::string& str, int& ind, int& left_del, int& right_del) {
-  const int n = (int)G.state_strs.size();
-  std::vector<double> probs(n);
-  const double* column = germ_junction_T.data() + (std::size_t)junction_inds.front() * germ_junction_T.rows();
-  for (int j = 0; j < n; ++j) probs[j] = column[j] * G.forward[j];
-  distr.param(std::discrete_distribution<int>::param_type(probs.begin(), probs.end()));
-  ind = distr(rng);
+                         std::string& naive, std::string& str, int& ind, int& left_del, int& right_del,
+                         const int32_t* preset = nullptr) {
+  if (preset) {
+    ind = *preset;
+  } else {
+    const int n = (int)G.state_strs.size();
+    std::vector<double> probs(n);
+    const double* column = germ_junction_T.data() + (std::size_t)junction_inds.front() * germ_junction_T.rows();
+    for (int j = 0; j < n; ++j) probs[j] = column[j] * G.forward[j];
+    distr.param(std::discrete_distribution<int>::param_type(probs.begin(), probs.end()));
+    ind = distr(rng);
+  }
   str = G.state_strs[ind];
   left_del = G.left_del[ind];
   if (right_del == -1) right_del = G.right_del[ind];
@@ -395,9 +406,13 @@ void HMM::InitializeTransition() {
 }
 
 // src/HMM.cpp:323-341
-void HMM::SampleInitialState() {
-  distr_.param(std::discrete_distribution<int>::param_type(jgerm_.forward.begin(), jgerm_.forward.end()));
-  jgerm_state_ind_samp_ = distr_(rng_);
+void HMM::SampleInitialState(const int32_t* preset) {
+  if (preset) {
+    jgerm_state_ind_samp_ = *preset;
+  } else {
+    distr_.param(std::discrete_distribution<int>::param_type(jgerm_.forward.begin(), jgerm_.forward.end()));
+    jgerm_state_ind_samp_ = distr_(rng_);
+  }
   jgerm_state_str_samp_ = jgerm_.state_strs[jgerm_state_ind_samp_];
   jgerm_left_del_samp_ = jgerm_.left_del[jgerm_state_ind_samp_];
   jgerm_right_del_samp_ = jgerm_.right_del[jgerm_state_ind_samp_];
@@ -411,29 +426,51 @@ std::string HMM::SampleNaiveSequence() {
     RunForwardAlgorithm();
     cache_forward_ = false;
   }
+  return SamplePath(nullptr);
+}
+
+// The annotation of a path whose states were drawn elsewhere (k_sample through lh_sample_paths): J gene | D-J states,
+// site 0 first | D gene | V-D states | V gene (light chains: J gene | V-J states | V gene). The forward tables are not
+// read; everything SampleNaiveSequence derives from the drawn states is derived here by the same code.
+std::string HMM::ApplySampledPath(const int32_t* idx) { return SamplePath(idx); }
+
+std::string HMM::SamplePath(const int32_t* idx) {
+  const int32_t* jgerm_idx = idx;
+  const int32_t *dj_idx = nullptr, *dgerm_idx = nullptr, *vd_idx = nullptr, *vgerm_idx = nullptr;
+  if (idx) {
+    const int32_t* p = idx + 1;
+    if (locus_ == "igh") {
+      dj_idx = p;
+      p += dj_junction_.xmsa_inds.rows();
+      dgerm_idx = p++;
+    }
+    vd_idx = p;
+    p += vd_junction_.xmsa_inds.rows();
+    vgerm_idx = p;
+  }
   naive_seq_samp_.assign(msa_.cols(), 'N');
-  SampleInitialState();
+  SampleInitialState(jgerm_idx);
   if (locus_ == "igh") {
     SampleJunctionStates(jgerm_state_ind_samp_, dj_junction_jgerm_transition_, dj_junction_, dj_junction_transition_, 'D', 'J',
                          flexbounds_.at("d_r").first, alphabet_, rng_, distr_, naive_seq_samp_, jgerm_left_del_samp_,
                          dj_junction_state_str_samps_, dj_junction_state_ind_samps_, dj_junction_insertion_samp_,
-                         dgerm_right_del_samp_);
+                         dgerm_right_del_samp_, dj_idx);
     SampleGermlineState(dj_junction_state_ind_samps_, dgerm_dj_junction_transition_, dgerm_, alphabet_, rng_, distr_,
                         naive_seq_samp_, dgerm_state_str_samp_, dgerm_state_ind_samp_, dgerm_left_del_samp_,
-                        dgerm_right_del_samp_);
+                        dgerm_right_del_samp_, dgerm_idx);
     SampleJunctionStates(dgerm_state_ind_samp_, vd_junction_dgerm_transition_, vd_junction_, vd_junction_transition_, 'V', 'D',
                          flexbounds_.at("v_r").first, alphabet_, rng_, distr_, naive_seq_samp_, dgerm_left_del_samp_,
                          vd_junction_state_str_samps_, vd_junction_state_ind_samps_, vd_junction_insertion_samp_,
-                         vgerm_right_del_samp_);
+                         vgerm_right_del_samp_, vd_idx);
   } else {
     SampleJunctionStates(jgerm_state_ind_samp_, vd_junction_dgerm_transition_, vd_junction_, vd_junction_transition_, 'V', 'J',
                          flexbounds_.at("v_r").first, alphabet_, rng_, distr_, naive_seq_samp_, jgerm_left_del_samp_,
                          vd_junction_state_str_samps_, vd_junction_state_ind_samps_, vd_junction_insertion_samp_,
-                         vgerm_right_del_samp_);
+                         vgerm_right_del_samp_, vd_idx);
   }
   SampleGermlineState(vd_junction_state_ind_samps_, vgerm_vd_junction_transition_, vgerm_, alphabet_, rng_, distr_,
                       naive_seq_samp_, vgerm_state_str_samp_, vgerm_state_ind_samp_, vgerm_left_del_samp_,
-                      vgerm_right_del_samp_);
+                      vgerm_right_del_samp_, vgerm_idx);
   // V / J framework insertions: the leading and trailing runs of N around a run of alphabet
   // bases (GetFrameworkInsertionRegex, src/utils.cpp:97-99: ^(N*)[ACGT]+(N*)$)
   vgerm_left_insertion_samp_.clear();

@@ -113,6 +113,10 @@ int lhh_phylohmm_set_host_threads(lhh_phylohmm_t* h, int32_t n_threads) {
   return guarded([&] { H(h).set_host_threads(n_threads); });
 }
 
+int lhh_phylohmm_set_device_sampler(lhh_phylohmm_t* h, int32_t on) {
+  return guarded([&] { H(h).set_device_sampler(on != 0); });
+}
+
 int lhh_phylohmm_family_desc(lhh_phylohmm_t* h, lh_family_desc_t* out) {
   return guarded([&] { *out = H(h).family_desc(); });
 }

@@ -17,6 +17,7 @@
 #include <sstream>
 #include <stdexcept>
 
+#include "../pool.hpp"
 #include "../../../include/linearham_b200.h"
 #include "../../../include/linearham_b200_host.h"
 
@@ -603,6 +604,12 @@ struct PipeBatch {
   std::string err;          // a stage's failure, reported by the sampler in file order
   bool err_is_input = false;
   int state = 0;            // 0 free, 1 read, 2 scored
+  // the draws of the rows' annotations made on the device (lh_sample_paths), or where the run's generator stood
+  // before the batch for the host sampler
+  std::vector<int32_t> idx;
+  std::vector<uint8_t> sflag;
+  std::mt19937 rng_start;
+  bool device_sampled = false;
 };
 
 // A copy of what SampleNaiveSequence reads and writes - state space, transitions, forward tables, the sampled
@@ -669,6 +676,20 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
   const lh_family_desc_t& d = flat_->desc;
   const std::size_t vd_n = (std::size_t)d.vd_sites * d.vd_states, dj_n = (std::size_t)d.dj_sites * d.dj_states;
   sr_.assign(num_rates, 0.0);
+  // The draws of SampleNaiveSequence are made on the device, from the forward tables k_hmm leaves there
+  // (lh_sample_paths), when the run is on one device: the host then only turns the drawn states into the annotation
+  // strings, and the tables (53 KB per row at the benchmark shapes) stay where they are. The one generator of the
+  // run is advanced by the scorer thread in file order - a fixed number of raw outputs per row - and handed back at
+  // the end. LH_HOST_SAMPLER=1 (or several devices) keeps the host sampler.
+  const unsigned long long words_per_row = rng_outputs_per_row(d);
+  const int n_idx = 2 + d.vd_sites + (d.has_d ? 1 + d.dj_sites : 0);
+  const bool dev_sampler = !dev_group_ && device_sampler_ && words_per_row > 0 && !std::getenv("LH_HOST_SAMPLER");
+  std::mt19937 run_gen = rng_;
+  if (dev_sampler && lh_set_option(dev_family_, "keep_tables", 1)) throw std::runtime_error(lh_last_error());
+  struct KeepTablesOff {
+    lh_family* f;
+    ~KeepTablesOff() { if (f) lh_set_option(f, "keep_tables", 0); }
+  } keep_tables_off{dev_sampler ? dev_family_ : nullptr};
 
   constexpr int kRing = 3;
   PipeBatch ring[kRing];
@@ -692,11 +713,53 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
   // ---- reader -----------------------------------------------------------------------------------------------
   double ms_reader = 0.0, ms_scorer = 0.0, ms_sampler = 0.0;   // busy time of the three stages (LH_TRACE)
   const int hw = host_threads_ > 0 ? host_threads_ : (int)std::max(1u, std::thread::hardware_concurrency());
-  const int reader_threads = std::max(1, hw / 2);
+  auto env_int = [](const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    return v && *v ? std::max(1, std::atoi(v)) : dflt;
+  };
+  // (with the draws on the device the rows' TSV fields and tree export are most of the host's work: the reader gets
+  // three quarters of the threads, the writer of the output lines a quarter; with the host sampler half and half)
+  const int reader_threads = env_int("LH_READER_THREADS", std::max(1, dev_sampler ? hw * 3 / 4 : hw / 2));
+  const int sampler_threads = env_int("LH_SAMPLER_THREADS", std::max(1, std::min(dev_sampler ? hw / 4 : hw / 2, 16)));
+  // (persistent workers for the two host stages: a thread created and joined per batch of 256 rows costs as much as
+  // a few rows)
+  lhb::WorkerPool reader_pool(std::min(reader_threads, 16) - 1), writer_pool(std::max(1, sampler_threads) - 1);
   std::thread reader([&] {
     std::string line;
     std::vector<std::string> lines;
     bool eof = false;
+    // the file comes in blocks of 4 MB and is cut at the newlines with memchr (std::getline on the stream moved a
+    // 9 KB row at about 1 GB/s on one thread - as long as all the other work of the row on eight)
+    std::string pending;
+    std::size_t ppos = 0;
+    bool file_end = false;
+    constexpr std::size_t kReadBlock = (std::size_t)4 << 20;
+    auto next_line = [&](std::string& out) -> bool {
+      for (;;) {
+        const char* base = pending.data();
+        const void* nl = ppos < pending.size() ? std::memchr(base + ppos, '\n', pending.size() - ppos) : nullptr;
+        if (nl) {
+          const std::size_t e = (std::size_t)(static_cast<const char*>(nl) - base);
+          out.assign(base + ppos, e - ppos);
+          ppos = e + 1;
+          return true;
+        }
+        if (file_end) {
+          if (ppos >= pending.size()) return false;
+          out.assign(base + ppos, pending.size() - ppos);   // a last line without a newline
+          ppos = pending.size();
+          return true;
+        }
+        pending.erase(0, ppos);
+        ppos = 0;
+        const std::size_t old = pending.size();
+        pending.resize(old + kReadBlock);
+        in.read(&pending[old], (std::streamsize)kReadBlock);
+        const std::size_t got = (std::size_t)in.gcount();
+        pending.resize(old + got);
+        if (got < kReadBlock) file_end = true;
+      }
+    };
     for (int bi = 0; !eof; ++bi) {
       PipeBatch& b = ring[bi % kRing];
       if (!wait_for(b, 0)) return;
@@ -712,7 +775,7 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
         // thousand rows the fill of a three-stage pipeline is otherwise a third of the run)
         const int want_rows = std::min<long long>(batch_size, 128LL << std::min(bi, 20));
         while ((int)lines.size() < want_rows) {
-          if (!std::getline(in, line)) { eof = true; break; }
+          if (!next_line(line)) { eof = true; break; }
           if (line.empty()) continue;
           lines.emplace_back(std::move(line));
         }
@@ -745,10 +808,8 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
           }
         };
         const int n_workers = std::max(1, std::min({reader_threads, n_lines / 16, 16}));
-        std::vector<std::thread> team;
-        for (int w = 1; w < n_workers; ++w) team.emplace_back(parse_rows, w, n_workers);
-        parse_rows(0, n_workers);
-        for (auto& t : team) t.join();
+        if (n_workers > 1) reader_pool.run(n_workers, [&](int w, int) { parse_rows(w, n_workers); });
+        else parse_rows(0, 1);
         for (int i = 0; i < n_lines; ++i)
           if (!row_err[i].empty()) throw std::runtime_error(row_err[i]);   // the first bad row, in file order
         ms_reader += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_r0).count();
@@ -786,6 +847,7 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
 
   // ---- scorer -----------------------------------------------------------------------------------------------
   std::thread scorer([&] {
+    std::vector<uint32_t> words;   // the generator's raw outputs for one batch, in file order
     for (int bi = 0;; ++bi) {
       {
         std::unique_lock<std::mutex> lk(m);
@@ -794,6 +856,7 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
       }
       PipeBatch& b = ring[bi % kRing];
       const std::size_t B = b.rows.size();
+      b.device_sampled = false;
       if (B && b.err.empty()) {
         b.ll.resize(B);
         b.xe.resize(B * (std::size_t)d.n_sites);
@@ -816,8 +879,34 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
         lh_outputs_t o{b.xe.data(), b.fv.data(), b.fvd.data(), b.fd.data(), b.fdj.data(), b.fj.data(),
                        b.gs.data(), b.vds.data(), b.djs.data(), nullptr};
         const auto t_s0 = std::chrono::steady_clock::now();
-        const int rc = dev_group_ ? lh_group_score_newick(dev_group_, &nb, b.ll.data(), &o)
-                                  : lh_score_newick(dev_family_, &nb, b.ll.data(), &o);
+        int rc;
+        b.device_sampled = false;
+        if (dev_sampler) {
+          b.rng_start = run_gen;
+          rc = lh_score_newick(dev_family_, &nb, b.ll.data(), nullptr);
+          if (!rc) {
+            lh_timings_t tm;
+            bool ok = lh_get_timings(dev_family_, &tm) == 0 && tm.newick_host_trees == 0;   // (else the tables are a sub-batch's)
+            if (ok) {
+              words.resize(B * words_per_row);
+              for (uint32_t& w : words) w = (uint32_t)run_gen();
+              b.idx.resize(B * (std::size_t)n_idx);
+              b.sflag.resize(B);
+              ok = lh_sample_paths(dev_family_, (int32_t)B, words.data(), (int32_t)words_per_row, b.idx.data(), n_idx,
+                                   b.sflag.data()) == 0;
+              for (std::size_t i = 0; ok && i < B; ++i) ok = b.sflag[i] == 0;
+            } else {
+              run_gen.discard(words_per_row * B);
+            }
+            b.device_sampled = ok;
+            // (a batch the device leaves to the host - a non-finite forward entry somewhere - is scored once more
+            // with the tables fetched; the host sampler starts from rng_start and uses the same outputs)
+            if (!ok) rc = lh_score_newick(dev_family_, &nb, b.ll.data(), &o);
+          }
+        } else {
+          rc = dev_group_ ? lh_group_score_newick(dev_group_, &nb, b.ll.data(), &o)
+                          : lh_score_newick(dev_family_, &nb, b.ll.data(), &o);
+        }
         ms_scorer += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_s0).count();
         if (rc) {
           b.err = dev_group_ ? lh_group_last_error() : lh_last_error();
@@ -832,9 +921,9 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
   std::string failure;
   bool failure_is_input = false, first = true;
   const unsigned long long per_row = rng_outputs_per_row(d);
-  const int sampler_threads = std::max(1, std::min(hw / 2, 16));
   std::vector<std::unique_ptr<SamplerClone>> clones;
   int last_clone = -1, last_batch = -1;   // where the last row's sampled state lives when a clone sampled it
+  bool last_on_device = false;            // ... and its forward tables never came to the host
   try {
     for (int bi = 0;; ++bi) {
       {
@@ -853,7 +942,44 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
       // ---- the rows of the batch on several threads (see SamplerClone); the lines are written in file order ----
       bool sampled = false;
       const int n_blocks = std::min(sampler_threads, B / 32);
-      if (n_blocks >= 2 && per_row > 0) {
+      if (b.device_sampled) {
+        // the states are drawn (k_sample): what is left per row is the annotation's strings and the output line
+        const int nb = std::max(1, n_blocks);
+        while ((int)clones.size() < nb) clones.emplace_back(new SamplerClone(*this));
+        std::vector<std::string> text(nb);
+        const int per_block = (B + nb - 1) / nb;
+        auto write_block = [&](int t) {
+          const int lo = std::min(B, t * per_block), hi = std::min(B, lo + per_block);
+          SamplerClone& c = *clones[t];
+          std::ostringstream os;
+          for (int i = lo; i < hi; ++i) {
+            const PipeRow& r = b.rows[i];
+            const std::string naive = c.ApplySampledPath(&b.idx[(std::size_t)i * n_idx]);
+            const std::string exported = r.exported.empty() ? ExportNewick(r.tree) : r.exported;
+            const LineFields f{r.iteration, r.rb, r.prior, r.alpha, r.er, r.pi, &b.rates[(std::size_t)i * num_rates], 6, 4, num_rates,
+                               &exported, b.ll[i], b.ll[i] - r.rb, &naive};
+            write_output_line(os, f, c);
+          }
+          text[t] = os.str();
+        };
+        if (nb > 1) writer_pool.run(nb, [&](int t, int) { write_block(t); });
+        else write_block(0);
+        if (first) {
+          er_.assign(b.rows[0].er, b.rows[0].er + 6);
+          pi_.assign(b.rows[0].pi, b.rows[0].pi + 4);
+          WriteOutputHeaders(outfile);
+          first = false;
+        }
+        for (const std::string& block : text) outfile << block;
+        // (which clone holds the last row's annotation: the last block that is not empty)
+        last_clone = std::min(nb - 1, (B - 1) / per_block);
+        last_batch = bi % kRing;
+        last_on_device = true;
+        sampled = true;
+      } else if (dev_sampler) {
+        rng_ = b.rng_start;   // the host sampler below draws this batch's rows from where the generator stood
+      }
+      if (!sampled && n_blocks >= 2 && per_row > 0) {
         while ((int)clones.size() < n_blocks) clones.emplace_back(new SamplerClone(*this));
         std::vector<std::string> text(n_blocks);
         std::vector<std::mt19937> start(n_blocks + 1, rng_), finish(n_blocks, rng_);
@@ -876,10 +1002,7 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
           finish[t] = c.rng();
           text[t] = os.str();
         };
-        std::vector<std::thread> team;
-        for (int t = 1; t < n_blocks; ++t) team.emplace_back(sample_block, t);
-        sample_block(0);
-        for (auto& th : team) th.join();
+        writer_pool.run(n_blocks, [&](int t, int) { sample_block(t); });
         start[n_blocks].discard(per_row * (unsigned long long)B);
         sampled = true;
         for (int t = 0; t < n_blocks; ++t) sampled = sampled && finish[t] == start[t + 1];
@@ -894,10 +1017,14 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
           rng_ = finish[n_blocks - 1];
           last_clone = n_blocks - 1;
           last_batch = bi % kRing;
+          last_on_device = false;
         }
       }
       if (!sampled) {
-        if (B) last_clone = -1;
+        if (B) {
+          last_clone = -1;
+          last_on_device = false;
+        }
         for (int i = 0; i < B; ++i) {
           const PipeRow& r = b.rows[i];
           iteration_ = r.iteration;
@@ -982,7 +1109,16 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
     logweight_ = lh_loglikelihood_ - rb_loglikelihood_;
     naive_sequence_ = naive_seq_samp_;
     cache_forward_ = false;
+    if (last_on_device) {
+      // the row's forward tables stayed on the device: score it once more as the current sample to have them (and
+      // the emission and scaler counts) in the object, as the reference's object has them after its last row
+      tree_ = r.tree;
+      const double ll = b.ll[i];
+      ScoreCurrentSample();
+      loglik_cached_ = lh_loglikelihood_ = ll;
+    }
   }
+  if (dev_sampler) rng_ = run_gen;   // the generator stands where the serial walk would have left it
   tree_.clear();
   tree_export_cache_.clear();
   outfile.close();

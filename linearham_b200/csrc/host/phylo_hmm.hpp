@@ -81,6 +81,9 @@ class HMM {
 
   virtual double LogLikelihood() = 0;
   std::string SampleNaiveSequence();
+  // the same for a path whose states were drawn on the device (lh_sample_paths): no forward table is read, no random
+  // number drawn; idx as that call lays it out
+  std::string ApplySampledPath(const int32_t* idx);
 
   // ---- accessors (names as in src/HMM.hpp:197-409) ------------------------------------------
   const std::string& locus() const { return locus_; }
@@ -164,7 +167,8 @@ class HMM {
   void InitializeMsa();
   void InitializeStateSpace();
   void InitializeTransition();
-  void SampleInitialState();
+  void SampleInitialState(const int32_t* preset = nullptr);
+  std::string SamplePath(const int32_t* idx);
 };
 
 class PhyloHMM : public HMM {
@@ -202,6 +206,8 @@ class PhyloHMM : public HMM {
   lh_family* device_family() { EnsureDeviceFamily(); return dev_family_; }
   // host threads for Newick ingest and traversal planning (0 = all hardware threads)
   void set_host_threads(int n);
+  // RunPipeline: draw the annotations' states on the device (default) or with the host sampler
+  void set_device_sampler(bool on) { device_sampler_ = on; }
 
   const MatrixXi& xmsa() const { return xmsa_; }
   const std::vector<std::string>& xmsa_labels() const { return xmsa_labels_; }
@@ -260,6 +266,7 @@ class PhyloHMM : public HMM {
   lh_group* dev_group_ = nullptr;
   std::vector<int> devices_{0};
   int host_threads_ = 0;
+  bool device_sampler_ = true;
 };
 
 typedef std::shared_ptr<PhyloHMM> PhyloHMMPtr;

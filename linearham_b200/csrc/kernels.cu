@@ -1080,6 +1080,144 @@ void launch_hmm(const FamilyDev& f, const BatchDev& b, const HmmOut& o, int tree
   k_hmm<<<blocks, warps * 32, smem, s>>>(f, b, o, tree0, ntrees);
 }
 
+// ----------------------------------------------------------------- k_sample ---
+// The random draws of HMM::SampleNaiveSequence (src/HMM.cpp:323-341, 1222-1353) for every tree of a scored batch,
+// from the forward tables k_hmm left on the device: the J gene from jgerm_forward, then backwards through the D-J
+// junction sites, the D gene, the V-D junction sites and the V gene, every draw a std::discrete_distribution over
+// (transition column of the state drawn before) x (forward row). What the reference's standard library computes is
+// reproduced operation by operation (libstdc++ bits/random.tcc): the weights summed left to right from 0.0, every
+// weight divided by the sum, a running sum of those with the last entry forced to 1.0, u from
+// generate_canonical<double, 53> = (x0 + x1 * 2^32) / 2^64 over two raw outputs of the generator (nextafter(1, 0) if
+// that rounds to 1), and std::lower_bound = the first entry not below u. The raw std::mt19937 outputs come from the
+// host, which advances the one generator of the run in file order (a fixed number of outputs per row, see
+// rng_outputs_per_row in host/phylo_hmm.cpp); the strings of the annotation are put together there from the indices.
+// The transition matrices are CSC (rows ascending) where the host multiplies dense columns: a zero entry adds 0.0 to
+// the sum and leaves the running sum where it is, so the arithmetic is the same - as long as the forward row is
+// finite. A row with a non-finite entry (0 x inf = NaN in the dense product) or a sum that is not a positive finite
+// number is flagged and its batch is sampled by the host code instead.
+// One warp per tree: the lanes form the weights of a draw in shared memory, lane 0 does the sequential sums.
+struct SampleDev {
+  const double *fv, *fvd, *fd, *fdj, *fj;   // forward tables of the batch (k_hmm's layout)
+  const uint32_t* words;                    // [B][n_words] raw generator outputs, in draw order
+  int32_t n_words;
+  int32_t* idx;                             // [B][n_idx]: J gene | D-J states, site 0 first | D gene | V-D states | V gene
+  int32_t n_idx;
+  uint8_t* flag;                            // [B] 1: leave the tree to the host sampler
+};
+
+__device__ __forceinline__ double canonical_u(uint32_t x0, uint32_t x1) {
+  const double sum = __dadd_rn((double)x0, __dmul_rn((double)x1, 4294967296.0));
+  const double u = __dmul_rn(sum, 0x1p-64);
+  return u >= 1.0 ? 0x1.fffffffffffffp-1 : u;
+}
+
+// one draw over n states with weights w[j] = (m ? m(j, col) : 1) * fwd[j * fstride]; returns the index to every lane
+__device__ int sample_draw(const CscDev* m, int col, const double* __restrict__ fwd, int fstride, int n,
+                           double* sw, int* sr, const uint32_t*& words, bool& bad, int lane) {
+  if (n < 2) return 0;   // discrete_distribution keeps no weights then and draws nothing
+  bool nonfinite = false;
+  for (int j = lane; j < n; j += 32) nonfinite |= !(fabs(fwd[(size_t)j * fstride]) <= DBL_MAX);
+  int cnt;
+  if (m) {
+    const int p0 = m->colptr[col];
+    cnt = m->colptr[col + 1] - p0;
+    for (int p = lane; p < cnt; p += 32) {
+      const double2 en = __ldg(m->ent + p0 + p);
+      const int row = __double2loint(en.y);
+      sw[p] = __dmul_rn(en.x, fwd[(size_t)row * fstride]);
+      sr[p] = row;
+    }
+  } else {
+    cnt = n;
+    for (int p = lane; p < n; p += 32) {
+      sw[p] = fwd[(size_t)p * fstride];
+      sr[p] = p;
+    }
+  }
+  if (__any_sync(0xffffffffu, nonfinite)) bad = true;
+  __syncwarp();
+  int k = n - 1;
+  if (lane == 0) {
+    double sum = 0.0;
+    for (int p = 0; p < cnt; ++p) sum = __dadd_rn(sum, sw[p]);
+    if (!(sum > 0.0) || !(sum <= DBL_MAX)) {
+      bad = true;
+    } else {
+      const double u = canonical_u(words[0], words[1]);
+      if (u == 0.0) {
+        k = 0;
+      } else {
+        double cp = 0.0;
+        for (int p = 0; p < cnt; ++p) {
+          cp = __dadd_rn(cp, __ddiv_rn(sw[p], sum));
+          const double c = sr[p] == n - 1 ? 1.0 : cp;
+          if (!(c < u)) {
+            k = sr[p];
+            break;
+          }
+        }
+      }
+    }
+  }
+  words += 2;
+  bad = __shfl_sync(0xffffffffu, (int)bad, 0) != 0 || bad;
+  k = __shfl_sync(0xffffffffu, k, 0);
+  __syncwarp();
+  return k;
+}
+
+__global__ void __launch_bounds__(128) k_sample(FamilyDev f, SampleDev sd, int ntrees) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warps = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cap = max(max(f.s_max, f.g_max), 2);
+  double* sw = reinterpret_cast<double*>(smem_raw) + (size_t)wid * cap;
+  int* sr = reinterpret_cast<int*>(reinterpret_cast<double*>(smem_raw) + (size_t)warps * cap) + (size_t)wid * cap;
+  for (int t = blockIdx.x * warps + wid; t < ntrees; t += gridDim.x * warps) {
+    const uint32_t* words = sd.words + (size_t)t * sd.n_words;
+    int32_t* idx = sd.idx + (size_t)t * sd.n_idx;
+    bool bad = false;
+    int at = 0;
+    // the J gene (SampleInitialState)
+    int germ = sample_draw(nullptr, 0, sd.fj + (size_t)t * f.n_j, 1, f.n_j, sw, sr, words, bad, lane);
+    if (lane == 0) idx[at] = germ;
+    ++at;
+    // junctions backwards from the gene to their right, then the gene to their left (SampleJunctionStates,
+    // SampleGermlineState); light chains have one junction and no D gene
+    for (int pass = f.has_d ? 0 : 1; pass < 2; ++pass) {
+      const bool dj = pass == 0;
+      const int L = dj ? f.dj_sites : f.vd_sites, Sj = dj ? f.dj_states : f.vd_states;
+      const double* fw = dj ? sd.fdj + (size_t)t * L * Sj : sd.fvd + (size_t)t * L * Sj;
+      const CscDev& t_out = dj ? f.t_dj_j : f.t_vd_d;   // junction -> the gene to its right
+      const CscDev& t_jj = dj ? f.t_dj : f.t_vd;
+      int prev = germ;
+      for (int i = L - 1; i >= 0; --i) {
+        prev = sample_draw(i == L - 1 ? &t_out : &t_jj, prev, fw + i, L, Sj, sw, sr, words, bad, lane);
+        if (lane == 0) idx[at + i] = prev;
+      }
+      at += L;
+      // the gene to the left of the junction, given the junction's first state
+      const int n_g = dj ? f.n_d : f.n_v;
+      const double* fg = dj ? sd.fd + (size_t)t * n_g : sd.fv + (size_t)t * n_g;
+      germ = sample_draw(dj ? &f.t_d_dj : &f.t_v_vd, prev, fg, 1, n_g, sw, sr, words, bad, lane);
+      if (lane == 0) idx[at] = germ;
+      ++at;
+    }
+    if (lane == 0) sd.flag[t] = bad ? 1 : 0;
+  }
+}
+
+void launch_sample(const FamilyDev& f, const double* fv, const double* fvd, const double* fd, const double* fdj,
+                   const double* fj, const uint32_t* words, int n_words, int32_t* idx, int n_idx, uint8_t* flag,
+                   int ntrees, cudaStream_t s) {
+  const int warps = 4;
+  const int cap = std::max(std::max(f.s_max, f.g_max), 2);
+  const size_t smem = (size_t)warps * cap * (sizeof(double) + sizeof(int));
+  ensure_dynamic_smem(reinterpret_cast<const void*>(&k_sample), smem);
+  SampleDev sd{fv, fvd, fd, fdj, fj, words, n_words, idx, n_idx, flag};
+  int blocks = std::min((ntrees + warps - 1) / warps, 148 * 8);
+  k_sample<<<std::max(blocks, 1), warps * 32, smem, s>>>(f, sd, ntrees);
+}
+
 // ------------------------------------------------------------- diagnostics ---
 // Register-resident DFMA loop: the FP64 denominator for the on-chip pruning regime
 // (MEASURED_PEAKS.json has no FP64 entry). 8 independent chains per thread.

@@ -184,6 +184,11 @@ size_t hmm_smem_bytes(const FamilyDev& f, int warps);
 // launches the DFMA diagnostic kernel; returns the flop count of the launch
 double fp64_peak_flops_per_launch(double* scratch, int blocks, int iters, cudaStream_t s);
 
+// k_sample: the index draws of SampleNaiveSequence for every tree of a scored batch (forward tables on the device)
+void launch_sample(const FamilyDev& f, const double* fv, const double* fvd, const double* fd, const double* fdj,
+                   const double* fj, const uint32_t* words, int n_words, int32_t* idx, int n_idx, uint8_t* flag,
+                   int ntrees, cudaStream_t s);
+
 // asr.cu: ancestral-state sampling (lh_asr_sample); synchronous; *cache keeps its device pool between calls
 // (nullptr at first, released with asr_cache_free). 0, or 1 with *err set.
 void asr_cache_free(void* cache);

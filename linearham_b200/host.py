@@ -138,6 +138,10 @@ class PhyloHMM:
         arr = np.ascontiguousarray(devices, dtype=np.int32)
         _ck(self._lib.lhh_phylohmm_set_devices(self._h, arr.ctypes.data_as(_abi._i32p), len(arr)))
 
+    def set_device_sampler(self, on):
+        """RunPipeline: draw the annotations' states on the device (default) or with the host sampler."""
+        _ck(self._lib.lhh_phylohmm_set_device_sampler(self._h, int(bool(on))))
+
     def set_host_threads(self, n):
         """host threads for Newick ingest and traversal planning (0 = all hardware threads)"""
         _ck(self._lib.lhh_phylohmm_set_host_threads(self._h, int(n)))

@@ -13,7 +13,7 @@ rows = [{"newick": text[i], "er": tb["er"][i], "pi": tb["pi"][i], "alpha": float
 tsv = os.path.join(d, "trace.tsv"); synth.write_tsv(tsv, rows)
 out = os.path.join(d, "out.tsv")
 ref_text = None
-for bs in (1024, 512, 256, 4096):
+for bs in (256, 1024):
     ph = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
     ph.RunPipeline(tsv, out, 4, bs)
     first = open(out).read()

@@ -202,6 +202,7 @@ def test_run_pipeline_parallel_sampler_equals_the_serial_walk(tiny):
         tout = os.path.join(d, f"out300_{threads}_{batch}.trees")
         h = host.PhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
         h.set_host_threads(threads)
+        h.set_device_sampler(False)
         h.RunPipeline(tin, tout, int(z["num_rates"]), batch_size=batch)
         draws.append([h.SampleNaiveSequence() for _ in range(3)])   # continues the generator where the run left it
         h.close()
@@ -209,3 +210,48 @@ def test_run_pipeline_parallel_sampler_equals_the_serial_walk(tiny):
     assert outs[0].count("\n") == 301
     assert outs[1] == outs[0] and outs[2] == outs[0]
     assert draws[1] == draws[0] and draws[2] == draws[0]
+
+
+def _pipeline_runs(yaml_path, hmm_dir, tin, d, num_rates, configs):
+    outs, draws, lls = [], [], []
+    for k, (device_sampler, threads, batch) in enumerate(configs):
+        tout = os.path.join(d, f"out_ds_{k}.trees")
+        h = host.PhyloHMM(yaml_path, 0, hmm_dir, 0)
+        h.set_host_threads(threads)
+        h.set_device_sampler(device_sampler)
+        h.RunPipeline(tin, tout, num_rates, batch_size=batch)
+        lls.append(h.LogLikelihood())                               # the object holds the last row
+        draws.append([h.SampleNaiveSequence() for _ in range(3)])   # and the generator stands where the run left it
+        h.close()
+        outs.append(open(tout).read())
+    return outs, draws, lls
+
+
+def test_run_pipeline_device_sampler_equals_the_host_sampler(tiny):
+    """The states of every row's annotation drawn on the device (k_sample through lh_sample_paths: libstdc++'s
+    discrete_distribution and generate_canonical restated operation by operation, fed with the raw outputs of the
+    run's std::mt19937) against the host's SampleNaiveSequence: the same output file, the same object afterwards -
+    last row's likelihood, and the next draws, which need both the generator's state and the last row's forward
+    tables. Heavy chain (two junctions, D gene) and light chain (one junction)."""
+    import numpy as np
+    from linearham_b200 import synth
+    z, ff, d = tiny
+    samples = synth.tree_samples(np.random.default_rng(78), ff["tree"], 700, outgroup="naive")
+    tin = os.path.join(d, "in700.trees")
+    synth.write_tsv(tin, samples)
+    configs = ((False, 1, 128), (True, 0, 256), (True, 1, 64), (True, 0, 1024), (True, 0, 1))
+    outs, draws, lls = _pipeline_runs(ff["yaml_path"], ff["hmm_dir"], tin, d, int(z["num_rates"]), configs)
+    assert outs[0].count("\n") == 701
+    for k in range(1, len(configs)):
+        assert outs[k] == outs[0], configs[k]
+        assert draws[k] == draws[0] and lls[k] == lls[0], configs[k]
+    # light chain
+    dk = os.path.join(d, "igk")
+    os.makedirs(dk, exist_ok=True)
+    genes = synth.make_germline_set(os.path.join(dk, "hmmk"), seed=9, locus="igk")
+    fam = synth.make_light_family(dk, genes, 30, seed=1305, name="fam_igk")
+    samples = synth.tree_samples(np.random.default_rng(79), fam["tree"], 300, outgroup="naive")
+    tin = os.path.join(dk, "in300.trees")
+    synth.write_tsv(tin, samples)
+    outs, draws, lls = _pipeline_runs(fam["yaml_path"], os.path.join(dk, "hmmk"), tin, dk, 4, ((False, 1, 128), (True, 0, 128)))
+    assert outs[0].count("\n") == 301 and outs[1] == outs[0] and draws[1] == draws[0] and lls[1] == lls[0]
