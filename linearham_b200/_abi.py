@@ -243,6 +243,8 @@ def load_library(path=None):
     lib.lh_debug_fetch_plan.argtypes = [C.c_void_p, _i32p, _f64p]
     lib.lh_family_rebind.argtypes = [C.c_void_p, C.POINTER(FamilyDesc)]
     lib.lh_family_set_labels.argtypes = [C.c_void_p, C.POINTER(C.c_char_p)]
+    lib.lh_sample_paths.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_uint32), C.c_int32, C.POINTER(C.c_int32), C.c_int32,
+                                    C.POINTER(C.c_uint8)]
     lib.lh_pin_host.argtypes = [C.c_void_p, C.c_size_t]
     lib.lh_unpin_host.argtypes = [C.c_void_p]
     lib.lh_asr_sample.argtypes = [C.c_void_p, C.POINTER(AsrBatch), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8), _f64p]

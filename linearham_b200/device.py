@@ -104,6 +104,17 @@ class Family:
                                      out["site_rate"].ctypes.data_as(u8p), srl))
         return out
 
+    def sample_paths(self, words):
+        """lh_sample_paths on the batch scored last (option keep_tables = 1, or read-outs requested):
+        words [B][n_words] uint32 raw generator outputs -> (idx [B][n_idx] int32, flags [B] uint8)."""
+        w = np.ascontiguousarray(words, dtype=np.uint32)
+        B, fam = w.shape[0], self.fam
+        n_idx = 2 + int(fam["vd_sites"]) + ((1 + int(fam["dj_sites"])) if int(fam["has_d"]) else 0)
+        idx, flags = np.zeros((B, n_idx), dtype=np.int32), np.zeros(B, dtype=np.uint8)
+        self._ck(lib().lh_sample_paths(self._h, B, w.ctypes.data_as(C.POINTER(C.c_uint32)), w.shape[1],
+                                       idx.ctypes.data_as(C.POINTER(C.c_int32)), n_idx, flags.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return idx, flags
+
     # Newick text in ------------------------------------------------------------
     def set_labels(self, labels):
         """xMSA row labels (row 0 = "naive") for the device Newick parser (lh_family_set_labels)."""
