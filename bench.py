@@ -13,7 +13,8 @@ IGH family, 400 nt, Gamma-4, batch 16384 trees sharded over the N GPUs).
               lh_batch_run per step); CUDA events on the library's stream, max over ranks
   e2e         trees/s through the class API a linearham user calls, PhyloHMM::ScoreSamples: NEWICK STRINGS
               + er/pi/alpha on the host in, log-likelihoods of the whole batch on rank 0's host out. The
-              text goes to the GPU and is parsed there (k_newick); H2D, Gamma rates (host threads), parse,
+              text lives in PINNED host memory (the contract's "inputs from pinned host memory"; --pageable-text
+              for ordinary memory), goes to the GPU and is parsed there (k_newick); H2D, Gamma rates (host threads), parse,
               planning, kernels, D2H and - at N > 1 - the NCCL gather are all inside the timed region. This is
               what the reference arm times (src/PhyloHMM.cpp:419-430: parse + Gamma + emission + forward).
   e2e_arrays  the same through lh_score_batch with pre-flattened operation arrays and pre-computed rates
@@ -22,6 +23,8 @@ IGH family, 400 nt, Gamma-4, batch 16384 trees sharded over the N GPUs).
               streaming-model HBM figure and the measured DRAM traffic beside it
   cpu_baseline  the reference's own C++ (oracle/_ref) on all host cores, bounded sample (N=1 only), plus a
               single-thread figure and the reference "as shipped" (-O0, SConstruct:266)
+  e2e_pipeline  (c3) rows/s of the product's real entry point, PhyloHMM::RunPipeline: trace TSV in, linearham TSV
+              out (scoring from the Newick text + the annotation's draws on the GPU), beside the reference's own
   c3, c5      the other single-box configurations, each with its own parity check (c5 = families sharded
               over the ranks through lh_repertoire_score)
   parity_vs_n1  (N > 1) rank 0 re-scores a slice of every rank's shard on its own GPU: bit-identical
