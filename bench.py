@@ -494,8 +494,8 @@ def bench_family(env, args, cfg_name, steps, warmup, full_record):
             ours.close()
             pipe = {"value": Bs * steps / pipe_s, "unit": "rows/s", "rows_per_run": Bs, "batch_size": PIPE_BATCH,
                     "tsv_bytes": os.path.getsize(tsv_all),
-                    "api": "PhyloHMM::RunPipeline (TSV in -> TSV out; reader thread | device scoring from Newick text | "
-                           "SampleNaiveSequence + output line in file order, overlapped)"}
+                    "api": "PhyloHMM::RunPipeline (TSV in -> TSV out; reader | device scoring from Newick text + the "
+                           "annotation's draws on the device (k_sample) | output lines in file order; the stages overlap)"}
             if want_cpu and po.have_ref():
                 ref = po.RefPhyloHMM(ff["yaml_path"], 0, ff["hmm_dir"], 0)
                 ref_out = os.path.join(workdir, "ref_out.tsv")
