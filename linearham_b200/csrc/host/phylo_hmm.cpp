@@ -67,6 +67,18 @@ std::string read_file(const std::string& path) {
 // one line of a tab-separated file with "" quoting (fast-cpp-csv-parser double_quote_escape<'\t','"'>)
 std::vector<std::string> split_tsv(const std::string& line) {
   std::vector<std::string> out;
+  // (a row without a quote or a carriage return - every row RevBayes writes - is cut at its tabs with memchr: the
+  // character loop below costs as much per 9 KB row as re-exporting its tree)
+  if (!std::memchr(line.data(), '"', line.size()) && !std::memchr(line.data(), '\r', line.size())) {
+    const char* p = line.data();
+    const char* const end = p + line.size();
+    for (;;) {
+      const char* tab = static_cast<const char*>(std::memchr(p, '\t', (std::size_t)(end - p)));
+      out.emplace_back(p, tab ? tab : end);
+      if (!tab) return out;
+      p = tab + 1;
+    }
+  }
   std::string cur;
   bool quoted = false;
   for (std::size_t i = 0; i < line.size(); ++i) {
@@ -785,7 +797,7 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
         auto parse_rows = [&](int w, int nw) {
           for (int i = w; i < n_lines; i += nw) {
             try {
-              const std::vector<std::string> f = split_tsv(lines[i]);
+              std::vector<std::string> f = split_tsv(lines[i]);
               if ((int)f.size() < (int)header.size()) throw std::runtime_error("too few columns in a row of " + input_path);
               PipeRow& r = b.rows[i];
               r.iteration = (int)to_double(f[col[0]], "Iteration");
@@ -794,7 +806,7 @@ void PhyloHMM::RunPipeline(const std::string& input_path, const std::string& out
               r.alpha = to_double(f[col[3]], "alpha");
               for (int k = 0; k < 6; ++k) r.er[k] = to_double(f[col[4 + k]], "er");
               for (int k = 0; k < 4; ++k) r.pi[k] = to_double(f[col[10 + k]], "pi");
-              r.tree = f[col[14]];
+              r.tree = std::move(f[col[14]]);
               // the exported tree text of the output line (pll_utree_export_newick of the parsed tree; text work
               // only). A string it cannot read is left to the device call, whose parser words the error.
               try {
