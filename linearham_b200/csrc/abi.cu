@@ -1320,8 +1320,9 @@ int stage_text_chunk(lh_family* f, const lh_newick_batch_t* nb, int ci, int c0, 
     }
     // (every row but the last is followed by another string, so `width` bytes of it lie inside the caller's buffer;
     // the last row is copied with its own length: the buffer may end right behind its NUL)
-    LH_CUDA(cudaMemcpy2DAsync(buf.as<char>(), dpitch, nb->newick[c0], (size_t)stride, width, (size_t)(cn - 1),
-                              cudaMemcpyHostToDevice, cs));
+    if (cn > 1)
+      LH_CUDA(cudaMemcpy2DAsync(buf.as<char>(), dpitch, nb->newick[c0], (size_t)stride, width, (size_t)(cn - 1),
+                                cudaMemcpyHostToDevice, cs));
     LH_CUDA(cudaMemcpyAsync(buf.as<char>() + (size_t)(cn - 1) * dpitch, nb->newick[c0 + cn - 1], (size_t)lens[cn - 1] + 1,
                             cudaMemcpyHostToDevice, cs));
     LH_CUDA(cudaMemcpyAsync(f->d_toffs.as<uint64_t>() + c0, offs, (size_t)cn * 8, cudaMemcpyHostToDevice, cs));
