@@ -1137,24 +1137,30 @@ __device__ int sample_draw(const CscDev* m, int col, const double* __restrict__ 
   if (__any_sync(0xffffffffu, nonfinite)) bad = true;
   __syncwarp();
   int k = n - 1;
+  // the sum is a chain (left to right, as std::accumulate adds), the quotients are not: the lanes divide in parallel
+  // and lane 0's second chain is additions only
+  double sum = 0.0;
   if (lane == 0) {
-    double sum = 0.0;
     for (int p = 0; p < cnt; ++p) sum = __dadd_rn(sum, sw[p]);
-    if (!(sum > 0.0) || !(sum <= DBL_MAX)) {
-      bad = true;
+    if (!(sum > 0.0) || !(sum <= DBL_MAX)) bad = true;
+  }
+  sum = __shfl_sync(0xffffffffu, sum, 0);
+  const bool sum_ok = __shfl_sync(0xffffffffu, (int)bad, 0) == 0;
+  if (sum_ok)
+    for (int p = lane; p < cnt; p += 32) sw[p] = __ddiv_rn(sw[p], sum);
+  __syncwarp();
+  if (lane == 0 && sum_ok) {
+    const double u = canonical_u(words[0], words[1]);
+    if (u == 0.0) {
+      k = 0;
     } else {
-      const double u = canonical_u(words[0], words[1]);
-      if (u == 0.0) {
-        k = 0;
-      } else {
-        double cp = 0.0;
-        for (int p = 0; p < cnt; ++p) {
-          cp = __dadd_rn(cp, __ddiv_rn(sw[p], sum));
-          const double c = sr[p] == n - 1 ? 1.0 : cp;
-          if (!(c < u)) {
-            k = sr[p];
-            break;
-          }
+      double cp = 0.0;
+      for (int p = 0; p < cnt; ++p) {
+        cp = __dadd_rn(cp, sw[p]);
+        const double c = sr[p] == n - 1 ? 1.0 : cp;
+        if (!(c < u)) {
+          k = sr[p];
+          break;
         }
       }
     }
